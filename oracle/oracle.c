@@ -1,0 +1,628 @@
+/* ORACLE — TEST INFRASTRUCTURE ONLY.
+ *
+ * Plain-C restatement of the reference's CPU algorithms on the hot path
+ * (batched L2 / inner-product distance evaluation + top-k candidate selection).
+ * It is the checker for the CUDA product in hnsw-nsg_b200/csrc; it is never
+ * linked into, loaded by, or called from the product library. Only tests/,
+ * __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
+ * may load liboracle.so.
+ *
+ * Pinning: every function below is checked in tests/test_oracle_pinning.py against
+ * (a) the reference's own known-answer vectors (hnswlib/tests/python/bindings_test_spaces.py:11-33,
+ *     hnswlib/tests/cpp/data/ (.bin files) -> tests/golden/), and
+ * (b) outputs of the UNMODIFIED reference sources compiled into the oracle/_ref/ shared objects
+ *     (oracle/Makefile, wrappers oracle/ref_*_capi.cpp) on identical seeded inputs.
+ *
+ * Flat graph layout shared with the product:
+ *   adjacency  u32 [n, gstride], row i = out-neighbours of i in list order, padded with ORC_INVALID.
+ *   vectors    f32 [n, stride], stride >= dim (padding, if any, is zero).
+ *
+ * Where the reference leaves an order unspecified (std::sort / std::priority_queue on equal
+ * distances) the oracle uses the total order (distance, id) ascending — documented per function.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define ORC_INVALID 0xFFFFFFFFu
+#define EXPORT __attribute__((visibility("default")))
+
+/* ------------------------------------------------------------------ distances */
+/* distance modes */
+enum {
+  ORC_L2_SCALAR = 0,     /* hnswlib L2Sqr, space_l2.h:6-20 (what -DNO_MANUAL_VECTORIZATION selects) */
+  ORC_IP_SCALAR = 1,     /* hnswlib InnerProductDistance = 1 - dot, space_ip.h:6-19 */
+  ORC_L2_HNSW_AVX = 2,   /* hnswlib L2Space dispatch with USE_AVX (no AVX-512), space_l2.h:208-253 */
+  ORC_IP_HNSW_AVX = 3,   /* hnswlib InnerProductSpace dispatch with USE_AVX, space_ip.h:342-398 */
+  ORC_L2_EFANNA_AVX = 4, /* efanna2e::DistanceL2::compare __AVX__ branch, CNNS/include/nsg/distance.h:25-74 */
+  ORC_L2_GPU = 5,        /* summation order of the CUDA kernels (team of lanes, fmaf, xor-butterfly) */
+  ORC_IP_GPU = 6,        /* 1 - dot in the CUDA kernels' order */
+  ORC_FASTL2_EFANNA_AVX = 7 /* ||x||^2 - 2<q,x>, DistanceFastL2, distance.h:232-322 (needs norm; see orc_fastl2) */
+};
+
+/* space_l2.h:6-20 — sequential, multiply then add (no FMA: built with -ffp-contract=off) */
+static float l2_scalar(const float *a, const float *b, size_t qty) {
+  float res = 0;
+  for (size_t i = 0; i < qty; i++) {
+    float t = a[i] - b[i];
+    res += t * t;
+  }
+  return res;
+}
+/* space_ip.h:6-14 */
+static float dot_scalar(const float *a, const float *b, size_t qty) {
+  float res = 0;
+  for (size_t i = 0; i < qty; i++) res += a[i] * b[i];
+  return res;
+}
+
+/* space_l2.h:60-91 L2SqrSIMD16ExtAVX: 8 lane accumulators, two 8-blocks per 16, lane sum in index order */
+static float l2_hnsw_avx16(const float *a, const float *b, size_t qty) {
+  float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  size_t q16 = (qty >> 4) << 4;
+  for (size_t i = 0; i < q16; i += 8)
+    for (int l = 0; l < 8; l++) {
+      float d = a[i + l] - b[i + l];
+      s[l] = s[l] + d * d;
+    }
+  return s[0] + s[1] + s[2] + s[3] + s[4] + s[5] + s[6] + s[7];
+}
+/* space_l2.h:165-189 L2SqrSIMD4Ext: 4 SSE lanes */
+static float l2_hnsw_sse4(const float *a, const float *b, size_t qty) {
+  float s[4] = {0, 0, 0, 0};
+  size_t q4 = (qty >> 2) << 2;
+  for (size_t i = 0; i < q4; i += 4)
+    for (int l = 0; l < 4; l++) {
+      float d = a[i + l] - b[i + l];
+      s[l] = s[l] + d * d;
+    }
+  return s[0] + s[1] + s[2] + s[3];
+}
+/* L2Space::L2Space dispatch, space_l2.h:214-241 (+ residual wrappers :149-160, :191-205) */
+static float l2_hnsw_avx(const float *a, const float *b, size_t dim) {
+  if (dim % 16 == 0) return l2_hnsw_avx16(a, b, dim);
+  if (dim % 4 == 0) return l2_hnsw_sse4(a, b, dim);
+  if (dim > 16) {
+    size_t q16 = dim >> 4 << 4;
+    float res = l2_hnsw_avx16(a, b, q16);
+    float tail = l2_scalar(a + q16, b + q16, dim - q16);
+    return res + tail;
+  }
+  if (dim > 4) {
+    size_t q4 = dim >> 2 << 2;
+    float res = l2_hnsw_sse4(a, b, q4);
+    float tail = l2_scalar(a + q4, b + q4, dim - q4);
+    return res + tail;
+  }
+  return l2_scalar(a, b, dim);
+}
+
+/* space_ip.h:24-69 InnerProductSIMD4ExtAVX: 8-lane blocks of 16, fold to 4 lanes, 4-wide tail */
+static float dot_hnsw_avx4(const float *a, const float *b, size_t qty) {
+  float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  size_t q16 = (qty / 16) * 16, q4 = (qty / 4) * 4;
+  size_t i = 0;
+  for (; i < q16; i += 8)
+    for (int l = 0; l < 8; l++) s[l] = s[l] + a[i + l] * b[i + l];
+  float p[4];
+  for (int l = 0; l < 4; l++) p[l] = s[l] + s[l + 4];
+  for (; i < q4; i += 4)
+    for (int l = 0; l < 4; l++) p[l] = p[l] + a[i + l] * b[i + l];
+  return p[0] + p[1] + p[2] + p[3];
+}
+/* space_ip.h InnerProductSIMD16ExtAVX (:210-245): 8 lanes, index-order lane sum */
+static float dot_hnsw_avx16(const float *a, const float *b, size_t qty) {
+  float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  size_t q16 = (qty / 16) * 16;
+  for (size_t i = 0; i < q16; i += 8)
+    for (int l = 0; l < 8; l++) s[l] = s[l] + a[i + l] * b[i + l];
+  return s[0] + s[1] + s[2] + s[3] + s[4] + s[5] + s[6] + s[7];
+}
+/* InnerProductSpace dispatch, space_ip.h:348-385 (+ residual wrappers :313-339) */
+static float ip_hnsw_avx(const float *a, const float *b, size_t dim) {
+  if (dim % 16 == 0) return 1.0f - dot_hnsw_avx16(a, b, dim);
+  if (dim % 4 == 0) return 1.0f - dot_hnsw_avx4(a, b, dim);
+  if (dim > 16) {
+    size_t q16 = dim >> 4 << 4;
+    float res = dot_hnsw_avx16(a, b, q16);
+    float tail = dot_scalar(a + q16, b + q16, dim - q16);
+    return 1.0f - (res + tail);
+  }
+  if (dim > 4) {
+    size_t q4 = dim >> 2 << 2;
+    float res = dot_hnsw_avx4(a, b, q4);
+    float tail = dot_scalar(a + q4, b + q4, dim - q4);
+    return 1.0f - (res + tail);
+  }
+  return 1.0f - dot_scalar(a, b, dim);
+}
+
+/* efanna2e::DistanceL2::compare, __AVX__ branch (CNNS/include/nsg/distance.h:29-56).
+ * D rounds dim up to x8 and the reference then reads past the row end unless the caller padded the
+ * rows with zeros (util.h data_align :33-67); the restatement treats elements >= dim as zero. */
+static float l2_efanna_avx(const float *a, const float *b, size_t size) {
+  float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  size_t D = (size + 7) & ~(size_t)7, DR = D % 16, DD = D - DR;
+  if (DR)
+    for (int l = 0; l < 8; l++) {
+      size_t i = DD + l;
+      float d = (i < size ? a[i] : 0.f) - (i < size ? b[i] : 0.f);
+      s[l] = s[l] + d * d;
+    }
+  for (size_t i = 0; i < DD; i += 8)
+    for (int l = 0; l < 8; l++) {
+      float d = a[i + l] - b[i + l];
+      s[l] = s[l] + d * d;
+    }
+  return s[0] + s[1] + s[2] + s[3] + s[4] + s[5] + s[6] + s[7];
+}
+/* efanna2e::DistanceInnerProduct::compare (__AVX__, distance.h:133-171) / DistanceFastL2::norm (:232-258):
+ * same lane structure as l2_efanna_avx with a product instead of a squared difference. */
+static float dot_efanna_avx(const float *a, const float *b, size_t size) {
+  float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  size_t D = (size + 7) & ~(size_t)7, DR = D % 16, DD = D - DR;
+  if (DR)
+    for (int l = 0; l < 8; l++) {
+      size_t i = DD + l;
+      s[l] = s[l] + (i < size ? a[i] : 0.f) * (i < size ? b[i] : 0.f);
+    }
+  for (size_t i = 0; i < DD; i += 8)
+    for (int l = 0; l < 8; l++) s[l] = s[l] + a[i + l] * b[i + l];
+  return s[0] + s[1] + s[2] + s[3] + s[4] + s[5] + s[6] + s[7];
+}
+
+/* Summation order of the CUDA kernels (hnsw-nsg_b200/csrc/dist.cuh): a row of nch = ceil(dim/4)
+ * float4 chunks is split over a team of `team` lanes; lane t owns chunks t, t+team, t+2*team, ...
+ * and accumulates x,y,z,w of each chunk in that order with fmaf; lane sums are combined with an
+ * xor butterfly (offsets team/2 ... 1). Not a reference function: it exists so that GPU-vs-oracle
+ * comparisons are bit-exact on arbitrary float data. */
+static int g_gpu_team = 8;
+static float gpu_order(const float *a, const float *b, size_t dim, int team, int ip) {
+  float lane[32];
+  size_t nch = (dim + 3) / 4;
+  for (int t = 0; t < team; t++) {
+    float acc = 0.f;
+    for (size_t c = t; c < nch; c += team)
+      for (int j = 0; j < 4; j++) {
+        size_t i = c * 4 + j;
+        float x = i < dim ? a[i] : 0.f, y = i < dim ? b[i] : 0.f;
+        if (ip) acc = fmaf(x, y, acc);
+        else { float d = x - y; acc = fmaf(d, d, acc); }
+      }
+    lane[t] = acc;
+  }
+  for (int off = team / 2; off >= 1; off >>= 1) {
+    float nxt[32];
+    for (int t = 0; t < team; t++) nxt[t] = lane[t] + lane[t ^ off];
+    memcpy(lane, nxt, sizeof(float) * team);
+  }
+  return ip ? 1.0f - lane[0] : lane[0];
+}
+
+EXPORT void orc_set_gpu_team(int team) { g_gpu_team = team; }
+
+EXPORT float orc_dist(int mode, const float *a, const float *b, size_t dim) {
+  switch (mode) {
+    case ORC_L2_SCALAR: return l2_scalar(a, b, dim);
+    case ORC_IP_SCALAR: return 1.0f - dot_scalar(a, b, dim);
+    case ORC_L2_HNSW_AVX: return l2_hnsw_avx(a, b, dim);
+    case ORC_IP_HNSW_AVX: return ip_hnsw_avx(a, b, dim);
+    case ORC_L2_EFANNA_AVX: return l2_efanna_avx(a, b, dim);
+    case ORC_L2_GPU: return gpu_order(a, b, dim, g_gpu_team, 0);
+    case ORC_IP_GPU: return gpu_order(a, b, dim, g_gpu_team, 1);
+    case ORC_FASTL2_EFANNA_AVX: /* distance.h:318-322 with norm = ||b||^2 (:232-258) */
+      return -2 * dot_efanna_avx(a, b, dim) + dot_efanna_avx(b, b, dim);
+  }
+  return NAN;
+}
+
+/* ------------------------------------------------------------------ brute-force kNN */
+/* hnswlib::BruteforceSearch::searchKnn (bruteforce.h:106-135) and IndexGraph::generate_control_set
+ * (efanna_graph/src/index_graph.cpp:138-153): exact scan, keep the k smallest. The reference heap is
+ * std::priority_queue<pair<dist,label>> (lexicographic), admits dist <= lastdist and pops the largest
+ * pair, so the survivors are the k smallest under (distance, id) and ties go to the smaller id.
+ * Output rows ascending by (distance, id) (searchKnnCloserFirst order, hnswlib.h:203-221);
+ * if n < k the tail is filled with ORC_INVALID / +inf. */
+typedef struct { float d; uint32_t id; } orc_pair;
+
+static int pair_less(orc_pair a, orc_pair b) { return a.d < b.d || (a.d == b.d && a.id < b.id); }
+static int pair_cmp(const void *x, const void *y) {
+  orc_pair a = *(const orc_pair *)x, b = *(const orc_pair *)y;
+  return pair_less(a, b) ? -1 : (pair_less(b, a) ? 1 : 0);
+}
+/* max-heap on (d,id) */
+static void heap_sift_down(orc_pair *h, size_t n, size_t i) {
+  for (;;) {
+    size_t l = 2 * i + 1, r = l + 1, m = i;
+    if (l < n && pair_less(h[m], h[l])) m = l;
+    if (r < n && pair_less(h[m], h[r])) m = r;
+    if (m == i) return;
+    orc_pair t = h[i]; h[i] = h[m]; h[m] = t; i = m;
+  }
+}
+static void heap_sift_up(orc_pair *h, size_t i) {
+  while (i > 0) {
+    size_t p = (i - 1) / 2;
+    if (!pair_less(h[p], h[i])) return;
+    orc_pair t = h[i]; h[i] = h[p]; h[p] = t; i = p;
+  }
+}
+
+EXPORT int orc_bf_knn(const float *base, size_t n, size_t dim, size_t stride, const float *q, size_t nq,
+                      size_t qstride, size_t k, int mode, uint32_t *ids, float *dists) {
+  if (k == 0) return 0;
+#pragma omp parallel
+  {
+    orc_pair *h = (orc_pair *)malloc(sizeof(orc_pair) * k);
+#pragma omp for schedule(dynamic, 4)
+    for (long qi = 0; qi < (long)nq; qi++) {
+      const float *qv = q + (size_t)qi * qstride;
+      size_t m = 0;
+      for (size_t i = 0; i < n; i++) {
+        orc_pair c = {orc_dist(mode, qv, base + i * stride, dim), (uint32_t)i};
+        if (m < k) { h[m] = c; heap_sift_up(h, m); m++; }
+        else if (pair_less(c, h[0])) { h[0] = c; heap_sift_down(h, m, 0); }
+      }
+      qsort(h, m, sizeof(orc_pair), pair_cmp);
+      for (size_t j = 0; j < k; j++) {
+        ids[(size_t)qi * k + j] = j < m ? h[j].id : ORC_INVALID;
+        dists[(size_t)qi * k + j] = j < m ? h[j].d : INFINITY;
+      }
+    }
+    free(h);
+  }
+  return 0;
+}
+
+/* ------------------------------------------------------------------ sorted pool (efanna Neighbor) */
+/* efanna2e::Neighbor (CNNS/include/nsg/neighbor.h:18-30) */
+typedef struct { uint32_t id; float distance; int flag; } orc_nb;
+
+/* efanna2e::InsertIntoPool (neighbor.h:107-135), statement for statement. addr has K+1 slots. */
+static int insert_into_pool(orc_nb *addr, unsigned K, orc_nb nn) {
+  int left = 0, right = (int)K - 1;
+  if (addr[left].distance > nn.distance) {
+    memmove(&addr[left + 1], &addr[left], K * sizeof(orc_nb));
+    addr[left] = nn;
+    return left;
+  }
+  if (addr[right].distance < nn.distance) {
+    addr[K] = nn;
+    return (int)K;
+  }
+  while (left < right - 1) {
+    int mid = (left + right) / 2;
+    if (addr[mid].distance > nn.distance) right = mid;
+    else left = mid;
+  }
+  while (left > 0) {
+    if (addr[left].distance < nn.distance) break;
+    if (addr[left].id == nn.id) return (int)K + 1;
+    left--;
+  }
+  if (addr[left].id == nn.id || addr[right].id == nn.id) return (int)K + 1;
+  memmove(&addr[right + 1], &addr[right], (K - right) * sizeof(orc_nb));
+  addr[right] = nn;
+  return right;
+}
+EXPORT int orc_insert_into_pool(uint32_t *ids, float *dist, int *flags, unsigned K, uint32_t id, float d) {
+  orc_nb *p = (orc_nb *)malloc(sizeof(orc_nb) * (K + 1));
+  for (unsigned i = 0; i < K; i++) { p[i].id = ids[i]; p[i].distance = dist[i]; p[i].flag = flags[i]; }
+  p[K].id = ORC_INVALID; p[K].distance = INFINITY; p[K].flag = 0;
+  orc_nb nn = {id, d, 1};
+  int r = insert_into_pool(p, K, nn);
+  for (unsigned i = 0; i <= K; i++) { ids[i] = p[i].id; dist[i] = p[i].distance; flags[i] = p[i].flag; }
+  free(p);
+  return r;
+}
+
+/* std::sort(Neighbor) compares distance only (neighbor.h:26-28) and is unstable; the oracle orders
+ * equal distances by id. */
+static int nb_cmp(const void *x, const void *y) {
+  const orc_nb *a = (const orc_nb *)x, *b = (const orc_nb *)y;
+  if (a->distance < b->distance) return -1;
+  if (a->distance > b->distance) return 1;
+  return a->id < b->id ? -1 : (a->id > b->id ? 1 : 0);
+}
+
+/* random ids for seed fill. rng_mode 0: libc rand() exactly where the reference calls it
+ * (index_nsg.cpp:523). rng_mode 1: the product's counter hash (csrc/search.cu seed_hash): stateless,
+ * so batched/parallel execution is reproducible. */
+static uint32_t mix32(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
+  return x;
+}
+EXPORT uint32_t orc_seed_hash(uint32_t seed, uint32_t query, uint32_t counter) {
+  return mix32(mix32(seed ^ (query * 0x9E3779B9U)) + counter * 0x85EBCA6BU);
+}
+
+static unsigned row_degree(const uint32_t *row, unsigned gstride) {
+  unsigned d = 0;
+  while (d < gstride && row[d] != ORC_INVALID) d++;
+  return d;
+}
+
+/* ------------------------------------------------------------------ NSG beam search */
+/* Core of IndexNSG::Search (CNNS/src/nsg/index_nsg.cpp:506-568) and IndexNSG::get_neighbors
+ * (:218-285): seeds = first L out-neighbours of ep, random fill up to L, sorted pool of L,
+ * expand the first unexpanded entry, InsertIntoPool, k/nk rewind. When `full` is non-NULL every
+ * evaluated node is appended to it (get_neighbors' `fullset`, :250,:273) and `flags` is the
+ * caller's visited array (Link shares it with sync_prune, :447-448). stats[0] += distance
+ * evaluations, stats[1] += expanded nodes. Returns the pool length (L). */
+typedef struct { orc_nb *v; size_t n, cap; } nb_vec;
+static void nbv_push(nb_vec *v, orc_nb x) {
+  if (v->n == v->cap) { v->cap = v->cap ? v->cap * 2 : 1024; v->v = (orc_nb *)realloc(v->v, v->cap * sizeof(orc_nb)); }
+  v->v[v->n++] = x;
+}
+
+typedef struct {
+  const float *data; size_t n, dim, stride;
+  const uint32_t *graph; unsigned gstride;
+  int mode;
+} orc_index;
+
+static unsigned nsg_beam(const orc_index *ix, uint32_t ep, const float *query, unsigned L_in, int rng_mode,
+                         uint32_t seed, uint32_t qidx, uint8_t *flags, orc_nb *retset, nb_vec *full,
+                         uint64_t *stats) {
+  unsigned L = 0;
+  uint32_t *init_ids = (uint32_t *)malloc(sizeof(uint32_t) * (L_in ? L_in : 1));
+  const uint32_t *eprow = ix->graph + (size_t)ep * ix->gstride;
+  unsigned epdeg = row_degree(eprow, ix->gstride);
+  for (unsigned i = 0; i < L_in && i < epdeg; i++) { /* :516-519 / :229-233 */
+    init_ids[i] = eprow[i];
+    flags[init_ids[i]] = 1;
+    L++;
+  }
+  uint32_t ctr = 0;
+  while (L < L_in) { /* :521-527 / :234-240 */
+    uint32_t id = rng_mode == 0 ? (uint32_t)rand() % (uint32_t)ix->n
+                                : orc_seed_hash(seed, qidx, ctr++) % (uint32_t)ix->n;
+    if (flags[id]) continue;
+    init_ids[L] = id;
+    L++;
+    flags[id] = 1;
+  }
+  for (unsigned i = 0; i < L_in; i++) { /* :530-536 / :243-253 */
+    uint32_t id = init_ids[i];
+    float d = orc_dist(ix->mode, ix->data + ix->stride * (size_t)id, query, ix->dim);
+    retset[i].id = id; retset[i].distance = d; retset[i].flag = 1;
+    if (full) nbv_push(full, retset[i]);
+    if (stats) stats[0]++;
+  }
+  free(init_ids);
+  L = L_in;
+  qsort(retset, L, sizeof(orc_nb), nb_cmp); /* :538 */
+  int k = 0;
+  while (k < (int)L) { /* :539-564 */
+    int nk = (int)L;
+    if (retset[k].flag) {
+      retset[k].flag = 0;
+      uint32_t n = retset[k].id;
+      const uint32_t *row = ix->graph + (size_t)n * ix->gstride;
+      if (stats) stats[1]++;
+      for (unsigned m = 0; m < ix->gstride && row[m] != ORC_INVALID; ++m) {
+        uint32_t id = row[m];
+        if (flags[id]) continue;
+        flags[id] = 1;
+        float d = orc_dist(ix->mode, query, ix->data + ix->stride * (size_t)id, ix->dim);
+        if (stats) stats[0]++;
+        orc_nb nn = {id, d, 1};
+        if (full) nbv_push(full, nn);
+        if (d >= retset[L - 1].distance) continue;
+        int r = insert_into_pool(retset, L, nn);
+        if (r < nk) nk = r;
+      }
+    }
+    if (nk <= k) k = nk; else ++k;
+  }
+  return L;
+}
+
+/* IndexNSG::Search batched over queries (the reference loops / omp-parallelises outside, e.g.
+ * CNNS/tests/cluster_hnsw_nsg_search.cpp:138,207). ids [nq,K]; dists [nq,K] (the reference returns
+ * ids only — distances are an extra output, NULL allowed); stats [nq,2] = {n_dist, n_hops} or NULL.
+ * rng_mode 0 consumes libc rand() query by query, single-threaded, like the reference under srand(). */
+EXPORT int orc_nsg_search(const float *data, size_t n, size_t dim, size_t stride, const uint32_t *graph,
+                          unsigned gstride, uint32_t ep, const float *q, size_t nq, size_t qstride, unsigned K,
+                          unsigned L, int mode, int rng_mode, uint32_t seed, uint32_t *ids, float *dists,
+                          uint64_t *stats) {
+  if (L < K || L == 0 || L > n) return -1;
+  orc_index ix = {data, n, dim, stride, graph, gstride, mode};
+  if (stats) memset(stats, 0, sizeof(uint64_t) * 2 * nq);
+#pragma omp parallel if (rng_mode != 0)
+  {
+    uint8_t *flags = (uint8_t *)malloc(n);
+    orc_nb *retset = (orc_nb *)malloc(sizeof(orc_nb) * (L + 1));
+#pragma omp for schedule(dynamic, 8)
+    for (long qi = 0; qi < (long)nq; qi++) {
+      memset(flags, 0, n);
+      nsg_beam(&ix, ep, q + (size_t)qi * qstride, L, rng_mode, seed, (uint32_t)qi, flags, retset, NULL,
+               stats ? stats + 2 * qi : NULL);
+      for (unsigned i = 0; i < K; i++) { /* :565-567 */
+        ids[(size_t)qi * K + i] = retset[i].id;
+        if (dists) dists[(size_t)qi * K + i] = retset[i].distance;
+      }
+    }
+    free(flags); free(retset);
+  }
+  return 0;
+}
+
+/* ------------------------------------------------------------------ HNSW search */
+/* Flat HNSW layout (product device layout, built from hnswlib's saveIndex blob by the host shim):
+ *   links0      u32 [n, maxM0]   level-0 lists (hnswalg.h get_linklist0 :486), INVALID padded
+ *   levels      i32 [n]          element_levels_ (:63)
+ *   upper_ptr   u32 [n]          first row of node i in upper_links (valid when levels[i] > 0)
+ *   upper_links u32 [rows, maxM] row upper_ptr[i] + (l-1) = list of node i at level l>=1 (:496)
+ *   labels      u64 [n]          external labels (getExternalLabel :185-189)
+ */
+typedef struct {
+  const float *data; size_t n, dim, stride;
+  const uint32_t *links0; unsigned maxM0;
+  const int32_t *levels; const uint32_t *upper_ptr; const uint32_t *upper_links; unsigned maxM;
+  uint32_t ep; int maxlevel; int mode;
+} orc_hnsw;
+
+/* generic binary heap on (d,id); sign=+1 max-heap (top_candidates), sign=-1 min-heap (candidate_set).
+ * The reference uses CompareByFirst (hnswalg.h:68-73), i.e. leaves ties to the heap implementation;
+ * the oracle breaks them by id. */
+static int hless(orc_pair a, orc_pair b, int sign) { return sign > 0 ? pair_less(a, b) : pair_less(b, a); }
+static void hpush(orc_pair *h, size_t *n, orc_pair x, int sign) {
+  size_t i = (*n)++;
+  h[i] = x;
+  while (i > 0) {
+    size_t p = (i - 1) / 2;
+    if (!hless(h[p], h[i], sign)) break;
+    orc_pair t = h[i]; h[i] = h[p]; h[p] = t; i = p;
+  }
+}
+static void hpop(orc_pair *h, size_t *n, int sign) {
+  h[0] = h[--(*n)];
+  size_t i = 0, m = *n;
+  for (;;) {
+    size_t l = 2 * i + 1, r = l + 1, b = i;
+    if (l < m && hless(h[b], h[l], sign)) b = l;
+    if (r < m && hless(h[b], h[r], sign)) b = r;
+    if (b == i) break;
+    orc_pair t = h[i]; h[i] = h[b]; h[b] = t; i = b;
+  }
+}
+
+/* upper-layer greedy descent, HierarchicalNSW::searchKnn (hnswalg.h:1275-1303) */
+static uint32_t hnsw_descend(const orc_hnsw *ix, const float *q, float *curdist_out, uint64_t *stats) {
+  uint32_t cur = ix->ep;
+  float curdist = orc_dist(ix->mode, q, ix->data + ix->stride * (size_t)cur, ix->dim);
+  if (stats) stats[0]++;
+  for (int level = ix->maxlevel; level > 0; level--) {
+    int changed = 1;
+    while (changed) {
+      changed = 0;
+      const uint32_t *row = ix->upper_links + ((size_t)ix->upper_ptr[cur] + (level - 1)) * ix->maxM;
+      if (stats) stats[1]++;
+      for (unsigned i = 0; i < ix->maxM && row[i] != ORC_INVALID; i++) {
+        uint32_t cand = row[i];
+        float d = orc_dist(ix->mode, q, ix->data + ix->stride * (size_t)cand, ix->dim);
+        if (stats) stats[0]++;
+        if (d < curdist) { curdist = d; cur = cand; changed = 1; }
+      }
+    }
+  }
+  *curdist_out = curdist;
+  return cur;
+}
+
+/* searchBaseLayerST<bare_bone=true> (hnswalg.h:309-440), two heaps exactly as the reference.
+ * out: up to ef pairs, ascending (d,id). returns count. */
+static size_t hnsw_base_twoheap(const orc_hnsw *ix, uint32_t ep, const float *q, size_t ef, uint8_t *visited,
+                                orc_pair *top, orc_pair *cand, size_t cand_cap, uint64_t *stats) {
+  size_t nt = 0, nc = 0;
+  float dist = orc_dist(ix->mode, q, ix->data + ix->stride * (size_t)ep, ix->dim);
+  if (stats) stats[0]++;
+  float lowerBound = dist;
+  orc_pair e = {dist, ep};
+  hpush(top, &nt, e, +1);
+  hpush(cand, &nc, e, -1);
+  visited[ep] = 1;
+  while (nc) {
+    orc_pair cur = cand[0];
+    if (cur.d > lowerBound) break; /* :347-349 */
+    hpop(cand, &nc, -1);
+    const uint32_t *row = ix->links0 + (size_t)cur.id * ix->maxM0;
+    if (stats) stats[1]++;
+    for (unsigned j = 0; j < ix->maxM0 && row[j] != ORC_INVALID; j++) { /* :377 */
+      uint32_t cid = row[j];
+      if (visited[cid]) continue;
+      visited[cid] = 1;
+      float d = orc_dist(ix->mode, q, ix->data + ix->stride * (size_t)cid, ix->dim);
+      if (stats) stats[0]++;
+      if (nt < ef || lowerBound > d) { /* :395 */
+        orc_pair c = {d, cid};
+        if (nc < cand_cap) hpush(cand, &nc, c, -1);
+        hpush(top, &nt, c, +1);
+        while (nt > ef) hpop(top, &nt, +1);
+        if (nt) lowerBound = top[0].d;
+      }
+    }
+  }
+  qsort(top, nt, sizeof(orc_pair), pair_cmp);
+  return nt;
+}
+
+/* Canonical single-pool form used by the CUDA kernel: one ascending (d,id) pool of <= ef entries,
+ * each with an "expanded" flag; expand the best unexpanded entry; stop when none is left. It equals
+ * the two-heap form whenever no two pool entries tie on distance at the eviction boundary
+ * (an evicted entry has d >= lowerBound and is never expanded unless d == lowerBound). */
+static size_t hnsw_base_pool(const orc_hnsw *ix, uint32_t ep, const float *q, size_t ef, uint8_t *visited,
+                             orc_pair *pool, uint8_t *expanded, uint64_t *stats) {
+  size_t np = 0;
+  pool[0].d = orc_dist(ix->mode, q, ix->data + ix->stride * (size_t)ep, ix->dim);
+  pool[0].id = ep; expanded[0] = 0; np = 1;
+  if (stats) stats[0]++;
+  visited[ep] = 1;
+  for (;;) {
+    size_t k = 0;
+    while (k < np && expanded[k]) k++;
+    if (k == np) break;
+    expanded[k] = 1;
+    const uint32_t *row = ix->links0 + (size_t)pool[k].id * ix->maxM0;
+    if (stats) stats[1]++;
+    for (unsigned j = 0; j < ix->maxM0 && row[j] != ORC_INVALID; j++) {
+      uint32_t cid = row[j];
+      if (visited[cid]) continue;
+      visited[cid] = 1;
+      orc_pair c = {orc_dist(ix->mode, q, ix->data + ix->stride * (size_t)cid, ix->dim), cid};
+      if (stats) stats[0]++;
+      if (np < ef || c.d < pool[np - 1].d) {
+        size_t pos = np;
+        while (pos > 0 && pair_less(c, pool[pos - 1])) pos--;
+        size_t last = np < ef ? np : ef - 1; /* index that receives the shifted tail */
+        for (size_t t = last; t > pos; t--) { pool[t] = pool[t - 1]; expanded[t] = expanded[t - 1]; }
+        pool[pos] = c; expanded[pos] = 0;
+        if (np < ef) np++;
+      }
+    }
+  }
+  return np;
+}
+
+/* HierarchicalNSW::searchKnn batched (hnswalg.h:1270-1324; batch shape of
+ * python_bindings/bindings.cpp:612-695): rows ascending by (distance,id), external labels.
+ * variant 0 = two-heap form, 1 = single-pool form. Rows with fewer than k results are padded with
+ * label ~0 / +inf. stats [nq,2] = {distance evaluations, expanded nodes incl. upper layers}. */
+EXPORT int orc_hnsw_search(const float *data, size_t n, size_t dim, size_t stride, const uint32_t *links0,
+                           unsigned maxM0, const int32_t *levels, const uint32_t *upper_ptr,
+                           const uint32_t *upper_links, unsigned maxM, const uint64_t *labels, uint32_t ep,
+                           int maxlevel, const float *q, size_t nq, size_t qstride, size_t k, size_t ef,
+                           int mode, int variant, uint64_t *out_labels, float *out_dists, uint64_t *stats) {
+  orc_hnsw ix = {data, n, dim, stride, links0, maxM0, levels, upper_ptr, upper_links, maxM, ep, maxlevel, mode};
+  size_t efk = ef > k ? ef : k; /* :1309 std::max(ef_, k) */
+  if (stats) memset(stats, 0, sizeof(uint64_t) * 2 * nq);
+#pragma omp parallel
+  {
+    uint8_t *visited = (uint8_t *)malloc(n ? n : 1);
+    orc_pair *top = (orc_pair *)malloc(sizeof(orc_pair) * (efk + 2));
+    orc_pair *cand = (orc_pair *)malloc(sizeof(orc_pair) * (n + 2));
+    uint8_t *expd = (uint8_t *)malloc(efk + 2);
+#pragma omp for schedule(dynamic, 8)
+    for (long qi = 0; qi < (long)nq; qi++) {
+      const float *qv = q + (size_t)qi * qstride;
+      size_t m = 0;
+      if (n) {
+        memset(visited, 0, n);
+        float cd;
+        uint64_t *st = stats ? stats + 2 * qi : NULL;
+        uint32_t cur = hnsw_descend(&ix, qv, &cd, st);
+        if (st) st[0]--; /* the base layer re-evaluates the entry point; count it once */
+        m = variant == 0 ? hnsw_base_twoheap(&ix, cur, qv, efk, visited, top, cand, n + 1, st)
+                         : hnsw_base_pool(&ix, cur, qv, efk, visited, top, expd, st);
+      }
+      for (size_t j = 0; j < k; j++) {
+        out_labels[(size_t)qi * k + j] = j < m ? (labels ? labels[top[j].id] : top[j].id) : ~(uint64_t)0;
+        out_dists[(size_t)qi * k + j] = j < m ? top[j].d : INFINITY;
+      }
+    }
+    free(visited); free(top); free(cand); free(expd);
+  }
+  return 0;
+}

@@ -1,0 +1,362 @@
+"""Test-side helpers: ctypes bindings for the oracle (oracle/liboracle.so) and for the compiled
+UNMODIFIED reference (oracle/_ref/libref_*.so), seeded synthetic data and parsers
+for the reference's on-disk graph formats. TEST INFRASTRUCTURE ONLY — the product never imports this."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+REF_DIR = os.path.join(ORACLE_DIR, "_ref")
+INVALID = 0xFFFFFFFF
+
+# oracle distance modes (oracle/oracle.c)
+L2_SCALAR, IP_SCALAR, L2_HNSW_AVX, IP_HNSW_AVX, L2_EFANNA_AVX, L2_GPU, IP_GPU, FASTL2_EFANNA_AVX = range(8)
+
+f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+u32p = np.ctypeslib.ndpointer(np.uint32, flags="C_CONTIGUOUS")
+i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
+u64p = np.ctypeslib.ndpointer(np.uint64, flags="C_CONTIGUOUS")
+
+
+def _build_oracle():
+    so = os.path.join(ORACLE_DIR, "liboracle.so")
+    src = os.path.join(ORACLE_DIR, "oracle.c")
+    if not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", ORACLE_DIR, "-s", os.path.join(ORACLE_DIR, "liboracle.so")])
+    return so
+
+
+_oracle = None
+
+
+def oracle():
+    global _oracle
+    if _oracle is None:
+        lib = C.CDLL(_build_oracle())
+        lib.orc_dist.restype = C.c_float
+        lib.orc_dist.argtypes = [C.c_int, f32p, f32p, C.c_size_t]
+        lib.orc_set_gpu_team.argtypes = [C.c_int]
+        lib.orc_seed_hash.restype = C.c_uint32
+        lib.orc_seed_hash.argtypes = [C.c_uint32] * 3
+        lib.orc_bf_knn.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, f32p, C.c_size_t, C.c_size_t,
+                                   C.c_size_t, C.c_int, u32p, f32p]
+        lib.orc_insert_into_pool.argtypes = [u32p, f32p, i32p, C.c_uint, C.c_uint32, C.c_float]
+        lib.orc_nsg_search.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, u32p, C.c_uint, C.c_uint32,
+                                       f32p, C.c_size_t, C.c_size_t, C.c_uint, C.c_uint, C.c_int, C.c_int,
+                                       C.c_uint32, u32p, C.c_void_p, C.c_void_p]
+        lib.orc_hnsw_search.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, u32p, C.c_uint, i32p, u32p,
+                                        u32p, C.c_uint, C.c_void_p, C.c_uint32, C.c_int, f32p, C.c_size_t,
+                                        C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int, u64p, f32p,
+                                        C.c_void_p]
+        _oracle = lib
+    return _oracle
+
+
+def _vp(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+# ------------------------------------------------------------------ oracle wrappers
+def orc_bf_knn(base, q, k, mode):
+    n, dim = base.shape
+    nq = q.shape[0]
+    ids = np.empty((nq, k), np.uint32)
+    d = np.empty((nq, k), np.float32)
+    oracle().orc_bf_knn(base, n, dim, base.shape[1], q, nq, q.shape[1], k, mode, ids, d)
+    return ids, d
+
+
+def orc_nsg_search(base, graph, ep, q, K, L, mode, rng_mode=1, seed=0, want_stats=False):
+    n, dim = base.shape
+    nq = q.shape[0]
+    ids = np.empty((nq, K), np.uint32)
+    d = np.empty((nq, K), np.float32)
+    st = np.zeros((nq, 2), np.uint64) if want_stats else None
+    rc = oracle().orc_nsg_search(base, n, dim, dim, graph, graph.shape[1], ep, q, nq, q.shape[1], K, L, mode,
+                                 rng_mode, seed, ids, _vp(d), _vp(st))
+    assert rc == 0
+    return (ids, d, st) if want_stats else (ids, d)
+
+
+def orc_hnsw_search(base, h, q, k, ef, mode, variant=1, want_stats=False):
+    """h: dict with links0, levels, upper_ptr, upper_links, labels, ep, maxlevel (see parse_hnsw)."""
+    n, dim = base.shape
+    nq = q.shape[0]
+    lab = np.empty((nq, k), np.uint64)
+    d = np.empty((nq, k), np.float32)
+    st = np.zeros((nq, 2), np.uint64) if want_stats else None
+    up = h["upper_links"]
+    if up.size == 0:
+        up = np.full((1, max(1, h["maxM"])), INVALID, np.uint32)
+    oracle().orc_hnsw_search(base, n, dim, dim, h["links0"], h["links0"].shape[1], h["levels"], h["upper_ptr"],
+                             up, up.shape[1], _vp(h["labels"]), h["ep"], h["maxlevel"], q, nq, q.shape[1], k, ef,
+                             mode, variant, lab, d, _vp(st))
+    return (lab, d, st) if want_stats else (lab, d)
+
+
+# ------------------------------------------------------------------ reference on-disk formats
+def parse_hnsw(path):
+    """hnswlib saveIndex blob (hnswlib/hnswlib/hnswalg.h:685-713) -> flat arrays (oracle.c layout)."""
+    raw = np.fromfile(path, np.uint8)
+    hdr = raw[:96]
+    q = lambda off: int(hdr[off:off + 8].view(np.uint64)[0])
+    offL0, maxel, cur, sdpe, label_off, off_data = [q(8 * i) for i in range(6)]
+    maxlevel = int(hdr[48:52].view(np.int32)[0])
+    ep = int(hdr[52:56].view(np.uint32)[0])
+    maxM, maxM0, M = q(56), q(64), q(72)
+    efc = q(88)
+    n = cur
+    blob = raw[96:96 + n * sdpe].reshape(n, sdpe)
+    cnt = blob[:, offL0:offL0 + 2].copy().view(np.uint16).reshape(n).astype(np.int64)
+    l0 = blob[:, offL0 + 4:offL0 + 4 + 4 * maxM0].copy().view(np.uint32).reshape(n, maxM0)
+    links0 = np.where(np.arange(maxM0)[None, :] < cnt[:, None], l0, INVALID).astype(np.uint32)
+    dim = (label_off - off_data) // 4
+    vec = blob[:, off_data:off_data + 4 * dim].copy().view(np.float32).reshape(n, dim)
+    labels = blob[:, label_off:label_off + 8].copy().view(np.uint64).reshape(n)
+    pos = 96 + n * sdpe
+    levels = np.zeros(n, np.int32)
+    upper_ptr = np.zeros(n, np.uint32)
+    rows = []
+    slpe = maxM * 4 + 4
+    for i in range(n):
+        sz = int(raw[pos:pos + 4].view(np.uint32)[0])
+        pos += 4
+        if sz:
+            lv = sz // slpe
+            levels[i] = lv
+            upper_ptr[i] = len(rows)
+            for l in range(lv):
+                b = raw[pos + l * slpe: pos + (l + 1) * slpe]
+                c = int(b[:2].view(np.uint16)[0])
+                r = np.full(maxM, INVALID, np.uint32)
+                r[:c] = b[4:4 + 4 * c].view(np.uint32)
+                rows.append(r)
+            pos += sz
+    upper = np.stack(rows) if rows else np.zeros((0, maxM), np.uint32)
+    return dict(n=n, dim=dim, M=M, maxM=maxM, maxM0=maxM0, efc=efc, ep=ep, maxlevel=maxlevel,
+                links0=np.ascontiguousarray(links0), levels=levels, upper_ptr=upper_ptr,
+                upper_links=np.ascontiguousarray(upper), labels=np.ascontiguousarray(labels), vectors=vec)
+
+
+def parse_nsg(path, n):
+    """IndexNSG::Save (CNNS/src/nsg/index_nsg.cpp:37-49): [u32 width][u32 ep] then per node [u32 k][u32 x k]."""
+    raw = np.fromfile(path, np.uint32)
+    width, ep = int(raw[0]), int(raw[1])
+    rows, pos = [], 2
+    for _ in range(n):
+        k = int(raw[pos])
+        rows.append(raw[pos + 1:pos + 1 + k])
+        pos += 1 + k
+    assert pos == raw.size
+    gs = max(8, (max(len(r) for r in rows) + 7) // 8 * 8)
+    g = np.full((n, gs), INVALID, np.uint32)
+    for i, r in enumerate(rows):
+        g[i, :len(r)] = r
+    return g, ep, width
+
+
+def write_knn_graph(path, knn):
+    """efanna kNN-graph file (IndexGraph::Save, efanna_graph/src/index_graph.cpp:348-357; read by
+    IndexNSG::Load_nn_graph, index_nsg.cpp:128-148): per node [u32 K][u32 x K]."""
+    n, K = knn.shape
+    out = np.empty((n, K + 1), np.uint32)
+    out[:, 0] = K
+    out[:, 1:] = knn
+    out.tofile(path)
+
+
+def read_knn_graph(path):
+    raw = np.fromfile(path, np.uint32)
+    K = int(raw[0])
+    return np.ascontiguousarray(raw.reshape(-1, K + 1)[:, 1:])
+
+
+# ------------------------------------------------------------------ seeded synthetic data
+def data_uniform(n, dim, seed):
+    return np.random.default_rng(seed).random((n, dim), dtype=np.float32)
+
+
+def data_sift_like(n, dim, seed, n_clusters=64, centers_seed=12345):
+    """integer-valued fp32 in [0,218], clustered, heavy-tailed: every L2 partial sum is an integer
+    < 2^24, so fp32 distances are exact under ANY summation order (CPU SIMD, GPU, scalar)."""
+    cent = np.abs(np.random.default_rng(centers_seed).normal(0, 1, (n_clusters, dim))) * 40
+    rng = np.random.default_rng(seed)
+    a = rng.integers(0, n_clusters, n)
+    x = cent[a] + rng.normal(0, 1, (n, dim)) * 18
+    return np.floor(np.clip(np.abs(x), 0, 218)).astype(np.float32)
+
+
+def data_glove_like(n, dim, seed, n_clusters=100, centers_seed=54321):
+    cent = np.random.default_rng(centers_seed).normal(0, 1, (n_clusters, dim))
+    rng = np.random.default_rng(seed)
+    x = cent[rng.integers(0, n_clusters, n)] * 0.7 + rng.normal(0, 1, (n, dim))
+    x /= np.linalg.norm(x, axis=1, keepdims=True)
+    return x.astype(np.float32)
+
+
+def recall(found, truth):
+    """mean |found_row ∩ truth_row| / k"""
+    k = truth.shape[1]
+    hit = 0
+    for f, t in zip(found, truth):
+        hit += len(set(f.tolist()) & set(t.tolist()))
+    return hit / (truth.shape[0] * k)
+
+
+# ------------------------------------------------------------------ compiled reference (oracle/_ref)
+def have_ref():
+    return os.path.exists(os.path.join(REF_DIR, "libref_hnsw.so"))
+
+
+def host_has_avx512():
+    try:
+        return "avx512f" in open("/proc/cpuinfo").read()
+    except OSError:
+        return False
+
+
+_reflibs = {}
+
+
+def reflib(name):
+    """name in {hnsw, hnsw_avx, hnsw_fast, nsg, nsg_fast, efanna, efanna_fast}; *_fast resolves to the
+    AVX-512 build when the host supports it."""
+    if name.endswith("_fast") and host_has_avx512():
+        name += "512"
+    if name in _reflibs:
+        return _reflibs[name]
+    lib = C.CDLL(os.path.join(REF_DIR, "libref_%s.so" % name))
+    if name.startswith("hnsw"):
+        lib.ref_dist.restype = C.c_float
+        lib.ref_dist.argtypes = [C.c_int, f32p, f32p, C.c_size_t]
+        lib.ref_bf_knn.argtypes = [C.c_int, f32p, C.c_size_t, C.c_size_t, f32p, C.c_size_t, C.c_size_t, u64p,
+                                   f32p, C.c_int]
+        lib.ref_hnsw_new.restype = C.c_void_p
+        lib.ref_hnsw_new.argtypes = [C.c_int] + [C.c_size_t] * 5
+        lib.ref_hnsw_load.restype = C.c_void_p
+        lib.ref_hnsw_load.argtypes = [C.c_int, C.c_size_t, C.c_char_p]
+        lib.ref_hnsw_free.argtypes = [C.c_void_p]
+        lib.ref_hnsw_add.argtypes = [C.c_void_p, f32p, C.c_size_t, C.c_size_t, C.c_int]
+        lib.ref_hnsw_search.argtypes = [C.c_void_p, f32p, C.c_size_t, C.c_size_t, C.c_size_t, u64p, f32p,
+                                        C.c_int, C.c_void_p, C.c_void_p]
+        lib.ref_hnsw_save.argtypes = [C.c_void_p, C.c_char_p]
+    elif name.startswith("nsg"):
+        lib.ref_nsg_dist_l2.restype = C.c_float
+        lib.ref_nsg_dist_l2.argtypes = [f32p, f32p, C.c_uint]
+        lib.ref_nsg_build.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_char_p, C.c_uint, C.c_uint, C.c_uint,
+                                      C.c_char_p, C.c_uint, C.c_int]
+        lib.ref_nsg_load.restype = C.c_void_p
+        lib.ref_nsg_load.argtypes = [C.c_size_t, C.c_size_t, C.c_char_p]
+        lib.ref_nsg_free.argtypes = [C.c_void_p]
+        lib.ref_nsg_search.argtypes = [C.c_void_p, f32p, f32p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_uint,
+                                       u32p, C.c_uint, C.c_int]
+        lib.ref_nsg_optimize.argtypes = [C.c_void_p, f32p]
+        lib.ref_nsg_search_opt.argtypes = [C.c_void_p, f32p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_uint, u32p,
+                                           C.c_uint, C.c_int]
+    elif name.startswith("efanna"):
+        lib.ref_nndescent_build.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_uint, C.c_uint, C.c_uint, C.c_uint,
+                                            C.c_uint, C.c_char_p, C.c_uint, C.c_int]
+    _reflibs[name] = lib
+    return lib
+
+
+class _quiet:
+    """the reference prints a line per node in IndexNSG::Build (index_nsg.cpp:497): silence fd 1."""
+
+    def __enter__(self):
+        import sys
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        self.null = os.open(os.devnull, os.O_WRONLY)
+        os.dup2(self.null, 1)
+
+    def __exit__(self, *a):
+        os.dup2(self.saved, 1)
+        os.close(self.null)
+        os.close(self.saved)
+
+
+def ref_bf_knn(base, q, k, metric, lib="hnsw", threads=0):
+    n, dim = base.shape
+    lab = np.empty((q.shape[0], k), np.uint64)
+    d = np.empty((q.shape[0], k), np.float32)
+    reflib(lib).ref_bf_knn(metric, base, n, dim, q, q.shape[0], k, lab, d, threads)
+    return lab, d
+
+
+class RefHnsw:
+    def __init__(self, metric, dim, max_elements=0, M=16, efc=200, seed=100, lib="hnsw", path=None):
+        self.lib = reflib(lib)
+        self.dim = dim
+        if path is None:
+            self.h = self.lib.ref_hnsw_new(metric, dim, max_elements, M, efc, seed)
+        else:
+            self.h = self.lib.ref_hnsw_load(metric, dim, path.encode())
+        assert self.h
+
+    def add(self, data, label0=0, threads=1):
+        self.lib.ref_hnsw_add(self.h, data, data.shape[0], label0, threads)
+
+    def search(self, q, k, ef, threads=0):
+        lab = np.empty((q.shape[0], k), np.uint64)
+        d = np.empty((q.shape[0], k), np.float32)
+        self.lib.ref_hnsw_search(self.h, q, q.shape[0], k, ef, lab, d, threads, None, None)
+        return lab, d
+
+    def save(self, path):
+        self.lib.ref_hnsw_save(self.h, path.encode())
+
+    def close(self):
+        if self.h:
+            self.lib.ref_hnsw_free(self.h)
+            self.h = None
+
+    __del__ = close
+
+
+def ref_nsg_build(base, knn_path, L, R, C_, out_path, seed=1, threads=1, lib="nsg"):
+    n, dim = base.shape
+    with _quiet():
+        reflib(lib).ref_nsg_build(base, n, dim, knn_path.encode(), L, R, C_, out_path.encode(), seed, threads)
+
+
+class RefNsg:
+    def __init__(self, base, path, lib="nsg"):
+        self.lib = reflib(lib)
+        self.base = base
+        self.n, self.dim = base.shape
+        self.h = self.lib.ref_nsg_load(self.n, self.dim, path.encode())
+        self.opt = False
+
+    def search(self, q, K, L, seed=1, threads=1):
+        assert not self.opt
+        ids = np.empty((q.shape[0], K), np.uint32)
+        self.lib.ref_nsg_search(self.h, self.base, q, q.shape[0], self.dim, K, L, ids, seed, threads)
+        return ids
+
+    def optimize(self):
+        self.lib.ref_nsg_optimize(self.h, self.base)
+        self.opt = True
+
+    def search_opt(self, q, K, L, seed=1, threads=1):
+        assert self.opt
+        ids = np.empty((q.shape[0], K), np.uint32)
+        self.lib.ref_nsg_search_opt(self.h, q, q.shape[0], self.dim, K, L, ids, seed, threads)
+        return ids
+
+    def close(self):
+        if self.h:
+            self.lib.ref_nsg_free(self.h)
+            self.h = None
+
+    __del__ = close
+
+
+def ref_nndescent(base, K, L, it, S, R, out_path, seed=1, threads=0, lib="efanna"):
+    n, dim = base.shape
+    with _quiet():
+        reflib(lib).ref_nndescent_build(base, n, dim, K, L, it, S, R, out_path.encode(), seed, threads)
+    return read_knn_graph(out_path)

@@ -1,0 +1,205 @@
+"""hnsw-nsg_b200 — Python face of the C ABI in include/b200ann.h (ctypes over libb200ann.so).
+
+The library is hand-written sm_100a CUDA; there is no CPU fallback. Importing this module without the
+built library raises; creating a Handle without a CUDA device raises.
+
+Import with ``importlib.import_module("hnsw-nsg_b200")`` (the directory name carries a hyphen).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200ann.so")
+INVALID = 0xFFFFFFFF
+L2, IP = 0, 1
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        "hnsw-nsg_b200: %s is missing — build it with `make -C hnsw-nsg_b200/csrc` "
+        "(or __graft_entry__.build()); there is no CPU fallback." % LIB_PATH)
+
+_lib = C.CDLL(LIB_PATH)
+_vp = C.c_void_p
+_sz = C.c_size_t
+_lib.b200ann_create.argtypes = [C.c_int, C.POINTER(_vp)]
+_lib.b200ann_destroy.argtypes = [_vp]
+_lib.b200ann_last_error.restype = C.c_char_p
+_lib.b200ann_last_error.argtypes = [_vp]
+_lib.b200ann_stream.restype = _vp
+_lib.b200ann_stream.argtypes = [_vp]
+_lib.b200ann_launch_count.restype = C.c_uint64
+_lib.b200ann_launch_count.argtypes = [_vp]
+_lib.b200ann_last_kernel_ms.restype = C.c_float
+_lib.b200ann_last_kernel_ms.argtypes = [_vp]
+_lib.b200ann_set_visited_bits.argtypes = [_vp, C.c_int]
+_lib.b200ann_index_create.argtypes = [_vp, _vp, _sz, _sz, _sz, C.c_int, C.POINTER(_vp)]
+_lib.b200ann_index_destroy.argtypes = [_vp]
+_lib.b200ann_index_size.restype = _sz
+_lib.b200ann_index_size.argtypes = [_vp]
+_lib.b200ann_index_dim.restype = _sz
+_lib.b200ann_index_dim.argtypes = [_vp]
+_lib.b200ann_index_set_graph.argtypes = [_vp, _vp, _sz, C.c_uint32]
+_lib.b200ann_index_get_graph.argtypes = [_vp, _vp, _sz, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+_lib.b200ann_index_set_hnsw.argtypes = [_vp, _vp, _sz, _vp, _vp, _vp, _sz, _sz, _vp, C.c_uint32, C.c_int]
+_lib.b200ann_bf_knn.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _vp, _vp]
+_lib.b200ann_knn_graph.argtypes = [_vp, _vp, _sz, _vp]
+_lib.b200ann_nsg_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, C.c_uint32, _vp, _vp, _vp]
+_lib.b200ann_hnsw_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _vp, _vp, _vp]
+
+EXPORTS = [
+    "b200ann_create", "b200ann_destroy", "b200ann_last_error", "b200ann_stream", "b200ann_launch_count",
+    "b200ann_last_kernel_ms", "b200ann_set_visited_bits", "b200ann_index_create", "b200ann_index_destroy",
+    "b200ann_index_size", "b200ann_index_dim", "b200ann_index_set_graph", "b200ann_index_get_graph",
+    "b200ann_index_set_hnsw", "b200ann_bf_knn", "b200ann_knn_graph", "b200ann_nsg_search", "b200ann_hnsw_search",
+]
+
+
+class B200AnnError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("b200ann error %d: %s" % (code, msg))
+        self.code = code
+
+
+def dist_team(dim):
+    """lanes per row used by the search kernels (csrc/dist.cuh dist_team_for_nch)"""
+    return 8 if (dim + 3) // 4 <= 64 else 32
+
+
+def _ptr(a):
+    """numpy array -> host pointer; torch CUDA/CPU tensor -> data_ptr; int -> raw device pointer"""
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return _vp(a)
+    if isinstance(a, np.ndarray):
+        assert a.flags["C_CONTIGUOUS"]
+        return a.ctypes.data_as(_vp)
+    if hasattr(a, "data_ptr"):
+        assert a.is_contiguous()
+        return _vp(a.data_ptr())
+    raise TypeError(type(a))
+
+
+class Handle:
+    """one per GPU and host thread: device, stream, last error (include/b200ann.h)"""
+
+    def __init__(self, device=0):
+        h = _vp()
+        rc = _lib.b200ann_create(device, C.byref(h))
+        if rc != 0:
+            raise B200AnnError(rc, "b200ann_create(device=%d) failed: no usable CUDA device (no CPU fallback)" % device)
+        self._h = h
+
+    def _check(self, rc):
+        if rc != 0:
+            raise B200AnnError(rc, _lib.b200ann_last_error(self._h).decode())
+
+    def close(self):
+        if getattr(self, "_h", None):
+            _lib.b200ann_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    @property
+    def stream(self):
+        return _lib.b200ann_stream(self._h)
+
+    @property
+    def launch_count(self):
+        return int(_lib.b200ann_launch_count(self._h))
+
+    @property
+    def last_kernel_ms(self):
+        return float(_lib.b200ann_last_kernel_ms(self._h))
+
+    def set_visited_bits(self, bits):
+        self._check(_lib.b200ann_set_visited_bits(self._h, bits))
+
+
+class Index:
+    """vectors (+ graphs) resident in HBM"""
+
+    def __init__(self, handle, data, metric=L2, n=None, dim=None, stride=None):
+        self.h = handle
+        if n is None:
+            n, dim = data.shape
+            stride = dim
+        ix = _vp()
+        handle._check(_lib.b200ann_index_create(handle._h, _ptr(data), n, dim, stride, metric, C.byref(ix)))
+        self._ix = ix
+        self.n, self.dim, self.metric = n, dim, metric
+
+    def close(self):
+        if getattr(self, "_ix", None):
+            _lib.b200ann_index_destroy(self._ix)
+            self._ix = None
+
+    __del__ = close
+
+    # ---- graphs
+    def set_graph(self, graph, ep):
+        graph = np.ascontiguousarray(graph, np.uint32)
+        self.h._check(_lib.b200ann_index_set_graph(self._ix, _ptr(graph), graph.shape[1], ep))
+
+    def get_graph(self):
+        ep, width = C.c_uint32(), C.c_uint32()
+        self.h._check(_lib.b200ann_index_get_graph(self._ix, None, 0, C.byref(ep), C.byref(width)))
+        g = np.empty((self.n, max(1, width.value)), np.uint32)
+        self.h._check(_lib.b200ann_index_get_graph(self._ix, _ptr(g), g.shape[1], C.byref(ep), C.byref(width)))
+        return g, ep.value, width.value
+
+    def set_hnsw(self, links0, levels, upper_ptr, upper_links, labels, ep, maxlevel):
+        links0 = np.ascontiguousarray(links0, np.uint32)
+        levels = np.ascontiguousarray(levels, np.int32)
+        upper_ptr = np.ascontiguousarray(upper_ptr, np.uint32)
+        upper_links = np.ascontiguousarray(upper_links, np.uint32)
+        rows = upper_links.shape[0] if upper_links.ndim == 2 else 0
+        maxM = upper_links.shape[1] if upper_links.ndim == 2 else 0
+        labels = None if labels is None else np.ascontiguousarray(labels, np.uint64)
+        self.h._check(_lib.b200ann_index_set_hnsw(self._ix, _ptr(links0), links0.shape[1], _ptr(levels), _ptr(upper_ptr),
+                                                  _ptr(upper_links) if rows else None, rows, maxM, _ptr(labels), ep,
+                                                  maxlevel))
+
+    # ---- exact brute force
+    def bf_knn(self, q, k):
+        q = np.ascontiguousarray(q, np.float32)
+        ids = np.empty((q.shape[0], k), np.uint32)
+        d = np.empty((q.shape[0], k), np.float32)
+        self.h._check(_lib.b200ann_bf_knn(self.h._h, self._ix, _ptr(q), q.shape[0], q.shape[1], k, _ptr(ids), _ptr(d)))
+        return ids, d
+
+    def knn_graph(self, K):
+        knn = np.empty((self.n, K), np.uint32)
+        self.h._check(_lib.b200ann_knn_graph(self.h._h, self._ix, K, _ptr(knn)))
+        return knn
+
+    # ---- graph search
+    def nsg_search(self, q, K, L, seed=0, want_stats=False):
+        q = np.ascontiguousarray(q, np.float32)
+        ids = np.empty((q.shape[0], K), np.uint32)
+        d = np.empty((q.shape[0], K), np.float32)
+        st = np.zeros((q.shape[0], 2), np.uint32) if want_stats else None
+        self.h._check(_lib.b200ann_nsg_search(self.h._h, self._ix, _ptr(q), q.shape[0], q.shape[1], K, L, seed,
+                                              _ptr(ids), _ptr(d), _ptr(st)))
+        return (ids, d, st) if want_stats else (ids, d)
+
+    def hnsw_search(self, q, k, ef, want_stats=False):
+        q = np.ascontiguousarray(q, np.float32)
+        lab = np.empty((q.shape[0], k), np.uint64)
+        d = np.empty((q.shape[0], k), np.float32)
+        st = np.zeros((q.shape[0], 2), np.uint32) if want_stats else None
+        self.h._check(_lib.b200ann_hnsw_search(self.h._h, self._ix, _ptr(q), q.shape[0], q.shape[1], k, ef, _ptr(lab),
+                                               _ptr(d), _ptr(st)))
+        return (lab, d, st) if want_stats else (lab, d)
+
+    # raw (pointer-level) entry for device-resident buffers: torch tensors or ints
+    def nsg_search_raw(self, q, nq, qstride, K, L, seed, ids, dists=None, stats=None):
+        self.h._check(_lib.b200ann_nsg_search(self.h._h, self._ix, _ptr(q), nq, qstride, K, L, seed, _ptr(ids),
+                                              _ptr(dists), _ptr(stats)))
+
+
+def lib():
+    return _lib

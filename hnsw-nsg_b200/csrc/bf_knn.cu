@@ -1,0 +1,284 @@
+// Exact brute-force kNN, fp32 SIMT tiles with a fused running top-k.
+//
+// Replaces hnswlib::BruteforceSearch::searchKnn (hnswlib/hnswlib/bruteforce.h:106-135) and
+// IndexGraph::generate_control_set (CNNS/efanna_graph/src/index_graph.cpp:138-153), batched over
+// queries; with exclude_self it yields the exact kNN graph that IndexGraph::Build (:265-294)
+// approximates. Result = the k smallest under (distance, id), ties to the smaller id, ascending.
+//
+// CTA = 256 threads = 64 queries x 128 base rows per tile, 4x8 register tile per thread, DK=16 dims
+// per shared-memory stage. Distances are accumulated sequentially over the dimension with fmaf
+// (oracle mode ORC_*_SEQ_FMA restates this order). Each warp owns 8 queries outright, so the running
+// top-k needs no block-level synchronisation: candidates below the query's current k-th
+// (distance,id) go to a 32-entry shared-memory pending buffer; a full buffer is bitonic-sorted across
+// the warp and merged into the query's sorted k-list in global memory (ping-pong between two lists).
+#include "common.cuh"
+
+namespace {
+
+constexpr int QT = 64, BT = 128, DK = 16, NT = 256, PEND = 32;
+constexpr int QS = QT + 4, BS = BT + 4;  // padded smem row strides (floats), multiples of 4
+
+struct BfParams {
+  const float *base; size_t bstride; uint32_t n; uint32_t dim;
+  const float *q; size_t qstride; uint32_t nq;
+  uint32_t k; int ip; int exclude_self;
+  uint32_t splits;          // base range splits (grid.y)
+  float *list_d[2]; uint32_t *list_i[2];  // [splits, nq, k] ping-pong lists
+  uint8_t *cur;             // [splits, nq] which list is current at exit
+};
+
+__device__ __forceinline__ bool lex_less(float d0, uint32_t i0, float d1, uint32_t i1) {
+  return d0 < d1 || (d0 == d1 && i0 < i1);
+}
+
+// merge the (sorted ascending across lanes) pending entries of one query into its k-list
+__device__ __forceinline__ void merge_pending(float pd, uint32_t pi, const volatile float *src_d,
+                                              const volatile uint32_t *src_i, float *dst_d, uint32_t *dst_i,
+                                              uint32_t k, int lane, float &thr_d, uint32_t &thr_i) {
+  // bitonic sort of 32 (d,id) pairs across the warp
+#pragma unroll
+  for (int sz = 2; sz <= 32; sz <<= 1) {
+#pragma unroll
+    for (int st = sz >> 1; st >= 1; st >>= 1) {
+      float od = __shfl_xor_sync(0xffffffffu, pd, st);
+      uint32_t oi = __shfl_xor_sync(0xffffffffu, pi, st);
+      bool keep_min = (((lane & sz) == 0) == ((lane & st) == 0));
+      bool take = keep_min ? lex_less(od, oi, pd, pi) : lex_less(pd, pi, od, oi);
+      if (take) { pd = od; pi = oi; }
+    }
+  }
+  // list elements: new position = j + #{pending < list[j]}
+  for (uint32_t j0 = 0; j0 < k; j0 += 32) {
+    uint32_t j = j0 + lane;
+    float ld = INFINITY; uint32_t li = INVALID_ID;
+    if (j < k) { ld = src_d[j]; li = src_i[j]; }
+    uint32_t cnt = 0;
+#pragma unroll
+    for (int s = 0; s < 32; s++) {
+      float sd = __shfl_sync(0xffffffffu, pd, s);
+      uint32_t si = __shfl_sync(0xffffffffu, pi, s);
+      cnt += lex_less(sd, si, ld, li) ? 1u : 0u;
+    }
+    if (j < k && j + cnt < k) { dst_d[j + cnt] = ld; dst_i[j + cnt] = li; }
+  }
+  // pending elements: new position = lane + #{list < pending}  (binary search; keys are unique)
+  if (pi != INVALID_ID) {
+    uint32_t lo = 0, hi = k;
+    while (lo < hi) {
+      uint32_t mid = (lo + hi) >> 1;
+      if (lex_less(src_d[mid], src_i[mid], pd, pi)) lo = mid + 1; else hi = mid;
+    }
+    uint32_t pos = lo + lane;
+    if (pos < k) { dst_d[pos] = pd; dst_i[pos] = pi; }
+  }
+  __syncwarp();
+  thr_d = ((const volatile float *)dst_d)[k - 1];
+  thr_i = ((const volatile uint32_t *)dst_i)[k - 1];
+}
+
+__global__ void __launch_bounds__(NT) bf_knn_kernel(const BfParams p) {
+  __shared__ __align__(16) float Qs[DK][QS];
+  __shared__ __align__(16) float Bs[DK][BS];
+  __shared__ float pend_d[QT][PEND];
+  __shared__ uint32_t pend_i[QT][PEND];
+  __shared__ uint32_t pend_n[QT];
+  __shared__ float thr_d[QT];
+  __shared__ uint32_t thr_i[QT];
+  __shared__ uint8_t curbuf[QT];
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int ty = tid >> 4, tx = tid & 15;
+  const uint32_t q0 = blockIdx.x * QT;
+  const uint32_t split = blockIdx.y;
+  const uint32_t per = ((p.n + p.splits - 1) / p.splits + BT - 1) / BT * BT;
+  const uint32_t b_begin = split * per;
+  const uint32_t b_end = min(p.n, b_begin + per);
+  const size_t lbase = ((size_t)split * p.nq) * p.k;
+
+  for (int i = tid; i < QT; i += NT) {
+    pend_n[i] = 0; thr_d[i] = INFINITY; thr_i[i] = INVALID_ID; curbuf[i] = 0;
+  }
+  // lists start as (+inf, INVALID)
+  for (uint32_t qq = 0; qq < QT; qq++) {
+    uint32_t qg = q0 + qq;
+    if (qg >= p.nq) break;
+    for (uint32_t j = tid; j < p.k; j += NT) {
+      p.list_d[0][lbase + (size_t)qg * p.k + j] = INFINITY;
+      p.list_i[0][lbase + (size_t)qg * p.k + j] = INVALID_ID;
+    }
+  }
+  __syncthreads();
+
+  auto flush = [&](int ql) {  // warp-cooperative; ql is warp-uniform and owned by this warp
+    uint32_t cnt = pend_n[ql];
+    if (cnt == 0) return;
+    uint32_t qg = q0 + ql;
+    float pd = (uint32_t)lane < cnt ? pend_d[ql][lane] : INFINITY;
+    uint32_t pi = (uint32_t)lane < cnt ? pend_i[ql][lane] : INVALID_ID;
+    int c = curbuf[ql];
+    size_t off = lbase + (size_t)qg * p.k;
+    float td; uint32_t ti;
+    merge_pending(pd, pi, p.list_d[c] + off, p.list_i[c] + off, p.list_d[c ^ 1] + off, p.list_i[c ^ 1] + off, p.k,
+                  lane, td, ti);
+    if (lane == 0) { curbuf[ql] = c ^ 1; pend_n[ql] = 0; thr_d[ql] = td; thr_i[ql] = ti; }
+    __syncwarp();
+  };
+
+  for (uint32_t b0 = b_begin; b0 < b_end; b0 += BT) {
+    float acc[4][8];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+      for (int j = 0; j < 8; j++) acc[i][j] = 0.f;
+
+    for (uint32_t d0 = 0; d0 < p.dim; d0 += DK) {
+      // stage Q (64 x 16) and B (128 x 16) transposed into shared memory, zero padded
+      {
+        int r = tid >> 2, dc = (tid & 3) * 4;
+        uint32_t qg = q0 + r;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          uint32_t d = d0 + dc + j;
+          Qs[dc + j][r] = (qg < p.nq && d < p.dim) ? __ldg(p.q + (size_t)qg * p.qstride + d) : 0.f;
+        }
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          int rb = r + h * 64;
+          uint32_t bg = b0 + rb;
+          if (bg < b_end && d0 + dc + 3 < p.dim + 0u && ((p.bstride & 3) == 0)) {
+            float4 v = __ldg(reinterpret_cast<const float4 *>(p.base + (size_t)bg * p.bstride + d0 + dc));
+            Bs[dc + 0][rb] = v.x; Bs[dc + 1][rb] = v.y; Bs[dc + 2][rb] = v.z; Bs[dc + 3][rb] = v.w;
+          } else {
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+              uint32_t d = d0 + dc + j;
+              Bs[dc + j][rb] = (bg < b_end && d < p.dim) ? __ldg(p.base + (size_t)bg * p.bstride + d) : 0.f;
+            }
+          }
+        }
+      }
+      __syncthreads();
+#pragma unroll
+      for (int d = 0; d < DK; d++) {
+        float4 qv = *reinterpret_cast<const float4 *>(&Qs[d][ty * 4]);
+        float4 bA = *reinterpret_cast<const float4 *>(&Bs[d][tx * 4]);
+        float4 bB = *reinterpret_cast<const float4 *>(&Bs[d][64 + tx * 4]);
+        const float qa[4] = {qv.x, qv.y, qv.z, qv.w};
+        const float ba[8] = {bA.x, bA.y, bA.z, bA.w, bB.x, bB.y, bB.z, bB.w};
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+#pragma unroll
+          for (int j = 0; j < 8; j++) {
+            if (p.ip) acc[i][j] = fmaf(qa[i], ba[j], acc[i][j]);
+            else { float df = qa[i] - ba[j]; acc[i][j] = fmaf(df, df, acc[i][j]); }
+          }
+      }
+      __syncthreads();
+    }
+
+    // ---- running top-k: this warp owns queries ty*4+i of its two ty values
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const int ql = ty * 4 + i;
+      const uint32_t qg = q0 + ql;
+#pragma unroll
+      for (int j = 0; j < 8; j++) {
+        // make room: at most 16 lanes push to one query per step
+        int qa = (warp * 2) * 4 + i, qb = (warp * 2 + 1) * 4 + i;
+        if (pend_n[qa] > PEND - 16) flush(qa);
+        if (pend_n[qb] > PEND - 16) flush(qb);
+        uint32_t bg = b0 + (j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4));
+        float d = p.ip ? 1.0f - acc[i][j] : acc[i][j];
+        bool pass = qg < p.nq && bg < b_end && !(p.exclude_self && bg == qg) &&
+                    lex_less(d, bg, thr_d[ql], thr_i[ql]);
+        if (pass) {
+          uint32_t s = atomicAdd(&pend_n[ql], 1u);
+          pend_d[ql][s] = d; pend_i[ql][s] = bg;
+        }
+        __syncwarp();
+      }
+    }
+  }
+  // final flush of this warp's 8 queries
+  for (int i = 0; i < 8; i++) {
+    int ql = warp * 8 + i;
+    if (q0 + ql < p.nq) flush(ql);
+  }
+  __syncwarp();
+  for (int i = 0; i < 8; i++) {
+    int ql = warp * 8 + i;
+    if (q0 + ql < p.nq && lane == 0) p.cur[(size_t)split * p.nq + q0 + ql] = curbuf[ql];
+  }
+}
+
+// pick the current list of every (split, query), merge the splits: out = k smallest of the union.
+__global__ void bf_finalize_kernel(const BfParams p, uint32_t *out_i, float *out_d) {
+  const uint32_t qg = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (qg >= p.nq) return;
+  const uint32_t total = p.splits * p.k;
+  auto get = [&](uint32_t e, float &d, uint32_t &i) {
+    uint32_t s = e / p.k, j = e % p.k;
+    int c = p.cur[(size_t)s * p.nq + qg];
+    size_t off = ((size_t)s * p.nq + qg) * p.k + j;
+    d = p.list_d[c][off]; i = p.list_i[c][off];
+  };
+  for (uint32_t e = lane; e < total; e += 32) {
+    float d; uint32_t i;
+    get(e, d, i);
+    uint32_t s = e / p.k, j = e % p.k;
+    // rank = own index within its sorted list + number of smaller entries in the other lists
+    uint32_t rank = j;
+    for (uint32_t s2 = 0; s2 < p.splits; s2++) {
+      if (s2 == s) continue;
+      uint32_t lo = 0, hi = p.k;
+      while (lo < hi) {
+        uint32_t mid = (lo + hi) >> 1;
+        float d2; uint32_t i2;
+        get(s2 * p.k + mid, d2, i2);
+        // INVALID entries (+inf, INVALID) are never "less" than anything valid; among themselves
+        // order by split so that ranks stay unique
+        bool less = (i2 == INVALID_ID && i == INVALID_ID) ? (s2 < s) : lex_less(d2, i2, d, i);
+        if (less) lo = mid + 1; else hi = mid;
+      }
+      rank += lo;
+    }
+    if (rank < p.k) {
+      out_i[(size_t)qg * p.k + rank] = i;
+      if (out_d) out_d[(size_t)qg * p.k + rank] = d;
+    }
+  }
+}
+
+}  // namespace
+
+int launch_bf_knn(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
+                  size_t k, bool exclude_self, uint32_t *ids, float *dists) {
+  if (nq == 0) return 0;
+  BfParams p = {};
+  p.base = ix->vec; p.bstride = ix->stride; p.n = (uint32_t)ix->n; p.dim = (uint32_t)ix->dim;
+  p.q = q; p.qstride = qstride; p.nq = (uint32_t)nq; p.k = (uint32_t)k;
+  p.ip = ix->metric == B200ANN_IP; p.exclude_self = exclude_self;
+  uint32_t qtiles = (uint32_t)((nq + QT - 1) / QT);
+  uint32_t want = 2u * (uint32_t)h->sm_count;  // aim for >= 2 CTAs per SM
+  uint32_t splits = qtiles >= want ? 1u : (want + qtiles - 1) / qtiles;
+  uint32_t max_splits = (uint32_t)((ix->n + 4 * BT - 1) / (4 * BT));
+  if (splits > max_splits) splits = max_splits;
+  if (splits < 1) splits = 1;
+  if (splits > 64) splits = 64;
+  p.splits = splits;
+  size_t cnt = (size_t)splits * nq * k;
+  DevBuf<float> ld0, ld1; DevBuf<uint32_t> li0, li1; DevBuf<uint8_t> cur;
+  CU_CHECK(h, ld0.alloc(cnt, h->stream)); CU_CHECK(h, ld1.alloc(cnt, h->stream));
+  CU_CHECK(h, li0.alloc(cnt, h->stream)); CU_CHECK(h, li1.alloc(cnt, h->stream));
+  CU_CHECK(h, cur.alloc((size_t)splits * nq, h->stream));
+  p.list_d[0] = ld0.p; p.list_d[1] = ld1.p; p.list_i[0] = li0.p; p.list_i[1] = li1.p; p.cur = cur.p;
+  dim3 grid(qtiles, splits);
+  bf_knn_kernel<<<grid, NT, 0, h->stream>>>(p);
+  h->launches++;
+  CU_CHECK(h, cudaGetLastError());
+  bf_finalize_kernel<<<(unsigned)((nq + 3) / 4), 128, 0, h->stream>>>(p, ids, dists);
+  h->launches++;
+  CU_CHECK(h, cudaGetLastError());
+  return 0;
+}

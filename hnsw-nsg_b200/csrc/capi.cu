@@ -1,0 +1,308 @@
+// extern "C" boundary of libb200ann.so (declared in include/b200ann.h). Host-side only: argument
+// checks, host<->device staging, stream/event bookkeeping. All arithmetic is in the kernels.
+#include <math.h>
+#include <string.h>
+#include "common.cuh"
+
+namespace {
+
+struct CallTimer {  // device time of the kernels of one API call
+  b200ann_handle *h;
+  explicit CallTimer(b200ann_handle *hh) : h(hh) { cudaEventRecord(h->ev0, h->stream); }
+  void stop() { cudaEventRecord(h->ev1, h->stream); }
+  cudaError_t sync() {
+    cudaError_t e = cudaStreamSynchronize(h->stream);
+    if (e == cudaSuccess) cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
+    return e;
+  }
+};
+
+template <typename T>
+cudaError_t upload(T **dst, const T *src, size_t count, cudaStream_t st) {
+  cudaError_t e = cudaMalloc((void **)dst, (count ? count : 1) * sizeof(T));
+  if (e != cudaSuccess) return e;
+  return cudaMemcpyAsync(*dst, src, count * sizeof(T), cudaMemcpyDefault, st);
+}
+
+__global__ void pad_rows_kernel(const float *src, size_t sstride, float *dst, size_t dstride, size_t n, size_t dim) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  size_t total = n * dstride;
+  for (; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    size_t r = i / dstride, c = i % dstride;
+    dst[i] = c < dim ? src[r * sstride + c] : 0.f;
+  }
+}
+
+__global__ void regraph_kernel(const uint32_t *src, size_t sstride, uint32_t *dst, size_t dstride, size_t n,
+                               uint32_t *width) {
+  size_t r = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (r >= n) return;
+  uint32_t deg = 0;
+  bool ended = false;
+  for (size_t c = 0; c < dstride; c++) {
+    uint32_t v = (c < sstride && !ended) ? src[r * sstride + c] : INVALID_ID;
+    if (v == INVALID_ID) ended = true; else deg++;
+    dst[r * dstride + c] = v;
+  }
+  if (width) atomicMax(width, deg);
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200ann_create(int device, b200ann_handle_t *out) {
+  if (!out) return B200ANN_ERR_ARG;
+  *out = nullptr;
+  int cnt = 0;
+  if (cudaGetDeviceCount(&cnt) != cudaSuccess || cnt <= 0 || device < 0 || device >= cnt) {
+    cudaGetLastError();
+    return B200ANN_ERR_CUDA;  // no CPU fallback: the product needs a CUDA device
+  }
+  b200ann_handle *h = new b200ann_handle;
+  h->device = device;
+  if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreate(&h->ev0) != cudaSuccess || cudaEventCreate(&h->ev1) != cudaSuccess) {
+    delete h;
+    return B200ANN_ERR_CUDA;
+  }
+  cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device);
+  *out = h;
+  return 0;
+}
+
+int b200ann_destroy(b200ann_handle_t h) {
+  if (!h) return 0;
+  cudaSetDevice(h->device);
+  cudaStreamSynchronize(h->stream);
+  cudaEventDestroy(h->ev0);
+  cudaEventDestroy(h->ev1);
+  cudaStreamDestroy(h->stream);
+  delete h;
+  return 0;
+}
+
+const char *b200ann_last_error(b200ann_handle_t h) { return h ? h->err.c_str() : "null handle"; }
+void *b200ann_stream(b200ann_handle_t h) { return h ? (void *)h->stream : nullptr; }
+uint64_t b200ann_launch_count(b200ann_handle_t h) { return h ? h->launches : 0; }
+float b200ann_last_kernel_ms(b200ann_handle_t h) { return h ? h->last_ms : 0.f; }
+
+int b200ann_set_visited_bits(b200ann_handle_t h, int bits) {
+  if (!h) return B200ANN_ERR_ARG;
+  if (bits < 5 || bits > 14) return set_err(h, B200ANN_ERR_ARG, "visited_bits must be in [5,14]");
+  h->visited_bits = bits;
+  return 0;
+}
+
+int b200ann_index_create(b200ann_handle_t h, const float *data, size_t n, size_t dim, size_t stride, int metric,
+                         b200ann_index_t *out) {
+  if (!h || !out) return B200ANN_ERR_ARG;
+  *out = nullptr;
+  if (!data || n == 0 || dim == 0 || stride < dim) return set_err(h, B200ANN_ERR_ARG, "index_create: bad data/n/dim/stride");
+  if (n >= 0x7fffffffu) return set_err(h, B200ANN_ERR_ARG, "index_create: n must be < 2^31");
+  if (metric != B200ANN_L2 && metric != B200ANN_IP) return set_err(h, B200ANN_ERR_ARG, "index_create: unknown metric");
+  CU_CHECK(h, cudaSetDevice(h->device));
+  b200ann_index *ix = new b200ann_index;
+  ix->h = h; ix->n = n; ix->dim = dim; ix->stride = (dim + 3) / 4 * 4; ix->metric = metric;
+  cudaError_t e = cudaMalloc((void **)&ix->vec, n * ix->stride * sizeof(float));
+  if (e == cudaSuccess) {
+    if (is_device_ptr(data)) {
+      pad_rows_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(data, stride, ix->vec, ix->stride, n, dim);
+      h->launches++;
+      e = cudaGetLastError();
+    } else {
+      if (ix->stride != dim) e = cudaMemsetAsync(ix->vec, 0, n * ix->stride * sizeof(float), h->stream);
+      if (e == cudaSuccess)
+        e = cudaMemcpy2DAsync(ix->vec, ix->stride * sizeof(float), data, stride * sizeof(float), dim * sizeof(float), n,
+                              cudaMemcpyHostToDevice, h->stream);
+    }
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+  if (e != cudaSuccess) {
+    if (ix->vec) cudaFree(ix->vec);
+    delete ix;
+    return set_err(h, B200ANN_ERR_CUDA, std::string("index_create: ") + cudaGetErrorString(e));
+  }
+  *out = ix;
+  return 0;
+}
+
+static void free_graph(b200ann_index *ix) {
+  if (ix->graph) cudaFree(ix->graph);
+  ix->graph = nullptr;
+}
+static void free_hnsw(b200ann_index *ix) {
+  if (ix->links0) cudaFree(ix->links0);
+  if (ix->levels) cudaFree(ix->levels);
+  if (ix->upper_ptr) cudaFree(ix->upper_ptr);
+  if (ix->upper_links) cudaFree(ix->upper_links);
+  if (ix->labels) cudaFree(ix->labels);
+  ix->links0 = ix->upper_ptr = ix->upper_links = nullptr;
+  ix->levels = nullptr; ix->labels = nullptr; ix->has_hnsw = false;
+}
+
+int b200ann_index_destroy(b200ann_index_t ix) {
+  if (!ix) return 0;
+  cudaSetDevice(ix->h->device);
+  cudaStreamSynchronize(ix->h->stream);
+  free_graph(ix);
+  free_hnsw(ix);
+  if (ix->vec) cudaFree(ix->vec);
+  delete ix;
+  return 0;
+}
+
+size_t b200ann_index_size(b200ann_index_t ix) { return ix ? ix->n : 0; }
+size_t b200ann_index_dim(b200ann_index_t ix) { return ix ? ix->dim : 0; }
+
+int b200ann_index_set_graph(b200ann_index_t ix, const uint32_t *graph, size_t gstride, uint32_t ep) {
+  if (!ix) return B200ANN_ERR_ARG;
+  b200ann_handle *h = ix->h;
+  if (!graph || gstride == 0 || ep >= ix->n) return set_err(h, B200ANN_ERR_ARG, "set_graph: bad graph/gstride/ep");
+  CU_CHECK(h, cudaSetDevice(h->device));
+  free_graph(ix);
+  size_t gs = (gstride + 7) / 8 * 8;  // 32-byte rows
+  InArg<uint32_t> in;
+  CU_CHECK(h, in.stage(graph, ix->n * gstride, h->stream));
+  CU_CHECK(h, cudaMalloc((void **)&ix->graph, ix->n * gs * sizeof(uint32_t)));
+  DevBuf<uint32_t> w;
+  CU_CHECK(h, w.alloc(1, h->stream));
+  CU_CHECK(h, cudaMemsetAsync(w.p, 0, 4, h->stream));
+  regraph_kernel<<<(unsigned)((ix->n + 127) / 128), 128, 0, h->stream>>>(in.d, gstride, ix->graph, gs, ix->n, w.p);
+  h->launches++;
+  CU_CHECK(h, cudaGetLastError());
+  CU_CHECK(h, cudaMemcpyAsync(&ix->width, w.p, 4, cudaMemcpyDeviceToHost, h->stream));
+  CU_CHECK(h, cudaStreamSynchronize(h->stream));
+  ix->gstride = gs; ix->ep = ep;
+  return 0;
+}
+
+int b200ann_index_get_graph(b200ann_index_t ix, uint32_t *graph, size_t gstride_out, uint32_t *ep, uint32_t *width) {
+  if (!ix) return B200ANN_ERR_ARG;
+  b200ann_handle *h = ix->h;
+  if (!ix->graph) return set_err(h, B200ANN_ERR_STATE, "get_graph: index has no graph");
+  if (ep) *ep = ix->ep;
+  if (width) *width = ix->width;
+  if (!graph) return 0;
+  if (gstride_out < ix->width) return set_err(h, B200ANN_ERR_ARG, "get_graph: gstride_out < width");
+  CU_CHECK(h, cudaSetDevice(h->device));
+  OutArg<uint32_t> out;
+  CU_CHECK(h, out.stage(graph, ix->n * gstride_out, h->stream));
+  regraph_kernel<<<(unsigned)((ix->n + 127) / 128), 128, 0, h->stream>>>(ix->graph, ix->gstride, out.d, gstride_out, ix->n, nullptr);
+  h->launches++;
+  CU_CHECK(h, cudaGetLastError());
+  CU_CHECK(h, out.finish(h->stream));
+  CU_CHECK(h, cudaStreamSynchronize(h->stream));
+  return 0;
+}
+
+int b200ann_index_set_hnsw(b200ann_index_t ix, const uint32_t *links0, size_t maxM0, const int32_t *levels,
+                           const uint32_t *upper_ptr, const uint32_t *upper_links, size_t upper_rows, size_t maxM,
+                           const uint64_t *labels, uint32_t ep, int maxlevel) {
+  if (!ix) return B200ANN_ERR_ARG;
+  b200ann_handle *h = ix->h;
+  if (!links0 || maxM0 == 0 || !levels || !upper_ptr || ep >= ix->n || maxlevel < 0 || (maxlevel > 0 && (!upper_links || maxM == 0)))
+    return set_err(h, B200ANN_ERR_ARG, "set_hnsw: bad arguments");
+  CU_CHECK(h, cudaSetDevice(h->device));
+  free_hnsw(ix);
+  size_t n = ix->n;
+  CU_CHECK(h, upload(&ix->links0, links0, n * maxM0, h->stream));
+  CU_CHECK(h, upload(&ix->levels, levels, n, h->stream));
+  CU_CHECK(h, upload(&ix->upper_ptr, upper_ptr, n, h->stream));
+  if (upper_rows) CU_CHECK(h, upload(&ix->upper_links, upper_links, upper_rows * maxM, h->stream));
+  if (labels) CU_CHECK(h, upload(&ix->labels, labels, n, h->stream));
+  CU_CHECK(h, cudaStreamSynchronize(h->stream));
+  ix->maxM0 = maxM0; ix->maxM = maxM ? maxM : 1; ix->upper_rows = upper_rows;
+  ix->hnsw_ep = ep; ix->maxlevel = maxlevel; ix->has_hnsw = true;
+  return 0;
+}
+
+int b200ann_bf_knn(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_t nq, size_t qstride, size_t k,
+                   uint32_t *ids, float *dists) {
+  if (!h || !ix) return B200ANN_ERR_ARG;
+  if (!q || !ids || k == 0 || qstride < ix->dim) return set_err(h, B200ANN_ERR_ARG, "bf_knn: bad q/ids/k/qstride");
+  if (nq == 0) return 0;
+  CU_CHECK(h, cudaSetDevice(h->device));
+  InArg<float> qin; OutArg<uint32_t> oi; OutArg<float> od;
+  CU_CHECK(h, qin.stage(q, nq * qstride, h->stream));
+  CU_CHECK(h, oi.stage(ids, nq * k, h->stream));
+  CU_CHECK(h, od.stage(dists, nq * k, h->stream));
+  CallTimer t(h);
+  int rc = launch_bf_knn(h, ix, qin.d, nq, qstride, k, false, oi.d, od.d);
+  t.stop();
+  if (rc) return rc;
+  CU_CHECK(h, oi.finish(h->stream));
+  CU_CHECK(h, od.finish(h->stream));
+  CU_CHECK(h, t.sync());
+  return 0;
+}
+
+int b200ann_knn_graph(b200ann_handle_t h, b200ann_index_t ix, size_t K, uint32_t *knn) {
+  if (!h || !ix) return B200ANN_ERR_ARG;
+  if (!knn || K == 0 || K >= ix->n) return set_err(h, B200ANN_ERR_ARG, "knn_graph: need 0 < K < n");
+  CU_CHECK(h, cudaSetDevice(h->device));
+  OutArg<uint32_t> oi;
+  CU_CHECK(h, oi.stage(knn, ix->n * K, h->stream));
+  CallTimer t(h);
+  int rc = launch_bf_knn(h, ix, ix->vec, ix->n, ix->stride, K, true, oi.d, nullptr);
+  t.stop();
+  if (rc) return rc;
+  CU_CHECK(h, oi.finish(h->stream));
+  CU_CHECK(h, t.sync());
+  return 0;
+}
+
+int b200ann_nsg_search(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_t nq, size_t qstride, size_t K,
+                       size_t L, uint32_t seed, uint32_t *ids, float *dists, uint32_t *stats) {
+  if (!h || !ix) return B200ANN_ERR_ARG;
+  if (!ix->graph) return set_err(h, B200ANN_ERR_STATE, "nsg_search: index has no graph (set_graph / nsg_build first)");
+  if (!q || !ids || K == 0 || L < K || L > ix->n || qstride < ix->dim)
+    return set_err(h, B200ANN_ERR_ARG, "nsg_search: need q, ids, 0 < K <= L <= n, qstride >= dim");
+  if (nq == 0) return 0;
+  CU_CHECK(h, cudaSetDevice(h->device));
+  InArg<float> qin; OutArg<uint32_t> oi; OutArg<float> od; OutArg<uint32_t> os;
+  CU_CHECK(h, qin.stage(q, nq * qstride, h->stream));
+  CU_CHECK(h, oi.stage(ids, nq * K, h->stream));
+  CU_CHECK(h, od.stage(dists, nq * K, h->stream));
+  CU_CHECK(h, os.stage(stats, nq * 2, h->stream));
+  CallTimer t(h);
+  int rc = launch_nsg_search(h, ix, qin.d, nq, qstride, K, L, seed, oi.d, od.d, os.d);
+  t.stop();
+  if (rc) return rc;
+  CU_CHECK(h, oi.finish(h->stream));
+  CU_CHECK(h, od.finish(h->stream));
+  CU_CHECK(h, os.finish(h->stream));
+  CU_CHECK(h, t.sync());
+  return 0;
+}
+
+int b200ann_hnsw_search(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_t nq, size_t qstride, size_t k,
+                        size_t ef, uint64_t *labels, float *dists, uint32_t *stats) {
+  if (!h || !ix) return B200ANN_ERR_ARG;
+  if (!ix->has_hnsw) return set_err(h, B200ANN_ERR_STATE, "hnsw_search: index has no HNSW graph (set_hnsw first)");
+  if (!q || !labels || !dists || k == 0 || qstride < ix->dim)
+    return set_err(h, B200ANN_ERR_ARG, "hnsw_search: need q, labels, dists, k > 0, qstride >= dim");
+  if (nq == 0) return 0;
+  CU_CHECK(h, cudaSetDevice(h->device));
+  InArg<float> qin; OutArg<uint64_t> ol; OutArg<float> od; OutArg<uint32_t> os;
+  CU_CHECK(h, qin.stage(q, nq * qstride, h->stream));
+  CU_CHECK(h, ol.stage(labels, nq * k, h->stream));
+  CU_CHECK(h, od.stage(dists, nq * k, h->stream));
+  CU_CHECK(h, os.stage(stats, nq * 2, h->stream));
+  CallTimer t(h);
+  int rc = launch_hnsw_search(h, ix, qin.d, nq, qstride, k, ef, ol.d, od.d, os.d);
+  t.stop();
+  if (rc) return rc;
+  CU_CHECK(h, ol.finish(h->stream));
+  CU_CHECK(h, od.finish(h->stream));
+  CU_CHECK(h, os.finish(h->stream));
+  CU_CHECK(h, t.sync());
+  // fewer than k results for some query -> error like bindings.cpp:646-648 (rows stay padded)
+  if (!ol.host) return 0;
+  for (size_t i = 0; i < nq; i++)
+    if (labels[i * k + k - 1] == ~(uint64_t)0)
+      return set_err(h, B200ANN_ERR_FEWER, "hnsw_search: fewer than k results for some query; raise ef or lower k");
+  return 0;
+}
+
+}  // extern "C"

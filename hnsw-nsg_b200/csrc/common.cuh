@@ -1,0 +1,127 @@
+// Shared host-side plumbing for the b200ann C ABI: handle / index structs, error capture,
+// host-or-device pointer staging. No torch types; plain CUDA runtime.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+#include "../../include/b200ann.h"
+
+#define INVALID_ID 0xFFFFFFFFu
+
+struct b200ann_handle {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  std::string err;
+  uint64_t launches = 0;
+  float last_ms = 0.f;
+  int visited_bits = 10;
+  int sm_count = 148;
+};
+
+struct b200ann_index {
+  b200ann_handle *h = nullptr;
+  size_t n = 0, dim = 0, stride = 0;  // stride in floats, multiple of 4
+  int metric = 0;
+  float *vec = nullptr;  // [n, stride]
+  // flat NSG / kNN graph
+  uint32_t *graph = nullptr;
+  size_t gstride = 0;
+  uint32_t ep = 0, width = 0;
+  // flat HNSW
+  uint32_t *links0 = nullptr;
+  size_t maxM0 = 0;
+  int32_t *levels = nullptr;
+  uint32_t *upper_ptr = nullptr, *upper_links = nullptr;
+  size_t upper_rows = 0, maxM = 0;
+  uint64_t *labels = nullptr;
+  uint32_t hnsw_ep = 0;
+  int maxlevel = -1;
+  bool has_hnsw = false;
+};
+
+inline int set_err(b200ann_handle *h, int code, const std::string &msg) {
+  if (h) h->err = msg;
+  return code;
+}
+
+#define CU_CHECK(h, call)                                                                         \
+  do {                                                                                            \
+    cudaError_t e__ = (call);                                                                     \
+    if (e__ != cudaSuccess) {                                                                     \
+      char b__[512];                                                                              \
+      snprintf(b__, sizeof b__, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, \
+               __LINE__);                                                                         \
+      return set_err(h, B200ANN_ERR_CUDA, b__);                                                   \
+    }                                                                                             \
+  } while (0)
+
+inline bool is_device_ptr(const void *p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+// RAII device scratch buffer (freed with the stream ordered allocator)
+template <typename T>
+struct DevBuf {
+  T *p = nullptr;
+  cudaStream_t s = nullptr;
+  cudaError_t alloc(size_t count, cudaStream_t st) {
+    s = st;
+    return cudaMallocAsync((void **)&p, (count ? count : 1) * sizeof(T), st);
+  }
+  ~DevBuf() {
+    if (p) cudaFreeAsync(p, s);
+  }
+};
+
+// Input staging: returns a device pointer for `src` (copying host memory to a scratch buffer).
+template <typename T>
+struct InArg {
+  DevBuf<T> buf;
+  const T *d = nullptr;
+  cudaError_t stage(const T *src, size_t count, cudaStream_t st) {
+    if (!src) { d = nullptr; return cudaSuccess; }
+    if (is_device_ptr(src)) { d = src; return cudaSuccess; }
+    cudaError_t e = buf.alloc(count, st);
+    if (e != cudaSuccess) return e;
+    d = buf.p;
+    return cudaMemcpyAsync(buf.p, src, count * sizeof(T), cudaMemcpyHostToDevice, st);
+  }
+};
+
+// Output staging: kernels write to .d; finish() copies back when the destination is host memory.
+template <typename T>
+struct OutArg {
+  DevBuf<T> buf;
+  T *d = nullptr, *dst = nullptr;
+  size_t count = 0;
+  bool host = false;
+  cudaError_t stage(T *out, size_t cnt, cudaStream_t st) {
+    dst = out; count = cnt;
+    if (!out) { d = nullptr; return cudaSuccess; }
+    if (is_device_ptr(out)) { d = out; return cudaSuccess; }
+    host = true;
+    cudaError_t e = buf.alloc(cnt, st);
+    d = buf.p;
+    return e;
+  }
+  cudaError_t finish(cudaStream_t st) {
+    if (host && dst) return cudaMemcpyAsync(dst, d, count * sizeof(T), cudaMemcpyDeviceToHost, st);
+    return cudaSuccess;
+  }
+};
+
+// kernel launchers implemented in the .cu files (all asynchronous on h->stream)
+int launch_nsg_search(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
+                      size_t K, size_t L, uint32_t seed, uint32_t *ids, float *dists, uint32_t *stats);
+int launch_hnsw_search(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
+                       size_t k, size_t ef, uint64_t *labels, float *dists, uint32_t *stats);
+int launch_bf_knn(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
+                  size_t k, bool exclude_self, uint32_t *ids, float *dists);

@@ -1,0 +1,83 @@
+// Team-of-lanes distance evaluation shared by every graph kernel.
+//
+// A vector row is nch = ceil(dim/4) float4 chunks (rows are stored with a 16-byte aligned, zero padded
+// stride). A team of TEAM consecutive lanes owns one row: lane t loads chunks t, t+TEAM, t+2*TEAM, ...
+// so each load instruction of a team touches TEAM*16 contiguous bytes (128 B for TEAM=8), and
+// accumulates x,y,z,w of each chunk in that order with fmaf. The TEAM partial sums are combined with
+// an xor butterfly, which leaves the same bits in every lane of the team (fp add is commutative).
+// oracle/oracle.c gpu_order() restates exactly this order, so GPU-vs-oracle comparisons are
+// bit-exact on arbitrary float data.
+//
+// Replaces: hnswlib::L2Sqr* / InnerProduct* (hnswlib/hnswlib/space_l2.h:6-205, space_ip.h:6-339) and
+// efanna2e::DistanceL2/DistanceInnerProduct::compare (CNNS/include/nsg/distance.h:25-227).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+// read-only, streaming 16-byte load: rows are gathered once per query, keep them out of L1
+__device__ __forceinline__ float4 ld_row16(const float4 *p) {
+  float4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p));
+  return v;
+}
+
+template <bool IP>
+__device__ __forceinline__ float acc4(float acc, const float4 &q, const float4 &v) {
+  if (IP) {
+    acc = fmaf(q.x, v.x, acc);
+    acc = fmaf(q.y, v.y, acc);
+    acc = fmaf(q.z, v.z, acc);
+    acc = fmaf(q.w, v.w, acc);
+  } else {
+    float d;
+    d = q.x - v.x; acc = fmaf(d, d, acc);
+    d = q.y - v.y; acc = fmaf(d, d, acc);
+    d = q.z - v.z; acc = fmaf(d, d, acc);
+    d = q.w - v.w; acc = fmaf(d, d, acc);
+  }
+  return acc;
+}
+
+template <int TEAM>
+__device__ __forceinline__ float team_reduce(float acc) {
+#pragma unroll
+  for (int off = TEAM / 2; off >= 1; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+  return acc;
+}
+
+// Distances of two rows per team in one go (2*NCH independent 16-byte loads in flight per lane).
+// r0/r1 may be nullptr (no row): the result is then unspecified and must be ignored by the caller.
+template <int TEAM, int NCH, bool IP>
+__device__ __forceinline__ void team_dist2(const float4 *r0, const float4 *r1, const float4 (&q)[NCH], int t,
+                                           int nch, float &d0, float &d1) {
+  float4 v0[NCH], v1[NCH];
+  const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int c = 0; c < NCH; c++) {
+    int ch = t + c * TEAM;
+    v0[c] = (r0 != nullptr && ch < nch) ? ld_row16(r0 + ch) : z;
+  }
+#pragma unroll
+  for (int c = 0; c < NCH; c++) {
+    int ch = t + c * TEAM;
+    v1[c] = (r1 != nullptr && ch < nch) ? ld_row16(r1 + ch) : z;
+  }
+  float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+  for (int c = 0; c < NCH; c++) {
+    int ch = t + c * TEAM;
+    if (ch < nch) {
+      a0 = acc4<IP>(a0, q[c], v0[c]);
+      a1 = acc4<IP>(a1, q[c], v1[c]);
+    }
+  }
+  a0 = team_reduce<TEAM>(a0);
+  a1 = team_reduce<TEAM>(a1);
+  d0 = IP ? 1.0f - a0 : a0;
+  d1 = IP ? 1.0f - a1 : a1;
+}
+
+// team size / chunks-per-lane rule shared by all launchers (and restated in tests via b200ann_dist_team)
+__host__ __device__ inline int dist_team_for_nch(int nch) { return nch <= 64 ? 8 : 32; }

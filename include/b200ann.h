@@ -1,0 +1,114 @@
+/* b200ann — C ABI of the B200-native hot path of Cookiecoolkid/hnsw-nsg.
+ *
+ * Everything behind this header is hand-written sm_100a CUDA (hnsw-nsg_b200/csrc). There is no CPU
+ * fallback: every entry point fails with B200ANN_ERR_CUDA when no CUDA device is usable.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative B200ANN_ERR_* code; the message is kept per
+ *     handle and read with b200ann_last_error() (the C++ shims re-throw it as std::runtime_error, the
+ *     reference's error convention: hnswlib/hnswlib/hnswalg.h:1178, :720).
+ *   - pointers marked [h|d] may be host or device memory (resolved with cudaPointerGetAttributes);
+ *     results are written to wherever the output pointer lives.
+ *   - vectors are fp32 row-major [n, stride] (stride in floats, >= dim); ids are u32; an index copies
+ *     the rows to HBM with stride rounded up to 4 floats (16 B) and zero padding.
+ *   - adjacency is the flat layout u32 [n, gstride], row i = out-neighbours in list order, padded
+ *     with B200ANN_INVALID.
+ *   - one handle per GPU and per host thread; calls on different handles run concurrently.
+ */
+#ifndef B200ANN_H
+#define B200ANN_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+#pragma GCC visibility push(default)
+
+#define B200ANN_INVALID 0xFFFFFFFFu
+
+enum { B200ANN_L2 = 0, B200ANN_IP = 1 }; /* L2Space / InnerProductSpace (1 - <a,b>) */
+
+enum {
+  B200ANN_OK = 0,
+  B200ANN_ERR_ARG = -1,   /* bad argument (message says which) */
+  B200ANN_ERR_CUDA = -2,  /* CUDA runtime error / no device */
+  B200ANN_ERR_STATE = -3, /* index has no graph of the requested kind */
+  B200ANN_ERR_FEWER = -4  /* fewer than k results for some query (bindings.cpp:646-648) */
+};
+
+typedef struct b200ann_handle *b200ann_handle_t;
+typedef struct b200ann_index *b200ann_index_t;
+
+/* ---- handle: device + stream + workspace + last error ------------------------------------ */
+int b200ann_create(int device, b200ann_handle_t *out);
+int b200ann_destroy(b200ann_handle_t h);
+const char *b200ann_last_error(b200ann_handle_t h);
+/* cudaStream_t the handle launches on (for CUDA-event timing by the caller) */
+void *b200ann_stream(b200ann_handle_t h);
+/* number of kernels this handle has launched since creation */
+uint64_t b200ann_launch_count(b200ann_handle_t h);
+/* milliseconds the kernels of the last search/build call took on the device (CUDA events) */
+float b200ann_last_kernel_ms(b200ann_handle_t h);
+
+/* ---- index: vectors (+ graphs) resident in HBM -------------------------------------------- */
+/* replaces: the data ownership of hnswlib::HierarchicalNSW (data_level0_memory_, hnswalg.h:130) and
+ * the borrowed `data_` of efanna2e::IndexNSG (CNNS/src/nsg/index_nsg.cpp:469,509) */
+int b200ann_index_create(b200ann_handle_t h, const float *data /*[h|d]*/, size_t n, size_t dim, size_t stride,
+                         int metric, b200ann_index_t *out);
+int b200ann_index_destroy(b200ann_index_t ix);
+size_t b200ann_index_size(b200ann_index_t ix);
+size_t b200ann_index_dim(b200ann_index_t ix);
+
+/* NSG / kNN flat graph: final_graph_ + ep_ (+ width) of efanna2e::IndexNSG (index_nsg.h:62-84);
+ * what IndexNSG::Load (index_nsg.cpp:51-68) or OptimizeGraph (:659-682) produce on the CPU */
+int b200ann_index_set_graph(b200ann_index_t ix, const uint32_t *graph /*[h|d]*/, size_t gstride, uint32_t ep);
+/* copy the graph back: graph [n, gstride_out] */
+int b200ann_index_get_graph(b200ann_index_t ix, uint32_t *graph /*[h|d]*/, size_t gstride_out, uint32_t *ep,
+                            uint32_t *width);
+
+/* HNSW graph in the flat layout: what HierarchicalNSW::loadIndex (hnswalg.h:716-822)
+ * holds in data_level0_memory_/linkLists_/element_levels_. upper_links [upper_rows, maxM]. */
+int b200ann_index_set_hnsw(b200ann_index_t ix, const uint32_t *links0, size_t maxM0, const int32_t *levels,
+                           const uint32_t *upper_ptr, const uint32_t *upper_links, size_t upper_rows,
+                           size_t maxM, const uint64_t *labels /* NULL = identity */, uint32_t ep,
+                           int maxlevel);
+
+/* ---- exact brute-force kNN ---------------------------------------------------------------- */
+/* replaces hnswlib::BruteforceSearch::searchKnn (bruteforce.h:106-135) and
+ * IndexGraph::generate_control_set (efanna_graph/src/index_graph.cpp:138-153), batched.
+ * ids/dists [nq,k] ascending by (distance,id); ties -> smaller id. Unfilled slots (k > n):
+ * B200ANN_INVALID / +inf. */
+int b200ann_bf_knn(b200ann_handle_t h, b200ann_index_t ix, const float *q /*[h|d]*/, size_t nq, size_t qstride,
+                   size_t k, uint32_t *ids /*[h|d]*/, float *dists /*[h|d] or NULL*/);
+/* exact kNN graph of the index's own rows, self excluded: knn [n,K] ascending (distance,id).
+ * The exact counterpart of IndexGraph::Build's output (index_graph.cpp:275-292). */
+int b200ann_knn_graph(b200ann_handle_t h, b200ann_index_t ix, size_t K, uint32_t *knn /*[h|d]*/);
+
+/* ---- graph search ------------------------------------------------------------------------- */
+/* replaces efanna2e::IndexNSG::Search / SearchWithOptGraph (index_nsg.cpp:506-568, :570-657) for a
+ * batch of queries. K results per query from a sorted pool of L (= "L_search"), seeds = first L
+ * out-neighbours of ep then pseudo-random ids (counter hash of (seed, query index, draw)).
+ * ids [nq,K]; dists [nq,K] or NULL (the reference returns ids only); stats [nq,2] u32 =
+ * {distance evaluations, expanded nodes} or NULL. */
+int b200ann_nsg_search(b200ann_handle_t h, b200ann_index_t ix, const float *q /*[h|d]*/, size_t nq,
+                       size_t qstride, size_t K, size_t L, uint32_t seed, uint32_t *ids /*[h|d]*/,
+                       float *dists /*[h|d]*/, uint32_t *stats /*[h|d]*/);
+
+/* replaces hnswlib::HierarchicalNSW::searchKnn (hnswalg.h:1270-1324: upper-layer greedy descent +
+ * searchBaseLayerST<true> :309-440) for a batch of queries, in the [nq,k] row shape of
+ * python_bindings/bindings.cpp:612-695. labels/dists ascending by (distance, internal id);
+ * beam = max(ef,k). Returns B200ANN_ERR_FEWER if some row has fewer than k results (rows are then
+ * padded with ~0 / +inf). */
+int b200ann_hnsw_search(b200ann_handle_t h, b200ann_index_t ix, const float *q /*[h|d]*/, size_t nq,
+                        size_t qstride, size_t k, size_t ef, uint64_t *labels /*[h|d]*/,
+                        float *dists /*[h|d]*/, uint32_t *stats /*[h|d]*/);
+
+/* tuning knob: log2 of the per-query visited-filter size in shared memory (default 10). */
+int b200ann_set_visited_bits(b200ann_handle_t h, int bits);
+
+#pragma GCC visibility pop
+#ifdef __cplusplus
+}
+#endif
+#endif

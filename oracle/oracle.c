@@ -38,7 +38,9 @@ enum {
   ORC_L2_EFANNA_AVX = 4, /* efanna2e::DistanceL2::compare __AVX__ branch, CNNS/include/nsg/distance.h:25-74 */
   ORC_L2_GPU = 5,        /* summation order of the CUDA kernels (team of lanes, fmaf, xor-butterfly) */
   ORC_IP_GPU = 6,        /* 1 - dot in the CUDA kernels' order */
-  ORC_FASTL2_EFANNA_AVX = 7 /* ||x||^2 - 2<q,x>, DistanceFastL2, distance.h:232-322 (needs norm; see orc_fastl2) */
+  ORC_FASTL2_EFANNA_AVX = 7, /* ||x||^2 - 2<q,x>, DistanceFastL2, distance.h:232-322 */
+  ORC_L2_SEQ_FMA = 8,    /* order of csrc/bf_knn.cu: sequential over the dimension with fmaf */
+  ORC_IP_SEQ_FMA = 9
 };
 
 /* space_l2.h:6-20 — sequential, multiply then add (no FMA: built with -ffp-contract=off) */
@@ -200,6 +202,16 @@ static float gpu_order(const float *a, const float *b, size_t dim, int team, int
   return ip ? 1.0f - lane[0] : lane[0];
 }
 
+/* csrc/bf_knn.cu accumulates one (query,row) pair sequentially over the dimension with fmaf */
+static float seq_fma(const float *a, const float *b, size_t dim, int ip) {
+  float acc = 0.f;
+  for (size_t i = 0; i < dim; i++) {
+    if (ip) acc = fmaf(a[i], b[i], acc);
+    else { float d = a[i] - b[i]; acc = fmaf(d, d, acc); }
+  }
+  return ip ? 1.0f - acc : acc;
+}
+
 EXPORT void orc_set_gpu_team(int team) { g_gpu_team = team; }
 
 EXPORT float orc_dist(int mode, const float *a, const float *b, size_t dim) {
@@ -211,6 +223,8 @@ EXPORT float orc_dist(int mode, const float *a, const float *b, size_t dim) {
     case ORC_L2_EFANNA_AVX: return l2_efanna_avx(a, b, dim);
     case ORC_L2_GPU: return gpu_order(a, b, dim, g_gpu_team, 0);
     case ORC_IP_GPU: return gpu_order(a, b, dim, g_gpu_team, 1);
+    case ORC_L2_SEQ_FMA: return seq_fma(a, b, dim, 0);
+    case ORC_IP_SEQ_FMA: return seq_fma(a, b, dim, 1);
     case ORC_FASTL2_EFANNA_AVX: /* distance.h:318-322 with norm = ||b||^2 (:232-258) */
       return -2 * dot_efanna_avx(a, b, dim) + dot_efanna_avx(b, b, dim);
   }

@@ -13,7 +13,8 @@ REF_DIR = os.path.join(ORACLE_DIR, "_ref")
 INVALID = 0xFFFFFFFF
 
 # oracle distance modes (oracle/oracle.c)
-L2_SCALAR, IP_SCALAR, L2_HNSW_AVX, IP_HNSW_AVX, L2_EFANNA_AVX, L2_GPU, IP_GPU, FASTL2_EFANNA_AVX = range(8)
+(L2_SCALAR, IP_SCALAR, L2_HNSW_AVX, IP_HNSW_AVX, L2_EFANNA_AVX, L2_GPU, IP_GPU, FASTL2_EFANNA_AVX, L2_SEQ_FMA,
+ IP_SEQ_FMA) = range(10)
 
 f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
 u32p = np.ctypeslib.ndpointer(np.uint32, flags="C_CONTIGUOUS")

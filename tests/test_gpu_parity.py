@@ -1,0 +1,245 @@
+"""Parity of the CUDA path (through the C ABI, libb200ann.so) against the oracle, the compiled
+reference (oracle/_ref, when present) and the golden fixtures. Bar: ids bit-exact; distances bit-exact
+against the oracle run in the kernels' summation order, and within 1e-5 relative of the reference's
+scalar order (BASELINE.json north_star)."""
+import importlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+import refutil as R
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(R.ROOT, "tests", "golden")
+REL_TOL = 1e-5  # north_star: distances within 1e-5 relative error
+
+
+@pytest.fixture(scope="module")
+def B():
+    return importlib.import_module("hnsw-nsg_b200")
+
+
+@pytest.fixture(scope="module")
+def H(B):
+    return B.Handle(0)
+
+
+def _relerr(a, b):
+    return np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-12))
+
+
+# ---------------------------------------------------------------- brute force
+@pytest.mark.parametrize("n,dim,nq,k,metric", [
+    (5000, 128, 200, 10, 0), (5000, 100, 130, 10, 1), (3000, 24, 70, 100, 0), (777, 7, 33, 5, 0),
+    (20000, 96, 64, 200, 0), (300, 960, 17, 10, 0), (50, 16, 9, 64, 0)])
+def test_bf_knn_vs_oracle(B, H, n, dim, nq, k, metric):
+    base = R.data_uniform(n, dim, 1) if metric == 0 else R.data_glove_like(n, dim, 1)
+    q = R.data_uniform(nq, dim, 2) if metric == 0 else R.data_glove_like(nq, dim, 2)
+    ix = B.Index(H, base, metric)
+    ids, d = ix.bf_knn(q, k)
+    oid, od = R.orc_bf_knn(base, q, k, R.L2_SEQ_FMA if metric == 0 else R.IP_SEQ_FMA)
+    assert (ids == oid).all()
+    assert (d == od).all()
+    sid, sd = R.orc_bf_knn(base, q, k, R.L2_SCALAR if metric == 0 else R.IP_SCALAR)
+    m = np.isfinite(sd)
+    if metric == 0:
+        assert _relerr(d[m], sd[m]) < REL_TOL
+    else:
+        assert np.max(np.abs(d[m] - sd[m])) < 1e-5  # 1 - dot: absolute, dot of unit vectors
+    assert (ids == sid).mean() > 0.999  # only fp near-ties may swap between summation orders
+
+
+def test_bf_knn_ties_smaller_id_wins(B, H):
+    rng = np.random.default_rng(3)
+    base = rng.integers(0, 3, (5000, 6)).astype(np.float32)
+    q = rng.integers(0, 3, (100, 6)).astype(np.float32)
+    ix = B.Index(H, base, 0)
+    ids, d = ix.bf_knn(q, 20)
+    oid, od = R.orc_bf_knn(base, q, 20, R.L2_SCALAR)  # integer data: every order is exact
+    assert (ids == oid).all() and (d == od).all()
+    if R.have_ref():
+        lab, rd = R.ref_bf_knn(base, q, 20, 0)
+        assert (lab.astype(np.uint32) == ids).all() and (rd == d).all()
+
+
+def test_bf_knn_sift_like_bit_exact_vs_reference(B, H):
+    """integer-valued SIFT-shaped data: GPU == oracle == compiled reference, ids and distances"""
+    base = R.data_sift_like(20000, 128, 1)
+    q = R.data_sift_like(300, 128, 2)
+    ix = B.Index(H, base, 0)
+    ids, d = ix.bf_knn(q, 10)
+    oid, od = R.orc_bf_knn(base, q, 10, R.L2_SCALAR)
+    assert (ids == oid).all() and (d == od).all()
+    if R.have_ref():
+        lab, rd = R.ref_bf_knn(base, q, 10, 0, lib="hnsw_avx")
+        assert (lab.astype(np.uint32) == ids).all() and (rd == d).all()
+
+
+def test_bf_knn_golden_updates(B, H):
+    """hnswlib/tests/cpp/data: gt.bin = exact top-5 by dot product"""
+    n, _, nq, dd, k = [int(x) for x in open(os.path.join(GOLD, "hnswlib_updates_config.txt")).read().split()]
+    base = np.fromfile(os.path.join(GOLD, "hnswlib_updates_batch_final.bin"), np.float32).reshape(n, dd)
+    q = np.fromfile(os.path.join(GOLD, "hnswlib_updates_queries.bin"), np.float32).reshape(nq, dd)
+    gt = np.fromfile(os.path.join(GOLD, "hnswlib_updates_gt.bin"), np.int32).reshape(nq, k)
+    ix = B.Index(H, base, 1)
+    ids, _ = ix.bf_knn(q, k)
+    assert R.recall(ids, gt) > 0.999
+
+
+def test_spaces_known_answers_gpu(B, H):
+    """hnswlib/tests/python/bindings_test_spaces.py:11-33 through the GPU distance paths"""
+    ka = json.load(open(os.path.join(GOLD, "spaces_known_answers.json")))
+    data1 = np.asarray(ka["data1"], np.float32)
+    for rd in ka["rightdims"][::4]:
+        for ld in ka["leftdims"][::2]:
+            d2 = np.ascontiguousarray(np.concatenate(
+                [np.zeros((5, ld), np.float32), data1, np.zeros((5, rd), np.float32)], axis=1))
+            for metric, key in ((0, "l2"), (1, "ip")):
+                ix = B.Index(H, d2, metric)
+                _, d = ix.bf_knn(d2[-1:], 5)
+                assert np.mean(np.abs(d[0] - np.array(ka[key]))) < ka["tol_mean_abs"]
+                ix.close()
+
+
+def test_knn_graph_excludes_self(B, H):
+    base = R.data_uniform(3000, 32, 5)
+    ix = B.Index(H, base, 0)
+    knn = ix.knn_graph(20)
+    oid, _ = R.orc_bf_knn(base, base, 21, R.L2_SEQ_FMA)
+    want = np.stack([row[row != i][:20] for i, row in enumerate(oid)])
+    assert (knn == want).all()
+
+
+# ---------------------------------------------------------------- NSG search
+def _knn_as_graph(base, K):
+    ids, _ = R.orc_bf_knn(base, base, K + 1, R.L2_SCALAR)
+    knn = np.stack([row[row != i][:K] for i, row in enumerate(ids)]).astype(np.uint32)
+    gs = (K + 7) // 8 * 8
+    g = np.full((base.shape[0], gs), R.INVALID, np.uint32)
+    g[:, :K] = knn
+    return g
+
+
+@pytest.mark.parametrize("n,dim,K,L,deg", [(4000, 128, 10, 40, 24), (4000, 128, 10, 100, 24), (3000, 100, 5, 20, 16),
+                                           (2500, 96, 100, 120, 30), (1500, 960, 10, 50, 20), (2000, 20, 1, 1, 8)])
+def test_nsg_search_vs_oracle(B, H, n, dim, K, L, deg):
+    """bit-exact ids and distances against the oracle run in the kernel's summation order, on float
+    data, with the seed-fill path exercised (L > deg(ep))"""
+    base = R.data_uniform(n, dim, 1)
+    q = R.data_uniform(150, dim, 2)
+    g = _knn_as_graph(base, deg)
+    ep = 17
+    ix = B.Index(H, base, 0)
+    ix.set_graph(g, ep)
+    ids, d, st = ix.nsg_search(q, K, L, seed=11, want_stats=True)
+    R.oracle().orc_set_gpu_team(B.dist_team(dim))
+    oid, od, ost = R.orc_nsg_search(base, g, ep, q, K, L, R.L2_GPU, rng_mode=1, seed=11, want_stats=True)
+    assert (ids == oid).all()
+    assert (d == od).all()
+    assert (st[:, 1] == ost[:, 1]).all()          # same nodes expanded
+    assert (st[:, 0] >= ost[:, 0]).all()          # forgetful visited filter may only add evaluations
+    # and against the reference's own summation order: same answers up to fp near-ties
+    sid, sd = R.orc_nsg_search(base, g, ep, q, K, L, R.L2_EFANNA_AVX, rng_mode=1, seed=11)
+    assert (ids == sid).mean() > 0.995
+    assert _relerr(d, sd) < REL_TOL or (ids != sid).any()
+
+
+@pytest.mark.parametrize("bits", [5, 8, 12])
+def test_nsg_search_visited_filter_size_does_not_change_results(B, bits):
+    h = B.Handle(0)
+    h.set_visited_bits(bits)
+    base = R.data_uniform(5000, 64, 1)
+    q = R.data_uniform(100, 64, 2)
+    g = _knn_as_graph(base, 20)
+    ix = B.Index(h, base, 0)
+    ix.set_graph(g, 3)
+    ids, d = ix.nsg_search(q, 10, 60, seed=1)
+    R.oracle().orc_set_gpu_team(8)
+    oid, od = R.orc_nsg_search(base, g, 3, q, 10, 60, R.L2_GPU, rng_mode=1, seed=1)
+    assert (ids == oid).all() and (d == od).all()
+
+
+@pytest.mark.skipif(not R.have_ref(), reason="needs oracle/_ref")
+def test_nsg_search_on_reference_built_graph(B, H, tmp_path):
+    """IndexNSG::Build by the unmodified reference -> .nsg file -> GPU search == reference Search on
+    integer-valued data (all summation orders exact), no seed fill (L <= deg(ep) not guaranteed, so
+    compare through the oracle with the product's seed hash as well)."""
+    n, dim = 6000, 128
+    base = R.data_sift_like(n, dim, 1)
+    q = R.data_sift_like(200, dim, 2)
+    ids0, _ = R.orc_bf_knn(base, base, 41, R.L2_SCALAR)
+    knn = np.stack([row[row != i][:40] for i, row in enumerate(ids0)]).astype(np.uint32)
+    kp, gp = str(tmp_path / "k.graph"), str(tmp_path / "g.nsg")
+    R.write_knn_graph(kp, knn)
+    R.ref_nsg_build(base, kp, 40, 30, 300, gp, seed=7, threads=1)
+    g, ep, width = R.parse_nsg(gp, n)
+    ix = B.Index(H, base, 0)
+    ix.set_graph(g, ep)
+    deg_ep = int((g[ep] != R.INVALID).sum())
+    L = min(deg_ep, 30)
+    ids, d = ix.nsg_search(q, 10, L, seed=0)
+    ref = R.RefNsg(base, gp)
+    rids = ref.search(q, 10, L, seed=1, threads=1)       # L <= deg(ep): no rand() involved
+    # integer data has exact distance ties: std::sort / equal-distance order may differ -> compare distances
+    truth, _ = R.orc_bf_knn(base, q, 10, R.L2_SCALAR)
+    assert abs(R.recall(ids, truth) - R.recall(rids, truth)) <= 0.005
+    oid, od = R.orc_nsg_search(base, g, ep, q, 10, L, R.L2_SCALAR, rng_mode=1, seed=0)
+    assert (ids == oid).all() and (d == od).all()
+
+
+# ---------------------------------------------------------------- HNSW search
+@pytest.mark.skipif(not R.have_ref(), reason="needs oracle/_ref to build the HNSW graph")
+@pytest.mark.parametrize("metric,dim,M", [(0, 128, 16), (1, 100, 32), (0, 20, 8)])
+def test_hnsw_search_vs_reference_and_oracle(B, H, tmp_path, metric, dim, M):
+    n = 6000
+    base = R.data_uniform(n, dim, 1) if metric == 0 else R.data_glove_like(n, dim, 1)
+    q = R.data_uniform(200, dim, 2) if metric == 0 else R.data_glove_like(200, dim, 2)
+    ref = R.RefHnsw(metric, dim, n, M, 100)
+    ref.add(base, label0=1000, threads=1)            # labels != internal ids
+    p = str(tmp_path / "h.bin")
+    ref.save(p)
+    Hh = R.parse_hnsw(p)
+    ix = B.Index(H, base, metric)
+    ix.set_hnsw(Hh["links0"], Hh["levels"], Hh["upper_ptr"], Hh["upper_links"], Hh["labels"], Hh["ep"], Hh["maxlevel"])
+    truth, _ = R.orc_bf_knn(base, q, 10, R.L2_SCALAR if metric == 0 else R.IP_SCALAR)
+    R.oracle().orc_set_gpu_team(B.dist_team(dim))
+    for ef in (10, 50, 200):
+        lab, d, st = ix.hnsw_search(q, 10, ef, want_stats=True)
+        ol, od, ost = R.orc_hnsw_search(base, Hh, q, 10, ef, R.L2_GPU if metric == 0 else R.IP_GPU, variant=1,
+                                        want_stats=True)
+        assert (lab == ol).all() and (d == od).all()
+        assert (st[:, 1] == ost[:, 1]).all() and (st[:, 0] >= ost[:, 0]).all()
+        rl, rd = ref.search(q, 10, ef, threads=1)       # reference, scalar summation order
+        assert (lab == rl).mean() > 0.995
+        rec_g = R.recall(lab - 1000, truth)
+        rec_r = R.recall(rl - 1000, truth)
+        assert abs(rec_g - rec_r) <= 0.005               # north_star: recall within 0.005 at matched ef
+
+
+@pytest.mark.skipif(not R.have_ref(), reason="needs oracle/_ref")
+def test_hnsw_fewer_than_k_raises(B, H, tmp_path):
+    base = R.data_uniform(30, 8, 1)
+    ref = R.RefHnsw(0, 8, 30, 4, 10)
+    ref.add(base, threads=1)
+    p = str(tmp_path / "h.bin")
+    ref.save(p)
+    Hh = R.parse_hnsw(p)
+    ix = B.Index(H, base, 0)
+    ix.set_hnsw(Hh["links0"], Hh["levels"], Hh["upper_ptr"], Hh["upper_links"], Hh["labels"], Hh["ep"], Hh["maxlevel"])
+    with pytest.raises(B.B200AnnError):
+        ix.hnsw_search(base[:3], 64, 64)                 # k > n
+
+
+def test_argument_errors(B, H):
+    base = R.data_uniform(100, 8, 1)
+    ix = B.Index(H, base, 0)
+    with pytest.raises(B.B200AnnError):
+        ix.nsg_search(base[:2], 5, 10)                   # no graph yet
+    g = _knn_as_graph(base, 8)
+    ix.set_graph(g, 0)
+    with pytest.raises(B.B200AnnError):
+        ix.nsg_search(base[:2], 20, 10)                  # K > L
+    ids, d = ix.nsg_search(np.zeros((0, 8), np.float32), 5, 10)   # empty batch
+    assert ids.shape == (0, 5)

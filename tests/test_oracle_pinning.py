@@ -1,0 +1,197 @@
+"""Pins oracle/oracle.c: against the reference's own known answers / golden files (tests/golden) and
+against the UNMODIFIED reference compiled into oracle/_ref (oracle/Makefile) on identical seeded inputs.
+CPU only."""
+import ctypes
+import json
+import os
+
+import numpy as np
+import pytest
+
+import refutil as R
+
+GOLD = os.path.join(R.ROOT, "tests", "golden")
+needs_ref = pytest.mark.skipif(not R.have_ref(), reason="oracle/_ref not built (needs /root/reference)")
+
+
+# ---------------------------------------------------------------- known answers of the reference's tests
+@pytest.mark.parametrize("mode_l2,mode_ip", [(R.L2_SCALAR, R.IP_SCALAR), (R.L2_HNSW_AVX, R.IP_HNSW_AVX),
+                                             (R.L2_GPU, R.IP_GPU), (R.L2_SEQ_FMA, R.IP_SEQ_FMA)])
+def test_spaces_known_answers(mode_l2, mode_ip):
+    """hnswlib/tests/python/bindings_test_spaces.py:11-33 — every SIMD/residual dispatch branch"""
+    ka = json.load(open(os.path.join(GOLD, "spaces_known_answers.json")))
+    data1 = np.asarray(ka["data1"], np.float32)
+    lib = R.oracle()
+    for rd in ka["rightdims"]:
+        for ld in ka["leftdims"]:
+            d2 = np.concatenate([np.zeros((5, ld), np.float32), data1, np.zeros((5, rd), np.float32)], axis=1)
+            d2 = np.ascontiguousarray(d2)
+            dim = d2.shape[1]
+            lib.orc_set_gpu_team(8 if (dim + 3) // 4 <= 64 else 32)
+            q = d2[ka["query_row"]]
+            l2 = sorted(lib.orc_dist(mode_l2, q, d2[i], dim) for i in range(5))
+            ip = sorted(lib.orc_dist(mode_ip, q, d2[i], dim) for i in range(5))
+            assert np.mean(np.abs(np.array(l2) - ka["l2"])) < ka["tol_mean_abs"]
+            assert np.mean(np.abs(np.array(ip) - ka["ip"])) < ka["tol_mean_abs"]
+
+
+def _golden_updates():
+    n, _, nq, d, k = [int(x) for x in open(os.path.join(GOLD, "hnswlib_updates_config.txt")).read().split()]
+    base = np.fromfile(os.path.join(GOLD, "hnswlib_updates_batch_final.bin"), np.float32).reshape(n, d)
+    q = np.fromfile(os.path.join(GOLD, "hnswlib_updates_queries.bin"), np.float32).reshape(nq, d)
+    gt = np.fromfile(os.path.join(GOLD, "hnswlib_updates_gt.bin"), np.int32).reshape(nq, k)
+    return base, q, gt
+
+
+def test_golden_updates_bruteforce():
+    """hnswlib/tests/cpp/data/{batch_final,queries,gt}.bin: exact top-5 by dot product (update_gen_data.py:25-26).
+    The oracle's exact IP scan must reproduce gt up to fp32 near-ties of the numpy generator."""
+    base, q, gt = _golden_updates()
+    ids, _ = R.orc_bf_knn(base, q[:200], 5, R.IP_SCALAR)
+    rec = R.recall(ids, gt[:200])
+    assert rec > 0.999, rec
+    # data are L2-normalised, so the L2 ranking equals the IP ranking
+    ids2, _ = R.orc_bf_knn(base, q[:200], 5, R.L2_SCALAR)
+    assert R.recall(ids2, gt[:200]) > 0.999
+
+
+# ---------------------------------------------------------------- InsertIntoPool edge cases
+def _pool(dists, ids):
+    K = len(dists)
+    return (np.array(list(ids) + [0], np.uint32), np.array(list(dists) + [0], np.float32),
+            np.array([1] * K + [0], np.int32), K)
+
+
+def test_insert_into_pool_semantics():
+    """CNNS/include/nsg/neighbor.h:107-135"""
+    lib = R.oracle()
+    ids, d, f, K = _pool([1, 2, 2, 3], [10, 11, 12, 13])
+    assert lib.orc_insert_into_pool(ids, d, f, K, 99, 0.5) == 0          # before the head
+    assert ids[:5].tolist() == [99, 10, 11, 12, 13]
+    ids, d, f, K = _pool([1, 2, 2, 3], [10, 11, 12, 13])
+    assert lib.orc_insert_into_pool(ids, d, f, K, 99, 4.0) == K          # beyond the tail -> slot K
+    ids, d, f, K = _pool([1, 2, 2, 3], [10, 11, 12, 13])
+    assert lib.orc_insert_into_pool(ids, d, f, K, 99, 2.0) == 3          # after every entry <= d
+    assert ids[:5].tolist() == [10, 11, 12, 99, 13]
+    ids, d, f, K = _pool([1, 2, 2, 3], [10, 11, 12, 13])
+    assert lib.orc_insert_into_pool(ids, d, f, K, 11, 2.0) == K + 1      # duplicate id among equal distances
+    ids, d, f, K = _pool([1, 2, 2, 3], [10, 11, 12, 13])
+    assert lib.orc_insert_into_pool(ids, d, f, K, 12, 2.0) == K + 1
+
+
+# ---------------------------------------------------------------- against the compiled reference
+@needs_ref
+@pytest.mark.parametrize("dim", [3, 8, 20, 33, 128, 100])
+def test_distances_vs_reference(dim):
+    rng = np.random.default_rng(dim)
+    a = rng.normal(size=(16, dim)).astype(np.float32)
+    b = rng.normal(size=(16, dim)).astype(np.float32)
+    lib = R.oracle()
+    for i in range(16):
+        for metric, ms, ma in ((0, R.L2_SCALAR, R.L2_HNSW_AVX), (1, R.IP_SCALAR, R.IP_HNSW_AVX)):
+            assert lib.orc_dist(ms, a[i], b[i], dim) == R.reflib("hnsw").ref_dist(metric, a[i], b[i], dim)
+            assert lib.orc_dist(ma, a[i], b[i], dim) == R.reflib("hnsw_avx").ref_dist(metric, a[i], b[i], dim)
+        if dim % 8 == 0:  # efanna's AVX path over-reads unless rows are padded to x8 (util.h data_align)
+            assert lib.orc_dist(R.L2_EFANNA_AVX, a[i], b[i], dim) == R.reflib("nsg").ref_nsg_dist_l2(a[i], b[i], dim)
+
+
+@needs_ref
+@pytest.mark.parametrize("metric,mode", [(0, R.L2_SCALAR), (1, R.IP_SCALAR)])
+def test_bruteforce_vs_reference(metric, mode):
+    base = R.data_uniform(3000, 24, 1)
+    q = R.data_uniform(40, 24, 2)
+    lab, d = R.ref_bf_knn(base, q, 10, metric)
+    ids, d2 = R.orc_bf_knn(base, q, 10, mode)
+    assert (lab.astype(np.uint32) == ids).all() and (d == d2).all()
+
+
+@needs_ref
+def test_bruteforce_ties_vs_reference():
+    """integer data with many exact ties: smaller id must win (bruteforce.h:119-131)"""
+    rng = np.random.default_rng(3)
+    base = rng.integers(0, 3, (2000, 6)).astype(np.float32)
+    q = rng.integers(0, 3, (30, 6)).astype(np.float32)
+    lab, d = R.ref_bf_knn(base, q, 15, 0)
+    ids, d2 = R.orc_bf_knn(base, q, 15, R.L2_SCALAR)
+    assert (lab.astype(np.uint32) == ids).all() and (d == d2).all()
+
+
+@pytest.fixture(scope="module")
+def hnsw_case(tmp_path_factory):
+    base = R.data_uniform(4000, 32, 1)
+    q = R.data_uniform(100, 32, 2)
+    h = R.RefHnsw(0, 32, 4000, 16, 200)
+    h.add(base, threads=1)
+    p = str(tmp_path_factory.mktemp("hnsw") / "h.bin")
+    h.save(p)
+    return base, q, h, R.parse_hnsw(p)
+
+
+@needs_ref
+@pytest.mark.parametrize("ef", [10, 40, 200])
+def test_hnsw_search_vs_reference(hnsw_case, ef):
+    """oracle searchKnn (both formulations) == HierarchicalNSW::searchKnn, bit for bit"""
+    base, q, h, H = hnsw_case
+    assert (H["vectors"] == base).all()
+    rl, rd = h.search(q, 10, ef, threads=1)
+    for variant in (0, 1):
+        ol, od = R.orc_hnsw_search(base, H, q, 10, ef, R.L2_SCALAR, variant=variant)
+        assert (rl == ol).all() and (rd == od).all()
+
+
+@pytest.fixture(scope="module")
+def nsg_case(tmp_path_factory):
+    n, dim = 3000, 24
+    base = R.data_uniform(n, dim, 1)
+    q = R.data_uniform(64, dim, 2)
+    ids, _ = R.orc_bf_knn(base, base, 41, R.L2_EFANNA_AVX)
+    knn = np.stack([row[row != i][:40] for i, row in enumerate(ids)]).astype(np.uint32)
+    d = tmp_path_factory.mktemp("nsg")
+    kp, gp = str(d / "k.graph"), str(d / "g.nsg")
+    R.write_knn_graph(kp, knn)
+    R.ref_nsg_build(base, kp, 40, 20, 200, gp, seed=7, threads=1)
+    g, ep, width = R.parse_nsg(gp, n)
+    return base, q, knn, g, ep, width, gp
+
+
+@needs_ref
+@pytest.mark.parametrize("L", [10, 30, 64])
+def test_nsg_search_vs_reference(nsg_case, L):
+    """oracle beam search == IndexNSG::Search incl. the rand() seed fill (srand-synchronised)"""
+    base, q, knn, g, ep, width, gp = nsg_case
+    ix = R.RefNsg(base, gp)
+    rids = ix.search(q, 10, L, seed=5, threads=1)
+    ctypes.CDLL(None).srand(5)
+    oids, _ = R.orc_nsg_search(base, g, ep, q, 10, L, R.L2_EFANNA_AVX, rng_mode=0)
+    assert (rids == oids).all()
+
+
+@needs_ref
+def test_nsg_search_optgraph_vs_reference(nsg_case):
+    """SearchWithOptGraph ranks by ||x||^2 - 2<q,x>: same ids as the L2 search up to fp near-ties"""
+    base, q, knn, g, ep, width, gp = nsg_case
+    ix = R.RefNsg(base, gp)
+    ix.optimize()
+    rids = ix.search_opt(q, 10, 30, seed=5, threads=1)
+    ctypes.CDLL(None).srand(5)
+    oids, _ = R.orc_nsg_search(base, g, ep, q, 10, 30, R.L2_EFANNA_AVX, rng_mode=0)
+    assert (rids == oids).mean() > 0.99
+
+
+def test_hnsw_pool_equals_twoheap_on_ties():
+    """the single-pool form may differ from the two heaps only through distance ties at the eviction
+    boundary; on heavily tied integer data the returned distance lists must still agree"""
+    if not R.have_ref():
+        pytest.skip("needs oracle/_ref to build an HNSW graph")
+    rng = np.random.default_rng(9)
+    base = rng.integers(0, 4, (2000, 8)).astype(np.float32)
+    q = rng.integers(0, 4, (50, 8)).astype(np.float32)
+    h = R.RefHnsw(0, 8, 2000, 8, 50)
+    h.add(base, threads=1)
+    import tempfile
+    p = os.path.join(tempfile.mkdtemp(), "h.bin")
+    h.save(p)
+    H = R.parse_hnsw(p)
+    _, d0 = R.orc_hnsw_search(base, H, q, 5, 20, R.L2_SCALAR, variant=0)
+    _, d1 = R.orc_hnsw_search(base, H, q, 5, 20, R.L2_SCALAR, variant=1)
+    assert np.mean(d0 == d1) > 0.95

@@ -208,7 +208,9 @@ struct Beam {
         uint32_t r = 0;
         for (uint32_t j = 0; j < m; j++) {
           float dj = cand_d[j]; uint32_t ij = cand_i[j];
-          r += (dj < di || (dj == di && ij < ii)) ? 1u : 0u;
+          // position breaks (distance,id) ties: a reference-built row can list an id twice
+          // (InterInsert leaves stale tail entries, index_nsg.cpp:399-404) and Search keeps both seeds
+          r += (dj < di || (dj == di && (ij < ii || (ij == ii && j < i)))) ? 1u : 0u;
         }
         pool_d[r] = di; pool_i[r] = ii | FLAG;
         tab[slot(ii)] = ii;

@@ -378,7 +378,7 @@ typedef struct {
 
 static unsigned nsg_beam(const orc_index *ix, uint32_t ep, const float *query, unsigned L_in, int rng_mode,
                          uint32_t seed, uint32_t qidx, uint8_t *flags, orc_nb *retset, nb_vec *full,
-                         uint64_t *stats) {
+                         int full_seeds, uint64_t *stats) {
   unsigned L = 0;
   uint32_t *init_ids = (uint32_t *)malloc(sizeof(uint32_t) * (L_in ? L_in : 1));
   const uint32_t *eprow = ix->graph + (size_t)ep * ix->gstride;
@@ -401,7 +401,7 @@ static unsigned nsg_beam(const orc_index *ix, uint32_t ep, const float *query, u
     uint32_t id = init_ids[i];
     float d = orc_dist(ix->mode, ix->data + ix->stride * (size_t)id, query, ix->dim);
     retset[i].id = id; retset[i].distance = d; retset[i].flag = 1;
-    if (full) nbv_push(full, retset[i]);
+    if (full && full_seeds) nbv_push(full, retset[i]); /* only the flags overload records seeds (:250) */
     if (stats) stats[0]++;
   }
   free(init_ids);
@@ -451,7 +451,7 @@ EXPORT int orc_nsg_search(const float *data, size_t n, size_t dim, size_t stride
 #pragma omp for schedule(dynamic, 8)
     for (long qi = 0; qi < (long)nq; qi++) {
       memset(flags, 0, n);
-      nsg_beam(&ix, ep, q + (size_t)qi * qstride, L, rng_mode, seed, (uint32_t)qi, flags, retset, NULL,
+      nsg_beam(&ix, ep, q + (size_t)qi * qstride, L, rng_mode, seed, (uint32_t)qi, flags, retset, NULL, 0,
                stats ? stats + 2 * qi : NULL);
       for (unsigned i = 0; i < K; i++) { /* :565-567 */
         ids[(size_t)qi * K + i] = retset[i].id;
@@ -639,4 +639,285 @@ EXPORT int orc_hnsw_search(const float *data, size_t n, size_t dim, size_t strid
     free(visited); free(top); free(cand); free(expd);
   }
   return 0;
+}
+
+/* ================================================================== NSG build */
+/* IndexNSG::Build (CNNS/src/nsg/index_nsg.cpp:465-504) phase by phase. Graphs are flat u32 [n,gstride]
+ * rows padded with ORC_INVALID; the cut graph (SimpleNeighbor[nd*R], :471) is two flat arrays
+ * cut_ids/cut_d [n,R] whose unused tail carries ORC_INVALID / -1 (the reference only writes the -1
+ * sentinel, :352-354). */
+
+/* IndexNSG::init_graph (:287-303): centroid by sequential fp32 accumulation over rows, divided by
+ * nd_; ep0 is the reference's `rand() % nd_` (:299, drawn by the caller); navigating node = nearest
+ * pool entry of a beam search for the centroid started at ep0. */
+EXPORT uint32_t orc_nsg_init_ep(const float *data, size_t n, size_t dim, size_t stride, const uint32_t *graph,
+                                unsigned gstride, uint32_t ep0, unsigned L, int mode, int rng_mode, uint32_t seed,
+                                float *center_out) {
+  float *center = (float *)calloc(dim, sizeof(float));
+  for (size_t i = 0; i < n; i++)
+    for (size_t j = 0; j < dim; j++) center[j] += data[i * stride + j];
+  for (size_t j = 0; j < dim; j++) center[j] /= (float)(unsigned)n;
+  if (center_out) memcpy(center_out, center, dim * sizeof(float));
+  orc_index ix = {data, n, dim, stride, graph, gstride, mode};
+  uint8_t *flags = (uint8_t *)calloc(n, 1);
+  orc_nb *retset = (orc_nb *)malloc(sizeof(orc_nb) * (L + 1));
+  nsg_beam(&ix, ep0, center, L, rng_mode, seed, (uint32_t)n, flags, retset, NULL, 0, NULL);
+  uint32_t ep = retset[0].id;
+  free(center); free(flags); free(retset);
+  return ep;
+}
+
+/* the occlusion rule shared by sync_prune (:328-345) and InterInsert (:386-404): scan `pool`
+ * (ascending) from index `start`, keep p iff no kept r has p.id == r.id or d(r,p) < d(q,p);
+ * stop at `range` kept, at the pool end, or at index maxc. res must hold `range` entries. */
+static unsigned occlude_scan(const orc_index *ix, const orc_nb *pool, size_t npool, size_t start, size_t maxc,
+                             unsigned range, orc_nb *res, uint64_t *n_eval) {
+  unsigned nres = 0;
+  if (start >= npool) return 0;
+  res[nres++] = pool[start];
+  while (nres < range && (++start) < npool && start < maxc) {
+    const orc_nb *p = &pool[start];
+    int occ = 0;
+    for (unsigned t = 0; t < nres; t++) {
+      if (p->id == res[t].id) { occ = 1; break; }
+      float djk = orc_dist(ix->mode, ix->data + ix->stride * (size_t)res[t].id,
+                           ix->data + ix->stride * (size_t)p->id, ix->dim);
+      if (n_eval) (*n_eval)++;
+      if (djk < p->distance) { occ = 1; break; }
+    }
+    if (!occ) res[nres++] = *p;
+  }
+  return nres;
+}
+
+/* Link, first loop (:437-457): per node get_neighbors (flags overload, :218-285) over the kNN graph
+ * then sync_prune (:305-355). stats [n,3] = {beam distance evaluations, expanded nodes, prune
+ * distance evaluations incl. the own-list additions} or NULL.
+ * std::sort(pool) (:323) is unstable on equal distances; the oracle orders them by id. */
+EXPORT int orc_nsg_link(const float *data, size_t n, size_t dim, size_t stride, const uint32_t *knn,
+                        unsigned kstride, uint32_t ep, unsigned L, unsigned R, unsigned C, int mode, int rng_mode,
+                        uint32_t seed, uint32_t *cut_ids, float *cut_d, uint64_t *stats) {
+  orc_index ix = {data, n, dim, stride, knn, kstride, mode};
+  if (stats) memset(stats, 0, sizeof(uint64_t) * 3 * n);
+#pragma omp parallel if (rng_mode != 0)
+  {
+    uint8_t *flags = (uint8_t *)malloc(n);
+    orc_nb *retset = (orc_nb *)malloc(sizeof(orc_nb) * (L + 1));
+    orc_nb *res = (orc_nb *)malloc(sizeof(orc_nb) * (R + 1));
+    nb_vec full = {0, 0, 0};
+#pragma omp for schedule(dynamic, 16)
+    for (long q = 0; q < (long)n; q++) {
+      uint64_t st[2] = {0, 0}, npr = 0;
+      memset(flags, 0, n);
+      full.n = 0;
+      nsg_beam(&ix, ep, data + stride * (size_t)q, L, rng_mode, seed, (uint32_t)q, flags, retset, &full, 1, st);
+      const uint32_t *row = knn + (size_t)q * kstride;
+      for (unsigned m = 0; m < kstride && row[m] != ORC_INVALID; m++) { /* :314-321 */
+        uint32_t id = row[m];
+        if (flags[id]) continue;
+        orc_nb nb = {id, orc_dist(mode, data + stride * (size_t)q, data + stride * (size_t)id, dim), 1};
+        npr++;
+        nbv_push(&full, nb);
+      }
+      qsort(full.v, full.n, sizeof(orc_nb), nb_cmp);
+      size_t start = 0;
+      if (full.n && full.v[0].id == (uint32_t)q) start++; /* :326 */
+      unsigned nres = occlude_scan(&ix, full.v, full.n, start, C, R, res, &npr);
+      for (unsigned t = 0; t < R; t++) {
+        cut_ids[(size_t)q * R + t] = t < nres ? res[t].id : ORC_INVALID;
+        cut_d[(size_t)q * R + t] = t < nres ? res[t].distance : -1.0f;
+      }
+      if (stats) { stats[3 * q] = st[0]; stats[3 * q + 1] = st[1]; stats[3 * q + 2] = npr; }
+    }
+    free(flags); free(retset); free(res); free(full.v);
+  }
+  return 0;
+}
+
+/* IndexNSG::InterInsert over all nodes (:357-424, called serially from Link :459-462 because the
+ * `omp for` there is orphaned).
+ * variant 0 — the reference, statement for statement, in node order, in place; including its quirk
+ *   that a re-pruned row shorter than R keeps its stale tail (no -1 is written after :399-404).
+ * variant 1 — the order-independent batch form the CUDA build uses: for every node `des`,
+ *   candidates = its own sync_prune row + every n whose sync_prune row lists des (and that des does
+ *   not list itself), each with the distance sync_prune stored; if they fit in R the reverse
+ *   candidates are appended in ascending n (what the serial form does when no row overflows),
+ *   otherwise the candidates are sorted by (distance,id) and pruned with the occlusion rule.
+ *   Reads the sync_prune rows only (snapshot), writes new rows; rows are -1/INVALID terminated. */
+EXPORT int orc_nsg_interinsert(const float *data, size_t n, size_t dim, size_t stride, unsigned R, int mode,
+                               int variant, uint32_t *cut_ids, float *cut_d, uint64_t *n_eval_out) {
+  orc_index ix = {data, n, dim, stride, NULL, 0, mode};
+  uint64_t n_eval = 0;
+  if (variant == 0) {
+    orc_nb *tmp = (orc_nb *)malloc(sizeof(orc_nb) * (R + 2));
+    orc_nb *res = (orc_nb *)malloc(sizeof(orc_nb) * (R + 2));
+    for (size_t nn = 0; nn < n; nn++) {
+      uint32_t *src_i = cut_ids + nn * R; float *src_d = cut_d + nn * R;
+      for (size_t i = 0; i < R; i++) {
+        if (src_d[i] == -1) break;
+        orc_nb sn = {(uint32_t)nn, src_d[i], 1};
+        size_t des = src_i[i];
+        uint32_t *des_i = cut_ids + des * R; float *des_d = cut_d + des * R;
+        unsigned nt = 0; int dup = 0;
+        for (size_t j = 0; j < R; j++) {
+          if (des_d[j] == -1) break;
+          if ((uint32_t)nn == des_i[j]) { dup = 1; break; }
+          tmp[nt].id = des_i[j]; tmp[nt].distance = des_d[j]; tmp[nt].flag = 1; nt++;
+        }
+        if (dup) continue;
+        tmp[nt++] = sn;
+        if (nt > R) {
+          qsort(tmp, nt, sizeof(orc_nb), nb_cmp);
+          unsigned nres = occlude_scan(&ix, tmp, nt, 0, (size_t)-1, R, res, &n_eval);
+          for (unsigned t = 0; t < nres; t++) { des_i[t] = res[t].id; des_d[t] = res[t].distance; }
+        } else {
+          for (unsigned t = 0; t < R; t++)
+            if (des_d[t] == -1) {
+              des_i[t] = sn.id; des_d[t] = sn.distance;
+              if (t + 1 < R) des_d[t + 1] = -1;
+              break;
+            }
+        }
+      }
+    }
+    free(tmp); free(res);
+  } else {
+    /* reverse lists (CSR by destination, sources ascending) from the snapshot */
+    size_t *off = (size_t *)calloc(n + 1, sizeof(size_t));
+    for (size_t i = 0; i < n; i++)
+      for (unsigned j = 0; j < R && cut_d[i * R + j] != -1; j++) off[cut_ids[i * R + j] + 1]++;
+    for (size_t i = 0; i < n; i++) off[i + 1] += off[i];
+    size_t *fill = (size_t *)malloc(sizeof(size_t) * n);
+    memcpy(fill, off, sizeof(size_t) * n);
+    orc_nb *rev = (orc_nb *)malloc(sizeof(orc_nb) * (off[n] ? off[n] : 1));
+    for (size_t i = 0; i < n; i++)
+      for (unsigned j = 0; j < R && cut_d[i * R + j] != -1; j++) {
+        orc_nb e = {(uint32_t)i, cut_d[i * R + j], 1};
+        rev[fill[cut_ids[i * R + j]]++] = e;
+      }
+    uint32_t *new_i = (uint32_t *)malloc(sizeof(uint32_t) * n * R);
+    float *new_d = (float *)malloc(sizeof(float) * n * R);
+#pragma omp parallel reduction(+ : n_eval)
+    {
+      nb_vec cand = {0, 0, 0};
+      orc_nb *res = (orc_nb *)malloc(sizeof(orc_nb) * (R + 1));
+#pragma omp for schedule(dynamic, 64)
+      for (long des = 0; des < (long)n; des++) {
+        cand.n = 0;
+        unsigned own = 0;
+        for (unsigned j = 0; j < R && cut_d[(size_t)des * R + j] != -1; j++, own++) {
+          orc_nb e = {cut_ids[(size_t)des * R + j], cut_d[(size_t)des * R + j], 1};
+          nbv_push(&cand, e);
+        }
+        for (size_t e = off[des]; e < off[des + 1]; e++) {
+          int dup = 0;
+          for (unsigned j = 0; j < own; j++) dup |= cand.v[j].id == rev[e].id;
+          if (!dup) nbv_push(&cand, rev[e]);
+        }
+        unsigned nres;
+        const orc_nb *src;
+        if (cand.n <= R) { nres = (unsigned)cand.n; src = cand.v; }
+        else {
+          qsort(cand.v, cand.n, sizeof(orc_nb), nb_cmp);
+          uint64_t ne = 0;
+          nres = occlude_scan(&ix, cand.v, cand.n, 0, (size_t)-1, R, res, &ne);
+          n_eval += ne;
+          src = res;
+        }
+        for (unsigned t = 0; t < R; t++) {
+          new_i[(size_t)des * R + t] = t < nres ? src[t].id : ORC_INVALID;
+          new_d[(size_t)des * R + t] = t < nres ? src[t].distance : -1.0f;
+        }
+      }
+      free(cand.v); free(res);
+    }
+    memcpy(cut_ids, new_i, sizeof(uint32_t) * n * R);
+    memcpy(cut_d, new_d, sizeof(float) * n * R);
+    free(off); free(fill); free(rev); free(new_i); free(new_d);
+  }
+  if (n_eval_out) *n_eval_out = n_eval;
+  return 0;
+}
+
+/* compaction of the cut graph into adjacency rows (:473-487), with the reference's length rule
+ * (pool_size = index of the last entry before the first -1, plus one). graph [n,gstride], gstride >= R. */
+EXPORT int orc_nsg_cut_to_graph(const uint32_t *cut_ids, const float *cut_d, size_t n, unsigned R, uint32_t *graph,
+                                unsigned gstride) {
+  for (size_t i = 0; i < n; i++) {
+    unsigned pool_size = 0;
+    for (unsigned j = 0; j < R; j++) {
+      if (cut_d[i * R + j] == -1) break;
+      pool_size = j;
+    }
+    pool_size++;
+    for (unsigned j = 0; j < gstride; j++) graph[i * gstride + j] = j < pool_size ? cut_ids[i * R + j] : ORC_INVALID;
+  }
+  return 0;
+}
+
+/* IndexNSG::tree_grow (:750-764) with DFS (:684-710) and findroot (:712-749), on a flat graph
+ * [n,gstride] (in place). DFS only computes the set reachable from `root`, so the traversal order
+ * is immaterial and the oracle marks reachability with an explicit stack. findroot: the first
+ * unreached id in index order; get_neighbors (first overload, :150-216 — its fullset holds the
+ * expanded nodes' neighbours only, not the seeds) over the current graph; sort; the first reached
+ * pool entry becomes the parent and gains the edge parent -> id.
+ * Deviation forced by the flat layout: a parent must have a free slot (degree < gstride); the
+ * reference's rows are unbounded vectors. With gstride >= the reference's final width both agree.
+ * When no pool entry qualifies the reference draws rand() until it hits a reached node (:739-746);
+ * rng_mode 1 draws seed_hash(seed, id, 0x10000 + t) instead. Returns the number of added edges;
+ * *width_out = max degree (:759-763, never below `width_in` = R, :310). */
+static void mark_reachable(const uint32_t *graph, unsigned gstride, uint8_t *flag, uint32_t root, size_t *cnt,
+                           uint32_t *stack) {
+  size_t sp = 0;
+  if (!flag[root]) { flag[root] = 1; (*cnt)++; }
+  stack[sp++] = root;
+  while (sp) {
+    uint32_t v = stack[--sp];
+    const uint32_t *row = graph + (size_t)v * gstride;
+    for (unsigned i = 0; i < gstride && row[i] != ORC_INVALID; i++)
+      if (!flag[row[i]]) { flag[row[i]] = 1; (*cnt)++; stack[sp++] = row[i]; }
+  }
+}
+
+EXPORT long orc_nsg_tree_grow(const float *data, size_t n, size_t dim, size_t stride, uint32_t *graph,
+                              unsigned gstride, uint32_t ep, unsigned L, int mode, int rng_mode, uint32_t seed,
+                              unsigned width_in, unsigned *width_out) {
+  orc_index ix = {data, n, dim, stride, graph, gstride, mode};
+  uint8_t *flag = (uint8_t *)calloc(n, 1), *vis = (uint8_t *)malloc(n);
+  uint32_t *stack = (uint32_t *)malloc(sizeof(uint32_t) * n);
+  orc_nb *retset = (orc_nb *)malloc(sizeof(orc_nb) * (L + 1));
+  nb_vec full = {0, 0, 0};
+  size_t cnt = 0, scan = 0;
+  long added = 0;
+  uint32_t root = ep;
+  while (cnt < n) {
+    mark_reachable(graph, gstride, flag, root, &cnt, stack);
+    if (cnt >= n) break;
+    while (scan < n && flag[scan]) scan++;
+    uint32_t id = (uint32_t)scan;
+    memset(vis, 0, n);
+    full.n = 0;
+    nsg_beam(&ix, ep, data + stride * (size_t)id, L, rng_mode, seed, id, vis, retset, &full, 0, NULL);
+    qsort(full.v, full.n, sizeof(orc_nb), nb_cmp);
+    int found = 0;
+    for (size_t i = 0; i < full.n && !found; i++) {
+      uint32_t c = full.v[i].id;
+      if (flag[c] && row_degree(graph + (size_t)c * gstride, gstride) < gstride) { root = c; found = 1; }
+    }
+    for (uint32_t t = 0; !found; t++) {
+      uint32_t rid = rng_mode == 0 ? (uint32_t)rand() % (uint32_t)n : orc_seed_hash(seed, id, 0x10000u + t) % (uint32_t)n;
+      if (flag[rid] && row_degree(graph + (size_t)rid * gstride, gstride) < gstride) { root = rid; found = 1; }
+    }
+    uint32_t *row = graph + (size_t)root * gstride;
+    row[row_degree(row, gstride)] = id;
+    added++;
+  }
+  unsigned w = width_in;
+  for (size_t i = 0; i < n; i++) {
+    unsigned d = row_degree(graph + i * gstride, gstride);
+    if (d > w) w = d;
+  }
+  if (width_out) *width_out = w;
+  free(flag); free(vis); free(stack); free(retset); free(full.v);
+  return added;
 }

@@ -52,6 +52,17 @@ def oracle():
                                         u32p, C.c_uint, C.c_void_p, C.c_uint32, C.c_int, f32p, C.c_size_t,
                                         C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int, u64p, f32p,
                                         C.c_void_p]
+        lib.orc_nsg_init_ep.restype = C.c_uint32
+        lib.orc_nsg_init_ep.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, u32p, C.c_uint, C.c_uint32, C.c_uint,
+                                        C.c_int, C.c_int, C.c_uint32, C.c_void_p]
+        lib.orc_nsg_link.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, u32p, C.c_uint, C.c_uint32, C.c_uint,
+                                     C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_uint32, u32p, f32p, C.c_void_p]
+        lib.orc_nsg_interinsert.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_uint, C.c_int, C.c_int,
+                                            u32p, f32p, C.c_void_p]
+        lib.orc_nsg_cut_to_graph.argtypes = [u32p, f32p, C.c_size_t, C.c_uint, u32p, C.c_uint]
+        lib.orc_nsg_tree_grow.restype = C.c_long
+        lib.orc_nsg_tree_grow.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, u32p, C.c_uint, C.c_uint32,
+                                          C.c_uint, C.c_int, C.c_int, C.c_uint32, C.c_uint, C.POINTER(C.c_uint)]
         _oracle = lib
     return _oracle
 
@@ -96,6 +107,59 @@ def orc_hnsw_search(base, h, q, k, ef, mode, variant=1, want_stats=False):
                              up, up.shape[1], _vp(h["labels"]), h["ep"], h["maxlevel"], q, nq, q.shape[1], k, ef,
                              mode, variant, lab, d, _vp(st))
     return (lab, d, st) if want_stats else (lab, d)
+
+
+def pad_graph(knn, gstride=None):
+    """[n,K] ids -> flat adjacency [n,gstride] (gstride multiple of 8) padded with INVALID"""
+    n, K = knn.shape
+    gs = gstride or (K + 7) // 8 * 8
+    g = np.full((n, gs), INVALID, np.uint32)
+    g[:, :K] = knn
+    return g
+
+
+def orc_nsg_init_ep(base, graph, ep0, L, mode, rng_mode=1, seed=0):
+    n, dim = base.shape
+    center = np.empty(dim, np.float32)
+    ep = oracle().orc_nsg_init_ep(base, n, dim, dim, graph, graph.shape[1], ep0, L, mode, rng_mode, seed, _vp(center))
+    return int(ep), center
+
+
+def orc_nsg_link(base, knn_graph, ep, L, R_, C_, mode, rng_mode=1, seed=0, want_stats=False):
+    n, dim = base.shape
+    ci = np.empty((n, R_), np.uint32)
+    cd = np.empty((n, R_), np.float32)
+    st = np.zeros((n, 3), np.uint64) if want_stats else None
+    oracle().orc_nsg_link(base, n, dim, dim, knn_graph, knn_graph.shape[1], ep, L, R_, C_, mode, rng_mode, seed, ci, cd,
+                          _vp(st))
+    return (ci, cd, st) if want_stats else (ci, cd)
+
+
+def orc_nsg_interinsert(base, ci, cd, mode, variant):
+    n, dim = base.shape
+    ci, cd = ci.copy(), cd.copy()
+    ne = C.c_uint64(0)
+    oracle().orc_nsg_interinsert(base, n, dim, dim, ci.shape[1], mode, variant, ci, cd, C.byref(ne))
+    return ci, cd, ne.value
+
+
+def orc_nsg_cut_to_graph(ci, cd, gstride):
+    n, R_ = ci.shape
+    g = np.empty((n, gstride), np.uint32)
+    oracle().orc_nsg_cut_to_graph(ci, cd, n, R_, g, gstride)
+    return g
+
+
+def orc_nsg_tree_grow(base, graph, ep, L, mode, width_in, rng_mode=1, seed=0):
+    n, dim = base.shape
+    g = graph.copy()
+    w = C.c_uint(0)
+    added = oracle().orc_nsg_tree_grow(base, n, dim, dim, g, g.shape[1], ep, L, mode, rng_mode, seed, width_in, C.byref(w))
+    return g, int(added), w.value
+
+
+def libc():
+    return C.CDLL("libc.so.6")
 
 
 # ------------------------------------------------------------------ reference on-disk formats

@@ -195,3 +195,59 @@ def test_hnsw_pool_equals_twoheap_on_ties():
     _, d0 = R.orc_hnsw_search(base, H, q, 5, 20, R.L2_SCALAR, variant=0)
     _, d1 = R.orc_hnsw_search(base, H, q, 5, 20, R.L2_SCALAR, variant=1)
     assert np.mean(d0 == d1) > 0.95
+
+
+# ---------------------------------------------------------------- NSG build (Link / InterInsert / tree_grow)
+def _exact_knn(base, K):
+    ids0, _ = R.orc_bf_knn(base, base, K + 1, R.L2_SCALAR)
+    return np.stack([row[row != i][:K] for i, row in enumerate(ids0)]).astype(np.uint32)
+
+
+@needs_ref
+@pytest.mark.parametrize("n,dim,K,L,Rr,Cc,seed", [(3000, 32, 24, 20, 12, 100, 7), (2000, 24, 10, 16, 8, 50, 3),
+                                                  (1500, 128, 30, 30, 20, 200, 11)])
+def test_nsg_build_vs_reference(tmp_path, n, dim, K, L, Rr, Cc, seed):
+    """IndexNSG::Build by the unmodified reference (1 thread, srand(seed)) == the oracle's phases chained
+    with libc rand() drawn at the same places: identical navigating node, identical adjacency rows.
+    The second case has L > K so the rand() seed fill of get_neighbors (:234-240) is exercised (dims are
+    multiples of 8: the reference AVX distance reads past the row end otherwise, distance.h:41-51)."""
+    base = R.data_uniform(n, dim, 1)
+    knn = _exact_knn(base, K)
+    kp, gp = str(tmp_path / "k.graph"), str(tmp_path / "g.nsg")
+    R.write_knn_graph(kp, knn)
+    R.ref_nsg_build(base, kp, L, Rr, Cc, gp, seed=seed, threads=1)
+    g_ref, ep_ref, width_ref = R.parse_nsg(gp, n)
+    lc = R.libc()
+    lc.srand(seed)
+    ep0 = lc.rand() % n
+    kg = R.pad_graph(knn)
+    mode = R.L2_EFANNA_AVX
+    ep, _ = R.orc_nsg_init_ep(base, kg, ep0, L, mode, rng_mode=0)
+    assert ep == ep_ref
+    ci, cd = R.orc_nsg_link(base, kg, ep, L, Rr, Cc, mode, rng_mode=0)
+    ci, cd, _ = R.orc_nsg_interinsert(base, ci, cd, mode, 0)
+    g = R.orc_nsg_cut_to_graph(ci, cd, g_ref.shape[1] + 32)
+    g, added, width = R.orc_nsg_tree_grow(base, g, ep, L, mode, Rr, rng_mode=0)
+    assert width == width_ref
+    gs = g_ref.shape[1]
+    assert (g[:, :gs] == g_ref).all() and (g[:, gs:] == R.INVALID).all()
+
+
+def test_nsg_interinsert_batch_form_properties():
+    """the batch InterInsert (what the CUDA build runs): every row is duplicate free, -1 terminated,
+    carries the true distances, and gains reverse edges up to the cap R"""
+    n, dim, K, L, Rr, Cc = 2500, 24, 20, 20, 10, 80
+    base = R.data_uniform(n, dim, 5)
+    kg = R.pad_graph(_exact_knn(base, K))
+    mode = R.L2_SCALAR
+    ci, cd = R.orc_nsg_link(base, kg, 0, L, Rr, Cc, mode)
+    bi, bd, _ = R.orc_nsg_interinsert(base, ci, cd, mode, 1)
+    for i in range(0, n, 37):
+        ids = bi[i][bd[i] != -1]
+        assert len(set(ids.tolist())) == len(ids) and i not in ids
+        assert (bi[i][bd[i] == -1] == R.INVALID).all()
+        d = bd[i][bd[i] != -1]
+        want = ((base[ids] - base[i]) ** 2).sum(1)
+        assert np.allclose(d, want, rtol=1e-5)
+    assert (bd != -1).sum(1).mean() > (cd != -1).sum(1).mean()
+    assert ((bd != -1).sum(1) <= Rr).all()

@@ -47,12 +47,21 @@ _lib.b200ann_bf_knn.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _vp, _vp]
 _lib.b200ann_knn_graph.argtypes = [_vp, _vp, _sz, _vp]
 _lib.b200ann_nsg_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, C.c_uint32, _vp, _vp, _vp]
 _lib.b200ann_hnsw_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _vp, _vp, _vp]
+_u32 = C.c_uint32
+_lib.b200ann_set_link_visited_bits.argtypes = [_vp, C.c_int]
+_lib.b200ann_nsg_build.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _u32, _u32, _vp]
+_lib.b200ann_nsg_init_ep.argtypes = [_vp, _vp, _vp, _sz, _sz, _u32, _u32, C.POINTER(_u32), _vp]
+_lib.b200ann_nsg_link.argtypes = [_vp, _vp, _vp, _sz, _u32, _sz, _sz, _sz, _u32, _vp, _vp, _vp]
+_lib.b200ann_nsg_interinsert.argtypes = [_vp, _vp, _sz, _vp, _vp, C.POINTER(C.c_uint64)]
+_lib.b200ann_nsg_finish.argtypes = [_vp, _vp, _vp, _vp, _sz, _u32, _sz, _u32, _sz, C.POINTER(_u32)]
 
 EXPORTS = [
     "b200ann_create", "b200ann_destroy", "b200ann_last_error", "b200ann_stream", "b200ann_launch_count",
     "b200ann_last_kernel_ms", "b200ann_set_visited_bits", "b200ann_index_create", "b200ann_index_destroy",
     "b200ann_index_size", "b200ann_index_dim", "b200ann_index_set_graph", "b200ann_index_get_graph",
     "b200ann_index_set_hnsw", "b200ann_bf_knn", "b200ann_knn_graph", "b200ann_nsg_search", "b200ann_hnsw_search",
+    "b200ann_set_link_visited_bits", "b200ann_nsg_build", "b200ann_nsg_init_ep", "b200ann_nsg_link",
+    "b200ann_nsg_interinsert", "b200ann_nsg_finish",
 ]
 
 
@@ -118,6 +127,9 @@ class Handle:
     def set_visited_bits(self, bits):
         self._check(_lib.b200ann_set_visited_bits(self._h, bits))
 
+    def set_link_visited_bits(self, bits):
+        self._check(_lib.b200ann_set_link_visited_bits(self._h, bits))
+
 
 class Index:
     """vectors (+ graphs) resident in HBM"""
@@ -175,6 +187,47 @@ class Index:
         knn = np.empty((self.n, K), np.uint32)
         self.h._check(_lib.b200ann_knn_graph(self.h._h, self._ix, K, _ptr(knn)))
         return knn
+
+    # ---- NSG construction (IndexNSG::Build and its phases)
+    def nsg_build(self, knn, L, R, C_, seed=0, ep0=INVALID):
+        """knn: numpy [n,kstride] u32, or (device pointer / torch tensor, kstride)"""
+        kptr, kstride = (knn if isinstance(knn, tuple) else (np.ascontiguousarray(knn, np.uint32), knn.shape[1]))
+        info = np.zeros(8, np.uint64)
+        self.h._check(_lib.b200ann_nsg_build(self.h._h, self._ix, _ptr(kptr), kstride, L, R, C_, seed, ep0, _ptr(info)))
+        keys = ("ep", "width", "tree_grow_edges", "beam_evals", "hops", "prune_evals", "interinsert_evals")
+        return dict(zip(keys, (int(x) for x in info)))
+
+    def nsg_init_ep(self, knn, L, seed=0, ep0=INVALID):
+        knn = np.ascontiguousarray(knn, np.uint32)
+        ep = _u32()
+        center = np.empty(self.dim, np.float32)
+        self.h._check(_lib.b200ann_nsg_init_ep(self.h._h, self._ix, _ptr(knn), knn.shape[1], L, seed, ep0, C.byref(ep),
+                                               _ptr(center)))
+        return ep.value, center
+
+    def nsg_link(self, knn, ep, L, R, C_, seed=0, want_stats=False):
+        knn = np.ascontiguousarray(knn, np.uint32)
+        ci = np.empty((self.n, R), np.uint32)
+        cd = np.empty((self.n, R), np.float32)
+        st = np.zeros((self.n, 3), np.uint32) if want_stats else None
+        self.h._check(_lib.b200ann_nsg_link(self.h._h, self._ix, _ptr(knn), knn.shape[1], ep, L, R, C_, seed, _ptr(ci),
+                                            _ptr(cd), _ptr(st)))
+        return (ci, cd, st) if want_stats else (ci, cd)
+
+    def nsg_interinsert(self, cut_ids, cut_d):
+        ci = np.ascontiguousarray(cut_ids, np.uint32).copy()
+        cd = np.ascontiguousarray(cut_d, np.float32).copy()
+        ne = C.c_uint64(0)
+        self.h._check(_lib.b200ann_nsg_interinsert(self.h._h, self._ix, ci.shape[1], _ptr(ci), _ptr(cd), C.byref(ne)))
+        return ci, cd, ne.value
+
+    def nsg_finish(self, cut_ids, cut_d, ep, L, seed=0, slack=14):
+        ci = np.ascontiguousarray(cut_ids, np.uint32)
+        cd = np.ascontiguousarray(cut_d, np.float32)
+        added = _u32()
+        self.h._check(_lib.b200ann_nsg_finish(self.h._h, self._ix, _ptr(ci), _ptr(cd), ci.shape[1], ep, L, seed, slack,
+                                              C.byref(added)))
+        return added.value
 
     # ---- graph search
     def nsg_search(self, q, K, L, seed=0, want_stats=False):

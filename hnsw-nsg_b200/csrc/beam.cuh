@@ -1,0 +1,330 @@
+// Warp-per-query beam search core shared by the search kernels (search.cu) and the NSG build
+// kernels (nsg_build.cu).
+//
+// One core, two front-ends:
+//   NSG  — efanna2e::IndexNSG::Search / SearchWithOptGraph (CNNS/src/nsg/index_nsg.cpp:506-568, :570-657)
+//          and IndexNSG::get_neighbors (:150-285): sorted pool of L, seeds = first L out-neighbours of
+//          ep + pseudo-random fill, expand the first unexpanded pool entry, InsertIntoPool
+//          (CNNS/include/nsg/neighbor.h:107-135), k/nk rewind.
+//   HNSW — hnswlib::HierarchicalNSW::searchKnn (hnswlib/hnswlib/hnswalg.h:1270-1324): greedy descent on
+//          levels >= 1, then searchBaseLayerST<bare_bone> (:309-440) in its single-pool form (one
+//          ascending (distance,id) pool of <= ef entries with an "unexpanded" flag; see oracle.c
+//          hnsw_base_pool for why it equals the reference's two heaps).
+//
+// Per-warp shared memory: the pool (distance + id|flag), the compacted candidate list of the node
+// being expanded, and the visited set: an open-addressing hash set of u32 ids (2^hbits slots, linear
+// probing, <= PROBES probes). It never reports an unvisited node as visited. When a probe sequence
+// is full the home slot is overwritten ("forgets" one id); a forgotten node's distance is recomputed
+// and the pool's (distance,id) duplicate check / the monotone admission threshold reject it again,
+// so results are identical to an exact visited set (the reference's N-bit bitset, index_nsg.cpp:512,
+// or u16[N] epoch array, visited_list_pool.h:10-31) without N bits per query.
+//
+// Neighbour vectors are gathered with 16-byte loads, a team of 8 (dim <= 256) or 32 lanes per row,
+// two rows per team in flight (dist.cuh).
+//
+// `Rec` is a warp-uniform callback rec(cand_i, cand_d, m, is_seed) invoked after every batch of
+// distance evaluations; get_neighbors' `fullset` (:250,:273) is built through it.
+#pragma once
+#include "common.cuh"
+#include "dist.cuh"
+
+namespace beam {
+
+constexpr uint32_t FLAG = 0x80000000u;
+constexpr int BIGPOS = 0x7fffffff;
+constexpr int PROBES = 8;
+
+struct SearchParams {
+  const float *vec; size_t stride; uint32_t n; int nch;
+  const uint32_t *graph; uint32_t gstride; uint32_t ep;
+  const uint32_t *upper_links; const uint32_t *upper_ptr; uint32_t maxM; int maxlevel;
+  const uint64_t *labels;
+  const float *q; size_t qstride; uint32_t nq; uint32_t dim;
+  uint32_t K, L, seed; int hbits;
+  uint32_t qidx_base;           // query index fed to the seed hash = qidx_base + query
+  uint32_t cand_cap, pool_cap;  // words
+  uint32_t *ids; uint64_t *labels_out; float *dists; uint32_t *stats;
+};
+
+__device__ __forceinline__ uint32_t mix32(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
+  return x;
+}
+// stateless replacement for the reference's rand() seed fill (index_nsg.cpp:521-527)
+__device__ __forceinline__ uint32_t seed_hash(uint32_t seed, uint32_t query, uint32_t counter) {
+  return mix32(mix32(seed ^ (query * 0x9E3779B9U)) + counter * 0x85EBCA6BU);
+}
+
+struct NoRec {
+  __device__ __forceinline__ void operator()(const uint32_t *, const float *, uint32_t, bool) const {}
+};
+
+// words of shared memory one warp needs
+__host__ __device__ inline uint32_t smem_words(uint32_t pool_cap, uint32_t cand_cap, int hbits) {
+  return 2 * pool_cap + 2 * cand_cap + (1u << hbits);
+}
+
+// COHERENT: adjacency rows are read with ordinary (L2-coherent) loads instead of the read-only path,
+// for kernels that append edges while they search (tree_grow).
+template <int TEAM, int NCH, bool IP, bool HNSW, bool COHERENT = false>
+struct Beam {
+  static constexpr int TPW = 32 / TEAM;
+  static constexpr int TEAMSZ = TEAM, NCHUNK = NCH;
+  static constexpr bool IS_IP = IP;
+  const SearchParams &p;
+  float *pool_d; uint32_t *pool_i;   // [pool_cap]
+  uint32_t *cand_i; float *cand_d;   // [cand_cap]
+  uint32_t *tab; uint32_t hshift, hmask;
+  float4 qreg[NCH];
+  int lane, t, g;
+  uint32_t np, cap;
+  uint32_t n_dist, n_hops;
+
+  __device__ __forceinline__ Beam(const SearchParams &pp, uint32_t *smem_base) : p(pp) {
+    pool_d = reinterpret_cast<float *>(smem_base);
+    pool_i = smem_base + p.pool_cap;
+    cand_i = smem_base + 2 * p.pool_cap;
+    cand_d = reinterpret_cast<float *>(smem_base + 2 * p.pool_cap + p.cand_cap);
+    tab = smem_base + 2 * p.pool_cap + 2 * p.cand_cap;
+    hshift = 32 - p.hbits;
+    hmask = (1u << p.hbits) - 1;
+    lane = threadIdx.x & 31;
+    t = lane % TEAM;
+    g = lane / TEAM;
+  }
+
+  __device__ __forceinline__ uint32_t slot(uint32_t id) const { return (id * 0x9E3779B1u) >> hshift; }
+
+  // visited set: true if `id` was already present, else inserts it
+  __device__ __forceinline__ bool test_and_set(uint32_t id) {
+    uint32_t s = slot(id);
+#pragma unroll 1
+    for (int pr = 0; pr < PROBES; pr++) {
+      uint32_t old = atomicCAS(&tab[(s + pr) & hmask], INVALID_ID, id);
+      if (old == INVALID_ID) return false;
+      if (old == id) return true;
+    }
+    tab[s] = id;  // probe sequence full: forget the home slot's id
+    return false;
+  }
+
+  __device__ __forceinline__ void load_query(const float *qv) {
+#pragma unroll
+    for (int c = 0; c < NCH; c++) {
+      uint32_t b = (uint32_t)(t + c * TEAM) * 4;
+      qreg[c].x = b + 0 < p.dim ? __ldg(qv + b + 0) : 0.f;
+      qreg[c].y = b + 1 < p.dim ? __ldg(qv + b + 1) : 0.f;
+      qreg[c].z = b + 2 < p.dim ? __ldg(qv + b + 2) : 0.f;
+      qreg[c].w = b + 3 < p.dim ? __ldg(qv + b + 3) : 0.f;
+    }
+  }
+
+  // distances of cand_i[0..m) -> cand_d[0..m)
+  __device__ __forceinline__ void eval(uint32_t m) {
+    __syncwarp();
+    for (uint32_t c0 = 0; c0 < m; c0 += 2 * TPW) {
+      uint32_t i0 = c0 + g, i1 = c0 + TPW + g;
+      const float4 *r0 = nullptr, *r1 = nullptr;
+      if (i0 < m) r0 = reinterpret_cast<const float4 *>(p.vec + (size_t)cand_i[i0] * p.stride);
+      if (i1 < m) r1 = reinterpret_cast<const float4 *>(p.vec + (size_t)cand_i[i1] * p.stride);
+      float d0, d1;
+      team_dist2<TEAM, NCH, IP>(r0, r1, qreg, t, p.nch, d0, d1);
+      if (t == 0) {
+        if (i0 < m) cand_d[i0] = d0;
+        if (i1 < m) cand_d[i1] = d1;
+      }
+    }
+    n_dist += m;
+    __syncwarp();
+  }
+
+  __device__ __forceinline__ uint32_t ld_adj(const uint32_t *a) const {
+    if (COHERENT) return __ldcg(a);
+    return __ldg(a);
+  }
+
+  // copy an adjacency row into cand_i; with `filter`, drop ids already in the visited set.
+  __device__ __forceinline__ uint32_t load_row(const uint32_t *row, uint32_t rowlen, uint32_t limit, bool filter) {
+    uint32_t m = 0;
+    __syncwarp();
+    for (uint32_t j0 = 0; j0 < rowlen; j0 += 32) {
+      uint32_t j = j0 + lane;
+      uint32_t id = (j < rowlen && j < limit) ? ld_adj(row + j) : INVALID_ID;
+      bool valid = id != INVALID_ID;
+      if (valid && filter) valid = !test_and_set(id);
+      unsigned mask = __ballot_sync(0xffffffffu, valid);
+      if (valid) cand_i[m + __popc(mask & ((1u << lane) - 1))] = id;
+      m += __popc(mask);
+      if (__any_sync(0xffffffffu, id == INVALID_ID)) break;
+    }
+    __syncwarp();
+    return m;
+  }
+
+  // sorted insert. NSG: after every entry with distance <= d (InsertIntoPool, neighbor.h:107-135);
+  // HNSW: (distance,id) lexicographic. Returns the position, or BIGPOS for a duplicate.
+  __device__ __forceinline__ int insert(float d, uint32_t id) {
+    int pos = 0;
+    bool dup = false;
+    for (uint32_t j0 = 0; j0 < np; j0 += 32) {
+      uint32_t j = j0 + lane;
+      bool in = j < np;
+      float pdj = in ? pool_d[j] : 0.f;
+      uint32_t pij = in ? (pool_i[j] & ~FLAG) : INVALID_ID;
+      bool before = in && (HNSW ? (pdj < d || (pdj == d && pij < id)) : (pdj <= d));
+      dup |= in && pdj == d && pij == id;
+      pos += __popc(__ballot_sync(0xffffffffu, before));
+    }
+    if (__any_sync(0xffffffffu, dup)) return BIGPOS;
+    int end = (np < cap) ? (int)np : (int)cap - 1;  // entries [pos,end) move up by one
+    if (end > pos) {
+      for (int jb = pos + ((end - 1 - pos) / 32) * 32; jb >= pos; jb -= 32) {
+        int j = jb + lane;
+        bool mv = j < end;
+        float td = 0.f; uint32_t ti = 0;
+        if (mv) { td = pool_d[j]; ti = pool_i[j]; }
+        __syncwarp();
+        if (mv) { pool_d[j + 1] = td; pool_i[j + 1] = ti; }
+        __syncwarp();
+      }
+    }
+    if (lane == 0) { pool_d[pos] = d; pool_i[pos] = id | FLAG; }
+    if (np < cap) np++;
+    __syncwarp();
+    return pos;
+  }
+
+  // query -> registers (any alignment / stride), empty visited set
+  __device__ __forceinline__ void begin(const float *qv) {
+    load_query(qv);
+    for (uint32_t i = lane; i <= hmask; i += 32) tab[i] = INVALID_ID;
+    n_dist = 0; n_hops = 0;
+    cap = p.L;
+    np = 0;
+    __syncwarp();
+  }
+
+  // HNSW upper layers: greedy descent (hnswalg.h:1275-1303); the base layer then starts from the
+  // one entry it ends on (:323-340)
+  __device__ __forceinline__ void descend_hnsw() {
+    uint32_t cur = p.ep;
+    if (lane == 0) cand_i[0] = cur;
+    eval(1);
+    float curdist = cand_d[0];
+    for (int level = p.maxlevel; level > 0; level--) {
+      bool changed = true;
+      while (changed) {
+        changed = false;
+        const uint32_t *row = p.upper_links + ((size_t)__ldg(p.upper_ptr + cur) + (level - 1)) * p.maxM;
+        uint32_t m = load_row(row, p.maxM, p.maxM, false);
+        n_hops++;
+        eval(m);
+        // sequential "if (d < curdist)" over the list == first index of the minimum, if below curdist
+        float bd = INFINITY; uint32_t bi = INVALID_ID;
+        for (uint32_t c = lane; c < m; c += 32) {
+          float d = cand_d[c];
+          if (d < bd) { bd = d; bi = c; }
+        }
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) {
+          float od = __shfl_xor_sync(0xffffffffu, bd, off);
+          uint32_t oi = __shfl_xor_sync(0xffffffffu, bi, off);
+          if (od < bd || (od == bd && oi < bi)) { bd = od; bi = oi; }
+        }
+        if (bi != INVALID_ID && bd < curdist) { curdist = bd; cur = cand_i[bi]; changed = true; }
+      }
+    }
+    if (lane == 0) { pool_d[0] = curdist; pool_i[0] = cur | FLAG; }
+    test_and_set(cur);  // every lane offers the same id: one wins, the rest see it present
+    np = 1;
+    __syncwarp();
+  }
+
+  // NSG seeds: first L out-neighbours of ep (index_nsg.cpp:516-519), then pseudo-random ids not yet
+  // chosen (:521-527); distances; std::sort(retset) (:538) as a rank sort on (distance,id,position)
+  template <class Rec>
+  __device__ __forceinline__ void seed_nsg(uint32_t qidx, Rec &rec) {
+    uint32_t m = load_row(p.graph + (size_t)p.ep * p.gstride, p.gstride, p.L, false);
+    uint32_t ctr = 0;
+    while (m < p.L) {
+      uint32_t id = seed_hash(p.seed, qidx, ctr++) % p.n;
+      bool hit = false;
+      for (uint32_t j = lane; j < m; j += 32) hit |= cand_i[j] == id;
+      if (!__any_sync(0xffffffffu, hit)) {
+        if (lane == 0) cand_i[m] = id;
+        m++;
+      }
+      __syncwarp();
+    }
+    eval(m);
+    rec(cand_i, cand_d, m, true);
+    for (uint32_t i = lane; i < m; i += 32) {
+      float di = cand_d[i]; uint32_t ii = cand_i[i];
+      uint32_t r = 0;
+      for (uint32_t j = 0; j < m; j++) {
+        float dj = cand_d[j]; uint32_t ij = cand_i[j];
+        // position breaks (distance,id) ties: a reference-built row can list an id twice
+        // (InterInsert leaves stale tail entries, index_nsg.cpp:399-404) and Search keeps both seeds
+        r += (dj < di || (dj == di && (ij < ii || (ij == ii && j < i)))) ? 1u : 0u;
+      }
+      pool_d[r] = di; pool_i[r] = ii | FLAG;
+      test_and_set(ii);
+    }
+    np = m;
+    __syncwarp();
+  }
+
+  // main loop (index_nsg.cpp:539-564 / hnswalg.h:342-436)
+  template <class Rec>
+  __device__ __forceinline__ void expand_all(Rec &rec) {
+    uint32_t k = 0;
+    while (k < np) {
+      int nk = (int)np;
+      uint32_t e = pool_i[k];
+      if (e & FLAG) {
+        __syncwarp();
+        if (lane == 0) pool_i[k] = e & ~FLAG;
+        uint32_t node = e & ~FLAG;
+        n_hops++;
+        uint32_t m = load_row(p.graph + (size_t)node * p.gstride, p.gstride, p.gstride, true);
+        eval(m);
+        rec(cand_i, cand_d, m, false);
+        for (uint32_t c0 = 0; c0 < m; c0 += 32) {
+          uint32_t c = c0 + lane;
+          float d = c < m ? cand_d[c] : INFINITY;
+          float last = pool_d[np - 1];
+          bool pass = c < m && ((HNSW && np < cap) || d < last);
+          unsigned mask = __ballot_sync(0xffffffffu, pass);
+          while (mask) {
+            int b = __ffs(mask) - 1;
+            mask &= mask - 1;
+            float dd = __shfl_sync(0xffffffffu, d, b);
+            uint32_t id = cand_i[c0 + b];
+            last = pool_d[np - 1];
+            if (!((HNSW && np < cap) || dd < last)) continue;  // threshold moved since the vote
+            int r = insert(dd, id);
+            if (r < nk) nk = r;
+          }
+        }
+      }
+      k = ((uint32_t)nk <= k) ? (uint32_t)nk : k + 1;
+    }
+    __syncwarp();
+  }
+};
+
+// dispatch on the row length: nch = ceil(dim/4) float4 chunks -> (TEAM, NCH)
+#define BEAM_DISPATCH_NCH(nch, CALL)                 \
+  do {                                               \
+    if ((nch) <= 8) { CALL(8, 1); }                  \
+    else if ((nch) <= 16) { CALL(8, 2); }            \
+    else if ((nch) <= 32) { CALL(8, 4); }            \
+    else if ((nch) <= 64) { CALL(8, 8); }            \
+    else if ((nch) <= 128) { CALL(32, 4); }          \
+    else if ((nch) <= 256) { CALL(32, 8); }          \
+    else if ((nch) <= 512) { CALL(32, 16); }         \
+  } while (0)
+
+inline uint32_t round_up(uint32_t x, uint32_t m) { return (x + m - 1) / m * m; }
+
+}  // namespace beam

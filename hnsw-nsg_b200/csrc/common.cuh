@@ -18,6 +18,7 @@ struct b200ann_handle {
   uint64_t launches = 0;
   float last_ms = 0.f;
   int visited_bits = 10;
+  int link_visited_bits = 12;
   int sm_count = 148;
 };
 
@@ -120,8 +121,18 @@ struct OutArg {
 
 // kernel launchers implemented in the .cu files (all asynchronous on h->stream)
 int launch_nsg_search(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
-                      size_t K, size_t L, uint32_t seed, uint32_t *ids, float *dists, uint32_t *stats);
+                      size_t K, size_t L, uint32_t seed, uint32_t *ids, float *dists, uint32_t *stats,
+                      uint32_t qidx_base = 0);
 int launch_hnsw_search(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
                        size_t k, size_t ef, uint64_t *labels, float *dists, uint32_t *stats);
 int launch_bf_knn(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
                   size_t k, bool exclude_self, uint32_t *ids, float *dists);
+
+// NSG build phases (nsg_build.cu); device pointers only
+int nsg_centroid_launch(b200ann_handle *h, const b200ann_index *ix, float *center);
+int nsg_link_launch(b200ann_handle *h, const b200ann_index *ix, const uint32_t *knn, size_t kstride, uint32_t ep,
+                    size_t L, size_t R, size_t C, uint32_t seed, uint32_t *cut_ids, float *cut_d, uint32_t *stats);
+int nsg_interinsert_launch(b200ann_handle *h, const b200ann_index *ix, size_t R, uint32_t *cut_ids, float *cut_d,
+                           unsigned long long *n_eval_dev);
+int nsg_finish(b200ann_handle *h, b200ann_index *ix, const uint32_t *cut_ids, const float *cut_d, size_t R, uint32_t ep,
+               size_t L, uint32_t seed, size_t slack, uint32_t *added_out);

@@ -23,6 +23,9 @@ __device__ __forceinline__ float4 ld_row16(const float4 *p) {
   return v;
 }
 
+// cached 16-byte load: rows that are re-read soon (the kept set of the occlusion prune) stay in L1
+__device__ __forceinline__ float4 ld_row16_ca(const float4 *p) { return __ldg(p); }
+
 template <bool IP>
 __device__ __forceinline__ float acc4(float acc, const float4 &q, const float4 &v) {
   if (IP) {
@@ -49,7 +52,7 @@ __device__ __forceinline__ float team_reduce(float acc) {
 
 // Distances of two rows per team in one go (2*NCH independent 16-byte loads in flight per lane).
 // r0/r1 may be nullptr (no row): the result is then unspecified and must be ignored by the caller.
-template <int TEAM, int NCH, bool IP>
+template <int TEAM, int NCH, bool IP, bool CACHE = false>
 __device__ __forceinline__ void team_dist2(const float4 *r0, const float4 *r1, const float4 (&q)[NCH], int t,
                                            int nch, float &d0, float &d1) {
   float4 v0[NCH], v1[NCH];
@@ -57,12 +60,12 @@ __device__ __forceinline__ void team_dist2(const float4 *r0, const float4 *r1, c
 #pragma unroll
   for (int c = 0; c < NCH; c++) {
     int ch = t + c * TEAM;
-    v0[c] = (r0 != nullptr && ch < nch) ? ld_row16(r0 + ch) : z;
+    v0[c] = (r0 != nullptr && ch < nch) ? (CACHE ? ld_row16_ca(r0 + ch) : ld_row16(r0 + ch)) : z;
   }
 #pragma unroll
   for (int c = 0; c < NCH; c++) {
     int ch = t + c * TEAM;
-    v1[c] = (r1 != nullptr && ch < nch) ? ld_row16(r1 + ch) : z;
+    v1[c] = (r1 != nullptr && ch < nch) ? (CACHE ? ld_row16_ca(r1 + ch) : ld_row16(r1 + ch)) : z;
   }
   float a0 = 0.f, a1 = 0.f;
 #pragma unroll

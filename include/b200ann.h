@@ -104,8 +104,41 @@ int b200ann_hnsw_search(b200ann_handle_t h, b200ann_index_t ix, const float *q /
                         size_t qstride, size_t k, size_t ef, uint64_t *labels /*[h|d]*/,
                         float *dists /*[h|d]*/, uint32_t *stats /*[h|d]*/);
 
-/* tuning knob: log2 of the per-query visited-filter size in shared memory (default 10). */
+/* tuning knob: log2 of the per-query visited-set size in shared memory (default 10). */
 int b200ann_set_visited_bits(b200ann_handle_t h, int bits);
+/* same for the per-node searches of b200ann_nsg_link (default 12) */
+int b200ann_set_link_visited_bits(b200ann_handle_t h, int bits);
+
+/* ---- NSG construction --------------------------------------------------------------------- */
+/* replaces efanna2e::IndexNSG::Build (CNNS/src/nsg/index_nsg.cpp:465-504): init_graph, Link
+ * (get_neighbors + sync_prune per node, then InterInsert), compaction, tree_grow. knn [n,kstride] is
+ * the kNN graph IndexNSG::Load_nn_graph (:128-148) reads (rows may be padded with B200ANN_INVALID),
+ * e.g. the output of b200ann_knn_graph. L, R, C are the reference's "L", "R", "C" parameters.
+ * ep0 = the node the reference draws with rand() % nd_ (:299); B200ANN_INVALID = derive it from seed.
+ * On success the index holds the NSG graph (b200ann_nsg_search / b200ann_index_get_graph).
+ * InterInsert runs in its order-independent batch form; rows have R + slack slots
+ * (slack = 14) for the edges tree_grow appends.
+ * info (optional, 8 x u64): {ep, width, tree_grow edges added, beam distance evaluations, expanded
+ * nodes, prune distance evaluations, InterInsert distance evaluations, 0}. */
+int b200ann_nsg_build(b200ann_handle_t h, b200ann_index_t ix, const uint32_t *knn /*[h|d]*/, size_t kstride,
+                      size_t L, size_t R, size_t C, uint32_t seed, uint32_t ep0, uint64_t *info /*[h]*/);
+
+/* the phases of b200ann_nsg_build one by one (parity tests compare each with the oracle) */
+/* init_graph (:287-303): centroid + beam search from ep0; center_out [dim] may be NULL */
+int b200ann_nsg_init_ep(b200ann_handle_t h, b200ann_index_t ix, const uint32_t *knn /*[h|d]*/, size_t kstride,
+                        size_t L, uint32_t seed, uint32_t ep0, uint32_t *ep_out /*[h]*/, float *center_out /*[h|d]*/);
+/* Link's first loop (:437-457): cut_ids/cut_d [n,R], unused tail = B200ANN_INVALID / -1;
+ * stats [n,3] u32 = {beam distance evaluations, expanded nodes, prune distance evaluations} or NULL */
+int b200ann_nsg_link(b200ann_handle_t h, b200ann_index_t ix, const uint32_t *knn /*[h|d]*/, size_t kstride,
+                     uint32_t ep, size_t L, size_t R, size_t C, uint32_t seed, uint32_t *cut_ids /*[h|d]*/,
+                     float *cut_d /*[h|d]*/, uint32_t *stats /*[h|d]*/);
+/* InterInsert (:357-424, batch form), in place on cut_ids/cut_d [n,R]; n_eval (optional) = distance evaluations */
+int b200ann_nsg_interinsert(b200ann_handle_t h, b200ann_index_t ix, size_t R, uint32_t *cut_ids /*[h|d]*/,
+                            float *cut_d /*[h|d]*/, uint64_t *n_eval /*[h]*/);
+/* compaction (:473-487) + tree_grow (:684-764): installs the graph in the index; rows get R+slack slots */
+int b200ann_nsg_finish(b200ann_handle_t h, b200ann_index_t ix, const uint32_t *cut_ids /*[h|d]*/,
+                       const float *cut_d /*[h|d]*/, size_t R, uint32_t ep, size_t L, uint32_t seed, size_t slack,
+                       uint32_t *added /*[h]*/);
 
 #pragma GCC visibility pop
 #ifdef __cplusplus

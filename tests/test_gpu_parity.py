@@ -243,3 +243,76 @@ def test_argument_errors(B, H):
         ix.nsg_search(base[:2], 20, 10)                  # K > L
     ids, d = ix.nsg_search(np.zeros((0, 8), np.float32), 5, 10)   # empty batch
     assert ids.shape == (0, 5)
+
+
+# ---------------------------------------------------------------- NSG build (IndexNSG::Build phase by phase)
+def _exact_knn(base, K):
+    ids0, _ = R.orc_bf_knn(base, base, K + 1, R.L2_SCALAR)
+    return np.stack([row[row != i][:K] for i, row in enumerate(ids0)]).astype(np.uint32)
+
+
+@pytest.mark.parametrize("n,dim,K,L,Rr,Cc,lbits", [(3000, 32, 24, 20, 12, 100, 12), (2000, 24, 10, 16, 8, 50, 12),
+                                                    (1500, 128, 30, 30, 20, 200, 7), (1200, 960, 16, 20, 10, 60, 12),
+                                                    (2500, 100, 40, 40, 50, 500, 12)])
+def test_nsg_build_phases_vs_oracle(B, n, dim, K, L, Rr, Cc, lbits):
+    """every phase of the CUDA build, fed the previous phase's output, is bit-identical to the oracle
+    run in the kernels' summation order: navigating node, centroid, cut rows and their distances
+    after sync_prune and after the batch InterInsert, final adjacency after tree_grow.
+    lbits=7 forces the visited set to forget (duplicate evaluations must not change anything)."""
+    h = B.Handle(0)
+    h.set_link_visited_bits(lbits)
+    base = R.data_uniform(n, dim, 1)
+    knn = _exact_knn(base, K)
+    kg = R.pad_graph(knn)
+    ix = B.Index(h, base, 0)
+    R.oracle().orc_set_gpu_team(B.dist_team(dim))
+    mode = R.L2_GPU
+    ep0 = 123 % n
+    ep, center = ix.nsg_init_ep(kg, L, seed=5, ep0=ep0)
+    oep, ocenter = R.orc_nsg_init_ep(base, kg, ep0, L, mode, rng_mode=1, seed=5)
+    assert (center == ocenter).all()
+    assert ep == oep
+    ci, cd, st = ix.nsg_link(kg, ep, L, Rr, Cc, seed=5, want_stats=True)
+    oi, od, ost = R.orc_nsg_link(base, kg, ep, L, Rr, Cc, mode, rng_mode=1, seed=5, want_stats=True)
+    assert (ci == oi).all() and (cd == od).all()
+    assert (st[:, 1] == ost[:, 1]).all() and (st[:, 0] >= ost[:, 0]).all()
+    bi, bd, _ = ix.nsg_interinsert(ci, cd)
+    obi, obd, _ = R.orc_nsg_interinsert(base, oi, od, mode, 1)
+    assert (bi == obi).all() and (bd == obd).all()
+    added = ix.nsg_finish(bi, bd, ep, L, seed=5, slack=14)
+    g, gep, width = ix.get_graph()
+    gs = (Rr + 14 + 7) // 8 * 8
+    og = R.orc_nsg_cut_to_graph(obi, obd, gs)
+    og, oadded, owidth = R.orc_nsg_tree_grow(base, og, ep, L, mode, Rr, rng_mode=1, seed=5)
+    assert added == oadded and width == owidth and gep == ep
+    assert (g == og[:, :g.shape[1]]).all() and (og[:, g.shape[1]:] == R.INVALID).all()
+
+
+def test_nsg_build_end_to_end_recall_vs_reference(B, H, tmp_path):
+    """b200ann_nsg_build on clustered data (tree_grow has components to attach, hubs overflow in
+    InterInsert) vs the unmodified reference Build on the same kNN graph: recall@10 of a search at
+    matched L within 0.005 (north_star), every node reachable."""
+    n, dim, K, L, Rr, Cc = 8000, 64, 32, 40, 24, 200
+    base = R.data_sift_like(n, dim, 1, n_clusters=40)
+    q = R.data_sift_like(300, dim, 2, n_clusters=40)
+    knn = _exact_knn(base, K)
+    ix = B.Index(H, base, 0)
+    info = ix.nsg_build(R.pad_graph(knn), L, Rr, Cc, seed=3)
+    g, ep, width = ix.get_graph()
+    assert ep == info["ep"] and width == info["width"]
+    reach = np.zeros(n, bool); reach[ep] = True; front = [ep]
+    while front:
+        nb = g[front].ravel(); nb = nb[nb != R.INVALID]; nb = np.unique(nb[~reach[nb]])
+        reach[nb] = True; front = nb.tolist()
+    assert reach.all()
+    truth, _ = R.orc_bf_knn(base, q, 10, R.L2_SCALAR)
+    ids, _ = ix.nsg_search(q, 10, 60, seed=1)
+    rec_gpu = R.recall(ids, truth)
+    if R.have_ref():
+        kp, gp = str(tmp_path / "k.graph"), str(tmp_path / "g.nsg")
+        R.write_knn_graph(kp, knn)
+        R.ref_nsg_build(base, kp, L, Rr, Cc, gp, seed=3, threads=1)
+        ref = R.RefNsg(base, gp)
+        rec_ref = R.recall(ref.search(q, 10, 60, seed=1, threads=1), truth)
+        assert rec_gpu >= rec_ref - 0.005
+    assert rec_gpu > 0.9

@@ -188,6 +188,10 @@ class Index:
         self.h._check(_lib.b200ann_knn_graph(self.h._h, self._ix, K, _ptr(knn)))
         return knn
 
+    def knn_graph_raw(self, K, out):
+        """out: device buffer [n,K] u32/i32 (torch tensor or raw pointer)"""
+        self.h._check(_lib.b200ann_knn_graph(self.h._h, self._ix, K, _ptr(out)))
+
     # ---- NSG construction (IndexNSG::Build and its phases)
     def nsg_build(self, knn, L, R, C_, seed=0, ep0=INVALID):
         """knn: numpy [n,kstride] u32, or (device pointer / torch tensor, kstride)"""

@@ -254,21 +254,17 @@ def data_sift_like(n, dim, seed, n_clusters=64, centers_seed=12345):
     return np.floor(np.clip(np.abs(x), 0, 218)).astype(np.float32)
 
 
-def data_sift_shape(n, dim, seed, latent=24, basis_seed=777, chunk=1 << 18):
-    """SIFT-shaped synthetic rows: integer-valued fp32 in [0,218], non-negative and
-    heavy-tailed like SIFT histograms, with a low intrinsic dimension (`latent` Gaussian factors mixed
-    by a fixed basis, plus small isotropic noise) so that the kNN graph is connected the way real
-    descriptor sets are. Every value is an integer <= 218: exactly representable in bf16, and every
-    L2 partial sum is an integer < 2^24, so distances are exact under any summation order."""
-    W = np.random.default_rng(basis_seed).normal(0, 1, (latent, dim)).astype(np.float32) / np.sqrt(latent)
-    rng = np.random.default_rng(seed)
-    out = np.empty((n, dim), np.float32)
-    for a in range(0, n, chunk):
-        b = min(n, a + chunk)
-        z = rng.standard_normal((b - a, latent), dtype=np.float32)
-        y = np.abs(z @ W) * 45.0 + rng.standard_normal((b - a, dim), dtype=np.float32) * 6.0
-        out[a:b] = np.floor(np.clip(np.abs(y), 0, 218))
-    return out
+def _synth():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("b200ann_synth", os.path.join(ROOT, "hnsw-nsg_b200", "synth.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m
+
+
+def data_sift_shape(n, dim, seed, latent=16):
+    """bench.py's SIFT-shaped generator (hnsw-nsg_b200/synth.py)"""
+    return _synth().sift_shape(n, dim, seed, latent)
 
 
 def data_glove_like(n, dim, seed, n_clusters=100, centers_seed=54321):

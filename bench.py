@@ -265,8 +265,8 @@ def run_ours(args):
     q_dev = torch.from_numpy(q).cuda()
     ids_dev = torch.empty((nq, K), dtype=torch.int32, device="cuda")
     d_dev = torch.empty((nq, K), dtype=torch.float32, device="cuda")
-    gathered_i = torch.empty((world, nq, K), dtype=torch.int32, device="cuda") if world > 1 else None
-    gathered_d = torch.empty((world, nq, K), dtype=torch.float32, device="cuda") if world > 1 else None
+    gathered_i = torch.empty((world * nq, K), dtype=torch.int32, device="cuda") if world > 1 else None
+    gathered_d = torch.empty((world * nq, K), dtype=torch.float32, device="cuda") if world > 1 else None
     out_i = torch.empty((nq, K), dtype=torch.int32, device="cuda")
     out_d = torch.empty((nq, K), dtype=torch.float32, device="cuda")
     torch.cuda.synchronize()
@@ -339,9 +339,10 @@ def run_ours(args):
         gtd_i, gtd_d = ix.bf_knn(q, K)
         gi = torch.from_numpy(gtd_i.view(np.int32)).cuda() + rank * N_BASE
         gd = torch.from_numpy(gtd_d).cuda()
-        all_i = torch.empty((world, nq, K), dtype=torch.int32, device="cuda")
-        all_d = torch.empty((world, nq, K), dtype=torch.float32, device="cuda")
+        all_i = torch.empty((world * nq, K), dtype=torch.int32, device="cuda")
+        all_d = torch.empty((world * nq, K), dtype=torch.float32, device="cuda")
         dist.all_gather_into_tensor(all_i, gi); dist.all_gather_into_tensor(all_d, gd)
+        all_i = all_i.view(world, nq, K); all_d = all_d.view(world, nq, K)
         order = torch.argsort(all_d.permute(1, 0, 2).reshape(nq, -1), dim=1, stable=True)[:, :K]
         truth = torch.gather(all_i.permute(1, 0, 2).reshape(nq, -1), 1, order).cpu().numpy()
         rec = recall_at_k(out_i.cpu().numpy(), truth)

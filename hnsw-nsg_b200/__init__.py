@@ -53,6 +53,7 @@ _lib.b200ann_nsg_build.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _u32, _u32
 _lib.b200ann_nsg_init_ep.argtypes = [_vp, _vp, _vp, _sz, _sz, _u32, _u32, C.POINTER(_u32), _vp]
 _lib.b200ann_nsg_link.argtypes = [_vp, _vp, _vp, _sz, _u32, _sz, _sz, _sz, _u32, _vp, _vp, _vp]
 _lib.b200ann_nsg_interinsert.argtypes = [_vp, _vp, _sz, _vp, _vp, C.POINTER(C.c_uint64)]
+_lib.b200ann_merge_topk.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _vp, _vp]
 _lib.b200ann_nsg_finish.argtypes = [_vp, _vp, _vp, _vp, _sz, _u32, _sz, _u32, _sz, C.POINTER(_u32)]
 
 EXPORTS = [
@@ -61,7 +62,7 @@ EXPORTS = [
     "b200ann_index_size", "b200ann_index_dim", "b200ann_index_set_graph", "b200ann_index_get_graph",
     "b200ann_index_set_hnsw", "b200ann_bf_knn", "b200ann_knn_graph", "b200ann_nsg_search", "b200ann_hnsw_search",
     "b200ann_set_link_visited_bits", "b200ann_nsg_build", "b200ann_nsg_init_ep", "b200ann_nsg_link",
-    "b200ann_nsg_interinsert", "b200ann_nsg_finish",
+    "b200ann_nsg_interinsert", "b200ann_nsg_finish", "b200ann_merge_topk",
 ]
 
 
@@ -126,6 +127,19 @@ class Handle:
 
     def set_visited_bits(self, bits):
         self._check(_lib.b200ann_set_visited_bits(self._h, bits))
+
+    def merge_topk(self, d, ids, kout):
+        """d/ids: numpy [parts, nq, k] -> (out_d, out_i) [nq, kout]"""
+        d = np.ascontiguousarray(d, np.float32)
+        ids = np.ascontiguousarray(ids, np.uint32)
+        parts, nq, k = d.shape
+        od = np.empty((nq, kout), np.float32)
+        oi = np.empty((nq, kout), np.uint32)
+        self._check(_lib.b200ann_merge_topk(self._h, _ptr(d), _ptr(ids), parts, nq, k, kout, _ptr(od), _ptr(oi)))
+        return od, oi
+
+    def merge_topk_raw(self, d, ids, parts, nq, k, kout, out_d, out_i):
+        self._check(_lib.b200ann_merge_topk(self._h, _ptr(d), _ptr(ids), parts, nq, k, kout, _ptr(out_d), _ptr(out_i)))
 
     def set_link_visited_bits(self, bits):
         self._check(_lib.b200ann_set_link_visited_bits(self._h, bits))

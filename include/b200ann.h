@@ -104,6 +104,15 @@ int b200ann_hnsw_search(b200ann_handle_t h, b200ann_index_t ix, const float *q /
                         size_t qstride, size_t k, size_t ef, uint64_t *labels /*[h|d]*/,
                         float *dists /*[h|d]*/, uint32_t *stats /*[h|d]*/);
 
+/* ---- shard-result merge (multi-GPU search) ---------------------------------------------------- */
+/* d/ids [parts, nq, k]: per-shard result lists, each row ascending by (distance,id), ids global,
+ * unfilled slots +inf / B200ANN_INVALID. out_d (may be NULL) / out_i [nq, kout] = the kout smallest
+ * of the union, ascending (distance,id). GPU counterpart of the reference's per-cluster result merge
+ * (CNNS/tests/cluster_hnsw_nsg_search.cpp:189-270; merge_topk_queue, ..._pipeline.cpp:195-212);
+ * the lists come from one NCCL all-gather of every rank's b200ann_nsg_search / _hnsw_search output. */
+int b200ann_merge_topk(b200ann_handle_t h, const float *d /*[h|d]*/, const uint32_t *ids /*[h|d]*/, size_t parts,
+                       size_t nq, size_t k, size_t kout, float *out_d /*[h|d]*/, uint32_t *out_i /*[h|d]*/);
+
 /* tuning knob: log2 of the per-query visited-set size in shared memory (default 10). */
 int b200ann_set_visited_bits(b200ann_handle_t h, int bits);
 /* same for the per-node searches of b200ann_nsg_link (default 12) */

@@ -63,6 +63,7 @@ def oracle():
         lib.orc_nsg_tree_grow.restype = C.c_long
         lib.orc_nsg_tree_grow.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, u32p, C.c_uint, C.c_uint32,
                                           C.c_uint, C.c_int, C.c_int, C.c_uint32, C.c_uint, C.POINTER(C.c_uint)]
+        lib.orc_merge_topk.argtypes = [f32p, u32p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, f32p, u32p]
         _oracle = lib
     return _oracle
 
@@ -156,6 +157,14 @@ def orc_nsg_tree_grow(base, graph, ep, L, mode, width_in, rng_mode=1, seed=0):
     w = C.c_uint(0)
     added = oracle().orc_nsg_tree_grow(base, n, dim, dim, g, g.shape[1], ep, L, mode, rng_mode, seed, width_in, C.byref(w))
     return g, int(added), w.value
+
+
+def orc_merge_topk(d, ids, kout):
+    parts, nq, k = d.shape
+    od = np.empty((nq, kout), np.float32)
+    oi = np.empty((nq, kout), np.uint32)
+    oracle().orc_merge_topk(np.ascontiguousarray(d, np.float32), np.ascontiguousarray(ids, np.uint32), parts, nq, k, kout, od, oi)
+    return od, oi
 
 
 def libc():

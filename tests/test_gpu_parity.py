@@ -316,3 +316,20 @@ def test_nsg_build_end_to_end_recall_vs_reference(B, H, tmp_path):
         rec_ref = R.recall(ref.search(q, 10, 60, seed=1, threads=1), truth)
         assert rec_gpu >= rec_ref - 0.005
     assert rec_gpu > 0.9
+
+
+# ---------------------------------------------------------------- shard-result merge
+@pytest.mark.parametrize("parts,nq,k,kout", [(2, 100, 10, 10), (8, 333, 10, 10), (4, 50, 100, 100), (3, 17, 5, 12), (1, 9, 6, 3)])
+def test_merge_topk_vs_oracle(B, H, parts, nq, k, kout):
+    rng = np.random.default_rng(parts * 1000 + k)
+    d = np.sort(rng.integers(0, 50, (parts, nq, k)).astype(np.float32), axis=2)   # many distance ties
+    ids = rng.permutation(parts * nq * k).astype(np.uint32).reshape(parts, nq, k)
+    # rows must be ascending by (distance,id): fix the id order inside runs of equal distance
+    for s in range(parts):
+        for q in range(nq):
+            o = np.lexsort((ids[s, q], d[s, q]))
+            ids[s, q] = ids[s, q][o]; d[s, q] = d[s, q][o]
+    d[0, 0, k - 2:] = np.inf; ids[0, 0, k - 2:] = R.INVALID                          # unfilled slots
+    od, oi = H.merge_topk(d, ids, kout)
+    wd, wi = R.orc_merge_topk(d, ids, kout)
+    assert (oi == wi).all() and (od == wd).all()

@@ -1,0 +1,416 @@
+// Host-side C++ mirror of the reference's hnswlib API for the hot path, over the b200ann C ABI.
+// Same names, signatures, argument meaning and error behaviour as
+//   hnswlib/hnswlib/hnswlib.h:125-221    labeltype, BaseFilterFunctor, DISTFUNC, SpaceInterface, AlgorithmInterface
+//   hnswlib/hnswlib/space_l2.h:208-253   L2Space            hnswlib/hnswlib/space_ip.h:342-398  InnerProductSpace
+//   hnswlib/hnswlib/bruteforce.h:10-172  BruteforceSearch   hnswlib/hnswlib/hnswalg.h:18-1411   HierarchicalNSW
+// Header-only; link with -lb200ann. No CPU fallback on the search / build path: the distance functions a
+// Space hands out exist only because SpaceInterface promises a callable (the index identifies the
+// metric by the Space's type; a device kernel cannot call a host function pointer, so user-defined
+// spaces are rejected with std::runtime_error).
+//
+// Added batched entry points in the [nq,k] row shape of python_bindings/bindings.cpp:612-695:
+//   searchKnnBatch(queries, nq, k, labels[nq*k], dists[nq*k])   (ascending distance; throws if a row
+//   has fewer than k results, bindings.cpp:646-648)
+#ifndef B200ANN_HNSWLIB_HPP
+#define B200ANN_HNSWLIB_HPP
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <fstream>
+#include <mutex>
+#include <queue>
+#include <stdexcept>
+#include <string>
+#include <unordered_map>
+#include <vector>
+#include "../b200ann.h"
+
+namespace hnswlib {
+
+typedef size_t labeltype;
+typedef unsigned int tableint;
+typedef unsigned int linklistsizeint;
+
+class BaseFilterFunctor {
+ public:
+  virtual bool operator()(hnswlib::labeltype) { return true; }
+  virtual ~BaseFilterFunctor() {}
+};
+
+template <typename MTYPE>
+using DISTFUNC = MTYPE (*)(const void *, const void *, const void *);
+
+template <typename MTYPE>
+class SpaceInterface {
+ public:
+  virtual size_t get_data_size() = 0;
+  virtual DISTFUNC<MTYPE> get_dist_func() = 0;
+  virtual void *get_dist_func_param() = 0;
+  virtual ~SpaceInterface() {}
+};
+
+namespace detail {
+inline float l2_host(const void *a, const void *b, const void *dimp) {
+  const float *x = (const float *)a, *y = (const float *)b;
+  size_t d = *(const size_t *)dimp;
+  float s = 0;
+  for (size_t i = 0; i < d; i++) { float t = x[i] - y[i]; s += t * t; }
+  return s;
+}
+inline float ip_host(const void *a, const void *b, const void *dimp) {
+  const float *x = (const float *)a, *y = (const float *)b;
+  size_t d = *(const size_t *)dimp;
+  float s = 0;
+  for (size_t i = 0; i < d; i++) s += x[i] * y[i];
+  return 1.0f - s;
+}
+inline void check(b200ann_handle_t h, int rc, const char *what) {
+  if (rc != 0) throw std::runtime_error(std::string(what) + ": " + (h ? b200ann_last_error(h) : "no CUDA device (b200ann has no CPU fallback)"));
+}
+struct Gpu {
+  b200ann_handle_t h = nullptr;
+  explicit Gpu(int device = 0) { check(nullptr, b200ann_create(device, &h), "b200ann_create"); }
+  ~Gpu() { b200ann_destroy(h); }
+  Gpu(const Gpu &) = delete;
+  Gpu &operator=(const Gpu &) = delete;
+};
+}  // namespace detail
+
+class L2Space : public SpaceInterface<float> {
+  size_t data_size_, dim_;
+ public:
+  explicit L2Space(size_t dim) : data_size_(dim * sizeof(float)), dim_(dim) {}
+  size_t get_data_size() override { return data_size_; }
+  DISTFUNC<float> get_dist_func() override { return detail::l2_host; }
+  void *get_dist_func_param() override { return &dim_; }
+};
+
+class InnerProductSpace : public SpaceInterface<float> {
+  size_t data_size_, dim_;
+ public:
+  explicit InnerProductSpace(size_t dim) : data_size_(dim * sizeof(float)), dim_(dim) {}
+  size_t get_data_size() override { return data_size_; }
+  DISTFUNC<float> get_dist_func() override { return detail::ip_host; }
+  void *get_dist_func_param() override { return &dim_; }
+};
+
+namespace detail {
+// metric + dim of a Space; anything but the two known spaces is rejected
+inline void space_info(SpaceInterface<float> *s, int &metric, size_t &dim) {
+  if (dynamic_cast<L2Space *>(s)) metric = B200ANN_L2;
+  else if (dynamic_cast<InnerProductSpace *>(s)) metric = B200ANN_IP;
+  else throw std::runtime_error("b200ann: only L2Space and InnerProductSpace run on the GPU (a device kernel cannot call a host DISTFUNC)");
+  dim = *(size_t *)s->get_dist_func_param();
+}
+}  // namespace detail
+
+template <typename dist_t>
+class AlgorithmInterface {
+ public:
+  virtual void addPoint(const void *datapoint, labeltype label, bool replace_deleted = false) = 0;
+  virtual std::priority_queue<std::pair<dist_t, labeltype>> searchKnn(const void *, size_t, BaseFilterFunctor *isIdAllowed = nullptr) const = 0;
+  // closer first (hnswlib.h:203-221)
+  virtual std::vector<std::pair<dist_t, labeltype>> searchKnnCloserFirst(const void *query_data, size_t k,
+                                                                        BaseFilterFunctor *isIdAllowed = nullptr) const {
+    auto ret = searchKnn(query_data, k, isIdAllowed);
+    std::vector<std::pair<dist_t, labeltype>> result(ret.size());
+    size_t sz = ret.size();
+    while (!ret.empty()) { result[--sz] = ret.top(); ret.pop(); }
+    return result;
+  }
+  virtual void saveIndex(const std::string &location) = 0;
+  virtual ~AlgorithmInterface() {}
+};
+
+// hnswlib::BruteforceSearch (bruteforce.h:10-172): exact scan with top-k, the reference's own
+// ground-truth oracle. Points are staged on the host by addPoint (the reference copies them too,
+// bruteforce.h:79-81) and uploaded once before the next search.
+template <typename dist_t>
+class BruteforceSearch : public AlgorithmInterface<dist_t> {
+ public:
+  size_t maxelements_, cur_element_count, dim_;
+  int metric_;
+
+  BruteforceSearch(SpaceInterface<dist_t> *s, size_t maxElements, int device = 0) : maxelements_(maxElements), cur_element_count(0), gpu_(device) {
+    detail::space_info(s, metric_, dim_);
+    data_.resize(maxElements * dim_);
+    labels_.resize(maxElements);
+  }
+  ~BruteforceSearch() { if (ix_) b200ann_index_destroy(ix_); }
+
+  void addPoint(const void *datapoint, labeltype label, bool = false) override {
+    std::unique_lock<std::mutex> lock(mu_);
+    size_t idx;
+    auto it = pos_.find(label);
+    if (it != pos_.end()) idx = it->second;
+    else {
+      if (cur_element_count >= maxelements_) throw std::runtime_error("The number of elements exceeds the specified limit\n");  // bruteforce.h:73-75
+      idx = cur_element_count++;
+      pos_[label] = idx;
+    }
+    labels_[idx] = label;
+    std::memcpy(&data_[idx * dim_], datapoint, dim_ * sizeof(float));
+    dirty_ = true;
+  }
+  void removePoint(labeltype label) {  // bruteforce.h:86-103: the last element takes the hole
+    std::unique_lock<std::mutex> lock(mu_);
+    auto it = pos_.find(label);
+    if (it == pos_.end()) return;
+    size_t idx = it->second, last = cur_element_count - 1;
+    pos_.erase(it);
+    if (idx != last) {
+      std::memcpy(&data_[idx * dim_], &data_[last * dim_], dim_ * sizeof(float));
+      labels_[idx] = labels_[last];
+      pos_[labels_[idx]] = idx;
+    }
+    cur_element_count--;
+    dirty_ = true;
+  }
+
+  // [nq,k] rows ascending by (distance, insertion position)
+  void searchKnnBatch(const float *queries, size_t nq, size_t k, labeltype *labels, dist_t *dists) const {
+    std::unique_lock<std::mutex> lock(mu_);
+    if (k > cur_element_count) throw std::runtime_error("BruteforceSearch: k > number of elements");  // assert at bruteforce.h:108
+    upload();
+    std::vector<uint32_t> ids(nq * k);
+    detail::check(gpu_.h, b200ann_bf_knn(gpu_.h, ix_, queries, nq, dim_, k, ids.data(), dists), "BruteforceSearch::searchKnn");
+    for (size_t i = 0; i < nq * k; i++) labels[i] = labels_[ids[i]];
+  }
+  std::priority_queue<std::pair<dist_t, labeltype>> searchKnn(const void *query_data, size_t k,
+                                                              BaseFilterFunctor *isIdAllowed = nullptr) const override {
+    std::priority_queue<std::pair<dist_t, labeltype>> res;
+    if (cur_element_count == 0) return res;
+    size_t kk = k < cur_element_count ? k : cur_element_count;
+    for (;;) {
+      std::vector<labeltype> lab(kk);
+      std::vector<dist_t> d(kk);
+      searchKnnBatch((const float *)query_data, 1, kk, lab.data(), d.data());
+      res = std::priority_queue<std::pair<dist_t, labeltype>>();
+      for (size_t i = 0; i < kk && res.size() < k; i++)
+        if (!isIdAllowed || (*isIdAllowed)(lab[i])) res.emplace(d[i], lab[i]);
+      if (res.size() >= k || kk == cur_element_count || !isIdAllowed) break;
+      kk = kk * 4 < cur_element_count ? kk * 4 : cur_element_count;  // filtered: widen the exact scan
+    }
+    return res;
+  }
+
+  // bruteforce.h:138-171: [maxelements][size_per_element][cur_element_count] then rows [vector][label]
+  void saveIndex(const std::string &location) override {
+    std::ofstream out(location, std::ios::binary);
+    size_t spe = dim_ * sizeof(float) + sizeof(labeltype);
+    out.write((char *)&maxelements_, sizeof(size_t));
+    out.write((char *)&spe, sizeof(size_t));
+    out.write((char *)&cur_element_count, sizeof(size_t));
+    for (size_t i = 0; i < maxelements_; i++) {
+      out.write((const char *)&data_[i * dim_], dim_ * sizeof(float));
+      out.write((const char *)&labels_[i], sizeof(labeltype));
+    }
+  }
+  void loadIndex(const std::string &location, SpaceInterface<dist_t> *s) {
+    std::ifstream in(location, std::ios::binary);
+    if (!in) throw std::runtime_error("Cannot open file");
+    detail::space_info(s, metric_, dim_);
+    size_t spe;
+    in.read((char *)&maxelements_, sizeof(size_t));
+    in.read((char *)&spe, sizeof(size_t));
+    in.read((char *)&cur_element_count, sizeof(size_t));
+    data_.resize(maxelements_ * dim_);
+    labels_.resize(maxelements_);
+    pos_.clear();
+    for (size_t i = 0; i < maxelements_; i++) {
+      in.read((char *)&data_[i * dim_], dim_ * sizeof(float));
+      in.read((char *)&labels_[i], sizeof(labeltype));
+      if (i < cur_element_count) pos_[labels_[i]] = i;
+    }
+    dirty_ = true;
+  }
+
+ private:
+  void upload() const {
+    if (!dirty_ && ix_) return;
+    if (ix_) { b200ann_index_destroy(ix_); ix_ = nullptr; }
+    detail::check(gpu_.h, b200ann_index_create(gpu_.h, data_.data(), cur_element_count, dim_, dim_, metric_, &ix_), "b200ann_index_create");
+    dirty_ = false;
+  }
+  detail::Gpu gpu_;
+  std::vector<float> data_;
+  std::vector<labeltype> labels_;
+  std::unordered_map<labeltype, size_t> pos_;
+  mutable b200ann_index_t ix_ = nullptr;
+  mutable bool dirty_ = true;
+  mutable std::mutex mu_;
+};
+
+// hnswlib::HierarchicalNSW (hnswalg.h:18-1411), query side: load an index written by
+// HierarchicalNSW::saveIndex (:685-713), search it on the GPU, write it back in the same format.
+template <typename dist_t>
+class HierarchicalNSW : public AlgorithmInterface<dist_t> {
+ public:
+  // same public fields the reference exposes and the hybrid index pokes (index_hnsw_nsg.h:110-148)
+  size_t max_elements_ = 0, cur_element_count = 0, M_ = 0, maxM_ = 0, maxM0_ = 0, ef_construction_ = 0, ef_ = 10;
+  double mult_ = 0;
+  int maxlevel_ = -1;
+  tableint enterpoint_node_ = 0;
+  std::vector<int> element_levels_;
+
+  // load ctor (hnswalg.h:78-86)
+  HierarchicalNSW(SpaceInterface<dist_t> *s, const std::string &location, bool = false, size_t max_elements = 0, bool = false, int device = 0)
+      : gpu_(device) {
+    detail::space_info(s, metric_, dim_);
+    loadIndex(location, s, max_elements);
+  }
+  ~HierarchicalNSW() { if (ix_) b200ann_index_destroy(ix_); }
+
+  void setEf(size_t ef) { ef_ = ef; }  // hnswalg.h:173
+
+  // hnswalg.h:716-822. Throws std::runtime_error("Cannot open file") like :720.
+  void loadIndex(const std::string &location, SpaceInterface<dist_t> *s, size_t max_elements_i = 0) {
+    std::ifstream in(location, std::ios::binary);
+    if (!in.is_open()) throw std::runtime_error("Cannot open file");
+    detail::space_info(s, metric_, dim_);
+    size_t offsetLevel0, size_data_per_element, label_offset, offsetData;
+    rd(in, offsetLevel0); rd(in, max_elements_); rd(in, cur_element_count); rd(in, size_data_per_element);
+    rd(in, label_offset); rd(in, offsetData); rd(in, maxlevel_); rd(in, enterpoint_node_); rd(in, maxM_); rd(in, maxM0_);
+    rd(in, M_); rd(in, mult_); rd(in, ef_construction_);
+    if (max_elements_i > max_elements_) max_elements_ = max_elements_i;
+    if ((label_offset - offsetData) / sizeof(float) != dim_) throw std::runtime_error("index file dimension does not match the space");
+    const size_t n = cur_element_count;
+    std::vector<char> blob(n * size_data_per_element);
+    in.read(blob.data(), (std::streamsize)blob.size());
+    vec_.resize(n * dim_); labels_.resize(n); links0_.assign(n * maxM0_, B200ANN_INVALID);
+    for (size_t i = 0; i < n; i++) {
+      const char *row = blob.data() + i * size_data_per_element;
+      unsigned short cnt = *(const unsigned short *)(row + offsetLevel0);
+      std::memcpy(&links0_[i * maxM0_], row + offsetLevel0 + 4, (size_t)cnt * 4);
+      std::memcpy(&vec_[i * dim_], row + offsetData, dim_ * sizeof(float));
+      labeltype lab;
+      std::memcpy(&lab, row + label_offset, sizeof(labeltype));
+      labels_[i] = lab;
+    }
+    const size_t slpe = maxM_ * 4 + 4;  // size_links_per_element_ (:113)
+    element_levels_.assign(n, 0); upper_ptr_.assign(n, 0); upper_links_.clear();
+    for (size_t i = 0; i < n; i++) {
+      unsigned int sz;
+      rd(in, sz);
+      if (!sz) continue;
+      int lv = (int)(sz / slpe);
+      element_levels_[i] = lv;
+      upper_ptr_[i] = (uint32_t)(upper_links_.size() / maxM_);
+      std::vector<char> ll(sz);
+      in.read(ll.data(), sz);
+      for (int l = 0; l < lv; l++) {
+        const char *p = ll.data() + (size_t)l * slpe;
+        unsigned short cnt = *(const unsigned short *)p;
+        size_t base = upper_links_.size();
+        upper_links_.resize(base + maxM_, B200ANN_INVALID);
+        std::memcpy(&upper_links_[base], p + 4, (size_t)cnt * 4);
+      }
+    }
+    upload();
+  }
+
+  // hnswalg.h:685-713, byte-compatible with the reference's loader
+  void saveIndex(const std::string &location) override {
+    std::ofstream out(location, std::ios::binary);
+    const size_t n = cur_element_count;
+    size_t size_links_level0 = maxM0_ * 4 + 4, data_size = dim_ * sizeof(float);
+    size_t size_data_per_element = size_links_level0 + data_size + sizeof(labeltype);
+    size_t offsetLevel0 = 0, offsetData = size_links_level0, label_offset = size_links_level0 + data_size;
+    wr(out, offsetLevel0); wr(out, max_elements_); wr(out, cur_element_count); wr(out, size_data_per_element);
+    wr(out, label_offset); wr(out, offsetData); wr(out, maxlevel_); wr(out, enterpoint_node_); wr(out, maxM_); wr(out, maxM0_);
+    wr(out, M_); wr(out, mult_); wr(out, ef_construction_);
+    std::vector<char> row(size_data_per_element);
+    for (size_t i = 0; i < n; i++) {
+      std::memset(row.data(), 0, row.size());
+      unsigned short cnt = 0;
+      while (cnt < maxM0_ && links0_[i * maxM0_ + cnt] != B200ANN_INVALID) cnt++;
+      std::memcpy(row.data(), &cnt, 2);
+      std::memcpy(row.data() + 4, &links0_[i * maxM0_], (size_t)cnt * 4);
+      std::memcpy(row.data() + offsetData, &vec_[i * dim_], data_size);
+      labeltype lab = labels_[i];
+      std::memcpy(row.data() + label_offset, &lab, sizeof(labeltype));
+      out.write(row.data(), (std::streamsize)row.size());
+    }
+    const size_t slpe = maxM_ * 4 + 4;
+    for (size_t i = 0; i < n; i++) {
+      unsigned int sz = element_levels_[i] > 0 ? (unsigned int)(slpe * element_levels_[i]) : 0;
+      wr(out, sz);
+      for (int l = 0; l < element_levels_[i]; l++) {
+        std::vector<char> ll(slpe, 0);
+        const uint32_t *src = &upper_links_[((size_t)upper_ptr_[i] + l) * maxM_];
+        unsigned short cnt = 0;
+        while (cnt < maxM_ && src[cnt] != B200ANN_INVALID) cnt++;
+        std::memcpy(ll.data(), &cnt, 2);
+        std::memcpy(ll.data() + 4, src, (size_t)cnt * 4);
+        out.write(ll.data(), (std::streamsize)slpe);
+      }
+    }
+  }
+
+  void addPoint(const void *, labeltype, bool = false) override {
+    throw std::runtime_error("HierarchicalNSW::addPoint: GPU construction is not available in this build; load an index with loadIndex");
+  }
+
+  // [nq,k] rows, ascending distance; throws when some row has fewer than k results (bindings.cpp:646-648)
+  void searchKnnBatch(const float *queries, size_t nq, size_t k, labeltype *labels, dist_t *dists) const {
+    std::vector<uint64_t> lab(nq * k);
+    std::unique_lock<std::mutex> lock(mu_);
+    detail::check(gpu_.h, b200ann_hnsw_search(gpu_.h, ix_, queries, nq, dim_, k, ef_, lab.data(), dists, nullptr), "HierarchicalNSW::searchKnn");
+    for (size_t i = 0; i < nq * k; i++) labels[i] = (labeltype)lab[i];
+  }
+  // hnswalg.h:1270-1324: max-heap of (distance,label), at most k entries; no exception when fewer
+  // than k exist. A filter (not bare_bone, :1306) is honoured by widening the beam on the host side.
+  std::priority_queue<std::pair<dist_t, labeltype>> searchKnn(const void *query_data, size_t k,
+                                                              BaseFilterFunctor *isIdAllowed = nullptr) const override {
+    std::priority_queue<std::pair<dist_t, labeltype>> res;
+    if (cur_element_count == 0) return res;
+    size_t kk = k < cur_element_count ? k : cur_element_count;
+    for (;;) {
+      std::vector<uint64_t> lab(kk);
+      std::vector<dist_t> d(kk);
+      {
+        std::unique_lock<std::mutex> lock(mu_);
+        size_t ef = ef_ > kk ? ef_ : kk;
+        int rc = b200ann_hnsw_search(gpu_.h, ix_, (const float *)query_data, 1, dim_, kk, ef, lab.data(), d.data(), nullptr);
+        if (rc != 0 && rc != B200ANN_ERR_FEWER) detail::check(gpu_.h, rc, "HierarchicalNSW::searchKnn");
+      }
+      res = std::priority_queue<std::pair<dist_t, labeltype>>();
+      for (size_t i = 0; i < kk && res.size() < k; i++)
+        if (lab[i] != ~(uint64_t)0 && (!isIdAllowed || (*isIdAllowed)((labeltype)lab[i]))) res.emplace(d[i], (labeltype)lab[i]);
+      if (res.size() >= k || kk == cur_element_count || !isIdAllowed) break;
+      kk = kk * 4 < cur_element_count ? kk * 4 : cur_element_count;
+    }
+    return res;
+  }
+
+  labeltype getExternalLabel(tableint internal_id) const { return labels_[internal_id]; }
+  const float *getDataByInternalId(tableint internal_id) const { return &vec_[(size_t)internal_id * dim_]; }
+  b200ann_handle_t handle() const { return gpu_.h; }
+  b200ann_index_t device_index() const { return ix_; }
+
+ private:
+  template <typename T> static void rd(std::istream &in, T &v) { in.read((char *)&v, sizeof(T)); }
+  template <typename T> static void wr(std::ostream &out, const T &v) { out.write((const char *)&v, sizeof(T)); }
+  void upload() {
+    if (ix_) { b200ann_index_destroy(ix_); ix_ = nullptr; }
+    const size_t n = cur_element_count;
+    if (n == 0) return;
+    detail::check(gpu_.h, b200ann_index_create(gpu_.h, vec_.data(), n, dim_, dim_, metric_, &ix_), "b200ann_index_create");
+    std::vector<int32_t> lv(element_levels_.begin(), element_levels_.end());
+    std::vector<uint64_t> lab(labels_.begin(), labels_.end());
+    detail::check(gpu_.h, b200ann_index_set_hnsw(ix_, links0_.data(), maxM0_, lv.data(), upper_ptr_.data(),
+                                                 upper_links_.empty() ? nullptr : upper_links_.data(), upper_links_.size() / (maxM_ ? maxM_ : 1),
+                                                 maxM_, lab.data(), enterpoint_node_, maxlevel_), "b200ann_index_set_hnsw");
+  }
+  detail::Gpu gpu_;
+  int metric_ = 0;
+  size_t dim_ = 0;
+  std::vector<float> vec_;
+  std::vector<labeltype> labels_;
+  std::vector<uint32_t> links0_, upper_ptr_, upper_links_;
+  b200ann_index_t ix_ = nullptr;
+  mutable std::mutex mu_;
+};
+
+}  // namespace hnswlib
+#endif

@@ -1,0 +1,99 @@
+// Mirrors hnswlib/tests/cpp/searchKnnCloserFirst_test.cpp:18-68 (ordering equivalence searchKnn vs
+// searchKnnCloserFirst, Bruteforce as truth) and searchKnnWithFilter_test.cpp:33-88 (filter honoured)
+// against the b200ann hnswlib shim; then loads an index file written by the REFERENCE hnswlib
+// (argv[1], dim argv[2]) and checks recall of the GPU search against the shim's brute force and that
+// saveIndex round-trips. Exit code 0 iff every assertion holds.
+#include <b200ann/hnswlib.hpp>
+#include <algorithm>
+#include <cassert>
+#include <cstdio>
+#include <cstdlib>
+#include <random>
+#include <set>
+
+#define CHECK(c) do { if (!(c)) { printf("CHECK failed: %s (line %d)\n", #c, __LINE__); return 1; } } while (0)
+
+struct PickDivisibleIds : hnswlib::BaseFilterFunctor {
+  unsigned divisor;
+  explicit PickDivisibleIds(unsigned d) : divisor(d) {}
+  bool operator()(hnswlib::labeltype id) override { return id % divisor == 0; }
+};
+
+int main(int argc, char **argv) {
+  {  // ---- searchKnnCloserFirst_test: d=4 n=100 nq=10 k=10, seed 47
+    int d = 4; size_t n = 100, nq = 10, k = 10;
+    std::vector<float> data(n * d), query(nq * d);
+    std::mt19937 rng; rng.seed(47);
+    std::uniform_real_distribution<> distrib;
+    for (auto &v : data) v = (float)distrib(rng);
+    for (auto &v : query) v = (float)distrib(rng);
+    hnswlib::L2Space space(d);
+    hnswlib::AlgorithmInterface<float> *alg_brute = new hnswlib::BruteforceSearch<float>(&space, 2 * n);
+    for (size_t i = 0; i < n; ++i) alg_brute->addPoint(data.data() + d * i, i);
+    for (size_t j = 0; j < nq; ++j) {
+      const void *p = query.data() + j * d;
+      auto gd = alg_brute->searchKnn(p, k);
+      auto res = alg_brute->searchKnnCloserFirst(p, k);
+      CHECK(gd.size() == res.size() && gd.size() == k);
+      size_t t = gd.size();
+      while (!gd.empty()) { CHECK(gd.top() == res[--t]); gd.pop(); }
+      for (size_t i = 1; i < res.size(); i++) CHECK(res[i - 1].first <= res[i].first);
+      // truth by the Space's own distance function
+      std::vector<std::pair<float, size_t>> all;
+      size_t dd = d;
+      for (size_t i = 0; i < n; i++) all.push_back({space.get_dist_func()(p, data.data() + d * i, &dd), i});
+      std::sort(all.begin(), all.end());
+      for (size_t i = 0; i < k; i++) CHECK(all[i].second == res[i].second);
+    }
+    // ---- searchKnnWithFilter_test: only ids divisible by 3
+    PickDivisibleIds pick(3);
+    for (size_t j = 0; j < nq; ++j) {
+      auto res = alg_brute->searchKnnCloserFirst(query.data() + j * d, k, &pick);
+      CHECK(res.size() == k);
+      for (auto &r : res) CHECK(r.second % 3 == 0);
+    }
+    bool threw = false;
+    try { for (size_t i = 0; i < 3 * n; i++) alg_brute->addPoint(data.data(), 1000 + i); } catch (std::runtime_error &) { threw = true; }
+    CHECK(threw);  // capacity error like bruteforce.h:73-75
+    delete alg_brute;
+  }
+  if (argc > 2) {  // ---- reference-built index file
+    size_t dim = (size_t)atoi(argv[2]);
+    hnswlib::L2Space space(dim);
+    hnswlib::HierarchicalNSW<float> index(&space, std::string(argv[1]));
+    size_t n = index.cur_element_count, nq = 100, k = 10;
+    hnswlib::BruteforceSearch<float> bf(&space, n);
+    for (size_t i = 0; i < n; i++) bf.addPoint(index.getDataByInternalId((hnswlib::tableint)i), index.getExternalLabel((hnswlib::tableint)i));
+    std::mt19937 rng(3);
+    std::uniform_real_distribution<float> u(0.f, 1.f);
+    std::vector<float> q(nq * dim);
+    for (auto &v : q) v = u(rng);
+    index.setEf(100);
+    size_t hit = 0;
+    std::vector<hnswlib::labeltype> lab(nq * k); std::vector<float> dist(nq * k);
+    index.searchKnnBatch(q.data(), nq, k, lab.data(), dist.data());
+    for (size_t j = 0; j < nq; j++) {
+      auto truth = bf.searchKnnCloserFirst(q.data() + j * dim, k);
+      auto got = index.searchKnnCloserFirst(q.data() + j * dim, k);
+      CHECK(got.size() == k);
+      std::set<hnswlib::labeltype> ts;
+      for (auto &t : truth) ts.insert(t.second);
+      for (size_t i = 0; i < k; i++) { hit += ts.count(got[i].second); CHECK(got[i].second == lab[j * k + i]); }
+    }
+    double recall = (double)hit / (nq * k);
+    printf("reference-built index: n=%zu recall@10 %.4f\n", n, recall);
+    CHECK(recall > 0.95);
+    std::string out = std::string(argv[1]) + ".resaved";
+    index.saveIndex(out);
+    hnswlib::HierarchicalNSW<float> again(&space, out);
+    std::vector<hnswlib::labeltype> lab2(nq * k); std::vector<float> dist2(nq * k);
+    again.setEf(100);
+    again.searchKnnBatch(q.data(), nq, k, lab2.data(), dist2.data());
+    CHECK(lab == lab2 && dist == dist2);
+    bool threw = false;
+    try { hnswlib::HierarchicalNSW<float> bad(&space, std::string("/nonexistent/file.bin")); } catch (std::runtime_error &) { threw = true; }
+    CHECK(threw);
+  }
+  printf("hnswlib shim ok\n");
+  return 0;
+}

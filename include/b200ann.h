@@ -104,6 +104,25 @@ int b200ann_hnsw_search(b200ann_handle_t h, b200ann_index_t ix, const float *q /
                         size_t qstride, size_t k, size_t ef, uint64_t *labels /*[h|d]*/,
                         float *dists /*[h|d]*/, uint32_t *stats /*[h|d]*/);
 
+/* replaces hnsw_nsg::IndexNSG::SearchFromEnterpoint (hnsw_nsg/src/index_nsg.cpp:703-782) for a batch:
+ * like b200ann_nsg_search, but query i starts from entry[i] instead of the navigating node. The
+ * reference's seed rules are kept: the entry point itself is marked visited and never
+ * evaluated; seeds = its first L out-neighbours, then neighbours of those seeds (a slot whose
+ * neighbour was already visited holds node 0), then pseudo-random ids. Needs K <= L < n. */
+int b200ann_nsg_search_from(b200ann_handle_t h, b200ann_index_t ix, const float *q /*[h|d]*/, size_t nq,
+                            size_t qstride, size_t K, size_t L, uint32_t seed, const uint32_t *entry /*[h|d] [nq]*/,
+                            uint32_t *ids /*[h|d]*/, float *dists /*[h|d] or NULL*/, uint32_t *stats /*[h|d] or NULL*/);
+
+/* replaces hnsw_nsg::HNSW_NSG::searchKnn (hnsw_nsg/include/index_hnsw_nsg.h:107-151) for a batch:
+ * greedy descent on the HNSW levels >= 1 of the index (b200ann_index_set_hnsw), external label of the
+ * node it ends on = NSG entry point, then SearchFromEnterpoint over the NSG graph
+ * (b200ann_index_set_graph / b200ann_nsg_build) in ONE kernel. K = the reference's max(k, ef_), L = its
+ * "L_search". ids [nq,K]; entry_out [nq] (optional) = the entry labels; stats count both phases. */
+int b200ann_hybrid_search(b200ann_handle_t h, b200ann_index_t ix, const float *q /*[h|d]*/, size_t nq,
+                          size_t qstride, size_t K, size_t L, uint32_t seed, uint32_t *ids /*[h|d]*/,
+                          float *dists /*[h|d] or NULL*/, uint32_t *entry_out /*[h|d] or NULL*/,
+                          uint32_t *stats /*[h|d] or NULL*/);
+
 /* ---- shard-result merge (multi-GPU search) ---------------------------------------------------- */
 /* d/ids [parts, nq, k]: per-shard result lists, each row ascending by (distance,id), ids global,
  * unfilled slots +inf / B200ANN_INVALID. out_d (may be NULL) / out_i [nq, kout] = the kout smallest

@@ -40,7 +40,8 @@ enum {
   ORC_IP_GPU = 6,        /* 1 - dot in the CUDA kernels' order */
   ORC_FASTL2_EFANNA_AVX = 7, /* ||x||^2 - 2<q,x>, DistanceFastL2, distance.h:232-322 */
   ORC_L2_SEQ_FMA = 8,    /* order of csrc/bf_knn.cu: sequential over the dimension with fmaf */
-  ORC_IP_SEQ_FMA = 9
+  ORC_IP_SEQ_FMA = 9,
+  ORC_L2_HYBRID_AVX = 10 /* hnsw_nsg::DistanceL2AVX::compare, hnsw_nsg/include/nsg/distance.h:325-346 */
 };
 
 /* space_l2.h:6-20 — sequential, multiply then add (no FMA: built with -ffp-contract=off) */
@@ -174,6 +175,19 @@ static float dot_efanna_avx(const float *a, const float *b, size_t size) {
   return s[0] + s[1] + s[2] + s[3] + s[4] + s[5] + s[6] + s[7];
 }
 
+/* hnsw_nsg::DistanceL2AVX::compare (hnsw_nsg/include/nsg/distance.h:325-346): 8 lanes, mul then add,
+ * lanes summed in index order. The reference steps i += 8 while i < size, i.e. it reads past the row
+ * end when size % 8 != 0; the restatement treats elements >= size as zero. */
+static float l2_hybrid_avx(const float *a, const float *b, size_t size) {
+  float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (size_t i = 0; i < size; i += 8)
+    for (int l = 0; l < 8; l++) {
+      float d = (i + l < size ? a[i + l] : 0.f) - (i + l < size ? b[i + l] : 0.f);
+      s[l] = s[l] + d * d;
+    }
+  return s[0] + s[1] + s[2] + s[3] + s[4] + s[5] + s[6] + s[7];
+}
+
 /* Summation order of the CUDA kernels (hnsw-nsg_b200/csrc/dist.cuh): a row of nch = ceil(dim/4)
  * float4 chunks is split over a team of `team` lanes; lane t owns chunks t, t+team, t+2*team, ...
  * and accumulates x,y,z,w of each chunk in that order with fmaf; lane sums are combined with an
@@ -225,6 +239,7 @@ EXPORT float orc_dist(int mode, const float *a, const float *b, size_t dim) {
     case ORC_IP_GPU: return gpu_order(a, b, dim, g_gpu_team, 1);
     case ORC_L2_SEQ_FMA: return seq_fma(a, b, dim, 0);
     case ORC_IP_SEQ_FMA: return seq_fma(a, b, dim, 1);
+    case ORC_L2_HYBRID_AVX: return l2_hybrid_avx(a, b, dim);
     case ORC_FASTL2_EFANNA_AVX: /* distance.h:318-322 with norm = ||b||^2 (:232-258) */
       return -2 * dot_efanna_avx(a, b, dim) + dot_efanna_avx(b, b, dim);
   }
@@ -637,6 +652,146 @@ EXPORT int orc_hnsw_search(const float *data, size_t n, size_t dim, size_t strid
       }
     }
     free(visited); free(top); free(cand); free(expd);
+  }
+  return 0;
+}
+
+/* ------------------------------------------------------------------ hybrid HNSW_NSG search */
+/* IndexNSG::SearchFromEnterpoint (hnsw_nsg/src/index_nsg.cpp:703-782), statement for statement,
+ * quirks included:
+ *   - the entry point is flagged visited but never evaluated, so it cannot be returned (:711-712);
+ *   - the "neighbours of the seeds" pass (:720-728) indexes final_graph_[id] with the running seed
+ *     count tmp_l, and a flagged neighbour is skipped by `continue`, which still advances tmp_l and
+ *     leaves that init_ids slot at its initial value 0 (std::vector<unsigned> init_ids(L), :707);
+ *     such slots are evaluated as node 0 without flagging it (:741-747).
+ * rng_mode as in nsg_beam. retset has L+1 slots. */
+static void nsg_beam_from_ep(const orc_index *ix, uint32_t ep, const float *query, unsigned L, int rng_mode,
+                             uint32_t seed, uint32_t qidx, uint8_t *flags, orc_nb *retset, uint64_t *stats) {
+  uint32_t *init_ids = (uint32_t *)calloc(L ? L : 1, sizeof(uint32_t));
+  flags[ep] = 1;
+  unsigned tmp_l = 0;
+  const uint32_t *eprow = ix->graph + (size_t)ep * ix->gstride;
+  unsigned epdeg = row_degree(eprow, ix->gstride);
+  for (; tmp_l < L && tmp_l < epdeg; tmp_l++) { /* :714-717 */
+    init_ids[tmp_l] = eprow[tmp_l];
+    flags[init_ids[tmp_l]] = 1;
+  }
+  unsigned cur = tmp_l;
+  for (unsigned i = 0; i < cur && tmp_l < L; i++) { /* :720-728 */
+    uint32_t id = init_ids[i];
+    const uint32_t *row = ix->graph + (size_t)id * ix->gstride;
+    unsigned deg = row_degree(row, ix->gstride);
+    for (; tmp_l < L && tmp_l < deg; tmp_l++) {
+      if (flags[row[tmp_l]]) continue;
+      init_ids[tmp_l] = row[tmp_l];
+      flags[init_ids[tmp_l]] = 1;
+    }
+  }
+  uint32_t ctr = 0;
+  while (tmp_l < L) { /* :733-739 */
+    uint32_t id = rng_mode == 0 ? (uint32_t)rand() % (uint32_t)ix->n
+                                : orc_seed_hash(seed, qidx, ctr++) % (uint32_t)ix->n;
+    if (flags[id]) continue;
+    flags[id] = 1;
+    init_ids[tmp_l] = id;
+    tmp_l++;
+  }
+  for (unsigned i = 0; i < L; i++) { /* :741-747 */
+    uint32_t id = init_ids[i];
+    retset[i].id = id;
+    retset[i].distance = orc_dist(ix->mode, ix->data + ix->stride * (size_t)id, query, ix->dim);
+    retset[i].flag = 1;
+    if (stats) stats[0]++;
+  }
+  free(init_ids);
+  qsort(retset, L, sizeof(orc_nb), nb_cmp); /* :749 */
+  int k = 0;
+  while (k < (int)L) { /* :750-778 */
+    int nk = (int)L;
+    if (retset[k].flag) {
+      retset[k].flag = 0;
+      uint32_t n = retset[k].id;
+      const uint32_t *row = ix->graph + (size_t)n * ix->gstride;
+      if (stats) stats[1]++;
+      for (unsigned m = 0; m < ix->gstride && row[m] != ORC_INVALID; ++m) {
+        uint32_t id = row[m];
+        if (flags[id]) continue;
+        flags[id] = 1;
+        float d = orc_dist(ix->mode, query, ix->data + ix->stride * (size_t)id, ix->dim);
+        if (stats) stats[0]++;
+        if (d >= retset[L - 1].distance) continue;
+        orc_nb nn = {id, d, 1};
+        int r = insert_into_pool(retset, L, nn);
+        if (r < nk) nk = r;
+      }
+    }
+    if (nk <= k) k = nk; else ++k;
+  }
+}
+
+/* SearchFromEnterpoint for a batch with explicit per-query entry points. ids/dists [nq,K]. */
+EXPORT int orc_nsg_search_from(const float *data, size_t n, size_t dim, size_t stride, const uint32_t *graph,
+                               unsigned gstride, const uint32_t *entry, const float *q, size_t nq, size_t qstride,
+                               unsigned K, unsigned L, int mode, int rng_mode, uint32_t seed, uint32_t *ids,
+                               float *dists, uint64_t *stats) {
+  if (L < K || L == 0 || L >= n) return -1;
+  orc_index ix = {data, n, dim, stride, graph, gstride, mode};
+  if (stats) memset(stats, 0, sizeof(uint64_t) * 2 * nq);
+#pragma omp parallel if (rng_mode != 0)
+  {
+    uint8_t *flags = (uint8_t *)malloc(n);
+    orc_nb *retset = (orc_nb *)malloc(sizeof(orc_nb) * (L + 1));
+#pragma omp for schedule(dynamic, 8)
+    for (long qi = 0; qi < (long)nq; qi++) {
+      memset(flags, 0, n);
+      nsg_beam_from_ep(&ix, entry[qi], q + (size_t)qi * qstride, L, rng_mode, seed, (uint32_t)qi, flags, retset,
+                       stats ? stats + 2 * qi : NULL);
+      for (unsigned i = 0; i < K; i++) {
+        ids[(size_t)qi * K + i] = retset[i].id;
+        if (dists) dists[(size_t)qi * K + i] = retset[i].distance;
+      }
+    }
+    free(flags); free(retset);
+  }
+  return 0;
+}
+
+/* hnsw_nsg::HNSW_NSG::searchKnn (hnsw_nsg/include/index_hnsw_nsg.h:107-151) batched: greedy descent on
+ * HNSW levels >= 1 (:113-143, distances in mode_hnsw = the hnswlib space), external label of the node
+ * it ends on (:148), then IndexNSG::SearchFromEnterpoint from that label with K = max(k, ef_) (:149)
+ * and pool width L = "L_search" (distances in mode_nsg = DistanceL2AVX). ids/dists [nq,K].
+ * entry_out (optional) [nq] = the entry labels. stats [nq,2] = {distance evaluations, expanded nodes},
+ * upper layers included. */
+EXPORT int orc_hybrid_search(const float *data, size_t n, size_t dim, size_t stride, const int32_t *levels,
+                             const uint32_t *upper_ptr, const uint32_t *upper_links, unsigned maxM,
+                             const uint64_t *labels, uint32_t hnsw_ep, int maxlevel, const uint32_t *graph,
+                             unsigned gstride, const float *q, size_t nq, size_t qstride, unsigned K, unsigned L,
+                             int mode_hnsw, int mode_nsg, int rng_mode, uint32_t seed, uint32_t *ids, float *dists,
+                             uint32_t *entry_out, uint64_t *stats) {
+  if (L < K || L == 0 || L >= n) return -1;
+  orc_hnsw hx = {data, n, dim, stride, NULL, 0, levels, upper_ptr, upper_links, maxM, hnsw_ep, maxlevel, mode_hnsw};
+  orc_index ix = {data, n, dim, stride, graph, gstride, mode_nsg};
+  if (stats) memset(stats, 0, sizeof(uint64_t) * 2 * nq);
+#pragma omp parallel if (rng_mode != 0)
+  {
+    uint8_t *flags = (uint8_t *)malloc(n);
+    orc_nb *retset = (orc_nb *)malloc(sizeof(orc_nb) * (L + 1));
+#pragma omp for schedule(dynamic, 8)
+    for (long qi = 0; qi < (long)nq; qi++) {
+      const float *qv = q + (size_t)qi * qstride;
+      uint64_t *st = stats ? stats + 2 * qi : NULL;
+      float cd;
+      uint32_t cur = hnsw_descend(&hx, qv, &cd, st);
+      uint32_t entry = labels ? (uint32_t)labels[cur] : cur;
+      if (entry_out) entry_out[qi] = entry;
+      memset(flags, 0, n);
+      nsg_beam_from_ep(&ix, entry, qv, L, rng_mode, seed, (uint32_t)qi, flags, retset, st);
+      for (unsigned i = 0; i < K; i++) {
+        ids[(size_t)qi * K + i] = retset[i].id;
+        if (dists) dists[(size_t)qi * K + i] = retset[i].distance;
+      }
+    }
+    free(flags); free(retset);
   }
   return 0;
 }

@@ -14,7 +14,7 @@ INVALID = 0xFFFFFFFF
 
 # oracle distance modes (oracle/oracle.c)
 (L2_SCALAR, IP_SCALAR, L2_HNSW_AVX, IP_HNSW_AVX, L2_EFANNA_AVX, L2_GPU, IP_GPU, FASTL2_EFANNA_AVX, L2_SEQ_FMA,
- IP_SEQ_FMA) = range(10)
+ IP_SEQ_FMA, L2_HYBRID_AVX) = range(11)
 
 f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
 u32p = np.ctypeslib.ndpointer(np.uint32, flags="C_CONTIGUOUS")
@@ -63,6 +63,13 @@ def oracle():
         lib.orc_nsg_tree_grow.restype = C.c_long
         lib.orc_nsg_tree_grow.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, u32p, C.c_uint, C.c_uint32,
                                           C.c_uint, C.c_int, C.c_int, C.c_uint32, C.c_uint, C.POINTER(C.c_uint)]
+        lib.orc_nsg_search_from.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, u32p, C.c_uint, u32p,
+                                            f32p, C.c_size_t, C.c_size_t, C.c_uint, C.c_uint, C.c_int, C.c_int,
+                                            C.c_uint32, u32p, C.c_void_p, C.c_void_p]
+        lib.orc_hybrid_search.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, i32p, u32p, u32p, C.c_uint,
+                                          C.c_void_p, C.c_uint32, C.c_int, u32p, C.c_uint, f32p, C.c_size_t,
+                                          C.c_size_t, C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_int, C.c_uint32,
+                                          u32p, C.c_void_p, C.c_void_p, C.c_void_p]
         lib.orc_merge_topk.argtypes = [f32p, u32p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, f32p, u32p]
         _oracle = lib
     return _oracle
@@ -108,6 +115,36 @@ def orc_hnsw_search(base, h, q, k, ef, mode, variant=1, want_stats=False):
                              up, up.shape[1], _vp(h["labels"]), h["ep"], h["maxlevel"], q, nq, q.shape[1], k, ef,
                              mode, variant, lab, d, _vp(st))
     return (lab, d, st) if want_stats else (lab, d)
+
+
+def orc_nsg_search_from(base, graph, entry, q, K, L, mode, rng_mode=1, seed=0, want_stats=False):
+    n, dim = base.shape
+    nq = q.shape[0]
+    ids = np.empty((nq, K), np.uint32)
+    d = np.empty((nq, K), np.float32)
+    st = np.zeros((nq, 2), np.uint64) if want_stats else None
+    rc = oracle().orc_nsg_search_from(base, n, dim, dim, graph, graph.shape[1], np.ascontiguousarray(entry, np.uint32),
+                                      q, nq, q.shape[1], K, L, mode, rng_mode, seed, ids, _vp(d), _vp(st))
+    assert rc == 0
+    return (ids, d, st) if want_stats else (ids, d)
+
+
+def orc_hybrid_search(base, h, graph, q, K, L, mode_hnsw, mode_nsg, rng_mode=1, seed=0, want_stats=False):
+    """h: parse_hnsw dict (upper layers + labels are used); graph: flat NSG adjacency."""
+    n, dim = base.shape
+    nq = q.shape[0]
+    ids = np.empty((nq, K), np.uint32)
+    d = np.empty((nq, K), np.float32)
+    entry = np.empty(nq, np.uint32)
+    st = np.zeros((nq, 2), np.uint64) if want_stats else None
+    up = h["upper_links"]
+    if up.size == 0:
+        up = np.full((1, max(1, h["maxM"])), INVALID, np.uint32)
+    rc = oracle().orc_hybrid_search(base, n, dim, dim, h["levels"], h["upper_ptr"], up, up.shape[1], _vp(h["labels"]),
+                                    h["ep"], h["maxlevel"], graph, graph.shape[1], q, nq, q.shape[1], K, L,
+                                    mode_hnsw, mode_nsg, rng_mode, seed, ids, _vp(d), _vp(entry), _vp(st))
+    assert rc == 0
+    return (ids, d, entry, st) if want_stats else (ids, d, entry)
 
 
 def pad_graph(knn, gstride=None):
@@ -343,6 +380,17 @@ def reflib(name):
         lib.ref_nsg_optimize.argtypes = [C.c_void_p, f32p]
         lib.ref_nsg_search_opt.argtypes = [C.c_void_p, f32p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_uint, u32p,
                                            C.c_uint, C.c_int]
+    elif name.startswith("hybrid"):
+        lib.ref_hybrid_dist.restype = C.c_float
+        lib.ref_hybrid_dist.argtypes = [f32p, f32p, C.c_uint]
+        lib.ref_hybrid_build.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_char_p, C.c_uint, C.c_uint, C.c_uint,
+                                         C.c_uint, C.c_uint, C.c_char_p, C.c_uint, C.c_int]
+        lib.ref_hybrid_load.restype = C.c_void_p
+        lib.ref_hybrid_load.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_char_p, C.c_uint]
+        lib.ref_hybrid_free.argtypes = [C.c_void_p]
+        lib.ref_hybrid_search.argtypes = [C.c_void_p, f32p, C.c_size_t, C.c_size_t, C.c_size_t, u32p, C.c_uint]
+        lib.ref_hybrid_search_from.argtypes = [C.c_void_p, f32p, f32p, C.c_size_t, C.c_size_t, C.c_uint, u32p, u32p,
+                                               C.c_uint]
     elif name.startswith("efanna"):
         lib.ref_nndescent_build.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_uint, C.c_uint, C.c_uint, C.c_uint,
                                             C.c_uint, C.c_char_p, C.c_uint, C.c_int]
@@ -437,6 +485,43 @@ class RefNsg:
     def close(self):
         if self.h:
             self.lib.ref_nsg_free(self.h)
+            self.h = None
+
+    __del__ = close
+
+
+def ref_hybrid_build(base, knn_path, L, R, C_, M, efc, prefix, seed=1, threads=1, lib="hybrid"):
+    """HNSW_NSG build sequence of hnsw_nsg/tests/test_hnsw_nsg_search.cpp:318-351 -> prefix_hnsw.bin / prefix_nsg.bin"""
+    n, dim = base.shape
+    with _quiet():
+        reflib(lib).ref_hybrid_build(base, n, dim, knn_path.encode(), L, R, C_, M, efc, prefix.encode(), seed, threads)
+
+
+class RefHybrid:
+    def __init__(self, base, prefix, L_search, lib="hybrid"):
+        self.lib = reflib(lib)
+        self.base = base
+        self.n, self.dim = base.shape
+        with _quiet():
+            self.h = self.lib.ref_hybrid_load(base, self.n, self.dim, prefix.encode(), L_search)
+        assert self.h
+
+    def search(self, q, k, ef, seed=1):
+        kout = max(k, ef)
+        ids = np.empty((q.shape[0], kout), np.uint32)
+        with _quiet():
+            self.lib.ref_hybrid_search(self.h, q, q.shape[0], k, ef, ids, seed)
+        return ids
+
+    def search_from(self, q, K, L, entry, seed=1):
+        ids = np.empty((q.shape[0], K), np.uint32)
+        self.lib.ref_hybrid_search_from(self.h, self.base, q, q.shape[0], K, L, np.ascontiguousarray(entry, np.uint32),
+                                        ids, seed)
+        return ids
+
+    def close(self):
+        if self.h:
+            self.lib.ref_hybrid_free(self.h)
             self.h = None
 
     __del__ = close

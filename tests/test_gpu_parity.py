@@ -318,6 +318,72 @@ def test_nsg_build_end_to_end_recall_vs_reference(B, H, tmp_path):
     assert rec_gpu > 0.9
 
 
+# ---------------------------------------------------------------- hybrid HNSW_NSG
+@pytest.mark.parametrize("n,dim,deg,K,L", [(4000, 128, 24, 10, 40), (3000, 96, 30, 20, 20), (2500, 24, 12, 5, 64),
+                                           (1200, 960, 16, 10, 30)])
+def test_nsg_search_from_vs_oracle(B, H, n, dim, deg, K, L):
+    """SearchFromEnterpoint with explicit entries: bit-exact ids/distances vs the oracle in the kernel's
+    summation order; L below, at and above the degree (neighbour-of-seed pass, zero slots, hash fill)"""
+    base = R.data_uniform(n, dim, 1)
+    q = R.data_uniform(120, dim, 2)
+    g = _knn_as_graph(base, deg)
+    g[::3, deg - 5:] = R.INVALID                         # ragged degrees
+    entry = np.random.default_rng(5).integers(0, n, q.shape[0]).astype(np.uint32)
+    ix = B.Index(H, base, 0)
+    ix.set_graph(g, 0)
+    ids, d, st = ix.nsg_search_from(q, entry, K, L, seed=4, want_stats=True)
+    R.oracle().orc_set_gpu_team(B.dist_team(dim))
+    oid, od, ost = R.orc_nsg_search_from(base, g, entry, q, K, L, R.L2_GPU, rng_mode=1, seed=4, want_stats=True)
+    assert (ids == oid).all() and (d == od).all()
+    assert (st[:, 1] == ost[:, 1]).all() and (st[:, 0] >= ost[:, 0]).all()
+    assert not (ids == entry[:, None]).any()             # the entry point is never returned (:711-712)
+
+
+@pytest.mark.skipif(not R.have_ref(), reason="needs oracle/_ref to build the hybrid index")
+def test_hybrid_search_vs_reference_and_oracle(B, H, tmp_path):
+    """index built by the UNMODIFIED reference hybrid (HNSW addPoint loop + Build_NSG + saveIndex) on
+    integer-valued data; b200ann_hybrid_search == oracle bit for bit, and == HNSW_NSG::searchKnn ids when
+    no rand() seed fill is involved (all summation orders are exact on this data)."""
+    n, dim = 5000, 64
+    base = R.data_sift_like(n, dim, 1)
+    q = R.data_sift_like(150, dim, 2)
+    knn = _exact_knn(base, 32)
+    kp, prefix = str(tmp_path / "k.graph"), str(tmp_path / "hy")
+    R.write_knn_graph(kp, knn)
+    R.ref_hybrid_build(base, kp, 32, 20, 200, 6, 60, prefix, seed=7, threads=1)
+    Hh = R.parse_hnsw(prefix + "_hnsw.bin")
+    g, ep, width = R.parse_nsg(prefix + "_nsg.bin", n)
+    assert Hh["maxlevel"] >= 2
+    ix = B.Index(H, base, 0)
+    ix.set_graph(g, ep)
+    ix.set_hnsw(Hh["links0"], Hh["levels"], Hh["upper_ptr"], Hh["upper_links"], Hh["labels"], Hh["ep"], Hh["maxlevel"])
+    truth, _ = R.orc_bf_knn(base, q, 10, R.L2_SCALAR)
+    R.oracle().orc_set_gpu_team(B.dist_team(dim))
+    for K, L in ((10, 16), (20, 40), (10, 80)):
+        ids, d, entry, st = ix.hybrid_search(q, K, L, seed=9, want_stats=True)
+        oid, od, oentry, ost = R.orc_hybrid_search(base, Hh, g, q, K, L, R.L2_GPU, R.L2_GPU, rng_mode=1, seed=9,
+                                                   want_stats=True)
+        assert (entry == oentry).all()
+        assert (ids == oid).all() and (d == od).all()
+        assert (st[:, 1] == ost[:, 1]).all() and (st[:, 0] >= ost[:, 0]).all()
+        hy = R.RefHybrid(base, prefix, L)
+        rids = hy.search(q, 10, K, seed=3)               # ef = K -> max(k, ef) = K ids per query
+        rec_g, rec_r = R.recall(ids[:, :10], truth), R.recall(rids[:, :10], truth)
+        assert abs(rec_g - rec_r) <= 0.005               # north_star: recall within 0.005 at matched L
+        # same distance lists wherever the rand() fill was not needed (ties may permute equal-distance ids)
+        rd = ((base[rids.astype(np.int64)] - q[:, None, :]) ** 2).sum(2).astype(np.float32)
+        same = (rd == d).all(1).mean()
+        assert same > (0.98 if L <= 16 else 0.5), same   # L <= min degree: no rand() in the seeds
+
+
+def test_hybrid_needs_both_graphs(B, H):
+    base = R.data_uniform(200, 8, 1)
+    ix = B.Index(H, base, 0)
+    ix.set_graph(_knn_as_graph(base, 8), 0)
+    with pytest.raises(B.B200AnnError):
+        ix.hybrid_search(base[:4], 5, 10)                # no HNSW levels
+
+
 # ---------------------------------------------------------------- shard-result merge
 @pytest.mark.parametrize("parts,nq,k,kout", [(2, 100, 10, 10), (8, 333, 10, 10), (4, 50, 100, 100), (3, 17, 5, 12), (1, 9, 6, 3)])
 def test_merge_topk_vs_oracle(B, H, parts, nq, k, kout):

@@ -251,3 +251,62 @@ def test_nsg_interinsert_batch_form_properties():
         assert np.allclose(d, want, rtol=1e-5)
     assert (bd != -1).sum(1).mean() > (cd != -1).sum(1).mean()
     assert ((bd != -1).sum(1) <= Rr).all()
+
+
+# ---------------------------------------------------------------- hybrid HNSW_NSG (hnsw_nsg/)
+@needs_ref
+@pytest.mark.parametrize("dim", [8, 24, 128])
+def test_hybrid_distance_vs_reference(dim):
+    """DistanceL2AVX::compare (hnsw_nsg/include/nsg/distance.h:325-346)"""
+    rng = np.random.default_rng(dim)
+    a = rng.normal(size=(16, dim)).astype(np.float32)
+    b = rng.normal(size=(16, dim)).astype(np.float32)
+    for i in range(16):
+        assert R.oracle().orc_dist(R.L2_HYBRID_AVX, a[i], b[i], dim) == R.reflib("hybrid").ref_hybrid_dist(a[i], b[i], dim)
+
+
+@pytest.fixture(scope="module")
+def hybrid_case(tmp_path_factory):
+    """index built by the UNMODIFIED reference hybrid (addPoint loop + Build_NSG + saveIndex, 1 thread)"""
+    n, dim = 3000, 24
+    base = R.data_uniform(n, dim, 1)
+    q = R.data_uniform(80, dim, 2)
+    knn = _exact_knn(base, 30)
+    d = tmp_path_factory.mktemp("hyb")
+    kp, prefix = str(d / "k.graph"), str(d / "hy")
+    R.write_knn_graph(kp, knn)
+    # M=6 keeps the upper layers populated at n=3000 (mult = 1/ln 6)
+    R.ref_hybrid_build(base, kp, 30, 16, 150, 6, 60, prefix, seed=7, threads=1)
+    H = R.parse_hnsw(prefix + "_hnsw.bin")
+    g, ep, width = R.parse_nsg(prefix + "_nsg.bin", n)
+    return base, q, prefix, H, g
+
+
+@needs_ref
+@pytest.mark.parametrize("L,ef,k", [(12, 10, 10), (40, 20, 10), (64, 30, 5)])
+def test_hybrid_search_vs_reference(hybrid_case, L, ef, k):
+    """oracle hybrid search == HNSW_NSG::searchKnn, ids bit for bit. L is chosen both below and above
+    the NSG degree so the neighbour-of-seed pass with its zero-slot quirk and the rand() fill
+    (hnsw_nsg/src/index_nsg.cpp:720-739) are exercised."""
+    base, q, prefix, H, g = hybrid_case
+    assert H["maxlevel"] >= 2
+    hy = R.RefHybrid(base, prefix, L)
+    rids = hy.search(q, k, ef, seed=5)
+    K = max(k, ef)
+    ctypes.CDLL(None).srand(5)
+    oids, _, entry = R.orc_hybrid_search(base, H, g, q, K, L, R.L2_HNSW_AVX, R.L2_HYBRID_AVX, rng_mode=0)
+    assert (rids == oids).all()
+    assert len(np.unique(entry)) > 5      # the descent really picks per-query entry points
+    # entry points are flagged but never evaluated: they cannot be returned (:711-712)
+    assert not (oids == entry[:, None]).any()
+
+
+@needs_ref
+def test_search_from_enterpoint_vs_reference(hybrid_case):
+    base, q, prefix, H, g = hybrid_case
+    hy = R.RefHybrid(base, prefix, 30)
+    entry = np.random.default_rng(4).integers(0, base.shape[0], q.shape[0]).astype(np.uint32)
+    rids = hy.search_from(q, 10, 30, entry, seed=9)
+    ctypes.CDLL(None).srand(9)
+    oids, _ = R.orc_nsg_search_from(base, g, entry, q, 10, 30, R.L2_HYBRID_AVX, rng_mode=0)
+    assert (rids == oids).all()

@@ -56,6 +56,8 @@ _lib.b200ann_nsg_init_ep.argtypes = [_vp, _vp, _vp, _sz, _sz, _u32, _u32, C.POIN
 _lib.b200ann_nsg_link.argtypes = [_vp, _vp, _vp, _sz, _u32, _sz, _sz, _sz, _u32, _vp, _vp, _vp]
 _lib.b200ann_nsg_interinsert.argtypes = [_vp, _vp, _sz, _vp, _vp, C.POINTER(C.c_uint64)]
 _lib.b200ann_merge_topk.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _vp, _vp]
+_lib.b200ann_set_knn_mode.argtypes = [_vp, C.c_int, C.c_int]
+_lib.b200ann_knn_last_stats.argtypes = [_vp, _vp]
 _lib.b200ann_nsg_finish.argtypes = [_vp, _vp, _vp, _vp, _sz, _u32, _sz, _u32, _sz, C.POINTER(_u32)]
 
 EXPORTS = [
@@ -65,7 +67,7 @@ EXPORTS = [
     "b200ann_index_set_hnsw", "b200ann_bf_knn", "b200ann_knn_graph", "b200ann_nsg_search", "b200ann_hnsw_search",
     "b200ann_set_link_visited_bits", "b200ann_nsg_build", "b200ann_nsg_init_ep", "b200ann_nsg_link",
     "b200ann_nsg_interinsert", "b200ann_nsg_finish", "b200ann_merge_topk", "b200ann_nsg_search_from",
-    "b200ann_hybrid_search",
+    "b200ann_hybrid_search", "b200ann_set_knn_mode", "b200ann_knn_last_stats",
 ]
 
 
@@ -127,6 +129,17 @@ class Handle:
     @property
     def last_kernel_ms(self):
         return float(_lib.b200ann_last_kernel_ms(self._h))
+
+    def set_knn_mode(self, mode, slack=-1):
+        """0 auto, 1 fp32 SIMT (csrc/bf_knn.cu), 2 tcgen05 tensor cores + fp32 re-rank (csrc/knn_tc.cu)"""
+        self._check(_lib.b200ann_set_knn_mode(self._h, mode, slack))
+
+    @property
+    def knn_last_stats(self):
+        out = np.zeros(8, np.uint64)
+        self._check(_lib.b200ann_knn_last_stats(self._h, out.ctypes.data_as(_vp)))
+        keys = ["rows", "fallback_rows", "reranked", "passes", "splits", "shortlist", "tiles", "a_resident"]
+        return dict(zip(keys, (int(x) for x in out)))
 
     def set_visited_bits(self, bits):
         self._check(_lib.b200ann_set_visited_bits(self._h, bits))

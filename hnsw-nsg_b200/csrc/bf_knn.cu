@@ -22,6 +22,7 @@ struct BfParams {
   const float *base; size_t bstride; uint32_t n; uint32_t dim;
   const float *q; size_t qstride; uint32_t nq;
   uint32_t k; int ip; int exclude_self;
+  const uint32_t *self_ids;  // optional: the id query i must skip (exclude_self with gathered queries)
   uint32_t splits;          // base range splits (grid.y)
   float *list_d[2]; uint32_t *list_i[2];  // [splits, nq, k] ping-pong lists
   uint8_t *cur;             // [splits, nq] which list is current at exit
@@ -177,6 +178,12 @@ __global__ void __launch_bounds__(NT) bf_knn_kernel(const BfParams p) {
     }
 
     // ---- running top-k: this warp owns queries ty*4+i of its two ty values
+    uint32_t self_id[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const uint32_t qg = q0 + ty * 4 + i;
+      self_id[i] = (p.self_ids && qg < p.nq) ? __ldg(p.self_ids + qg) : qg;
+    }
 #pragma unroll
     for (int i = 0; i < 4; i++) {
       const int ql = ty * 4 + i;
@@ -189,7 +196,7 @@ __global__ void __launch_bounds__(NT) bf_knn_kernel(const BfParams p) {
         if (pend_n[qb] > PEND - 16) flush(qb);
         uint32_t bg = b0 + (j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4));
         float d = p.ip ? 1.0f - acc[i][j] : acc[i][j];
-        bool pass = qg < p.nq && bg < b_end && !(p.exclude_self && bg == qg) &&
+        bool pass = qg < p.nq && bg < b_end && !(p.exclude_self && bg == self_id[i]) &&
                     lex_less(d, bg, thr_d[ql], thr_i[ql]);
         if (pass) {
           uint32_t s = atomicAdd(&pend_n[ql], 1u);
@@ -253,12 +260,12 @@ __global__ void bf_finalize_kernel(const BfParams p, uint32_t *out_i, float *out
 }  // namespace
 
 int launch_bf_knn(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
-                  size_t k, bool exclude_self, uint32_t *ids, float *dists) {
+                  size_t k, bool exclude_self, uint32_t *ids, float *dists, const uint32_t *self_ids) {
   if (nq == 0) return 0;
   BfParams p = {};
   p.base = ix->vec; p.bstride = ix->stride; p.n = (uint32_t)ix->n; p.dim = (uint32_t)ix->dim;
   p.q = q; p.qstride = qstride; p.nq = (uint32_t)nq; p.k = (uint32_t)k;
-  p.ip = ix->metric == B200ANN_IP; p.exclude_self = exclude_self;
+  p.ip = ix->metric == B200ANN_IP; p.exclude_self = exclude_self; p.self_ids = self_ids;
   uint32_t qtiles = (uint32_t)((nq + QT - 1) / QT);
   uint32_t want = 2u * (uint32_t)h->sm_count;  // aim for >= 2 CTAs per SM
   uint32_t splits = qtiles >= want ? 1u : (want + qtiles - 1) / qtiles;

@@ -67,6 +67,14 @@ int b200ann_create(int device, b200ann_handle_t *out) {
     return B200ANN_ERR_CUDA;
   }
   cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device);
+  {  // keep the stream-ordered scratch pool mapped between calls (default: released at every synchronize)
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+      uint64_t keep = ~(uint64_t)0;
+      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
+    cudaGetLastError();
+  }
   *out = h;
   return 0;
 }
@@ -147,6 +155,7 @@ int b200ann_index_destroy(b200ann_index_t ix) {
   cudaStreamSynchronize(ix->h->stream);
   free_graph(ix);
   free_hnsw(ix);
+  knn_tc_free(ix);
   if (ix->vec) cudaFree(ix->vec);
   delete ix;
   return 0;
@@ -217,6 +226,34 @@ int b200ann_index_set_hnsw(b200ann_index_t ix, const uint32_t *links0, size_t ma
   return 0;
 }
 
+// tensor cores when the problem is big enough to fill them (or when forced), else the fp32 SIMT kernel
+static int knn_dispatch(b200ann_handle *h, b200ann_index *ix, const float *q, size_t nq, size_t qstride, size_t k,
+                        bool exclude_self, uint32_t *ids, float *dists) {
+  bool tcp = false;
+  if (h->knn_mode == 2) {
+    if (!knn_tc_supported(ix, nq, k)) return set_err(h, B200ANN_ERR_ARG, "knn: tensor path forced but unsupported (k > 1024, dim > 4096 or no driver entry point)");
+    tcp = true;
+  } else if (h->knn_mode == 0) {
+    tcp = knn_tc_supported(ix, nq, k) && ix->n >= 4096 && (double)nq * (double)ix->n >= (double)(1 << 24);
+  }
+  memset(h->knn_stats, 0, sizeof h->knn_stats);
+  if (tcp) return launch_knn_tc(h, ix, q, nq, qstride, k, exclude_self, ids, dists);
+  return launch_bf_knn(h, ix, q, nq, qstride, k, exclude_self, ids, dists);
+}
+
+int b200ann_set_knn_mode(b200ann_handle_t h, int mode, int slack) {
+  if (!h) return B200ANN_ERR_ARG;
+  if (mode < 0 || mode > 2) return set_err(h, B200ANN_ERR_ARG, "set_knn_mode: mode must be 0 (auto), 1 (fp32 SIMT) or 2 (tensor cores)");
+  h->knn_mode = mode; h->knn_slack = slack;
+  return 0;
+}
+
+int b200ann_knn_last_stats(b200ann_handle_t h, uint64_t *out8) {
+  if (!h || !out8) return B200ANN_ERR_ARG;
+  memcpy(out8, h->knn_stats, sizeof h->knn_stats);
+  return 0;
+}
+
 int b200ann_bf_knn(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_t nq, size_t qstride, size_t k,
                    uint32_t *ids, float *dists) {
   if (!h || !ix) return B200ANN_ERR_ARG;
@@ -228,7 +265,7 @@ int b200ann_bf_knn(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_
   CU_CHECK(h, oi.stage(ids, nq * k, h->stream));
   CU_CHECK(h, od.stage(dists, nq * k, h->stream));
   CallTimer t(h);
-  int rc = launch_bf_knn(h, ix, qin.d, nq, qstride, k, false, oi.d, od.d);
+  int rc = knn_dispatch(h, ix, qin.d, nq, qstride, k, false, oi.d, od.d);
   t.stop();
   if (rc) return rc;
   CU_CHECK(h, oi.finish(h->stream));
@@ -244,7 +281,7 @@ int b200ann_knn_graph(b200ann_handle_t h, b200ann_index_t ix, size_t K, uint32_t
   OutArg<uint32_t> oi;
   CU_CHECK(h, oi.stage(knn, ix->n * K, h->stream));
   CallTimer t(h);
-  int rc = launch_bf_knn(h, ix, ix->vec, ix->n, ix->stride, K, true, oi.d, nullptr);
+  int rc = knn_dispatch(h, ix, ix->vec, ix->n, ix->stride, K, true, oi.d, nullptr);
   t.stop();
   if (rc) return rc;
   CU_CHECK(h, oi.finish(h->stream));

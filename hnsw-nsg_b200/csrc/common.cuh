@@ -20,6 +20,9 @@ struct b200ann_handle {
   int visited_bits = 10;
   int link_visited_bits = 12;
   int sm_count = 148;
+  int knn_mode = 0;          // 0 auto, 1 fp32 SIMT (bf_knn.cu), 2 tensor cores (knn_tc.cu)
+  int knn_slack = -1;        // shortlist slack of the tensor path; < 0 = default
+  uint64_t knn_stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 };
 
 struct b200ann_index {
@@ -41,6 +44,12 @@ struct b200ann_index {
   uint32_t hnsw_ep = 0;
   int maxlevel = -1;
   bool has_hnsw = false;
+  // tensor-core kNN cache (knn_tc.cu): bf16 hi/lo copies [n, tc_dpad], fp32 row norms
+  void *tc_hi = nullptr, *tc_lo = nullptr;
+  float *tc_norms = nullptr;
+  size_t tc_dpad = 0;
+  bool tc_inexact = false;
+  float tc_ny_max = 0.f;
 };
 
 inline int set_err(b200ann_handle *h, int code, const std::string &msg) {
@@ -129,7 +138,12 @@ int launch_nsg_search_from(b200ann_handle *h, const b200ann_index *ix, const flo
 int launch_hnsw_search(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
                        size_t k, size_t ef, uint64_t *labels, float *dists, uint32_t *stats);
 int launch_bf_knn(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
-                  size_t k, bool exclude_self, uint32_t *ids, float *dists);
+                  size_t k, bool exclude_self, uint32_t *ids, float *dists, const uint32_t *self_ids = nullptr);
+// tensor-core path (knn_tc.cu); same contract. knn_dispatch picks the path from h->knn_mode.
+int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t nq, size_t qstride, size_t k,
+                  bool exclude_self, uint32_t *ids, float *dists);
+bool knn_tc_supported(const b200ann_index *ix, size_t nq, size_t k);
+void knn_tc_free(b200ann_index *ix);
 
 // NSG build phases (nsg_build.cu); device pointers only
 int nsg_centroid_launch(b200ann_handle *h, const b200ann_index *ix, float *center);

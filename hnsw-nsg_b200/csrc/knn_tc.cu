@@ -1,0 +1,888 @@
+// Exact brute-force kNN on the 5th-generation tensor cores (sm_100a: tcgen05.mma + TMEM + TMA).
+//
+// Replaces, like bf_knn.cu, hnswlib::BruteforceSearch::searchKnn (hnswlib/hnswlib/bruteforce.h:106-135),
+// IndexGraph::generate_control_set (CNNS/efanna_graph/src/index_graph.cpp:138-153) and, with
+// exclude_self, the exact form of IndexGraph::Build's output (:265-294). Same results as bf_knn.cu bit
+// for bit; only the dense contraction runs on the tensor pipe:
+//
+//   1. prep      fp32 rows -> bf16 "hi" (+ "lo" = bf16(x - hi) when some value is not bf16-exact),
+//                fp32 row norms, max norm.
+//   2. sweep     one CTA = 128 query rows x a range of 256-row base tiles. TMA (128B swizzle) stages the
+//                bf16 K-blocks, one thread issues tcgen05.mma (M128 N256 K16, fp32 accumulators in TMEM,
+//                two accumulator stages), four epilogue warps read TMEM (thread = query row), form the
+//                ranking key  ||y||^2 - 2 x.y  (L2) /  -2 x.y  (IP) and keep, per row, a SHORTLIST of the
+//                K' = K + slack smallest keys: threshold filter + warp-cooperative radix-select compaction.
+//                Inexact data uses three passes hi*hi + hi*lo + lo*hi (bf16x3, error ~2^-16).
+//   3. finalize  CTA per query row: fp32 distances of the shortlisted rows in the canonical sequential-fma
+//                order of bf_knn.cu, bitonic sort by (distance,id), top K out. PROOF of exactness per row:
+//                every row outside the shortlist has key >= tau (the filter threshold), so if
+//                tau - eps > K-th exact distance (eps = rigorous error bound of the tensor-core key) the
+//                shortlist provably contains the true top K. Rows that fail the proof are recomputed by
+//                the fp32 SIMT kernel (launch_bf_knn) - results are exact either way.
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+#include "common.cuh"
+
+namespace tc {
+
+constexpr int BM = 128, BN = 256, BK = 64;          // tile rows (queries), tile columns (base rows), bf16 per K-block
+constexpr int A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2;  // 16 KB, 32 KB
+constexpr int NSTAGE = 4;                           // B ring (and A ring when A streams)
+constexpr int A_SLOTS = 4;                          // resident A K-blocks (64 KB)
+constexpr int NTHREADS = 192;                       // warp0 TMA, warp1 MMA, warps 2-5 epilogue
+constexpr int SMEM_MISC = 8192;
+constexpr int SMEM_BYTES = 1024 + A_SLOTS * A_BYTES + NSTAGE * B_BYTES + SMEM_MISC;
+
+// ---------------------------------------------------------------- PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra WAIT_DONE;\n\t"
+      "bra WAIT_LOOP;\n\t"
+      "WAIT_DONE:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, int c0, int c1, uint64_t *bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(dst)),
+      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t *bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc]; kind::f16 covers bf16 inputs with fp32 accumulation
+__device__ __forceinline__ void tc_mma(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// K-major, 128B-swizzled operand tile: rows are 128 B apart, 8-row groups 1024 B apart (SBO), LBO unused
+__device__ __forceinline__ uint64_t smem_desc(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)1 << 16;                 // leading byte offset (ignored for swizzled K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;       // stride byte offset
+  d |= (uint64_t)1 << 46;                 // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;                 // SWIZZLE_128B
+  return d;
+}
+// instruction descriptor: D=f32, A=B=bf16, both K-major, N=256, M=128
+constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+
+#define TC_LD32(taddr, v)                                                                                           \
+  asm volatile(                                                                                                     \
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "                                                                     \
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28," \
+      "%29,%30,%31}, [%32];"                                                                                        \
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), \
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),      \
+        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),     \
+        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])                   \
+      : "r"(taddr))
+// wait for the TMEM loads; the registers are operands so that no use of them can be scheduled above it
+#define TC_LD_WAIT(v)                                                                                               \
+  asm volatile("tcgen05.wait::ld.sync.aligned;"                                                                     \
+               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]),    \
+                 "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]),           \
+                 "+r"(v[15]), "+r"(v[16]), "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]), "+r"(v[21]),         \
+                 "+r"(v[22]), "+r"(v[23]), "+r"(v[24]), "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]),         \
+                 "+r"(v[29]), "+r"(v[30]), "+r"(v[31])::"memory")
+
+// ---------------------------------------------------------------- prep: fp32 -> bf16 hi/lo + norms
+// flags[0] |= 1 when some value is not exactly a bf16; flags[1] = max ||row||^2 (as ordered uint bits)
+__global__ void prep_kernel(const float *src, size_t sstride, uint32_t n, uint32_t dim, uint32_t dpad, __nv_bfloat16 *hi,
+                            __nv_bfloat16 *lo, float *norms, uint32_t *flags) {
+  const uint32_t row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= n) return;
+  float s = 0.f;
+  bool inexact = false;
+  for (uint32_t d = lane; d < dpad; d += 32) {
+    float x = d < dim ? src[(size_t)row * sstride + d] : 0.f;
+    __nv_bfloat16 h = __float2bfloat16_rn(x);
+    float r = x - __bfloat162float(h);
+    __nv_bfloat16 l = __float2bfloat16_rn(r);
+    hi[(size_t)row * dpad + d] = h;
+    lo[(size_t)row * dpad + d] = l;
+    inexact |= (r != 0.f);
+    s = fmaf(x, x, s);
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  inexact = __any_sync(0xffffffffu, inexact);
+  if (lane == 0) {
+    norms[row] = s;
+    if (inexact) atomicOr(&flags[0], 1u);
+    atomicMax(&flags[1], __float_as_uint(s));  // s >= 0: uint order == float order
+  }
+}
+
+// ---------------------------------------------------------------- sweep kernel
+struct SweepParams {
+  uint32_t nq_rows;   // query rows of this launch
+  uint32_t q_row0;    // row of the query bf16 arrays the launch starts at (also the self id of local row 0)
+  uint32_t n;         // base rows
+  uint32_t nkb;       // K-blocks per pass = dpad / 64
+  uint32_t passes;    // 1 (bf16-exact data) or 3 (hi*hi + hi*lo + lo*hi)
+  uint32_t a_resident;
+  uint32_t ntiles, tiles_per_split;
+  const float *ny;    // base row norms; NULL for inner product
+  int exclude_self;
+  uint32_t Kp, cap, rows_pad;
+  float *cand_d; uint32_t *cand_i;    // [splits, rows_pad, cap]
+  uint32_t *cand_n; float *cand_tau;  // [splits, rows_pad]
+  unsigned long long *prof;           // optional [8]: cycles {wait tmem_full, slow path, compaction, total}, counts {compactions, pushes, slow chunks, chunks}
+};
+
+__device__ __forceinline__ uint32_t ord_key(float f) {
+  uint32_t b = __float_as_uint(f);
+  return b ^ ((uint32_t)((int32_t)b >> 31) | 0x80000000u);
+}
+__device__ __forceinline__ float unord_key(uint32_t u) {
+  uint32_t b = (u & 0x80000000u) ? (u ^ 0x80000000u) : ~u;
+  return __uint_as_float(b);
+}
+
+// Warp-cooperative: keep the Kp smallest keys of cd[0..cnt) (ties: first in buffer order = smallest ids),
+// stable, in place. Returns the Kp-th smallest key = the new filter threshold. hist: 256 u32 of shared memory.
+__device__ float compact_row(float *cd, uint32_t *ci, uint32_t cnt, uint32_t Kp, uint32_t *hist, int lane) {
+  uint32_t prefix = 0, mask = 0, kth = Kp;
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  for (int shift = 24; shift >= 0; shift -= 8) {
+    for (int i = lane; i < 256; i += 32) hist[i] = 0;
+    __syncwarp();
+    for (uint32_t e = lane; e < cnt; e += 32) {
+      uint32_t u = ord_key(__ldcg(cd + e));
+      if ((u & mask) == prefix) atomicAdd(&hist[(u >> shift) & 255u], 1u);
+    }
+    __syncwarp();
+    uint32_t hb[8], s = 0;
+#pragma unroll
+    for (int b = 0; b < 8; b++) { hb[b] = hist[8 * lane + b]; s += hb[b]; }
+    uint32_t incl = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    uint32_t excl = incl - s;
+    bool mine = excl < kth && kth <= incl;
+    uint32_t sel = 0, before = 0;
+    if (mine) {
+      uint32_t run = excl;
+      bool found = false;
+#pragma unroll
+      for (int b = 0; b < 8; b++) {
+        if (!found && run + hb[b] >= kth) { sel = 8 * lane + b; before = run; found = true; }
+        run += hb[b];
+      }
+    }
+    int src = __ffs(__ballot_sync(0xffffffffu, mine)) - 1;
+    sel = __shfl_sync(0xffffffffu, sel, src);
+    before = __shfl_sync(0xffffffffu, before, src);
+    kth -= before;
+    prefix |= sel << shift;
+    mask |= 0xFFu << shift;
+    __syncwarp();
+  }
+  const uint32_t ustar = prefix;  // kth = how many of the entries equal to ustar stay
+  uint32_t out = 0, tie_seen = 0;
+  for (uint32_t e0 = 0; e0 < cnt; e0 += 32) {
+    uint32_t e = e0 + lane;
+    bool valid = e < cnt;
+    float d = valid ? __ldcg(cd + e) : 0.f;
+    uint32_t id = valid ? __ldcg(ci + e) : 0u;
+    uint32_t u = ord_key(d);
+    bool lt = valid && u < ustar, eq = valid && u == ustar;
+    uint32_t beq = __ballot_sync(0xffffffffu, eq);
+    bool keep = lt || (eq && tie_seen + __popc(beq & lt_mask) < kth);
+    uint32_t bk = __ballot_sync(0xffffffffu, keep);
+    if (keep) {
+      uint32_t pos = out + __popc(bk & lt_mask);
+      __stcg(cd + pos, d);
+      __stcg(ci + pos, id);
+    }
+    out += __popc(bk);
+    tie_seen += __popc(beq);
+    __syncwarp();
+  }
+  return unord_key(ustar);
+}
+
+// Same contract as compact_row with the row's entries held in registers (EPL per lane, cap <= 32*EPL): one
+// round trip to L2 instead of one per radix pass.
+template <int EPL>
+__device__ float compact_row_reg(float *cd, uint32_t *ci, uint32_t cnt, uint32_t Kp, uint32_t *hist, int lane) {
+  uint32_t u[EPL], id[EPL];
+#pragma unroll
+  for (int i = 0; i < EPL; i++) {
+    const uint32_t e = i * 32 + lane;
+    u[i] = e < cnt ? ord_key(__ldcg(cd + e)) : 0xFFFFFFFFu;
+    id[i] = e < cnt ? __ldcg(ci + e) : 0u;
+  }
+  uint32_t prefix = 0, mask = 0, kth = Kp;
+  const uint32_t lt_mask = (1u << lane) - 1u;
+#pragma unroll 1
+  for (int shift = 24; shift >= 0; shift -= 8) {
+    for (int i = lane; i < 256; i += 32) hist[i] = 0;
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < EPL; i++)
+      if ((uint32_t)(i * 32 + lane) < cnt && (u[i] & mask) == prefix) atomicAdd(&hist[(u[i] >> shift) & 255u], 1u);
+    __syncwarp();
+    uint32_t hb[8], s = 0;
+#pragma unroll
+    for (int b = 0; b < 8; b++) { hb[b] = hist[8 * lane + b]; s += hb[b]; }
+    uint32_t incl = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    uint32_t excl = incl - s;
+    bool mine = excl < kth && kth <= incl;
+    uint32_t sel = 0, before = 0;
+    if (mine) {
+      uint32_t run = excl;
+      bool found = false;
+#pragma unroll
+      for (int b = 0; b < 8; b++) {
+        if (!found && run + hb[b] >= kth) { sel = 8 * lane + b; before = run; found = true; }
+        run += hb[b];
+      }
+    }
+    int src = __ffs(__ballot_sync(0xffffffffu, mine)) - 1;
+    sel = __shfl_sync(0xffffffffu, sel, src);
+    before = __shfl_sync(0xffffffffu, before, src);
+    kth -= before;
+    prefix |= sel << shift;
+    mask |= 0xFFu << shift;
+    __syncwarp();
+  }
+  const uint32_t ustar = prefix;
+  uint32_t out = 0, tie_seen = 0;
+#pragma unroll
+  for (int i = 0; i < EPL; i++) {
+    if ((uint32_t)(i * 32) < cnt) {  // warp-uniform
+      const bool valid = (uint32_t)(i * 32 + lane) < cnt;
+      const bool lt = valid && u[i] < ustar, eq = valid && u[i] == ustar;
+      const uint32_t beq = __ballot_sync(0xffffffffu, eq);
+      const bool keep = lt || (eq && tie_seen + __popc(beq & lt_mask) < kth);
+      const uint32_t bk = __ballot_sync(0xffffffffu, keep);
+      if (keep) {
+        const uint32_t pos = out + __popc(bk & lt_mask);
+        __stcg(cd + pos, unord_key(u[i]));
+        __stcg(ci + pos, id[i]);
+      }
+      out += __popc(bk);
+      tie_seen += __popc(beq);
+    }
+  }
+  __syncwarp();
+  return unord_key(ustar);
+}
+
+__global__ void __launch_bounds__(NTHREADS, 1)
+sweep_kernel(const __grid_constant__ CUtensorMap mA_hi, const __grid_constant__ CUtensorMap mA_lo,
+             const __grid_constant__ CUtensorMap mB_hi, const __grid_constant__ CUtensorMap mB_lo, const SweepParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t *sA = smem;                                  // A_SLOTS x 16 KB
+  uint8_t *sB = smem + A_SLOTS * A_BYTES;              // NSTAGE x 32 KB
+  uint8_t *misc = sB + NSTAGE * B_BYTES;
+  float *ny_s = (float *)misc;                         // [2][256]
+  uint32_t *hist = (uint32_t *)(misc + 2048);          // [4][256]
+  uint64_t *bars = (uint64_t *)(misc + 2048 + 4096);
+  uint64_t *full = bars, *empty = bars + NSTAGE, *a_full = bars + 2 * NSTAGE;
+  uint64_t *tmem_full = bars + 2 * NSTAGE + 1, *tmem_empty = bars + 2 * NSTAGE + 3;
+  uint32_t *tmem_ptr = (uint32_t *)(bars + 2 * NSTAGE + 5);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t m0 = p.q_row0 + blockIdx.x * BM;
+  const uint32_t tile_begin = blockIdx.y * p.tiles_per_split;
+  const uint32_t tile_end = min(p.ntiles, tile_begin + p.tiles_per_split);
+  const uint32_t T = p.nkb * p.passes;  // K-block steps per tile
+
+  if (warp == 0 && lane == 0) {
+    for (int i = 0; i < NSTAGE; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(a_full, 1);
+    for (int i = 0; i < 2; i++) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&mA_hi) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&mB_hi) : "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmem_ptr)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      if (p.a_resident) {
+        const uint32_t nA = p.nkb * (p.passes == 3 ? 2u : 1u);
+        mbar_expect_tx(a_full, nA * A_BYTES);
+        for (uint32_t b = 0; b < nA; b++)
+          tma_load_2d(sA + b * A_BYTES, b < p.nkb ? &mA_hi : &mA_lo, (int)((b % p.nkb) * BK), (int)m0, a_full);
+      }
+      uint32_t it = 0;
+      for (uint32_t tile = tile_begin; tile < tile_end; tile++) {
+        const int n0 = (int)(tile * BN);
+        for (uint32_t t = 0; t < T; t++, it++) {
+          const uint32_t stage = it % NSTAGE, phase = (it / NSTAGE) & 1u;
+          const uint32_t seg = t / p.nkb, kb = t % p.nkb;
+          mbar_wait(&empty[stage], phase ^ 1u);
+          mbar_expect_tx(&full[stage], B_BYTES + (p.a_resident ? 0 : A_BYTES));
+          tma_load_2d(sB + stage * B_BYTES, seg == 1 ? &mB_lo : &mB_hi, (int)(kb * BK), n0, &full[stage]);
+          if (!p.a_resident)
+            tma_load_2d(sA + stage * A_BYTES, seg == 2 ? &mA_lo : &mA_hi, (int)(kb * BK), (int)m0, &full[stage]);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (p.a_resident) mbar_wait(a_full, 0);
+    uint32_t it = 0, ti = 0;
+    for (uint32_t tile = tile_begin; tile < tile_end; tile++, ti++) {
+      const uint32_t as = ti & 1u, aphase = (ti >> 1) & 1u;
+      mbar_wait(&tmem_empty[as], aphase ^ 1u);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + as * BN;
+      for (uint32_t t = 0; t < T; t++, it++) {
+        const uint32_t stage = it % NSTAGE, phase = (it / NSTAGE) & 1u;
+        const uint32_t seg = t / p.nkb, kb = t % p.nkb;
+        mbar_wait(&full[stage], phase);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t aslot = p.a_resident ? (seg == 2 ? p.nkb : 0u) + kb : stage;
+          const uint32_t a_addr = smem_u32(sA + aslot * A_BYTES), b_addr = smem_u32(sB + stage * B_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / 16; k++)
+            tc_mma(d_tmem, smem_desc(a_addr + k * 32), smem_desc(b_addr + k * 32), IDESC, (t > 0 || k > 0) ? 1u : 0u);
+          tc_commit(&empty[stage]);               // frees the smem stage once these MMAs have read it
+          if (t == T - 1) tc_commit(&tmem_full[as]);  // accumulator complete
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    // ===== epilogue: thread = query row =====
+    const int ew = warp - 2;              // 0..3
+    const int lg = warp & 3;              // TMEM lane group this warp may read
+    const int et = ew * 32 + lane;        // 0..127
+    const uint32_t row_local = blockIdx.x * BM + lg * 32 + lane;
+    const bool row_valid = row_local < p.nq_rows;
+    const uint32_t self = p.exclude_self ? p.q_row0 + row_local : INVALID_ID;
+    const size_t sr = (size_t)blockIdx.y * p.rows_pad + row_local;
+    float *cd = p.cand_d + sr * p.cap;
+    uint32_t *ci = p.cand_i + sr * p.cap;
+    uint32_t *myhist = hist + ew * 256;
+    uint32_t cnt = 0;
+    float tau = row_valid ? INFINITY : -INFINITY;
+    const uint32_t full_at = p.cap - 32;
+
+    long long pf_wait = 0, pf_slow = 0, pf_comp = 0, pf_t0 = clock64();
+    uint32_t pf_ncomp = 0, pf_push = 0, pf_nslow = 0, pf_nchunk = 0;
+    auto maybe_compact = [&](uint32_t limit) {
+      uint32_t need = __ballot_sync(0xffffffffu, cnt > limit);
+      if (!need) return;
+      long long c0 = clock64();
+      while (need) {
+        pf_ncomp++;
+        int l = __ffs(need) - 1;
+        need &= need - 1;
+        float *rcd = (float *)__shfl_sync(0xffffffffu, (unsigned long long)cd, l);
+        uint32_t *rci = (uint32_t *)__shfl_sync(0xffffffffu, (unsigned long long)ci, l);
+        uint32_t rcnt = __shfl_sync(0xffffffffu, cnt, l);
+        float t;
+        if (p.cap <= 256) t = compact_row_reg<8>(rcd, rci, rcnt, p.Kp, myhist, lane);
+        else if (p.cap <= 640) t = compact_row_reg<20>(rcd, rci, rcnt, p.Kp, myhist, lane);
+        else t = compact_row(rcd, rci, rcnt, p.Kp, myhist, lane);
+        if (lane == l) { cnt = p.Kp; tau = t; }
+      }
+      pf_comp += clock64() - c0;
+    };
+
+    uint32_t ti = 0;
+    for (uint32_t tile = tile_begin; tile < tile_end; tile++, ti++) {
+      const uint32_t as = ti & 1u, aphase = (ti >> 1) & 1u;
+      const uint32_t n0 = tile * BN;
+      {
+        float *nys = ny_s + as * BN;
+        uint32_t c0 = n0 + et, c1 = n0 + et + 128;
+        nys[et] = c0 < p.n ? (p.ny ? __ldg(p.ny + c0) : 0.f) : INFINITY;
+        nys[et + 128] = c1 < p.n ? (p.ny ? __ldg(p.ny + c1) : 0.f) : INFINITY;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      { long long c0 = clock64(); mbar_wait(&tmem_full[as], aphase); pf_wait += clock64() - c0; }
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + as * BN;
+      const float *nys = ny_s + as * BN;
+
+      auto process = [&](const uint32_t(&v)[32], int c) {
+        const float4 *ny4 = (const float4 *)(nys + c * 32);
+        const uint32_t colb = n0 + c * 32;
+        pf_nchunk++;
+        long long c0 = clock64();
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+          const float4 y = ny4[j];
+          const float d0 = fmaf(-2.f, __uint_as_float(v[4 * j + 0]), y.x), d1 = fmaf(-2.f, __uint_as_float(v[4 * j + 1]), y.y);
+          const float d2 = fmaf(-2.f, __uint_as_float(v[4 * j + 2]), y.z), d3 = fmaf(-2.f, __uint_as_float(v[4 * j + 3]), y.w);
+          // warp-uniform test per column pair; the pushes themselves are rare (~0.3 % of the elements)
+          if (__any_sync(0xffffffffu, (d0 < tau) | (d1 < tau))) {
+            pf_nslow++;
+            if (d0 < tau && colb + 4 * j + 0 != self) { __stcg(cd + cnt, d0); __stcg(ci + cnt, colb + 4 * j + 0); cnt++; pf_push++; }
+            if (d1 < tau && colb + 4 * j + 1 != self) { __stcg(cd + cnt, d1); __stcg(ci + cnt, colb + 4 * j + 1); cnt++; pf_push++; }
+          }
+          if (__any_sync(0xffffffffu, (d2 < tau) | (d3 < tau))) {
+            pf_nslow++;
+            if (d2 < tau && colb + 4 * j + 2 != self) { __stcg(cd + cnt, d2); __stcg(ci + cnt, colb + 4 * j + 2); cnt++; pf_push++; }
+            if (d3 < tau && colb + 4 * j + 3 != self) { __stcg(cd + cnt, d3); __stcg(ci + cnt, colb + 4 * j + 3); cnt++; pf_push++; }
+          }
+        }
+        pf_slow += clock64() - c0;
+        maybe_compact(full_at);
+      };
+
+      uint32_t va[32], vb[32];
+      TC_LD32(taddr, va);
+      TC_LD_WAIT(va);
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; c += 2) {
+        TC_LD32(taddr + (c + 1) * 32, vb);
+        process(va, c);
+        TC_LD_WAIT(vb);
+        if (c + 2 < BN / 32) TC_LD32(taddr + (c + 2) * 32, va);
+        process(vb, c + 1);
+        if (c + 2 < BN / 32) TC_LD_WAIT(va);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[as]);
+    }
+    // leave at most Kp entries per row
+    maybe_compact(p.Kp);
+    if (row_valid) { p.cand_n[sr] = cnt; p.cand_tau[sr] = tau; }
+    if (p.prof) {
+      for (int o = 16; o; o >>= 1) pf_push += __shfl_xor_sync(0xffffffffu, pf_push, o);
+      if (lane == 0) {
+        atomicAdd(p.prof + 0, (unsigned long long)pf_wait); atomicAdd(p.prof + 1, (unsigned long long)pf_slow);
+        atomicAdd(p.prof + 2, (unsigned long long)pf_comp); atomicAdd(p.prof + 3, (unsigned long long)(clock64() - pf_t0));
+        atomicAdd(p.prof + 4, (unsigned long long)pf_ncomp); atomicAdd(p.prof + 5, (unsigned long long)pf_push);
+        atomicAdd(p.prof + 6, (unsigned long long)pf_nslow); atomicAdd(p.prof + 7, (unsigned long long)pf_nchunk);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
+  }
+}
+
+// ---------------------------------------------------------------- finalize kernel
+struct FinParams {
+  const float *base; size_t bstride; uint32_t dim, stride4;  // fp32 index rows (stride4 = dim rounded up to 4)
+  const float *q; size_t qstride;                            // fp32 query rows of this launch
+  const float *nx;                                           // query norms of this launch
+  uint32_t nq_rows, q_row0, K, Kp, cap, rows_pad, splits, P;
+  const float *cand_d; const uint32_t *cand_i; const uint32_t *cand_n; const float *cand_tau;
+  float c1, c2, ny_max;  // eps = c1*sqrt(nx*ny_max) + c2*(nx+ny_max)
+  int ip;
+  uint32_t *out_i; float *out_d;  // [nq_rows, K] of this launch
+  uint32_t *fail_cnt, *fail_rows; // rows whose shortlist could not be proven complete
+  unsigned long long *n_cand;     // total shortlisted rows re-ranked (statistics)
+};
+
+constexpr int FIN_THREADS = 128;
+constexpr int RS4 = 33;  // float4 per staged candidate row (32 + 1 pad: conflict-free LDS.128)
+
+__device__ __forceinline__ bool lex_less(float d0, uint32_t i0, float d1, uint32_t i1) {
+  return d0 < d1 || (d0 == d1 && i0 < i1);
+}
+
+__global__ void __launch_bounds__(FIN_THREADS) finalize_kernel(const FinParams p) {
+  extern __shared__ __align__(16) uint8_t fsm[];
+  float4 *tile = (float4 *)fsm;                                   // [4 warps][32][RS4]
+  float4 *qs4 = tile + 4 * 32 * RS4;                              // [stride4/4]
+  float *sd = (float *)(qs4 + p.stride4 / 4);                     // [P]
+  uint32_t *si = (uint32_t *)(sd + p.P);                          // [P]
+  __shared__ uint32_t off_s[65];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t row = blockIdx.x;
+  if (row >= p.nq_rows) return;
+
+  if (tid == 0) {
+    uint32_t o = 0;
+    for (uint32_t s = 0; s < p.splits; s++) { off_s[s] = o; o += p.cand_n[(size_t)s * p.rows_pad + row]; }
+    off_s[p.splits] = o;
+  }
+  for (uint32_t d4 = tid; d4 < p.stride4 / 4; d4 += FIN_THREADS) {
+    float v[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) { uint32_t d = d4 * 4 + j; v[j] = d < p.dim ? __ldg(p.q + (size_t)row * p.qstride + d) : 0.f; }
+    qs4[d4] = make_float4(v[0], v[1], v[2], v[3]);
+  }
+  __syncthreads();
+  const uint32_t C = off_s[p.splits];
+  for (uint32_t e = tid; e < p.P; e += FIN_THREADS) { sd[e] = INFINITY; si[e] = INVALID_ID; }
+  __syncthreads();
+  for (uint32_t s = 0; s < p.splits; s++) {
+    const uint32_t o = off_s[s], c = off_s[s + 1] - o;
+    const uint32_t *src = p.cand_i + ((size_t)s * p.rows_pad + row) * p.cap;
+    for (uint32_t e = tid; e < c; e += FIN_THREADS) si[o + e] = __ldcg(src + e);
+  }
+  __syncthreads();
+
+  // exact fp32 distances in the order of bf_knn.cu: sequential over the dimension, one fmaf per element
+  float4 *mytile = tile + warp * 32 * RS4;
+  for (uint32_t e0 = warp * 32; e0 < C; e0 += 4 * 32) {
+    const uint32_t nb = min(32u, C - e0);
+    const uint32_t myid = (uint32_t)lane < nb ? si[e0 + lane] : 0u;
+    float acc = 0.f;
+    for (uint32_t d0 = 0; d0 < p.stride4; d0 += 128) {
+      const uint32_t n4 = min(32u, (p.stride4 - d0) / 4);
+      // lane r holds candidate id r; 8 independent 512-byte row loads in flight per step
+      for (uint32_t r0 = 0; r0 < nb; r0 += 8) {
+        float4 v[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+          const uint32_t id = __shfl_sync(0xffffffffu, myid, (r0 + u) & 31);
+          v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (r0 + u < nb && (uint32_t)lane < n4)
+            v[u] = __ldg((const float4 *)(p.base + (size_t)id * p.bstride + d0) + lane);
+        }
+#pragma unroll
+        for (int u = 0; u < 8; u++)
+          if (r0 + u < nb && (uint32_t)lane < n4) mytile[(r0 + u) * RS4 + lane] = v[u];
+      }
+      __syncwarp();
+      if ((uint32_t)lane < nb) {
+        const float4 *brow = mytile + lane * RS4;
+        const float4 *qrow = qs4 + d0 / 4;
+        for (uint32_t c4 = 0; c4 < n4; c4++) {
+          const float4 b = brow[c4], q = qrow[c4];
+          if (p.ip) {
+            acc = fmaf(q.x, b.x, acc); acc = fmaf(q.y, b.y, acc); acc = fmaf(q.z, b.z, acc); acc = fmaf(q.w, b.w, acc);
+          } else {
+            float t;
+            t = q.x - b.x; acc = fmaf(t, t, acc);
+            t = q.y - b.y; acc = fmaf(t, t, acc);
+            t = q.z - b.z; acc = fmaf(t, t, acc);
+            t = q.w - b.w; acc = fmaf(t, t, acc);
+          }
+        }
+      }
+      __syncwarp();
+    }
+    if ((uint32_t)lane < nb) sd[e0 + lane] = p.ip ? 1.0f - acc : acc;
+  }
+  __syncthreads();
+
+  // bitonic sort of P (distance,id) pairs, ascending
+  for (uint32_t sz = 2; sz <= p.P; sz <<= 1) {
+    for (uint32_t st = sz >> 1; st >= 1; st >>= 1) {
+      for (uint32_t t = tid; t < p.P / 2; t += FIN_THREADS) {
+        uint32_t i = ((t / st) * 2 * st) + (t % st), j = i + st;
+        bool up = (i & sz) == 0;
+        float di = sd[i], dj = sd[j];
+        uint32_t ii = si[i], ij = si[j];
+        bool sw = up ? lex_less(dj, ij, di, ii) : lex_less(di, ii, dj, ij);
+        if (sw) { sd[i] = dj; sd[j] = di; si[i] = ij; si[j] = ii; }
+      }
+      __syncthreads();
+    }
+  }
+  for (uint32_t j = tid; j < p.K; j += FIN_THREADS) {
+    p.out_i[(size_t)row * p.K + j] = j < C ? si[j] : INVALID_ID;
+    if (p.out_d) p.out_d[(size_t)row * p.K + j] = j < C ? sd[j] : INFINITY;
+  }
+  if (tid == 0) {
+    const float dK = C >= p.K ? sd[p.K - 1] : INFINITY;
+    const float nx = p.nx[row];
+    const float eps = p.c1 * sqrtf(nx * p.ny_max) + p.c2 * (nx + p.ny_max);
+    bool ok = true;
+    for (uint32_t s = 0; s < p.splits; s++) {
+      const float tau = p.cand_tau[(size_t)s * p.rows_pad + row];
+      if (tau == INFINITY) continue;  // nothing was ever dropped in this split
+      const float bound = p.ip ? 1.0f + 0.5f * (tau - eps) : (tau - eps) + nx;
+      ok = ok && (bound > dK);
+    }
+    if (!ok) p.fail_rows[atomicAdd(p.fail_cnt, 1u)] = p.q_row0 + row;
+    atomicAdd(p.n_cand, (unsigned long long)C);
+  }
+}
+
+// results of the fallback (compact rows) -> their rows of the output
+__global__ void scatter_rows_kernel(const uint32_t *rows, uint32_t nf, uint32_t K, const uint32_t *src_i, const float *src_d,
+                                    uint32_t *out_i, float *out_d) {
+  size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (t >= (size_t)nf * K) return;
+  uint32_t r = rows[t / K];
+  out_i[(size_t)r * K + t % K] = src_i[t];
+  if (out_d) out_d[(size_t)r * K + t % K] = src_d[t];
+}
+__global__ void gather_rows_kernel(const uint32_t *rows, uint32_t nf, const float *src, size_t sstride, uint32_t dim, float *dst) {
+  size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (t >= (size_t)nf * dim) return;
+  dst[t] = src[(size_t)rows[t / dim] * sstride + t % dim];
+}
+
+}  // namespace tc
+
+// ---------------------------------------------------------------- host side
+namespace {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) == cudaSuccess &&
+        qr == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+// bf16 [rows, dpad] row-major, box = 64 elements (128 B) x box_rows, 128B swizzle, zero fill outside
+bool make_map(CUtensorMap *m, void *ptr, uint64_t rows, uint64_t dpad, uint32_t box_rows) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return false;
+  cuuint64_t dims[2] = {dpad, rows};
+  cuuint64_t strides[1] = {dpad * 2};
+  cuuint32_t box[2] = {(cuuint32_t)tc::BK, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  return enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+struct Bf16Set {  // bf16 hi/lo + norms of a row set
+  void *hi = nullptr, *lo = nullptr;
+  float *norms = nullptr;
+  bool inexact = false;
+  float nmax = 0.f;
+};
+
+int prep_rows(b200ann_handle *h, const float *src, size_t sstride, size_t n, size_t dim, size_t dpad, Bf16Set *o) {
+  CU_CHECK(h, cudaMalloc(&o->hi, n * dpad * 2));
+  CU_CHECK(h, cudaMalloc(&o->lo, n * dpad * 2));
+  CU_CHECK(h, cudaMalloc((void **)&o->norms, n * sizeof(float)));
+  DevBuf<uint32_t> flags;
+  CU_CHECK(h, flags.alloc(2, h->stream));
+  CU_CHECK(h, cudaMemsetAsync(flags.p, 0, 8, h->stream));
+  tc::prep_kernel<<<(unsigned)((n + 7) / 8), 256, 0, h->stream>>>(src, sstride, (uint32_t)n, (uint32_t)dim, (uint32_t)dpad,
+                                                                   (__nv_bfloat16 *)o->hi, (__nv_bfloat16 *)o->lo, o->norms, flags.p);
+  h->launches++;
+  CU_CHECK(h, cudaGetLastError());
+  uint32_t f[2];
+  CU_CHECK(h, cudaMemcpyAsync(f, flags.p, 8, cudaMemcpyDeviceToHost, h->stream));
+  CU_CHECK(h, cudaStreamSynchronize(h->stream));
+  o->inexact = f[0] != 0;
+  memcpy(&o->nmax, &f[1], 4);
+  return 0;
+}
+void free_set(Bf16Set *s) {
+  if (s->hi) cudaFree(s->hi);
+  if (s->lo) cudaFree(s->lo);
+  if (s->norms) cudaFree(s->norms);
+  s->hi = s->lo = nullptr; s->norms = nullptr;
+}
+
+uint32_t next_pow2(uint32_t x) { uint32_t p = 1; while (p < x) p <<= 1; return p; }
+
+uint32_t shortlist_size(const b200ann_handle *h, size_t k) {
+  size_t slack = h->knn_slack >= 0 ? (size_t)h->knn_slack : (k / 4 > 32 ? k / 4 : 32);
+  return (uint32_t)(k + slack);
+}
+
+}  // namespace
+
+void knn_tc_free(b200ann_index *ix) {
+  if (ix->tc_hi) cudaFree(ix->tc_hi);
+  if (ix->tc_lo) cudaFree(ix->tc_lo);
+  if (ix->tc_norms) cudaFree(ix->tc_norms);
+  ix->tc_hi = ix->tc_lo = nullptr; ix->tc_norms = nullptr;
+}
+
+bool knn_tc_supported(const b200ann_index *ix, size_t nq, size_t k) {
+  (void)nq;
+  if (k == 0 || k > 1024) return false;
+  if (ix->dim > 4096) return false;
+  return get_encode() != nullptr;
+}
+
+int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t nq, size_t qstride, size_t k,
+                  bool exclude_self, uint32_t *ids, float *dists) {
+  if (nq == 0) return 0;
+  if (!knn_tc_supported(ix, nq, k)) return set_err(h, B200ANN_ERR_ARG, "knn (tensor path): unsupported k/dim or no cuTensorMapEncodeTiled");
+  const size_t n = ix->n, dim = ix->dim;
+  const size_t dpad = (dim + tc::BK - 1) / tc::BK * tc::BK;
+  const bool ip = ix->metric == B200ANN_IP;
+
+  // 1. bf16 copies + norms of the base (cached in the index) and of the queries
+  if (!ix->tc_hi) {
+    Bf16Set b;
+    int rc = prep_rows(h, ix->vec, ix->stride, n, dim, dpad, &b);
+    if (rc) { free_set(&b); return rc; }
+    ix->tc_hi = b.hi; ix->tc_lo = b.lo; ix->tc_norms = b.norms; ix->tc_dpad = dpad;
+    ix->tc_inexact = b.inexact; ix->tc_ny_max = b.nmax;
+  }
+  Bf16Set qs;
+  const bool self_queries = (q == ix->vec && nq == n);
+  struct QGuard { Bf16Set *s; bool own; ~QGuard() { if (own) free_set(s); } } qguard{&qs, !self_queries};
+  if (self_queries) {
+    qs.hi = ix->tc_hi; qs.lo = ix->tc_lo; qs.norms = ix->tc_norms; qs.inexact = ix->tc_inexact; qs.nmax = ix->tc_ny_max;
+  } else {
+    int rc = prep_rows(h, q, qstride, nq, dim, dpad, &qs);
+    if (rc) return rc;
+  }
+  const uint32_t passes = (ix->tc_inexact || qs.inexact) ? 3u : 1u;
+  const uint32_t nkb = (uint32_t)(dpad / tc::BK);
+  const uint32_t a_res = nkb * (passes == 3 ? 2u : 1u) <= (uint32_t)tc::A_SLOTS ? 1u : 0u;
+
+  CUtensorMap mA_hi, mA_lo, mB_hi, mB_lo;
+  if (!make_map(&mA_hi, qs.hi, nq, dpad, tc::BM) || !make_map(&mA_lo, qs.lo, nq, dpad, tc::BM) ||
+      !make_map(&mB_hi, ix->tc_hi, n, dpad, tc::BN) || !make_map(&mB_lo, ix->tc_lo, n, dpad, tc::BN))
+    return set_err(h, B200ANN_ERR_CUDA, "knn (tensor path): cuTensorMapEncodeTiled failed");
+
+  // 2. geometry
+  const uint32_t Kp = shortlist_size(h, k);
+  const uint32_t cap = (2 * Kp + 64 + 31) / 32 * 32;
+  const uint32_t ntiles = (uint32_t)((n + tc::BN - 1) / tc::BN);
+  const size_t chunk_rows = (size_t)h->sm_count * 4 * tc::BM;
+  const size_t rows0 = nq < chunk_rows ? nq : chunk_rows;
+  const uint32_t mtiles0 = (uint32_t)((rows0 + tc::BM - 1) / tc::BM);
+  uint32_t splits = 1;
+  {
+    double best = 1e30;
+    uint32_t smax = ntiles / 4 < 32 ? ntiles / 4 : 32;
+    if (smax < 1) smax = 1;
+    while (smax > 1 && next_pow2(smax * Kp) > 4096) smax--;
+    for (uint32_t s = 1; s <= smax; s++) {
+      uint32_t tps = (ntiles + s - 1) / s;
+      double waves = ceil((double)mtiles0 * s / h->sm_count);
+      double t = waves * (tps + 2.0);  // +2: per-CTA start-up
+      if (t < best * 0.98) { best = t; splits = s; }
+    }
+  }
+  const uint32_t tiles_per_split = (ntiles + splits - 1) / splits;
+  const uint32_t P = next_pow2(splits * Kp);
+  const uint32_t rows_pad = mtiles0 * tc::BM;
+
+  DevBuf<float> cand_d, cand_tau; DevBuf<uint32_t> cand_i, cand_n, fail; DevBuf<unsigned long long> ncand;
+  const size_t slots = (size_t)splits * rows_pad;
+  CU_CHECK(h, cand_d.alloc(slots * cap, h->stream));
+  CU_CHECK(h, cand_i.alloc(slots * cap, h->stream));
+  CU_CHECK(h, cand_n.alloc(slots, h->stream));
+  CU_CHECK(h, cand_tau.alloc(slots, h->stream));
+  CU_CHECK(h, fail.alloc(1 + nq, h->stream));
+  CU_CHECK(h, ncand.alloc(1, h->stream));
+  CU_CHECK(h, cudaMemsetAsync(fail.p, 0, 4, h->stream));
+  CU_CHECK(h, cudaMemsetAsync(ncand.p, 0, 8, h->stream));
+
+  const size_t stride4 = (dim + 3) / 4 * 4;
+  const size_t fin_smem = (size_t)4 * 32 * tc::RS4 * 16 + stride4 * 4 + (size_t)P * 8;
+  CU_CHECK(h, cudaFuncSetAttribute(tc::sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
+  CU_CHECK(h, cudaFuncSetAttribute(tc::finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fin_smem));
+
+  // error bound of the tensor-core ranking key (see the file header): inputs, accumulation, fp32 roundings
+  const double keff = (double)dpad * passes;
+  const float c_in = passes == 3 ? ldexpf(1.f, -16) : 0.f;
+  const float c1 = 2.f * (c_in + (float)keff * ldexpf(1.f, -22));
+  const float c2 = (float)(dim + 8) * ldexpf(1.f, -23);
+  const float ny_max = ip ? ix->tc_ny_max : ix->tc_ny_max;
+
+  DevBuf<unsigned long long> prof;
+  const bool want_prof = getenv("B200ANN_KNN_PROF") != nullptr;
+  if (want_prof) { CU_CHECK(h, prof.alloc(8, h->stream)); CU_CHECK(h, cudaMemsetAsync(prof.p, 0, 64, h->stream)); }
+  for (size_t r0 = 0; r0 < nq; r0 += chunk_rows) {
+    const uint32_t rows = (uint32_t)((nq - r0) < chunk_rows ? (nq - r0) : chunk_rows);
+    const uint32_t mtiles = (rows + tc::BM - 1) / tc::BM;
+    tc::SweepParams sp = {};
+    sp.nq_rows = rows; sp.q_row0 = (uint32_t)r0; sp.n = (uint32_t)n; sp.nkb = nkb; sp.passes = passes; sp.a_resident = a_res;
+    sp.ntiles = ntiles; sp.tiles_per_split = tiles_per_split; sp.ny = ip ? nullptr : ix->tc_norms;
+    sp.exclude_self = exclude_self; sp.Kp = Kp; sp.cap = cap; sp.rows_pad = rows_pad;
+    sp.cand_d = cand_d.p; sp.cand_i = cand_i.p; sp.cand_n = cand_n.p; sp.cand_tau = cand_tau.p;
+    sp.prof = want_prof ? prof.p : nullptr;
+    tc::sweep_kernel<<<dim3(mtiles, splits), tc::NTHREADS, tc::SMEM_BYTES, h->stream>>>(mA_hi, mA_lo, mB_hi, mB_lo, sp);
+    h->launches++;
+    CU_CHECK(h, cudaGetLastError());
+    tc::FinParams fp = {};
+    fp.base = ix->vec; fp.bstride = ix->stride; fp.dim = (uint32_t)dim; fp.stride4 = (uint32_t)stride4;
+    fp.q = q + r0 * qstride; fp.qstride = qstride; fp.nx = qs.norms + r0;
+    fp.nq_rows = rows; fp.q_row0 = (uint32_t)r0; fp.K = (uint32_t)k; fp.Kp = Kp; fp.cap = cap; fp.rows_pad = rows_pad;
+    fp.splits = splits; fp.P = P;
+    fp.cand_d = cand_d.p; fp.cand_i = cand_i.p; fp.cand_n = cand_n.p; fp.cand_tau = cand_tau.p;
+    fp.c1 = c1; fp.c2 = c2; fp.ny_max = ny_max; fp.ip = ip;
+    fp.out_i = ids + r0 * k; fp.out_d = dists ? dists + r0 * k : nullptr;
+    fp.fail_cnt = fail.p; fp.fail_rows = fail.p + 1; fp.n_cand = ncand.p;
+    tc::finalize_kernel<<<rows, tc::FIN_THREADS, fin_smem, h->stream>>>(fp);
+    h->launches++;
+    CU_CHECK(h, cudaGetLastError());
+  }
+
+  // 3. rows whose shortlist could not be proven complete: recompute with the fp32 SIMT kernel
+  uint32_t nf = 0;
+  unsigned long long nc = 0;
+  CU_CHECK(h, cudaMemcpyAsync(&nf, fail.p, 4, cudaMemcpyDeviceToHost, h->stream));
+  CU_CHECK(h, cudaMemcpyAsync(&nc, ncand.p, 8, cudaMemcpyDeviceToHost, h->stream));
+  CU_CHECK(h, cudaStreamSynchronize(h->stream));
+  if (want_prof) {
+    unsigned long long pv[8];
+    CU_CHECK(h, cudaMemcpy(pv, prof.p, 64, cudaMemcpyDeviceToHost));
+    fprintf(stderr, "[knn_tc prof] per-warp-sum cycles: wait %llu slow %llu compact %llu total %llu | compactions %llu pushes %llu slow chunks %llu of %llu\n",
+            pv[0], pv[1], pv[2], pv[3], pv[4], pv[5], pv[6], pv[7]);
+  }
+  h->knn_stats[0] = nq; h->knn_stats[1] = nf; h->knn_stats[2] = nc; h->knn_stats[3] = passes;
+  h->knn_stats[4] = splits; h->knn_stats[5] = Kp; h->knn_stats[6] = (uint64_t)ntiles * ((nq + tc::BM - 1) / tc::BM); h->knn_stats[7] = a_res;
+  if (nf) {
+    DevBuf<float> fq, fd; DevBuf<uint32_t> fi;
+    CU_CHECK(h, fq.alloc((size_t)nf * dim, h->stream));
+    CU_CHECK(h, fi.alloc((size_t)nf * k, h->stream));
+    CU_CHECK(h, fd.alloc((size_t)nf * k, h->stream));
+    size_t tot = (size_t)nf * dim;
+    tc::gather_rows_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, h->stream>>>(fail.p + 1, nf, q, qstride, (uint32_t)dim, fq.p);
+    h->launches++;
+    int rc = launch_bf_knn(h, ix, fq.p, nf, dim, k, exclude_self, fi.p, fd.p, fail.p + 1);
+    if (rc) return rc;
+    tot = (size_t)nf * k;
+    tc::scatter_rows_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, h->stream>>>(fail.p + 1, nf, (uint32_t)k, fi.p, fd.p, ids, dists);
+    h->launches++;
+    CU_CHECK(h, cudaGetLastError());
+    CU_CHECK(h, cudaStreamSynchronize(h->stream));
+  }
+  return 0;
+}

@@ -85,6 +85,17 @@ int b200ann_bf_knn(b200ann_handle_t h, b200ann_index_t ix, const float *q /*[h|d
  * The exact counterpart of IndexGraph::Build's output (index_graph.cpp:275-292). */
 int b200ann_knn_graph(b200ann_handle_t h, b200ann_index_t ix, size_t K, uint32_t *knn /*[h|d]*/);
 
+/* Which kernel b200ann_bf_knn / b200ann_knn_graph run on: 0 = auto (tensor cores when n >= 4096 and
+ * nq*n >= 2^24, else fp32 SIMT), 1 = fp32 SIMT tiles (csrc/bf_knn.cu), 2 = tcgen05 tensor cores with fp32
+ * re-ranking (csrc/knn_tc.cu). Both give the same bits. slack = extra shortlist entries per row kept by the
+ * tensor path beyond k (< 0 = default max(32, k/4)); rows whose shortlist cannot be PROVEN to hold the exact
+ * top k are recomputed by the SIMT kernel, so slack only moves work between the two. */
+int b200ann_set_knn_mode(b200ann_handle_t h, int mode, int slack);
+/* statistics of the last bf_knn / knn_graph call on this handle, 8 x u64: {query rows, rows recomputed by the
+ * SIMT fallback, shortlisted candidates re-ranked in fp32, tensor passes (1 = bf16-exact data, 3 = bf16x3),
+ * base-range splits, shortlist size, 128x256 tiles, A-resident}; all 0 when the SIMT kernel ran. */
+int b200ann_knn_last_stats(b200ann_handle_t h, uint64_t *out8);
+
 /* ---- graph search ------------------------------------------------------------------------- */
 /* replaces efanna2e::IndexNSG::Search / SearchWithOptGraph (index_nsg.cpp:506-568, :570-657) for a
  * batch of queries. K results per query from a sorted pool of L (= "L_search"), seeds = first L

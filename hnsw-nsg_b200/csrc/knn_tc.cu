@@ -30,11 +30,10 @@ namespace tc {
 
 constexpr int BM = 128, BN = 256, BK = 64;          // tile rows (queries), tile columns (base rows), bf16 per K-block
 constexpr int A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2;  // 16 KB, 32 KB
-constexpr int NSTAGE = 4;                           // B ring (and A ring when A streams)
-constexpr int A_SLOTS = 4;                          // resident A K-blocks (64 KB)
-constexpr int NTHREADS = 192;                       // warp0 TMA, warp1 MMA, warps 2-5 epilogue
-constexpr int SMEM_MISC = 8192;
-constexpr int SMEM_BYTES = 1024 + A_SLOTS * A_BYTES + NSTAGE * B_BYTES + SMEM_MISC;
+constexpr int A_SLOTS = 4;                          // at most this many resident A K-blocks (64 KB)
+constexpr int NTHREADS = 320;                       // warp0 TMA, warp1 MMA, warps 2-9 epilogue
+constexpr int SMEM_MISC = 49152;                    // spill 36 KB, norms 2 KB, histograms 8 KB, row state 1 KB, barriers
+constexpr int SMEM_MAX = 232448;                    // 227 KB opt-in limit of sm_100
 
 // ---------------------------------------------------------------- PTX wrappers
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -147,13 +146,14 @@ struct SweepParams {
   uint32_t nkb;       // K-blocks per pass = dpad / 64
   uint32_t passes;    // 1 (bf16-exact data) or 3 (hi*hi + hi*lo + lo*hi)
   uint32_t a_resident;
+  uint32_t a_slots, nstage;  // shared-memory carve: A K-block slots, B (and streamed A) ring stages
   uint32_t ntiles, tiles_per_split;
   const float *ny;    // base row norms; NULL for inner product
   int exclude_self;
   uint32_t Kp, cap, rows_pad;
   float *cand_d; uint32_t *cand_i;    // [splits, rows_pad, cap]
   uint32_t *cand_n; float *cand_tau;  // [splits, rows_pad]
-  unsigned long long *prof;           // optional [8]: cycles {wait tmem_full, slow path, compaction, total}, counts {compactions, pushes, slow chunks, chunks}
+  unsigned long long *prof;           // optional [8]: per-epilogue-warp cycle sums {wait tmem_full, process, compaction, total}, compactions
 };
 
 __device__ __forceinline__ uint32_t ord_key(float f) {
@@ -304,20 +304,29 @@ __device__ float compact_row_reg(float *cd, uint32_t *ci, uint32_t cnt, uint32_t
   return unord_key(ustar);
 }
 
+// Epilogue geometry: 8 warps. Warp (quarter q = warp & 3, half hf) reads TMEM lanes [32q, 32q+32) (the rows
+// it may address) and the columns [128 hf, 128 hf + 128) of every tile; the two warps of a quarter share the
+// per-row state (count, threshold) in shared memory and synchronise on a 64-thread named barrier per tile.
 __global__ void __launch_bounds__(NTHREADS, 1)
 sweep_kernel(const __grid_constant__ CUtensorMap mA_hi, const __grid_constant__ CUtensorMap mA_lo,
              const __grid_constant__ CUtensorMap mB_hi, const __grid_constant__ CUtensorMap mB_lo, const SweepParams p) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  uint8_t *sA = smem;                                  // A_SLOTS x 16 KB
-  uint8_t *sB = smem + A_SLOTS * A_BYTES;              // NSTAGE x 32 KB
-  uint8_t *misc = sB + NSTAGE * B_BYTES;
-  float *ny_s = (float *)misc;                         // [2][256]
-  uint32_t *hist = (uint32_t *)(misc + 2048);          // [4][256]
-  uint64_t *bars = (uint64_t *)(misc + 2048 + 4096);
-  uint64_t *full = bars, *empty = bars + NSTAGE, *a_full = bars + 2 * NSTAGE;
-  uint64_t *tmem_full = bars + 2 * NSTAGE + 1, *tmem_empty = bars + 2 * NSTAGE + 3;
-  uint32_t *tmem_ptr = (uint32_t *)(bars + 2 * NSTAGE + 5);
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // 1024-byte alignment for the 128B swizzle; plain pointer arithmetic keeps the shared address space
+  // known to the compiler (LDS/STS/ATOMS instead of generic accesses)
+  uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  const uint32_t NS = p.nstage;
+  uint8_t *sA = smem;                                  // a_slots x 16 KB
+  uint8_t *sB = smem + p.a_slots * A_BYTES;            // NS x 32 KB
+  uint8_t *misc = sB + NS * B_BYTES;
+  float *spill = (float *)misc;                        // [8 warps][32 lanes][36]
+  float *ny_s = (float *)(misc + 36864);               // [2][256]
+  uint32_t *hist = (uint32_t *)(misc + 36864 + 2048);  // [8][256]
+  uint32_t *cnt_s = (uint32_t *)(misc + 36864 + 2048 + 8192);  // [128]
+  float *tau_s = (float *)(cnt_s + 128);                       // [128]
+  uint64_t *bars = (uint64_t *)(tau_s + 128);
+  uint64_t *full = bars, *empty = bars + NS, *a_full = bars + 2 * NS;
+  uint64_t *tmem_full = bars + 2 * NS + 1, *tmem_empty = bars + 2 * NS + 3;
+  uint32_t *tmem_ptr = (uint32_t *)(bars + 2 * NS + 5);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t m0 = p.q_row0 + blockIdx.x * BM;
@@ -326,9 +335,9 @@ sweep_kernel(const __grid_constant__ CUtensorMap mA_hi, const __grid_constant__ 
   const uint32_t T = p.nkb * p.passes;  // K-block steps per tile
 
   if (warp == 0 && lane == 0) {
-    for (int i = 0; i < NSTAGE; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    for (uint32_t i = 0; i < NS; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
     mbar_init(a_full, 1);
-    for (int i = 0; i < 2; i++) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4); }
+    for (int i = 0; i < 2; i++) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 8); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mA_hi) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mB_hi) : "memory");
@@ -351,31 +360,30 @@ sweep_kernel(const __grid_constant__ CUtensorMap mA_hi, const __grid_constant__ 
         for (uint32_t b = 0; b < nA; b++)
           tma_load_2d(sA + b * A_BYTES, b < p.nkb ? &mA_hi : &mA_lo, (int)((b % p.nkb) * BK), (int)m0, a_full);
       }
-      uint32_t it = 0;
+      uint32_t stage = 0, phase = 0;
       for (uint32_t tile = tile_begin; tile < tile_end; tile++) {
         const int n0 = (int)(tile * BN);
-        for (uint32_t t = 0; t < T; t++, it++) {
-          const uint32_t stage = it % NSTAGE, phase = (it / NSTAGE) & 1u;
+        for (uint32_t t = 0; t < T; t++) {
           const uint32_t seg = t / p.nkb, kb = t % p.nkb;
           mbar_wait(&empty[stage], phase ^ 1u);
           mbar_expect_tx(&full[stage], B_BYTES + (p.a_resident ? 0 : A_BYTES));
           tma_load_2d(sB + stage * B_BYTES, seg == 1 ? &mB_lo : &mB_hi, (int)(kb * BK), n0, &full[stage]);
           if (!p.a_resident)
             tma_load_2d(sA + stage * A_BYTES, seg == 2 ? &mA_lo : &mA_hi, (int)(kb * BK), (int)m0, &full[stage]);
+          if (++stage == NS) { stage = 0; phase ^= 1u; }
         }
       }
     }
   } else if (warp == 1) {
     // ===== MMA issuer =====
     if (p.a_resident) mbar_wait(a_full, 0);
-    uint32_t it = 0, ti = 0;
+    uint32_t stage = 0, phase = 0, ti = 0;
     for (uint32_t tile = tile_begin; tile < tile_end; tile++, ti++) {
       const uint32_t as = ti & 1u, aphase = (ti >> 1) & 1u;
       mbar_wait(&tmem_empty[as], aphase ^ 1u);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + as * BN;
-      for (uint32_t t = 0; t < T; t++, it++) {
-        const uint32_t stage = it % NSTAGE, phase = (it / NSTAGE) & 1u;
+      for (uint32_t t = 0; t < T; t++) {
         const uint32_t seg = t / p.nkb, kb = t % p.nkb;
         mbar_wait(&full[stage], phase);
         tc_fence_after();
@@ -385,48 +393,59 @@ sweep_kernel(const __grid_constant__ CUtensorMap mA_hi, const __grid_constant__ 
 #pragma unroll
           for (int k = 0; k < BK / 16; k++)
             tc_mma(d_tmem, smem_desc(a_addr + k * 32), smem_desc(b_addr + k * 32), IDESC, (t > 0 || k > 0) ? 1u : 0u);
-          tc_commit(&empty[stage]);               // frees the smem stage once these MMAs have read it
+          tc_commit(&empty[stage]);                   // frees the smem stage once these MMAs have read it
           if (t == T - 1) tc_commit(&tmem_full[as]);  // accumulator complete
         }
         __syncwarp();
+        if (++stage == NS) { stage = 0; phase ^= 1u; }
       }
     }
   } else {
-    // ===== epilogue: thread = query row =====
-    const int ew = warp - 2;              // 0..3
-    const int lg = warp & 3;              // TMEM lane group this warp may read
-    const int et = ew * 32 + lane;        // 0..127
-    const uint32_t row_local = blockIdx.x * BM + lg * 32 + lane;
+    // ===== epilogue =====
+    const int ew = warp - 2;   // 0..7
+    const int q = warp & 3;    // TMEM lane quarter this warp may read
+    const int hf = ew >> 2;    // column half of every tile
+    const int et = ew * 32 + lane;
+    const int rowi = q * 32 + lane;  // row within the CTA
+    const uint32_t row_local = blockIdx.x * BM + rowi;
     const bool row_valid = row_local < p.nq_rows;
     const uint32_t self = p.exclude_self ? p.q_row0 + row_local : INVALID_ID;
-    const size_t sr = (size_t)blockIdx.y * p.rows_pad + row_local;
-    float *cd = p.cand_d + sr * p.cap;
-    uint32_t *ci = p.cand_i + sr * p.cap;
+    const size_t sr0 = (size_t)blockIdx.y * p.rows_pad + blockIdx.x * BM + q * 32;  // scratch row of lane 0
+    float *cd = p.cand_d + (sr0 + lane) * p.cap;
+    uint32_t *ci = p.cand_i + (sr0 + lane) * p.cap;
     uint32_t *myhist = hist + ew * 256;
-    uint32_t cnt = 0;
-    float tau = row_valid ? INFINITY : -INFINITY;
-    const uint32_t full_at = p.cap - 32;
+    float *sp = spill + ew * (32 * 36) + lane * 36;
+    const int pair_bar = 2 + q;
+    long long pf_wait = 0, pf_proc = 0, pf_comp = 0, pf_t0 = clock64();
+    uint32_t pf_ncomp = 0;
 
-    long long pf_wait = 0, pf_slow = 0, pf_comp = 0, pf_t0 = clock64();
-    uint32_t pf_ncomp = 0, pf_push = 0, pf_nslow = 0, pf_nchunk = 0;
-    auto maybe_compact = [&](uint32_t limit) {
-      uint32_t need = __ballot_sync(0xffffffffu, cnt > limit);
-      if (!need) return;
-      long long c0 = clock64();
-      while (need) {
-        pf_ncomp++;
-        int l = __ffs(need) - 1;
-        need &= need - 1;
-        float *rcd = (float *)__shfl_sync(0xffffffffu, (unsigned long long)cd, l);
-        uint32_t *rci = (uint32_t *)__shfl_sync(0xffffffffu, (unsigned long long)ci, l);
-        uint32_t rcnt = __shfl_sync(0xffffffffu, cnt, l);
-        float t;
-        if (p.cap <= 256) t = compact_row_reg<8>(rcd, rci, rcnt, p.Kp, myhist, lane);
-        else if (p.cap <= 640) t = compact_row_reg<20>(rcd, rci, rcnt, p.Kp, myhist, lane);
-        else t = compact_row(rcd, rci, rcnt, p.Kp, myhist, lane);
-        if (lane == l) { cnt = p.Kp; tau = t; }
+    if (hf == 0) { cnt_s[rowi] = 0; tau_s[rowi] = row_valid ? INFINITY : -INFINITY; }
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    float tau = tau_s[rowi];
+
+    // rows of this quarter whose count exceeds `limit`: the even rows are compacted by half 0, the odd by half 1
+    auto compact_phase = [&](uint32_t limit) {
+      asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+      uint32_t need = __ballot_sync(0xffffffffu, cnt_s[rowi] > limit && (lane & 1) == hf);
+      if (need) {
+        long long c0 = clock64();
+        while (need) {
+          const int l = __ffs(need) - 1;
+          need &= need - 1;
+          float *rcd = p.cand_d + (sr0 + l) * p.cap;
+          uint32_t *rci = p.cand_i + (sr0 + l) * p.cap;
+          const uint32_t rcnt = cnt_s[q * 32 + l];
+          float t;
+          if (p.cap <= 384) t = compact_row_reg<12>(rcd, rci, rcnt, p.Kp, myhist, lane);
+          else if (p.cap <= 768) t = compact_row_reg<24>(rcd, rci, rcnt, p.Kp, myhist, lane);
+          else t = compact_row(rcd, rci, rcnt, p.Kp, myhist, lane);
+          if (lane == 0) { cnt_s[q * 32 + l] = p.Kp; tau_s[q * 32 + l] = t; }
+          pf_ncomp++;
+        }
+        pf_comp += clock64() - c0;
       }
-      pf_comp += clock64() - c0;
+      asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+      tau = tau_s[rowi];
     };
 
     uint32_t ti = 0;
@@ -434,70 +453,74 @@ sweep_kernel(const __grid_constant__ CUtensorMap mA_hi, const __grid_constant__ 
       const uint32_t as = ti & 1u, aphase = (ti >> 1) & 1u;
       const uint32_t n0 = tile * BN;
       {
-        float *nys = ny_s + as * BN;
-        uint32_t c0 = n0 + et, c1 = n0 + et + 128;
-        nys[et] = c0 < p.n ? (p.ny ? __ldg(p.ny + c0) : 0.f) : INFINITY;
-        nys[et + 128] = c1 < p.n ? (p.ny ? __ldg(p.ny + c1) : 0.f) : INFINITY;
+        const uint32_t c0 = n0 + et;
+        ny_s[as * BN + et] = c0 < p.n ? (p.ny ? __ldg(p.ny + c0) : 0.f) : INFINITY;
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync 1, 256;" ::: "memory");
       { long long c0 = clock64(); mbar_wait(&tmem_full[as], aphase); pf_wait += clock64() - c0; }
       tc_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + as * BN;
-      const float *nys = ny_s + as * BN;
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + hf * 128;
+      const float *nys = ny_s + as * BN + hf * 128;
+      const uint32_t colh = n0 + hf * 128;
+      long long pc0 = clock64();
 
       auto process = [&](const uint32_t(&v)[32], int c) {
+        uint4 *dst = (uint4 *)sp;
+#pragma unroll
+        for (int j = 0; j < 8; j++) dst[j] = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
         const float4 *ny4 = (const float4 *)(nys + c * 32);
-        const uint32_t colb = n0 + c * 32;
-        pf_nchunk++;
-        long long c0 = clock64();
+        uint32_t hm = 0;
 #pragma unroll
         for (int j = 0; j < 8; j++) {
           const float4 y = ny4[j];
           const float d0 = fmaf(-2.f, __uint_as_float(v[4 * j + 0]), y.x), d1 = fmaf(-2.f, __uint_as_float(v[4 * j + 1]), y.y);
           const float d2 = fmaf(-2.f, __uint_as_float(v[4 * j + 2]), y.z), d3 = fmaf(-2.f, __uint_as_float(v[4 * j + 3]), y.w);
-          // warp-uniform test per column pair; the pushes themselves are rare (~0.3 % of the elements)
-          if (__any_sync(0xffffffffu, (d0 < tau) | (d1 < tau))) {
-            pf_nslow++;
-            if (d0 < tau && colb + 4 * j + 0 != self) { __stcg(cd + cnt, d0); __stcg(ci + cnt, colb + 4 * j + 0); cnt++; pf_push++; }
-            if (d1 < tau && colb + 4 * j + 1 != self) { __stcg(cd + cnt, d1); __stcg(ci + cnt, colb + 4 * j + 1); cnt++; pf_push++; }
-          }
-          if (__any_sync(0xffffffffu, (d2 < tau) | (d3 < tau))) {
-            pf_nslow++;
-            if (d2 < tau && colb + 4 * j + 2 != self) { __stcg(cd + cnt, d2); __stcg(ci + cnt, colb + 4 * j + 2); cnt++; pf_push++; }
-            if (d3 < tau && colb + 4 * j + 3 != self) { __stcg(cd + cnt, d3); __stcg(ci + cnt, colb + 4 * j + 3); cnt++; pf_push++; }
+          if (d0 < tau) hm |= 1u << (4 * j + 0);
+          if (d1 < tau) hm |= 1u << (4 * j + 1);
+          if (d2 < tau) hm |= 1u << (4 * j + 2);
+          if (d3 < tau) hm |= 1u << (4 * j + 3);
+        }
+        if (__any_sync(0xffffffffu, hm != 0)) {
+          while (hm) {  // rare (~0.3 % of the elements): lanes diverge here
+            const int j = __ffs(hm) - 1;
+            hm &= hm - 1;
+            const uint32_t col = colh + c * 32 + j;
+            if (col != self) {
+              const float d = fmaf(-2.f, sp[j], nys[c * 32 + j]);
+              const uint32_t pos = atomicAdd(&cnt_s[rowi], 1u);
+              __stcg(cd + pos, d);
+              __stcg(ci + pos, col);
+            }
           }
         }
-        pf_slow += clock64() - c0;
-        maybe_compact(full_at);
+        __syncwarp();
       };
 
       uint32_t va[32], vb[32];
       TC_LD32(taddr, va);
       TC_LD_WAIT(va);
-#pragma unroll 1
-      for (int c = 0; c < BN / 32; c += 2) {
-        TC_LD32(taddr + (c + 1) * 32, vb);
-        process(va, c);
-        TC_LD_WAIT(vb);
-        if (c + 2 < BN / 32) TC_LD32(taddr + (c + 2) * 32, va);
-        process(vb, c + 1);
-        if (c + 2 < BN / 32) TC_LD_WAIT(va);
-      }
+      TC_LD32(taddr + 32, vb);
+      process(va, 0);
+      TC_LD_WAIT(vb);
+      TC_LD32(taddr + 64, va);
+      process(vb, 1);
+      TC_LD_WAIT(va);
+      TC_LD32(taddr + 96, vb);
+      process(va, 2);
+      TC_LD_WAIT(vb);
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tmem_empty[as]);
+      if (lane == 0) mbar_arrive(&tmem_empty[as]);  // all TMEM reads of this warp are done
+      process(vb, 3);
+      pf_proc += clock64() - pc0;
+      compact_phase(p.cap - 256);
     }
-    // leave at most Kp entries per row
-    maybe_compact(p.Kp);
-    if (row_valid) { p.cand_n[sr] = cnt; p.cand_tau[sr] = tau; }
-    if (p.prof) {
-      for (int o = 16; o; o >>= 1) pf_push += __shfl_xor_sync(0xffffffffu, pf_push, o);
-      if (lane == 0) {
-        atomicAdd(p.prof + 0, (unsigned long long)pf_wait); atomicAdd(p.prof + 1, (unsigned long long)pf_slow);
-        atomicAdd(p.prof + 2, (unsigned long long)pf_comp); atomicAdd(p.prof + 3, (unsigned long long)(clock64() - pf_t0));
-        atomicAdd(p.prof + 4, (unsigned long long)pf_ncomp); atomicAdd(p.prof + 5, (unsigned long long)pf_push);
-        atomicAdd(p.prof + 6, (unsigned long long)pf_nslow); atomicAdd(p.prof + 7, (unsigned long long)pf_nchunk);
-      }
+    compact_phase(p.Kp);  // leave at most Kp entries per row
+    if (hf == 0 && row_valid) { p.cand_n[sr0 + lane] = cnt_s[rowi]; p.cand_tau[sr0 + lane] = tau_s[rowi]; }
+    if (p.prof && lane == 0) {
+      atomicAdd(p.prof + 0, (unsigned long long)pf_wait); atomicAdd(p.prof + 1, (unsigned long long)pf_proc);
+      atomicAdd(p.prof + 2, (unsigned long long)pf_comp); atomicAdd(p.prof + 3, (unsigned long long)(clock64() - pf_t0));
+      atomicAdd(p.prof + 4, (unsigned long long)pf_ncomp);
     }
   }
   tc_fence_before();
@@ -772,6 +795,16 @@ int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t n
   const uint32_t passes = (ix->tc_inexact || qs.inexact) ? 3u : 1u;
   const uint32_t nkb = (uint32_t)(dpad / tc::BK);
   const uint32_t a_res = nkb * (passes == 3 ? 2u : 1u) <= (uint32_t)tc::A_SLOTS ? 1u : 0u;
+  uint32_t a_slots, nstage;
+  if (a_res) {
+    a_slots = nkb * (passes == 3 ? 2u : 1u);
+    nstage = (tc::SMEM_MAX - 1024 - tc::SMEM_MISC - a_slots * tc::A_BYTES) / tc::B_BYTES;
+  } else {
+    nstage = (tc::SMEM_MAX - 1024 - tc::SMEM_MISC) / (tc::A_BYTES + tc::B_BYTES);
+    a_slots = nstage;
+  }
+  if (nstage > 6) nstage = 6;
+  const int sweep_smem = 1024 + (int)(a_slots * tc::A_BYTES + nstage * tc::B_BYTES) + tc::SMEM_MISC;
 
   CUtensorMap mA_hi, mA_lo, mB_hi, mB_lo;
   if (!make_map(&mA_hi, qs.hi, nq, dpad, tc::BM) || !make_map(&mA_lo, qs.lo, nq, dpad, tc::BM) ||
@@ -780,7 +813,7 @@ int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t n
 
   // 2. geometry
   const uint32_t Kp = shortlist_size(h, k);
-  const uint32_t cap = (2 * Kp + 64 + 31) / 32 * 32;
+  const uint32_t cap = (2 * Kp + 256 + 31) / 32 * 32;  // a tile adds at most 256 entries to a row between compactions
   const uint32_t ntiles = (uint32_t)((n + tc::BN - 1) / tc::BN);
   const size_t chunk_rows = (size_t)h->sm_count * 4 * tc::BM;
   const size_t rows0 = nq < chunk_rows ? nq : chunk_rows;
@@ -815,7 +848,7 @@ int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t n
 
   const size_t stride4 = (dim + 3) / 4 * 4;
   const size_t fin_smem = (size_t)4 * 32 * tc::RS4 * 16 + stride4 * 4 + (size_t)P * 8;
-  CU_CHECK(h, cudaFuncSetAttribute(tc::sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
+  CU_CHECK(h, cudaFuncSetAttribute(tc::sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sweep_smem));
   CU_CHECK(h, cudaFuncSetAttribute(tc::finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fin_smem));
 
   // error bound of the tensor-core ranking key (see the file header): inputs, accumulation, fp32 roundings
@@ -832,12 +865,12 @@ int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t n
     const uint32_t rows = (uint32_t)((nq - r0) < chunk_rows ? (nq - r0) : chunk_rows);
     const uint32_t mtiles = (rows + tc::BM - 1) / tc::BM;
     tc::SweepParams sp = {};
-    sp.nq_rows = rows; sp.q_row0 = (uint32_t)r0; sp.n = (uint32_t)n; sp.nkb = nkb; sp.passes = passes; sp.a_resident = a_res;
+    sp.nq_rows = rows; sp.q_row0 = (uint32_t)r0; sp.n = (uint32_t)n; sp.nkb = nkb; sp.passes = passes; sp.a_resident = a_res; sp.a_slots = a_slots; sp.nstage = nstage;
     sp.ntiles = ntiles; sp.tiles_per_split = tiles_per_split; sp.ny = ip ? nullptr : ix->tc_norms;
     sp.exclude_self = exclude_self; sp.Kp = Kp; sp.cap = cap; sp.rows_pad = rows_pad;
     sp.cand_d = cand_d.p; sp.cand_i = cand_i.p; sp.cand_n = cand_n.p; sp.cand_tau = cand_tau.p;
     sp.prof = want_prof ? prof.p : nullptr;
-    tc::sweep_kernel<<<dim3(mtiles, splits), tc::NTHREADS, tc::SMEM_BYTES, h->stream>>>(mA_hi, mA_lo, mB_hi, mB_lo, sp);
+    tc::sweep_kernel<<<dim3(mtiles, splits), tc::NTHREADS, sweep_smem, h->stream>>>(mA_hi, mA_lo, mB_hi, mB_lo, sp);
     h->launches++;
     CU_CHECK(h, cudaGetLastError());
     tc::FinParams fp = {};
@@ -863,8 +896,8 @@ int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t n
   if (want_prof) {
     unsigned long long pv[8];
     CU_CHECK(h, cudaMemcpy(pv, prof.p, 64, cudaMemcpyDeviceToHost));
-    fprintf(stderr, "[knn_tc prof] per-warp-sum cycles: wait %llu slow %llu compact %llu total %llu | compactions %llu pushes %llu slow chunks %llu of %llu\n",
-            pv[0], pv[1], pv[2], pv[3], pv[4], pv[5], pv[6], pv[7]);
+    fprintf(stderr, "[knn_tc prof] epilogue-warp cycle sums: wait %llu process %llu compact %llu total %llu | compactions %llu | nstage %u a_slots %u\n",
+            pv[0], pv[1], pv[2], pv[3], pv[4], nstage, a_slots);
   }
   h->knn_stats[0] = nq; h->knn_stats[1] = nf; h->knn_stats[2] = nc; h->knn_stats[3] = passes;
   h->knn_stats[4] = splits; h->knn_stats[5] = Kp; h->knn_stats[6] = (uint64_t)ntiles * ((nq + tc::BM - 1) / tc::BM); h->knn_stats[7] = a_res;

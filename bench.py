@@ -54,6 +54,14 @@ def recall_at_k(found, truth):
     return hit / float(truth.size)
 
 
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f)
+    except Exception:
+        return {}
+
+
 def measured_peak_gbs():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -176,6 +184,16 @@ def build_index(B, h, base, q, rank):
         ix.knn_graph_raw(KNN_K, knn)
         info["knn_graph_s"] = time.time() - t
         info["knn_graph_kernel_ms"] = h.last_kernel_ms
+        st = h.knn_last_stats
+        info["knn_graph_stats"] = st
+        # tensor roofline of the kNN-graph build: 2*n*n*dim useful flops (x passes issued) over the device time
+        flops = 2.0 * N_BASE * N_BASE * DIM
+        info["knn_graph_roofline"] = {
+            "bound": "tensor", "kernel": "tc::sweep_kernel (tcgen05 bf16)" if st["rows"] else "bf_knn_kernel (fp32 SIMT)",
+            "achieved": flops * max(1, st["passes"]) / (h.last_kernel_ms * 1e-3) / 1e12, "useful": flops / (h.last_kernel_ms * 1e-3) / 1e12,
+            "peak": measured_peaks().get("bf16_tflops_sustained"), "unit": "TFLOP/s"}
+        if info["knn_graph_roofline"]["peak"]:
+            info["knn_graph_roofline"]["frac"] = info["knn_graph_roofline"]["achieved"] / info["knn_graph_roofline"]["peak"]
         log("rank %d: exact kNN graph K=%d in %.2fs" % (rank, KNN_K, info["knn_graph_s"]))
         t = time.time()
         bi = ix.nsg_build((knn, KNN_K), NSG_L, NSG_R, NSG_C, seed=1)
@@ -388,7 +406,7 @@ def run_ours(args):
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": alg_bytes,
                          "dist_evals_per_query": n_dist / nq, "hops_per_query": n_hops / nq},
-            "build": {k: info.get(k) for k in ("knn_graph_s", "knn_graph_kernel_ms", "nsg_build_s", "nsg_build_device_ms",
+            "build": {k: info.get(k) for k in ("knn_graph_s", "knn_graph_kernel_ms", "knn_graph_stats", "knn_graph_roofline", "nsg_build_s", "nsg_build_device_ms",
                                                "nsg", "graph_from_cache", "gt_ms")},
         }
         if world == 1 and not args.no_cpu_baseline:

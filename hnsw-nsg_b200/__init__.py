@@ -45,6 +45,7 @@ _lib.b200ann_index_get_graph.argtypes = [_vp, _vp, _sz, C.POINTER(C.c_uint32), C
 _lib.b200ann_index_set_hnsw.argtypes = [_vp, _vp, _sz, _vp, _vp, _vp, _sz, _sz, _vp, C.c_uint32, C.c_int]
 _lib.b200ann_bf_knn.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _vp, _vp]
 _lib.b200ann_knn_graph.argtypes = [_vp, _vp, _sz, _vp]
+_lib.b200ann_nndescent.argtypes = [_vp, _vp, _sz, _sz, _sz, _sz, _sz, C.c_uint32, _vp, _vp, _vp]
 _lib.b200ann_nsg_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, C.c_uint32, _vp, _vp, _vp]
 _lib.b200ann_hnsw_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _vp, _vp, _vp]
 _u32 = C.c_uint32
@@ -67,7 +68,7 @@ EXPORTS = [
     "b200ann_index_set_hnsw", "b200ann_bf_knn", "b200ann_knn_graph", "b200ann_nsg_search", "b200ann_hnsw_search",
     "b200ann_set_link_visited_bits", "b200ann_nsg_build", "b200ann_nsg_init_ep", "b200ann_nsg_link",
     "b200ann_nsg_interinsert", "b200ann_nsg_finish", "b200ann_merge_topk", "b200ann_nsg_search_from",
-    "b200ann_hybrid_search", "b200ann_set_knn_mode", "b200ann_knn_last_stats",
+    "b200ann_hybrid_search", "b200ann_set_knn_mode", "b200ann_knn_last_stats", "b200ann_nndescent",
 ]
 
 
@@ -221,6 +222,17 @@ class Index:
     def knn_graph_raw(self, K, out):
         """out: device buffer [n,K] u32/i32 (torch tensor or raw pointer)"""
         self.h._check(_lib.b200ann_knn_graph(self.h._h, self._ix, K, _ptr(out)))
+
+    def nndescent(self, K, L, it, S, R, seed=0, want_dists=False, out=None):
+        """IndexGraph::Build (NN-descent) on the GPU: returns knn [n,K] (+ dists) and the info dict.
+        out: optional device buffer [n,K] (torch tensor / raw pointer) instead of a numpy result."""
+        knn = out if out is not None else np.empty((self.n, K), np.uint32)
+        d = np.empty((self.n, K), np.float32) if want_dists else None
+        info = np.zeros(8, np.uint64)
+        self.h._check(_lib.b200ann_nndescent(self.h._h, self._ix, K, L, it, S, R, seed, _ptr(knn), _ptr(d), _ptr(info)))
+        keys = ("dist_evals", "offers", "inserts", "iterations", "join_us", "update_us")
+        inf = dict(zip(keys, (int(x) for x in info)))
+        return (knn, d, inf) if want_dists else (knn, inf)
 
     # ---- NSG construction (IndexNSG::Build and its phases)
     def nsg_build(self, knn, L, R, C_, seed=0, ep0=INVALID):

@@ -289,6 +289,24 @@ int b200ann_knn_graph(b200ann_handle_t h, b200ann_index_t ix, size_t K, uint32_t
   return 0;
 }
 
+int b200ann_nndescent(b200ann_handle_t h, b200ann_index_t ix, size_t K, size_t L, size_t iter, size_t S, size_t R,
+                      uint32_t seed, uint32_t *knn, float *dists, uint64_t *info) {
+  if (!h || !ix) return B200ANN_ERR_ARG;
+  if (!knn) return set_err(h, B200ANN_ERR_ARG, "nndescent: knn output is NULL");
+  CU_CHECK(h, cudaSetDevice(h->device));
+  OutArg<uint32_t> oi; OutArg<float> od;
+  CU_CHECK(h, oi.stage(knn, ix->n * K, h->stream));
+  CU_CHECK(h, od.stage(dists, ix->n * K, h->stream));
+  CallTimer t(h);
+  int rc = nndescent_launch(h, ix, K, L, iter, S, R, seed, oi.d, od.d, info);
+  t.stop();
+  if (rc) return rc;
+  CU_CHECK(h, oi.finish(h->stream));
+  CU_CHECK(h, od.finish(h->stream));
+  CU_CHECK(h, t.sync());
+  return 0;
+}
+
 int b200ann_nsg_search(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_t nq, size_t qstride, size_t K,
                        size_t L, uint32_t seed, uint32_t *ids, float *dists, uint32_t *stats) {
   if (!h || !ix) return B200ANN_ERR_ARG;

@@ -145,6 +145,10 @@ int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t n
 bool knn_tc_supported(const b200ann_index *ix, size_t nq, size_t k);
 void knn_tc_free(b200ann_index *ix);
 
+// NN-descent (nndescent.cu); device pointers only
+int nndescent_launch(b200ann_handle *h, const b200ann_index *ix, size_t K, size_t L, size_t iter, size_t S, size_t R,
+                     uint32_t seed, uint32_t *knn, float *knn_d, uint64_t *info8);
+
 // NSG build phases (nsg_build.cu); device pointers only
 int nsg_centroid_launch(b200ann_handle *h, const b200ann_index *ix, float *center);
 int nsg_link_launch(b200ann_handle *h, const b200ann_index *ix, const uint32_t *knn, size_t kstride, uint32_t ep,

@@ -1,0 +1,499 @@
+// NN-descent kNN-graph construction on the GPU.
+//
+// Replaces efanna2e::IndexGraph::Build with the IndexRandom initializer
+// (CNNS/efanna_graph/src/index_graph.cpp:265-294 = InitializeGraph :175-201 + NNDescent :122-136 =
+// iter x { join :22-33 (nhood::join / nhood::insert, efanna2e/neighbor.h:57-87), update :34-120 } + the
+// top-K extraction :275-291; index_random.cpp:24-27, util.h:17-31 GenRandom).
+//
+// The reference is a lock-per-node, order-dependent CPU loop. Here every phase is a set function of its
+// inputs ("batch form", restated serially by oracle/oracle.c orc_nndescent_batch and compared bit for bit):
+//   pool        u64 [n, L] sorted ascending, key = distance bits << 32 | id << 1 | flag (L2 distances are
+//               >= 0, so the raw bits order like the floats). A pool is the set of the <= L smallest keys it
+//               has been offered (dedup by id); an offer is admitted only if distance <= the pool's largest
+//               distance at the start of the join (nhood::insert's heap-top test, neighbor.h:59).
+//   join        one CTA per node: the sampled rows are gathered into shared memory in 64 x 64 tiles and all
+//               new x new (each unordered pair once) and new x old distances are computed in fp32, k
+//               sequential with fmaf (oracle mode L2_SEQ_FMA); pairs that pass the destination's threshold
+//               go through a shared-memory queue to warp-cooperative sorted inserts under a per-node lock.
+//   update      M / new / old sampling exactly as :49-98; the reverse lists keep the R offers with the smallest
+//               (hash(seed_it, node, source), source) instead of "first R then overwrite slot rand() % R"
+//               (:78-82), through the same sorted-insert primitive; `pool.back()` (:76,:88) follows the
+//               reference's one-thread schedule: the largest distance when the other node's id is larger,
+//               the std::make_heap leaf when it is smaller (leaf_rank table).
+#include <algorithm>
+#include <vector>
+#include "common.cuh"
+
+namespace nnd {
+
+__device__ __forceinline__ uint32_t mix32(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
+  return x;
+}
+// same stream as beam::seed_hash / oracle orc_seed_hash
+__device__ __forceinline__ uint32_t seed_hash(uint32_t seed, uint32_t query, uint32_t counter) {
+  return mix32(mix32(seed ^ (query * 0x9E3779B9U)) + counter * 0x85EBCA6BU);
+}
+
+constexpr uint32_t SEED_POOL = 0x68E31DA4U;
+constexpr int MAX_GEN = 128;   // 2S and S+1 must fit
+constexpr uint64_t EMPTY = ~0ull;
+
+struct State {
+  const float *vec; size_t stride; uint32_t n, dim;
+  uint32_t L, S, R, K;
+  uint32_t cap_fnew, cap_fold;          // 2S, min(L, 2R)
+  uint64_t *pool;                       // [n, L]
+  uint32_t *psize, *M, *worst, *leafd;  // [n]
+  uint32_t *fwd_new, *fwd_old;          // [n, cap_fnew], [n, cap_fold]
+  uint32_t *n_fnew, *n_fold;            // [n]
+  uint64_t *rnn_new, *rnn_old;          // [n, R]
+  uint32_t *n_rnew, *n_rold;            // [n]
+  uint32_t *lock_pool, *lock_rnew, *lock_rold;  // [n]
+  const uint32_t *leaf_rank;            // [L+1]
+  unsigned long long *stats;            // {distance evaluations, offers queued, inserts done, next node}
+};
+
+// efanna2e::GenRandom (util.h:17-31) over the stateless stream seed_hash(seed, node, draw)
+__device__ void gen_random(uint32_t seed, uint32_t node, uint32_t *addr, uint32_t size, uint32_t N) {
+  uint32_t ctr = 0;
+  for (uint32_t i = 0; i < size; ++i) {
+    uint32_t v = seed_hash(seed, node, ctr++) % (N - size);
+    uint32_t j = i;  // insertion sort == std::sort on integers
+    while (j > 0 && addr[j - 1] > v) { addr[j] = addr[j - 1]; --j; }
+    addr[j] = v;
+  }
+  for (uint32_t i = 1; i < size; ++i)
+    if (addr[i] <= addr[i - 1]) addr[i] = addr[i - 1] + 1;
+  uint32_t off = seed_hash(seed, node, ctr++) % N;
+  for (uint32_t i = 0; i < size; ++i) addr[i] = (addr[i] + off) % N;
+}
+
+// sequential-over-k fmaf order (oracle ORC_L2_SEQ_FMA), one thread
+__device__ float seq_l2(const float *a, const float *b, uint32_t dim) {
+  float acc = 0.f;
+  for (uint32_t k = 0; k < dim; ++k) { float t = a[k] - b[k]; acc = fmaf(t, t, acc); }
+  return acc;
+}
+
+// InitializeGraph (:175-201): nn_new = 2S random ids (nhood ctor), pool = first S of S+1 random ids minus self
+__global__ void init_kernel(State s, uint32_t seed) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= s.n) return;
+  uint32_t tmp[MAX_GEN];
+  gen_random(seed, i, tmp, 2 * s.S, s.n);
+  for (uint32_t j = 0; j < 2 * s.S; ++j) s.fwd_new[(size_t)i * s.cap_fnew + j] = tmp[j];
+  s.n_fnew[i] = 2 * s.S;
+  s.n_fold[i] = 0; s.n_rnew[i] = 0; s.n_rold[i] = 0;
+  s.M[i] = s.S;
+  s.lock_pool[i] = 0; s.lock_rnew[i] = 0; s.lock_rold[i] = 0;
+  gen_random(seed ^ SEED_POOL, i, tmp, s.S + 1, s.n);
+  uint64_t *pool = s.pool + (size_t)i * s.L;
+  uint32_t sz = 0;
+  for (uint32_t j = 0; j < s.S; ++j) {
+    uint32_t id = tmp[j];
+    if (id == i) continue;
+    float d = seq_l2(s.vec + (size_t)i * s.stride, s.vec + (size_t)id * s.stride, s.dim);
+    uint64_t key = ((uint64_t)__float_as_uint(d) << 32) | (id << 1) | 1u;
+    uint32_t p = sz;
+    while (p > 0 && pool[p - 1] > key) { pool[p] = pool[p - 1]; --p; }
+    pool[p] = key;
+    ++sz;
+  }
+  for (uint32_t j = sz; j < s.L; ++j) pool[j] = EMPTY;
+  s.psize[i] = sz;
+  s.worst[i] = (uint32_t)(pool[sz - 1] >> 32);
+  atomicAdd(s.stats + 0, (unsigned long long)sz);
+}
+
+// ---- warp-cooperative "keep the cap smallest keys, sorted" under a per-list lock -------------------------
+// All list accesses go through L2 (.cg) because other SMs update the same lists.
+template <int NT>
+__device__ bool warp_topl_insert(uint64_t *list, uint32_t *size_p, uint32_t *lock, uint32_t cap, uint64_t key,
+                                 bool dedup, int lane) {
+  // racy prefilter: the last slot only ever decreases (EMPTY while the list is not full)
+  if (__ldcg((const unsigned long long *)(list + cap - 1)) <= key) return false;
+  if (lane == 0) {
+    while (atomicCAS(lock, 0u, 1u) != 0u) __nanosleep(32);
+    __threadfence();
+  }
+  __syncwarp();
+  uint32_t size = __ldcg(size_p);
+  uint64_t e[NT];
+  const uint32_t id = (uint32_t)key >> 1;
+  int less = 0;
+  bool dup = false;
+#pragma unroll
+  for (int t = 0; t < NT; ++t) {
+    uint32_t idx = t * 32 + lane;
+    e[t] = idx < size ? __ldcg((const unsigned long long *)(list + idx)) : EMPTY;
+    if (idx < size) {
+      less += e[t] < key;
+      dup |= dedup && (((uint32_t)e[t] >> 1) == id);
+    }
+  }
+  uint32_t pos = __reduce_add_sync(0xffffffffu, less);
+  bool ok = !__any_sync(0xffffffffu, dup) && pos < cap;
+  if (ok) {
+#pragma unroll
+    for (int t = 0; t < NT; ++t) {
+      uint32_t idx = t * 32 + lane;
+      if (idx >= pos && idx < size && idx + 1 < cap) __stcg((unsigned long long *)(list + idx + 1), e[t]);
+    }
+    if (lane == 0) {
+      __stcg((unsigned long long *)(list + pos), key);
+      if (size < cap) __stcg(size_p, size + 1);
+    }
+  }
+  __threadfence();
+  __syncwarp();
+  if (lane == 0) atomicExch(lock, 0u);
+  return ok;
+}
+
+__device__ __forceinline__ bool topl_insert_dispatch(uint64_t *list, uint32_t *size_p, uint32_t *lock, uint32_t cap,
+                                                     uint64_t key, bool dedup, int lane) {
+  if (cap <= 64) return warp_topl_insert<2>(list, size_p, lock, cap, key, dedup, lane);
+  if (cap <= 128) return warp_topl_insert<4>(list, size_p, lock, cap, key, dedup, lane);
+  if (cap <= 256) return warp_topl_insert<8>(list, size_p, lock, cap, key, dedup, lane);
+  return warp_topl_insert<16>(list, size_p, lock, cap, key, dedup, lane);
+}
+
+// ---- join (:22-33) ---------------------------------------------------------------------------------------
+constexpr int JT = 256;          // threads per CTA
+constexpr int TILE = 64;         // pairs tile TILE x TILE, 4 x 4 per thread
+constexpr int KC = 128;          // floats of the dimension staged per pass
+constexpr int ROWF = KC + 4;     // padded shared-memory row (bank shift of 4 per row, 16-byte aligned)
+constexpr int QCAP = 2048;       // offer queue entries per CTA
+
+struct Offer { uint32_t dst, src, dbits; };
+
+__device__ __forceinline__ void load_rows(float *sm, const State &s, const uint32_t *ids, uint32_t pos0, uint32_t limit,
+                                          uint32_t kc, uint32_t kw4, int tid) {
+  // TILE rows x kw4 float4; one warp covers one row's 32 float4 (512 contiguous bytes)
+  const int warp = tid >> 5, lane = tid & 31;
+  for (int r = warp; r < TILE; r += JT / 32) {
+    uint32_t pos = pos0 + r;
+    float4 *dst = reinterpret_cast<float4 *>(sm + r * ROWF);
+    if (pos < limit) {
+      const float4 *src = reinterpret_cast<const float4 *>(s.vec + (size_t)ids[pos] * s.stride + kc);
+      for (uint32_t c = lane; c < kw4; c += 32) dst[c] = __ldg(src + c);
+    } else {
+      for (uint32_t c = lane; c < kw4; c += 32) dst[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(JT, 2) join_kernel(State s, uint32_t cn_max) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float *As = reinterpret_cast<float *>(smem_raw);
+  float *Bs = As + TILE * ROWF;
+  Offer *queue = reinterpret_cast<Offer *>(Bs + TILE * ROWF);
+  uint32_t *ids = reinterpret_cast<uint32_t *>(queue + QCAP);
+  uint32_t *thr = ids + cn_max;
+  __shared__ uint32_t sh_node, sh_nn, sh_no, sh_qn;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int ty = tid >> 4, tx = tid & 15;
+  const uint32_t cap_old = 2 * s.R;
+  unsigned long long my_dist = 0, my_offer = 0, my_ins = 0;
+
+  for (;;) {
+    if (tid == 0) {
+      uint32_t node = (uint32_t)atomicAdd(s.stats + 3, 1ull);
+      sh_node = node;
+      if (node < s.n) {
+        uint32_t nfn = s.n_fnew[node], nrn = s.n_rnew[node];
+        uint32_t nfo = s.n_fold[node], nro = s.n_rold[node];
+        uint32_t no = nfo + nro;
+        sh_nn = nfn + nrn;
+        sh_no = no < cap_old ? no : cap_old;
+      }
+      sh_qn = 0;
+    }
+    __syncthreads();
+    const uint32_t node = sh_node;
+    if (node >= s.n) break;
+    const uint32_t nn = sh_nn, no = sh_no, ct = nn + no;
+    {  // member ids: new = fwd_new ++ rnn_new, old = (fwd_old ++ rnn_old)[:2R]; thresholds
+      const uint32_t nfn = s.n_fnew[node], nfo = s.n_fold[node];
+      for (uint32_t p = tid; p < ct; p += JT) {
+        uint32_t id;
+        if (p < nn) id = p < nfn ? s.fwd_new[(size_t)node * s.cap_fnew + p] : (uint32_t)s.rnn_new[(size_t)node * s.R + (p - nfn)];
+        else {
+          uint32_t q = p - nn;
+          id = q < nfo ? s.fwd_old[(size_t)node * s.cap_fold + q] : (uint32_t)s.rnn_old[(size_t)node * s.R + (q - nfo)];
+        }
+        ids[p] = id;
+        uint32_t last = (uint32_t)(__ldcg((const unsigned long long *)(s.pool + (size_t)id * s.L + s.L - 1)) >> 32);
+        uint32_t w = s.worst[id];
+        thr[p] = last < w ? last : w;
+      }
+    }
+    __syncthreads();
+    const uint32_t a_tiles = (nn + TILE - 1) / TILE, b_tiles = (ct + TILE - 1) / TILE;
+    const uint32_t kchunks = ((uint32_t)s.stride + KC - 1) / KC;
+    for (uint32_t at = 0; at < a_tiles; ++at) {
+      if (kchunks == 1) load_rows(As, s, ids, at * TILE, nn, 0, (uint32_t)s.stride / 4, tid);
+      for (uint32_t bt = at; bt < b_tiles; ++bt) {
+        float acc[4][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+        for (uint32_t kcn = 0; kcn < kchunks; ++kcn) {
+          const uint32_t kc = kcn * KC;
+          const uint32_t kw4 = (((uint32_t)s.stride - kc) < (uint32_t)KC ? ((uint32_t)s.stride - kc) : (uint32_t)KC) / 4;
+          if (kchunks > 1) load_rows(As, s, ids, at * TILE, nn, kc, kw4, tid);
+          load_rows(Bs, s, ids, bt * TILE, ct, kc, kw4, tid);
+          __syncthreads();
+          for (uint32_t k4 = 0; k4 < kw4; ++k4) {
+            float4 a[4], b[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) a[i] = *reinterpret_cast<const float4 *>(As + (ty + 16 * i) * ROWF + 4 * k4);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) b[j] = *reinterpret_cast<const float4 *>(Bs + (tx + 16 * j) * ROWF + 4 * k4);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                float t;
+                t = a[i].x - b[j].x; acc[i][j] = fmaf(t, t, acc[i][j]);
+                t = a[i].y - b[j].y; acc[i][j] = fmaf(t, t, acc[i][j]);
+                t = a[i].z - b[j].z; acc[i][j] = fmaf(t, t, acc[i][j]);
+                t = a[i].w - b[j].w; acc[i][j] = fmaf(t, t, acc[i][j]);
+              }
+          }
+          __syncthreads();
+        }
+        // ---- offers: bit 2*(4i+j) = to the A member, bit 2*(4i+j)+1 = to the B member
+        uint32_t pend = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint32_t pa = at * TILE + ty + 16 * i, pb = bt * TILE + tx + 16 * j;
+            if (pa < nn && pb < ct && (pb >= nn || pb > pa) && ids[pa] != ids[pb]) {
+              ++my_dist;
+              uint32_t db = __float_as_uint(acc[i][j]);
+              if (db <= thr[pa]) pend |= 1u << (2 * (4 * i + j));
+              if (db <= thr[pb]) pend |= 2u << (2 * (4 * i + j));
+            }
+          }
+        while (__syncthreads_or(pend != 0)) {
+          while (pend) {
+            uint32_t slot = atomicAdd(&sh_qn, 1u);
+            if (slot >= QCAP) break;
+            int bit = __ffs(pend) - 1;
+            pend &= pend - 1;
+            int pr = bit >> 1, i = pr >> 2, j = pr & 3;
+            uint32_t pa = at * TILE + ty + 16 * i, pb = bt * TILE + tx + 16 * j;
+            // register arrays indexed dynamically would spill: select acc[i][j] with a static scan
+            float d = 0.f;
+#pragma unroll
+            for (int ii = 0; ii < 4; ++ii)
+#pragma unroll
+              for (int jj = 0; jj < 4; ++jj)
+                if (ii == i && jj == j) d = acc[ii][jj];
+            Offer o;
+            o.dst = (bit & 1) ? ids[pb] : ids[pa];
+            o.src = (bit & 1) ? ids[pa] : ids[pb];
+            o.dbits = __float_as_uint(d);
+            queue[slot] = o;
+            ++my_offer;
+          }
+          __syncthreads();
+          const uint32_t total = sh_qn < (uint32_t)QCAP ? sh_qn : (uint32_t)QCAP;
+          for (uint32_t e = warp; e < total; e += JT / 32) {
+            Offer o = queue[e];
+            uint64_t key = ((uint64_t)o.dbits << 32) | (o.src << 1) | 1u;
+            bool ok = topl_insert_dispatch(s.pool + (size_t)o.dst * s.L, s.psize + o.dst, s.lock_pool + o.dst, s.L, key,
+                                           true, lane);
+            if (ok && lane == 0) ++my_ins;
+          }
+          __syncthreads();
+          if (tid == 0) sh_qn = 0;
+          __syncthreads();
+        }
+      }
+    }
+    __syncthreads();
+  }
+  if (my_dist) atomicAdd(s.stats + 0, my_dist);
+  if (my_offer) atomicAdd(s.stats + 1, my_offer);
+  if (my_ins) atomicAdd(s.stats + 2, my_ins);
+}
+
+// ---- update (:34-120) ------------------------------------------------------------------------------------
+// phase A (:49-64): M, and the two values `pool.back()` can take for this pool; resets the sample lists
+__global__ void update_a_kernel(State s) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= s.n) return;
+  const uint64_t *pool = s.pool + (size_t)i * s.L;
+  uint32_t psize = s.psize[i];
+  uint32_t maxl = s.M[i] + s.S < psize ? s.M[i] + s.S : psize;
+  uint32_t c = 0, l = 0;
+  while (l < maxl && c < s.S) {
+    if (pool[l] & 1ull) ++c;
+    ++l;
+  }
+  s.M[i] = l;
+  s.worst[i] = (uint32_t)(pool[psize - 1] >> 32);
+  s.leafd[i] = (uint32_t)(pool[s.leaf_rank[psize]] >> 32);
+  s.n_fnew[i] = 0; s.n_fold[i] = 0; s.n_rnew[i] = 0; s.n_rold[i] = 0;
+}
+
+// the reverse lists start empty every iteration
+__global__ void fill_u64_kernel(uint64_t *p, size_t count, uint64_t v) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  for (; i < count; i += (size_t)gridDim.x * blockDim.x) p[i] = v;
+}
+
+// phase B (:66-98): one warp per node; forward lists in pool order, reverse offers through the sorted insert
+__global__ void update_b_kernel(State s, uint32_t seed_new, uint32_t seed_old) {
+  const int lane = threadIdx.x & 31;
+  uint32_t nd = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (nd >= s.n) return;
+  uint64_t *pool = s.pool + (size_t)nd * s.L;
+  const uint32_t M = s.M[nd];
+  uint32_t cnt_new = 0, cnt_old = 0;
+  for (uint32_t base = 0; base < M; base += 32) {
+    uint32_t l = base + lane;
+    bool valid = l < M;
+    uint64_t e = valid ? pool[l] : 0ull;
+    uint32_t id = (uint32_t)e >> 1, db = (uint32_t)(e >> 32);
+    bool isnew = valid && (e & 1ull);
+    bool isold = valid && !(e & 1ull);
+    uint32_t mnew = __ballot_sync(0xffffffffu, isnew), mold = __ballot_sync(0xffffffffu, isold);
+    uint32_t below = (1u << lane) - 1u;
+    if (isnew) {
+      s.fwd_new[(size_t)nd * s.cap_fnew + cnt_new + __popc(mnew & below)] = id;
+      pool[l] = e & ~1ull;
+    }
+    if (isold) {
+      uint32_t slot = cnt_old + __popc(mold & below);
+      if (slot < s.cap_fold) s.fwd_old[(size_t)nd * s.cap_fold + slot] = id;
+    }
+    cnt_new += __popc(mnew);
+    cnt_old += __popc(mold);
+    bool rev = valid && db > (id < nd ? s.leafd[id] : s.worst[id]);
+    uint32_t mrev = __ballot_sync(0xffffffffu, rev);
+    while (mrev) {
+      int src = __ffs(mrev) - 1;
+      mrev &= mrev - 1;
+      uint32_t o = __shfl_sync(0xffffffffu, id, src);
+      bool onew = (mnew >> src) & 1u;
+      uint64_t key = ((uint64_t)seed_hash(onew ? seed_new : seed_old, o, nd) << 32) | nd;
+      if (onew) topl_insert_dispatch(s.rnn_new + (size_t)o * s.R, s.n_rnew + o, s.lock_rnew + o, s.R, key, false, lane);
+      else topl_insert_dispatch(s.rnn_old + (size_t)o * s.R, s.n_rold + o, s.lock_rold + o, s.R, key, false, lane);
+    }
+  }
+  if (lane == 0) {
+    s.n_fnew[nd] = cnt_new;
+    s.n_fold[nd] = cnt_old < s.cap_fold ? cnt_old : s.cap_fold;
+  }
+}
+
+// :275-291: the K best ids (and distances) of every pool
+__global__ void extract_kernel(State s, uint32_t *knn, float *knn_d) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  size_t total = (size_t)s.n * s.K;
+  for (; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    uint32_t node = (uint32_t)(i / s.K), j = (uint32_t)(i % s.K);
+    bool have = j < s.psize[node];
+    uint64_t e = have ? s.pool[(size_t)node * s.L + j] : EMPTY;
+    knn[i] = have ? (uint32_t)e >> 1 : INVALID_ID;
+    if (knn_d) knn_d[i] = have ? __uint_as_float((uint32_t)(e >> 32)) : __int_as_float(0x7f800000);
+  }
+}
+
+}  // namespace nnd
+
+// Host driver. knn [n,K] / knn_d [n,K] are device pointers. info8 = {distance evaluations, offers queued,
+// pool inserts, iterations, join ms, update ms, 0, 0}.
+int nndescent_launch(b200ann_handle *h, const b200ann_index *ix, size_t K, size_t L, size_t iter, size_t S, size_t R,
+                     uint32_t seed, uint32_t *knn, float *knn_d, uint64_t *info8) {
+  using namespace nnd;
+  const size_t n = ix->n;
+  if (ix->metric != B200ANN_L2)
+    return set_err(h, B200ANN_ERR_ARG, "nndescent: the reference NN-descent is L2 only (efanna2e::Index always builds DistanceL2)");
+  if (S < 2 || 2 * S > (size_t)MAX_GEN || S + 1 > L || K > L || K == 0 || R == 0 || L > 512 || R > 512 || n <= 2 * S + 1 ||
+      n >= (1ull << 31))
+    return set_err(h, B200ANN_ERR_ARG, "nndescent: need 2 <= S <= 64, S < L <= 512, 0 < K <= L, 0 < R <= 512, n > 2S+1");
+  cudaStream_t st = h->stream;
+  State s{};
+  s.vec = ix->vec; s.stride = ix->stride; s.n = (uint32_t)n; s.dim = (uint32_t)ix->dim;
+  s.L = (uint32_t)L; s.S = (uint32_t)S; s.R = (uint32_t)R; s.K = (uint32_t)K;
+  s.cap_fnew = (uint32_t)(2 * S);
+  s.cap_fold = (uint32_t)std::min(L, 2 * R);
+  DevBuf<uint64_t> pool, rnew, rold;
+  DevBuf<uint32_t> u32s, fnew, fold, leaf;
+  DevBuf<unsigned long long> stats;
+  CU_CHECK(h, pool.alloc(n * L, st));
+  CU_CHECK(h, rnew.alloc(n * R, st));
+  CU_CHECK(h, rold.alloc(n * R, st));
+  CU_CHECK(h, u32s.alloc(n * 11, st));
+  CU_CHECK(h, fnew.alloc(n * s.cap_fnew, st));
+  CU_CHECK(h, fold.alloc(n * s.cap_fold, st));
+  CU_CHECK(h, leaf.alloc(L + 1, st));
+  CU_CHECK(h, stats.alloc(4, st));
+  s.pool = pool.p; s.rnn_new = rnew.p; s.rnn_old = rold.p;
+  uint32_t *u = u32s.p;
+  s.psize = u; s.M = u + n; s.worst = u + 2 * n; s.leafd = u + 3 * n; s.n_fnew = u + 4 * n; s.n_fold = u + 5 * n;
+  s.n_rnew = u + 6 * n; s.n_rold = u + 7 * n; s.lock_pool = u + 8 * n; s.lock_rnew = u + 9 * n; s.lock_rold = u + 10 * n;
+  s.fwd_new = fnew.p; s.fwd_old = fold.p; s.stats = stats.p;
+  // leaf_rank[p]: sorted rank of the element std::make_heap (the reference's own libstdc++ algorithm,
+  // index_graph.cpp:97) leaves at position p-1 of an ascending array of p distinct values
+  std::vector<uint32_t> lr(L + 1, 0), hp;
+  for (size_t p = 1; p <= L; ++p) {
+    hp.resize(p);
+    for (size_t i = 0; i < p; ++i) hp[i] = (uint32_t)i;
+    std::make_heap(hp.begin(), hp.end());
+    lr[p] = hp[p - 1];
+  }
+  CU_CHECK(h, cudaMemcpyAsync(leaf.p, lr.data(), (L + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+  s.leaf_rank = leaf.p;
+  CU_CHECK(h, cudaMemsetAsync(stats.p, 0, 4 * sizeof(unsigned long long), st));
+  const int TB = 128;
+  const unsigned nb = (unsigned)((n + TB - 1) / TB);
+  init_kernel<<<nb, TB, 0, st>>>(s, seed);
+  h->launches++;
+  const uint32_t cn_max = (uint32_t)(std::max(2 * S, S + R) + 2 * R);
+  const size_t smem = 2 * (size_t)TILE * ROWF * sizeof(float) + QCAP * sizeof(Offer) + 2 * (size_t)cn_max * sizeof(uint32_t);
+  CU_CHECK(h, cudaFuncSetAttribute(join_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 0;
+  CU_CHECK(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, join_kernel, JT, smem));
+  if (occ < 1) return set_err(h, B200ANN_ERR_ARG, "nndescent: sample lists do not fit in shared memory (S, R too large)");
+  const unsigned jgrid = (unsigned)std::min<size_t>((size_t)h->sm_count * occ, n);
+  cudaEvent_t e0, e1, e2;
+  CU_CHECK(h, cudaEventCreate(&e0)); CU_CHECK(h, cudaEventCreate(&e1)); CU_CHECK(h, cudaEventCreate(&e2));
+  float join_ms = 0.f, upd_ms = 0.f;
+  for (size_t it = 0; it < iter; ++it) {
+    cudaMemsetAsync(stats.p + 3, 0, sizeof(unsigned long long), st);
+    cudaEventRecord(e0, st);
+    join_kernel<<<jgrid, JT, smem, st>>>(s, cn_max);
+    cudaEventRecord(e1, st);
+    update_a_kernel<<<nb, TB, 0, st>>>(s);
+    fill_u64_kernel<<<h->sm_count * 8, 256, 0, st>>>(rnew.p, n * R, EMPTY);
+    fill_u64_kernel<<<h->sm_count * 8, 256, 0, st>>>(rold.p, n * R, EMPTY);
+    const uint32_t seed_new = seed + (uint32_t)(2 * it + 1) * 0x9E3779B1U, seed_old = seed + (uint32_t)(2 * it + 2) * 0x9E3779B1U;
+    update_b_kernel<<<(unsigned)((n * 32 + 255) / 256), 256, 0, st>>>(s, seed_new, seed_old);
+    cudaEventRecord(e2, st);
+    h->launches += 5;
+    CU_CHECK(h, cudaEventSynchronize(e2));
+    float a = 0.f, b = 0.f;
+    cudaEventElapsedTime(&a, e0, e1); cudaEventElapsedTime(&b, e1, e2);
+    join_ms += a; upd_ms += b;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
+  extract_kernel<<<h->sm_count * 8, 256, 0, st>>>(s, knn, knn_d);
+  h->launches++;
+  CU_CHECK(h, cudaGetLastError());
+  unsigned long long hs[4];
+  CU_CHECK(h, cudaMemcpyAsync(hs, stats.p, sizeof hs, cudaMemcpyDeviceToHost, st));
+  CU_CHECK(h, cudaStreamSynchronize(st));
+  if (info8) {
+    info8[0] = hs[0]; info8[1] = hs[1]; info8[2] = hs[2]; info8[3] = iter;
+    info8[4] = (uint64_t)(join_ms * 1000.f); info8[5] = (uint64_t)(upd_ms * 1000.f); info8[6] = info8[7] = 0;
+  }
+  return 0;
+}

@@ -85,6 +85,19 @@ int b200ann_bf_knn(b200ann_handle_t h, b200ann_index_t ix, const float *q /*[h|d
  * The exact counterpart of IndexGraph::Build's output (index_graph.cpp:275-292). */
 int b200ann_knn_graph(b200ann_handle_t h, b200ann_index_t ix, size_t K, uint32_t *knn /*[h|d]*/);
 
+/* replaces efanna2e::IndexGraph::Build with the IndexRandom initializer (CNNS/efanna_graph/src/index_graph.cpp:
+ * 265-294: InitializeGraph :175-201, NNDescent :122-136 = iter x {join :22-33, update :34-120}, top-K extraction
+ * :275-291; index_random.cpp:24-27). K, L, iter, S, R are the reference's parameters of the same names. L2 indexes
+ * only (the reference's Index base always constructs DistanceL2, CNNS/src/nsg/index.cpp:8-16).
+ * knn [n,K] = the K best pool entries per node, ascending (distance,id), B200ANN_INVALID past the pool;
+ * dists [n,K] optional. The approximate kNN graph b200ann_nsg_build / IndexNSG::Load_nn_graph consume.
+ * Every phase is computed in an execution-order independent "batch form" (DESIGN.md): rand() -> counter hash of
+ * (seed, node, draw), pools = sets of the L smallest admitted offers, reverse samples = R smallest hashes.
+ * info (optional, 8 x u64): {distance evaluations, offers queued, pool inserts, iterations, join us, update us, 0, 0}.
+ * Needs 2 <= S <= 64, S < L <= 512, K <= L, 0 < R <= 512, n > 2S+1. */
+int b200ann_nndescent(b200ann_handle_t h, b200ann_index_t ix, size_t K, size_t L, size_t iter, size_t S, size_t R,
+                      uint32_t seed, uint32_t *knn /*[h|d]*/, float *dists /*[h|d] or NULL*/, uint64_t *info /*[h]*/);
+
 /* Which kernel b200ann_bf_knn / b200ann_knn_graph run on: 0 = auto (tensor cores when n >= 4096 and
  * nq*n >= 2^24, else fp32 SIMT), 1 = fp32 SIMT tiles (csrc/bf_knn.cu), 2 = tcgen05 tensor cores with fp32
  * re-ranking (csrc/knn_tc.cu). Both give the same bits. slack = extra shortlist entries per row kept by the

@@ -1102,3 +1102,391 @@ EXPORT int orc_merge_topk(const float *d, const uint32_t *ids, size_t parts, siz
   free(tmp);
   return 0;
 }
+
+/* ================================================================== NN-descent (efanna_graph IndexGraph) */
+/* std::mt19937 (the generator behind GenRandom's callers: index_graph.cpp:124,181; index_random.h:19).
+ * Standard MT19937: seeding x[i] = 1812433253 * (x[i-1] ^ (x[i-1] >> 30)) + i, tempering 11/7/15/18. */
+typedef struct { uint32_t mt[624]; int idx; } orc_mt;
+static void mt_seed(orc_mt *m, uint32_t s) {
+  m->mt[0] = s;
+  for (int i = 1; i < 624; i++) m->mt[i] = 1812433253U * (m->mt[i - 1] ^ (m->mt[i - 1] >> 30)) + (uint32_t)i;
+  m->idx = 624;
+}
+static uint32_t mt_next(void *st) {
+  orc_mt *m = (orc_mt *)st;
+  if (m->idx >= 624) {
+    for (int i = 0; i < 624; i++) {
+      uint32_t y = (m->mt[i] & 0x80000000U) | (m->mt[(i + 1) % 624] & 0x7fffffffU);
+      m->mt[i] = m->mt[(i + 397) % 624] ^ (y >> 1) ^ ((y & 1U) ? 0x9908b0dfU : 0U);
+    }
+    m->idx = 0;
+  }
+  uint32_t y = m->mt[m->idx++];
+  y ^= y >> 11; y ^= (y << 7) & 0x9d2c5680U; y ^= (y << 15) & 0xefc60000U; y ^= y >> 18;
+  return y;
+}
+EXPORT void orc_mt19937(uint32_t seed, uint32_t *out, size_t count) {
+  orc_mt m; mt_seed(&m, seed);
+  for (size_t i = 0; i < count; i++) out[i] = mt_next(&m);
+}
+/* the product's stateless stream: draw c of stream (seed, node) = orc_seed_hash(seed, node, c) */
+typedef struct { uint32_t seed, node, ctr; } orc_hs;
+static uint32_t hs_next(void *st) {
+  orc_hs *s = (orc_hs *)st;
+  return orc_seed_hash(s->seed, s->node, s->ctr++);
+}
+static int u32_cmp(const void *a, const void *b) {
+  uint32_t x = *(const uint32_t *)a, y = *(const uint32_t *)b;
+  return x < y ? -1 : (x > y ? 1 : 0);
+}
+/* efanna2e::GenRandom (efanna_graph/include/efanna2e/util.h:17-31): `size` distinct ids in [0,N) */
+static void gen_random(uint32_t (*next)(void *), void *st, uint32_t *addr, unsigned size, unsigned N) {
+  for (unsigned i = 0; i < size; ++i) addr[i] = next(st) % (N - size);
+  qsort(addr, size, sizeof(uint32_t), u32_cmp);
+  for (unsigned i = 1; i < size; ++i)
+    if (addr[i] <= addr[i - 1]) addr[i] = addr[i - 1] + 1;
+  unsigned off = next(st) % N;
+  for (unsigned i = 0; i < size; ++i) addr[i] = (addr[i] + off) % N;
+}
+EXPORT void orc_gen_random(int rng, uint32_t seed, uint32_t node, uint32_t *addr, unsigned size, unsigned N) {
+  if (rng == 0) { orc_mt m; mt_seed(&m, seed); gen_random(mt_next, &m, addr, size, N); }
+  else { orc_hs s = {seed, node, 0}; gen_random(hs_next, &s, addr, size, N); }
+}
+
+/* libstdc++ heap algorithms over Neighbor with operator< = distance only (neighbor.h:26-28), restated
+ * (bits/stl_heap.h __push_heap / __adjust_heap / make_heap / pop_heap): the element order inside the
+ * heap decides what `pool.back()` is in IndexGraph::update (index_graph.cpp:74,88). */
+static void std_push_heap_(orc_nb *f, long hole, long top, orc_nb v) {
+  long parent = (hole - 1) / 2;
+  while (hole > top && f[parent].distance < v.distance) {
+    f[hole] = f[parent]; hole = parent; parent = (hole - 1) / 2;
+  }
+  f[hole] = v;
+}
+static void std_adjust_heap(orc_nb *f, long hole, long len, orc_nb v) {
+  long top = hole, child = hole;
+  while (child < (len - 1) / 2) {
+    child = 2 * (child + 1);
+    if (f[child].distance < f[child - 1].distance) child--;
+    f[hole] = f[child]; hole = child;
+  }
+  if ((len & 1) == 0 && child == (len - 2) / 2) {
+    child = 2 * (child + 1);
+    f[hole] = f[child - 1]; hole = child - 1;
+  }
+  std_push_heap_(f, hole, top, v);
+}
+static void std_make_heap(orc_nb *f, long len) {
+  if (len < 2) return;
+  for (long parent = (len - 2) / 2;; parent--) {
+    orc_nb v = f[parent];
+    std_adjust_heap(f, parent, len, v);
+    if (parent == 0) return;
+  }
+}
+static void std_push_heap(orc_nb *f, long len) { orc_nb v = f[len - 1]; std_push_heap_(f, len - 1, 0, v); }
+static void std_pop_heap(orc_nb *f, long len) {
+  if (len < 2) return;
+  orc_nb v = f[len - 1];
+  f[len - 1] = f[0];
+  std_adjust_heap(f, 0, len - 1, v);
+}
+
+/* efanna2e::nhood (efanna_graph/include/efanna2e/neighbor.h:32-88) with flat storage */
+typedef struct {
+  orc_nb *pool; unsigned psize;           /* capacity L */
+  unsigned M;
+  uint32_t *nn_new, *nn_old, *rnn_new, *rnn_old;
+  unsigned n_new, n_old, n_rnew, n_rold;
+} orc_hood;
+
+/* nhood::insert (neighbor.h:57-72), statement for statement (the mutex is dropped: single thread) */
+static void hood_insert(orc_hood *h, unsigned L, uint32_t id, float dist, uint64_t *n_ins) {
+  if (dist > h->pool[0].distance) return;
+  for (unsigned i = 0; i < h->psize; i++)
+    if (id == h->pool[i].id) return;
+  orc_nb nn = {id, dist, 1};
+  if (h->psize < L) {
+    h->pool[h->psize++] = nn;
+    std_push_heap(h->pool, h->psize);
+  } else {
+    std_pop_heap(h->pool, h->psize);
+    h->pool[h->psize - 1] = nn;
+    std_push_heap(h->pool, h->psize);
+  }
+  if (n_ins) (*n_ins)++;
+}
+
+/* IndexGraph::Build (index_graph.cpp:265-294) = InitializeGraph (:175-201) + NNDescent (:122-136: iter x
+ * {join :22-33, update :34-120}) + top-K extraction, with the IndexRandom initializer
+ * (index_random.cpp:24-27), executed as ONE thread (OMP_NUM_THREADS=1 is the only reproducible
+ * schedule of the reference) and consuming libc rand() exactly where the reference does
+ * (:181 mt19937 seed, :124 mt19937 seed, :81/:92 reservoir slot). IndexRandom's own generator is a
+ * default-constructed std::mt19937 (seed 5489, index_random.h:19).
+ * std::sort on equal distances is unspecified: ordered by id here (pinning data has no ties).
+ * knn [n,K]; info (optional) [4] = {distance evaluations, pool insertions, 0, 0}. */
+EXPORT int orc_nndescent_ref(const float *data, size_t n, size_t dim, size_t stride, unsigned K, unsigned L,
+                             unsigned iter, unsigned S, unsigned R, int mode, uint32_t *knn, uint64_t *info) {
+  if (n <= 2 * S || n <= 100 || S + 1 > L || K > L || R == 0) return -1;
+  unsigned cap_new = (2 * S > S + R ? 2 * S : S + R), cap_old = L + R;
+  orc_hood *g = (orc_hood *)calloc(n, sizeof(orc_hood));
+  uint64_t n_dist = 0, n_ins = 0;
+  orc_mt rng; mt_seed(&rng, (uint32_t)rand());                 /* :181 */
+  for (size_t i = 0; i < n; i++) {                               /* :182-184, nhood ctor neighbor.h:41-47 */
+    orc_hood *h = &g[i];
+    h->pool = (orc_nb *)malloc(sizeof(orc_nb) * L);
+    h->nn_new = (uint32_t *)malloc(sizeof(uint32_t) * cap_new);
+    h->nn_old = (uint32_t *)malloc(sizeof(uint32_t) * cap_old);
+    h->rnn_new = (uint32_t *)malloc(sizeof(uint32_t) * R);
+    h->rnn_old = (uint32_t *)malloc(sizeof(uint32_t) * R);
+    h->M = S;
+    h->n_new = 2 * S;
+    gen_random(mt_next, &rng, h->nn_new, 2 * S, (unsigned)n);
+  }
+  orc_mt init_rng; mt_seed(&init_rng, 5489U);
+  uint32_t *tmp = (uint32_t *)malloc(sizeof(uint32_t) * (S + 1));
+  for (size_t i = 0; i < n; i++) {                               /* :185-200 */
+    gen_random(mt_next, &init_rng, tmp, S + 1, (unsigned)n);     /* IndexRandom::Search */
+    orc_hood *h = &g[i];
+    for (unsigned j = 0; j < S; j++) {
+      uint32_t id = tmp[j];
+      if (id == i) continue;
+      float d = orc_dist(mode, data + i * stride, data + (size_t)id * stride, dim);
+      n_dist++;
+      orc_nb nn = {id, d, 1};
+      h->pool[h->psize++] = nn;
+    }
+    std_make_heap(h->pool, h->psize);
+  }
+  free(tmp);
+  { /* NNDescent :124-128: seeds a second generator and draws the control points (not used by the result) */
+    orc_mt crng; mt_seed(&crng, (uint32_t)rand());
+    uint32_t ctrl[100];
+    gen_random(mt_next, &crng, ctrl, 100, (unsigned)n);
+  }
+  for (unsigned it = 0; it < iter; it++) {
+    /* ---- join (:22-33, nhood::join neighbor.h:74-87) */
+    for (size_t nd = 0; nd < n; nd++) {
+      orc_hood *h = &g[nd];
+      for (unsigned a = 0; a < h->n_new; a++) {
+        uint32_t i = h->nn_new[a];
+        for (unsigned b = 0; b < h->n_new + h->n_old; b++) {
+          uint32_t j = b < h->n_new ? h->nn_new[b] : h->nn_old[b - h->n_new];
+          if (b < h->n_new && !(i < j)) continue;
+          if (i == j) continue;
+          float d = orc_dist(mode, data + (size_t)i * stride, data + (size_t)j * stride, dim);
+          n_dist++;
+          hood_insert(&g[i], L, j, d, &n_ins);
+          hood_insert(&g[j], L, i, d, &n_ins);
+        }
+      }
+    }
+    /* ---- update (:34-120) */
+    for (size_t i = 0; i < n; i++) g[i].n_new = g[i].n_old = 0;  /* :38-47 */
+    for (size_t nd = 0; nd < n; nd++) {                          /* :49-64 */
+      orc_hood *nn = &g[nd];
+      qsort(nn->pool, nn->psize, sizeof(orc_nb), nb_cmp);
+      if (nn->psize > L) nn->psize = L;
+      unsigned maxl = nn->M + S < nn->psize ? nn->M + S : nn->psize;
+      unsigned c = 0, l = 0;
+      while (l < maxl && c < S) {
+        if (nn->pool[l].flag) ++c;
+        ++l;
+      }
+      nn->M = l;
+    }
+    for (size_t nd = 0; nd < n; nd++) {                          /* :66-98 */
+      orc_hood *h = &g[nd];
+      for (unsigned l = 0; l < h->M; ++l) {
+        orc_nb *nn = &h->pool[l];
+        orc_hood *o = &g[nn->id];
+        if (nn->flag) {
+          h->nn_new[h->n_new++] = nn->id;
+          if (nn->distance > o->pool[o->psize - 1].distance) {
+            if (o->n_rnew < R) o->rnn_new[o->n_rnew++] = (uint32_t)nd;
+            else o->rnn_new[(unsigned)rand() % R] = (uint32_t)nd;
+          }
+          nn->flag = 0;
+        } else {
+          h->nn_old[h->n_old++] = nn->id;
+          if (nn->distance > o->pool[o->psize - 1].distance) {
+            if (o->n_rold < R) o->rnn_old[o->n_rold++] = (uint32_t)nd;
+            else o->rnn_old[(unsigned)rand() % R] = (uint32_t)nd;
+          }
+        }
+      }
+      std_make_heap(h->pool, h->psize);
+    }
+    for (size_t i = 0; i < n; i++) {                             /* :100-119 (the shuffles never trigger: size <= R) */
+      orc_hood *h = &g[i];
+      memcpy(h->nn_new + h->n_new, h->rnn_new, sizeof(uint32_t) * h->n_rnew); h->n_new += h->n_rnew;
+      memcpy(h->nn_old + h->n_old, h->rnn_old, sizeof(uint32_t) * h->n_rold); h->n_old += h->n_rold;
+      if (h->n_old > R * 2) h->n_old = R * 2;
+      h->n_rnew = h->n_rold = 0;
+    }
+  }
+  int rc = 0;
+  for (size_t i = 0; i < n; i++) {                               /* :275-291 */
+    orc_hood *h = &g[i];
+    qsort(h->pool, h->psize, sizeof(orc_nb), nb_cmp);
+    for (unsigned j = 0; j < K; j++) {
+      if (j < h->psize) knn[i * K + j] = h->pool[j].id;
+      else { knn[i * K + j] = ORC_INVALID; rc = 1; }             /* the reference reads past the pool here */
+    }
+  }
+  for (size_t i = 0; i < n; i++) { free(g[i].pool); free(g[i].nn_new); free(g[i].nn_old); free(g[i].rnn_new); free(g[i].rnn_old); }
+  free(g);
+  if (info) { info[0] = n_dist; info[1] = n_ins; info[2] = info[3] = 0; }
+  return rc;
+}
+
+/* ---- NN-descent, batch form: what the CUDA path (csrc/nndescent.cu) computes, restated serially.
+ * Same phases, sizes and sampling rules as IndexGraph::Build above, made independent of execution order:
+ *  - a pool is the sorted list of the <= L smallest keys (distance bits << 32 | id << 1 | flag) it has been
+ *    offered, deduplicated by id, where an offer is admitted only if distance <= the pool's largest distance
+ *    at the start of the join (nhood::insert's `dist > pool.front().distance` test, neighbor.h:59, evaluated
+ *    against the join's starting state: the heap top never grows during a join). A set function of the offers.
+ *  - the reverse lists keep, per node, the R offers with the smallest (hash(seed_it, node, source), source)
+ *    instead of "first R, then overwrite slot rand() % R" (index_graph.cpp:78-82,89-94);
+ *  - `pool.back()` (:76,:88): in the reference's one-thread schedule node nd reads the pool of node o while it
+ *    is still sorted when o > nd (back() = largest distance) and after std::make_heap (:97) when o < nd
+ *    (back() = the heap's last leaf). With distinct distances the sorted rank of that leaf depends only on the
+ *    pool size p: leaf_rank[p], computed by heapifying 0..p-1. The batch form uses exactly that rule, which
+ *    depends on ids and not on execution order (measured: comparing against the largest distance everywhere
+ *    loses 0.04 recall on uniform 32-d data at matched parameters);
+ *  - GenRandom draws from the stateless stream orc_seed_hash(seed, node, draw) instead of a shared mt19937.
+ * knn [n,K] (ORC_INVALID past the pool), knn_d [n,K] or NULL, info [4] = {distance evaluations, offers that
+ * passed the static test, 0, 0}. */
+typedef struct {
+  uint64_t *pool; unsigned psize, M;
+  uint32_t *fwd_new, *fwd_old; unsigned n_fnew, n_fold;
+  uint64_t *rnn_new, *rnn_old; unsigned n_rnew, n_rold;
+} orc_bhood;
+static uint32_t f2u(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
+static float u2f(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
+/* keep the `cap` smallest keys, sorted ascending; dedup on (low word >> 1) when dedup != 0. returns 1 if inserted */
+static int topl_insert(uint64_t *list, unsigned *size, unsigned cap, uint64_t key, int dedup) {
+  unsigned sz = *size, pos = 0;
+  uint32_t id = (uint32_t)key >> 1;
+  for (unsigned i = 0; i < sz; i++) {
+    if (dedup && ((uint32_t)list[i] >> 1) == id) return 0;
+    if (list[i] < key) pos++;
+  }
+  if (pos >= cap) return 0;
+  unsigned last = sz < cap ? sz : cap - 1;
+  for (unsigned i = last; i > pos; i--) list[i] = list[i - 1];
+  list[pos] = key;
+  if (sz < cap) *size = sz + 1;
+  return 1;
+}
+#define NND_SEED_POOL 0x68E31DA4U
+EXPORT int orc_nndescent_batch(const float *data, size_t n, size_t dim, size_t stride, unsigned K, unsigned L,
+                               unsigned iter, unsigned S, unsigned R, uint32_t seed, int mode, uint32_t *knn,
+                               float *knn_d, uint64_t *info) {
+  if (n <= 2 * S + 1 || S + 1 > L || K > L || R == 0 || S == 0 || n >= (1u << 31)) return -1;
+  orc_bhood *g = (orc_bhood *)calloc(n, sizeof(orc_bhood));
+  uint32_t *oldmax = (uint32_t *)malloc(sizeof(uint32_t) * n);
+  unsigned cap_new = (2 * S > S + R ? 2 * S : S + R), cap_old = 2 * R;
+  uint32_t *lst = (uint32_t *)malloc(sizeof(uint32_t) * (cap_new + L + R));
+  uint32_t *tmp = (uint32_t *)malloc(sizeof(uint32_t) * (S + 1));
+  uint64_t n_dist = 0, n_offer = 0;
+  /* leaf_rank[p]: sorted rank of the element std::make_heap leaves at position p-1 of an ascending array */
+  unsigned *leaf_rank = (unsigned *)calloc(L + 1, sizeof(unsigned));
+  uint32_t *leafd = (uint32_t *)malloc(sizeof(uint32_t) * n);
+  {
+    orc_nb *hp = (orc_nb *)malloc(sizeof(orc_nb) * (L + 1));
+    for (unsigned p = 1; p <= L; p++) {
+      for (unsigned i = 0; i < p; i++) { hp[i].id = i; hp[i].distance = (float)i; hp[i].flag = 0; }
+      std_make_heap(hp, p);
+      leaf_rank[p] = hp[p - 1].id;
+    }
+    free(hp);
+  }
+  for (size_t i = 0; i < n; i++) {
+    orc_bhood *h = &g[i];
+    h->pool = (uint64_t *)malloc(sizeof(uint64_t) * L);
+    h->fwd_new = (uint32_t *)malloc(sizeof(uint32_t) * 2 * S);
+    h->fwd_old = (uint32_t *)malloc(sizeof(uint32_t) * L);
+    h->rnn_new = (uint64_t *)malloc(sizeof(uint64_t) * R);
+    h->rnn_old = (uint64_t *)malloc(sizeof(uint64_t) * R);
+    h->M = S;
+    orc_hs s1 = {seed, (uint32_t)i, 0};
+    gen_random(hs_next, &s1, h->fwd_new, 2 * S, (unsigned)n);    /* nhood ctor, neighbor.h:41-47 */
+    h->n_fnew = 2 * S;
+    orc_hs s2 = {seed ^ NND_SEED_POOL, (uint32_t)i, 0};
+    gen_random(hs_next, &s2, tmp, S + 1, (unsigned)n);           /* IndexRandom::Search, :189 */
+    for (unsigned j = 0; j < S; j++) {
+      if (tmp[j] == i) continue;
+      float d = orc_dist(mode, data + i * stride, data + (size_t)tmp[j] * stride, dim);
+      n_dist++;
+      topl_insert(h->pool, &h->psize, L, ((uint64_t)f2u(d) << 32) | (tmp[j] << 1) | 1u, 1);
+    }
+  }
+  for (unsigned it = 0; it < iter; it++) {
+    for (size_t i = 0; i < n; i++) oldmax[i] = (uint32_t)(g[i].pool[g[i].psize - 1] >> 32);
+    /* ---- join */
+    for (size_t nd = 0; nd < n; nd++) {
+      orc_bhood *h = &g[nd];
+      unsigned nn = 0, no = 0;
+      for (unsigned a = 0; a < h->n_fnew; a++) lst[nn++] = h->fwd_new[a];
+      for (unsigned a = 0; a < h->n_rnew; a++) lst[nn++] = (uint32_t)h->rnn_new[a];
+      for (unsigned a = 0; a < h->n_fold && no < cap_old; a++) lst[nn + no++] = h->fwd_old[a];
+      for (unsigned a = 0; a < h->n_rold && no < cap_old; a++) lst[nn + no++] = (uint32_t)h->rnn_old[a];
+      for (unsigned a = 0; a < nn; a++)
+        for (unsigned b = 0; b < nn + no; b++) {
+          if (b < nn && b <= a) continue;                        /* each unordered new x new pair once */
+          uint32_t i = lst[a], j = lst[b];
+          if (i == j) continue;
+          float d = orc_dist(mode, data + (size_t)i * stride, data + (size_t)j * stride, dim);
+          n_dist++;
+          uint32_t db = f2u(d);
+          if (db <= oldmax[i]) { n_offer++; topl_insert(g[i].pool, &g[i].psize, L, ((uint64_t)db << 32) | (j << 1) | 1u, 1); }
+          if (db <= oldmax[j]) { n_offer++; topl_insert(g[j].pool, &g[j].psize, L, ((uint64_t)db << 32) | (i << 1) | 1u, 1); }
+        }
+    }
+    /* ---- update */
+    for (size_t nd = 0; nd < n; nd++) {
+      orc_bhood *h = &g[nd];
+      unsigned maxl = h->M + S < h->psize ? h->M + S : h->psize, c = 0, l = 0;
+      while (l < maxl && c < S) { if (h->pool[l] & 1u) ++c; ++l; }
+      h->M = l;
+      oldmax[nd] = (uint32_t)(h->pool[h->psize - 1] >> 32);      /* pool.back() of a sorted pool */
+      leafd[nd] = (uint32_t)(h->pool[leaf_rank[h->psize]] >> 32); /* pool.back() of a heapified pool */
+      h->n_fnew = h->n_fold = h->n_rnew = h->n_rold = 0;
+    }
+    uint32_t seed_new = seed + (2 * it + 1) * 0x9E3779B1U, seed_old = seed + (2 * it + 2) * 0x9E3779B1U;
+    for (size_t nd = 0; nd < n; nd++) {
+      orc_bhood *h = &g[nd];
+      for (unsigned l = 0; l < h->M; l++) {
+        uint64_t e = h->pool[l];
+        uint32_t id = (uint32_t)e >> 1, db = (uint32_t)(e >> 32);
+        orc_bhood *o = &g[id];
+        if (e & 1u) {
+          h->fwd_new[h->n_fnew++] = id;
+          if (db > (id < nd ? leafd[id] : oldmax[id]))
+            topl_insert(o->rnn_new, &o->n_rnew, R, ((uint64_t)orc_seed_hash(seed_new, id, (uint32_t)nd) << 32) | nd, 0);
+          h->pool[l] = e & ~(uint64_t)1;
+        } else {
+          h->fwd_old[h->n_fold++] = id;
+          if (db > (id < nd ? leafd[id] : oldmax[id]))
+            topl_insert(o->rnn_old, &o->n_rold, R, ((uint64_t)orc_seed_hash(seed_old, id, (uint32_t)nd) << 32) | nd, 0);
+        }
+      }
+    }
+  }
+  int rc = 0;
+  for (size_t i = 0; i < n; i++)
+    for (unsigned j = 0; j < K; j++) {
+      if (j < g[i].psize) {
+        knn[i * K + j] = (uint32_t)g[i].pool[j] >> 1;
+        if (knn_d) knn_d[i * K + j] = u2f((uint32_t)(g[i].pool[j] >> 32));
+      } else {
+        knn[i * K + j] = ORC_INVALID; rc = 1;
+        if (knn_d) knn_d[i * K + j] = INFINITY;
+      }
+    }
+  for (size_t i = 0; i < n; i++) { free(g[i].pool); free(g[i].fwd_new); free(g[i].fwd_old); free(g[i].rnn_new); free(g[i].rnn_old); }
+  free(g); free(oldmax); free(lst); free(tmp); free(leaf_rank); free(leafd);
+  if (info) { info[0] = n_dist; info[1] = n_offer; info[2] = info[3] = 0; }
+  return rc;
+}

@@ -71,6 +71,12 @@ def oracle():
                                           C.c_size_t, C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_int, C.c_uint32,
                                           u32p, C.c_void_p, C.c_void_p, C.c_void_p]
         lib.orc_merge_topk.argtypes = [f32p, u32p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, f32p, u32p]
+        lib.orc_mt19937.argtypes = [C.c_uint32, u32p, C.c_size_t]
+        lib.orc_gen_random.argtypes = [C.c_int, C.c_uint32, C.c_uint32, u32p, C.c_uint, C.c_uint]
+        lib.orc_nndescent_ref.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_uint, C.c_uint, C.c_uint,
+                                          C.c_uint, C.c_uint, C.c_int, u32p, C.c_void_p]
+        lib.orc_nndescent_batch.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_uint, C.c_uint, C.c_uint,
+                                            C.c_uint, C.c_uint, C.c_uint32, C.c_int, u32p, C.c_void_p, C.c_void_p]
         _oracle = lib
     return _oracle
 
@@ -194,6 +200,28 @@ def orc_nsg_tree_grow(base, graph, ep, L, mode, width_in, rng_mode=1, seed=0):
     w = C.c_uint(0)
     added = oracle().orc_nsg_tree_grow(base, n, dim, dim, g, g.shape[1], ep, L, mode, rng_mode, seed, width_in, C.byref(w))
     return g, int(added), w.value
+
+
+def orc_nndescent_ref(base, K, L, it, S, R_, mode, seed=1):
+    """IndexGraph::Build restated statement for statement (one thread, libc rand() seeded with `seed`)."""
+    n, dim = base.shape
+    libc().srand(seed)
+    knn = np.zeros((n, K), np.uint32)
+    info = np.zeros(4, np.uint64)
+    rc = oracle().orc_nndescent_ref(base, n, dim, dim, K, L, it, S, R_, mode, knn, _vp(info))
+    assert rc >= 0
+    return knn, info
+
+
+def orc_nndescent_batch(base, K, L, it, S, R_, mode, seed=1):
+    """the order-independent batch form the CUDA path computes; returns ids, distances, info."""
+    n, dim = base.shape
+    knn = np.zeros((n, K), np.uint32)
+    d = np.zeros((n, K), np.float32)
+    info = np.zeros(4, np.uint64)
+    rc = oracle().orc_nndescent_batch(base, n, dim, dim, K, L, it, S, R_, seed, mode, knn, _vp(d), _vp(info))
+    assert rc >= 0
+    return knn, d, info
 
 
 def orc_merge_topk(d, ids, kout):

@@ -346,7 +346,7 @@ def test_hybrid_search_vs_reference_and_oracle(B, H, tmp_path):
     no rand() seed fill is involved (all summation orders are exact on this data)."""
     n, dim = 5000, 64
     base = R.data_sift_like(n, dim, 1)
-    q = R.data_sift_like(150, dim, 2)
+    q = R.data_sift_like(1000, dim, 2)              # 1000 queries x 8 seeds: seed-to-seed recall noise < 0.002
     knn = _exact_knn(base, 32)
     kp, prefix = str(tmp_path / "k.graph"), str(tmp_path / "hy")
     R.write_knn_graph(kp, knn)
@@ -369,9 +369,9 @@ def test_hybrid_search_vs_reference_and_oracle(B, H, tmp_path):
         hy = R.RefHybrid(base, prefix, L)
         rids = hy.search(q, 10, K, seed=3)               # ef = K -> max(k, ef) = K ids per query
         # both sides fill the pool with pseudo-random ids (rand() there, a counter hash here): compare the
-        # recall averaged over 5 seeds each so that the 0.005 bar is not inside the seed-to-seed noise
-        rec_g = np.mean([R.recall(ix.hybrid_search(q, K, L, seed=s)[0][:, :10], truth) for s in range(9, 14)])
-        rec_r = np.mean([R.recall(hy.search(q, 10, K, seed=s)[:, :10], truth) for s in range(3, 8)])
+        # recall averaged over 8 seeds each so that the 0.005 bar is not inside the seed-to-seed noise
+        rec_g = np.mean([R.recall(ix.hybrid_search(q, K, L, seed=s)[0][:, :10], truth) for s in range(9, 17)])
+        rec_r = np.mean([R.recall(hy.search(q, 10, K, seed=s)[:, :10], truth) for s in range(3, 11)])
         assert abs(rec_g - rec_r) <= 0.005, (K, L, rec_g, rec_r)  # north_star: recall within 0.005 at matched L
         # same distance lists wherever the rand() fill was not needed (ties may permute equal-distance ids)
         rd = ((base[rids.astype(np.int64)] - q[:, None, :]) ** 2).sum(2).astype(np.float32)

@@ -310,3 +310,76 @@ def test_search_from_enterpoint_vs_reference(hybrid_case):
     ctypes.CDLL(None).srand(9)
     oids, _ = R.orc_nsg_search_from(base, g, entry, q, 10, 30, R.L2_HYBRID_AVX, rng_mode=0)
     assert (rids == oids).all()
+
+
+# ---------------------------------------------------------------- NN-descent (IndexGraph::Build)
+def test_mt19937_known_answer():
+    """std::mt19937 default seed: the 10000th draw is 4123659995 (the C++ standard's own check value)."""
+    out = np.zeros(10000, np.uint32)
+    R.oracle().orc_mt19937(5489, out, 10000)
+    assert int(out[0]) == 3499211612 and int(out[-1]) == 4123659995
+
+
+def test_gen_random_properties():
+    """GenRandom (util.h:17-31): `size` distinct ids below N, for both generators."""
+    for rng in (0, 1):
+        for size, N in ((16, 100), (21, 22), (64, 5000)):
+            a = np.zeros(size, np.uint32)
+            R.oracle().orc_gen_random(rng, 7, 3, a, size, N)
+            assert len(set(a.tolist())) == size and a.max() < N
+
+
+@needs_ref
+@pytest.mark.parametrize("n,dim,K,L,it,S,Rr,seed", [(2000, 32, 20, 30, 4, 5, 10, 3), (3000, 24, 10, 40, 6, 10, 20, 5),
+                                                   (1500, 16, 30, 30, 3, 8, 4, 7), (1200, 40, 5, 16, 0, 6, 6, 2)])
+def test_nndescent_ref_form_vs_reference(tmp_path, n, dim, K, L, it, S, Rr, seed):
+    """orc_nndescent_ref == the UNMODIFIED IndexGraph::Build + IndexRandom run with one OpenMP thread under
+    srand(seed), graph for graph (float data: no distance ties, so std::sort's tie order does not matter).
+    Pins mt19937, GenRandom, libstdc++'s heap layout (pool.back()), the join/update order and rand() use."""
+    base = R.data_uniform(n, dim, seed)
+    ref = R.ref_nndescent(base, K, L, it, S, Rr, str(tmp_path / "g"), seed=seed, threads=1)
+    got, info = R.orc_nndescent_ref(base, K, L, it, S, Rr, R.L2_EFANNA_AVX, seed=seed)
+    assert (got == ref).all()
+    assert info[0] > 0
+
+
+def _knn_recall(knn, truth):
+    K = knn.shape[1]
+    return float(np.mean([len(set(knn[i].tolist()) & set(truth[i].tolist())) / K for i in range(len(knn))]))
+
+
+@needs_ref
+@pytest.mark.parametrize("n,dim,K,L,it,S,Rr,kind", [(5000, 32, 20, 40, 6, 8, 20, "u"), (4000, 64, 20, 40, 5, 8, 20, "s")])
+def test_nndescent_batch_form_recall_vs_reference(tmp_path, n, dim, K, L, it, S, Rr, kind):
+    """the batch form (what the GPU computes) reaches the reference's graph quality at matched K/L/iter/S/R:
+    recall of the K-NN lists against the exact graph within 0.005 (north_star bar), averaged over 3 seeds."""
+    base = R.data_uniform(n, dim, 1) if kind == "u" else R.data_sift_like(n, dim, 1)
+    oid, _ = R.orc_bf_knn(base, base, K + 1, R.L2_SCALAR)
+    truth = np.stack([row[row != i][:K] for i, row in enumerate(oid)])
+    rr = np.mean([_knn_recall(R.ref_nndescent(base, K, L, it, S, Rr, str(tmp_path / "g"), seed=s, threads=1), truth)
+                  for s in (1, 2, 3)])
+    rb = np.mean([_knn_recall(R.orc_nndescent_batch(base, K, L, it, S, Rr, R.L2_SEQ_FMA, seed=s)[0], truth)
+                  for s in (1, 2, 3)])
+    assert rb >= rr - 0.005, (rb, rr)
+    assert abs(rb - rr) < 0.02
+
+
+def test_nndescent_batch_form_properties():
+    """rows sorted by (distance, id), no self, no duplicates, distances = the oracle's own distance of the pair;
+    iter=0 returns the initial random pools; more iterations never make a row worse."""
+    n, dim, K, L, S, Rr = 1500, 16, 12, 24, 6, 10
+    base = R.data_uniform(n, dim, 4)
+    prev = None
+    for it in (0, 1, 3):
+        knn, d, info = R.orc_nndescent_batch(base, K, L, it, S, Rr, R.L2_SEQ_FMA, seed=5)
+        for i in range(0, n, 97):
+            row = knn[i][knn[i] != R.INVALID]
+            assert i not in row and len(set(row.tolist())) == len(row)
+            dd = d[i][:len(row)]
+            assert (np.diff(dd) >= 0).all()
+            for j, v in enumerate(row[:3]):
+                assert dd[j] == R.oracle().orc_dist(R.L2_SEQ_FMA, base[i], base[v], dim)
+        if prev is not None:
+            both = (knn[:, S - 2] != R.INVALID) & (prev[0][:, S - 2] != R.INVALID)
+            assert (d[both, S - 2] <= prev[1][both, S - 2]).all()
+        prev = (knn, d)

@@ -164,23 +164,197 @@ constexpr int JT = 256;          // threads per CTA
 constexpr int TILE = 64;         // pairs tile TILE x TILE, 4 x 4 per thread
 constexpr int KC = 128;          // floats of the dimension staged per pass
 constexpr int ROWF = KC + 4;     // padded shared-memory row (bank shift of 4 per row, 16-byte aligned)
-constexpr int QCAP = 2048;       // offer queue entries per CTA
-
-struct Offer { uint32_t dst, src, dbits; };
+constexpr int DROW = TILE + 1;   // padded row of the tile's distance matrix (conflict-free column reads)
+constexpr uint32_t NO_PAIR = 0x7f800000u;  // +inf: never <= a threshold (thresholds are finite)
 
 __device__ __forceinline__ void load_rows(float *sm, const State &s, const uint32_t *ids, uint32_t pos0, uint32_t limit,
                                           uint32_t kc, uint32_t kw4, int tid) {
-  // TILE rows x kw4 float4; one warp covers one row's 32 float4 (512 contiguous bytes)
+  // rows pos0 .. min(pos0 + TILE, limit): a warp covers one row's float4s (512 contiguous bytes at KC = 128),
+  // four rows per warp in flight. Rows past `limit` are never read by a pair that counts.
   const int warp = tid >> 5, lane = tid & 31;
-  for (int r = warp; r < TILE; r += JT / 32) {
-    uint32_t pos = pos0 + r;
-    float4 *dst = reinterpret_cast<float4 *>(sm + r * ROWF);
-    if (pos < limit) {
-      const float4 *src = reinterpret_cast<const float4 *>(s.vec + (size_t)ids[pos] * s.stride + kc);
-      for (uint32_t c = lane; c < kw4; c += 32) dst[c] = __ldg(src + c);
-    } else {
-      for (uint32_t c = lane; c < kw4; c += 32) dst[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+  const int rows = (int)(limit > pos0 ? (limit - pos0 < (uint32_t)TILE ? limit - pos0 : (uint32_t)TILE) : 0u);
+  for (int r0 = warp * 4; r0 < rows; r0 += (JT / 32) * 4) {
+    for (uint32_t c = lane; c < kw4; c += 32) {
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (r0 + u < rows)
+          v[u] = __ldg(reinterpret_cast<const float4 *>(s.vec + (size_t)ids[pos0 + r0 + u] * s.stride + kc) + c);
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (r0 + u < rows) reinterpret_cast<float4 *>(sm + (r0 + u) * ROWF)[c] = v[u];
     }
+  }
+}
+
+#ifdef NND_PROF
+__device__ unsigned long long g_prof[16];
+#define MPROF(i) do { if (lane == 0) { long long now__ = clock64(); atomicAdd(&g_prof[i], (unsigned long long)(now__ - mt__)); mt__ = now__; } } while (0)
+#define MPROF_START() long long mt__ = clock64()
+#else
+#define MPROF(i)
+#define MPROF_START()
+#endif
+// All offers one join tile makes to ONE destination pool, merged under one lock acquisition: the pool is
+// loaded once into registers (entry idx = t*32 + lane), every admitted candidate is inserted by a
+// register shift (shuffles, no memory traffic), and the pool is written back once.
+// c0/c1: this lane's two candidate distance bits (members mpos0 + lane and mpos0 + lane + 32 of the tile's
+// other side), NO_PAIR where the pair does not exist. Returns the number of inserts; *new_last = the pool's
+// largest distance bits afterwards when it is full (else 0xFFFFFFFF).
+template <int NT>
+__device__ uint32_t warp_pool_merge(uint64_t *list, uint32_t *size_p, uint32_t *lock, uint32_t cap, const uint32_t (&c)[4],
+                                    const uint32_t (&src)[4], uint32_t thr, int lane, uint32_t *new_last) {
+  // lane-major registers: lane holds entries [lane*NT, lane*NT + NT) -> an insert shifts inside the lanes and
+  // passes ONE entry to the next lane (one 64-bit shuffle per candidate)
+  uint32_t mk[4];
+#pragma unroll
+  for (int g = 0; g < 4; ++g) mk[g] = __ballot_sync(0xffffffffu, c[g] <= thr);
+  *new_last = 0xFFFFFFFFu;
+  if (!(mk[0] | mk[1] | mk[2] | mk[3])) return 0;
+  MPROF_START();
+  if (lane == 0) {
+    while (atomicCAS(lock, 0u, 1u) != 0u) __nanosleep(32);
+    __threadfence();
+  }
+  __syncwarp();
+  MPROF(0);
+  uint32_t size = __ldcg(size_p);
+  uint64_t e[NT];
+  const uint32_t base = lane * NT;
+  const bool vec = base + NT <= cap && (reinterpret_cast<uintptr_t>(list) & 15) == 0;   // 16-byte accesses
+  if (vec) {                                    // slots past `size` hold EMPTY: no dependence on the size load
+#pragma unroll
+    for (int t = 0; t < NT; t += 2) {
+      ulonglong2 v = __ldcg(reinterpret_cast<const ulonglong2 *>(list + base + t));
+      e[t] = v.x; e[t + 1] = v.y;
+    }
+  } else {
+#pragma unroll
+    for (int t = 0; t < NT; ++t) e[t] = base + t < cap ? __ldcg((const unsigned long long *)(list + base + t)) : EMPTY;
+  }
+  uint32_t inserted = 0;
+#ifdef NND_PROF
+  { unsigned long long sink = 0;
+    for (int t = 0; t < NT; ++t) sink += e[t];
+    if (sink == 0x1234567ull) g_prof[15] = 1; }
+#endif
+  MPROF(1);
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    uint32_t m = mk[g];
+#pragma unroll 1
+    while (m) {
+      int srcl = __ffs(m) - 1;
+      m &= m - 1;
+      uint32_t db = __shfl_sync(0xffffffffu, c[g], srcl);
+      uint32_t sid = __shfl_sync(0xffffffffu, src[g], srcl);
+      uint64_t key = ((uint64_t)db << 32) | (sid << 1) | 1u;
+      int less = 0;
+      bool dup = false;
+#pragma unroll
+      for (int t = 0; t < NT; ++t) {
+        less += e[t] < key;                       // EMPTY slots are never < key
+        dup |= ((uint32_t)e[t] >> 1) == sid && e[t] != EMPTY;
+      }
+      uint32_t pos = __reduce_add_sync(0xffffffffu, less);
+      if (__any_sync(0xffffffffu, dup) || pos >= cap) continue;
+      uint64_t carry = __shfl_up_sync(0xffffffffu, e[NT - 1], 1);   // lane-1's last entry (before the shift)
+      if (base + NT > pos) {                      // this lane holds pos or entries after it
+        const int p = pos > base ? (int)(pos - base) : -1;          // local insert slot; -1: whole lane shifts
+#pragma unroll
+        for (int t = NT - 1; t >= 1; --t) e[t] = t > p ? e[t - 1] : e[t];
+        if (p < 0) e[0] = carry;
+#pragma unroll
+        for (int t = 0; t < NT; ++t)
+          if (t == p) e[t] = key;
+        if (pos == base) e[0] = key;
+      }
+#pragma unroll
+      for (int t = 0; t < NT; ++t)
+        if (base + t >= cap) e[t] = EMPTY;        // the entry pushed out of a full pool is dropped
+      if (size < cap) ++size;
+      ++inserted;
+    }
+  }
+  MPROF(2);
+  if (inserted) {
+    if (vec) {
+#pragma unroll
+      for (int t = 0; t < NT; t += 2) {
+        if (base + t < size) __stcg(reinterpret_cast<ulonglong2 *>(list + base + t), make_ulonglong2(e[t], e[t + 1]));
+      }
+    } else {
+#pragma unroll
+      for (int t = 0; t < NT; ++t)
+        if (base + t < size) __stcg((unsigned long long *)(list + base + t), e[t]);
+    }
+    if (lane == 0) __stcg(size_p, size);
+  }
+  if (size == cap) {
+    const uint32_t lidx = cap - 1;
+    uint64_t le = EMPTY;
+#pragma unroll
+    for (int t = 0; t < NT; ++t) {
+      uint64_t v = __shfl_sync(0xffffffffu, e[t], lidx / NT);
+      if (t == (int)(lidx % NT)) le = v;
+    }
+    *new_last = (uint32_t)(le >> 32);
+  }
+  __threadfence();
+  __syncwarp();
+  MPROF(3);
+  if (lane == 0) atomicExch(lock, 0u);
+#ifdef NND_PROF
+  if (lane == 0) atomicAdd(&g_prof[4], 1ull);
+#endif
+  return inserted;
+}
+
+__device__ __forceinline__ uint32_t pool_merge_dispatch(uint64_t *list, uint32_t *size_p, uint32_t *lock, uint32_t cap,
+                                                     const uint32_t (&c)[4], const uint32_t (&src)[4], uint32_t thr,
+                                                     int lane, uint32_t *new_last) {
+  if (cap <= 64) return warp_pool_merge<2>(list, size_p, lock, cap, c, src, thr, lane, new_last);
+  if (cap <= 128) return warp_pool_merge<4>(list, size_p, lock, cap, c, src, thr, lane, new_last);
+  if (cap <= 256) return warp_pool_merge<8>(list, size_p, lock, cap, c, src, thr, lane, new_last);
+  return warp_pool_merge<16>(list, size_p, lock, cap, c, src, thr, lane, new_last);
+}
+
+// one k-chunk of a tile: NI x NJ 16-row sub-blocks per thread, k sequential per pair (fmaf), no branches
+template <int NI, int NJ>
+__device__ __forceinline__ void tile_fma(const float *As, const float *Bs, float (&acc)[4][4], uint32_t kw4, int ty, int tx) {
+  const float4 *ap = reinterpret_cast<const float4 *>(As + ty * ROWF);
+  const float4 *bp = reinterpret_cast<const float4 *>(Bs + tx * ROWF);
+#pragma unroll 2
+  for (uint32_t k4 = 0; k4 < kw4; ++k4) {
+    float4 a[NI], b[NJ];
+#pragma unroll
+    for (int i = 0; i < NI; ++i) a[i] = ap[i * 16 * (ROWF / 4) + k4];
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) b[j] = bp[j * 16 * (ROWF / 4) + k4];
+#pragma unroll
+    for (int i = 0; i < NI; ++i)
+#pragma unroll
+      for (int j = 0; j < NJ; ++j) {
+        float t = a[i].x - b[j].x; acc[i][j] = fmaf(t, t, acc[i][j]);
+      }
+#pragma unroll
+    for (int i = 0; i < NI; ++i)
+#pragma unroll
+      for (int j = 0; j < NJ; ++j) {
+        float t = a[i].y - b[j].y; acc[i][j] = fmaf(t, t, acc[i][j]);
+      }
+#pragma unroll
+    for (int i = 0; i < NI; ++i)
+#pragma unroll
+      for (int j = 0; j < NJ; ++j) {
+        float t = a[i].z - b[j].z; acc[i][j] = fmaf(t, t, acc[i][j]);
+      }
+#pragma unroll
+    for (int i = 0; i < NI; ++i)
+#pragma unroll
+      for (int j = 0; j < NJ; ++j) {
+        float t = a[i].w - b[j].w; acc[i][j] = fmaf(t, t, acc[i][j]);
+      }
   }
 }
 
@@ -188,27 +362,34 @@ __global__ void __launch_bounds__(JT, 2) join_kernel(State s, uint32_t cn_max) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float *As = reinterpret_cast<float *>(smem_raw);
   float *Bs = As + TILE * ROWF;
-  Offer *queue = reinterpret_cast<Offer *>(Bs + TILE * ROWF);
-  uint32_t *ids = reinterpret_cast<uint32_t *>(queue + QCAP);
+  uint32_t *Dm = reinterpret_cast<uint32_t *>(Bs + TILE * ROWF);   // [TILE][DROW] distance bits of the tile
+  uint32_t *ids = Dm + TILE * DROW;
   uint32_t *thr = ids + cn_max;
-  __shared__ uint32_t sh_node, sh_nn, sh_no, sh_qn;
+  __shared__ uint32_t sh_node, sh_nn, sh_no;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int ty = tid >> 4, tx = tid & 15;
   const uint32_t cap_old = 2 * s.R;
   unsigned long long my_dist = 0, my_offer = 0, my_ins = 0;
+#ifdef NND_PROF
+  long long t_fetch = 0, t_tile = 0, t_drain = 0, t_gather = 0, t_mark;
+  unsigned long long sum_nn = 0, sum_no = 0, sum_tiles = 0;
+#define PROF_MARK() t_mark = clock64()
+#define PROF_ADD(x) do { long long now__ = clock64(); x += now__ - t_mark; t_mark = now__; } while (0)
+#else
+#define PROF_MARK()
+#define PROF_ADD(x)
+#endif
 
   for (;;) {
+    PROF_MARK();
     if (tid == 0) {
       uint32_t node = (uint32_t)atomicAdd(s.stats + 3, 1ull);
       sh_node = node;
       if (node < s.n) {
-        uint32_t nfn = s.n_fnew[node], nrn = s.n_rnew[node];
-        uint32_t nfo = s.n_fold[node], nro = s.n_rold[node];
-        uint32_t no = nfo + nro;
-        sh_nn = nfn + nrn;
+        uint32_t no = s.n_fold[node] + s.n_rold[node];
+        sh_nn = s.n_fnew[node] + s.n_rnew[node];
         sh_no = no < cap_old ? no : cap_old;
       }
-      sh_qn = 0;
     }
     __syncthreads();
     const uint32_t node = sh_node;
@@ -230,7 +411,12 @@ __global__ void __launch_bounds__(JT, 2) join_kernel(State s, uint32_t cn_max) {
       }
     }
     __syncthreads();
+    PROF_ADD(t_fetch);
     const uint32_t a_tiles = (nn + TILE - 1) / TILE, b_tiles = (ct + TILE - 1) / TILE;
+#ifdef NND_PROF
+    sum_nn += nn; sum_no += no;
+    for (uint32_t a_ = 0; a_ < a_tiles; ++a_) sum_tiles += b_tiles - a_;
+#endif
     const uint32_t kchunks = ((uint32_t)s.stride + KC - 1) / KC;
     for (uint32_t at = 0; at < a_tiles; ++at) {
       if (kchunks == 1) load_rows(As, s, ids, at * TILE, nn, 0, (uint32_t)s.stride / 4, tid);
@@ -240,87 +426,89 @@ __global__ void __launch_bounds__(JT, 2) join_kernel(State s, uint32_t cn_max) {
         for (int i = 0; i < 4; ++i)
 #pragma unroll
           for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+        // 16-row sub-blocks of the tile that hold members (short sample lists leave most of a tile empty)
+        const int ni = (int)(((nn - at * TILE < (uint32_t)TILE ? nn - at * TILE : (uint32_t)TILE) + 15) / 16);
+        const int nj = (int)(((ct - bt * TILE < (uint32_t)TILE ? ct - bt * TILE : (uint32_t)TILE) + 15) / 16);
         for (uint32_t kcn = 0; kcn < kchunks; ++kcn) {
           const uint32_t kc = kcn * KC;
           const uint32_t kw4 = (((uint32_t)s.stride - kc) < (uint32_t)KC ? ((uint32_t)s.stride - kc) : (uint32_t)KC) / 4;
           if (kchunks > 1) load_rows(As, s, ids, at * TILE, nn, kc, kw4, tid);
           load_rows(Bs, s, ids, bt * TILE, ct, kc, kw4, tid);
           __syncthreads();
-          for (uint32_t k4 = 0; k4 < kw4; ++k4) {
-            float4 a[4], b[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) a[i] = *reinterpret_cast<const float4 *>(As + (ty + 16 * i) * ROWF + 4 * k4);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) b[j] = *reinterpret_cast<const float4 *>(Bs + (tx + 16 * j) * ROWF + 4 * k4);
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                float t;
-                t = a[i].x - b[j].x; acc[i][j] = fmaf(t, t, acc[i][j]);
-                t = a[i].y - b[j].y; acc[i][j] = fmaf(t, t, acc[i][j]);
-                t = a[i].z - b[j].z; acc[i][j] = fmaf(t, t, acc[i][j]);
-                t = a[i].w - b[j].w; acc[i][j] = fmaf(t, t, acc[i][j]);
-              }
+#ifdef NND_PROF
+          PROF_ADD(t_gather);
+#endif
+          // 16-row sub-blocks that hold members, rounded up to 1, 2 or 4 (short sample lists leave most of a tile empty)
+          if (ni <= 1) {
+            if (nj <= 1) tile_fma<1, 1>(As, Bs, acc, kw4, ty, tx);
+            else if (nj <= 2) tile_fma<1, 2>(As, Bs, acc, kw4, ty, tx);
+            else tile_fma<1, 4>(As, Bs, acc, kw4, ty, tx);
+          } else if (ni <= 2) {
+            if (nj <= 2) tile_fma<2, 2>(As, Bs, acc, kw4, ty, tx);
+            else tile_fma<2, 4>(As, Bs, acc, kw4, ty, tx);
+          } else {
+            tile_fma<4, 4>(As, Bs, acc, kw4, ty, tx);
           }
           __syncthreads();
         }
-        // ---- offers: bit 2*(4i+j) = to the A member, bit 2*(4i+j)+1 = to the B member
-        uint32_t pend = 0;
+        // ---- the tile's distance matrix: row = A member, column = B member; NO_PAIR where no pair exists
 #pragma unroll
         for (int i = 0; i < 4; ++i)
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            uint32_t pa = at * TILE + ty + 16 * i, pb = bt * TILE + tx + 16 * j;
-            if (pa < nn && pb < ct && (pb >= nn || pb > pa) && ids[pa] != ids[pb]) {
-              ++my_dist;
-              uint32_t db = __float_as_uint(acc[i][j]);
-              if (db <= thr[pa]) pend |= 1u << (2 * (4 * i + j));
-              if (db <= thr[pb]) pend |= 2u << (2 * (4 * i + j));
-            }
+            uint32_t ra = ty + 16 * i, rb = tx + 16 * j;
+            uint32_t pa = at * TILE + ra, pb = bt * TILE + rb;
+            bool pair = pa < nn && pb < ct && (pb >= nn || pb > pa) && ids[pa] != ids[pb];
+            my_dist += pair;
+            Dm[ra * DROW + rb] = pair ? __float_as_uint(acc[i][j]) : NO_PAIR;
           }
-        while (__syncthreads_or(pend != 0)) {
-          while (pend) {
-            uint32_t slot = atomicAdd(&sh_qn, 1u);
-            if (slot >= QCAP) break;
-            int bit = __ffs(pend) - 1;
-            pend &= pend - 1;
-            int pr = bit >> 1, i = pr >> 2, j = pr & 3;
-            uint32_t pa = at * TILE + ty + 16 * i, pb = bt * TILE + tx + 16 * j;
-            // register arrays indexed dynamically would spill: select acc[i][j] with a static scan
-            float d = 0.f;
-#pragma unroll
-            for (int ii = 0; ii < 4; ++ii)
-#pragma unroll
-              for (int jj = 0; jj < 4; ++jj)
-                if (ii == i && jj == j) d = acc[ii][jj];
-            Offer o;
-            o.dst = (bit & 1) ? ids[pb] : ids[pa];
-            o.src = (bit & 1) ? ids[pa] : ids[pb];
-            o.dbits = __float_as_uint(d);
-            queue[slot] = o;
-            ++my_offer;
+        __syncthreads();
+        PROF_ADD(t_tile);
+        // ---- offers, one destination per warp step: the A members (rows of Dm) and the B members (columns).
+        // On the diagonal tile member r is both row r and column r: one merge takes both.
+        const bool diag = at == bt;
+        for (uint32_t dsel = warp; dsel < (diag ? TILE : 2 * TILE); dsel += JT / 32) {
+          const bool to_a = dsel < TILE;
+          const uint32_t r = to_a ? dsel : dsel - TILE;
+          const uint32_t pd = (to_a ? at : bt) * TILE + r;           // destination member position
+          if (pd >= (to_a && !diag ? nn : ct)) continue;
+          const uint32_t obase = (to_a ? bt : at) * TILE;            // the other side's first position
+          uint32_t c[4], src[4];
+          c[0] = c[1] = c[2] = c[3] = NO_PAIR;
+          if (to_a) { c[0] = Dm[r * DROW + lane]; c[1] = Dm[r * DROW + lane + 32]; }
+          if (!to_a || diag) { c[2] = Dm[lane * DROW + r]; c[3] = Dm[(lane + 32) * DROW + r]; }
+          const uint32_t t = thr[pd];
+          if (!__any_sync(0xffffffffu, c[0] <= t || c[1] <= t || c[2] <= t || c[3] <= t)) continue;
+          const uint32_t p0 = obase + lane, p1 = obase + lane + 32;
+          src[0] = c[0] != NO_PAIR ? ids[p0] : 0u; src[1] = c[1] != NO_PAIR ? ids[p1] : 0u;
+          src[2] = c[2] != NO_PAIR ? ids[p0] : 0u; src[3] = c[3] != NO_PAIR ? ids[p1] : 0u;
+          const uint32_t dst = ids[pd];
+          my_offer += (c[0] <= t) + (c[1] <= t) + (c[2] <= t) + (c[3] <= t);
+          uint32_t new_last;
+          uint32_t ins = pool_merge_dispatch(s.pool + (size_t)dst * s.L, s.psize + dst, s.lock_pool + dst, s.L, c, src, t,
+                                             lane, &new_last);
+          if (lane == 0) {
+            my_ins += ins;
+            if (new_last < t) thr[pd] = new_last;                    // tighter threshold for the next tiles
           }
-          __syncthreads();
-          const uint32_t total = sh_qn < (uint32_t)QCAP ? sh_qn : (uint32_t)QCAP;
-          for (uint32_t e = warp; e < total; e += JT / 32) {
-            Offer o = queue[e];
-            uint64_t key = ((uint64_t)o.dbits << 32) | (o.src << 1) | 1u;
-            bool ok = topl_insert_dispatch(s.pool + (size_t)o.dst * s.L, s.psize + o.dst, s.lock_pool + o.dst, s.L, key,
-                                           true, lane);
-            if (ok && lane == 0) ++my_ins;
-          }
-          __syncthreads();
-          if (tid == 0) sh_qn = 0;
-          __syncthreads();
         }
+        __syncthreads();
+        PROF_ADD(t_drain);
       }
     }
-    __syncthreads();
   }
   if (my_dist) atomicAdd(s.stats + 0, my_dist);
   if (my_offer) atomicAdd(s.stats + 1, my_offer);
   if (my_ins) atomicAdd(s.stats + 2, my_ins);
+#ifdef NND_PROF
+  if (tid == 0) {
+    atomicAdd(s.stats + 8, sum_nn); atomicAdd(s.stats + 9, sum_no); atomicAdd(s.stats + 10, sum_tiles);
+    atomicAdd(s.stats + 7, (unsigned long long)t_gather);
+    atomicAdd(s.stats + 4, (unsigned long long)t_fetch);
+    atomicAdd(s.stats + 5, (unsigned long long)t_tile);
+    atomicAdd(s.stats + 6, (unsigned long long)t_drain);
+  }
+#endif
 }
 
 // ---- update (:34-120) ------------------------------------------------------------------------------------
@@ -435,7 +623,7 @@ int nndescent_launch(b200ann_handle *h, const b200ann_index *ix, size_t K, size_
   CU_CHECK(h, fnew.alloc(n * s.cap_fnew, st));
   CU_CHECK(h, fold.alloc(n * s.cap_fold, st));
   CU_CHECK(h, leaf.alloc(L + 1, st));
-  CU_CHECK(h, stats.alloc(4, st));
+  CU_CHECK(h, stats.alloc(16, st));
   s.pool = pool.p; s.rnn_new = rnew.p; s.rnn_old = rold.p;
   uint32_t *u = u32s.p;
   s.psize = u; s.M = u + n; s.worst = u + 2 * n; s.leafd = u + 3 * n; s.n_fnew = u + 4 * n; s.n_fold = u + 5 * n;
@@ -452,13 +640,13 @@ int nndescent_launch(b200ann_handle *h, const b200ann_index *ix, size_t K, size_
   }
   CU_CHECK(h, cudaMemcpyAsync(leaf.p, lr.data(), (L + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
   s.leaf_rank = leaf.p;
-  CU_CHECK(h, cudaMemsetAsync(stats.p, 0, 4 * sizeof(unsigned long long), st));
+  CU_CHECK(h, cudaMemsetAsync(stats.p, 0, 16 * sizeof(unsigned long long), st));
   const int TB = 128;
   const unsigned nb = (unsigned)((n + TB - 1) / TB);
   init_kernel<<<nb, TB, 0, st>>>(s, seed);
   h->launches++;
   const uint32_t cn_max = (uint32_t)(std::max(2 * S, S + R) + 2 * R);
-  const size_t smem = 2 * (size_t)TILE * ROWF * sizeof(float) + QCAP * sizeof(Offer) + 2 * (size_t)cn_max * sizeof(uint32_t);
+  const size_t smem = 2 * (size_t)TILE * ROWF * sizeof(float) + (size_t)TILE * DROW * sizeof(uint32_t) + 2 * (size_t)cn_max * sizeof(uint32_t);
   CU_CHECK(h, cudaFuncSetAttribute(join_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int occ = 0;
   CU_CHECK(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, join_kernel, JT, smem));
@@ -483,17 +671,32 @@ int nndescent_launch(b200ann_handle *h, const b200ann_index *ix, size_t K, size_
     float a = 0.f, b = 0.f;
     cudaEventElapsedTime(&a, e0, e1); cudaEventElapsedTime(&b, e1, e2);
     join_ms += a; upd_ms += b;
+#ifdef NND_PROF
+    {
+      unsigned long long ps[16];
+      cudaMemcpy(ps, stats.p, sizeof ps, cudaMemcpyDeviceToHost);
+      fprintf(stderr, "NND_PROF it %zu: join %.1f ms update %.1f ms | cum dist %llu offers %llu ins %llu | cum members new %llu old %llu tiles %llu | cyc fetch %llu tile %llu drain %llu\n",
+              it, a, b, ps[0], ps[1], ps[2], ps[8], ps[9], ps[10], ps[4], ps[5], ps[6]);
+    }
+#endif
   }
   cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
   extract_kernel<<<h->sm_count * 8, 256, 0, st>>>(s, knn, knn_d);
   h->launches++;
   CU_CHECK(h, cudaGetLastError());
-  unsigned long long hs[4];
+  unsigned long long hs[16];
   CU_CHECK(h, cudaMemcpyAsync(hs, stats.p, sizeof hs, cudaMemcpyDeviceToHost, st));
   CU_CHECK(h, cudaStreamSynchronize(st));
   if (info8) {
     info8[0] = hs[0]; info8[1] = hs[1]; info8[2] = hs[2]; info8[3] = iter;
     info8[4] = (uint64_t)(join_ms * 1000.f); info8[5] = (uint64_t)(upd_ms * 1000.f); info8[6] = info8[7] = 0;
+#ifdef NND_PROF
+    unsigned long long gp[16];
+    cudaMemcpyFromSymbol(gp, nnd::g_prof, sizeof gp);
+    fprintf(stderr, "NND_PROF cycles(thread 0 of each CTA): fetch %llu gather %llu compute+Dm %llu drain %llu\n", hs[4], hs[7], hs[5], hs[6]);
+    fprintf(stderr, "NND_PROF merges %llu: avg cycles lock %llu load %llu insert %llu writeback+fence %llu\n", gp[4], gp[0] / (gp[4] + 1),
+            gp[1] / (gp[4] + 1), gp[2] / (gp[4] + 1), gp[3] / (gp[4] + 1));
+#endif
   }
   return 0;
 }

@@ -51,6 +51,7 @@ class Parameters {
   T Get(const std::string &name, const T &dflt) const {
     return kv_.count(name) ? Get<T>(name) : dflt;
   }
+  bool Has(const std::string &name) const { return kv_.count(name) != 0; }
 
  private:
   std::unordered_map<std::string, std::string> kv_;
@@ -249,10 +250,11 @@ class IndexNSG : public Index {
 };
 
 // efanna2e::IndexGraph (efanna_graph/include/efanna2e/index_graph.h:23-72): Build produces the kNN
-// graph NSG consumes. The reference approximates it with NN-descent ("K","L","iter","S","R",
-// index_graph.cpp:265-294); here Build computes the EXACT K-NN graph with the brute-force tile
-// kernel (ties to the smaller id), which is what NN-descent converges towards. "L","iter","S","R"
-// are accepted and ignored.
+// graph NSG consumes. Like the reference (index_graph.cpp:265-294) Build runs NN-descent with "K","L",
+// "iter","S","R" (b200ann_nndescent: InitializeGraph from random ids, iter x {join, update}, top K).
+// Two additions: "seed" (default 0) replaces the process-global rand(), and "exact"=1 (or a Build
+// without "iter") computes the EXACT K-NN graph with the tensor-core brute-force kernel instead
+// (b200ann_knn_graph) - what NN-descent converges towards, and faster than it below a few million rows.
 class IndexGraph : public Index {
  public:
   explicit IndexGraph(const size_t dimension, const size_t n, Metric m, Index *initializer, int device = 0)
@@ -266,7 +268,15 @@ class IndexGraph : public Index {
     detail::check(gpu_.h, b200ann_index_create(gpu_.h, data, n, dimension_, dimension_,
                                                 metric_ == INNER_PRODUCT ? B200ANN_IP : B200ANN_L2, &ix), "b200ann_index_create");
     knn_.resize(n * (size_t)K_);
-    int rc = b200ann_knn_graph(gpu_.h, ix, K_, knn_.data());
+    int rc;
+    bool exact = parameters.Get<unsigned>("exact", 0u) != 0 || !parameters.Has("iter");
+    if (exact) {
+      rc = b200ann_knn_graph(gpu_.h, ix, K_, knn_.data());
+    } else {
+      rc = b200ann_nndescent(gpu_.h, ix, K_, parameters.Get<unsigned>("L"), parameters.Get<unsigned>("iter"),
+                             parameters.Get<unsigned>("S"), parameters.Get<unsigned>("R"),
+                             parameters.Get<unsigned>("seed", 0u), knn_.data(), nullptr, info_);
+    }
     b200ann_index_destroy(ix);
     detail::check(gpu_.h, rc, "IndexGraph::Build");
     has_built = true;
@@ -292,6 +302,7 @@ class IndexGraph : public Index {
   }
   const std::vector<uint32_t> &Graph() const { return knn_; }  // [n,K] row-major
   unsigned K() const { return K_; }
+  const uint64_t *BuildInfo() const { return info_; }            // b200ann_nndescent's info (0 after an exact build)
 
  protected:
   Index *initializer_;
@@ -300,6 +311,7 @@ class IndexGraph : public Index {
   detail::Gpu gpu_;
   std::vector<uint32_t> knn_;
   unsigned K_ = 0;
+  uint64_t info_[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 };
 
 // efanna2e::IndexRandom (efanna_graph/src/index_random.cpp): the NN-descent initializer object the

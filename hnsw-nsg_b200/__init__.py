@@ -45,6 +45,9 @@ _lib.b200ann_index_get_graph.argtypes = [_vp, _vp, _sz, C.POINTER(C.c_uint32), C
 _lib.b200ann_index_set_hnsw.argtypes = [_vp, _vp, _sz, _vp, _vp, _vp, _sz, _sz, _vp, C.c_uint32, C.c_int]
 _lib.b200ann_bf_knn.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _vp, _vp]
 _lib.b200ann_knn_graph.argtypes = [_vp, _vp, _sz, _vp]
+_lib.b200ann_hnsw_build.argtypes = [_vp, _vp, _sz, _sz, C.c_uint32, _sz, _sz, _vp, _vp]
+_lib.b200ann_index_hnsw_shape.argtypes = [_vp, _vp]
+_lib.b200ann_index_get_hnsw.argtypes = [_vp, _vp, _vp, _vp, _vp, _vp]
 _lib.b200ann_nndescent.argtypes = [_vp, _vp, _sz, _sz, _sz, _sz, _sz, C.c_uint32, _vp, _vp, _vp]
 _lib.b200ann_nsg_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, C.c_uint32, _vp, _vp, _vp]
 _lib.b200ann_hnsw_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _vp, _vp, _vp]
@@ -69,6 +72,7 @@ EXPORTS = [
     "b200ann_set_link_visited_bits", "b200ann_nsg_build", "b200ann_nsg_init_ep", "b200ann_nsg_link",
     "b200ann_nsg_interinsert", "b200ann_nsg_finish", "b200ann_merge_topk", "b200ann_nsg_search_from",
     "b200ann_hybrid_search", "b200ann_set_knn_mode", "b200ann_knn_last_stats", "b200ann_nndescent",
+    "b200ann_hnsw_build", "b200ann_index_hnsw_shape", "b200ann_index_get_hnsw",
 ]
 
 
@@ -222,6 +226,29 @@ class Index:
     def knn_graph_raw(self, K, out):
         """out: device buffer [n,K] u32/i32 (torch tensor or raw pointer)"""
         self.h._check(_lib.b200ann_knn_graph(self.h._h, self._ix, K, _ptr(out)))
+
+    def hnsw_build(self, M=16, efc=200, seed=100, ratio=0, bmax=0, labels=None):
+        """HierarchicalNSW(space, n, M, efc, seed) + addPoint(row i, label i) for every row, on the GPU."""
+        info = np.zeros(8, np.uint64)
+        lab = None if labels is None else np.ascontiguousarray(labels, np.uint64)
+        self.h._check(_lib.b200ann_hnsw_build(self.h._h, self._ix, M, efc, seed, ratio, bmax, _ptr(lab), _ptr(info)))
+        keys = ("beam_evals", "hops", "heuristic_evals", "batches", "upper_rows", "maxlevel", "ep", "largest_group")
+        return dict(zip(keys, (int(x) for x in info)))
+
+    def get_hnsw(self):
+        """the HNSW graph in the flat layout set_hnsw takes (dict like tests/refutil.parse_hnsw)"""
+        sh = np.zeros(5, np.uint64)
+        self.h._check(_lib.b200ann_index_hnsw_shape(self._ix, _ptr(sh)))
+        maxM0, maxM, rows, maxlevel, ep = (int(x) for x in sh)
+        links0 = np.empty((self.n, maxM0), np.uint32)
+        levels = np.empty(self.n, np.int32)
+        upper_ptr = np.empty(self.n, np.uint32)
+        upper = np.empty((rows, maxM), np.uint32)
+        labels = np.empty(self.n, np.uint64)
+        self.h._check(_lib.b200ann_index_get_hnsw(self._ix, _ptr(links0), _ptr(levels), _ptr(upper_ptr),
+                                                  _ptr(upper) if rows else None, _ptr(labels)))
+        return dict(n=self.n, maxM=maxM, maxM0=maxM0, ep=ep, maxlevel=maxlevel, links0=links0, levels=levels,
+                    upper_ptr=upper_ptr, upper_links=upper, labels=labels)
 
     def nndescent(self, K, L, it, S, R, seed=0, want_dists=False, out=None):
         """IndexGraph::Build (NN-descent) on the GPU: returns knn [n,K] (+ dists) and the info dict.

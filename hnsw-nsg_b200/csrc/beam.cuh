@@ -84,6 +84,7 @@ struct Beam {
   int lane, t, g;
   uint32_t np, cap;
   uint32_t n_dist, n_hops;
+  int lvl = 0;  // HNSW only: the layer expand_all walks (0 = links0 rows, l >= 1 = the node's upper row l-1)
 
   __device__ __forceinline__ Beam(const SearchParams &pp, uint32_t *smem_base) : p(pp) {
     pool_d = reinterpret_cast<float *>(smem_base);
@@ -222,12 +223,12 @@ struct Beam {
 
   // the greedy walk itself (also the first phase of HNSW_NSG::searchKnn,
   // hnsw_nsg/include/index_hnsw_nsg.h:111-143): returns the node it ends on
-  __device__ __forceinline__ uint32_t descend_upper(uint32_t start, float &curdist) {
+  __device__ __forceinline__ uint32_t descend_upper(uint32_t start, float &curdist, int stop_level = 0) {
     uint32_t cur = start;
     if (lane == 0) cand_i[0] = cur;
     eval(1);
     curdist = cand_d[0];
-    for (int level = p.maxlevel; level > 0; level--) {
+    for (int level = p.maxlevel; level > stop_level; level--) {
       bool changed = true;
       while (changed) {
         changed = false;
@@ -351,7 +352,13 @@ struct Beam {
         if (lane == 0) pool_i[k] = e & ~FLAG;
         uint32_t node = e & ~FLAG;
         n_hops++;
-        uint32_t m = load_row(p.graph + (size_t)node * p.gstride, p.gstride, p.gstride, true);
+        const uint32_t *row = p.graph + (size_t)node * p.gstride;
+        uint32_t rl = p.gstride;
+        if (HNSW && lvl > 0) {
+          row = p.upper_links + ((size_t)__ldg(p.upper_ptr + node) + (lvl - 1)) * p.maxM;
+          rl = p.maxM;
+        }
+        uint32_t m = load_row(row, rl, rl, true);
         eval(m);
         rec(cand_i, cand_d, m, false);
         for (uint32_t c0 = 0; c0 < m; c0 += 32) {
@@ -377,6 +384,50 @@ struct Beam {
     __syncwarp();
   }
 };
+
+// ---------------------------------------------------------------- occlusion scan
+// The rule shared by sync_prune (index_nsg.cpp:328-345), InterInsert (:386-404) and hnswlib's
+// getNeighborsByHeuristic2 (hnswalg.h:443-483): scan sorted candidates
+// [start,end), keep p iff no kept r has r.id == p.id or d(r,p) < d(q,p); stop at R kept.
+// Kept rows are compared 2*TPW at a time; the first kept entry must be placed by the caller or by
+// passing nres == 0 (then the first candidate is kept unconditionally, like `result.push_back(pool[start])`).
+template <class B>
+__device__ __forceinline__ void occlude_scan(B &b, const float *sd, const uint32_t *si, uint32_t start,
+                                             uint32_t end, uint32_t R, uint32_t *res_i, float *res_d,
+                                             uint32_t &nres, uint32_t &n_eval) {
+  constexpr int TPW = B::TPW;
+  for (uint32_t s = start; s < end && nres < R; s++) {
+    const uint32_t pid = si[s];
+    const float pd = sd[s];
+    bool occ = false;
+    if (nres > 0) {
+      const float4 *prow = reinterpret_cast<const float4 *>(b.p.vec + (size_t)pid * b.p.stride);
+#pragma unroll
+      for (int c = 0; c < B::NCHUNK; c++) {
+        int ch = b.t + c * B::TEAMSZ;
+        b.qreg[c] = ch < b.p.nch ? ld_row16_ca(prow + ch) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      for (uint32_t t0 = 0; t0 < nres && !occ; t0 += 2 * TPW) {
+        uint32_t i0 = t0 + b.g, i1 = t0 + TPW + b.g;
+        const float4 *r0 = nullptr, *r1 = nullptr;
+        uint32_t id0 = INVALID_ID, id1 = INVALID_ID;
+        if (i0 < nres) { id0 = res_i[i0]; r0 = reinterpret_cast<const float4 *>(b.p.vec + (size_t)id0 * b.p.stride); }
+        if (i1 < nres) { id1 = res_i[i1]; r1 = reinterpret_cast<const float4 *>(b.p.vec + (size_t)id1 * b.p.stride); }
+        float d0, d1;
+        team_dist2<B::TEAMSZ, B::NCHUNK, B::IS_IP, true>(r0, r1, b.qreg, b.t, b.p.nch, d0, d1);
+        bool o = (i0 < nres && (id0 == pid || d0 < pd)) || (i1 < nres && (id1 == pid || d1 < pd));
+        occ = __any_sync(0xffffffffu, o);
+        n_eval += min(nres - t0, (uint32_t)(2 * TPW));
+      }
+    }
+    if (!occ) {
+      __syncwarp();
+      if (b.lane == 0) { res_i[nres] = pid; res_d[nres] = pd; }
+      nres++;
+      __syncwarp();
+    }
+  }
+}
 
 // dispatch on the row length: nch = ceil(dim/4) float4 chunks -> (TEAM, NCH)
 #define BEAM_DISPATCH_NCH(nch, CALL)                 \

@@ -226,6 +226,51 @@ int b200ann_index_set_hnsw(b200ann_index_t ix, const uint32_t *links0, size_t ma
   return 0;
 }
 
+int b200ann_hnsw_build(b200ann_handle_t h, b200ann_index_t ix, size_t M, size_t efc, uint32_t seed, size_t ratio,
+                       size_t bmax, const uint64_t *labels, uint64_t *info) {
+  if (!h || !ix) return B200ANN_ERR_ARG;
+  CU_CHECK(h, cudaSetDevice(h->device));
+  free_hnsw(ix);
+  CallTimer t(h);
+  int rc = hnsw_build_launch(h, ix, M, efc, seed, ratio, bmax, labels, info);
+  t.stop();
+  if (rc) return rc;
+  CU_CHECK(h, t.sync());
+  return 0;
+}
+
+int b200ann_index_hnsw_shape(b200ann_index_t ix, uint64_t *out5) {
+  if (!ix || !out5) return B200ANN_ERR_ARG;
+  if (!ix->has_hnsw) return set_err(ix->h, B200ANN_ERR_STATE, "index has no HNSW graph (set_hnsw / hnsw_build first)");
+  out5[0] = ix->maxM0; out5[1] = ix->maxM; out5[2] = ix->upper_rows; out5[3] = (uint64_t)ix->maxlevel; out5[4] = ix->hnsw_ep;
+  return 0;
+}
+
+int b200ann_index_get_hnsw(b200ann_index_t ix, uint32_t *links0, int32_t *levels, uint32_t *upper_ptr,
+                           uint32_t *upper_links, uint64_t *labels) {
+  if (!ix) return B200ANN_ERR_ARG;
+  b200ann_handle *h = ix->h;
+  if (!ix->has_hnsw) return set_err(h, B200ANN_ERR_STATE, "index has no HNSW graph (set_hnsw / hnsw_build first)");
+  CU_CHECK(h, cudaSetDevice(h->device));
+  cudaStream_t st = h->stream;
+  if (links0) CU_CHECK(h, cudaMemcpyAsync(links0, ix->links0, ix->n * ix->maxM0 * 4, cudaMemcpyDefault, st));
+  if (levels) CU_CHECK(h, cudaMemcpyAsync(levels, ix->levels, ix->n * 4, cudaMemcpyDefault, st));
+  if (upper_ptr) CU_CHECK(h, cudaMemcpyAsync(upper_ptr, ix->upper_ptr, ix->n * 4, cudaMemcpyDefault, st));
+  if (upper_links && ix->upper_rows)
+    CU_CHECK(h, cudaMemcpyAsync(upper_links, ix->upper_links, ix->upper_rows * ix->maxM * 4, cudaMemcpyDefault, st));
+  if (labels) {
+    if (ix->labels) CU_CHECK(h, cudaMemcpyAsync(labels, ix->labels, ix->n * 8, cudaMemcpyDefault, st));
+    else {
+      std::vector<uint64_t> ident(ix->n);
+      for (size_t i = 0; i < ix->n; i++) ident[i] = i;
+      CU_CHECK(h, cudaMemcpyAsync(labels, ident.data(), ix->n * 8, cudaMemcpyDefault, st));
+      CU_CHECK(h, cudaStreamSynchronize(st));
+    }
+  }
+  CU_CHECK(h, cudaStreamSynchronize(st));
+  return 0;
+}
+
 // tensor cores when the problem is big enough to fill them (or when forced), else the fp32 SIMT kernel
 static int knn_dispatch(b200ann_handle *h, b200ann_index *ix, const float *q, size_t nq, size_t qstride, size_t k,
                         bool exclude_self, uint32_t *ids, float *dists) {

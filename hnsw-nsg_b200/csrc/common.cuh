@@ -145,6 +145,10 @@ int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t n
 bool knn_tc_supported(const b200ann_index *ix, size_t nq, size_t k);
 void knn_tc_free(b200ann_index *ix);
 
+// HNSW construction (hnsw_build.cu): builds and installs the graph in the index
+int hnsw_build_launch(b200ann_handle *h, b200ann_index *ix, size_t M, size_t efc, uint32_t seed, size_t ratio, size_t bmax,
+                      const uint64_t *labels_host_or_dev, uint64_t *info8);
+
 // NN-descent (nndescent.cu); device pointers only
 int nndescent_launch(b200ann_handle *h, const b200ann_index *ix, size_t K, size_t L, size_t iter, size_t S, size_t R,
                      uint32_t seed, uint32_t *knn, float *knn_d, uint64_t *info8);

@@ -1,0 +1,425 @@
+// HNSW construction on the GPU.
+//
+// Replaces the addPoint loop of hnswlib::HierarchicalNSW (hnswlib/hnswlib/hnswalg.h:1153-1267: level draw
+// :206-210, greedy descent :1214-1239, searchBaseLayer :225-305, mutuallyConnectNewElement :506-630 with
+// getNeighborsByHeuristic2 :443-483), as the drivers run it over a whole dataset
+// (hnswlib/tests/cpp/sift_1m.cpp:321-336, python_bindings/bindings.cpp:287-303).
+//
+// The reference inserts one point at a time under per-node mutexes. Here points are inserted in batches
+// ("batch form", restated serially by oracle/oracle.c orc_hnsw_build variant 1 and compared link for link):
+//   schedule   batch = min(bmax, max(1, inserted / ratio)) consecutive rows; a row whose level exceeds the
+//              current top level is a batch of its own (it becomes the new entry point, :1262-1265).
+//   insert     one warp per new point, on the graph as it was BEFORE the batch: greedy descent to the point's
+//              level, then per level the ef_construction beam (beam.cuh, single-pool form) and the heuristic
+//              (occlude_scan) pick <= M links; the point's own rows are written (farthest first, the order the
+//              reference pops its max-heap in, :514-517) and every link is recorded as a reverse edge.
+//   reverse    reverse edges are grouped per (neighbour, level) row; one warp per touched row appends them in
+//              ascending id when they fit in Mmax (M0 = 2M on level 0), else re-runs the heuristic over
+//              existing + new candidates sorted by (distance, id) (:581-618 does it one edge at a time).
+// Levels come from the same std::default_random_engine / uniform_real_distribution<double> sequence as the
+// reference (this file is compiled against the same libstdc++), so level assignment is identical to it.
+#include <algorithm>
+#include <cmath>
+#include <random>
+#include <vector>
+#include "beam.cuh"
+
+using namespace beam;
+
+namespace {
+
+constexpr int WARPS = 4;
+
+struct InsertParams {
+  SearchParams sp;          // graph = links0 (gstride = maxM0), upper_*, ep = entry point, maxlevel, L = ef_construction
+  uint32_t s, e;            // batch rows [s, e)
+  uint32_t M, nlev;         // links per new point; levels per point in the edge buffer
+  const int32_t *levels;
+  uint32_t *links0, *upper_links;   // writable views of sp.graph / sp.upper_links
+  uint32_t *rev_row, *rev_src; float *rev_d;   // [(e-s) * nlev * M]
+  uint32_t *rcount, *touched, *counters;       // [n + rows], [n + rows], {ntouched, maxgroup, cursor}
+  unsigned long long *stats;                   // {beam distance evaluations, hops, heuristic evaluations}
+};
+
+__host__ __device__ inline uint32_t insert_smem_words(const InsertParams &ip) {
+  return smem_words(ip.sp.pool_cap, ip.sp.cand_cap, ip.sp.hbits) + 2 * ip.sp.gstride;
+}
+
+template <int TEAM, int NCH, bool IP>
+__global__ void __launch_bounds__(WARPS * 32) hnsw_insert_kernel(const InsertParams ip) {
+  extern __shared__ uint32_t smem[];
+  const SearchParams &p = ip.sp;
+  const int warp = threadIdx.x >> 5;
+  const uint32_t pt = ip.s + blockIdx.x * WARPS + warp;
+  if (pt >= ip.e) return;
+  uint32_t *base = smem + (size_t)warp * insert_smem_words(ip);
+  typedef Beam<TEAM, NCH, IP, true> B;
+  B b(p, base);
+  uint32_t *res_i = base + smem_words(p.pool_cap, p.cand_cap, p.hbits);
+  float *res_d = reinterpret_cast<float *>(res_i + p.gstride);
+  NoRec rec;
+  const float *qv = p.vec + (size_t)pt * p.stride;
+  b.begin(qv);
+  const int curlevel = ip.levels[pt];
+  uint32_t cur = p.ep;
+  if (curlevel < p.maxlevel) {  // :1214-1239
+    float cd;
+    cur = b.descend_upper(p.ep, cd, curlevel);
+  }
+  uint32_t n_heur = 0;
+  for (int level = curlevel < p.maxlevel ? curlevel : p.maxlevel; level >= 0; --level) {
+    // ---- searchBaseLayer(cur, point, level)
+    b.lvl = level;
+    for (uint32_t i = b.lane; i <= b.hmask; i += 32) b.tab[i] = INVALID_ID;
+    __syncwarp();
+    if (b.lane == 0) b.cand_i[0] = cur;
+    b.eval(1);
+    if (b.lane == 0) { b.pool_d[0] = b.cand_d[0]; b.pool_i[0] = cur | FLAG; }
+    b.test_and_set(cur);
+    b.np = 1;
+    __syncwarp();
+    b.expand_all(rec);
+    // ---- getNeighborsByHeuristic2(top_candidates, M): fewer than M -> all kept
+    uint32_t nres = 0;
+    if (b.np < ip.M) {
+      for (uint32_t i = b.lane; i < b.np; i += 32) { res_i[i] = b.pool_i[i] & ~FLAG; res_d[i] = b.pool_d[i]; }
+      nres = b.np;
+      __syncwarp();
+    } else {
+      occlude_scan(b, b.pool_d, b.pool_i, 0, b.np, ip.M, res_i, res_d, nres, n_heur);
+      b.load_query(qv);  // occlude_scan used the query registers for the candidate rows
+    }
+    __syncwarp();
+    // ---- own row, farthest first; reverse edges
+    uint32_t *row; uint32_t rl;
+    if (level == 0) { row = ip.links0 + (size_t)pt * p.gstride; rl = p.gstride; }
+    else { row = ip.upper_links + ((size_t)p.upper_ptr[pt] + (level - 1)) * p.maxM; rl = p.maxM; }
+    for (uint32_t i = b.lane; i < rl; i += 32) row[i] = i < nres ? res_i[nres - 1 - i] : INVALID_ID;
+    const size_t eb = ((size_t)(pt - ip.s) * ip.nlev + level) * ip.M;
+    for (uint32_t i = b.lane; i < nres; i += 32) {
+      uint32_t sn = res_i[i];
+      uint32_t ridx = level == 0 ? sn : p.n + p.upper_ptr[sn] + (level - 1);
+      ip.rev_row[eb + i] = ridx; ip.rev_src[eb + i] = pt; ip.rev_d[eb + i] = res_d[i];
+      uint32_t c = atomicAdd(&ip.rcount[ridx], 1u);
+      if (c == 0) ip.touched[atomicAdd(&ip.counters[0], 1u)] = ridx;
+      atomicMax(&ip.counters[1], c + 1);
+    }
+    cur = res_i[0];  // closest selected = next entry point (:520)
+    __syncwarp();
+  }
+  if (b.lane == 0) {
+    atomicAdd(ip.stats + 0, (unsigned long long)b.n_dist);
+    atomicAdd(ip.stats + 1, (unsigned long long)b.n_hops);
+    atomicAdd(ip.stats + 2, (unsigned long long)n_heur);
+  }
+}
+
+// offsets of the touched rows' groups in the grouped edge arrays (any order: groups are sorted when used)
+__global__ void rev_offsets_kernel(const uint32_t *touched, const uint32_t *counters, const uint32_t *rcount, uint32_t *roff,
+                                   uint32_t *cursor) {
+  uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= counters[0]) return;
+  uint32_t r = touched[t];
+  roff[r] = atomicAdd(cursor, rcount[r]);
+}
+__global__ void rev_group_kernel(const uint32_t *rev_row, const uint32_t *rev_src, const float *rev_d, size_t total,
+                                 const uint32_t *roff, uint32_t *rfill, uint32_t *g_src, float *g_d) {
+  size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (e >= total) return;
+  uint32_t r = rev_row[e];
+  if (r == INVALID_ID) return;
+  uint32_t pos = roff[r] + atomicAdd(&rfill[r], 1u);
+  g_src[pos] = rev_src[e];
+  g_d[pos] = rev_d[e];
+}
+
+struct ReverseParams {
+  SearchParams sp;          // vec/stride/nch/dim (+ pool_cap/cand_cap/hbits for the smem carve-up); gstride = maxM0
+  uint32_t *links0, *upper_links;
+  const uint32_t *row_owner;        // [rows]: node that owns upper row r
+  const uint32_t *touched, *counters, *roff, *g_src; const float *g_d;
+  uint32_t *rcount, *rfill;
+  uint32_t mcap;                    // candidates a warp can hold: Mmax0 + largest group
+  unsigned long long *stats;
+};
+__host__ __device__ inline uint32_t reverse_smem_words(const ReverseParams &rp) {
+  return smem_words(rp.sp.pool_cap, rp.sp.cand_cap, rp.sp.hbits) + 4 * rp.mcap + 2 * rp.sp.gstride;
+}
+
+template <int TEAM, int NCH, bool IP>
+__global__ void __launch_bounds__(WARPS * 32) hnsw_reverse_kernel(const ReverseParams rp) {
+  extern __shared__ uint32_t smem[];
+  const SearchParams &p = rp.sp;
+  const int warp = threadIdx.x >> 5;
+  const uint32_t t = blockIdx.x * WARPS + warp;
+  if (t >= rp.counters[0]) return;
+  uint32_t *base = smem + (size_t)warp * reverse_smem_words(rp);
+  typedef Beam<TEAM, NCH, IP, true> B;
+  B b(p, base);
+  uint32_t *ui = base + smem_words(p.pool_cap, p.cand_cap, p.hbits);   // unsorted ids / distances
+  float *ud = reinterpret_cast<float *>(ui + rp.mcap);
+  uint32_t *si = ui + 2 * rp.mcap;                                     // sorted
+  float *sd = reinterpret_cast<float *>(si + rp.mcap);
+  uint32_t *res_i = si + 2 * rp.mcap;
+  float *res_d = reinterpret_cast<float *>(res_i + p.gstride);
+  const int lane = b.lane;
+
+  const uint32_t ridx = rp.touched[t];
+  uint32_t node, cap; uint32_t *row;
+  if (ridx < p.n) { node = ridx; cap = p.gstride; row = rp.links0 + (size_t)node * p.gstride; }
+  else { node = rp.row_owner[ridx - p.n]; cap = p.maxM; row = rp.upper_links + (size_t)(ridx - p.n) * p.maxM; }
+  const uint32_t k = rp.rcount[ridx], off = rp.roff[ridx];
+  // existing links (rows are padded with INVALID)
+  uint32_t c = 0;
+  for (uint32_t j0 = 0; j0 < cap; j0 += 32) {
+    uint32_t j = j0 + lane;
+    uint32_t id = j < cap ? row[j] : INVALID_ID;
+    c += __popc(__ballot_sync(0xffffffffu, id != INVALID_ID));
+    if (j < cap) b.cand_i[j] = id;
+  }
+  __syncwarp();
+  uint32_t n_heur = 0;
+  if (c + k <= cap) {
+    // append in ascending id (the order a one-thread addPoint loop would append them in)
+    for (uint32_t i = lane; i < k; i += 32) {
+      uint32_t id = rp.g_src[off + i], r = 0;
+      for (uint32_t j = 0; j < k; j++) r += rp.g_src[off + j] < id;
+      row[c + r] = id;
+    }
+  } else {
+    // candidates = existing (distance from this node) + new (distance already known), sorted by (distance,id)
+    b.load_query(p.vec + (size_t)node * p.stride);
+    b.n_dist = 0;
+    b.eval(c);
+    for (uint32_t i = lane; i < c; i += 32) { ui[i] = b.cand_i[i]; ud[i] = b.cand_d[i]; }
+    for (uint32_t i = lane; i < k; i += 32) { ui[c + i] = rp.g_src[off + i]; ud[c + i] = rp.g_d[off + i]; }
+    const uint32_t m = c + k;
+    __syncwarp();
+    for (uint32_t i = lane; i < m; i += 32) {
+      float di = ud[i]; uint32_t ii = ui[i], r = 0;
+      for (uint32_t j = 0; j < m; j++) {
+        float dj = ud[j]; uint32_t ij = ui[j];
+        r += (dj < di || (dj == di && ij < ii)) ? 1u : 0u;
+      }
+      sd[r] = di; si[r] = ii;
+    }
+    __syncwarp();
+    uint32_t nres = 0;
+    occlude_scan(b, sd, si, 0, m, cap, res_i, res_d, nres, n_heur);
+    __syncwarp();
+    for (uint32_t i = lane; i < cap; i += 32) row[i] = i < nres ? res_i[nres - 1 - i] : INVALID_ID;
+    n_heur += c;
+  }
+  if (lane == 0) {
+    rp.rcount[ridx] = 0; rp.rfill[ridx] = 0;
+    if (n_heur) atomicAdd(rp.stats + 2, (unsigned long long)n_heur);
+  }
+}
+
+template <int TEAM, int NCH, bool IP>
+int launch_insert_t(b200ann_handle *h, const InsertParams &ip) {
+  size_t smem = (size_t)WARPS * insert_smem_words(ip) * 4;
+  if (smem > 227 * 1024) return set_err(h, B200ANN_ERR_ARG, "hnsw_build: ef_construction / M need more than 227 KB shared memory per block");
+  auto kern = hnsw_insert_kernel<TEAM, NCH, IP>;
+  CU_CHECK(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<(ip.e - ip.s + WARPS - 1) / WARPS, WARPS * 32, smem, h->stream>>>(ip);
+  h->launches++;
+  return 0;
+}
+template <int TEAM, int NCH, bool IP>
+int launch_reverse_t(b200ann_handle *h, const ReverseParams &rp, uint32_t ntouched) {
+  size_t smem = (size_t)WARPS * reverse_smem_words(rp) * 4;
+  if (smem > 227 * 1024) return set_err(h, B200ANN_ERR_ARG, "hnsw_build: a reverse-link group needs more than 227 KB shared memory (lower bmax)");
+  auto kern = hnsw_reverse_kernel<TEAM, NCH, IP>;
+  CU_CHECK(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<(ntouched + WARPS - 1) / WARPS, WARPS * 32, smem, h->stream>>>(rp);
+  h->launches++;
+  return 0;
+}
+
+#define HB_DISPATCH(FN, ...)                                                                   \
+  do {                                                                                         \
+    if (nch > 512) return set_err(h, B200ANN_ERR_ARG, "dim > 2048 is not supported");          \
+    if (ip_metric) {                                                                           \
+      if (nch <= 8) return FN<8, 1, true>(__VA_ARGS__);                                        \
+      if (nch <= 16) return FN<8, 2, true>(__VA_ARGS__);                                       \
+      if (nch <= 32) return FN<8, 4, true>(__VA_ARGS__);                                       \
+      if (nch <= 64) return FN<8, 8, true>(__VA_ARGS__);                                       \
+      if (nch <= 128) return FN<32, 4, true>(__VA_ARGS__);                                     \
+      if (nch <= 256) return FN<32, 8, true>(__VA_ARGS__);                                     \
+      return FN<32, 16, true>(__VA_ARGS__);                                                    \
+    } else {                                                                                   \
+      if (nch <= 8) return FN<8, 1, false>(__VA_ARGS__);                                       \
+      if (nch <= 16) return FN<8, 2, false>(__VA_ARGS__);                                      \
+      if (nch <= 32) return FN<8, 4, false>(__VA_ARGS__);                                      \
+      if (nch <= 64) return FN<8, 8, false>(__VA_ARGS__);                                      \
+      if (nch <= 128) return FN<32, 4, false>(__VA_ARGS__);                                    \
+      if (nch <= 256) return FN<32, 8, false>(__VA_ARGS__);                                    \
+      return FN<32, 16, false>(__VA_ARGS__);                                                   \
+    }                                                                                          \
+  } while (0)
+
+int launch_insert(b200ann_handle *h, const InsertParams &ip, bool ip_metric) {
+  int nch = ip.sp.nch;
+  HB_DISPATCH(launch_insert_t, h, ip);
+}
+int launch_reverse(b200ann_handle *h, const ReverseParams &rp, uint32_t ntouched, bool ip_metric) {
+  int nch = rp.sp.nch;
+  HB_DISPATCH(launch_reverse_t, h, rp, ntouched);
+}
+
+__global__ void fill_u32_kernel(uint32_t *p, size_t count, uint32_t v) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  for (; i < count; i += (size_t)gridDim.x * blockDim.x) p[i] = v;
+}
+
+}  // namespace
+
+// HierarchicalNSW::getRandomLevel (hnswalg.h:206-210) for rows 0..n-1 in insertion order
+static void draw_levels(size_t n, size_t M, uint32_t seed, std::vector<int32_t> &levels) {
+  std::default_random_engine level_generator(seed);            // hnswalg.h:122
+  const double mult = 1 / std::log(1.0 * (double)M);          // :114
+  levels.resize(n);
+  for (size_t i = 0; i < n; i++) {
+    std::uniform_real_distribution<double> distribution(0.0, 1.0);
+    double r = -std::log(distribution(level_generator)) * mult;
+    levels[i] = (int)r;
+  }
+}
+
+// Builds the HNSW graph of the index's rows (inserted in row order) and installs it in the index.
+// info8 = {beam distance evaluations, expanded nodes, heuristic distance evaluations, batches, upper rows,
+// maxlevel, entry point, largest reverse group}.
+int hnsw_build_launch(b200ann_handle *h, b200ann_index *ix, size_t M, size_t efc, uint32_t seed, size_t ratio, size_t bmax,
+                      const uint64_t *labels_host_or_dev, uint64_t *info8) {
+  const size_t n = ix->n;
+  if (M < 2 || M > 128 || n >= (1ull << 31))
+    return set_err(h, B200ANN_ERR_ARG, "hnsw_build: need 2 <= M <= 128");
+  if (efc < M) efc = M;                                        // hnswalg.h:107
+  if (ratio == 0) ratio = 32;
+  if (bmax == 0) bmax = 8192;
+  const size_t maxM = M, maxM0 = 2 * M;
+  cudaStream_t st = h->stream;
+  std::vector<int32_t> levels;
+  draw_levels(n, M, seed, levels);
+  std::vector<uint32_t> upper_ptr(n), row_owner;
+  size_t rows = 0;
+  int toplevel = 0;
+  for (size_t i = 0; i < n; i++) {
+    upper_ptr[i] = (uint32_t)rows;
+    for (int l = 0; l < levels[i]; l++) row_owner.push_back((uint32_t)i);
+    rows += (size_t)levels[i];
+    toplevel = std::max(toplevel, (int)levels[i]);
+  }
+  const uint32_t nlev = (uint32_t)toplevel + 1;
+
+  // the graph arrays become the index's (freed by b200ann_index_destroy / a later set_hnsw)
+  uint32_t *links0 = nullptr, *upper_links = nullptr, *d_upper_ptr = nullptr;
+  int32_t *d_levels = nullptr;
+  uint64_t *d_labels = nullptr;
+  CU_CHECK(h, cudaMalloc((void **)&links0, n * maxM0 * 4));
+  CU_CHECK(h, cudaMalloc((void **)&upper_links, (rows ? rows : 1) * maxM * 4));
+  CU_CHECK(h, cudaMalloc((void **)&d_upper_ptr, n * 4));
+  CU_CHECK(h, cudaMalloc((void **)&d_levels, n * 4));
+  CU_CHECK(h, cudaMemcpyAsync(d_upper_ptr, upper_ptr.data(), n * 4, cudaMemcpyHostToDevice, st));
+  CU_CHECK(h, cudaMemcpyAsync(d_levels, levels.data(), n * 4, cudaMemcpyHostToDevice, st));
+  if (labels_host_or_dev) {
+    CU_CHECK(h, cudaMalloc((void **)&d_labels, n * 8));
+    CU_CHECK(h, cudaMemcpyAsync(d_labels, labels_host_or_dev, n * 8, cudaMemcpyDefault, st));
+  }
+  fill_u32_kernel<<<h->sm_count * 8, 256, 0, st>>>(links0, n * maxM0, INVALID_ID);
+  fill_u32_kernel<<<h->sm_count * 8, 256, 0, st>>>(upper_links, (rows ? rows : 1) * maxM, INVALID_ID);
+
+  DevBuf<uint32_t> owner, rstate, touched, counters, rev_row, rev_src, g_src;
+  DevBuf<float> rev_d, g_d;
+  DevBuf<unsigned long long> stats;
+  const size_t nr = n + rows, ecap = bmax * nlev * M;
+  CU_CHECK(h, owner.alloc(rows, st));
+  CU_CHECK(h, rstate.alloc(3 * nr, st));          // rcount | rfill | roff
+  CU_CHECK(h, touched.alloc(nr, st));
+  CU_CHECK(h, counters.alloc(4, st));
+  CU_CHECK(h, rev_row.alloc(ecap, st)); CU_CHECK(h, rev_src.alloc(ecap, st)); CU_CHECK(h, rev_d.alloc(ecap, st));
+  CU_CHECK(h, g_src.alloc(ecap, st)); CU_CHECK(h, g_d.alloc(ecap, st));
+  CU_CHECK(h, stats.alloc(4, st));
+  if (rows) CU_CHECK(h, cudaMemcpyAsync(owner.p, row_owner.data(), rows * 4, cudaMemcpyHostToDevice, st));
+  CU_CHECK(h, cudaMemsetAsync(rstate.p, 0, 3 * nr * 4, st));
+  CU_CHECK(h, cudaMemsetAsync(stats.p, 0, 4 * sizeof(unsigned long long), st));
+  uint32_t *rcount = rstate.p, *rfill = rstate.p + nr, *roff = rstate.p + 2 * nr;
+
+  const bool ipm = ix->metric == B200ANN_IP;
+  InsertParams ip = {};
+  ip.sp.vec = ix->vec; ip.sp.stride = ix->stride; ip.sp.n = (uint32_t)n; ip.sp.nch = (int)((ix->dim + 3) / 4);
+  ip.sp.dim = (uint32_t)ix->dim;
+  ip.sp.graph = links0; ip.sp.gstride = (uint32_t)maxM0;
+  ip.sp.upper_links = upper_links; ip.sp.upper_ptr = d_upper_ptr; ip.sp.maxM = (uint32_t)maxM;
+  ip.sp.L = (uint32_t)efc; ip.sp.K = (uint32_t)M; ip.sp.hbits = h->link_visited_bits;
+  ip.sp.pool_cap = round_up((uint32_t)efc + 1, 32);
+  ip.sp.cand_cap = round_up((uint32_t)maxM0, 32);
+  ip.M = (uint32_t)M; ip.nlev = nlev; ip.levels = d_levels; ip.links0 = links0; ip.upper_links = upper_links;
+  ip.rev_row = rev_row.p; ip.rev_src = rev_src.p; ip.rev_d = rev_d.p;
+  ip.rcount = rcount; ip.touched = touched.p; ip.counters = counters.p; ip.stats = stats.p;
+  ReverseParams rp = {};
+  rp.sp = ip.sp; rp.sp.pool_cap = 32; rp.sp.hbits = 5;
+  rp.links0 = links0; rp.upper_links = upper_links; rp.row_owner = owner.p;
+  rp.touched = touched.p; rp.counters = counters.p; rp.roff = roff; rp.g_src = g_src.p; rp.g_d = g_d.p;
+  rp.rcount = rcount; rp.rfill = rfill; rp.stats = stats.p;
+
+  uint32_t ep = 0;
+  int maxlevel = levels[0];                                    // first element: entry point, nothing to link (:1255-1258)
+  uint64_t batches = 1, biggest = 0;
+  size_t s = 1;
+  int rc = 0;
+  while (s < n && rc == 0) {
+    size_t e;
+    if (levels[s] > maxlevel) e = s + 1;
+    else {
+      size_t b = std::min(bmax, std::max<size_t>(1, s / ratio));
+      e = std::min(n, s + b);
+      for (size_t i = s + 1; i < e; i++)
+        if (levels[i] > maxlevel) { e = i; break; }
+    }
+    batches++;
+    const size_t total = (e - s) * nlev * M;
+    cudaMemsetAsync(rev_row.p, 0xFF, total * 4, st);
+    cudaMemsetAsync(counters.p, 0, 4 * 4, st);
+    ip.s = (uint32_t)s; ip.e = (uint32_t)e; ip.sp.ep = ep; ip.sp.maxlevel = maxlevel;
+    rc = launch_insert(h, ip, ipm);
+    if (rc) break;
+    uint32_t hc[4];
+    cudaMemcpyAsync(hc, counters.p, sizeof hc, cudaMemcpyDeviceToHost, st);
+    cudaError_t ce = cudaStreamSynchronize(st);
+    if (ce != cudaSuccess) { rc = set_err(h, B200ANN_ERR_CUDA, std::string("hnsw_build: ") + cudaGetErrorString(ce)); break; }
+    if (hc[0]) {
+      biggest = std::max<uint64_t>(biggest, hc[1]);
+      rev_offsets_kernel<<<(hc[0] + 255) / 256, 256, 0, st>>>(touched.p, counters.p, rcount, roff, counters.p + 2);
+      rev_group_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(rev_row.p, rev_src.p, rev_d.p, total, roff, rfill, g_src.p, g_d.p);
+      h->launches += 2;
+      rp.mcap = round_up((uint32_t)maxM0 + hc[1], 32);
+      rc = launch_reverse(h, rp, hc[0], ipm);
+      if (rc) break;
+    }
+    for (size_t i = s; i < e; i++)
+      if (levels[i] > maxlevel) { maxlevel = levels[i]; ep = (uint32_t)i; }   // :1262-1265
+    s = e;
+  }
+  unsigned long long hs[4] = {0, 0, 0, 0};
+  if (rc == 0) {
+    cudaMemcpyAsync(hs, stats.p, sizeof hs, cudaMemcpyDeviceToHost, st);
+    cudaError_t ce = cudaStreamSynchronize(st);
+    if (ce == cudaSuccess) ce = cudaGetLastError();
+    if (ce != cudaSuccess) rc = set_err(h, B200ANN_ERR_CUDA, std::string("hnsw_build: ") + cudaGetErrorString(ce));
+  }
+  if (rc) {
+    cudaFree(links0); cudaFree(upper_links); cudaFree(d_upper_ptr); cudaFree(d_levels); if (d_labels) cudaFree(d_labels);
+    return rc;
+  }
+  // install (the caller freed any previous HNSW graph)
+  ix->links0 = links0; ix->maxM0 = maxM0; ix->levels = d_levels; ix->upper_ptr = d_upper_ptr;
+  ix->upper_links = upper_links; ix->upper_rows = rows; ix->maxM = maxM; ix->labels = d_labels;
+  ix->hnsw_ep = ep; ix->maxlevel = maxlevel; ix->has_hnsw = true;
+  if (info8) {
+    info8[0] = hs[0]; info8[1] = hs[1]; info8[2] = hs[2]; info8[3] = batches; info8[4] = rows;
+    info8[5] = (uint64_t)maxlevel; info8[6] = ep; info8[7] = biggest;
+  }
+  return 0;
+}

@@ -112,49 +112,6 @@ struct TopRec {  // Beam callback: every evaluated node goes to the collector (L
   }
 };
 
-// ---------------------------------------------------------------- occlusion scan
-// The rule shared by sync_prune (:328-345) and InterInsert (:386-404): scan sorted candidates
-// [start,end), keep p iff no kept r has r.id == p.id or d(r,p) < d(q,p); stop at R kept.
-// Kept rows are compared 2*TPW at a time; the first kept entry must be placed by the caller or by
-// passing nres == 0 (then the first candidate is kept unconditionally, like `result.push_back(pool[start])`).
-template <class B>
-__device__ __forceinline__ void occlude_scan(B &b, const float *sd, const uint32_t *si, uint32_t start,
-                                             uint32_t end, uint32_t R, uint32_t *res_i, float *res_d,
-                                             uint32_t &nres, uint32_t &n_eval) {
-  constexpr int TPW = B::TPW;
-  for (uint32_t s = start; s < end && nres < R; s++) {
-    const uint32_t pid = si[s];
-    const float pd = sd[s];
-    bool occ = false;
-    if (nres > 0) {
-      const float4 *prow = reinterpret_cast<const float4 *>(b.p.vec + (size_t)pid * b.p.stride);
-#pragma unroll
-      for (int c = 0; c < B::NCHUNK; c++) {
-        int ch = b.t + c * B::TEAMSZ;
-        b.qreg[c] = ch < b.p.nch ? ld_row16_ca(prow + ch) : make_float4(0.f, 0.f, 0.f, 0.f);
-      }
-      for (uint32_t t0 = 0; t0 < nres && !occ; t0 += 2 * TPW) {
-        uint32_t i0 = t0 + b.g, i1 = t0 + TPW + b.g;
-        const float4 *r0 = nullptr, *r1 = nullptr;
-        uint32_t id0 = INVALID_ID, id1 = INVALID_ID;
-        if (i0 < nres) { id0 = res_i[i0]; r0 = reinterpret_cast<const float4 *>(b.p.vec + (size_t)id0 * b.p.stride); }
-        if (i1 < nres) { id1 = res_i[i1]; r1 = reinterpret_cast<const float4 *>(b.p.vec + (size_t)id1 * b.p.stride); }
-        float d0, d1;
-        team_dist2<B::TEAMSZ, B::NCHUNK, B::IS_IP, true>(r0, r1, b.qreg, b.t, b.p.nch, d0, d1);
-        bool o = (i0 < nres && (id0 == pid || d0 < pd)) || (i1 < nres && (id1 == pid || d1 < pd));
-        occ = __any_sync(0xffffffffu, o);
-        n_eval += min(nres - t0, (uint32_t)(2 * TPW));
-      }
-    }
-    if (!occ) {
-      __syncwarp();
-      if (b.lane == 0) { res_i[nres] = pid; res_d[nres] = pd; }
-      nres++;
-      __syncwarp();
-    }
-  }
-}
-
 // ---------------------------------------------------------------- init_graph: centroid
 // center[j] = (sum over rows in index order of x[i][j]) / n, one thread per dimension so that the
 // fp32 additions happen in the reference's order (:290-297). Loads are unrolled to keep several

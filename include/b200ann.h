@@ -74,6 +74,25 @@ int b200ann_index_set_hnsw(b200ann_index_t ix, const uint32_t *links0, size_t ma
                            size_t maxM, const uint64_t *labels /* NULL = identity */, uint32_t ep,
                            int maxlevel);
 
+/* replaces the hnswlib construction loop: HierarchicalNSW(space, n, M, ef_construction, random_seed) followed by
+ * addPoint(row i, label i) for i = 0..n-1 (hnswlib/hnswlib/hnswalg.h:89-144 ctor, :954-992 / :1153-1267 addPoint,
+ * :225-305 searchBaseLayer, :443-483 getNeighborsByHeuristic2, :506-630 mutuallyConnectNewElement; driven like
+ * hnswlib/tests/cpp/sift_1m.cpp:321-336). Levels are drawn exactly like the reference (:206-210, same generator
+ * and seed); rows are inserted in batches (DESIGN.md "HNSW build"): ratio = rows already inserted per new row of a
+ * batch (0 = 32), bmax = largest batch (0 = 8192). labels [n] (NULL = row number) are what addPoint's `label` is.
+ * On success the index holds the HNSW graph (b200ann_hnsw_search, b200ann_index_get_hnsw, hybrid search).
+ * info (optional, 8 x u64): {beam distance evaluations, expanded nodes, heuristic distance evaluations, batches,
+ * upper rows, maxlevel, entry point, largest reverse-link group}. */
+int b200ann_hnsw_build(b200ann_handle_t h, b200ann_index_t ix, size_t M, size_t ef_construction, uint32_t random_seed,
+                       size_t ratio, size_t bmax, const uint64_t *labels /*[h|d] or NULL*/, uint64_t *info /*[h]*/);
+/* sizes of the index's HNSW graph: {maxM0, maxM, upper_rows, maxlevel, entry point} */
+int b200ann_index_hnsw_shape(b200ann_index_t ix, uint64_t *out5 /*[h]*/);
+/* copy the HNSW graph back in the layout b200ann_index_set_hnsw takes (what HierarchicalNSW::saveIndex
+ * serialises, hnswalg.h:685-713): links0 [n,maxM0], levels [n], upper_ptr [n], upper_links [upper_rows,maxM],
+ * labels [n]; any pointer may be NULL. */
+int b200ann_index_get_hnsw(b200ann_index_t ix, uint32_t *links0 /*[h|d]*/, int32_t *levels, uint32_t *upper_ptr,
+                           uint32_t *upper_links, uint64_t *labels);
+
 /* ---- exact brute-force kNN ---------------------------------------------------------------- */
 /* replaces hnswlib::BruteforceSearch::searchKnn (bruteforce.h:106-135) and
  * IndexGraph::generate_control_set (efanna_graph/src/index_graph.cpp:138-153), batched.

@@ -1490,3 +1490,270 @@ EXPORT int orc_nndescent_batch(const float *data, size_t n, size_t dim, size_t s
   if (info) { info[0] = n_dist; info[1] = n_offer; info[2] = info[3] = 0; }
   return rc;
 }
+
+/* ================================================================== HNSW construction (hnswlib addPoint) */
+/* std::default_random_engine (libstdc++: minstd_rand0, x <- 16807 x mod 2^31-1) driving
+ * std::uniform_real_distribution<double>(0,1) = std::generate_canonical<double,53>: two draws,
+ * (x1-1) + (x2-1)*R over R^2 with R = 2147483646 (bits/random.tcc), then
+ * HierarchicalNSW::getRandomLevel (hnswalg.h:206-210): (int)(-log(u) * mult), mult = 1/log(M) (:114). */
+EXPORT void orc_hnsw_levels(size_t n, unsigned M, uint32_t seed, int32_t *levels) {
+  uint64_t x = seed % 2147483647ULL;
+  if (x == 0) x = 1;
+  const long double r = 2147483646.0L;
+  const double mult = 1.0 / log(1.0 * M);
+  for (size_t i = 0; i < n; i++) {
+    double sum = 0.0, tmp = 1.0;
+    for (int k = 0; k < 2; k++) {
+      x = (x * 16807ULL) % 2147483647ULL;
+      sum += (double)(x - 1) * tmp;
+      tmp = (double)((long double)tmp * r);
+    }
+    double u = sum / tmp;
+    if (u >= 1.0) u = nextafter(1.0, 0.0);
+    levels[i] = (int)(-log(u) * mult);
+  }
+}
+
+typedef struct {
+  const float *data; size_t n, dim, stride; int mode;
+  unsigned M, maxM, maxM0, efc;
+  uint32_t *links0, *cnt0;            /* [n,maxM0], [n] */
+  const int32_t *levels; uint32_t *upper_ptr, *upper_links, *cntu;   /* [n], [n], [rows,maxM], [rows] */
+  uint32_t ep; int maxlevel;
+  uint32_t *visited, tag;             /* epoch array like VisitedList (visited_list_pool.h:10-31) */
+  uint64_t n_dist;
+} hb_t;
+static uint32_t *hb_row(hb_t *h, uint32_t node, int level, uint32_t **cnt, unsigned *cap) {
+  if (level == 0) { *cnt = &h->cnt0[node]; *cap = h->maxM0; return h->links0 + (size_t)node * h->maxM0; }
+  size_t r = (size_t)h->upper_ptr[node] + (level - 1);
+  *cnt = &h->cntu[r]; *cap = h->maxM;
+  return h->upper_links + r * h->maxM;
+}
+static float hb_dist(hb_t *h, const float *a, uint32_t id) {
+  h->n_dist++;
+  return orc_dist(h->mode, a, h->data + h->stride * (size_t)id, h->dim);
+}
+/* searchBaseLayer (hnswalg.h:225-305; no deleted elements). variant 0: the reference's two heaps;
+ * variant 1: the CUDA kernel's single ascending (d,id) pool with expanded flags (see hnsw_base_pool).
+ * out: <= efc pairs ascending (d,id); returns the count. */
+static size_t hb_search(hb_t *h, uint32_t ep, const float *q, int level, int variant, orc_pair *top, orc_pair *cand,
+                        uint8_t *expanded) {
+  const size_t ef = h->efc;
+  uint32_t tag = ++h->tag;
+  size_t nt = 0, nc = 0;
+  uint32_t *cnt; unsigned cap;
+  float dist = hb_dist(h, q, ep);
+  orc_pair e = {dist, ep};
+  h->visited[ep] = tag;
+  if (variant == 0) {
+    float lowerBound = dist;
+    hpush(top, &nt, e, +1);
+    hpush(cand, &nc, e, -1);
+    while (nc) {
+      orc_pair cur = cand[0];
+      if (cur.d > lowerBound && nt == ef) break;                  /* :245-247 */
+      hpop(cand, &nc, -1);
+      const uint32_t *row = hb_row(h, cur.id, level, &cnt, &cap);
+      for (unsigned j = 0; j < *cnt; j++) {
+        uint32_t cid = row[j];
+        if (h->visited[cid] == tag) continue;
+        h->visited[cid] = tag;
+        float d = hb_dist(h, q, cid);
+        if (nt < ef || lowerBound > d) {                          /* :284 */
+          orc_pair c = {d, cid};
+          hpush(cand, &nc, c, -1);
+          hpush(top, &nt, c, +1);
+          if (nt > ef) hpop(top, &nt, +1);
+          lowerBound = top[0].d;
+        }
+      }
+    }
+    qsort(top, nt, sizeof(orc_pair), pair_cmp);
+    return nt;
+  }
+  top[0] = e; expanded[0] = 0; nt = 1;
+  for (;;) {
+    size_t k = 0;
+    while (k < nt && expanded[k]) k++;
+    if (k == nt) break;
+    expanded[k] = 1;
+    const uint32_t *row = hb_row(h, top[k].id, level, &cnt, &cap);
+    for (unsigned j = 0; j < *cnt; j++) {
+      uint32_t cid = row[j];
+      if (h->visited[cid] == tag) continue;
+      h->visited[cid] = tag;
+      orc_pair c = {hb_dist(h, q, cid), cid};
+      if (nt < ef || c.d < top[nt - 1].d) {
+        size_t pos = nt;
+        while (pos > 0 && pair_less(c, top[pos - 1])) pos--;
+        size_t last = nt < ef ? nt : ef - 1;
+        for (size_t t = last; t > pos; t--) { top[t] = top[t - 1]; expanded[t] = expanded[t - 1]; }
+        top[pos] = c; expanded[pos] = 0;
+        if (nt < ef) nt++;
+      }
+    }
+  }
+  return nt;
+}
+/* getNeighborsByHeuristic2 (hnswalg.h:443-483): fewer than M candidates -> all kept; otherwise scan in
+ * ascending distance (ties by id here; the reference's pair heap pops the larger id first) and keep c iff
+ * no kept r has d(r,c) < d(q,c); stop at M. In/out: c[0..n) -> the kept ones, ascending. returns count. */
+static size_t hb_heuristic(hb_t *h, orc_pair *c, size_t n, size_t M) {
+  qsort(c, n, sizeof(orc_pair), pair_cmp);
+  if (n < M) return n;
+  size_t kept = 0;
+  for (size_t i = 0; i < n && kept < M; i++) {
+    int good = 1;
+    for (size_t r = 0; r < kept; r++) {
+      float cur = hb_dist(h, h->data + h->stride * (size_t)c[r].id, c[i].id);
+      if (cur < c[i].d) { good = 0; break; }
+    }
+    if (good) c[kept++] = c[i];
+  }
+  return kept;
+}
+static void hb_write_row(uint32_t *row, uint32_t *cnt, const orc_pair *sel, size_t k) {
+  for (size_t i = 0; i < k; i++) row[i] = sel[k - 1 - i].id;      /* popped from a max-heap: farthest first (:514-517,:611-615) */
+  *cnt = (uint32_t)k;
+}
+/* greedy descent of addPoint (hnswalg.h:1214-1239) from level `from` down to `to`+1 */
+static uint32_t hb_descend(hb_t *h, const float *q, uint32_t cur, int from, int to) {
+  float curdist = hb_dist(h, q, cur);
+  uint32_t *cnt; unsigned cap;
+  for (int level = from; level > to; level--) {
+    int changed = 1;
+    while (changed) {
+      changed = 0;
+      const uint32_t *row = hb_row(h, cur, level, &cnt, &cap);
+      unsigned size = *cnt;
+      for (unsigned i = 0; i < size; i++) {
+        uint32_t cand = row[i];
+        float d = hb_dist(h, q, cand);
+        if (d < curdist) { curdist = d; cur = cand; changed = 1; }
+      }
+    }
+  }
+  return cur;
+}
+
+/* Builds the HNSW graph of rows 0..n-1 inserted in index order (hnswlib addPoint loop, e.g.
+ * hnswlib/tests/cpp/sift_1m.cpp:321-336 run with one thread). Flat outputs as parse_hnsw / b200ann_index_set_hnsw:
+ * links0 [n,maxM0], levels [n] (input: from orc_hnsw_levels), upper_ptr [n], upper_links [rows,maxM] with
+ * rows = sum(levels), all padded with ORC_INVALID. ep_out/maxlevel_out.
+ * variant 0: the reference statement for statement, one point at a time (pinned to the compiled reference).
+ * variant 1: the CUDA path's batch form (csrc/hnsw_build.cu): points are inserted in batches of
+ *   min(bmax, max(1, inserted/ratio)) (a point whose level exceeds the current top level is a batch of its own);
+ *   every point of a batch searches the graph as it was BEFORE the batch (single-pool beam) and selects its M
+ *   links with the heuristic; then, per (neighbour, level), all new reverse links are merged at once: appended in
+ *   ascending id if they fit in Mmax, else the heuristic runs over existing + new (the reference does the same
+ *   one reverse link at a time, :554-627). Order independent inside a batch.
+ * info [4] = {distance evaluations, batches, 0, 0}. */
+typedef struct { uint32_t row_node; int level; uint32_t src; float d; } hb_rev;
+static int rev_cmp(const void *x, const void *y) {
+  const hb_rev *a = (const hb_rev *)x, *b = (const hb_rev *)y;
+  if (a->row_node != b->row_node) return a->row_node < b->row_node ? -1 : 1;
+  if (a->level != b->level) return a->level < b->level ? -1 : 1;
+  return a->src < b->src ? -1 : (a->src > b->src ? 1 : 0);
+}
+EXPORT size_t orc_hnsw_batch_end(size_t s, size_t n, const int32_t *levels, int maxlevel, unsigned ratio, unsigned bmax) {
+  if (s == 0 || levels[s] > maxlevel) return s + 1;
+  size_t b = s / ratio;
+  if (b < 1) b = 1;
+  if (b > bmax) b = bmax;
+  size_t e = s + b < n ? s + b : n;
+  for (size_t i = s + 1; i < e; i++)
+    if (levels[i] > maxlevel) return i;
+  return e;
+}
+EXPORT int orc_hnsw_build(const float *data, size_t n, size_t dim, size_t stride, unsigned M, unsigned efc, int mode,
+                          int variant, unsigned ratio, unsigned bmax, const int32_t *levels, uint32_t *links0,
+                          uint32_t *upper_ptr, uint32_t *upper_links, uint32_t *ep_out, int *maxlevel_out, uint64_t *info) {
+  hb_t h; memset(&h, 0, sizeof h);
+  h.data = data; h.n = n; h.dim = dim; h.stride = stride; h.mode = mode;
+  h.M = M; h.maxM = M; h.maxM0 = 2 * M; h.efc = efc > M ? efc : M;   /* hnswalg.h:104-107 */
+  h.links0 = links0; h.levels = levels; h.upper_ptr = upper_ptr; h.upper_links = upper_links;
+  size_t rows = 0;
+  for (size_t i = 0; i < n; i++) { upper_ptr[i] = (uint32_t)rows; rows += (size_t)levels[i]; }
+  h.cnt0 = (uint32_t *)calloc(n, 4); h.cntu = (uint32_t *)calloc(rows ? rows : 1, 4);
+  h.visited = (uint32_t *)calloc(n, 4);
+  size_t capc = h.efc + h.maxM0 + 8;
+  orc_pair *top = (orc_pair *)malloc(sizeof(orc_pair) * (capc + 1)), *cand = (orc_pair *)malloc(sizeof(orc_pair) * (n + 1));
+  uint8_t *expanded = (uint8_t *)malloc(capc + 1);
+  orc_pair *tmp = (orc_pair *)malloc(sizeof(orc_pair) * (h.maxM0 + bmax + 8));
+  hb_rev *rev = NULL; size_t nrev = 0, caprev = 0;
+  uint64_t batches = 0;
+  h.ep = ORC_INVALID; h.maxlevel = -1;
+  size_t s = 0;
+  while (s < n) {
+    size_t e = variant == 0 ? s + 1 : orc_hnsw_batch_end(s, n, levels, h.maxlevel, ratio, bmax);
+    batches++;
+    nrev = 0;
+    for (size_t p = s; p < e; p++) {
+      const float *q = data + stride * p;
+      int curlevel = levels[p];
+      if (h.ep == ORC_INVALID) continue;                           /* first element: nothing to link (:1255-1258) */
+      uint32_t cur = h.ep;
+      if (curlevel < h.maxlevel) cur = hb_descend(&h, q, cur, h.maxlevel, curlevel);
+      for (int level = curlevel < h.maxlevel ? curlevel : h.maxlevel; level >= 0; level--) {
+        size_t nt = hb_search(&h, cur, q, level, variant, top, cand, expanded);
+        size_t k = hb_heuristic(&h, top, nt, h.M);                 /* mutuallyConnectNewElement :513 */
+        uint32_t *cnt; unsigned cap;
+        uint32_t *row = hb_row(&h, (uint32_t)p, level, &cnt, &cap);
+        hb_write_row(row, cnt, top, k);
+        cur = top[0].id;                                           /* next_closest_entry_point = closest selected (:520) */
+        for (size_t i = 0; i < k; i++) {
+          if (variant == 0) {                                      /* :554-627, one reverse link at a time */
+            uint32_t sn = top[k - 1 - i].id;
+            uint32_t *ocnt; unsigned ocap;
+            uint32_t *orow = hb_row(&h, sn, level, &ocnt, &ocap);
+            if (*ocnt < ocap) { orow[(*ocnt)++] = (uint32_t)p; continue; }
+            size_t m = 0;
+            tmp[m].d = hb_dist(&h, q, sn); tmp[m].id = (uint32_t)p; m++;
+            for (unsigned j = 0; j < *ocnt; j++) {
+              tmp[m].d = hb_dist(&h, data + stride * (size_t)orow[j], sn); tmp[m].id = orow[j]; m++;
+            }
+            size_t kk = hb_heuristic(&h, tmp, m, ocap);
+            hb_write_row(orow, ocnt, tmp, kk);
+          } else {
+            if (nrev == caprev) { caprev = caprev ? caprev * 2 : 4096; rev = (hb_rev *)realloc(rev, caprev * sizeof(hb_rev)); }
+            rev[nrev].row_node = top[i].id; rev[nrev].level = level; rev[nrev].src = (uint32_t)p; rev[nrev].d = top[i].d;
+            nrev++;
+          }
+        }
+      }
+    }
+    if (variant != 0 && nrev) {
+      qsort(rev, nrev, sizeof(hb_rev), rev_cmp);
+      for (size_t a = 0; a < nrev;) {
+        size_t b = a;
+        while (b < nrev && rev[b].row_node == rev[a].row_node && rev[b].level == rev[a].level) b++;
+        uint32_t sn = rev[a].row_node;
+        uint32_t *ocnt; unsigned ocap;
+        uint32_t *orow = hb_row(&h, sn, rev[a].level, &ocnt, &ocap);
+        if (*ocnt + (b - a) <= ocap) {
+          for (size_t t = a; t < b; t++) orow[(*ocnt)++] = rev[t].src;
+        } else {
+          size_t m = 0;
+          for (unsigned j = 0; j < *ocnt; j++) {
+            tmp[m].d = hb_dist(&h, data + stride * (size_t)sn, orow[j]); tmp[m].id = orow[j]; m++;
+          }
+          for (size_t t = a; t < b; t++) { tmp[m].d = rev[t].d; tmp[m].id = rev[t].src; m++; }
+          size_t kk = hb_heuristic(&h, tmp, m, ocap);
+          hb_write_row(orow, ocnt, tmp, kk);
+        }
+        a = b;
+      }
+    }
+    for (size_t p = s; p < e; p++)
+      if (h.ep == ORC_INVALID || levels[p] > h.maxlevel) { h.ep = (uint32_t)p; h.maxlevel = levels[p]; }  /* :1256-1265 */
+    s = e;
+  }
+  for (size_t i = 0; i < n; i++)
+    for (unsigned j = h.cnt0[i]; j < h.maxM0; j++) links0[i * h.maxM0 + j] = ORC_INVALID;
+  for (size_t r = 0; r < rows; r++)
+    for (unsigned j = h.cntu[r]; j < h.maxM; j++) upper_links[r * h.maxM + j] = ORC_INVALID;
+  *ep_out = h.ep; *maxlevel_out = h.maxlevel;
+  if (info) { info[0] = h.n_dist; info[1] = batches; info[2] = info[3] = 0; }
+  free(h.cnt0); free(h.cntu); free(h.visited); free(top); free(cand); free(expanded); free(tmp); free(rev);
+  return 0;
+}

@@ -77,6 +77,12 @@ def oracle():
                                           C.c_uint, C.c_uint, C.c_int, u32p, C.c_void_p]
         lib.orc_nndescent_batch.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_uint, C.c_uint, C.c_uint,
                                             C.c_uint, C.c_uint, C.c_uint32, C.c_int, u32p, C.c_void_p, C.c_void_p]
+        lib.orc_hnsw_levels.argtypes = [C.c_size_t, C.c_uint, C.c_uint32, i32p]
+        lib.orc_hnsw_batch_end.restype = C.c_size_t
+        lib.orc_hnsw_batch_end.argtypes = [C.c_size_t, C.c_size_t, i32p, C.c_int, C.c_uint, C.c_uint]
+        lib.orc_hnsw_build.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_uint, C.c_uint, C.c_int, C.c_int,
+                                       C.c_uint, C.c_uint, i32p, u32p, u32p, u32p, C.POINTER(C.c_uint32),
+                                       C.POINTER(C.c_int), C.c_void_p]
         _oracle = lib
     return _oracle
 
@@ -222,6 +228,31 @@ def orc_nndescent_batch(base, K, L, it, S, R_, mode, seed=1):
     rc = oracle().orc_nndescent_batch(base, n, dim, dim, K, L, it, S, R_, seed, mode, knn, _vp(d), _vp(info))
     assert rc >= 0
     return knn, d, info
+
+
+def orc_hnsw_levels(n, M, seed=100):
+    lv = np.zeros(n, np.int32)
+    oracle().orc_hnsw_levels(n, M, seed, lv)
+    return lv
+
+
+def orc_hnsw_build(base, M, efc, mode, variant, ratio=16, bmax=4096, seed=100, label0=0):
+    """hnswlib addPoint loop over rows 0..n-1 -> the flat dict parse_hnsw returns. variant 0 = the reference one
+    point at a time, 1 = the CUDA path's batch form."""
+    n, dim = base.shape
+    lv = orc_hnsw_levels(n, M, seed)
+    rows = int(lv.sum())
+    links0 = np.zeros((n, 2 * M), np.uint32)
+    upper_ptr = np.zeros(n, np.uint32)
+    upper = np.zeros((max(rows, 1), M), np.uint32)
+    ep, ml = C.c_uint32(0), C.c_int(0)
+    info = np.zeros(4, np.uint64)
+    rc = oracle().orc_hnsw_build(base, n, dim, dim, M, efc, mode, variant, ratio, bmax, lv, links0, upper_ptr, upper,
+                                 C.byref(ep), C.byref(ml), _vp(info))
+    assert rc == 0
+    return dict(n=n, dim=dim, M=M, maxM=M, maxM0=2 * M, efc=max(efc, M), ep=ep.value, maxlevel=ml.value, links0=links0,
+                levels=lv, upper_ptr=upper_ptr, upper_links=upper[:rows], labels=np.arange(n, dtype=np.uint64) + label0,
+                info=info)
 
 
 def orc_merge_topk(d, ids, kout):

@@ -383,3 +383,60 @@ def test_nndescent_batch_form_properties():
             both = (knn[:, S - 2] != R.INVALID) & (prev[0][:, S - 2] != R.INVALID)
             assert (d[both, S - 2] <= prev[1][both, S - 2]).all()
         prev = (knn, d)
+
+
+# ---------------------------------------------------------------- HNSW construction (addPoint loop)
+@needs_ref
+@pytest.mark.parametrize("n,dim,M,efc,metric", [(3000, 16, 8, 40, 0), (4000, 32, 16, 100, 0), (2000, 24, 6, 30, 1),
+                                              (1200, 8, 4, 8, 0)])
+def test_hnsw_build_ref_form_vs_reference(tmp_path, n, dim, M, efc, metric):
+    """orc_hnsw_build variant 0 == the UNMODIFIED hnswlib addPoint loop run with one thread, link for link:
+    levels (std::default_random_engine + uniform_real_distribution restated), entry point, every level-0 and
+    upper-level list in the reference's own order (float data: no distance ties)."""
+    base = R.data_uniform(n, dim, 3) if metric == 0 else R.data_glove_like(n, dim, 3)
+    ref = R.RefHnsw(metric, dim, n, M, efc)
+    ref.add(base, label0=0, threads=1)
+    path = str(tmp_path / "h.bin")
+    ref.save(path)
+    Hr = R.parse_hnsw(path)
+    Ho = R.orc_hnsw_build(base, M, efc, R.L2_SCALAR if metric == 0 else R.IP_SCALAR, 0)
+    assert (Hr["levels"] == Ho["levels"]).all()
+    assert Hr["ep"] == Ho["ep"] and Hr["maxlevel"] == Ho["maxlevel"]
+    assert (Hr["links0"] == Ho["links0"]).all()
+    assert Hr["upper_links"].shape == Ho["upper_links"].shape and (Hr["upper_links"] == Ho["upper_links"]).all()
+
+
+def test_hnsw_build_batch_form_quality_and_schedule():
+    """the batch form (what the GPU computes): same levels / entry point as the one-at-a-time form, every list within
+    its capacity and free of self links and duplicates, links only between nodes that exist on that level, and search
+    recall at matched ef within 0.005 of the one-at-a-time form (default ratio)."""
+    n, dim, M, efc = 6000, 32, 12, 100
+    base = R.data_uniform(n, dim, 5)
+    q = R.data_uniform(400, dim, 6)
+    H0 = R.orc_hnsw_build(base, M, efc, R.L2_SCALAR, 0)
+    H1 = R.orc_hnsw_build(base, M, efc, R.L2_SCALAR, 1, ratio=32, bmax=8192)
+    assert (H0["levels"] == H1["levels"]).all() and H0["ep"] == H1["ep"] and H0["maxlevel"] == H1["maxlevel"]
+    assert int(H1["info"][1]) < n // 8
+    for i in range(0, n, 37):
+        row = H1["links0"][i][H1["links0"][i] != R.INVALID]
+        assert i not in row and len(set(row.tolist())) == len(row)
+    up = H1["upper_links"]
+    for i in np.nonzero(H1["levels"] > 0)[0][:200]:
+        for l in range(1, H1["levels"][i] + 1):
+            row = up[H1["upper_ptr"][i] + l - 1]
+            row = row[row != R.INVALID]
+            assert (H1["levels"][row] >= l).all() and i not in row
+    truth, _ = R.orc_bf_knn(base, q, 10, R.L2_SCALAR)
+    for ef in (10, 30, 100):
+        r0 = R.recall(R.orc_hnsw_search(base, H0, q, 10, ef, R.L2_SCALAR)[0].astype(np.uint32), truth)
+        r1 = R.recall(R.orc_hnsw_search(base, H1, q, 10, ef, R.L2_SCALAR)[0].astype(np.uint32), truth)
+        assert r1 >= r0 - 0.005, (ef, r1, r0)
+    # schedule: first row alone, a level-raising row alone, sizes bounded by inserted / ratio and bmax
+    lv = H1["levels"]
+    s, ml = 0, -1
+    while s < n:
+        e = R.oracle().orc_hnsw_batch_end(s, n, lv, ml, 32, 64)
+        assert s < e <= n and e - s <= max(1, min(64, s // 32))
+        assert all(lv[i] <= ml for i in range(s + 1, e))
+        ml = max(ml, int(lv[s:e].max()))
+        s = e

@@ -296,7 +296,7 @@ int hnsw_build_launch(b200ann_handle *h, b200ann_index *ix, size_t M, size_t efc
   if (M < 2 || M > 128 || n >= (1ull << 31))
     return set_err(h, B200ANN_ERR_ARG, "hnsw_build: need 2 <= M <= 128");
   if (efc < M) efc = M;                                        // hnswalg.h:107
-  if (ratio == 0) ratio = 32;
+  if (ratio == 0) ratio = 64;
   if (bmax == 0) bmax = 8192;
   const size_t maxM = M, maxM0 = 2 * M;
   cudaStream_t st = h->stream;

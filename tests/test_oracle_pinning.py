@@ -412,11 +412,11 @@ def test_hnsw_build_batch_form_quality_and_schedule():
     recall at matched ef within 0.005 of the one-at-a-time form (default ratio)."""
     n, dim, M, efc = 6000, 32, 12, 100
     base = R.data_uniform(n, dim, 5)
-    q = R.data_uniform(400, dim, 6)
+    q = R.data_uniform(2000, dim, 6)
     H0 = R.orc_hnsw_build(base, M, efc, R.L2_SCALAR, 0)
-    H1 = R.orc_hnsw_build(base, M, efc, R.L2_SCALAR, 1, ratio=32, bmax=8192)
+    H1 = R.orc_hnsw_build(base, M, efc, R.L2_SCALAR, 1, ratio=64, bmax=8192)   # the product's default schedule
     assert (H0["levels"] == H1["levels"]).all() and H0["ep"] == H1["ep"] and H0["maxlevel"] == H1["maxlevel"]
-    assert int(H1["info"][1]) < n // 8
+    assert int(H1["info"][1]) < n // 8   # batches
     for i in range(0, n, 37):
         row = H1["links0"][i][H1["links0"][i] != R.INVALID]
         assert i not in row and len(set(row.tolist())) == len(row)
@@ -427,7 +427,7 @@ def test_hnsw_build_batch_form_quality_and_schedule():
             row = row[row != R.INVALID]
             assert (H1["levels"][row] >= l).all() and i not in row
     truth, _ = R.orc_bf_knn(base, q, 10, R.L2_SCALAR)
-    for ef in (10, 30, 100):
+    for ef in (20, 50, 100):
         r0 = R.recall(R.orc_hnsw_search(base, H0, q, 10, ef, R.L2_SCALAR)[0].astype(np.uint32), truth)
         r1 = R.recall(R.orc_hnsw_search(base, H1, q, 10, ef, R.L2_SCALAR)[0].astype(np.uint32), truth)
         assert r1 >= r0 - 0.005, (ef, r1, r0)

@@ -84,6 +84,7 @@ struct Beam {
   int lane, t, g;
   uint32_t np, cap;
   uint32_t n_dist, n_hops;
+  uint32_t never = INVALID_ID;  // a node load_row(filter) always drops, even after the visited set forgot it
   int lvl = 0;  // HNSW only: the layer expand_all walks (0 = links0 rows, l >= 1 = the node's upper row l-1)
 
   __device__ __forceinline__ Beam(const SearchParams &pp, uint32_t *smem_base) : p(pp) {
@@ -157,7 +158,7 @@ struct Beam {
       uint32_t j = j0 + lane;
       uint32_t id = (j < rowlen && j < limit) ? ld_adj(row + j) : INVALID_ID;
       bool valid = id != INVALID_ID;
-      if (valid && filter) valid = !test_and_set(id);
+      if (valid && filter) valid = id != never && !test_and_set(id);
       unsigned mask = __ballot_sync(0xffffffffu, valid);
       if (valid) cand_i[m + __popc(mask & ((1u << lane) - 1))] = id;
       m += __popc(mask);
@@ -286,6 +287,7 @@ struct Beam {
   // neighbour (:720-728; init_ids is zero-initialised, :707); slots holding that 0 are evaluated
   // without being flagged (:741-747).
   __device__ __forceinline__ void seed_from(uint32_t ep, uint32_t qidx) {
+    never = ep;  // flagged but never evaluated (:711-712): must stay excluded when the hash set forgets it
     test_and_set_uniform(ep);
     uint32_t m = load_row(p.graph + (size_t)ep * p.gstride, p.gstride, p.L, false);
     for (uint32_t j = lane; j < m; j += 32) test_and_set(cand_i[j]);

@@ -241,8 +241,13 @@ class BruteforceSearch : public AlgorithmInterface<dist_t> {
   mutable std::mutex mu_;
 };
 
-// hnswlib::HierarchicalNSW (hnswalg.h:18-1411), query side: load an index written by
-// HierarchicalNSW::saveIndex (:685-713), search it on the GPU, write it back in the same format.
+// hnswlib::HierarchicalNSW (hnswalg.h:18-1411): build with the construction ctor + addPoint, or load an index
+// written by HierarchicalNSW::saveIndex (:685-713); search it on the GPU; write it back in the same format.
+// addPoint copies the vector (like :1204) into a host staging area; the graph is built on the GPU
+// (b200ann_hnsw_build: same level sequence as the reference, batched insertion) by build(), or lazily by the
+// first searchKnn / saveIndex after an addPoint. Adding a point to a built index rebuilds it on the next use:
+// add in bulk, then search. addPoint with an existing label replaces that element's vector (the reference's
+// updatePoint, :1158-1175, re-links in place).
 template <typename dist_t>
 class HierarchicalNSW : public AlgorithmInterface<dist_t> {
  public:
@@ -253,6 +258,18 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
   tableint enterpoint_node_ = 0;
   std::vector<int> element_levels_;
 
+  // construction ctor (hnswalg.h:89-144)
+  HierarchicalNSW(SpaceInterface<dist_t> *s, size_t max_elements, size_t M = 16, size_t ef_construction = 200,
+                  size_t random_seed = 100, bool = false, int device = 0)
+      : gpu_(device) {
+    detail::space_info(s, metric_, dim_);
+    max_elements_ = max_elements;
+    M_ = M <= 10000 ? M : 10000;                       // :98-104
+    maxM_ = M_; maxM0_ = M_ * 2;
+    ef_construction_ = ef_construction > M_ ? ef_construction : M_;   // :107
+    mult_ = 1 / std::log(1.0 * (double)M_);            // :114
+    seed_ = random_seed;
+  }
   // load ctor (hnswalg.h:78-86)
   HierarchicalNSW(SpaceInterface<dist_t> *s, const std::string &location, bool = false, size_t max_elements = 0, bool = false, int device = 0)
       : gpu_(device) {
@@ -286,6 +303,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
       labeltype lab;
       std::memcpy(&lab, row + label_offset, sizeof(labeltype));
       labels_[i] = lab;
+      label_lookup_[lab] = i;
     }
     const size_t slpe = maxM_ * 4 + 4;  // size_links_per_element_ (:113)
     element_levels_.assign(n, 0); upper_ptr_.assign(n, 0); upper_links_.clear();
@@ -311,6 +329,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
 
   // hnswalg.h:685-713, byte-compatible with the reference's loader
   void saveIndex(const std::string &location) override {
+    { std::unique_lock<std::mutex> lock(mu_); build_locked(nullptr); }
     std::ofstream out(location, std::ios::binary);
     const size_t n = cur_element_count;
     size_t size_links_level0 = maxM0_ * 4 + 4, data_size = dim_ * sizeof(float);
@@ -347,14 +366,34 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     }
   }
 
-  void addPoint(const void *, labeltype, bool = false) override {
-    throw std::runtime_error("HierarchicalNSW::addPoint: GPU construction is not available in this build; load an index with loadIndex");
+  // hnswalg.h:954-992 / :1153-1267. Thread-safe (the drivers call it from omp / ParallelFor loops); internal ids are
+  // handed out in arrival order like cur_element_count++ (:1181).
+  void addPoint(const void *datapoint, labeltype label, bool = false) override {
+    std::unique_lock<std::mutex> lock(mu_);
+    auto it = label_lookup_.find(label);
+    if (it != label_lookup_.end()) {
+      std::memcpy(&vec_[it->second * dim_], datapoint, dim_ * sizeof(float));
+      dirty_ = true;
+      return;
+    }
+    if (cur_element_count >= max_elements_) throw std::runtime_error("The number of elements exceeds the specified limit");  // :1178
+    label_lookup_[label] = cur_element_count;
+    vec_.insert(vec_.end(), (const float *)datapoint, (const float *)datapoint + dim_);
+    labels_.push_back(label);
+    cur_element_count++;
+    dirty_ = true;
+  }
+  // builds the graph of everything added so far on the GPU (no-op when up to date). info8: b200ann_hnsw_build's.
+  void build(uint64_t *info8 = nullptr) {
+    std::unique_lock<std::mutex> lock(mu_);
+    build_locked(info8);
   }
 
   // [nq,k] rows, ascending distance; throws when some row has fewer than k results (bindings.cpp:646-648)
   void searchKnnBatch(const float *queries, size_t nq, size_t k, labeltype *labels, dist_t *dists) const {
     std::vector<uint64_t> lab(nq * k);
     std::unique_lock<std::mutex> lock(mu_);
+    build_locked(nullptr);
     detail::check(gpu_.h, b200ann_hnsw_search(gpu_.h, ix_, queries, nq, dim_, k, ef_, lab.data(), dists, nullptr), "HierarchicalNSW::searchKnn");
     for (size_t i = 0; i < nq * k; i++) labels[i] = (labeltype)lab[i];
   }
@@ -370,6 +409,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
       std::vector<dist_t> d(kk);
       {
         std::unique_lock<std::mutex> lock(mu_);
+        build_locked(nullptr);
         size_t ef = ef_ > kk ? ef_ : kk;
         int rc = b200ann_hnsw_search(gpu_.h, ix_, (const float *)query_data, 1, dim_, kk, ef, lab.data(), d.data(), nullptr);
         if (rc != 0 && rc != B200ANN_ERR_FEWER) detail::check(gpu_.h, rc, "HierarchicalNSW::searchKnn");
@@ -402,13 +442,40 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
                                                  upper_links_.empty() ? nullptr : upper_links_.data(), upper_links_.size() / (maxM_ ? maxM_ : 1),
                                                  maxM_, lab.data(), enterpoint_node_, maxlevel_), "b200ann_index_set_hnsw");
   }
+  // GPU construction of the staged points; caller holds mu_
+  void build_locked(uint64_t *info8) const {
+    if (!dirty_) return;
+    HierarchicalNSW *self = const_cast<HierarchicalNSW *>(this);
+    if (self->ix_) { b200ann_index_destroy(self->ix_); self->ix_ = nullptr; }
+    const size_t n = cur_element_count;
+    if (n == 0) { dirty_ = false; return; }
+    detail::check(gpu_.h, b200ann_index_create(gpu_.h, vec_.data(), n, dim_, dim_, metric_, &self->ix_), "b200ann_index_create");
+    std::vector<uint64_t> lab(labels_.begin(), labels_.end());
+    detail::check(gpu_.h, b200ann_hnsw_build(gpu_.h, ix_, M_, ef_construction_, (uint32_t)seed_, 0, 0, lab.data(), info8),
+                  "HierarchicalNSW::addPoint (b200ann_hnsw_build)");
+    uint64_t shape[5];
+    detail::check(gpu_.h, b200ann_index_hnsw_shape(ix_, shape), "b200ann_index_hnsw_shape");
+    self->links0_.assign(n * maxM0_, B200ANN_INVALID);
+    self->upper_ptr_.assign(n, 0);
+    self->upper_links_.assign((size_t)shape[2] * maxM_, B200ANN_INVALID);
+    std::vector<int32_t> lv(n);
+    detail::check(gpu_.h, b200ann_index_get_hnsw(ix_, self->links0_.data(), lv.data(), self->upper_ptr_.data(),
+                                                 shape[2] ? self->upper_links_.data() : nullptr, nullptr), "b200ann_index_get_hnsw");
+    self->element_levels_.assign(lv.begin(), lv.end());
+    self->maxlevel_ = (int)shape[3];
+    self->enterpoint_node_ = (tableint)shape[4];
+    dirty_ = false;
+  }
   detail::Gpu gpu_;
   int metric_ = 0;
   size_t dim_ = 0;
+  size_t seed_ = 100;
   std::vector<float> vec_;
   std::vector<labeltype> labels_;
+  std::unordered_map<labeltype, size_t> label_lookup_;
   std::vector<uint32_t> links0_, upper_ptr_, upper_links_;
   b200ann_index_t ix_ = nullptr;
+  mutable bool dirty_ = false;
   mutable std::mutex mu_;
 };
 

@@ -94,6 +94,44 @@ int main(int argc, char **argv) {
     try { hnswlib::HierarchicalNSW<float> bad(&space, std::string("/nonexistent/file.bin")); } catch (std::runtime_error &) { threw = true; }
     CHECK(threw);
   }
+  {  // ---- construction through the reference API (hnswlib/examples/cpp/example_search.cpp): addPoint loop from
+     // several threads, searchKnn of every stored point finds itself, capacity error, saveIndex -> load ctor
+    int dim = 16; size_t n = 3000;
+    std::mt19937 rng(47);
+    std::uniform_real_distribution<float> u(0.f, 1.f);
+    std::vector<float> data(n * dim);
+    for (auto &v : data) v = u(rng);
+    hnswlib::L2Space space(dim);
+    hnswlib::HierarchicalNSW<float> *alg = new hnswlib::HierarchicalNSW<float>(&space, n, 16, 200);
+#pragma omp parallel for
+    for (long i = 0; i < (long)n; i++) alg->addPoint(data.data() + (size_t)i * dim, (hnswlib::labeltype)(i + 10));
+    bool threw = false;
+    try { alg->addPoint(data.data(), 999999); } catch (std::runtime_error &) { threw = true; }
+    CHECK(threw);  // hnswalg.h:1178
+    uint64_t info[8];
+    alg->build(info);
+    CHECK(alg->cur_element_count == n && alg->maxlevel_ >= 1 && alg->M_ == 16 && alg->maxM0_ == 32);
+    float correct = 0;
+    for (size_t i = 0; i < n; i++) {
+      auto r = alg->searchKnn(data.data() + i * dim, 1);
+      CHECK(r.size() == 1);
+      if (r.top().second == alg->getExternalLabel((hnswlib::tableint)i) || r.top().first == 0.f) correct++;
+    }
+    printf("GPU-built index: n=%zu self-recall %.4f batches %llu\n", n, correct / n, (unsigned long long)info[3]);
+    CHECK(correct / n > 0.99);  // example_search.cpp prints this recall
+    if (argc > 1) {
+      std::string out = std::string(argv[1]) + ".gpubuilt";
+      alg->saveIndex(out);
+      hnswlib::HierarchicalNSW<float> again(&space, out);
+      CHECK(again.cur_element_count == n && again.maxlevel_ == alg->maxlevel_ && again.enterpoint_node_ == alg->enterpoint_node_);
+      std::vector<hnswlib::labeltype> a(10 * 5), b(10 * 5); std::vector<float> da(50), db(50);
+      alg->setEf(50); again.setEf(50);
+      alg->searchKnnBatch(data.data(), 10, 5, a.data(), da.data());
+      again.searchKnnBatch(data.data(), 10, 5, b.data(), db.data());
+      CHECK(a == b && da == db);
+    }
+    delete alg;
+  }
   printf("hnswlib shim ok\n");
   return 0;
 }

@@ -16,7 +16,7 @@ LIBDIR = os.path.join(R.ROOT, "hnsw-nsg_b200")
 def _build(name, tmp):
     exe = os.path.join(str(tmp), name)
     src = os.path.join(R.ROOT, "tests", "cpp", name + ".cpp")
-    subprocess.check_call(["g++", "-std=c++11", "-O2", "-I" + INC, src, "-o", exe, "-L" + LIBDIR, "-lb200ann",
+    subprocess.check_call(["g++", "-std=c++11", "-O2", "-fopenmp", "-I" + INC, src, "-o", exe, "-L" + LIBDIR, "-lb200ann",
                            "-Wl,-rpath," + LIBDIR])
     return exe
 
@@ -65,3 +65,10 @@ def test_hnswlib_shim_driver(tmp_path):
     a, ad = ref.search(q, 10, 50, threads=1)
     b, bd = again.search(q, 10, 50, threads=1)
     assert (a == b).all() and (ad == bd).all()
+    # the index the shim BUILT on the GPU (addPoint + build + saveIndex) loads in the unmodified reference, which
+    # finds every stored point as its own nearest neighbour
+    built = R.RefHnsw(0, 16, path=path + ".gpubuilt")
+    rng = np.random.RandomState(0)
+    Hb = R.parse_hnsw(path + ".gpubuilt")
+    lab, dd = built.search(np.ascontiguousarray(Hb["vectors"][:200]), 1, 50, threads=1)
+    assert (lab[:, 0] == Hb["labels"][:200]).mean() > 0.99

@@ -162,6 +162,62 @@ def write_nsg(path, graph, ep, width, invalid=0xFFFFFFFF):
     out.tofile(path)
 
 
+def other_builds(B, h, ix, base, knn_exact, info):
+    """the two other construction paths of SURVEY 8(a), timed on the same 1M x 128 rows (reported under "build"):
+    NN-descent (efanna IndexGraph::Build, the README's SIFT1M parameters K=200 L=200 iter=10 S=10 R=100) and the
+    HNSW addPoint loop (M=16 efC=200). Each also gets the UNMODIFIED reference timed on a bounded row sample."""
+    import torch
+    n = base.shape[0]
+    K, L, IT, S, R_ = KNN_K, 200, 10, 10, 100
+    out = torch.empty((n, K), dtype=torch.int32, device="cuda")
+    t = time.time()
+    _, ninfo = ix.nndescent(K, L, IT, S, R_, seed=1, out=out)
+    info["nndescent_s"] = time.time() - t
+    info["nndescent_device_ms"] = h.last_kernel_ms
+    a, b = out[:20000].cpu().numpy(), knn_exact[:20000].cpu().numpy()
+    rec = float(np.mean([len(set(a[i].tolist()) & set(b[i].tolist())) / K for i in range(0, 20000, 10)]))
+    # algorithmic bytes of the local join: two rows gathered per distance evaluation
+    info["nndescent"] = dict(ninfo, K=K, L=L, iter=IT, S=S, R=R_, recall_vs_exact=round(rec, 4),
+                             join_gather_GBps=ninfo["dist_evals"] * 2 * DIM * 4 / max(1e-9, ninfo["join_us"] * 1e-6) / 1e9)
+    del out
+    log("rank 0: NN-descent K=%d in %.2fs (%s)" % (K, info["nndescent_s"], info["nndescent"]))
+    t = time.time()
+    hinfo = ix.hnsw_build(16, 200, seed=100)
+    info["hnsw_build_s"] = time.time() - t
+    info["hnsw_build_device_ms"] = h.last_kernel_ms
+    bytes_ = (hinfo["beam_evals"] + hinfo["heuristic_evals"]) * DIM * 4 + hinfo["hops"] * 33 * 4
+    info["hnsw"] = dict(hinfo, M=16, efc=200, gather_GBps=bytes_ / (h.last_kernel_ms * 1e-3) / 1e9)
+    log("rank 0: HNSW build M=16 efC=200 in %.2fs (%s)" % (info["hnsw_build_s"], info["hnsw"]))
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import refutil as R
+        import tempfile
+        if R.have_ref():
+            m = 50000
+            sub = np.ascontiguousarray(base[:m])
+            threads = os.cpu_count() or 1
+            t = time.time()
+            R.ref_nndescent(sub, K, L, IT, S, R_, os.path.join(tempfile.mkdtemp(), "g"), seed=1, threads=0, lib="efanna_fast")
+            t_nd = time.time() - t
+            ref = R.RefHnsw(0, DIM, m, 16, 200, lib="hnsw_fast")
+            t = time.time()
+            ref.add(sub, label0=0, threads=0)
+            t_h = time.time() - t
+            ref.close()
+            sx = B.Index(h, sub, B.L2)
+            sx.nndescent(K, L, IT, S, R_, seed=1)
+            g_nd = h.last_kernel_ms * 1e-3
+            sx.hnsw_build(16, 200)
+            g_h = h.last_kernel_ms * 1e-3
+            sx.close()
+            info["build_cpu_reference"] = {"sample": "first %d rows, unmodified reference from oracle/_ref (-O3/-Ofast builds), OpenMP" % m,
+                                           "cores": threads, "nndescent_s": t_nd, "nndescent_gpu_same_rows_s": g_nd,
+                                           "hnsw_addpoint_s": t_h, "hnsw_gpu_same_rows_s": g_h}
+            log("rank 0: reference builds on %d rows: %s" % (m, info["build_cpu_reference"]))
+    except Exception as e:  # the build baselines are extras; the headline never depends on them
+        log("build cpu reference skipped: %r" % (e,))
+
+
 def build_index(B, h, base, q, rank):
     """upload, exact ground truth, exact kNN graph (K=200), NSG build, L_search sweep.
     Returns (ix, info). The graph is cached in /tmp so that the second arm on the same box reuses it."""
@@ -201,6 +257,8 @@ def build_index(B, h, base, q, rank):
         info["nsg_build_device_ms"] = h.last_kernel_ms
         info["nsg"] = bi
         log("rank %d: NSG build in %.2fs %s" % (rank, info["nsg_build_s"], bi))
+        if rank == 0:
+            other_builds(B, h, ix, base, knn, info)
         del knn
         torch.cuda.empty_cache()
         g, ep, width = ix.get_graph()
@@ -407,7 +465,8 @@ def run_ours(args):
                          "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": alg_bytes,
                          "dist_evals_per_query": n_dist / nq, "hops_per_query": n_hops / nq},
             "build": {k: info.get(k) for k in ("knn_graph_s", "knn_graph_kernel_ms", "knn_graph_stats", "knn_graph_roofline", "nsg_build_s", "nsg_build_device_ms",
-                                               "nsg", "graph_from_cache", "gt_ms")},
+                                               "nsg", "nndescent_s", "nndescent_device_ms", "nndescent", "hnsw_build_s",
+                                               "hnsw_build_device_ms", "hnsw", "build_cpu_reference", "graph_from_cache", "gt_ms")},
         }
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1

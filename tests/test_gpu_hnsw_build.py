@@ -84,6 +84,44 @@ def test_hnsw_build_search_recall_vs_reference(B, H, tmp_path, metric):
         assert rg >= rr - 0.005, (ef, rg, rr)
 
 
+@pytest.mark.parametrize("n,dim,M,efc,kind", [
+    (1, 8, 4, 10, "u"), (2, 8, 4, 10, "u"), (40, 16, 16, 50, "u"),   # lists never fill; first element alone
+    (3000, 32, 8, 60, "s"),                                          # integer-valued rows: exact distance ties
+    (1500, 8, 6, 40, "dup"),                                         # every vector stored twice: zero distances
+])
+def test_hnsw_build_edge_cases_vs_oracle(B, H, n, dim, M, efc, kind):
+    if kind == "u":
+        base = R.data_uniform(n, dim, 5)
+    elif kind == "s":
+        base = R.data_sift_like(n, dim, 5)
+    else:
+        half = R.data_uniform(n // 2, dim, 5)
+        base = np.ascontiguousarray(np.concatenate([half, half]))
+    ix = B.Index(H, base, 0)
+    ix.hnsw_build(M, efc, ratio=8, bmax=512)
+    G = ix.get_hnsw()
+    R.oracle().orc_set_gpu_team(B.dist_team(dim))
+    O = R.orc_hnsw_build(base, M, efc, R.L2_GPU, 1, ratio=8, bmax=512)
+    assert G["ep"] == O["ep"] and G["maxlevel"] == O["maxlevel"]
+    assert (G["links0"] == O["links0"]).all()
+    assert G["upper_links"].shape == O["upper_links"].shape and (G["upper_links"] == O["upper_links"]).all()
+    if n > 1:
+        lab, d = ix.hnsw_search(base[:min(n, 64)], 1, 30)
+        assert (d[:, 0] == 0).all()                                   # every stored point finds itself (or its twin)
+
+
+def test_hnsw_build_is_deterministic_and_rebuildable(B, H):
+    base = R.data_sift_like(8000, 48, 2)
+    ix = B.Index(H, base, 0)
+    a = ix.hnsw_build(16, 100)
+    Ga = ix.get_hnsw()
+    b = ix.hnsw_build(16, 100)           # rebuilding replaces the graph
+    Gb = ix.get_hnsw()
+    assert a == b and (Ga["links0"] == Gb["links0"]).all() and (Ga["upper_links"] == Gb["upper_links"]).all()
+    c = ix.hnsw_build(16, 100, seed=7)   # another level sequence -> another graph
+    assert (ix.get_hnsw()["levels"] != Ga["levels"]).any()
+
+
 def test_hnsw_build_labels_and_errors(B, H):
     base = R.data_uniform(600, 8, 1)
     ix = B.Index(H, base, 0)

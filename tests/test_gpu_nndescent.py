@@ -83,6 +83,23 @@ def test_nndescent_feeds_nsg_build(B, H):
     assert R.recall(ids, truth) > 0.95
 
 
+def test_nndescent_small_and_duplicate_rows(B, H):
+    """smallest legal n (2S+2 rows), and a dataset where every vector is stored twice (zero distances, ties)."""
+    base = R.data_uniform(10, 8, 1)
+    ix = B.Index(H, base, B.L2)
+    knn, d, _ = ix.nndescent(3, 5, 3, 4, 4, seed=2, want_dists=True)
+    o, od, _ = R.orc_nndescent_batch(base, 3, 5, 3, 4, 4, R.L2_SEQ_FMA, seed=2)
+    assert (knn == o).all() and (d.view(np.uint32) == od.view(np.uint32)).all()
+    half = R.data_uniform(1000, 16, 3)
+    base = np.ascontiguousarray(np.concatenate([half, half]))
+    ix = B.Index(H, base, B.L2)
+    knn, d, _ = ix.nndescent(10, 20, 6, 6, 10, seed=2, want_dists=True)
+    o, od, _ = R.orc_nndescent_batch(base, 10, 20, 6, 6, 10, R.L2_SEQ_FMA, seed=2)
+    assert (knn == o).all() and (d.view(np.uint32) == od.view(np.uint32)).all()
+    twin = (np.arange(2000) + 1000) % 2000
+    assert (knn[:, 0] == twin).mean() > 0.9 and (d[knn[:, 0] == twin, 0] == 0).all()
+
+
 def test_nndescent_argument_errors(B, H):
     base = R.data_uniform(500, 16, 1)
     ix = B.Index(H, base, B.L2)

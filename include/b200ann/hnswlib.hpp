@@ -427,11 +427,13 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
   const float *getDataByInternalId(tableint internal_id) const { return &vec_[(size_t)internal_id * dim_]; }
   b200ann_handle_t handle() const { return gpu_.h; }
   b200ann_index_t device_index() const { return ix_; }
+  size_t generation() const { return gen_; }  // bumped whenever the device index is re-created
 
  private:
   template <typename T> static void rd(std::istream &in, T &v) { in.read((char *)&v, sizeof(T)); }
   template <typename T> static void wr(std::ostream &out, const T &v) { out.write((const char *)&v, sizeof(T)); }
   void upload() {
+    gen_++;
     if (ix_) { b200ann_index_destroy(ix_); ix_ = nullptr; }
     const size_t n = cur_element_count;
     if (n == 0) return;
@@ -464,12 +466,14 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     self->element_levels_.assign(lv.begin(), lv.end());
     self->maxlevel_ = (int)shape[3];
     self->enterpoint_node_ = (tableint)shape[4];
+    self->gen_++;
     dirty_ = false;
   }
   detail::Gpu gpu_;
   int metric_ = 0;
   size_t dim_ = 0;
   size_t seed_ = 100;
+  size_t gen_ = 0;
   std::vector<float> vec_;
   std::vector<labeltype> labels_;
   std::unordered_map<labeltype, size_t> label_lookup_;

@@ -21,7 +21,7 @@ def _build(name, tmp):
     return exe
 
 
-@pytest.mark.parametrize("name", ["test_efanna_shim", "test_hnswlib_shim"])
+@pytest.mark.parametrize("name", ["test_efanna_shim", "test_hnswlib_shim", "test_hybrid_shim"])
 def test_shims_compile_and_fail_loudly_without_gpu(tmp_path, name):
     exe = _build(name, tmp_path)
     try:
@@ -72,3 +72,23 @@ def test_hnswlib_shim_driver(tmp_path):
     Hb = R.parse_hnsw(path + ".gpubuilt")
     lab, dd = built.search(np.ascontiguousarray(Hb["vectors"][:200]), 1, 50, threads=1)
     assert (lab[:, 0] == Hb["labels"][:200]).mean() > 0.99
+
+
+@pytest.mark.gpu
+def test_hybrid_shim_driver(tmp_path):
+    """hnsw_nsg::HNSW_NSG through the shim: build (addPoint + Build_NSG), search, saveIndex, load ctor; then the
+    UNMODIFIED reference hybrid loads the pair of files the shim wrote and reaches the same recall."""
+    exe = _build("test_hybrid_shim", tmp_path)
+    p = subprocess.run([exe, str(tmp_path)], capture_output=True, text=True)
+    print(p.stdout, p.stderr)
+    assert p.returncode == 0
+    if R.have_ref():
+        prefix = str(tmp_path / "hyshim")
+        Hb = R.parse_hnsw(prefix + "_hnsw.bin")
+        base = np.ascontiguousarray(Hb["vectors"])
+        assert (Hb["labels"] == np.arange(len(base))).all()
+        q = R.data_uniform(300, base.shape[1], 77)
+        truth, _ = R.orc_bf_knn(base, q, 10, R.L2_SCALAR)
+        hy = R.RefHybrid(base, prefix, 60)
+        ids = hy.search(q, 10, 10, seed=1)
+        assert R.recall(ids[:, :10], truth) > 0.9

@@ -317,6 +317,10 @@ int hnsw_build_launch(b200ann_handle *h, b200ann_index *ix, size_t M, size_t efc
   uint32_t *links0 = nullptr, *upper_links = nullptr, *d_upper_ptr = nullptr;
   int32_t *d_levels = nullptr;
   uint64_t *d_labels = nullptr;
+  struct Guard {  // frees the graph arrays unless the build succeeded and handed them to the index
+    uint32_t *&a, *&b, *&c; int32_t *&d; uint64_t *&e; bool keep = false;
+    ~Guard() { if (!keep) { cudaFree(a); cudaFree(b); cudaFree(c); cudaFree(d); cudaFree(e); } }
+  } guard{links0, upper_links, d_upper_ptr, d_levels, d_labels};
   CU_CHECK(h, cudaMalloc((void **)&links0, n * maxM0 * 4));
   CU_CHECK(h, cudaMalloc((void **)&upper_links, (rows ? rows : 1) * maxM * 4));
   CU_CHECK(h, cudaMalloc((void **)&d_upper_ptr, n * 4));
@@ -412,10 +416,8 @@ int hnsw_build_launch(b200ann_handle *h, b200ann_index *ix, size_t M, size_t efc
     if (ce == cudaSuccess) ce = cudaGetLastError();
     if (ce != cudaSuccess) rc = set_err(h, B200ANN_ERR_CUDA, std::string("hnsw_build: ") + cudaGetErrorString(ce));
   }
-  if (rc) {
-    cudaFree(links0); cudaFree(upper_links); cudaFree(d_upper_ptr); cudaFree(d_levels); if (d_labels) cudaFree(d_labels);
-    return rc;
-  }
+  if (rc) return rc;
+  guard.keep = true;
   // install (the caller freed any previous HNSW graph)
   ix->links0 = links0; ix->maxM0 = maxM0; ix->levels = d_levels; ix->upper_ptr = d_upper_ptr;
   ix->upper_links = upper_links; ix->upper_rows = rows; ix->maxM = maxM; ix->labels = d_labels;

@@ -652,8 +652,12 @@ int nndescent_launch(b200ann_handle *h, const b200ann_index *ix, size_t K, size_
   CU_CHECK(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, join_kernel, JT, smem));
   if (occ < 1) return set_err(h, B200ANN_ERR_ARG, "nndescent: sample lists do not fit in shared memory (S, R too large)");
   const unsigned jgrid = (unsigned)std::min<size_t>((size_t)h->sm_count * occ, n);
-  cudaEvent_t e0, e1, e2;
-  CU_CHECK(h, cudaEventCreate(&e0)); CU_CHECK(h, cudaEventCreate(&e1)); CU_CHECK(h, cudaEventCreate(&e2));
+  struct Events {  // destroyed on every return path
+    cudaEvent_t e[3] = {nullptr, nullptr, nullptr};
+    ~Events() { for (auto x : e) if (x) cudaEventDestroy(x); }
+  } evs;
+  for (auto &x : evs.e) CU_CHECK(h, cudaEventCreate(&x));
+  cudaEvent_t e0 = evs.e[0], e1 = evs.e[1], e2 = evs.e[2];
   float join_ms = 0.f, upd_ms = 0.f;
   for (size_t it = 0; it < iter; ++it) {
     cudaMemsetAsync(stats.p + 3, 0, sizeof(unsigned long long), st);
@@ -680,7 +684,6 @@ int nndescent_launch(b200ann_handle *h, const b200ann_index *ix, size_t K, size_
     }
 #endif
   }
-  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
   extract_kernel<<<h->sm_count * 8, 256, 0, st>>>(s, knn, knn_d);
   h->launches++;
   CU_CHECK(h, cudaGetLastError());

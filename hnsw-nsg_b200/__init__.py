@@ -53,6 +53,7 @@ _lib.b200ann_nsg_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, C.c_uint3
 _lib.b200ann_hnsw_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _vp, _vp, _vp]
 _u32 = C.c_uint32
 _lib.b200ann_nsg_search_from.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _u32, _vp, _vp, _vp, _vp]
+_lib.b200ann_nsg_search_clustered.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _u32, _vp, _vp, _vp, _vp, _vp, _vp]
 _lib.b200ann_hybrid_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _u32, _vp, _vp, _vp, _vp]
 _lib.b200ann_set_link_visited_bits.argtypes = [_vp, C.c_int]
 _lib.b200ann_nsg_build.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _u32, _u32, _vp]
@@ -72,7 +73,7 @@ EXPORTS = [
     "b200ann_set_link_visited_bits", "b200ann_nsg_build", "b200ann_nsg_init_ep", "b200ann_nsg_link",
     "b200ann_nsg_interinsert", "b200ann_nsg_finish", "b200ann_merge_topk", "b200ann_nsg_search_from",
     "b200ann_hybrid_search", "b200ann_set_knn_mode", "b200ann_knn_last_stats", "b200ann_nndescent",
-    "b200ann_hnsw_build", "b200ann_index_hnsw_shape", "b200ann_index_get_hnsw",
+    "b200ann_hnsw_build", "b200ann_index_hnsw_shape", "b200ann_index_get_hnsw", "b200ann_nsg_search_clustered",
 ]
 
 
@@ -330,6 +331,18 @@ class Index:
         st = np.zeros((q.shape[0], 2), np.uint32) if want_stats else None
         self.h._check(_lib.b200ann_nsg_search_from(self.h._h, self._ix, _ptr(q), q.shape[0], q.shape[1], K, L, seed,
                                                    _ptr(entry), _ptr(ids), _ptr(d), _ptr(st)))
+        return (ids, d, st) if want_stats else (ids, d)
+
+    def nsg_search_clustered(self, q, ep, base, size, K, L, seed=0, want_stats=False):
+        """query i searches the cluster (ep[i], base[i], size[i]) of a block-diagonal graph; size 0 = skip"""
+        q = np.ascontiguousarray(q, np.float32)
+        nq = q.shape[0]
+        ep, base, size = (np.ascontiguousarray(a, np.uint32) for a in (ep, base, size))
+        ids = np.empty((nq, K), np.uint32)
+        d = np.empty((nq, K), np.float32)
+        st = np.zeros((nq, 2), np.uint32) if want_stats else None
+        self.h._check(_lib.b200ann_nsg_search_clustered(self.h._h, self._ix, _ptr(q), nq, q.shape[1], K, L, seed, _ptr(ep),
+                                                        _ptr(base), _ptr(size), _ptr(ids), _ptr(d), _ptr(st)))
         return (ids, d, st) if want_stats else (ids, d)
 
     def hybrid_search(self, q, K, L, seed=0, want_stats=False):

@@ -43,7 +43,10 @@ struct SearchParams {
   uint32_t K, L, seed; int hbits;
   uint32_t qidx_base;           // query index fed to the seed hash = qidx_base + query
   int mode;                     // non-HNSW kernels: 0 = Search from ep, 2 = hybrid (HNSW descent, then
-                                // SearchFromEnterpoint), 3 = SearchFromEnterpoint from entry[query]
+                                // SearchFromEnterpoint), 3 = SearchFromEnterpoint from entry[query],
+                                // 4 = Search inside one cluster per query (block-diagonal graph):
+                                //     entry[q] = the cluster's navigating node, cl_base/cl_size = its rows
+  const uint32_t *cl_base, *cl_size;  // mode 4: [nq]; cl_size 0 = the query is skipped
   uint32_t ep_hnsw;             // mode 2: enterpoint_node_ of the HNSW levels
   const uint32_t *entry;        // mode 3: [nq]
   uint32_t *entry_out;          // mode 2: [nq] or NULL
@@ -340,6 +343,29 @@ struct Beam {
     eval(m);
     rec(cand_i, cand_d, m, true);
     seeds_to_pool(m, true);
+  }
+
+  // seed_nsg for a query confined to the rows [base, base + size) of a block-diagonal graph (one NSG per cluster,
+  // ids global): the per-cluster IndexNSG::Search of CNNS/tests/cluster_hnsw_nsg_search.cpp:203-207. The random
+  // fill draws inside the cluster (rand() % nd_ there is the cluster's own nd_); a cluster smaller than L is
+  // searched with a pool of its size.
+  __device__ __forceinline__ void seed_nsg_local(uint32_t qidx, uint32_t ep, uint32_t base, uint32_t size) {
+    const uint32_t Lq = p.L < size ? p.L : size;
+    uint32_t m = load_row(p.graph + (size_t)ep * p.gstride, p.gstride, Lq, false);
+    uint32_t ctr = 0;
+    while (m < Lq) {
+      uint32_t id = base + seed_hash(p.seed, qidx, ctr++) % size;
+      bool hit = false;
+      for (uint32_t j = lane; j < m; j += 32) hit |= cand_i[j] == id;
+      if (!__any_sync(0xffffffffu, hit)) {
+        if (lane == 0) cand_i[m] = id;
+        m++;
+      }
+      __syncwarp();
+    }
+    eval(m);
+    seeds_to_pool(m, true);
+    cap = Lq;
   }
 
   // main loop (index_nsg.cpp:539-564 / hnswalg.h:342-436)

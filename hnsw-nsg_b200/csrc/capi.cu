@@ -376,6 +376,34 @@ int b200ann_nsg_search(b200ann_handle_t h, b200ann_index_t ix, const float *q, s
   return 0;
 }
 
+int b200ann_nsg_search_clustered(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_t nq, size_t qstride,
+                                 size_t K, size_t L, uint32_t seed, const uint32_t *ep, const uint32_t *base,
+                                 const uint32_t *size, uint32_t *ids, float *dists, uint32_t *stats) {
+  if (!h || !ix) return B200ANN_ERR_ARG;
+  if (!ix->graph) return set_err(h, B200ANN_ERR_STATE, "nsg_search_clustered: index has no graph (set_graph first)");
+  if (!q || !ids || !ep || !base || !size || K == 0 || L < K || qstride < ix->dim)
+    return set_err(h, B200ANN_ERR_ARG, "nsg_search_clustered: need q, ids, ep, base, size, 0 < K <= L, qstride >= dim");
+  if (nq == 0) return 0;
+  CU_CHECK(h, cudaSetDevice(h->device));
+  InArg<float> qin; InArg<uint32_t> iep, ib, is; OutArg<uint32_t> oi; OutArg<float> od; OutArg<uint32_t> os;
+  CU_CHECK(h, qin.stage(q, nq * qstride, h->stream));
+  CU_CHECK(h, iep.stage(ep, nq, h->stream));
+  CU_CHECK(h, ib.stage(base, nq, h->stream));
+  CU_CHECK(h, is.stage(size, nq, h->stream));
+  CU_CHECK(h, oi.stage(ids, nq * K, h->stream));
+  CU_CHECK(h, od.stage(dists, nq * K, h->stream));
+  CU_CHECK(h, os.stage(stats, nq * 2, h->stream));
+  CallTimer t(h);
+  int rc = launch_nsg_search_clustered(h, ix, qin.d, nq, qstride, K, L, seed, iep.d, ib.d, is.d, oi.d, od.d, os.d);
+  t.stop();
+  if (rc) return rc;
+  CU_CHECK(h, oi.finish(h->stream));
+  CU_CHECK(h, od.finish(h->stream));
+  CU_CHECK(h, os.finish(h->stream));
+  CU_CHECK(h, t.sync());
+  return 0;
+}
+
 static int search_from_common(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_t nq, size_t qstride,
                               size_t K, size_t L, uint32_t seed, const uint32_t *entry, bool hybrid, uint32_t *ids,
                               float *dists, uint32_t *entry_out, uint32_t *stats, const char *who) {

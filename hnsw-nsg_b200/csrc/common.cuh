@@ -135,6 +135,9 @@ int launch_nsg_search(b200ann_handle *h, const b200ann_index *ix, const float *q
 int launch_nsg_search_from(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
                            size_t K, size_t L, uint32_t seed, const uint32_t *entry, uint32_t *entry_out, uint32_t *ids,
                            float *dists, uint32_t *stats);
+int launch_nsg_search_clustered(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
+                                size_t K, size_t L, uint32_t seed, const uint32_t *ep, const uint32_t *base,
+                                const uint32_t *size, uint32_t *ids, float *dists, uint32_t *stats);
 int launch_hnsw_search(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
                        size_t k, size_t ef, uint64_t *labels, float *dists, uint32_t *stats);
 int launch_bf_knn(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,

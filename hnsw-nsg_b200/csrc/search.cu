@@ -24,6 +24,17 @@ __global__ void __launch_bounds__(WARPS * 32) beam_search_kernel(const SearchPar
     b.descend_hnsw();
   } else if (p.mode == 0) {
     b.seed_nsg(p.qidx_base + qi, rec);
+  } else if (p.mode == 4) {
+    const uint32_t size = __ldg(p.cl_size + qi);
+    if (size == 0) {  // query not routed to any cluster in this pass
+      for (uint32_t i = b.lane; i < p.K; i += 32) {
+        p.ids[(size_t)qi * p.K + i] = INVALID_ID;
+        if (p.dists) p.dists[(size_t)qi * p.K + i] = INFINITY;
+      }
+      if (p.stats && b.lane == 0) { p.stats[2 * (size_t)qi] = 0; p.stats[2 * (size_t)qi + 1] = 0; }
+      return;
+    }
+    b.seed_nsg_local(p.qidx_base + qi, __ldg(p.entry + qi), __ldg(p.cl_base + qi), size);
   } else {
     uint32_t entry;
     if (p.mode == 2) {  // hybrid: HNSW levels >= 1, external label of the node reached = NSG entry
@@ -119,6 +130,22 @@ int launch_nsg_search_from(b200ann_handle *h, const b200ann_index *ix, const flo
     if (ix->maxM > cc) cc = ix->maxM;
   }
   p.cand_cap = round_up((uint32_t)cc, 32);
+  p.pool_cap = round_up((uint32_t)L + 1, 32);
+  p.ids = ids; p.dists = dists; p.stats = stats;
+  return ix->metric == B200ANN_IP ? launch_dim<true, false>(h, p) : launch_dim<false, false>(h, p);
+}
+
+// mode 4: every query searches its own cluster of a block-diagonal graph
+int launch_nsg_search_clustered(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
+                                size_t K, size_t L, uint32_t seed, const uint32_t *ep, const uint32_t *base,
+                                const uint32_t *size, uint32_t *ids, float *dists, uint32_t *stats) {
+  SearchParams p = {};
+  p.vec = ix->vec; p.stride = ix->stride; p.n = (uint32_t)ix->n; p.nch = (int)((ix->dim + 3) / 4);
+  p.graph = ix->graph; p.gstride = (uint32_t)ix->gstride; p.ep = ix->ep;
+  p.q = q; p.qstride = qstride; p.nq = (uint32_t)nq; p.dim = (uint32_t)ix->dim;
+  p.K = (uint32_t)K; p.L = (uint32_t)L; p.seed = seed; p.hbits = h->visited_bits;
+  p.mode = 4; p.entry = ep; p.cl_base = base; p.cl_size = size;
+  p.cand_cap = round_up((uint32_t)(ix->gstride > L ? ix->gstride : L), 32);
   p.pool_cap = round_up((uint32_t)L + 1, 32);
   p.ids = ids; p.dists = dists; p.stats = stats;
   return ix->metric == B200ANN_IP ? launch_dim<true, false>(h, p) : launch_dim<false, false>(h, p);

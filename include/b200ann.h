@@ -166,6 +166,18 @@ int b200ann_hybrid_search(b200ann_handle_t h, b200ann_index_t ix, const float *q
                           float *dists /*[h|d] or NULL*/, uint32_t *entry_out /*[h|d] or NULL*/,
                           uint32_t *stats /*[h|d] or NULL*/);
 
+/* replaces the per-cluster `nsg_index->Search(query, cluster_data, search_K, paras, tmp)` loop of the reference's
+ * cluster drivers (CNNS/tests/cluster_hnsw_nsg_search.cpp:189-215, ..._pipeline.cpp:165-270) for a batch: the index
+ * holds ALL clusters back to back (rows of cluster c = [base_c, base_c + size_c)) under one block-diagonal graph
+ * with global ids (each cluster's NSG shifted by base_c); query i searches the cluster given by ep[i] (that cluster's
+ * navigating node, global id), base[i], size[i] exactly like IndexNSG::Search would search the cluster alone
+ * (random seed fill inside the cluster; a cluster smaller than L is searched with a pool of its size).
+ * size[i] == 0 skips query i (its row is B200ANN_INVALID / +inf). ids are global rows of this index. */
+int b200ann_nsg_search_clustered(b200ann_handle_t h, b200ann_index_t ix, const float *q /*[h|d]*/, size_t nq,
+                                 size_t qstride, size_t K, size_t L, uint32_t seed, const uint32_t *ep /*[h|d] [nq]*/,
+                                 const uint32_t *base /*[h|d] [nq]*/, const uint32_t *size /*[h|d] [nq]*/,
+                                 uint32_t *ids /*[h|d]*/, float *dists /*[h|d] or NULL*/, uint32_t *stats /*[h|d] or NULL*/);
+
 /* ---- shard-result merge (multi-GPU search) ---------------------------------------------------- */
 /* d/ids [parts, nq, k]: per-shard result lists, each row ascending by (distance,id), ids global,
  * unfilled slots +inf / B200ANN_INVALID. out_d (may be NULL) / out_i [nq, kout] = the kout smallest

@@ -478,6 +478,28 @@ EXPORT int orc_nsg_search(const float *data, size_t n, size_t dim, size_t stride
   return 0;
 }
 
+/* same, with the hash stream index of every query given explicitly (qidx [nq]): what one cluster's share of a
+ * routed batch looks like (CNNS/tests/cluster_hnsw_nsg_search.cpp:203-207 runs IndexNSG::Search per (query, cluster);
+ * the product hashes with the query's position in the whole batch). */
+EXPORT int orc_nsg_search_qidx(const float *data, size_t n, size_t dim, size_t stride, const uint32_t *graph,
+                               unsigned gstride, uint32_t ep, const float *q, size_t nq, size_t qstride, unsigned K,
+                               unsigned L, int mode, uint32_t seed, const uint32_t *qidx, uint32_t *ids, float *dists) {
+  if (L < K || L == 0 || L > n) return -1;
+  orc_index ix = {data, n, dim, stride, graph, gstride, mode};
+  uint8_t *flags = (uint8_t *)malloc(n);
+  orc_nb *retset = (orc_nb *)malloc(sizeof(orc_nb) * (L + 1));
+  for (size_t qi = 0; qi < nq; qi++) {
+    memset(flags, 0, n);
+    nsg_beam(&ix, ep, q + qi * qstride, L, 1, seed, qidx[qi], flags, retset, NULL, 0, NULL);
+    for (unsigned i = 0; i < K; i++) {
+      ids[qi * K + i] = retset[i].id;
+      if (dists) dists[qi * K + i] = retset[i].distance;
+    }
+  }
+  free(flags); free(retset);
+  return 0;
+}
+
 /* ------------------------------------------------------------------ HNSW search */
 /* Flat HNSW layout (product device layout, built from hnswlib's saveIndex blob by the host shim):
  *   links0      u32 [n, maxM0]   level-0 lists (hnswalg.h get_linklist0 :486), INVALID padded

@@ -77,6 +77,8 @@ def oracle():
                                           C.c_uint, C.c_uint, C.c_int, u32p, C.c_void_p]
         lib.orc_nndescent_batch.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_uint, C.c_uint, C.c_uint,
                                             C.c_uint, C.c_uint, C.c_uint32, C.c_int, u32p, C.c_void_p, C.c_void_p]
+        lib.orc_nsg_search_qidx.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, u32p, C.c_uint, C.c_uint32, f32p,
+                                            C.c_size_t, C.c_size_t, C.c_uint, C.c_uint, C.c_int, C.c_uint32, u32p, u32p, f32p]
         lib.orc_hnsw_levels.argtypes = [C.c_size_t, C.c_uint, C.c_uint32, i32p]
         lib.orc_hnsw_batch_end.restype = C.c_size_t
         lib.orc_hnsw_batch_end.argtypes = [C.c_size_t, C.c_size_t, i32p, C.c_int, C.c_uint, C.c_uint]
@@ -228,6 +230,17 @@ def orc_nndescent_batch(base, K, L, it, S, R_, mode, seed=1):
     rc = oracle().orc_nndescent_batch(base, n, dim, dim, K, L, it, S, R_, seed, mode, knn, _vp(d), _vp(info))
     assert rc >= 0
     return knn, d, info
+
+
+def orc_nsg_search_qidx(base, graph, ep, q, qidx, K, L, mode, seed=0):
+    n, dim = base.shape
+    nq = q.shape[0]
+    ids = np.empty((nq, K), np.uint32)
+    d = np.empty((nq, K), np.float32)
+    rc = oracle().orc_nsg_search_qidx(base, n, dim, dim, np.ascontiguousarray(graph), graph.shape[1], ep, q, nq, q.shape[1],
+                                      K, L, mode, seed, np.ascontiguousarray(qidx, np.uint32), ids, d)
+    assert rc == 0
+    return ids, d
 
 
 def orc_hnsw_levels(n, M, seed=100):

@@ -30,6 +30,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+os.environ.setdefault("NCCL_DEBUG", "WARN")   # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
 
 N_BASE = int(os.environ.get("B200ANN_BENCH_N", 1000000))
 DIM = 128
@@ -79,8 +80,37 @@ class ClockSampler:
         self.index = index
         self.proc = None
         self.path = None
+        self.nvml = None
+        self.samples = []
+        self.stop_flag = False
+        self.thread = None
+
+    def _nvml_loop(self):
+        # NVML queries take microseconds: a short timed region (tens of ms) still gets dozens of samples,
+        # which nvidia-smi -lms 100 (one process start + 100 ms period) cannot deliver
+        n = self.nvml
+        hd = n.nvmlDeviceGetHandleByIndex(self.index)
+        while not self.stop_flag:
+            try:
+                sm = n.nvmlDeviceGetClockInfo(hd, n.NVML_CLOCK_SM)
+                mx = n.nvmlDeviceGetMaxClockInfo(hd, n.NVML_CLOCK_SM)
+                rs = n.nvmlDeviceGetCurrentClocksEventReasons(hd) if hasattr(n, "nvmlDeviceGetCurrentClocksEventReasons") \
+                    else n.nvmlDeviceGetCurrentClocksThrottleReasons(hd)
+                self.samples.append((sm, mx, rs))
+            except Exception:
+                break
+            time.sleep(0.002)
 
     def start(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nvml = pynvml
+            self.thread = threading.Thread(target=self._nvml_loop, daemon=True)
+            self.thread.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             fd, self.path = tempfile.mkstemp(suffix=".csv")
             os.close(fd)
@@ -92,6 +122,20 @@ class ClockSampler:
 
     def stop(self):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.nvml is not None:
+            self.stop_flag = True
+            self.thread.join(timeout=2)
+            n = self.nvml
+            bits = {"hw_slowdown": getattr(n, "nvmlClocksThrottleReasonHwSlowdown", 0x8),
+                    "hw_thermal_slowdown": getattr(n, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40),
+                    "sw_thermal_slowdown": getattr(n, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20),
+                    "sw_power_cap": getattr(n, "nvmlClocksThrottleReasonSwPowerCap", 0x4)}
+            if self.samples:
+                reasons = sorted(nm for nm, b in bits.items() if any(r & b for _, _, r in self.samples))
+                out = {"sm_mhz": float(np.median([x[0] for x in self.samples])),
+                       "sm_max_mhz": float(max(x[1] for x in self.samples)), "reasons": reasons,
+                       "samples": len(self.samples), "source": "nvml"}
+            return out
         if not self.proc:
             return out
         time.sleep(0.15)
@@ -119,7 +163,7 @@ class ClockSampler:
             pass
         if sm:
             out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
-                   "samples": len(sm)}
+                   "samples": len(sm), "source": "nvidia-smi"}
         return out
 
 
@@ -347,13 +391,19 @@ def run_ours(args):
     out_d = torch.empty((nq, K), dtype=torch.float32, device="cuda")
     torch.cuda.synchronize()
 
+    if world > 1:
+        h.set_async(True)   # search and merge are enqueued on the library's stream; no host sync inside a step
+
     def step_device():
-        ix.nsg_search_raw(q_dev, nq, DIM, K, L, 1, ids_dev, d_dev if world > 1 else None, None)
-        if world > 1:
+        if world == 1:
+            ix.nsg_search_raw(q_dev, nq, DIM, K, L, 1, ids_dev, None, None)
+            return
+        # one stream end to end: search kernel -> local->global ids -> NCCL all-gathers -> merge kernel
+        with torch.cuda.stream(ext):
+            ix.nsg_search_raw(q_dev, nq, DIM, K, L, 1, ids_dev, d_dev, None)
             ids_dev.add_(rank * N_BASE)  # local -> global row ids (u32 stored as i32 bits)
             dist.all_gather_into_tensor(gathered_d, d_dev)
             dist.all_gather_into_tensor(gathered_i, ids_dev)
-            torch.cuda.current_stream().synchronize()
             h.merge_topk_raw(gathered_d, gathered_i, world, nq, K, K, out_d, out_i)
 
     # ---- pinned host buffers for the end-to-end leg
@@ -365,12 +415,13 @@ def run_ours(args):
         if world == 1:
             ix.nsg_search_raw(q_pin, nq, DIM, K, L, 1, ids_pin, None, None)
         else:
-            q_dev.copy_(q_pin, non_blocking=True)
-            torch.cuda.current_stream().synchronize()
+            with torch.cuda.stream(ext):
+                q_dev.copy_(q_pin, non_blocking=True)
             step_device()
-            ids_pin.copy_(out_i, non_blocking=True)
-            d_pin.copy_(out_d, non_blocking=True)
-            torch.cuda.current_stream().synchronize()
+            with torch.cuda.stream(ext):
+                ids_pin.copy_(out_i, non_blocking=True)
+                d_pin.copy_(out_d, non_blocking=True)
+            ext.synchronize()   # the caller holds its results in host memory when the step returns
 
     def barrier():
         if world > 1:
@@ -405,6 +456,9 @@ def run_ours(args):
     step_ms = (dev_ms if world == 1 else wall_ms) / args.steps
     e2e_dev_ms, e2e_wall_ms, _ = timed(step_e2e, args.steps, args.warmup)
     e2e_ms = e2e_wall_ms / args.steps
+    if world > 1:
+        torch.cuda.synchronize()
+        h.set_async(False)   # the accounting below reads b200ann_last_kernel_ms
 
     # ---- correctness of what was timed + roofline accounting (untimed)
     if world == 1:

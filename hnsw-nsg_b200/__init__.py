@@ -62,6 +62,7 @@ _lib.b200ann_nsg_link.argtypes = [_vp, _vp, _vp, _sz, _u32, _sz, _sz, _sz, _u32,
 _lib.b200ann_nsg_interinsert.argtypes = [_vp, _vp, _sz, _vp, _vp, C.POINTER(C.c_uint64)]
 _lib.b200ann_merge_topk.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _vp, _vp]
 _lib.b200ann_set_knn_mode.argtypes = [_vp, C.c_int, C.c_int]
+_lib.b200ann_set_async.argtypes = [_vp, C.c_int]
 _lib.b200ann_knn_last_stats.argtypes = [_vp, _vp]
 _lib.b200ann_nsg_finish.argtypes = [_vp, _vp, _vp, _vp, _sz, _u32, _sz, _u32, _sz, C.POINTER(_u32)]
 
@@ -74,6 +75,7 @@ EXPORTS = [
     "b200ann_nsg_interinsert", "b200ann_nsg_finish", "b200ann_merge_topk", "b200ann_nsg_search_from",
     "b200ann_hybrid_search", "b200ann_set_knn_mode", "b200ann_knn_last_stats", "b200ann_nndescent",
     "b200ann_hnsw_build", "b200ann_index_hnsw_shape", "b200ann_index_get_hnsw", "b200ann_nsg_search_clustered",
+    "b200ann_set_async",
 ]
 
 
@@ -146,6 +148,10 @@ class Handle:
         self._check(_lib.b200ann_knn_last_stats(self._h, out.ctypes.data_as(_vp)))
         keys = ["rows", "fallback_rows", "reranked", "passes", "splits", "shortlist", "tiles", "a_resident"]
         return dict(zip(keys, (int(x) for x in out)))
+
+    def set_async(self, on):
+        """device-to-device nsg_search / merge_topk calls stop synchronizing the stream (see b200ann.h)"""
+        self._check(_lib.b200ann_set_async(self._h, 1 if on else 0))
 
     def set_visited_bits(self, bits):
         self._check(_lib.b200ann_set_visited_bits(self._h, bits))

@@ -286,6 +286,12 @@ static int knn_dispatch(b200ann_handle *h, b200ann_index *ix, const float *q, si
   return launch_bf_knn(h, ix, q, nq, qstride, k, exclude_self, ids, dists);
 }
 
+int b200ann_set_async(b200ann_handle_t h, int on) {
+  if (!h) return B200ANN_ERR_ARG;
+  h->async_mode = on != 0;
+  return 0;
+}
+
 int b200ann_set_knn_mode(b200ann_handle_t h, int mode, int slack) {
   if (!h) return B200ANN_ERR_ARG;
   if (mode < 0 || mode > 2) return set_err(h, B200ANN_ERR_ARG, "set_knn_mode: mode must be 0 (auto), 1 (fp32 SIMT) or 2 (tensor cores)");
@@ -372,6 +378,7 @@ int b200ann_nsg_search(b200ann_handle_t h, b200ann_index_t ix, const float *q, s
   CU_CHECK(h, oi.finish(h->stream));
   CU_CHECK(h, od.finish(h->stream));
   CU_CHECK(h, os.finish(h->stream));
+  if (h->async_mode && !oi.host && !od.host && !os.host && is_device_ptr(q)) return 0;  // stream-ordered, no host sync
   CU_CHECK(h, t.sync());
   return 0;
 }

@@ -23,6 +23,7 @@ struct b200ann_handle {
   int knn_mode = 0;          // 0 auto, 1 fp32 SIMT (bf_knn.cu), 2 tensor cores (knn_tc.cu)
   int knn_slack = -1;        // shortlist slack of the tensor path; < 0 = default
   uint64_t knn_stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  bool async_mode = false;   // b200ann_set_async: device-to-device search / merge calls do not synchronize the stream
 };
 
 struct b200ann_index {

@@ -69,6 +69,7 @@ extern "C" int b200ann_merge_topk(b200ann_handle_t h, const float *d, const uint
   cudaEventRecord(h->ev1, h->stream);
   CU_CHECK(h, od.finish(h->stream));
   CU_CHECK(h, oi.finish(h->stream));
+  if (h->async_mode && !od.host && !oi.host && is_device_ptr(d) && is_device_ptr(ids)) return 0;  // stream-ordered
   CU_CHECK(h, cudaStreamSynchronize(h->stream));
   cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
   return 0;

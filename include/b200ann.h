@@ -187,6 +187,13 @@ int b200ann_nsg_search_clustered(b200ann_handle_t h, b200ann_index_t ix, const f
 int b200ann_merge_topk(b200ann_handle_t h, const float *d /*[h|d]*/, const uint32_t *ids /*[h|d]*/, size_t parts,
                        size_t nq, size_t k, size_t kout, float *out_d /*[h|d]*/, uint32_t *out_i /*[h|d]*/);
 
+/* Stream-ordered mode for pipelines that keep everything on the device (multi-GPU search: search -> all-gather ->
+ * merge): when on, b200ann_nsg_search and b200ann_merge_topk calls whose inputs AND outputs are all device memory
+ * return as soon as their kernels are enqueued on the handle's stream (b200ann_stream); the caller orders later work
+ * on that stream or synchronizes it. b200ann_last_kernel_ms is not updated by such calls; a kernel fault surfaces at
+ * the next synchronizing call. Calls with any host buffer still synchronize. Default off. */
+int b200ann_set_async(b200ann_handle_t h, int on);
+
 /* tuning knob: log2 of the per-query visited-set size in shared memory (default 10). */
 int b200ann_set_visited_bits(b200ann_handle_t h, int bits);
 /* same for the per-node searches of b200ann_nsg_link (default 12) */

@@ -162,7 +162,7 @@ __device__ __forceinline__ bool topl_insert_dispatch(uint64_t *list, uint32_t *s
 // ---- join (:22-33) ---------------------------------------------------------------------------------------
 constexpr int JT = 256;          // threads per CTA
 constexpr int TILE = 64;         // pairs tile TILE x TILE, 4 x 4 per thread
-constexpr int KC = 128;          // floats of the dimension staged per pass
+constexpr int KC = 64;           // floats of the dimension staged per pass
 constexpr int ROWF = KC + 4;     // padded shared-memory row (bank shift of 4 per row, 16-byte aligned)
 constexpr int DROW = TILE + 1;   // padded row of the tile's distance matrix (conflict-free column reads)
 constexpr uint32_t NO_PAIR = 0x7f800000u;  // +inf: never <= a threshold (thresholds are finite)
@@ -358,7 +358,7 @@ __device__ __forceinline__ void tile_fma(const float *As, const float *Bs, float
   }
 }
 
-__global__ void __launch_bounds__(JT, 2) join_kernel(State s, uint32_t cn_max) {
+__global__ void __launch_bounds__(JT, 3) join_kernel(State s, uint32_t cn_max) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float *As = reinterpret_cast<float *>(smem_raw);
   float *Bs = As + TILE * ROWF;

@@ -196,7 +196,7 @@ int b200ann_set_async(b200ann_handle_t h, int on);
 
 /* tuning knob: log2 of the per-query visited-set size in shared memory (default 10). */
 int b200ann_set_visited_bits(b200ann_handle_t h, int bits);
-/* same for the per-node searches of b200ann_nsg_link (default 12) */
+/* same for the per-node searches of b200ann_nsg_link (default 11) */
 int b200ann_set_link_visited_bits(b200ann_handle_t h, int bits);
 
 /* ---- NSG construction --------------------------------------------------------------------- */

@@ -1,0 +1,174 @@
+"""The hnswlib Python-binding mirror (hnsw-nsg_b200/hnswlib_py.py) on the GPU, following the reference's own binding
+tests: hnswlib/tests/python/bindings_test_recall.py (HNSW recall against BFIndex), bindings_test_spaces.py (the three
+distances), bindings_test.py / bindings_test_labels.py (save -> load -> add more -> query), bindings_test_getdata.py,
+bindings_test_metadata.py, bindings_test_pickle.py; plus what the reference cannot test: the files written here load
+in the compiled reference and answer identically to the oracle."""
+import importlib
+import pickle
+
+import numpy as np
+import pytest
+
+import refutil as R
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def hnswlib():
+    return importlib.import_module("hnsw-nsg_b200.hnswlib_py")
+
+
+def test_recall_against_bruteforce(hnswlib):
+    # bindings_test_recall.py:7-87 (dim 32, k 10, M 16, ef_construction 200, ef 200, recall > 0.95)
+    dim, n, k, nq = 32, 100000, 10, 200
+    rng = np.random.default_rng(0)
+    data = rng.random((n, dim), dtype=np.float32)
+    hnsw_index = hnswlib.Index(space="l2", dim=dim)
+    bf_index = hnswlib.BFIndex(space="l2", dim=dim)
+    hnsw_index.init_index(max_elements=n, ef_construction=200, M=16)
+    bf_index.init_index(max_elements=n)
+    hnsw_index.set_ef(200)
+    hnsw_index.set_num_threads(4)
+    hnsw_index.add_items(data)
+    bf_index.add_items(data)
+    q = rng.random((nq, dim), dtype=np.float32)
+    labels_hnsw, distances_hnsw = hnsw_index.knn_query(q, k)
+    labels_bf, distances_bf = bf_index.knn_query(q, k)
+    assert labels_hnsw.dtype == np.uint64 and labels_hnsw.shape == (nq, k) and distances_hnsw.dtype == np.float32
+    correct = sum(len(set(labels_hnsw[i].tolist()) & set(labels_bf[i].tolist())) for i in range(nq))
+    assert correct / (nq * k) > 0.95
+    assert (np.diff(distances_hnsw, axis=1) >= 0).all() and (np.diff(distances_bf, axis=1) >= 0).all()
+    # exact scan == numpy
+    d2 = ((q[:8, None, :].astype(np.float64) - data[None, :, :]) ** 2).sum(-1)
+    assert (np.argsort(d2, axis=1, kind="stable")[:, :k] == labels_bf[:8].astype(np.int64)).all()
+    hnsw_index.close()
+    bf_index.close()
+
+
+def test_spaces(hnswlib):
+    # bindings_test_spaces.py:9-39, a subset of its (leftdim, rightdim) grid
+    data1 = np.asarray([[1, 0, 0], [0, 1, 0], [0, 0, 1], [1, 0, 1], [1, 1, 1]])
+    for space, expected in [("l2", [[0., 1., 2., 2., 2.]]), ("ip", [[-2., -1., 0., 0., 0.]]),
+                            ("cosine", [[0, 1.835e-01, 4.23e-01, 4.23e-01, 4.23e-01]])]:
+        for rightdim in (1, 4, 28, 127):
+            for leftdim in (1, 6, 31):
+                data2 = np.concatenate([np.zeros([5, leftdim]), data1, np.zeros([5, rightdim])], axis=1)
+                p = hnswlib.Index(space=space, dim=data2.shape[1])
+                p.init_index(max_elements=5, ef_construction=100, M=16)
+                p.set_ef(10)
+                p.add_items(data2)
+                labels, distances = p.knn_query(np.asarray(data2[-1:]), k=5)
+                assert np.mean(np.abs(distances - expected)) < 1e-3, (space, leftdim, rightdim, distances)
+                p.close()
+
+
+def test_save_load_add_query_getdata_metadata(hnswlib, tmp_path):
+    # bindings_test.py:7-64 + bindings_test_labels.py (without the mark_deleted half) + getdata + metadata
+    dim, n = 16, 10000
+    data = np.float32(np.random.default_rng(1).random((n, dim)))
+    p = hnswlib.Index(space="l2", dim=dim)
+    with pytest.raises(Exception):
+        p.get_items(np.arange(n))
+    p.init_index(max_elements=n, ef_construction=100, M=16)
+    p.set_ef(100)
+    data1, data2 = data[:n // 2], data[n // 2:]
+    p.add_items(data1)
+    labels, distances = p.knn_query(data1, k=1)
+    assert np.mean(labels.reshape(-1) == np.arange(len(data1))) > 0.9995
+    assert np.mean(np.abs(data1 - p.get_items(labels))) < 1e-4
+    assert (p.get_max_elements(), p.get_current_count()) == (n, n // 2)
+    assert (p.space, p.dim, p.M, p.ef_construction, p.max_elements, p.element_count) == ("l2", dim, 16, 100, n, n // 2)
+    path = str(tmp_path / "first_half.bin")
+    p.save_index(path)
+    assert p.index_file_size() == (tmp_path / "first_half.bin").stat().st_size
+    before = p.knn_query(data2[:300], k=7)
+    p.close()
+    del p
+    p = hnswlib.Index(space="l2", dim=dim)
+    p.load_index(path)
+    p.set_ef(100)
+    after = p.knn_query(data2[:300], k=7)                         # the loaded graph answers like the one that was saved
+    assert (before[0] == after[0]).all() and (before[1] == after[1]).all()
+    if R.have_ref():                                              # the reference (CPU) reads the GPU-built file
+        ref = R.RefHnsw(0, dim, path=path)
+        lr, dr = ref.search(data2[:300], 7, 100, threads=1)
+        ref.close()
+        assert np.mean([len(set(lr[i].tolist()) & set(after[0][i].tolist())) for i in range(300)]) / 7 > 0.99
+    with pytest.raises(RuntimeError, match="exceeds"):
+        p.add_items(data2[:n // 2 + 1])
+    p.add_items(data2)
+    labels, distances = p.knn_query(data, k=1)
+    assert np.mean(labels.reshape(-1) == np.arange(len(data))) > 0.9995
+    assert np.mean(np.abs(data - p.get_items(labels))) < 1e-4
+    assert sorted(p.get_ids_list()) == list(range(n))
+    with pytest.raises(RuntimeError, match="contiguous 2D array"):
+        p.knn_query(data[:2], k=n + 1)
+    # pickle round trip (bindings_test_pickle.py): same parameters, same answers
+    p2 = pickle.loads(pickle.dumps(p))
+    assert (p2.space, p2.dim, p2.M, p2.ef_construction, p2.max_elements, p2.element_count, p2.ef) == \
+           (p.space, p.dim, p.M, p.ef_construction, p.max_elements, p.element_count, p.ef)
+    a, b = p.knn_query(data[:500], k=5), p2.knn_query(data[:500], k=5)
+    assert (a[0] == b[0]).all() and (a[1] == b[1]).all()
+    p.close()
+    p2.close()
+
+
+def test_custom_labels_match_oracle(hnswlib):
+    # labels are arbitrary u64; the graph is the one b200ann_hnsw_build makes (pinned link for link to the oracle in
+    # test_gpu_hnsw_build.py), so knn_query must answer exactly like the oracle searching the oracle-built graph
+    B = importlib.import_module("hnsw-nsg_b200")
+    n, dim, M, efc = 4000, 48, 8, 50
+    base = R.data_uniform(n, dim, 9)
+    labs = (np.arange(n, dtype=np.uint64) * np.uint64(7919) + np.uint64(1 << 40))
+    p = hnswlib.Index("l2", dim)
+    p.init_index(n, M=M, ef_construction=efc, random_seed=100)
+    p.add_items(base[:1500], labs[:1500])
+    p.add_items(base[1500:], labs[1500:])
+    p.set_ef(64)
+    q = R.data_uniform(200, dim, 10)
+    lab, d = p.knn_query(q, k=10)
+    R.oracle().orc_set_gpu_team(B.dist_team(dim))
+    O = R.orc_hnsw_build(base, M, efc, R.L2_GPU, 1, ratio=64, bmax=8192)
+    O["labels"] = labs
+    ol, od = R.orc_hnsw_search(base, O, q, 10, 64, R.L2_GPU)
+    assert (lab == ol).all()
+    assert np.allclose(d, od, rtol=1e-5, atol=0)
+    p.close()
+
+
+def test_bfindex_filter_delete_cosine(hnswlib, tmp_path):
+    dim, n = 20, 3000
+    rng = np.random.default_rng(2)
+    data = rng.standard_normal((n, dim)).astype(np.float32)
+    q = rng.standard_normal((50, dim)).astype(np.float32)
+    bf = hnswlib.BFIndex("cosine", dim)
+    bf.init_index(n)
+    bf.add_items(data, np.arange(n) + 100)
+    lab, d = bf.knn_query(q, 5)
+    unit = data / np.linalg.norm(data, axis=1, keepdims=True)
+    want = 1.0 - q.astype(np.float64) @ unit.T.astype(np.float64)   # stored vectors normalised, queries as given
+    order = np.argsort(want, axis=1)[:, :5]
+    assert (lab.astype(np.int64) - 100 == order).all()
+    assert np.allclose(d, np.take_along_axis(want, order, 1), atol=1e-4)
+    lab_even, _ = bf.knn_query(q, 5, filter=lambda l: l % 2 == 0)   # bindings_test_filter.py: only even labels
+    assert (lab_even % 2 == 0).all()
+    sub = np.arange(0, n, 2)
+    assert (lab_even.astype(np.int64) - 100 == sub[np.argsort(want[:, sub], axis=1)[:, :5]]).all()
+    gone = int(lab[0, 0])
+    bf.delete_vector(gone)
+    lab2, _ = bf.knn_query(q[:1], 5)
+    assert gone not in lab2 and (lab2[0, :4] == lab[0, 1:]).all()
+    bf.save_index(str(tmp_path / "bf.bin"))
+    b2 = hnswlib.BFIndex("cosine", dim)
+    b2.load_index(str(tmp_path / "bf.bin"))
+    lab3, d3 = b2.knn_query(q, 5)
+    lab4, d4 = bf.knn_query(q, 5)
+    assert (lab3 == lab4).all() and (d3 == d4).all()
+    few = hnswlib.BFIndex("l2", dim)
+    few.init_index(10)
+    few.add_items(data[:3])
+    l5, d5 = few.knn_query(q[:2], 5)                               # k > count: 3 answers, then padding
+    assert np.isinf(d5[:, 3:]).all() and np.isfinite(d5[:, :3]).all()
+    for x in (bf, b2, few):
+        x.close()

@@ -213,24 +213,26 @@ class Index:
         if self._normalize:
             rows = _normalize(rows)
         new_rows, new_labels = [], []
-        for r, lab in enumerate(labels.tolist()):
-            at = self._lookup.get(lab)
-            if at is not None:
-                if at < len(self._vec):
-                    self._vec[at] = rows[r]
-                else:
-                    new_rows[at - len(self._vec)] = r
-                continue
-            if len(self._labels) + len(new_labels) >= self._max:
-                raise RuntimeError("The number of elements exceeds the specified limit")   # hnswalg.h:1187
-            self._lookup[lab] = len(self._labels) + len(new_labels)
-            new_rows.append(r)
-            new_labels.append(lab)
-        if new_rows:
-            self._vec = np.concatenate([self._vec, rows[new_rows]])
-            self._labels = np.concatenate([self._labels, np.array(new_labels, np.uint64)])
-        self._dirty = True
-        self._graph = None
+        try:
+            for r, lab in enumerate(labels.tolist()):
+                at = self._lookup.get(lab)
+                if at is not None:
+                    if at < len(self._vec):
+                        self._vec[at] = rows[r]
+                    else:
+                        new_rows[at - len(self._vec)] = r
+                    continue
+                if len(self._labels) + len(new_labels) >= self._max:
+                    raise RuntimeError("The number of elements exceeds the specified limit")   # hnswalg.h:1187
+                self._lookup[lab] = len(self._labels) + len(new_labels)
+                new_rows.append(r)
+                new_labels.append(lab)
+        finally:                                                  # rows accepted before an error stay, like the reference
+            if new_rows:
+                self._vec = np.concatenate([self._vec, rows[new_rows]])
+                self._labels = np.concatenate([self._labels, np.array(new_labels, np.uint64)])
+            self._dirty = True
+            self._graph = None
 
     def _build(self):
         """vectors -> device, graph built by b200ann_hnsw_build (or installed from a loaded file)"""

@@ -96,8 +96,8 @@ def test_save_load_add_query_getdata_metadata(hnswlib, tmp_path):
         ref.close()
         assert np.mean([len(set(lr[i].tolist()) & set(after[0][i].tolist())) for i in range(300)]) / 7 > 0.99
     with pytest.raises(RuntimeError, match="exceeds"):
-        p.add_items(data2[:n // 2 + 1])
-    p.add_items(data2)
+        p.add_items(np.concatenate([data2, data2[:1]]))          # one more than max_elements: the first 5000 stay
+    assert p.get_current_count() == n
     labels, distances = p.knn_query(data, k=1)
     assert np.mean(labels.reshape(-1) == np.arange(len(data))) > 0.9995
     assert np.mean(np.abs(data - p.get_items(labels))) < 1e-4

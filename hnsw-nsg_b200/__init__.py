@@ -51,6 +51,7 @@ _lib.b200ann_index_get_hnsw.argtypes = [_vp, _vp, _vp, _vp, _vp, _vp]
 _lib.b200ann_nndescent.argtypes = [_vp, _vp, _sz, _sz, _sz, _sz, _sz, C.c_uint32, _vp, _vp, _vp]
 _lib.b200ann_nsg_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, C.c_uint32, _vp, _vp, _vp]
 _lib.b200ann_hnsw_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _vp, _vp, _vp]
+_lib.b200ann_hnsw_search_filtered.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _vp, _vp, _vp, _vp, _vp]
 _u32 = C.c_uint32
 _lib.b200ann_nsg_search_from.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _u32, _vp, _vp, _vp, _vp]
 _lib.b200ann_nsg_search_clustered.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _u32, _vp, _vp, _vp, _vp, _vp, _vp]
@@ -71,6 +72,7 @@ EXPORTS = [
     "b200ann_last_kernel_ms", "b200ann_set_visited_bits", "b200ann_index_create", "b200ann_index_destroy",
     "b200ann_index_size", "b200ann_index_dim", "b200ann_index_set_graph", "b200ann_index_get_graph",
     "b200ann_index_set_hnsw", "b200ann_bf_knn", "b200ann_knn_graph", "b200ann_nsg_search", "b200ann_hnsw_search",
+    "b200ann_hnsw_search_filtered",
     "b200ann_set_link_visited_bits", "b200ann_nsg_build", "b200ann_nsg_init_ep", "b200ann_nsg_link",
     "b200ann_nsg_interinsert", "b200ann_nsg_finish", "b200ann_merge_topk", "b200ann_nsg_search_from",
     "b200ann_hybrid_search", "b200ann_set_knn_mode", "b200ann_knn_last_stats", "b200ann_nndescent",
@@ -327,6 +329,25 @@ class Index:
         self.h._check(_lib.b200ann_hnsw_search(self.h._h, self._ix, _ptr(q), q.shape[0], q.shape[1], k, ef, _ptr(lab),
                                                _ptr(d), _ptr(st)))
         return (lab, d, st) if want_stats else (lab, d)
+
+    def hnsw_search_filtered(self, q, k, ef, allow, want_stats=False):
+        """searchKnn(query, k, isIdAllowed) batched. allow: bool / 0-1 array [n] by internal id (row), True = the
+        element may be returned (passes the filter and is not deleted). -> (labels, dists, inexact[, stats]); short
+        rows are padded with ~0 / inf; inexact[q] = 1: the bounded candidate set overflowed for that query."""
+        q = np.ascontiguousarray(q, np.float32)
+        a = np.asarray(allow).astype(bool)
+        assert a.shape == (self.n,)
+        bits = np.packbits(a, bitorder="little")
+        words = np.zeros(((self.n + 31) // 32) * 4, np.uint8)
+        words[:len(bits)] = bits
+        words = words.view(np.uint32)
+        lab = np.empty((q.shape[0], k), np.uint64)
+        d = np.empty((q.shape[0], k), np.float32)
+        bad = np.zeros(q.shape[0], np.uint8)
+        st = np.zeros((q.shape[0], 2), np.uint32) if want_stats else None
+        self.h._check(_lib.b200ann_hnsw_search_filtered(self.h._h, self._ix, _ptr(q), q.shape[0], q.shape[1], k, ef,
+                                                        _ptr(words), _ptr(lab), _ptr(d), _ptr(st), _ptr(bad)))
+        return (lab, d, bad, st) if want_stats else (lab, d, bad)
 
     def nsg_search_from(self, q, entry, K, L, seed=0, want_stats=False):
         """IndexNSG::SearchFromEnterpoint batched: query i starts at entry[i]"""

@@ -2,6 +2,8 @@
 // checks, host<->device staging, stream/event bookkeeping. All arithmetic is in the kernels.
 #include <math.h>
 #include <string.h>
+#include <cstring>
+#include <vector>
 #include "common.cuh"
 
 namespace {
@@ -477,6 +479,49 @@ int b200ann_hnsw_search(b200ann_handle_t h, b200ann_index_t ix, const float *q, 
   for (size_t i = 0; i < nq; i++)
     if (labels[i * k + k - 1] == ~(uint64_t)0)
       return set_err(h, B200ANN_ERR_FEWER, "hnsw_search: fewer than k results for some query; raise ef or lower k");
+  return 0;
+}
+
+int b200ann_hnsw_search_filtered(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_t nq, size_t qstride, size_t k,
+                                 size_t ef, const uint32_t *allow, uint64_t *labels, float *dists, uint32_t *stats,
+                                 uint8_t *inexact) {
+  if (!h || !ix) return B200ANN_ERR_ARG;
+  if (!ix->has_hnsw) return set_err(h, B200ANN_ERR_STATE, "hnsw_search_filtered: index has no HNSW graph (set_hnsw / hnsw_build first)");
+  if (!q || !allow || !labels || !dists || k == 0 || qstride < ix->dim)
+    return set_err(h, B200ANN_ERR_ARG, "hnsw_search_filtered: need q, allow, labels, dists, k > 0, qstride >= dim");
+  if (inexact && is_device_ptr(inexact)) return set_err(h, B200ANN_ERR_ARG, "hnsw_search_filtered: inexact must be host memory");
+  if (nq == 0) return 0;
+  CU_CHECK(h, cudaSetDevice(h->device));
+  InArg<float> qin; InArg<uint32_t> ain; OutArg<uint64_t> ol; OutArg<float> od; OutArg<uint32_t> os;
+  DevBuf<uint8_t> flags;
+  CU_CHECK(h, qin.stage(q, nq * qstride, h->stream));
+  CU_CHECK(h, ain.stage(allow, (ix->n + 31) / 32, h->stream));
+  CU_CHECK(h, ol.stage(labels, nq * k, h->stream));
+  CU_CHECK(h, od.stage(dists, nq * k, h->stream));
+  CU_CHECK(h, os.stage(stats, nq * 2, h->stream));
+  CU_CHECK(h, flags.alloc(nq, h->stream));
+  std::vector<uint8_t> hf(nq);
+  CallTimer t(h);
+  size_t left = 0;
+  for (int pass = 0; pass < 2; pass++) {
+    int rc = launch_hnsw_search_filtered(h, ix, qin.d, nq, qstride, k, ef, ain.d, 0, pass == 1, pass ? flags.p : nullptr,
+                                         ol.d, od.d, os.d, flags.p, nullptr);
+    if (rc) return rc;
+    CU_CHECK(h, cudaMemcpyAsync(hf.data(), flags.p, nq, cudaMemcpyDeviceToHost, h->stream));
+    CU_CHECK(h, cudaStreamSynchronize(h->stream));
+    left = 0;
+    for (size_t i = 0; i < nq; i++) left += hf[i] != 0;
+    if (!left) break;  // pass 1 searches only the queries pass 0 reported
+  }
+  t.stop();
+  CU_CHECK(h, ol.finish(h->stream));
+  CU_CHECK(h, od.finish(h->stream));
+  CU_CHECK(h, os.finish(h->stream));
+  CU_CHECK(h, t.sync());
+  if (inexact) std::memcpy(inexact, hf.data(), nq);
+  else if (left)
+    return set_err(h, B200ANN_ERR_CAPACITY, "hnsw_search_filtered: the filter is too selective for the graph walk on some queries "
+                                            "(candidate set overflow); pass `inexact` to see which, or scan the allowed rows with bf_knn");
   return 0;
 }
 

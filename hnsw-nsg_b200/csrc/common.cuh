@@ -141,6 +141,10 @@ int launch_nsg_search_clustered(b200ann_handle *h, const b200ann_index *ix, cons
                                 const uint32_t *size, uint32_t *ids, float *dists, uint32_t *stats);
 int launch_hnsw_search(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
                        size_t k, size_t ef, uint64_t *labels, float *dists, uint32_t *stats);
+int launch_hnsw_search_filtered(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
+                                size_t k, size_t ef, const uint32_t *allow_bits, size_t ccap, bool big,
+                                const uint8_t *only, uint64_t *labels, float *dists, uint32_t *stats, uint8_t *inexact,
+                                size_t *ccap_used);
 int launch_bf_knn(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
                   size_t k, bool exclude_self, uint32_t *ids, float *dists, const uint32_t *self_ids = nullptr);
 // tensor-core path (knn_tc.cu); same contract. knn_dispatch picks the path from h->knn_mode.

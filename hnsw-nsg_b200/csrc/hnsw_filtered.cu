@@ -1,0 +1,280 @@
+// Filtered / deleted-element HNSW search: hnswlib::HierarchicalNSW::searchKnn(query, k, isIdAllowed) when a filter
+// functor is given or elements are marked deleted (hnswalg.h:1305-1313 -> searchBaseLayerST<false>, :309-440, no
+// stop condition). The host functor becomes a device bitmap over INTERNAL ids (bit = allowed and not deleted).
+//
+// One warp per query, persistent over the batch. Both of the reference's heaps are kept as ascending (distance,id)
+// arrays in shared memory: top_candidates (allowed elements only, <= ef) and candidate_set (every considered
+// element, consumed from the front). candidate_set is unbounded in the reference (a selective filter makes the
+// walk consider ~ef/selectivity elements before top_candidates fills); here it holds `ccap` entries, the farthest
+// entry is dropped when it is full, and the query is reported INEXACT as soon as the reference could have expanded
+// a dropped entry (oracle.c hnsw_base_pools_filtered states the rule) - a query that is not reported is the
+// reference's answer bit for bit. The launcher retries reported queries once with the largest ccap one warp per
+// block can hold. The visited set is exact (the reference's per-query tag array, visited_list_pool.h:10-31): one
+// bitmap of n bits per resident warp in global memory, cleared per query.
+#include "beam.cuh"
+
+using namespace beam;
+
+namespace {
+
+constexpr int FW = 4;  // warps per block (1 in the retry pass: the whole block's shared memory for one candidate_set)
+
+struct FilterParams {
+  SearchParams s;
+  const uint32_t *allow;   // [ceil(n/32)] bit i = internal id i may be returned
+  uint32_t ccap;           // candidate_set capacity (entries)
+  uint32_t *visited;       // [total_warps, vwords]
+  uint32_t vwords;         // multiple of 4
+  uint32_t total_warps;
+  uint32_t wpb;            // warps per block
+  uint8_t *inexact;        // [nq]
+  const uint8_t *only;     // NULL, or [nq]: search only the queries with only[q] != 0 (retry pass)
+};
+
+__host__ __device__ inline uint32_t fsmem_words(const FilterParams &p) {
+  return smem_words(p.s.pool_cap, p.s.cand_cap, 0) + 2 * p.ccap;
+}
+
+// number of entries of a[lo, lo+n) ordered before (d,id)
+__device__ __forceinline__ uint32_t count_before(const float *ad, const uint32_t *ai, uint32_t lo, uint32_t n, float d,
+                                                 uint32_t id, int lane) {
+  uint32_t pos = 0;
+  for (uint32_t j0 = 0; j0 < n; j0 += 32) {
+    uint32_t j = j0 + lane;
+    bool in = j < n;
+    float pd = in ? ad[lo + j] : 0.f;
+    uint32_t pi = in ? ai[lo + j] : 0u;
+    bool before = in && (pd < d || (pd == d && pi < id));
+    pos += __popc(__ballot_sync(0xffffffffu, before));
+  }
+  return pos;
+}
+// entries [from, to) move up by one slot
+__device__ __forceinline__ void shift_up(float *ad, uint32_t *ai, int from, int to, int lane) {
+  if (to <= from) return;
+  for (int jb = from + ((to - 1 - from) / 32) * 32; jb >= from; jb -= 32) {
+    int j = jb + lane;
+    bool mv = j < to;
+    float td = 0.f; uint32_t ti = 0;
+    if (mv) { td = ad[j]; ti = ai[j]; }
+    __syncwarp();
+    if (mv) { ad[j + 1] = td; ai[j + 1] = ti; }
+    __syncwarp();
+  }
+}
+// entries [from, to) move down by one slot
+__device__ __forceinline__ void shift_down(float *ad, uint32_t *ai, int from, int to, int lane) {
+  for (int jb = from; jb < to; jb += 32) {
+    int j = jb + lane;
+    bool mv = j < to;
+    float td = 0.f; uint32_t ti = 0;
+    if (mv) { td = ad[j]; ti = ai[j]; }
+    __syncwarp();
+    if (mv) { ad[j - 1] = td; ai[j - 1] = ti; }
+    __syncwarp();
+  }
+}
+
+template <int TEAM, int NCH, bool IP>
+__global__ void __launch_bounds__(FW * 32) hnsw_filtered_kernel(const FilterParams fp) {
+  extern __shared__ uint32_t smem[];
+  const SearchParams &p = fp.s;
+  const int warp = threadIdx.x >> 5;
+  const uint32_t gw = blockIdx.x * fp.wpb + warp;
+  if (gw >= fp.total_warps) return;
+  uint32_t *base = smem + (size_t)warp * fsmem_words(fp);
+  Beam<TEAM, NCH, IP, true> b(p, base);
+  float *cd = reinterpret_cast<float *>(base + smem_words(p.pool_cap, p.cand_cap, 0));
+  uint32_t *ci = base + smem_words(p.pool_cap, p.cand_cap, 0) + fp.ccap;
+  uint32_t *vis = fp.visited + (size_t)gw * fp.vwords;
+  const int lane = b.lane;
+  const uint32_t ef = p.L;
+
+  for (uint32_t qi = gw; qi < p.nq; qi += fp.total_warps) {
+    if (fp.only && !fp.only[qi]) continue;
+    b.begin(p.q + (size_t)qi * p.qstride);
+    {  // empty visited set
+      uint4 *v4 = reinterpret_cast<uint4 *>(vis);
+      for (uint32_t i = lane; i < fp.vwords / 4; i += 32) v4[i] = make_uint4(0, 0, 0, 0);
+    }
+    float curdist;
+    const uint32_t ep = b.descend_upper(p.ep, curdist);
+    uint32_t nt = 0, nc = 0, h = 0;
+    float LB, dmin = INFINITY;
+    bool bad = false;
+    const bool ep_ok = (__ldg(fp.allow + (ep >> 5)) >> (ep & 31)) & 1u;
+    if (ep_ok) {  // :325-333 (the reference evaluates the entry point again; same value)
+      LB = curdist;
+      if (lane == 0) { b.pool_d[0] = curdist; b.pool_i[0] = ep; cd[0] = curdist; ci[0] = ep; }
+      nt = 1;
+    } else {      // :334-337: queued at FLT_MAX, never evaluated by the base layer
+      LB = 3.402823466e+38f;
+      if (lane == 0) { cd[0] = LB; ci[0] = ep; }
+    }
+    nc = 1;
+    if (lane == 0) vis[ep >> 5] = 1u << (ep & 31);
+    __syncwarp();
+
+    for (;;) {
+      const float c0d = nc ? cd[h] : INFINITY;
+      if (dmin < INFINITY && (nc == 0 || dmin <= c0d) && !(dmin > LB && nt == ef)) bad = true;
+      if (nc == 0) break;
+      if (c0d > LB && nt == ef) break;  // :355
+      const uint32_t node = ci[h];
+      h++; nc--;
+      if (nc == 0) h = 0;
+      b.n_hops++;
+      // unvisited neighbours, in row order, marked visited (:385-386)
+      const uint32_t *row = p.graph + (size_t)node * p.gstride;
+      uint32_t m = 0;
+      __syncwarp();
+      for (uint32_t j0 = 0; j0 < p.gstride; j0 += 32) {
+        uint32_t j = j0 + lane;
+        uint32_t id = j < p.gstride ? __ldg(row + j) : INVALID_ID;
+        bool valid = id != INVALID_ID;
+        if (valid) {
+          uint32_t bit = 1u << (id & 31);
+          valid = !(atomicOr(vis + (id >> 5), bit) & bit);
+        }
+        unsigned mask = __ballot_sync(0xffffffffu, valid);
+        if (valid) b.cand_i[m + __popc(mask & ((1u << lane) - 1))] = id;
+        m += __popc(mask);
+        if (__any_sync(0xffffffffu, id == INVALID_ID)) break;
+      }
+      __syncwarp();
+      b.eval(m);
+      for (uint32_t c0 = 0; c0 < m; c0 += 32) {
+        uint32_t c = c0 + lane;
+        float d = c < m ? b.cand_d[c] : INFINITY;
+        bool pass = c < m && (nt < ef || d < LB);
+        unsigned mask = __ballot_sync(0xffffffffu, pass);
+        while (mask) {
+          int bsel = __ffs(mask) - 1;
+          mask &= mask - 1;
+          float dd = __shfl_sync(0xffffffffu, d, bsel);
+          uint32_t id = b.cand_i[c0 + bsel];
+          if (!(nt < ef || dd < LB)) continue;  // :395 with the live bound
+          // candidate_set.emplace (:398)
+          bool put = true;
+          if (nc == fp.ccap) {  // full: the farthest of (entries, new) goes
+            float ld = cd[h + nc - 1];
+            uint32_t li = ci[h + nc - 1];
+            float yd = dd;
+            if (dd < ld || (dd == ld && id < li)) { yd = ld; nc--; } else { put = false; }
+            if (!(nt == ef && yd > LB) && yd < dmin) dmin = yd;
+          }
+          if (put) {
+            uint32_t before = count_before(cd, ci, h, nc, dd, id, lane);
+            if (h + nc < fp.ccap) {
+              shift_up(cd, ci, (int)(h + before), (int)(h + nc), lane);
+              if (lane == 0) { cd[h + before] = dd; ci[h + before] = id; }
+            } else {  // no room behind the tail: the front part moves into the consumed slots
+              shift_down(cd, ci, (int)h, (int)(h + before), lane);
+              h--;
+              if (lane == 0) { cd[h + before] = dd; ci[h + before] = id; }
+            }
+            nc++;
+            __syncwarp();
+          }
+          // top_candidates.emplace for allowed elements (:406-408), pop the farthest beyond ef (:413-424)
+          if ((__ldg(fp.allow + (id >> 5)) >> (id & 31)) & 1u) {
+            if (nt == ef) nt--;  // the new element is closer than the farthest one (dd < LB)
+            uint32_t before = count_before(b.pool_d, b.pool_i, 0, nt, dd, id, lane);
+            shift_up(b.pool_d, b.pool_i, (int)before, (int)nt, lane);
+            if (lane == 0) { b.pool_d[before] = dd; b.pool_i[before] = id; }
+            nt++;
+            __syncwarp();
+          }
+          if (nt) LB = b.pool_d[nt - 1];  // :426-427
+        }
+      }
+    }
+
+    for (uint32_t i = lane; i < p.K; i += 32) {
+      bool ok = i < nt;
+      uint32_t id = ok ? b.pool_i[i] : INVALID_ID;
+      p.labels_out[(size_t)qi * p.K + i] = ok ? (p.labels ? __ldg(p.labels + id) : (uint64_t)id) : ~(uint64_t)0;
+      if (p.dists) p.dists[(size_t)qi * p.K + i] = ok ? b.pool_d[i] : INFINITY;
+    }
+    if (lane == 0) {
+      fp.inexact[qi] = bad ? 1 : 0;
+      if (p.stats) { p.stats[2 * (size_t)qi] = b.n_dist; p.stats[2 * (size_t)qi + 1] = b.n_hops; }
+    }
+    __syncwarp();
+  }
+}
+
+template <int TEAM, int NCH, bool IP>
+int launch_ft(b200ann_handle *h, FilterParams &fp) {
+  size_t smem = (size_t)fp.wpb * fsmem_words(fp) * 4;
+  auto kern = hnsw_filtered_kernel<TEAM, NCH, IP>;
+  CU_CHECK(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  dim3 grid((fp.total_warps + fp.wpb - 1) / fp.wpb), block(fp.wpb * 32);
+  kern<<<grid, block, smem, h->stream>>>(fp);
+  h->launches++;
+  CU_CHECK(h, cudaGetLastError());
+  return 0;
+}
+
+template <bool IP>
+int launch_fdim(b200ann_handle *h, FilterParams &fp) {
+  int nch = fp.s.nch;
+  if (nch <= 8) return launch_ft<8, 1, IP>(h, fp);
+  if (nch <= 16) return launch_ft<8, 2, IP>(h, fp);
+  if (nch <= 32) return launch_ft<8, 4, IP>(h, fp);
+  if (nch <= 64) return launch_ft<8, 8, IP>(h, fp);
+  if (nch <= 128) return launch_ft<32, 4, IP>(h, fp);
+  if (nch <= 256) return launch_ft<32, 8, IP>(h, fp);
+  if (nch <= 512) return launch_ft<32, 16, IP>(h, fp);
+  return set_err(h, B200ANN_ERR_ARG, "hnsw_search_filtered: dim > 2048 is not supported");
+}
+
+}  // namespace
+
+// big = false: 4 warps per block, candidate_set of min(ccap ? ccap : 2048, what fits) entries; big = true (retry pass):
+// one warp per block with the largest candidate_set 227 KB hold. only = NULL or a device mask of the queries to
+// search (may alias inexact). All pointers are device pointers.
+int launch_hnsw_search_filtered(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
+                                size_t k, size_t ef, const uint32_t *allow_bits, size_t ccap, bool big,
+                                const uint8_t *only, uint64_t *labels, float *dists, uint32_t *stats, uint8_t *inexact,
+                                size_t *ccap_used) {
+  FilterParams fp = {};
+  SearchParams &p = fp.s;
+  size_t L = ef > k ? ef : k;
+  p.vec = ix->vec; p.stride = ix->stride; p.n = (uint32_t)ix->n; p.nch = (int)((ix->dim + 3) / 4);
+  p.graph = ix->links0; p.gstride = (uint32_t)ix->maxM0; p.ep = ix->hnsw_ep;
+  p.upper_links = ix->upper_links; p.upper_ptr = ix->upper_ptr; p.maxM = (uint32_t)ix->maxM;
+  p.maxlevel = ix->maxlevel; p.labels = ix->labels;
+  p.q = q; p.qstride = qstride; p.nq = (uint32_t)nq; p.dim = (uint32_t)ix->dim;
+  p.K = (uint32_t)k; p.L = (uint32_t)L; p.seed = 0; p.hbits = 0;
+  size_t cc = ix->maxM0 > ix->maxM ? ix->maxM0 : ix->maxM;
+  p.cand_cap = round_up((uint32_t)cc, 32);
+  p.pool_cap = round_up((uint32_t)L + 1, 32);
+  p.labels_out = labels; p.dists = dists; p.stats = stats;
+  fp.allow = allow_bits; fp.inexact = inexact; fp.only = only;
+  fp.wpb = big ? 1 : FW;
+  const size_t fixed = smem_words(p.pool_cap, p.cand_cap, 0);
+  const size_t budget = 227 * 1024 / 4 / fp.wpb;
+  if (fixed + 2 * 64 > budget) return set_err(h, B200ANN_ERR_ARG, "hnsw_search_filtered: ef / degree need more than 227 KB shared memory per block");
+  size_t most = (budget - fixed) / 2 / 32 * 32;
+  if (ccap == 0) ccap = 2048;
+  if (big || ccap > most) ccap = most;
+  fp.ccap = (uint32_t)ccap;
+  if (ccap_used) *ccap_used = ccap;
+  // resident warps: blocks per SM by shared memory, capped so the visited bitmaps stay below 2 GiB
+  size_t smem_block = (size_t)fp.wpb * fsmem_words(fp) * 4;
+  size_t per_sm = 227 * 1024 / smem_block;
+  if (per_sm < 1) per_sm = 1;
+  if (per_sm > 8) per_sm = 8;
+  size_t warps = (size_t)h->sm_count * per_sm * fp.wpb;
+  fp.vwords = round_up((uint32_t)((ix->n + 31) / 32), 4);
+  size_t by_mem = ((size_t)2 << 30) / ((size_t)fp.vwords * 4);
+  if (by_mem < 1) by_mem = 1;
+  if (warps > by_mem) warps = by_mem;
+  if (warps > nq) warps = nq;
+  fp.total_warps = (uint32_t)warps;
+  DevBuf<uint32_t> vis;
+  CU_CHECK(h, vis.alloc((size_t)fp.total_warps * fp.vwords, h->stream));
+  fp.visited = vis.p;
+  return ix->metric == B200ANN_IP ? launch_fdim<true>(h, fp) : launch_fdim<false>(h, fp);
+}

@@ -34,7 +34,8 @@ enum {
   B200ANN_ERR_ARG = -1,   /* bad argument (message says which) */
   B200ANN_ERR_CUDA = -2,  /* CUDA runtime error / no device */
   B200ANN_ERR_STATE = -3, /* index has no graph of the requested kind */
-  B200ANN_ERR_FEWER = -4  /* fewer than k results for some query (bindings.cpp:646-648) */
+  B200ANN_ERR_FEWER = -4, /* fewer than k results for some query (bindings.cpp:646-648) */
+  B200ANN_ERR_CAPACITY = -5 /* filtered search: candidate set overflow on some query (see b200ann_hnsw_search_filtered) */
 };
 
 typedef struct b200ann_handle *b200ann_handle_t;
@@ -146,6 +147,21 @@ int b200ann_nsg_search(b200ann_handle_t h, b200ann_index_t ix, const float *q /*
 int b200ann_hnsw_search(b200ann_handle_t h, b200ann_index_t ix, const float *q /*[h|d]*/, size_t nq,
                         size_t qstride, size_t k, size_t ef, uint64_t *labels /*[h|d]*/,
                         float *dists /*[h|d]*/, uint32_t *stats /*[h|d]*/);
+
+/* replaces hnswlib::HierarchicalNSW::searchKnn(query, k, isIdAllowed) for a batch of queries when a filter functor
+ * is given and / or elements are marked deleted (hnswalg.h:1305-1313 -> searchBaseLayerST<false>, :309-440, no stop
+ * condition; markDelete / unmarkDelete :853-911). The host functor and the delete marks become ONE bitmap over
+ * internal ids (= rows of the index): bit (i & 31) of allow[i >> 5] set <=> element i is not deleted and its label
+ * passes the filter; allow holds ceil(n/32) words. Elements that are filtered out are still walked through, exactly
+ * like the reference; rows with fewer than k allowed results are padded with ~0 / +inf (no error: the reference
+ * returns short results too). The reference's candidate_set is unbounded; here it is bounded per query (shared
+ * memory), overflowing queries are retried once with the largest bound, and a query whose answer could still differ
+ * from the reference's is reported: inexact [nq] (host, 0 / 1), or, when inexact is NULL, the call fails with
+ * B200ANN_ERR_CAPACITY. A query reported 0 is the reference's answer bit for bit. */
+int b200ann_hnsw_search_filtered(b200ann_handle_t h, b200ann_index_t ix, const float *q /*[h|d]*/, size_t nq,
+                                 size_t qstride, size_t k, size_t ef, const uint32_t *allow /*[h|d]*/,
+                                 uint64_t *labels /*[h|d]*/, float *dists /*[h|d]*/, uint32_t *stats /*[h|d]*/,
+                                 uint8_t *inexact /*[h] or NULL*/);
 
 /* replaces hnsw_nsg::IndexNSG::SearchFromEnterpoint (hnsw_nsg/src/index_nsg.cpp:703-782) for a batch:
  * like b200ann_nsg_search, but query i starts from entry[i] instead of the navigating node. The

@@ -20,6 +20,7 @@
  * Where the reference leaves an order unspecified (std::sort / std::priority_queue on equal
  * distances) the oracle uses the total order (distance, id) ascending — documented per function.
  */
+#include <float.h>
 #include <math.h>
 #include <stdint.h>
 #include <stdlib.h>
@@ -674,6 +675,165 @@ EXPORT int orc_hnsw_search(const float *data, size_t n, size_t dim, size_t strid
       }
     }
     free(visited); free(top); free(cand); free(expd);
+  }
+  return 0;
+}
+
+/* ------------------------------------------------------------------ filtered / deleted-element HNSW search */
+/* searchBaseLayerST<bare_bone=false> without a stop condition (hnswalg.h:309-440), the form searchKnn runs when a
+ * filter functor is given or elements are marked deleted (:1305-1313). allow[id] != 0 stands for
+ * !isMarkedDeleted(id) && (*isIdAllowed)(getExternalLabel(id)) (:325-326, :406-407). Two heaps exactly as the
+ * reference: every considered element goes to candidate_set, only allowed ones to top_candidates; the entry point
+ * of a disallowed start is queued at FLT_MAX without a distance evaluation (:334-337). */
+static size_t hnsw_base_twoheap_filtered(const orc_hnsw *ix, uint32_t ep, const float *q, size_t ef,
+                                         const uint8_t *allow, uint8_t *visited, orc_pair *top, orc_pair *cand,
+                                         uint64_t *stats) {
+  size_t nt = 0, nc = 0;
+  float lowerBound;
+  if (allow[ep]) {
+    float dist = orc_dist(ix->mode, q, ix->data + ix->stride * (size_t)ep, ix->dim);
+    if (stats) stats[0]++;
+    lowerBound = dist;
+    orc_pair e = {dist, ep};
+    hpush(top, &nt, e, +1);
+    hpush(cand, &nc, e, -1);
+  } else {
+    lowerBound = FLT_MAX;
+    orc_pair e = {lowerBound, ep};
+    hpush(cand, &nc, e, -1);
+  }
+  visited[ep] = 1;
+  while (nc) {
+    orc_pair cur = cand[0];
+    if (cur.d > lowerBound && nt == ef) break; /* :355 */
+    hpop(cand, &nc, -1);
+    const uint32_t *row = ix->links0 + (size_t)cur.id * ix->maxM0;
+    if (stats) stats[1]++;
+    for (unsigned j = 0; j < ix->maxM0 && row[j] != ORC_INVALID; j++) {
+      uint32_t cid = row[j];
+      if (visited[cid]) continue;
+      visited[cid] = 1;
+      float d = orc_dist(ix->mode, q, ix->data + ix->stride * (size_t)cid, ix->dim);
+      if (stats) stats[0]++;
+      if (nt < ef || lowerBound > d) { /* :395 */
+        orc_pair c = {d, cid};
+        hpush(cand, &nc, c, -1);
+        if (allow[cid]) hpush(top, &nt, c, +1); /* :406-408 */
+        while (nt > ef) hpop(top, &nt, +1);
+        if (nt) lowerBound = top[0].d;
+      }
+    }
+  }
+  qsort(top, nt, sizeof(orc_pair), pair_cmp);
+  return nt;
+}
+
+/* The CUDA kernel's form of the same search: both heaps as ascending (d,id) arrays, candidate_set bounded by ccap
+ * entries. It is the two-heap form verbatim until candidate_set would hold more than ccap entries; then the
+ * farthest entry is dropped, and the query is reported inexact (*inexact = 1) as soon as the reference could have
+ * expanded a dropped entry: some dropped entry y is not beyond reach (!(y.d > lowerBound && nt == ef)) and the next
+ * candidate is not closer than it (or there is none). Without that report the result IS the reference's. */
+static void sorted_insert(orc_pair *a, size_t *n, orc_pair x) {
+  size_t pos = *n;
+  while (pos > 0 && pair_less(x, a[pos - 1])) { a[pos] = a[pos - 1]; pos--; }
+  a[pos] = x;
+  (*n)++;
+}
+static size_t hnsw_base_pools_filtered(const orc_hnsw *ix, uint32_t ep, const float *q, size_t ef, const uint8_t *allow,
+                                       size_t ccap, uint8_t *visited, orc_pair *top, orc_pair *cand, uint64_t *stats,
+                                       int *inexact) {
+  size_t nt = 0, nc = 0;
+  float lowerBound, dmin = INFINITY;
+  *inexact = 0;
+  if (allow[ep]) {
+    float dist = orc_dist(ix->mode, q, ix->data + ix->stride * (size_t)ep, ix->dim);
+    if (stats) stats[0]++;
+    lowerBound = dist;
+    orc_pair e = {dist, ep};
+    top[nt++] = e;
+    cand[nc++] = e;
+  } else {
+    lowerBound = FLT_MAX;
+    orc_pair e = {lowerBound, ep};
+    cand[nc++] = e;
+  }
+  visited[ep] = 1;
+  for (;;) {
+    if (dmin < INFINITY && (nc == 0 || dmin <= cand[0].d) && !(dmin > lowerBound && nt == ef)) *inexact = 1;
+    if (nc == 0) break;
+    orc_pair cur = cand[0];
+    if (cur.d > lowerBound && nt == ef) break;
+    memmove(cand, cand + 1, sizeof(orc_pair) * --nc);
+    const uint32_t *row = ix->links0 + (size_t)cur.id * ix->maxM0;
+    if (stats) stats[1]++;
+    for (unsigned j = 0; j < ix->maxM0 && row[j] != ORC_INVALID; j++) {
+      uint32_t cid = row[j];
+      if (visited[cid]) continue;
+      visited[cid] = 1;
+      float d = orc_dist(ix->mode, q, ix->data + ix->stride * (size_t)cid, ix->dim);
+      if (stats) stats[0]++;
+      if (nt < ef || lowerBound > d) {
+        orc_pair c = {d, cid};
+        if (nc == ccap) { /* full: the farthest of (entries, c) goes */
+          orc_pair y = c;
+          if (pair_less(c, cand[nc - 1])) { y = cand[--nc]; sorted_insert(cand, &nc, c); }
+          if (!(nt == ef && y.d > lowerBound) && y.d < dmin) dmin = y.d;
+        } else {
+          sorted_insert(cand, &nc, c);
+        }
+        if (allow[cid]) {
+          if (nt == ef) {
+            if (pair_less(c, top[nt - 1])) { nt--; sorted_insert(top, &nt, c); }
+          } else {
+            sorted_insert(top, &nt, c);
+          }
+        }
+        if (nt) lowerBound = top[nt - 1].d;
+      }
+    }
+  }
+  return nt;
+}
+
+/* HierarchicalNSW::searchKnn(query, k, isIdAllowed) batched, for an index with a filter and / or deleted elements.
+ * allow [n] by INTERNAL id. variant 0 = two heaps (the reference), 1 = the kernel's bounded arrays (ccap entries of
+ * candidate_set; inexact [nq] or NULL). Output as orc_hnsw_search. */
+EXPORT int orc_hnsw_search_filtered(const float *data, size_t n, size_t dim, size_t stride, const uint32_t *links0,
+                                    unsigned maxM0, const int32_t *levels, const uint32_t *upper_ptr,
+                                    const uint32_t *upper_links, unsigned maxM, const uint64_t *labels, uint32_t ep,
+                                    int maxlevel, const uint8_t *allow, const float *q, size_t nq, size_t qstride,
+                                    size_t k, size_t ef, size_t ccap, int mode, int variant, uint64_t *out_labels,
+                                    float *out_dists, uint64_t *stats, uint8_t *inexact) {
+  orc_hnsw ix = {data, n, dim, stride, links0, maxM0, levels, upper_ptr, upper_links, maxM, ep, maxlevel, mode};
+  size_t efk = ef > k ? ef : k;
+  if (stats) memset(stats, 0, sizeof(uint64_t) * 2 * nq);
+  if (variant == 1 && ccap == 0) return -1;
+#pragma omp parallel
+  {
+    uint8_t *visited = (uint8_t *)malloc(n ? n : 1);
+    orc_pair *top = (orc_pair *)malloc(sizeof(orc_pair) * (efk + 2));
+    orc_pair *cand = (orc_pair *)malloc(sizeof(orc_pair) * ((variant == 0 ? n : ccap) + 2));
+#pragma omp for schedule(dynamic, 8)
+    for (long qi = 0; qi < (long)nq; qi++) {
+      const float *qv = q + (size_t)qi * qstride;
+      size_t m = 0;
+      int bad = 0;
+      if (n) {
+        memset(visited, 0, n);
+        float cd;
+        uint64_t *st = stats ? stats + 2 * qi : NULL;
+        uint32_t cur = hnsw_descend(&ix, qv, &cd, st);
+        if (st && allow[cur]) st[0]--; /* an allowed entry point is evaluated again by the base layer; count it once */
+        m = variant == 0 ? hnsw_base_twoheap_filtered(&ix, cur, qv, efk, allow, visited, top, cand, st)
+                         : hnsw_base_pools_filtered(&ix, cur, qv, efk, allow, ccap, visited, top, cand, st, &bad);
+      }
+      if (inexact) inexact[qi] = (uint8_t)bad;
+      for (size_t j = 0; j < k; j++) {
+        out_labels[(size_t)qi * k + j] = j < m ? (labels ? labels[top[j].id] : top[j].id) : ~(uint64_t)0;
+        out_dists[(size_t)qi * k + j] = j < m ? top[j].d : INFINITY;
+      }
+    }
+    free(visited); free(top); free(cand);
   }
   return 0;
 }

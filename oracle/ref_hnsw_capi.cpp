@@ -116,6 +116,42 @@ int ref_hnsw_search(void *p, const float *q, size_t nq, size_t k, size_t ef,
   return 0;
 }
 
+// searchKnn(query, k, isIdAllowed) (hnswalg.h:1270-1324 -> searchBaseLayerST<false>, :309-440): allow [max label + 1]
+// by LABEL (NULL = no functor, only the deleted marks filter)
+struct BitmapFilter : public BaseFilterFunctor {
+  const unsigned char *allow;
+  explicit BitmapFilter(const unsigned char *a) : allow(a) {}
+  bool operator()(labeltype id) override { return allow[id] != 0; }
+};
+int ref_hnsw_search_filtered(void *p, const float *q, size_t nq, size_t k, size_t ef, const unsigned char *allow,
+                             unsigned long long *labels, float *dists, int threads) {
+  RefHnsw *h = (RefHnsw *)p;
+  h->index->setEf(ef);
+  if (threads <= 0) threads = omp_get_max_threads();
+#pragma omp parallel for num_threads(threads) schedule(dynamic, 16)
+  for (long i = 0; i < (long)nq; i++) {
+    BitmapFilter f(allow);
+    auto r = h->index->searchKnn(q + i * h->dim, k, allow ? &f : nullptr);
+    size_t m = r.size();
+    for (size_t j = m; j < k; j++) { labels[i * k + j] = (unsigned long long)-1; dists[i * k + j] = -1.f; }
+    while (!r.empty()) {
+      --m;
+      labels[i * k + m] = r.top().second;
+      dists[i * k + m] = r.top().first;
+      r.pop();
+    }
+  }
+  return 0;
+}
+// markDelete / unmarkDelete (hnswalg.h:853-911)
+int ref_hnsw_mark_deleted(void *p, size_t label, int on) {
+  RefHnsw *h = (RefHnsw *)p;
+  try {
+    if (on) h->index->markDelete(label); else h->index->unmarkDelete(label);
+  } catch (std::exception &e) { return -1; }
+  return 0;
+}
+
 int ref_hnsw_save(void *p, const char *path) {
   ((RefHnsw *)p)->index->saveIndex(path);
   return 0;

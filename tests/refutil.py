@@ -20,6 +20,7 @@ f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
 u32p = np.ctypeslib.ndpointer(np.uint32, flags="C_CONTIGUOUS")
 i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
 u64p = np.ctypeslib.ndpointer(np.uint64, flags="C_CONTIGUOUS")
+u8p = np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")
 
 
 def _build_oracle():
@@ -79,6 +80,10 @@ def oracle():
                                             C.c_uint, C.c_uint, C.c_uint32, C.c_int, u32p, C.c_void_p, C.c_void_p]
         lib.orc_nsg_search_qidx.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, u32p, C.c_uint, C.c_uint32, f32p,
                                             C.c_size_t, C.c_size_t, C.c_uint, C.c_uint, C.c_int, C.c_uint32, u32p, u32p, f32p]
+        lib.orc_hnsw_search_filtered.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, u32p, C.c_uint, i32p, u32p,
+                                                 u32p, C.c_uint, C.c_void_p, C.c_uint32, C.c_int, u8p, f32p,
+                                                 C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int,
+                                                 C.c_int, u64p, f32p, C.c_void_p, C.c_void_p]
         lib.orc_hnsw_levels.argtypes = [C.c_size_t, C.c_uint, C.c_uint32, i32p]
         lib.orc_hnsw_batch_end.restype = C.c_size_t
         lib.orc_hnsw_batch_end.argtypes = [C.c_size_t, C.c_size_t, i32p, C.c_int, C.c_uint, C.c_uint]
@@ -129,6 +134,26 @@ def orc_hnsw_search(base, h, q, k, ef, mode, variant=1, want_stats=False):
                              up, up.shape[1], _vp(h["labels"]), h["ep"], h["maxlevel"], q, nq, q.shape[1], k, ef,
                              mode, variant, lab, d, _vp(st))
     return (lab, d, st) if want_stats else (lab, d)
+
+
+def orc_hnsw_search_filtered(base, h, allow, q, k, ef, mode, variant=0, ccap=0, want_stats=False):
+    """allow [n] u8 by internal id (0 = filtered out or deleted). variant 0 = the reference's two heaps, 1 = the CUDA
+    kernel's bounded arrays (ccap). Returns (labels, d, inexact[, stats])."""
+    n, dim = base.shape
+    nq = q.shape[0]
+    lab = np.empty((nq, k), np.uint64)
+    d = np.empty((nq, k), np.float32)
+    bad = np.zeros(nq, np.uint8)
+    st = np.zeros((nq, 2), np.uint64) if want_stats else None
+    up = h["upper_links"]
+    if up.size == 0:
+        up = np.full((1, max(1, h["maxM"])), INVALID, np.uint32)
+    rc = oracle().orc_hnsw_search_filtered(base, n, dim, dim, h["links0"], h["links0"].shape[1], h["levels"],
+                                           h["upper_ptr"], up, up.shape[1], _vp(h["labels"]), h["ep"], h["maxlevel"],
+                                           np.ascontiguousarray(allow, np.uint8), q, nq, q.shape[1], k, ef, ccap, mode,
+                                           variant, lab, d, _vp(st), _vp(bad))
+    assert rc == 0
+    return (lab, d, bad, st) if want_stats else (lab, d, bad)
 
 
 def orc_nsg_search_from(base, graph, entry, q, K, L, mode, rng_mode=1, seed=0, want_stats=False):
@@ -439,6 +464,9 @@ def reflib(name):
         lib.ref_hnsw_search.argtypes = [C.c_void_p, f32p, C.c_size_t, C.c_size_t, C.c_size_t, u64p, f32p,
                                         C.c_int, C.c_void_p, C.c_void_p]
         lib.ref_hnsw_save.argtypes = [C.c_void_p, C.c_char_p]
+        lib.ref_hnsw_search_filtered.argtypes = [C.c_void_p, f32p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_void_p, u64p,
+                                                 f32p, C.c_int]
+        lib.ref_hnsw_mark_deleted.argtypes = [C.c_void_p, C.c_size_t, C.c_int]
     elif name.startswith("nsg"):
         lib.ref_nsg_dist_l2.restype = C.c_float
         lib.ref_nsg_dist_l2.argtypes = [f32p, f32p, C.c_uint]
@@ -512,6 +540,17 @@ class RefHnsw:
         d = np.empty((q.shape[0], k), np.float32)
         self.lib.ref_hnsw_search(self.h, q, q.shape[0], k, ef, lab, d, threads, None, None)
         return lab, d
+
+    def search_filtered(self, q, k, ef, allow_by_label=None, threads=0):
+        """searchKnn with a filter functor over a label bitmap (None = deleted marks only); short rows: ~0 / -1"""
+        lab = np.empty((q.shape[0], k), np.uint64)
+        d = np.empty((q.shape[0], k), np.float32)
+        a = None if allow_by_label is None else np.ascontiguousarray(allow_by_label, np.uint8)
+        self.lib.ref_hnsw_search_filtered(self.h, q, q.shape[0], k, ef, _vp(a), lab, d, threads)
+        return lab, d
+
+    def mark_deleted(self, label, on=True):
+        assert self.lib.ref_hnsw_mark_deleted(self.h, int(label), 1 if on else 0) == 0
 
     def save(self, path):
         self.lib.ref_hnsw_save(self.h, path.encode())

@@ -139,6 +139,49 @@ def test_hnsw_search_vs_reference(hnsw_case, ef):
         assert (rl == ol).all() and (rd == od).all()
 
 
+@needs_ref
+@pytest.mark.parametrize("keep,ef", [(0.5, 40), (0.1, 10), (0.02, 30), (0.9, 200), (0.0, 20)])
+def test_hnsw_filtered_search_vs_reference(hnsw_case, keep, ef):
+    """oracle searchBaseLayerST<false> == HierarchicalNSW::searchKnn(query, k, isIdAllowed), bit for bit, for a label
+    filter, for deleted marks and for both together; and the kernel's bounded-array form equals the two-heap form
+    wherever it does not report a query inexact"""
+    base, q, h, H = hnsw_case
+    n = len(base)
+    rng = np.random.default_rng(int(keep * 100) + ef)
+    allow_f = (rng.random(n) < keep).astype(np.uint8)
+    dele = rng.random(n) < 0.2
+    pad = lambda l, d: (l, np.where(l == np.uint64(0xFFFFFFFFFFFFFFFF), np.float32(np.inf), d))
+    # (a) functor only
+    rl, rd = pad(*h.search_filtered(q, 10, ef, allow_f, threads=1))
+    ol, od, _ = R.orc_hnsw_search_filtered(base, H, allow_f, q, 10, ef, R.L2_SCALAR, variant=0)
+    assert (rl == ol).all() and (rd == od).all()
+    if keep == 0.0:
+        assert (ol == np.uint64(0xFFFFFFFFFFFFFFFF)).all()
+    # (b) deleted marks only, (c) both
+    for lab in np.nonzero(dele)[0]:
+        h.mark_deleted(lab, True)
+    try:
+        rl, rd = pad(*h.search_filtered(q, 10, ef, None, threads=1))
+        ol, od, _ = R.orc_hnsw_search_filtered(base, H, (~dele).astype(np.uint8), q, 10, ef, R.L2_SCALAR, variant=0)
+        assert (rl == ol).all() and (rd == od).all()
+        both = (allow_f.astype(bool) & ~dele).astype(np.uint8)
+        rl, rd = pad(*h.search_filtered(q, 10, ef, allow_f, threads=1))
+        ol, od, _ = R.orc_hnsw_search_filtered(base, H, both, q, 10, ef, R.L2_SCALAR, variant=0)
+        assert (rl == ol).all() and (rd == od).all()
+    finally:
+        for lab in np.nonzero(dele)[0]:
+            h.mark_deleted(lab, False)
+    # bounded form: exact where not flagged; a large bound flags nothing; a tiny one flags (and says so)
+    for ccap in (n, 256, 16):
+        pl, pd_, bad = R.orc_hnsw_search_filtered(base, H, both, q, 10, ef, R.L2_SCALAR, variant=1, ccap=ccap)
+        ok = bad == 0
+        assert (pl[ok] == ol[ok]).all() and (pd_[ok] == od[ok]).all()
+        if ccap == n:
+            assert ok.all()
+    if keep <= 0.1:
+        assert bad.any()
+
+
 @pytest.fixture(scope="module")
 def nsg_case(tmp_path_factory):
     n, dim = 3000, 24

@@ -14,8 +14,10 @@ batched insertion) on the first knn_query / save_index after an add; knn_query i
 for the whole query batch. `num_threads` arguments are accepted and ignored. There is no CPU path: without the
 CUDA library every compute call raises.
 
-Not on the GPU path yet (raise NotImplementedError, loudly, instead of answering differently from the reference):
-knn_query(filter=...) on Index, mark_deleted / unmark_deleted, add_items(replace_deleted=True)."""
+knn_query(filter=...) and mark_deleted / unmark_deleted run the reference's searchBaseLayerST<false> on the GPU
+(b200ann_hnsw_search_filtered): the Python callable is evaluated once per call over all labels into a bitmap.
+Not on the GPU path yet (raises NotImplementedError instead of answering differently from the reference):
+add_items(replace_deleted=True)."""
 import importlib
 import pickle  # noqa: F401  (Index/BFIndex define __getstate__/__setstate__)
 
@@ -74,8 +76,9 @@ def _normalize(a):
 _INVALID = 0xFFFFFFFF
 
 
-def _write_hnsw_file(path, g, vec, max_elements, M, efc):
-    """g: the flat dict Index.get_hnsw() returns; vec [n,dim] fp32 as stored (normalised for cosine)"""
+def _write_hnsw_file(path, g, vec, max_elements, M, efc, deleted=None):
+    """g: the flat dict Index.get_hnsw() returns; vec [n,dim] fp32 as stored (normalised for cosine); deleted [n] bool:
+    markDelete's DELETE_MARK, bit 0 of byte 2 of the level-0 list header (hnswalg.h:21, :864-878)"""
     n, dim = vec.shape
     maxM, maxM0 = int(g["maxM"]), int(g["maxM0"])
     sl0 = maxM0 * 4 + 4
@@ -93,6 +96,8 @@ def _write_hnsw_file(path, g, vec, max_elements, M, efc):
         l0 = np.ascontiguousarray(g["links0"], np.uint32)
         cnt = (l0 != _INVALID).sum(1).astype(np.uint16)           # rows are packed first, INVALID padded
         blob[:, 0:2] = cnt.view(np.uint8).reshape(n, 2)
+        if deleted is not None:
+            blob[:, 2] = np.asarray(deleted, bool).astype(np.uint8)
         blob[:, 4:sl0] = np.where(l0 == _INVALID, 0, l0).astype(np.uint32).view(np.uint8).reshape(n, maxM0 * 4)
         blob[:, sl0:sl0 + dim * 4] = np.ascontiguousarray(vec, np.float32).view(np.uint8).reshape(n, dim * 4)
         blob[:, sl0 + dim * 4:] = np.ascontiguousarray(g["labels"], np.uint64).view(np.uint8).reshape(n, 8)
@@ -134,6 +139,7 @@ def _read_hnsw_file(path, dim):
         raise RuntimeError("index file dimension does not match the space")
     blob = raw[96:96 + n * sdpe].reshape(n, sdpe)
     cnt = blob[:, off_l0:off_l0 + 2].copy().view(np.uint16).reshape(n).astype(np.int64)
+    deleted = (blob[:, off_l0 + 2] & 1).astype(bool)             # hnswalg.h:811-815
     l0 = blob[:, off_l0 + 4:off_l0 + 4 + 4 * maxM0].copy().view(np.uint32).reshape(n, maxM0)
     links0 = np.where(np.arange(maxM0)[None, :] < cnt[:, None], l0, _INVALID).astype(np.uint32)
     vec = blob[:, off_data:off_data + 4 * dim].copy().view(np.float32).reshape(n, dim)
@@ -163,7 +169,7 @@ def _read_hnsw_file(path, dim):
     return dict(n=n, M=M, maxM=maxM, maxM0=maxM0, efc=efc, ep=ep, maxlevel=maxlevel, max_elements=maxel,
                 links0=np.ascontiguousarray(links0), levels=levels, upper_ptr=upper_ptr,
                 upper_links=np.ascontiguousarray(upper), labels=np.ascontiguousarray(labels),
-                vectors=np.ascontiguousarray(vec))
+                vectors=np.ascontiguousarray(vec), deleted=deleted)
 
 
 class Index:
@@ -193,6 +199,7 @@ class Index:
         self._allow_replace = bool(allow_replace_deleted)
         self._vec = np.zeros((0, self.dim), np.float32)
         self._labels = np.zeros(0, np.uint64)
+        self._deleted = np.zeros(0, bool)
         self._lookup = {}
         self._cur_l = 0
         self._inited = True
@@ -219,6 +226,7 @@ class Index:
                 if at is not None:
                     if at < len(self._vec):
                         self._vec[at] = rows[r]
+                        self._deleted[at] = False                 # hnswalg.h:1166-1168: an update un-deletes
                     else:
                         new_rows[at - len(self._vec)] = r
                     continue
@@ -231,6 +239,7 @@ class Index:
             if new_rows:
                 self._vec = np.concatenate([self._vec, rows[new_rows]])
                 self._labels = np.concatenate([self._labels, np.array(new_labels, np.uint64)])
+                self._deleted = np.concatenate([self._deleted, np.zeros(len(new_labels), bool)])
             self._dirty = True
             self._graph = None
 
@@ -260,18 +269,26 @@ class Index:
     def knn_query(self, data, k=1, num_threads=-1, filter=None):
         """bindings.cpp:612-698 -> (labels uint64 [rows,k], distances float32 [rows,k]), nearest first"""
         self._need_init()
-        if filter is not None:
-            raise NotImplementedError("knn_query(filter=...) is not on the GPU path yet (use BFIndex for a filtered exact scan)")
         q = _as_rows(data, self.dim)
         if self._normalize:
             q = _normalize(q)
         self._build()
         k = int(k)
+        short = "Cannot return the results in a contiguous 2D array. Probably ef or M is too small"
         if self._ix is None or k > len(self._labels):
-            raise RuntimeError("Cannot return the results in a contiguous 2D array. Probably ef or M is too small")
-        lab, d = self._ix.hnsw_search(q, k, max(self._ef, k))     # searchKnn uses max(ef_, k), hnswalg.h:1303
-        if (d[:, k - 1] == np.inf).any() or (lab[:, k - 1] == np.uint64(0xFFFFFFFFFFFFFFFF)).any():
-            raise RuntimeError("Cannot return the results in a contiguous 2D array. Probably ef or M is too small")
+            raise RuntimeError(short)
+        if filter is None and not self._deleted.any():            # hnswalg.h:1306 bare_bone_search
+            lab, d = self._ix.hnsw_search(q, k, max(self._ef, k))  # searchKnn uses max(ef_, k), :1309
+        else:
+            allow = ~self._deleted
+            if filter is not None:                                # CustomFilterFunctor, bindings.cpp:129-142
+                allow &= np.fromiter((bool(filter(l)) for l in self._labels.tolist()), bool, len(self._labels))
+            lab, d, bad = self._ix.hnsw_search_filtered(q, k, max(self._ef, k), allow)
+            if bad.any():
+                raise RuntimeError("knn_query: the filter is too selective for the graph walk on %d queries (candidate "
+                                   "set overflow); use BFIndex.knn_query(filter=...) for an exact scan" % int(bad.sum()))
+        if (lab[:, k - 1] == np.uint64(0xFFFFFFFFFFFFFFFF)).any():
+            raise RuntimeError(short)
         return lab, d
 
     def set_ef(self, ef):
@@ -317,11 +334,26 @@ class Index:
             raise RuntimeError("Cannot resize, max element is less than the current number of elements")
         self._max = int(new_size)
 
+    def _row_of(self, label):
+        self._need_init()
+        at = self._lookup.get(int(label))
+        if at is None:
+            raise RuntimeError("Label not found")                 # hnswalg.h:859
+        return at
+
     def mark_deleted(self, label):
-        raise NotImplementedError("mark_deleted is not on the GPU path yet")
+        """hnswalg.h:853-885 markDelete: the element stays in the graph, is walked through and never returned"""
+        at = self._row_of(label)
+        if self._deleted[at]:
+            raise RuntimeError("The requested to delete element is already deleted")
+        self._deleted[at] = True
 
     def unmark_deleted(self, label):
-        raise NotImplementedError("unmark_deleted is not on the GPU path yet")
+        """hnswalg.h:893-922 unmarkDelete"""
+        at = self._row_of(label)
+        if not self._deleted[at]:
+            raise RuntimeError("The requested to undelete element is not deleted")
+        self._deleted[at] = False
 
     M = property(lambda self: self._M if self._inited else 0)
     ef_construction = property(lambda self: self._efc if self._inited else 0)
@@ -338,7 +370,7 @@ class Index:
                      upper_links=np.zeros((0, self._M), np.uint32), labels=self._labels)
         else:
             g = self._ix.get_hnsw()
-        _write_hnsw_file(path_to_index, g, self._vec, self._max, self._M, self._efc)
+        _write_hnsw_file(path_to_index, g, self._vec, self._max, self._M, self._efc, self._deleted)
 
     def index_file_size(self):
         self._build()
@@ -356,6 +388,7 @@ class Index:
         self._seed = 100
         self._allow_replace = bool(allow_replace_deleted)
         self._vec, self._labels = g["vectors"], g["labels"]
+        self._deleted = g["deleted"].copy()
         self._lookup = {int(l): i for i, l in enumerate(self._labels.tolist())}
         self._graph = g
         self._cur_l = len(self._labels)                           # :236
@@ -368,7 +401,7 @@ class Index:
                   inited=self._inited)
         if self._inited:
             self._build()
-            st.update(cur_l=self._cur_l, max=self._max, M=self._M, efc=self._efc, seed=self._seed, vec=self._vec, labels=self._labels,
+            st.update(cur_l=self._cur_l, max=self._max, M=self._M, efc=self._efc, seed=self._seed, vec=self._vec, labels=self._labels, deleted=self._deleted,
                       graph=self._ix.get_hnsw() if self._ix is not None else None)
         return st
 
@@ -377,7 +410,7 @@ class Index:
         self._ef, self.num_threads = st["ef"], st["num_threads"]
         if st["inited"]:
             self.init_index(st["max"], st["M"], st["efc"], st["seed"])
-            self._vec, self._labels = st["vec"], st["labels"]
+            self._vec, self._labels, self._deleted = st["vec"], st["labels"], st["deleted"]
             self._lookup = {int(l): i for i, l in enumerate(self._labels.tolist())}
             self._graph = st["graph"]
             self._cur_l = st["cur_l"]

@@ -295,9 +295,11 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     std::vector<char> blob(n * size_data_per_element);
     in.read(blob.data(), (std::streamsize)blob.size());
     vec_.resize(n * dim_); labels_.resize(n); links0_.assign(n * maxM0_, B200ANN_INVALID);
+    deleted_.assign(n, 0); num_deleted_ = 0;
     for (size_t i = 0; i < n; i++) {
       const char *row = blob.data() + i * size_data_per_element;
       unsigned short cnt = *(const unsigned short *)(row + offsetLevel0);
+      if (*(const unsigned char *)(row + offsetLevel0 + 2) & DELETE_MARK) { deleted_[i] = 1; num_deleted_++; }  // :811-815
       std::memcpy(&links0_[i * maxM0_], row + offsetLevel0 + 4, (size_t)cnt * 4);
       std::memcpy(&vec_[i * dim_], row + offsetData, dim_ * sizeof(float));
       labeltype lab;
@@ -344,6 +346,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
       unsigned short cnt = 0;
       while (cnt < maxM0_ && links0_[i * maxM0_ + cnt] != B200ANN_INVALID) cnt++;
       std::memcpy(row.data(), &cnt, 2);
+      if (deleted_[i]) row[2] = (char)DELETE_MARK;  // the mark lives in the upper half of the list-size word (:864-878)
       std::memcpy(row.data() + 4, &links0_[i * maxM0_], (size_t)cnt * 4);
       std::memcpy(row.data() + offsetData, &vec_[i * dim_], data_size);
       labeltype lab = labels_[i];
@@ -372,6 +375,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     std::unique_lock<std::mutex> lock(mu_);
     auto it = label_lookup_.find(label);
     if (it != label_lookup_.end()) {
+      if (deleted_[it->second]) { deleted_[it->second] = 0; num_deleted_--; }  // :1166-1168: an update un-deletes
       std::memcpy(&vec_[it->second * dim_], datapoint, dim_ * sizeof(float));
       dirty_ = true;
       return;
@@ -380,46 +384,77 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     label_lookup_[label] = cur_element_count;
     vec_.insert(vec_.end(), (const float *)datapoint, (const float *)datapoint + dim_);
     labels_.push_back(label);
+    deleted_.push_back(0);
     cur_element_count++;
     dirty_ = true;
   }
+  // hnswalg.h:853-911 markDelete / :893-922 unmarkDelete: the element stays in the graph and is walked through, but is
+  // never returned (searchBaseLayerST<false>); same exceptions as the reference
+  void markDelete(labeltype label) {
+    std::unique_lock<std::mutex> lock(mu_);
+    auto it = label_lookup_.find(label);
+    if (it == label_lookup_.end()) throw std::runtime_error("Label not found");
+    if (deleted_[it->second]) throw std::runtime_error("The requested to delete element is already deleted");
+    deleted_[it->second] = 1; num_deleted_++;
+  }
+  void unmarkDelete(labeltype label) {
+    std::unique_lock<std::mutex> lock(mu_);
+    auto it = label_lookup_.find(label);
+    if (it == label_lookup_.end()) throw std::runtime_error("Label not found");
+    if (!deleted_[it->second]) throw std::runtime_error("The requested to undelete element is not deleted");
+    deleted_[it->second] = 0; num_deleted_--;
+  }
+  bool isMarkedDeleted(tableint internal_id) const { return deleted_[internal_id] != 0; }
+  size_t getDeletedCount() const { return num_deleted_; }
+  size_t getCurrentElementCount() const { return cur_element_count; }
+  size_t getMaxElements() const { return max_elements_; }
   // builds the graph of everything added so far on the GPU (no-op when up to date). info8: b200ann_hnsw_build's.
   void build(uint64_t *info8 = nullptr) {
     std::unique_lock<std::mutex> lock(mu_);
     build_locked(info8);
   }
 
-  // [nq,k] rows, ascending distance; throws when some row has fewer than k results (bindings.cpp:646-648)
-  void searchKnnBatch(const float *queries, size_t nq, size_t k, labeltype *labels, dist_t *dists) const {
+  // [nq,k] rows, ascending distance. Without a filter and without deleted elements: b200ann_hnsw_search (throws when
+  // some row has fewer than k results, bindings.cpp:646-648). Otherwise searchBaseLayerST<false> on the GPU
+  // (b200ann_hnsw_search_filtered): the functor is evaluated ONCE per batch over all labels into a bitmap; short
+  // rows are padded with ~0 / +inf.
+  void searchKnnBatch(const float *queries, size_t nq, size_t k, labeltype *labels, dist_t *dists,
+                      BaseFilterFunctor *isIdAllowed = nullptr) const {
     std::vector<uint64_t> lab(nq * k);
     std::unique_lock<std::mutex> lock(mu_);
     build_locked(nullptr);
-    detail::check(gpu_.h, b200ann_hnsw_search(gpu_.h, ix_, queries, nq, dim_, k, ef_, lab.data(), dists, nullptr), "HierarchicalNSW::searchKnn");
+    if (!num_deleted_ && !isIdAllowed) {  // :1306 bare_bone_search
+      detail::check(gpu_.h, b200ann_hnsw_search(gpu_.h, ix_, queries, nq, dim_, k, ef_, lab.data(), dists, nullptr), "HierarchicalNSW::searchKnn");
+    } else {
+      std::vector<uint32_t> allow = allow_bitmap(isIdAllowed);
+      detail::check(gpu_.h, b200ann_hnsw_search_filtered(gpu_.h, ix_, queries, nq, dim_, k, ef_, allow.data(), lab.data(), dists,
+                                                         nullptr, nullptr), "HierarchicalNSW::searchKnn (filtered)");
+    }
     for (size_t i = 0; i < nq * k; i++) labels[i] = (labeltype)lab[i];
   }
-  // hnswalg.h:1270-1324: max-heap of (distance,label), at most k entries; no exception when fewer
-  // than k exist. A filter (not bare_bone, :1306) is honoured by widening the beam on the host side.
+  // hnswalg.h:1270-1324: max-heap of (distance,label), at most k entries; no exception when fewer than k exist
   std::priority_queue<std::pair<dist_t, labeltype>> searchKnn(const void *query_data, size_t k,
                                                               BaseFilterFunctor *isIdAllowed = nullptr) const override {
     std::priority_queue<std::pair<dist_t, labeltype>> res;
     if (cur_element_count == 0) return res;
-    size_t kk = k < cur_element_count ? k : cur_element_count;
-    for (;;) {
-      std::vector<uint64_t> lab(kk);
-      std::vector<dist_t> d(kk);
-      {
-        std::unique_lock<std::mutex> lock(mu_);
-        build_locked(nullptr);
-        size_t ef = ef_ > kk ? ef_ : kk;
-        int rc = b200ann_hnsw_search(gpu_.h, ix_, (const float *)query_data, 1, dim_, kk, ef, lab.data(), d.data(), nullptr);
+    std::vector<uint64_t> lab(k);
+    std::vector<dist_t> d(k);
+    {
+      std::unique_lock<std::mutex> lock(mu_);
+      build_locked(nullptr);
+      if (!num_deleted_ && !isIdAllowed) {
+        size_t kk = k < cur_element_count ? k : cur_element_count;
+        int rc = b200ann_hnsw_search(gpu_.h, ix_, (const float *)query_data, 1, dim_, kk, ef_, lab.data(), d.data(), nullptr);
         if (rc != 0 && rc != B200ANN_ERR_FEWER) detail::check(gpu_.h, rc, "HierarchicalNSW::searchKnn");
+        for (size_t i = kk; i < k; i++) lab[i] = ~(uint64_t)0;
+      } else {
+        std::vector<uint32_t> allow = allow_bitmap(isIdAllowed);
+        detail::check(gpu_.h, b200ann_hnsw_search_filtered(gpu_.h, ix_, (const float *)query_data, 1, dim_, k, ef_, allow.data(),
+                                                           lab.data(), d.data(), nullptr, nullptr), "HierarchicalNSW::searchKnn (filtered)");
       }
-      res = std::priority_queue<std::pair<dist_t, labeltype>>();
-      for (size_t i = 0; i < kk && res.size() < k; i++)
-        if (lab[i] != ~(uint64_t)0 && (!isIdAllowed || (*isIdAllowed)((labeltype)lab[i]))) res.emplace(d[i], (labeltype)lab[i]);
-      if (res.size() >= k || kk == cur_element_count || !isIdAllowed) break;
-      kk = kk * 4 < cur_element_count ? kk * 4 : cur_element_count;
     }
+    for (size_t i = 0; i < k; i++)
+      if (lab[i] != ~(uint64_t)0) res.emplace(d[i], (labeltype)lab[i]);
     return res;
   }
 
@@ -430,6 +465,17 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
   size_t generation() const { return gen_; }  // bumped whenever the device index is re-created
 
  private:
+  // bit i set <=> !isMarkedDeleted(i) && (*isIdAllowed)(getExternalLabel(i)) (hnswalg.h:325-326, :406-407)
+  std::vector<uint32_t> allow_bitmap(BaseFilterFunctor *f) const {
+    const size_t n = cur_element_count;
+    std::vector<uint32_t> bits((n + 31) / 32, 0u);
+    for (size_t i = 0; i < n; i++)
+      if (!deleted_[i] && (!f || (*f)(labels_[i]))) bits[i >> 5] |= 1u << (i & 31);
+    return bits;
+  }
+  static const unsigned char DELETE_MARK = 0x01;  // hnswalg.h:21
+  std::vector<unsigned char> deleted_;
+  size_t num_deleted_ = 0;
   template <typename T> static void rd(std::istream &in, T &v) { in.read((char *)&v, sizeof(T)); }
   template <typename T> static void wr(std::ostream &out, const T &v) { out.write((const char *)&v, sizeof(T)); }
   void upload() {

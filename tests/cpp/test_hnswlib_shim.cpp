@@ -93,6 +93,51 @@ int main(int argc, char **argv) {
     bool threw = false;
     try { hnswlib::HierarchicalNSW<float> bad(&space, std::string("/nonexistent/file.bin")); } catch (std::runtime_error &) { threw = true; }
     CHECK(threw);
+    // ---- searchKnnWithFilter_test.cpp:33-88 on the HNSW index: only labels divisible by 3 come back, PickNothing
+    // gives an empty result; then markDelete (hnswalg.h:853-911): deleted labels never come back, unknown / repeated
+    // labels throw like the reference, the marks survive saveIndex -> load, unmarkDelete restores the answers
+    PickDivisibleIds pick3(3);
+    struct PickNothing : hnswlib::BaseFilterFunctor { bool operator()(hnswlib::labeltype) override { return false; } } none;
+    for (size_t j = 0; j < 20; j++) {
+      auto res = index.searchKnnCloserFirst(q.data() + j * dim, k, &pick3);
+      CHECK(res.size() == k);
+      for (auto &r : res) CHECK(r.second % 3 == 0);
+      for (size_t i = 1; i < res.size(); i++) CHECK(res[i - 1].first <= res[i].first);
+      CHECK(index.searchKnn(q.data() + j * dim, k, &none).empty());
+    }
+    std::set<hnswlib::labeltype> gone;
+    for (size_t j = 0; j < nq; j++) for (size_t i = 0; i < 3; i++) gone.insert(lab[j * k + i]);
+    for (auto l : gone) index.markDelete(l);
+    CHECK(index.getDeletedCount() == gone.size());
+    threw = false; try { index.markDelete(*gone.begin()); } catch (std::runtime_error &) { threw = true; } CHECK(threw);
+    threw = false; try { index.markDelete(987654321); } catch (std::runtime_error &) { threw = true; } CHECK(threw);
+    std::vector<hnswlib::labeltype> labd(nq * k); std::vector<float> distd(nq * k);
+    index.searchKnnBatch(q.data(), nq, k, labd.data(), distd.data(), &pick3);   // deleted marks AND a filter
+    for (size_t i = 0; i < nq * k; i++) CHECK(labd[i] % 3 == 0 && !gone.count(labd[i]));
+    index.searchKnnBatch(q.data(), nq, k, labd.data(), distd.data());           // deleted marks only
+    for (size_t i = 0; i < nq * k; i++) CHECK(!gone.count(labd[i]));
+    for (size_t j = 0; j < nq; j++) {  // what was 4th is first now
+      CHECK(labd[j * k] == lab[j * k + 3] || gone.count(lab[j * k + 3]));
+    }
+    std::string outd = std::string(argv[1]) + ".deleted";
+    index.saveIndex(outd);
+    hnswlib::HierarchicalNSW<float> marked(&space, outd);
+    CHECK(marked.getDeletedCount() == gone.size());
+    marked.setEf(100);
+    std::vector<hnswlib::labeltype> labm(nq * k); std::vector<float> distm(nq * k);
+    marked.searchKnnBatch(q.data(), nq, k, labm.data(), distm.data());
+    CHECK(labm == labd && distm == distd);
+    {  // queries + answers for the python driver, which asks the unmodified reference the same question
+      FILE *f = fopen((std::string(argv[1]) + ".deleted.q").c_str(), "wb");
+      fwrite(q.data(), sizeof(float), q.size(), f); fclose(f);
+      std::vector<unsigned long long> l64(labd.begin(), labd.end());
+      f = fopen((std::string(argv[1]) + ".deleted.labels").c_str(), "wb");
+      fwrite(l64.data(), 8, l64.size(), f); fclose(f);
+    }
+    for (auto l : gone) index.unmarkDelete(l);
+    threw = false; try { index.unmarkDelete(*gone.begin()); } catch (std::runtime_error &) { threw = true; } CHECK(threw);
+    index.searchKnnBatch(q.data(), nq, k, labd.data(), distd.data());
+    CHECK(labd == lab && distd == dist);
   }
   {  // ---- construction through the reference API (hnswlib/examples/cpp/example_search.cpp): addPoint loop from
      // several threads, searchKnn of every stored point finds itself, capacity error, saveIndex -> load ctor

@@ -65,6 +65,15 @@ def test_hnswlib_shim_driver(tmp_path):
     a, ad = ref.search(q, 10, 50, threads=1)
     b, bd = again.search(q, 10, 50, threads=1)
     assert (a == b).all() and (ad == bd).all()
+    # the file saved with delete marks: the unmodified reference sees the same marks and, searching the same queries
+    # (searchBaseLayerST<false> on the CPU), returns the labels the GPU returned (CPU vs GPU distance rounding only)
+    marked = R.RefHnsw(0, dim, path=path + ".deleted")
+    qd = np.fromfile(path + ".deleted.q", np.float32).reshape(-1, dim)
+    want = np.fromfile(path + ".deleted.labels", np.uint64).reshape(len(qd), 10)
+    got, _ = marked.search_filtered(qd, 10, 100, None, threads=1)
+    assert (got == want).mean() > 0.995
+    orig, _ = ref.search(qd, 10, 100, threads=1)
+    assert (got[:, 0] != orig[:, 0]).all()                            # the original nearest neighbours are the deleted ones
     # the index the shim BUILT on the GPU (addPoint + build + saveIndex) loads in the unmodified reference, which
     # finds every stored point as its own nearest neighbour
     built = R.RefHnsw(0, 16, path=path + ".gpubuilt")

@@ -172,3 +172,56 @@ def test_bfindex_filter_delete_cosine(hnswlib, tmp_path):
     assert np.isinf(d5[:, 3:]).all() and np.isfinite(d5[:, :3]).all()
     for x in (bf, b2, few):
         x.close()
+
+
+def test_filter_and_mark_deleted(hnswlib, tmp_path):
+    # bindings_test_filter.py (only even labels come back, recall against the filtered brute force) and the
+    # mark_deleted half of bindings_test_labels.py:77-127 (deleted labels never come back, the marks survive
+    # save_index -> load_index, unmark_deleted restores them)
+    dim, n, k = 16, 10000, 10
+    rng = np.random.default_rng(3)
+    data = rng.random((n, dim), dtype=np.float32)
+    q = rng.random((200, dim), dtype=np.float32)
+    p = hnswlib.Index("l2", dim)
+    p.init_index(n, ef_construction=100, M=16)
+    p.set_ef(100)
+    p.add_items(data)
+    bf = hnswlib.BFIndex("l2", dim)
+    bf.init_index(n)
+    bf.add_items(data)
+    even = lambda l: l % 2 == 0
+    lh, dh = p.knn_query(q, k, filter=even)
+    lb, db = bf.knn_query(q, k, filter=even)
+    assert (lh % 2 == 0).all()
+    rec = np.mean([len(set(lh[i].tolist()) & set(lb[i].tolist())) for i in range(len(q))]) / k
+    assert rec > 0.95, rec
+    with pytest.raises(RuntimeError, match="contiguous 2D array"):
+        p.knn_query(q[:3], k, filter=lambda l: l < 5)            # only 5 labels pass: fewer than k results
+    data1 = data[:n // 2]
+    first, _ = p.knn_query(data1, k=1)
+    assert np.mean(first.reshape(-1) == np.arange(len(data1))) > 0.999
+    dead = set(first.reshape(-1).tolist())
+    for l in dead:
+        p.mark_deleted(l)
+    after, _ = p.knn_query(data1, k=1)
+    assert not (set(after.reshape(-1).tolist()) & dead)
+    l2, _ = p.knn_query(data[n // 2:], k=1)                       # the other half is untouched
+    assert np.mean(np.abs(data[n // 2:] - p.get_items(l2))) < 1e-3
+    path = str(tmp_path / "with_deleted.bin")
+    p.save_index(path)
+    p2 = hnswlib.Index("l2", dim)
+    p2.load_index(path)
+    p2.set_ef(100)
+    again, _ = p2.knn_query(data1, k=1)
+    assert (again == after).all()
+    if R.have_ref():                                              # the reference reads the marks this file carries
+        ref = R.RefHnsw(0, dim, path=path)
+        rl, _ = ref.search_filtered(np.ascontiguousarray(data1[:500]), 1, 100, None, threads=1)
+        ref.close()
+        assert (rl == after[:500]).mean() > 0.99
+    for l in dead:
+        p2.unmark_deleted(l)
+    restored, _ = p2.knn_query(data1, k=1)
+    assert np.mean(restored.reshape(-1) == np.arange(len(data1))) > 0.999
+    for x in (p, p2, bf):
+        x.close()

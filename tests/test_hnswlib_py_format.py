@@ -40,6 +40,24 @@ def test_hnsw_file_writer_reader_vs_compiled_reference(tmp_path):
     assert (l0 == l1).all() and (d0 == d1).all()
     ref.close()
     again.close()
+    # delete marks: the reference's markDelete -> file -> our reader; our writer -> the reference's loader + search
+    ref2 = R.RefHnsw(0, dim, path=p_ref)
+    dele = np.zeros(n, bool)
+    dele[::7] = True
+    for i in np.nonzero(dele)[0]:
+        ref2.mark_deleted(1000 + i)
+    p_del = str(tmp_path / "ref_deleted.bin")
+    ref2.save(p_del)
+    gd = hp._read_hnsw_file(p_del, dim)
+    assert (gd["deleted"] == dele).all() and not g["deleted"].any()
+    p_del2 = str(tmp_path / "ours_deleted.bin")
+    hp._write_hnsw_file(p_del2, g, g["vectors"], n, M, efc, deleted=dele)
+    ref3 = R.RefHnsw(0, dim, path=p_del2)
+    l2, d2 = ref2.search_filtered(q, 5, 40, None, threads=1)
+    l3, d3 = ref3.search_filtered(q, 5, 40, None, threads=1)
+    assert (l2 == l3).all() and (d2 == d3).all() and not dele[(l3 - 1000).astype(np.int64)].any()
+    ref2.close()
+    ref3.close()
     with pytest.raises(RuntimeError, match="dimension"):
         hp._read_hnsw_file(p_ref, dim + 1)
     with pytest.raises(RuntimeError, match="Cannot open file"):
@@ -112,10 +130,21 @@ def test_binding_host_logic_without_compute(tmp_path):
         p.resize_index(2)
     p.resize_index(9)
     assert p.max_elements == 9
-    for call in (lambda: p.mark_deleted(0), lambda: p.unmark_deleted(0),
-                 lambda: p.knn_query(x, 1, filter=lambda l: True), lambda: p.add_items(x[:1], replace_deleted=True)):
-        with pytest.raises(NotImplementedError):
-            call()
+    with pytest.raises(NotImplementedError):
+        p.add_items(x[:1], replace_deleted=True)
+    # markDelete bookkeeping and its error messages (hnswalg.h:853-922); an update un-deletes (:1166-1168)
+    p.mark_deleted(7)
+    with pytest.raises(RuntimeError, match="already deleted"):
+        p.mark_deleted(7)
+    with pytest.raises(RuntimeError, match="Label not found"):
+        p.mark_deleted(4242)
+    with pytest.raises(RuntimeError, match="not deleted"):
+        p.unmark_deleted(0)
+    assert p._deleted.tolist() == [False, False, True, False, False]
+    p.unmark_deleted(7)
+    p.mark_deleted(9)
+    p.add_items(x[:1], ids=[9])
+    assert not p._deleted.any()
     c = hp.Index("cosine", 4)
     c.init_index(3)
     c.add_items(np.array([[3, 0, 4, 0]], np.float32))

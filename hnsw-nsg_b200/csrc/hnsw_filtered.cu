@@ -2,9 +2,12 @@
 // functor is given or elements are marked deleted (hnswalg.h:1305-1313 -> searchBaseLayerST<false>, :309-440, no
 // stop condition). The host functor becomes a device bitmap over INTERNAL ids (bit = allowed and not deleted).
 //
-// One warp per query, persistent over the batch. Both of the reference's heaps are kept as ascending (distance,id)
-// arrays in shared memory: top_candidates (allowed elements only, <= ef) and candidate_set (every considered
-// element, consumed from the front). candidate_set is unbounded in the reference (a selective filter makes the
+// One warp per query, persistent over the batch. Both of the reference's heaps live in shared memory: top_candidates
+// (allowed elements only, <= ef) as an ascending (distance,id) array, candidate_set (every considered element) as a
+// binary min-heap on (distance,id) maintained by lane 0 (O(log) per push / pop; a selective filter makes it hold
+// tens of thousands of entries, where shifting a sorted array costs 50x more). Ties are broken by id in both, so
+// the pop order and the eviction order are those of oracle.c's sorted arrays. candidate_set is unbounded in the
+// reference (a selective filter makes the
 // walk consider ~ef/selectivity elements before top_candidates fills); here it holds `ccap` entries, the farthest
 // entry is dropped when it is full, and the query is reported INEXACT as soon as the reference could have expanded
 // a dropped entry (oracle.c hnsw_base_pools_filtered states the rule) - a query that is not reported is the
@@ -62,17 +65,54 @@ __device__ __forceinline__ void shift_up(float *ad, uint32_t *ai, int from, int 
     __syncwarp();
   }
 }
-// entries [from, to) move down by one slot
-__device__ __forceinline__ void shift_down(float *ad, uint32_t *ai, int from, int to, int lane) {
-  for (int jb = from; jb < to; jb += 32) {
-    int j = jb + lane;
-    bool mv = j < to;
-    float td = 0.f; uint32_t ti = 0;
-    if (mv) { td = ad[j]; ti = ai[j]; }
-    __syncwarp();
-    if (mv) { ad[j - 1] = td; ai[j - 1] = ti; }
-    __syncwarp();
+__device__ __forceinline__ bool pless(float da, uint32_t ia, float db, uint32_t ib) {
+  return da < db || (da == db && ia < ib);
+}
+// binary min-heap on (d,id); called by ONE lane
+__device__ __forceinline__ void heap_sift_up(float *hd, uint32_t *hi, uint32_t i, float d, uint32_t id) {
+  while (i > 0) {
+    uint32_t par = (i - 1) >> 1;
+    float pd = hd[par]; uint32_t pi = hi[par];
+    if (!pless(d, id, pd, pi)) break;
+    hd[i] = pd; hi[i] = pi;
+    i = par;
   }
+  hd[i] = d; hi[i] = id;
+}
+// removes the root of a heap of n entries (n >= 1)
+__device__ __forceinline__ void heap_pop(float *hd, uint32_t *hi, uint32_t n) {
+  n--;
+  float d = hd[n]; uint32_t id = hi[n];
+  uint32_t i = 0;
+  for (;;) {
+    uint32_t l = 2 * i + 1;
+    if (l >= n) break;
+    float cdv = hd[l]; uint32_t civ = hi[l]; uint32_t c = l;
+    if (l + 1 < n) {
+      float rd = hd[l + 1]; uint32_t ri = hi[l + 1];
+      if (pless(rd, ri, cdv, civ)) { cdv = rd; civ = ri; c = l + 1; }
+    }
+    if (!pless(cdv, civ, d, id)) break;
+    hd[i] = cdv; hi[i] = civ;
+    i = c;
+  }
+  if (n) { hd[i] = d; hi[i] = id; }
+}
+// slot of the largest (d,id) of a heap of n entries: it is a leaf; warp-wide scan of the leaves
+__device__ __forceinline__ uint32_t heap_argmax(const float *hd, const uint32_t *hi, uint32_t n, int lane) {
+  float bd = -INFINITY; uint32_t bi = 0, bs = 0xffffffffu;
+  for (uint32_t j = n / 2 + lane; j < n; j += 32) {
+    float d = hd[j]; uint32_t id = hi[j];
+    if (bs == 0xffffffffu || pless(bd, bi, d, id)) { bd = d; bi = id; bs = j; }
+  }
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    float od = __shfl_xor_sync(0xffffffffu, bd, off);
+    uint32_t oi = __shfl_xor_sync(0xffffffffu, bi, off);
+    uint32_t os = __shfl_xor_sync(0xffffffffu, bs, off);
+    if (os != 0xffffffffu && (bs == 0xffffffffu || pless(bd, bi, od, oi))) { bd = od; bi = oi; bs = os; }
+  }
+  return bs;
 }
 
 template <int TEAM, int NCH, bool IP>
@@ -99,7 +139,7 @@ __global__ void __launch_bounds__(FW * 32) hnsw_filtered_kernel(const FilterPara
     }
     float curdist;
     const uint32_t ep = b.descend_upper(p.ep, curdist);
-    uint32_t nt = 0, nc = 0, h = 0;
+    uint32_t nt = 0, nc = 0;
     float LB, dmin = INFINITY;
     bool bad = false;
     const bool ep_ok = (__ldg(fp.allow + (ep >> 5)) >> (ep & 31)) & 1u;
@@ -116,13 +156,14 @@ __global__ void __launch_bounds__(FW * 32) hnsw_filtered_kernel(const FilterPara
     __syncwarp();
 
     for (;;) {
-      const float c0d = nc ? cd[h] : INFINITY;
+      const float c0d = nc ? cd[0] : INFINITY;
       if (dmin < INFINITY && (nc == 0 || dmin <= c0d) && !(dmin > LB && nt == ef)) bad = true;
       if (nc == 0) break;
       if (c0d > LB && nt == ef) break;  // :355
-      const uint32_t node = ci[h];
-      h++; nc--;
-      if (nc == 0) h = 0;
+      const uint32_t node = ci[0];
+      __syncwarp();
+      if (lane == 0) heap_pop(cd, ci, nc);
+      nc--;
       b.n_hops++;
       // unvisited neighbours, in row order, marked visited (:385-386)
       const uint32_t *row = p.graph + (size_t)node * p.gstride;
@@ -155,27 +196,22 @@ __global__ void __launch_bounds__(FW * 32) hnsw_filtered_kernel(const FilterPara
           uint32_t id = b.cand_i[c0 + bsel];
           if (!(nt < ef || dd < LB)) continue;  // :395 with the live bound
           // candidate_set.emplace (:398)
-          bool put = true;
           if (nc == fp.ccap) {  // full: the farthest of (entries, new) goes
-            float ld = cd[h + nc - 1];
-            uint32_t li = ci[h + nc - 1];
+            uint32_t slot = heap_argmax(cd, ci, nc, lane);
+            float ld = cd[slot];
+            uint32_t li = ci[slot];
             float yd = dd;
-            if (dd < ld || (dd == ld && id < li)) { yd = ld; nc--; } else { put = false; }
-            if (!(nt == ef && yd > LB) && yd < dmin) dmin = yd;
-          }
-          if (put) {
-            uint32_t before = count_before(cd, ci, h, nc, dd, id, lane);
-            if (h + nc < fp.ccap) {
-              shift_up(cd, ci, (int)(h + before), (int)(h + nc), lane);
-              if (lane == 0) { cd[h + before] = dd; ci[h + before] = id; }
-            } else {  // no room behind the tail: the front part moves into the consumed slots
-              shift_down(cd, ci, (int)h, (int)(h + before), lane);
-              h--;
-              if (lane == 0) { cd[h + before] = dd; ci[h + before] = id; }
-            }
-            nc++;
             __syncwarp();
+            if (pless(dd, id, ld, li)) {
+              yd = ld;
+              if (lane == 0) heap_sift_up(cd, ci, slot, dd, id);  // a leaf got smaller: it can only move up
+            }
+            if (!(nt == ef && yd > LB) && yd < dmin) dmin = yd;
+          } else {
+            if (lane == 0) heap_sift_up(cd, ci, nc, dd, id);
+            nc++;
           }
+          __syncwarp();
           // top_candidates.emplace for allowed elements (:406-408), pop the farthest beyond ef (:413-424)
           if ((__ldg(fp.allow + (id >> 5)) >> (id & 31)) & 1u) {
             if (nt == ef) nt--;  // the new element is closer than the farthest one (dd < LB)

@@ -404,6 +404,12 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     if (!deleted_[it->second]) throw std::runtime_error("The requested to undelete element is not deleted");
     deleted_[it->second] = 0; num_deleted_--;
   }
+  // hnswalg.h:640-675: only the capacity changes here (the staging vectors grow on demand)
+  void resizeIndex(size_t new_max_elements) {
+    std::unique_lock<std::mutex> lock(mu_);
+    if (new_max_elements < cur_element_count) throw std::runtime_error("Cannot resize, max element is less than the current number of elements");
+    max_elements_ = new_max_elements;
+  }
   bool isMarkedDeleted(tableint internal_id) const { return deleted_[internal_id] != 0; }
   size_t getDeletedCount() const { return num_deleted_; }
   size_t getCurrentElementCount() const { return cur_element_count; }

@@ -153,9 +153,15 @@ int main(int argc, char **argv) {
     bool threw = false;
     try { alg->addPoint(data.data(), 999999); } catch (std::runtime_error &) { threw = true; }
     CHECK(threw);  // hnswalg.h:1178
+    threw = false;
+    try { alg->resizeIndex(n - 1); } catch (std::runtime_error &) { threw = true; }
+    CHECK(threw);  // :642
+    alg->resizeIndex(n + 1);
+    alg->addPoint(data.data(), 999999);  // fits now; same vector as label 10
+    CHECK(alg->cur_element_count == n + 1);
     uint64_t info[8];
     alg->build(info);
-    CHECK(alg->cur_element_count == n && alg->maxlevel_ >= 1 && alg->M_ == 16 && alg->maxM0_ == 32);
+    CHECK(alg->cur_element_count == n + 1 && alg->maxlevel_ >= 1 && alg->M_ == 16 && alg->maxM0_ == 32);
     float correct = 0;
     for (size_t i = 0; i < n; i++) {
       auto r = alg->searchKnn(data.data() + i * dim, 1);
@@ -168,7 +174,7 @@ int main(int argc, char **argv) {
       std::string out = std::string(argv[1]) + ".gpubuilt";
       alg->saveIndex(out);
       hnswlib::HierarchicalNSW<float> again(&space, out);
-      CHECK(again.cur_element_count == n && again.maxlevel_ == alg->maxlevel_ && again.enterpoint_node_ == alg->enterpoint_node_);
+      CHECK(again.cur_element_count == n + 1 && again.maxlevel_ == alg->maxlevel_ && again.enterpoint_node_ == alg->enterpoint_node_);
       std::vector<hnswlib::labeltype> a(10 * 5), b(10 * 5); std::vector<float> da(50), db(50);
       alg->setEf(50); again.setEf(50);
       alg->searchKnnBatch(data.data(), 10, 5, a.data(), da.data());

@@ -52,6 +52,7 @@ struct SearchParams {
   uint32_t *entry_out;          // mode 2: [nq] or NULL
   uint32_t cand_cap, pool_cap;  // words
   uint32_t *ids; uint64_t *labels_out; float *dists; uint32_t *stats;
+  uint32_t *work;               // search kernels: queue counter (NULL = query index from the launch grid)
 };
 
 __device__ __forceinline__ uint32_t mix32(uint32_t x) {

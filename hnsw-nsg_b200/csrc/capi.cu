@@ -2,6 +2,7 @@
 // checks, host<->device staging, stream/event bookkeeping. All arithmetic is in the kernels.
 #include <math.h>
 #include <string.h>
+#include <stdlib.h>
 #include <cstring>
 #include <vector>
 #include "common.cuh"
@@ -69,6 +70,7 @@ int b200ann_create(int device, b200ann_handle_t *out) {
     return B200ANN_ERR_CUDA;
   }
   cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device);
+  if (const char *e = getenv("B200ANN_PERSISTENT")) h->persistent = atoi(e);  // tuning knob: 0 = one launch slot per query
   {  // keep the stream-ordered scratch pool mapped between calls (default: released at every synchronize)
     cudaMemPool_t pool;
     if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
@@ -85,6 +87,7 @@ int b200ann_destroy(b200ann_handle_t h) {
   if (!h) return 0;
   cudaSetDevice(h->device);
   cudaStreamSynchronize(h->stream);
+  if (h->work) cudaFree(h->work);
   cudaEventDestroy(h->ev0);
   cudaEventDestroy(h->ev1);
   cudaStreamDestroy(h->stream);

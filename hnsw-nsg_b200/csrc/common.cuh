@@ -18,11 +18,15 @@ struct b200ann_handle {
   uint64_t launches = 0;
   float last_ms = 0.f;
   int visited_bits = 10;
-  int link_visited_bits = 11;   // measured on 1M x 128 K=200 L=40: Link 1.99 s (2^12), 1.51 s (2^11), 1.61 s (2^10)
+  int link_visited_bits = 0;    // 0 = auto. NSG Link is occupancy-bound by shared memory: 1M x 128 K=200 L=40 C=500 takes
+                                // 1.45 / 1.30 / 1.23 / 1.28 s with 2^11 / 2^10 / 2^9 / 2^8 slots (more warps per SM against more
+                                // re-evaluations); at dim 960 2^10 wins. auto = 2^9 for dim <= 128, else 2^10; HNSW build 2^11
   int sm_count = 148;
   int knn_mode = 0;          // 0 auto, 1 fp32 SIMT (bf_knn.cu), 2 tensor cores (knn_tc.cu)
   int knn_slack = -1;        // shortlist slack of the tensor path; < 0 = default
   uint64_t knn_stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  uint32_t *work = nullptr;  // device work-queue counter of the persistent search kernel (search.cu)
+  int persistent = 1;        // 1: search warps pull queries from the queue; 0: one query per warp, one launch slot each
   bool async_mode = false;   // b200ann_set_async: device-to-device search / merge calls do not synchronize the stream
 };
 

@@ -359,7 +359,7 @@ int hnsw_build_launch(b200ann_handle *h, b200ann_index *ix, size_t M, size_t efc
   ip.sp.L = (uint32_t)efc; ip.sp.K = (uint32_t)M;
   // visited hash of 2^11 slots per warp: measured on 1M x 128, M=16, efC=200: 2^10 1.68 s, 2^11 1.64 s, 2^12 2.10 s,
   // 2^13 3.2 s (a smaller table re-evaluates ~5 % more rows but doubles the resident warps)
-  ip.sp.hbits = h->link_visited_bits < 11 ? h->link_visited_bits : 11;
+  ip.sp.hbits = (h->link_visited_bits && h->link_visited_bits < 11) ? h->link_visited_bits : 11;
   ip.sp.pool_cap = round_up((uint32_t)efc + 1, 32);
   ip.sp.cand_cap = round_up((uint32_t)maxM0, 32);
   ip.M = (uint32_t)M; ip.nlev = nlev; ip.levels = d_levels; ip.links0 = links0; ip.upper_links = upper_links;

@@ -24,6 +24,7 @@ using namespace beam;
 namespace {
 
 constexpr int WARPS = 4;
+constexpr int LINK_MAXW = 8;  // link_kernel: warps per block are chosen at launch (shared-memory occupancy)
 
 __device__ __forceinline__ bool lex_less(float d0, uint32_t i0, float d1, uint32_t i1) {
   return d0 < d1 || (d0 == d1 && i0 < i1);
@@ -145,11 +146,11 @@ __host__ __device__ inline uint32_t link_smem_words(const LinkParams &lp) {
 }
 
 template <int TEAM, int NCH, bool IP>
-__global__ void __launch_bounds__(WARPS * 32) link_kernel(const LinkParams lp) {
+__global__ void __launch_bounds__(LINK_MAXW * 32, 1) link_kernel(const LinkParams lp) {
   extern __shared__ uint32_t smem[];
   const SearchParams &p = lp.sp;
   const int warp = threadIdx.x >> 5;
-  const uint32_t node = blockIdx.x * WARPS + warp;
+  const uint32_t node = blockIdx.x * (blockDim.x >> 5) + warp;
   if (node >= p.n) return;
   uint32_t *base = smem + (size_t)warp * link_smem_words(lp);
   typedef Beam<TEAM, NCH, IP, false> B;
@@ -519,11 +520,22 @@ SearchParams base_params(const b200ann_index *ix) {
 
 template <int TEAM, int NCH, bool IP>
 int launch_link_t(b200ann_handle *h, const LinkParams &lp) {
-  size_t smem = (size_t)WARPS * link_smem_words(lp) * 4;
-  if (smem > 227 * 1024) return set_err(h, B200ANN_ERR_ARG, "nsg_link: L / K / C need more than 227 KB shared memory per block");
+  // the kernel is occupancy-bound by shared memory (pool + candidates + visited table + collector per warp): pick the
+  // warps per block that leave the fewest bytes of the SM's 228 KB unused (each block also reserves 1 KB)
+  const size_t per_warp = (size_t)link_smem_words(lp) * 4;
+  if (per_warp > 227 * 1024) return set_err(h, B200ANN_ERR_ARG, "nsg_link: L / K / C need more than 227 KB shared memory per block");
+  int W = 1; size_t best = 0;
+  for (int w = 1; w <= LINK_MAXW; w++) {
+    size_t blk = per_warp * w;
+    if (blk > 227 * 1024) break;
+    size_t resident = (228 * 1024 / (blk + 1024)) * w;
+    if (resident > 48) resident = 48;  // beyond the register limit more warps per block only coarsen the grid
+    if (resident > best || (resident == best && w <= 4)) { best = resident; W = w; }
+  }
+  size_t smem = per_warp * W;
   auto kern = link_kernel<TEAM, NCH, IP>;
   CU_CHECK(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<(lp.sp.n + WARPS - 1) / WARPS, WARPS * 32, smem, h->stream>>>(lp);
+  kern<<<(lp.sp.n + W - 1) / W, W * 32, smem, h->stream>>>(lp);
   h->launches++;
   CU_CHECK(h, cudaGetLastError());
   return 0;
@@ -566,7 +578,8 @@ int nsg_link_launch(b200ann_handle *h, const b200ann_index *ix, const uint32_t *
   LinkParams lp = {};
   lp.sp = base_params(ix);
   lp.sp.graph = knn; lp.sp.gstride = (uint32_t)kstride; lp.sp.ep = ep;
-  lp.sp.L = (uint32_t)L; lp.sp.K = (uint32_t)L; lp.sp.seed = seed; lp.sp.hbits = h->link_visited_bits;
+  lp.sp.L = (uint32_t)L; lp.sp.K = (uint32_t)L; lp.sp.seed = seed;
+  lp.sp.hbits = h->link_visited_bits ? h->link_visited_bits : (ix->dim <= 128 ? 9 : 10);
   size_t cc = kstride > L ? kstride : L;
   if (R > cc) cc = R;
   lp.sp.cand_cap = round_up((uint32_t)cc, 32);
@@ -743,7 +756,7 @@ extern "C" {
 
 int b200ann_set_link_visited_bits(b200ann_handle_t h, int bits) {
   if (!h) return B200ANN_ERR_ARG;
-  if (bits < 5 || bits > 14) return set_err(h, B200ANN_ERR_ARG, "link_visited_bits must be in [5,14]");
+  if (bits != 0 && (bits < 5 || bits > 14)) return set_err(h, B200ANN_ERR_ARG, "link_visited_bits must be 0 (auto) or in [5,14]");
   h->link_visited_bits = bits;
   return 0;
 }

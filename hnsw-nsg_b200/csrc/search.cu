@@ -11,70 +11,98 @@ namespace {
 
 constexpr int WARPS = 4;
 
+// Persistent form (p.work != NULL): the grid is one resident wave and every WARP pulls its next query from an
+// atomic counter, so a warp whose query ends early starts another one instead of idling until the slowest warp of
+// its block (and the last partial wave) is done. Results do not depend on which warp ran which query.
 template <int TEAM, int NCH, bool IP, bool HNSW>
-__global__ void __launch_bounds__(WARPS * 32) beam_search_kernel(const SearchParams p) {
+__global__ void __launch_bounds__(WARPS * 32, (NCH <= 4 ? 6 : 1)) beam_search_kernel(const SearchParams p) {
   extern __shared__ uint32_t smem[];
   const int warp = threadIdx.x >> 5;
-  const uint32_t qi = blockIdx.x * WARPS + warp;
-  if (qi >= p.nq) return;
   Beam<TEAM, NCH, IP, HNSW> b(p, smem + (size_t)warp * smem_words(p.pool_cap, p.cand_cap, p.hbits));
   NoRec rec;
-  b.begin(p.q + (size_t)qi * p.qstride);
-  if (HNSW) {
-    b.descend_hnsw();
-  } else if (p.mode == 0) {
-    b.seed_nsg(p.qidx_base + qi, rec);
-  } else if (p.mode == 4) {
-    const uint32_t size = __ldg(p.cl_size + qi);
-    if (size == 0) {  // query not routed to any cluster in this pass
-      for (uint32_t i = b.lane; i < p.K; i += 32) {
-        p.ids[(size_t)qi * p.K + i] = INVALID_ID;
-        if (p.dists) p.dists[(size_t)qi * p.K + i] = INFINITY;
-      }
-      if (p.stats && b.lane == 0) { p.stats[2 * (size_t)qi] = 0; p.stats[2 * (size_t)qi + 1] = 0; }
-      return;
-    }
-    b.seed_nsg_local(p.qidx_base + qi, __ldg(p.entry + qi), __ldg(p.cl_base + qi), size);
-  } else {
-    uint32_t entry;
-    if (p.mode == 2) {  // hybrid: HNSW levels >= 1, external label of the node reached = NSG entry
-      float cd;
-      uint32_t cur = b.descend_upper(p.ep_hnsw, cd);
-      entry = p.labels ? (uint32_t)__ldg(p.labels + cur) : cur;
-      if (p.entry_out && b.lane == 0) p.entry_out[qi] = entry;
+  for (bool first = true;; first = false) {
+    uint32_t qi;
+    if (p.work) {
+      qi = 0;
+      if (b.lane == 0) qi = atomicAdd(p.work, 1u);
+      qi = __shfl_sync(0xffffffffu, qi, 0);
     } else {
-      entry = __ldg(p.entry + qi);
+      if (!first) break;
+      qi = blockIdx.x * WARPS + warp;
     }
-    if (entry >= p.n) entry = p.ep;  // the reference would index out of bounds; start from the navigating node
-    b.seed_from(entry, p.qidx_base + qi);
-  }
-  b.expand_all(rec);
-
-  // ---- results
-  for (uint32_t i = b.lane; i < p.K; i += 32) {
-    bool ok = i < b.np;
-    uint32_t id = ok ? (b.pool_i[i] & ~FLAG) : INVALID_ID;
-    float d = ok ? b.pool_d[i] : INFINITY;
+    if (qi >= p.nq) break;
+    b.begin(p.q + (size_t)qi * p.qstride);
     if (HNSW) {
-      p.labels_out[(size_t)qi * p.K + i] = ok ? (p.labels ? __ldg(p.labels + id) : (uint64_t)id) : ~(uint64_t)0;
+      b.descend_hnsw();
+    } else if (p.mode == 0) {
+      b.seed_nsg(p.qidx_base + qi, rec);
+    } else if (p.mode == 4) {
+      const uint32_t size = __ldg(p.cl_size + qi);
+      if (size == 0) {  // query not routed to any cluster in this pass
+        for (uint32_t i = b.lane; i < p.K; i += 32) {
+          p.ids[(size_t)qi * p.K + i] = INVALID_ID;
+          if (p.dists) p.dists[(size_t)qi * p.K + i] = INFINITY;
+        }
+        if (p.stats && b.lane == 0) { p.stats[2 * (size_t)qi] = 0; p.stats[2 * (size_t)qi + 1] = 0; }
+        continue;
+      }
+      b.seed_nsg_local(p.qidx_base + qi, __ldg(p.entry + qi), __ldg(p.cl_base + qi), size);
     } else {
-      p.ids[(size_t)qi * p.K + i] = id;
+      uint32_t entry;
+      if (p.mode == 2) {  // hybrid: HNSW levels >= 1, external label of the node reached = NSG entry
+        float cd;
+        uint32_t cur = b.descend_upper(p.ep_hnsw, cd);
+        entry = p.labels ? (uint32_t)__ldg(p.labels + cur) : cur;
+        if (p.entry_out && b.lane == 0) p.entry_out[qi] = entry;
+      } else {
+        entry = __ldg(p.entry + qi);
+      }
+      if (entry >= p.n) entry = p.ep;  // the reference would index out of bounds; start from the navigating node
+      b.seed_from(entry, p.qidx_base + qi);
     }
-    if (p.dists) p.dists[(size_t)qi * p.K + i] = d;
-  }
-  if (p.stats && b.lane == 0) {
-    p.stats[2 * (size_t)qi] = b.n_dist;
-    p.stats[2 * (size_t)qi + 1] = b.n_hops;
+    b.expand_all(rec);
+
+    // ---- results
+    for (uint32_t i = b.lane; i < p.K; i += 32) {
+      bool ok = i < b.np;
+      uint32_t id = ok ? (b.pool_i[i] & ~FLAG) : INVALID_ID;
+      float d = ok ? b.pool_d[i] : INFINITY;
+      if (HNSW) {
+        p.labels_out[(size_t)qi * p.K + i] = ok ? (p.labels ? __ldg(p.labels + id) : (uint64_t)id) : ~(uint64_t)0;
+      } else {
+        p.ids[(size_t)qi * p.K + i] = id;
+      }
+      if (p.dists) p.dists[(size_t)qi * p.K + i] = d;
+    }
+    if (p.stats && b.lane == 0) {
+      p.stats[2 * (size_t)qi] = b.n_dist;
+      p.stats[2 * (size_t)qi + 1] = b.n_hops;
+    }
+    __syncwarp();
   }
 }
 
 template <int TEAM, int NCH, bool IP, bool HNSW>
-int launch_t(b200ann_handle *h, const SearchParams &p) {
+int launch_t(b200ann_handle *h, const SearchParams &p0) {
+  SearchParams p = p0;
   size_t smem = (size_t)WARPS * smem_words(p.pool_cap, p.cand_cap, p.hbits) * 4;
   if (smem > 227 * 1024) return set_err(h, B200ANN_ERR_ARG, "search: L / degree / visited_bits need more than 227 KB shared memory per block");
   auto kern = beam_search_kernel<TEAM, NCH, IP, HNSW>;
   CU_CHECK(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  dim3 grid((p.nq + WARPS - 1) / WARPS), block(WARPS * 32);
+  size_t blocks = (p.nq + WARPS - 1) / WARPS;
+  p.work = nullptr;
+  if (h->persistent) {
+    int occ = 0;
+    CU_CHECK(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, WARPS * 32, smem));
+    size_t wave = (size_t)(occ > 0 ? occ : 1) * (size_t)h->sm_count;
+    if (blocks > wave) {  // more than one wave of blocks: pull queries from a queue instead
+      if (!h->work) CU_CHECK(h, cudaMalloc((void **)&h->work, sizeof(uint32_t)));
+      CU_CHECK(h, cudaMemsetAsync(h->work, 0, sizeof(uint32_t), h->stream));
+      p.work = h->work;
+      blocks = wave;
+    }
+  }
+  dim3 grid((unsigned)blocks), block(WARPS * 32);
   kern<<<grid, block, smem, h->stream>>>(p);
   h->launches++;
   CU_CHECK(h, cudaGetLastError());

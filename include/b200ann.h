@@ -212,7 +212,8 @@ int b200ann_set_async(b200ann_handle_t h, int on);
 
 /* tuning knob: log2 of the per-query visited-set size in shared memory (default 10). */
 int b200ann_set_visited_bits(b200ann_handle_t h, int bits);
-/* same for the per-node searches of b200ann_nsg_link (default 11) */
+/* same for the per-node searches of b200ann_nsg_link / b200ann_hnsw_build. 0 (default) = auto: 9 (dim <= 128) or 10 for
+ * NSG Link, which is bound by shared-memory occupancy, 11 for the HNSW build. Results do not depend on it. */
 int b200ann_set_link_visited_bits(b200ann_handle_t h, int bits);
 
 /* ---- NSG construction --------------------------------------------------------------------- */

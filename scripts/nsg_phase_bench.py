@@ -14,7 +14,7 @@ knn = ix.knn_graph(K)
 print("knn_graph %.1f ms" % h.last_kernel_ms, flush=True)
 ep = ix.nsg_init_ep(knn, L, seed=1); print("init_ep %.1f ms" % h.last_kernel_ms, flush=True)
 ep = ep[0] if isinstance(ep, tuple) else ep
-for bits in (12, 11, 10):
+for bits in (11, 10, 9, 8):
     h.set_link_visited_bits(bits)
     ci, cd, st = ix.nsg_link(knn, ep, L, R_, C_, seed=1, want_stats=True)
     print("link (visited bits %d) %.1f ms  beam evals %d prune evals %d" % (bits, h.last_kernel_ms, st[:, 0].astype(np.int64).sum(), st[:, 2].astype(np.int64).sum()), flush=True)

@@ -253,7 +253,7 @@ def _exact_knn(base, K):
 
 @pytest.mark.parametrize("n,dim,K,L,Rr,Cc,lbits", [(3000, 32, 24, 20, 12, 100, 12), (2000, 24, 10, 16, 8, 50, 12),
                                                     (1500, 128, 30, 30, 20, 200, 7), (1200, 960, 16, 20, 10, 60, 12),
-                                                    (2500, 100, 40, 40, 50, 500, 12)])
+                                                    (2500, 100, 40, 40, 50, 500, 0)])  # 0 = auto
 def test_nsg_build_phases_vs_oracle(B, n, dim, K, L, Rr, Cc, lbits):
     """every phase of the CUDA build, fed the previous phase's output, is bit-identical to the oracle
     run in the kernels' summation order: navigating node, centroid, cut rows and their distances

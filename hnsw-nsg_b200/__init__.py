@@ -64,6 +64,8 @@ _lib.b200ann_nsg_interinsert.argtypes = [_vp, _vp, _sz, _vp, _vp, C.POINTER(C.c_
 _lib.b200ann_merge_topk.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _vp, _vp]
 _lib.b200ann_set_knn_mode.argtypes = [_vp, C.c_int, C.c_int]
 _lib.b200ann_set_async.argtypes = [_vp, C.c_int]
+_lib.b200ann_cluster_search.argtypes = [_vp, _vp, _vp, _sz, _vp, _vp, _vp, _sz, _vp, _vp, _sz, _sz, _sz, _sz, _sz, _sz, _u32,
+                                        C.c_int, _vp, _vp, _vp]
 _lib.b200ann_knn_last_stats.argtypes = [_vp, _vp]
 _lib.b200ann_nsg_finish.argtypes = [_vp, _vp, _vp, _vp, _sz, _u32, _sz, _u32, _sz, C.POINTER(_u32)]
 
@@ -77,7 +79,7 @@ EXPORTS = [
     "b200ann_nsg_interinsert", "b200ann_nsg_finish", "b200ann_merge_topk", "b200ann_nsg_search_from",
     "b200ann_hybrid_search", "b200ann_set_knn_mode", "b200ann_knn_last_stats", "b200ann_nndescent",
     "b200ann_hnsw_build", "b200ann_index_hnsw_shape", "b200ann_index_get_hnsw", "b200ann_nsg_search_clustered",
-    "b200ann_set_async",
+    "b200ann_set_async", "b200ann_cluster_search",
 ]
 
 
@@ -116,6 +118,7 @@ class Handle:
         if rc != 0:
             raise B200AnnError(rc, "b200ann_create(device=%d) failed: no usable CUDA device (no CPU fallback)" % device)
         self._h = h
+        self.device = device
 
     def _check(self, rc):
         if rc != 0:

@@ -165,6 +165,32 @@ class ClusterIndex:
             return gi.astype(np.uint32), out_d, dict(launches=launches, clusters_searched=int(sum(np.isfinite(d[:, 0]).sum() for d in parts_d)))
         return gi.astype(np.uint32), out_d
 
+    def search_device(self, q, k, nprobe, search_K, L, seed=0, early_stop=True, return_stats=False):
+        """search() as ONE C-ABI call (b200ann_cluster_search): routing, the per-rank searches, the early-stop rule and
+        the merge all stay on the device, no host round trip between ranks. Same results as search()."""
+        B = _B()
+        q = np.ascontiguousarray(q, np.float32)
+        nq = len(q)
+        if getattr(self, "_dev", None) is None:                   # cluster tables + row map resident on the device
+            import torch
+            dev = "cuda:%d" % self.h.device
+            as_dev = lambda a: torch.from_numpy(np.ascontiguousarray(a, np.uint32).view(np.int32)).to(dev)
+            self._dev = tuple(as_dev(a) for a in (self.eps, self.cl_base, self.cl_size, self.perm))
+            torch.cuda.synchronize()
+        ep, base, size, perm = self._dev
+        ids = np.empty((nq, k), np.uint32)
+        d = np.empty((nq, k), np.float32)
+        searched = np.zeros(nq, np.uint32)
+        lib = B.lib()
+        self.h._check(lib.b200ann_cluster_search(self.h._h, self.ix._ix, self.rix._ix, self.m + 1, B._ptr(ep),
+                                                 B._ptr(base), B._ptr(size), len(self.cl_size), B._ptr(perm),
+                                                 B._ptr(q), nq, q.shape[1], k, nprobe, search_K, L, seed,
+                                                 1 if early_stop else 0, B._ptr(ids), B._ptr(d), B._ptr(searched)))
+        if return_stats:
+            return ids, d, dict(launches=3 * nprobe + 4, clusters_searched=int(searched.sum()))
+        return ids, d
+
     def close(self):
+        self._dev = None
         self.ix.close()
         self.rix.close()

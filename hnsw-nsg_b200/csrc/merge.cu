@@ -49,6 +49,16 @@ __global__ void merge_topk_kernel(const float *d, const uint32_t *ids, uint32_t 
 
 }  // namespace
 
+// device pointers only, asynchronous on h->stream
+int launch_merge_topk(b200ann_handle *h, const float *d, const uint32_t *ids, size_t parts, size_t nq, size_t k, size_t kout,
+                      float *out_d, uint32_t *out_i) {
+  merge_topk_kernel<<<(unsigned)((nq + 3) / 4), 128, 0, h->stream>>>(d, ids, (uint32_t)parts, (uint32_t)nq, (uint32_t)k,
+                                                                   (uint32_t)kout, out_d, out_i);
+  h->launches++;
+  CU_CHECK(h, cudaGetLastError());
+  return 0;
+}
+
 extern "C" int b200ann_merge_topk(b200ann_handle_t h, const float *d, const uint32_t *ids, size_t parts, size_t nq,
                                   size_t k, size_t kout, float *out_d, uint32_t *out_i) {
   if (!h) return B200ANN_ERR_ARG;

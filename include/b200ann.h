@@ -194,6 +194,24 @@ int b200ann_nsg_search_clustered(b200ann_handle_t h, b200ann_index_t ix, const f
                                  const uint32_t *base /*[h|d] [nq]*/, const uint32_t *size /*[h|d] [nq]*/,
                                  uint32_t *ids /*[h|d]*/, float *dists /*[h|d] or NULL*/, uint32_t *stats /*[h|d] or NULL*/);
 
+/* the whole per-query loop of the reference's cluster search driver (CNNS/tests/cluster_hnsw_nsg_search.cpp:138-270)
+ * for a batch, as one stream of launches with no host round trip: the nprobe nearest routing points by an exact scan
+ * of route_ix (:143-160; the reference asks a faiss IndexHNSWFlat) -> clusters ranked by how many of their routing
+ * points were hit, ties to the smaller cluster id (:162-187) -> b200ann_nsg_search_clustered in "every query's r-th
+ * cluster" for r = 0..nprobe-1 with the early-stop rule between ranks when early_stop != 0 (:249-263: a query stops
+ * after the first cluster whose best distance is not below the k-th smallest distance found so far) -> the k smallest
+ * of everything found (:217-247, :265-270), local rows mapped through perm (mapping_<id>, NULL = rows).
+ * ix: all clusters back to back + block-diagonal graph (see b200ann_nsg_search_clustered); route_ix: n_clusters *
+ * per_cluster rows, cluster c's routing points (centroid + m samples: per_cluster = m + 1) at [c*per_cluster, ...);
+ * cl_ep / cl_base / cl_size [n_clusters]: navigating node, first row, row count of every cluster.
+ * ids / dists [nq,k] (B200ANN_INVALID / +inf padded); searched [nq] or NULL: clusters searched per query. */
+int b200ann_cluster_search(b200ann_handle_t h, b200ann_index_t ix, b200ann_index_t route_ix, size_t per_cluster,
+                           const uint32_t *cl_ep /*[h|d]*/, const uint32_t *cl_base /*[h|d]*/,
+                           const uint32_t *cl_size /*[h|d]*/, size_t n_clusters, const uint32_t *perm /*[h|d] [n] or NULL*/,
+                           const float *q /*[h|d]*/, size_t nq, size_t qstride, size_t k, size_t nprobe, size_t search_K,
+                           size_t L, uint32_t seed, int early_stop, uint32_t *ids /*[h|d]*/, float *dists /*[h|d] or NULL*/,
+                           uint32_t *searched /*[h|d] or NULL*/);
+
 /* ---- shard-result merge (multi-GPU search) ---------------------------------------------------- */
 /* d/ids [parts, nq, k]: per-shard result lists, each row ascending by (distance,id), ids global,
  * unfilled slots +inf / B200ANN_INVALID. out_d (may be NULL) / out_i [nq, kout] = the kout smallest

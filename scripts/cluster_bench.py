@@ -23,4 +23,11 @@ for early in (True, False):
     ci.search(q, 10, nprobe, 10, 40, seed=1, early_stop=early)
     t0 = time.time(); gi, gd, st = ci.search(q, 10, nprobe, 10, 40, seed=1, early_stop=early, return_stats=True); t = time.time() - t0
     out["early_stop" if early else "all_probed"] = dict(recall_at_10=round(rec(gi), 4), qps=len(q) / t, seconds=t, **st)
+    # the same loop as one C-ABI call with no host round trip (b200ann_cluster_search)
+    ci.search_device(q, 10, nprobe, 10, 40, seed=1, early_stop=early)
+    t0 = time.time(); di, dd, dst = ci.search_device(q, 10, nprobe, 10, 40, seed=1, early_stop=early, return_stats=True); t = time.time() - t0
+    out[("early_stop" if early else "all_probed") + "_device"] = dict(recall_at_10=round(rec(di), 4), qps=len(q) / t, seconds=t,
+                                                                      device_ms=h.last_kernel_ms, same_ids=bool((di == gi).all()), **dst)
 print(json.dumps(out), flush=True)
+os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+open(os.path.join(ROOT, "gpurun_out", "cluster_pipeline.json"), "w").write(json.dumps(out) + "\n")

@@ -82,6 +82,19 @@ def test_cluster_search_vs_oracle(B, case, k, nprobe, search_K, L, early):
     assert (gd.view(np.uint32) == od.view(np.uint32)).all()
 
 
+@pytest.mark.parametrize("k,nprobe,search_K,L,early", [(10, 8, 10, 30, True), (5, 12, 20, 40, True), (10, 6, 10, 24, False),
+                                                       (7, 40, 8, 16, True), (10, 1, 10, 32, True)])
+def test_cluster_search_on_device_vs_oracle(B, case, k, nprobe, search_K, L, early):
+    # b200ann_cluster_search: the same loop as ONE call (routing, per-rank searches, early stop, merge on the device)
+    cl, ci, base, q, assign = case
+    gi, gd, st = ci.search_device(q, k, nprobe, search_K, L, seed=5, early_stop=early, return_stats=True)
+    oi, od = _oracle_search(B, ci, base, q, k, nprobe, search_K, L, 5, early)
+    assert (gi == oi).all()
+    assert (gd.view(np.uint32) == od.view(np.uint32)).all()
+    hi, hd, hst = ci.search(q, k, nprobe, search_K, L, seed=5, early_stop=early, return_stats=True)
+    assert (gi == hi).all() and st["clusters_searched"] == hst["clusters_searched"]
+
+
 def test_cluster_search_recall_and_structure(B, H, case):
     cl, ci, base, q, assign = case
     # every cluster is a contiguous block whose edges stay inside it

@@ -11,8 +11,8 @@
 // walk consider ~ef/selectivity elements before top_candidates fills); here it holds `ccap` entries, the farthest
 // entry is dropped when it is full, and the query is reported INEXACT as soon as the reference could have expanded
 // a dropped entry (oracle.c hnsw_base_pools_filtered states the rule) - a query that is not reported is the
-// reference's answer bit for bit. The launcher retries reported queries once with the largest ccap one warp per
-// block can hold. The visited set is exact (the reference's per-query tag array, visited_list_pool.h:10-31): one
+// reference's answer bit for bit. Reported queries are searched again (retry pass) with the heap in global memory
+// and room for all n elements, which cannot overflow. The visited set is exact (the reference's per-query tag array, visited_list_pool.h:10-31): one
 // bitmap of n bits per resident warp in global memory, cleared per query.
 #include "beam.cuh"
 
@@ -20,7 +20,7 @@ using namespace beam;
 
 namespace {
 
-constexpr int FW = 4;  // warps per block (1 in the retry pass: the whole block's shared memory for one candidate_set)
+constexpr int FW = 4;  // warps per block
 
 struct FilterParams {
   SearchParams s;
@@ -30,12 +30,14 @@ struct FilterParams {
   uint32_t vwords;         // multiple of 4
   uint32_t total_warps;
   uint32_t wpb;            // warps per block
+  float *gheap_d;          // retry pass: candidate_set heaps in global memory, [total_warps, ccap] (NULL: shared memory)
+  uint32_t *gheap_i;
   uint8_t *inexact;        // [nq]
   const uint8_t *only;     // NULL, or [nq]: search only the queries with only[q] != 0 (retry pass)
 };
 
 __host__ __device__ inline uint32_t fsmem_words(const FilterParams &p) {
-  return smem_words(p.s.pool_cap, p.s.cand_cap, 0) + 2 * p.ccap;
+  return smem_words(p.s.pool_cap, p.s.cand_cap, 0) + (p.gheap_d ? 0u : 2 * p.ccap);
 }
 
 // number of entries of a[lo, lo+n) ordered before (d,id)
@@ -126,6 +128,10 @@ __global__ void __launch_bounds__(FW * 32) hnsw_filtered_kernel(const FilterPara
   Beam<TEAM, NCH, IP, true> b(p, base);
   float *cd = reinterpret_cast<float *>(base + smem_words(p.pool_cap, p.cand_cap, 0));
   uint32_t *ci = base + smem_words(p.pool_cap, p.cand_cap, 0) + fp.ccap;
+  if (fp.gheap_d) {  // retry pass: the heap lives in global memory (L2), sized so that it cannot overflow
+    cd = fp.gheap_d + (size_t)gw * fp.ccap;
+    ci = fp.gheap_i + (size_t)gw * fp.ccap;
+  }
   uint32_t *vis = fp.visited + (size_t)gw * fp.vwords;
   const int lane = b.lane;
   const uint32_t ef = p.L;
@@ -267,9 +273,10 @@ int launch_fdim(b200ann_handle *h, FilterParams &fp) {
 
 }  // namespace
 
-// big = false: 4 warps per block, candidate_set of min(ccap ? ccap : 2048, what fits) entries; big = true (retry pass):
-// one warp per block with the largest candidate_set 227 KB hold. only = NULL or a device mask of the queries to
-// search (may alias inexact). All pointers are device pointers.
+// big = false: candidate_set heaps of min(ccap ? ccap : 2048, what fits) entries in shared memory. big = true (retry
+// pass): the heaps move to global memory with up to n entries each (n entries cannot overflow: a query then is always
+// exact), as many resident warps as 16 GiB of heaps (a quarter of the free memory at most) and 2 GiB of visited bitmaps allow. only = NULL or a device mask of
+// the queries to search (may alias inexact). All pointers are device pointers.
 int launch_hnsw_search_filtered(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
                                 size_t k, size_t ef, const uint32_t *allow_bits, size_t ccap, bool big,
                                 const uint8_t *only, uint64_t *labels, float *dists, uint32_t *stats, uint8_t *inexact,
@@ -288,27 +295,44 @@ int launch_hnsw_search_filtered(b200ann_handle *h, const b200ann_index *ix, cons
   p.pool_cap = round_up((uint32_t)L + 1, 32);
   p.labels_out = labels; p.dists = dists; p.stats = stats;
   fp.allow = allow_bits; fp.inexact = inexact; fp.only = only;
-  fp.wpb = big ? 1 : FW;
+  fp.wpb = FW;
+  fp.vwords = round_up((uint32_t)((ix->n + 31) / 32), 4);
   const size_t fixed = smem_words(p.pool_cap, p.cand_cap, 0);
   const size_t budget = 227 * 1024 / 4 / fp.wpb;
   if (fixed + 2 * 64 > budget) return set_err(h, B200ANN_ERR_ARG, "hnsw_search_filtered: ef / degree need more than 227 KB shared memory per block");
-  size_t most = (budget - fixed) / 2 / 32 * 32;
-  if (ccap == 0) ccap = 2048;
-  if (big || ccap > most) ccap = most;
-  fp.ccap = (uint32_t)ccap;
-  if (ccap_used) *ccap_used = ccap;
-  // resident warps: blocks per SM by shared memory, capped so the visited bitmaps stay below 2 GiB
-  size_t smem_block = (size_t)fp.wpb * fsmem_words(fp) * 4;
-  size_t per_sm = 227 * 1024 / smem_block;
-  if (per_sm < 1) per_sm = 1;
-  if (per_sm > 8) per_sm = 8;
-  size_t warps = (size_t)h->sm_count * per_sm * fp.wpb;
-  fp.vwords = round_up((uint32_t)((ix->n + 31) / 32), 4);
+  size_t warps;
+  DevBuf<float> gd; DevBuf<uint32_t> gi;
+  if (!big) {
+    size_t most = (budget - fixed) / 2 / 32 * 32;
+    if (ccap == 0) ccap = 2048;
+    if (ccap > most) ccap = most;
+    fp.ccap = (uint32_t)ccap;
+    size_t per_sm = 227 * 1024 / ((size_t)fp.wpb * fsmem_words(fp) * 4);
+    if (per_sm < 1) per_sm = 1;
+    if (per_sm > 8) per_sm = 8;
+    warps = (size_t)h->sm_count * per_sm * fp.wpb;
+  } else {
+    ccap = ix->n;  // every element can be queued at most once (the visited set is exact)
+    warps = (size_t)h->sm_count * 6 * fp.wpb;
+    size_t free_b = 0, total_b = 0;
+    size_t heap_budget = (size_t)16 << 30;  // up to 16 GiB of heaps, at most a quarter of what is free
+    if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess && free_b / 4 < heap_budget) heap_budget = free_b / 4;
+    size_t by_heap = heap_budget / (ccap * 8);
+    if (by_heap < 1) by_heap = 1;
+    if (warps > by_heap) warps = by_heap;
+  }
   size_t by_mem = ((size_t)2 << 30) / ((size_t)fp.vwords * 4);
   if (by_mem < 1) by_mem = 1;
   if (warps > by_mem) warps = by_mem;
   if (warps > nq) warps = nq;
   fp.total_warps = (uint32_t)warps;
+  fp.ccap = (uint32_t)ccap;
+  if (ccap_used) *ccap_used = ccap;
+  if (big) {
+    CU_CHECK(h, gd.alloc(warps * ccap, h->stream));
+    CU_CHECK(h, gi.alloc(warps * ccap, h->stream));
+    fp.gheap_d = gd.p; fp.gheap_i = gi.p;
+  }
   DevBuf<uint32_t> vis;
   CU_CHECK(h, vis.alloc((size_t)fp.total_warps * fp.vwords, h->stream));
   fp.visited = vis.p;

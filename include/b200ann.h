@@ -154,10 +154,11 @@ int b200ann_hnsw_search(b200ann_handle_t h, b200ann_index_t ix, const float *q /
  * internal ids (= rows of the index): bit (i & 31) of allow[i >> 5] set <=> element i is not deleted and its label
  * passes the filter; allow holds ceil(n/32) words. Elements that are filtered out are still walked through, exactly
  * like the reference; rows with fewer than k allowed results are padded with ~0 / +inf (no error: the reference
- * returns short results too). The reference's candidate_set is unbounded; here it is bounded per query (shared
- * memory), overflowing queries are retried once with the largest bound, and a query whose answer could still differ
- * from the reference's is reported: inexact [nq] (host, 0 / 1), or, when inexact is NULL, the call fails with
- * B200ANN_ERR_CAPACITY. A query reported 0 is the reference's answer bit for bit. */
+ * returns short results too). The reference's candidate_set is unbounded; the first pass bounds it per query
+ * (shared memory) and PROVES per query whether the bound mattered; queries for which it could have are searched again
+ * with global-memory heaps that hold all n elements and cannot overflow, so every answer is the reference's bit for
+ * bit. inexact [nq] (host, optional) reports queries that stayed unproven (all 0 today; B200ANN_ERR_CAPACITY when
+ * inexact is NULL and one did). */
 int b200ann_hnsw_search_filtered(b200ann_handle_t h, b200ann_index_t ix, const float *q /*[h|d]*/, size_t nq,
                                  size_t qstride, size_t k, size_t ef, const uint32_t *allow /*[h|d]*/,
                                  uint64_t *labels /*[h|d]*/, float *dists /*[h|d]*/, uint32_t *stats /*[h|d]*/,

@@ -24,15 +24,6 @@ def H(B):
     return B.Handle(0)
 
 
-def retry_ccap(ef, k, maxM0, maxM):
-    """launch_hnsw_search_filtered's largest candidate_set: one warp per block, 227 KB"""
-    L = max(ef, k)
-    pool_cap = (L + 1 + 31) // 32 * 32
-    cand_cap = (max(maxM0, maxM) + 31) // 32 * 32
-    fixed = 2 * pool_cap + 2 * cand_cap + 1
-    return (227 * 1024 // 4 - fixed) // 2 // 32 * 32
-
-
 @pytest.fixture(scope="module")
 def case(B, H):
     n, dim, M = 20000, 32, 12
@@ -60,10 +51,10 @@ def test_filtered_search_vs_oracle(B, case, keep, ef, k):
     assert np.array_equal(d[ok], rd[ok])
     got = lab[lab != NOLAB].astype(np.int64)
     assert allow[got].all()                                       # labels == rows here: nothing filtered out comes back
-    # kernel form incl. the overflow report: pass 0 with 2048 entries, reported queries again with the largest bound
+    # kernel form incl. the overflow report: pass 0 with 2048 entries, reported queries again with room for all n
     l0, d0, b0, s0 = R.orc_hnsw_search_filtered(base, G, allow, q, k, ef, R.L2_GPU, variant=1, ccap=2048, want_stats=True)
-    l1, d1, b1, s1 = R.orc_hnsw_search_filtered(base, G, allow, q, k, ef, R.L2_GPU, variant=1,
-                                                ccap=retry_ccap(ef, k, G["maxM0"], G["maxM"]), want_stats=True)
+    l1, d1, b1, s1 = R.orc_hnsw_search_filtered(base, G, allow, q, k, ef, R.L2_GPU, variant=1, ccap=n, want_stats=True)
+    assert not b1.any()                                           # n entries cannot overflow
     again = b0 != 0
     el = np.where(again[:, None], l1, l0)
     ed = np.where(again[:, None], d1, d0)
@@ -71,8 +62,7 @@ def test_filtered_search_vs_oracle(B, case, keep, ef, k):
     assert (lab == el).all() and np.array_equal(d, ed)
     assert (bad == np.where(again, b1, 0)).all()
     assert (st.astype(np.uint64) == es).all()
-    if keep >= 0.1:
-        assert ok.all()
+    assert ok.all()                                               # after the retry pass every query is exact
     if keep == 0.003:
         assert again.any()                                        # the retry pass really ran
     if keep == 0.0:

@@ -6,14 +6,14 @@
 // (allowed elements only, <= ef) as an ascending (distance,id) array, candidate_set (every considered element) as a
 // binary min-heap on (distance,id) maintained by lane 0 (O(log) per push / pop; a selective filter makes it hold
 // tens of thousands of entries, where shifting a sorted array costs 50x more). Ties are broken by id in both, so
-// the pop order and the eviction order are those of oracle.c's sorted arrays. candidate_set is unbounded in the
-// reference (a selective filter makes the
-// walk consider ~ef/selectivity elements before top_candidates fills); here it holds `ccap` entries, the farthest
-// entry is dropped when it is full, and the query is reported INEXACT as soon as the reference could have expanded
-// a dropped entry (oracle.c hnsw_base_pools_filtered states the rule) - a query that is not reported is the
-// reference's answer bit for bit. Reported queries are searched again (retry pass) with the heap in global memory
-// and room for all n elements, which cannot overflow. The visited set is exact (the reference's per-query tag array, visited_list_pool.h:10-31): one
-// bitmap of n bits per resident warp in global memory, cleared per query.
+// the pop order and the eviction order are those of oracle.c's sorted arrays.
+// candidate_set is unbounded in the reference (a selective filter makes the walk consider ~ef/selectivity elements
+// before top_candidates fills). The first pass holds `ccap` entries per query: the farthest entry is dropped when the
+// heap is full, and the query is reported INEXACT as soon as the reference could have expanded a dropped entry
+// (oracle.c hnsw_base_pools_filtered states the rule) - a query that is not reported is the reference's answer bit
+// for bit. Reported queries are searched again (retry pass) with the heap in global memory and room for all n
+// elements, which cannot overflow. The visited set is exact (the reference's per-query tag array,
+// visited_list_pool.h:10-31): one bitmap of n bits per resident warp in global memory, cleared per query.
 #include "beam.cuh"
 
 using namespace beam;

@@ -45,6 +45,7 @@ _lib.b200ann_index_get_graph.argtypes = [_vp, _vp, _sz, C.POINTER(C.c_uint32), C
 _lib.b200ann_index_set_hnsw.argtypes = [_vp, _vp, _sz, _vp, _vp, _vp, _sz, _sz, _vp, C.c_uint32, C.c_int]
 _lib.b200ann_bf_knn.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _vp, _vp]
 _lib.b200ann_knn_graph.argtypes = [_vp, _vp, _sz, _vp]
+_lib.b200ann_bf_knn_u8.argtypes = [_vp, _vp, _sz, _sz, _sz, _vp, _sz, _sz, _sz, _vp, _vp]
 _lib.b200ann_hnsw_build.argtypes = [_vp, _vp, _sz, _sz, C.c_uint32, _sz, _sz, _vp, _vp]
 _lib.b200ann_index_hnsw_shape.argtypes = [_vp, _vp]
 _lib.b200ann_index_get_hnsw.argtypes = [_vp, _vp, _vp, _vp, _vp, _vp]
@@ -79,7 +80,7 @@ EXPORTS = [
     "b200ann_nsg_interinsert", "b200ann_nsg_finish", "b200ann_merge_topk", "b200ann_nsg_search_from",
     "b200ann_hybrid_search", "b200ann_set_knn_mode", "b200ann_knn_last_stats", "b200ann_nndescent",
     "b200ann_hnsw_build", "b200ann_index_hnsw_shape", "b200ann_index_get_hnsw", "b200ann_nsg_search_clustered",
-    "b200ann_set_async", "b200ann_cluster_search",
+    "b200ann_set_async", "b200ann_cluster_search", "b200ann_bf_knn_u8",
 ]
 
 
@@ -173,6 +174,22 @@ class Handle:
 
     def merge_topk_raw(self, d, ids, parts, nq, k, kout, out_d, out_i):
         self._check(_lib.b200ann_merge_topk(self._h, _ptr(d), _ptr(ids), parts, nq, k, kout, _ptr(out_d), _ptr(out_i)))
+
+    def bf_knn_u8(self, base, q, k):
+        """exact kNN over u8 rows with int squared-L2 (hnswlib L2SpaceI + BruteforceSearch<int>);
+        base [n,dim], q [nq,dim] uint8 numpy -> (ids u32 [nq,k], dists i32 [nq,k])"""
+        base = np.ascontiguousarray(base, np.uint8)
+        q = np.ascontiguousarray(q, np.uint8)
+        ids = np.empty((q.shape[0], k), np.uint32)
+        d = np.empty((q.shape[0], k), np.int32)
+        self._check(_lib.b200ann_bf_knn_u8(self._h, _ptr(base), base.shape[0], base.shape[1], base.shape[1], _ptr(q),
+                                           q.shape[0], q.shape[1], k, _ptr(ids), _ptr(d)))
+        return ids, d
+
+    def bf_knn_u8_raw(self, base, n, dim, bstride, q, nq, qstride, k, ids, dists):
+        """device (torch tensor / raw pointer) or host buffers, strides in bytes"""
+        self._check(_lib.b200ann_bf_knn_u8(self._h, _ptr(base), n, dim, bstride, _ptr(q), nq, qstride, k, _ptr(ids),
+                                           _ptr(dists)))
 
     def set_link_visited_bits(self, bits):
         self._check(_lib.b200ann_set_link_visited_bits(self._h, bits))

@@ -330,6 +330,30 @@ int b200ann_bf_knn(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_
   return 0;
 }
 
+int b200ann_bf_knn_u8(b200ann_handle_t h, const uint8_t *base, size_t n, size_t dim, size_t bstride, const uint8_t *q,
+                      size_t nq, size_t qstride, size_t k, uint32_t *ids, int32_t *dists) {
+  if (!h) return B200ANN_ERR_ARG;
+  if (!base || !q || !ids || k == 0 || dim == 0 || bstride < dim || qstride < dim)
+    return set_err(h, B200ANN_ERR_ARG, "bf_knn_u8: bad base/q/ids/k/dim/stride");
+  if (dim > 32768) return set_err(h, B200ANN_ERR_ARG, "bf_knn_u8: dim > 32768 (the reference's int distance can overflow)");
+  if (n >= 0xFFFFFFFFull || nq >= 0xFFFFFFFFull) return set_err(h, B200ANN_ERR_ARG, "bf_knn_u8: n / nq must fit 32 bits");
+  if (nq == 0) return 0;
+  CU_CHECK(h, cudaSetDevice(h->device));
+  InArg<uint8_t> bin, qin; OutArg<uint32_t> oi; OutArg<int32_t> od;
+  CU_CHECK(h, bin.stage(base, n ? (n - 1) * bstride + dim : 0, h->stream));
+  CU_CHECK(h, qin.stage(q, (nq - 1) * qstride + dim, h->stream));
+  CU_CHECK(h, oi.stage(ids, nq * k, h->stream));
+  CU_CHECK(h, od.stage(dists, nq * k, h->stream));
+  CallTimer t(h);
+  int rc = launch_bf_knn_u8(h, bin.d, n, dim, bstride, qin.d, nq, qstride, k, oi.d, od.d);
+  t.stop();
+  if (rc) return rc;
+  CU_CHECK(h, oi.finish(h->stream));
+  CU_CHECK(h, od.finish(h->stream));
+  CU_CHECK(h, t.sync());
+  return 0;
+}
+
 int b200ann_knn_graph(b200ann_handle_t h, b200ann_index_t ix, size_t K, uint32_t *knn) {
   if (!h || !ix) return B200ANN_ERR_ARG;
   if (!knn || K == 0 || K >= ix->n) return set_err(h, B200ANN_ERR_ARG, "knn_graph: need 0 < K < n");

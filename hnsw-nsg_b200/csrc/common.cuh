@@ -153,6 +153,9 @@ int launch_merge_topk(b200ann_handle *h, const float *d, const uint32_t *ids, si
                       float *out_d, uint32_t *out_i);
 int launch_bf_knn(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
                   size_t k, bool exclude_self, uint32_t *ids, float *dists, const uint32_t *self_ids = nullptr);
+// u8 rows, integer squared L2 (bf_knn_u8.cu); device pointers only
+int launch_bf_knn_u8(b200ann_handle *h, const uint8_t *base, size_t n, size_t dim, size_t bstride, const uint8_t *q,
+                     size_t nq, size_t qstride, size_t k, uint32_t *ids, int32_t *dists);
 // tensor-core path (knn_tc.cu); same contract. knn_dispatch picks the path from h->knn_mode.
 int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t nq, size_t qstride, size_t k,
                   bool exclude_self, uint32_t *ids, float *dists);

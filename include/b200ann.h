@@ -101,6 +101,14 @@ int b200ann_index_get_hnsw(b200ann_index_t ix, uint32_t *links0 /*[h|d]*/, int32
  * B200ANN_INVALID / +inf. */
 int b200ann_bf_knn(b200ann_handle_t h, b200ann_index_t ix, const float *q /*[h|d]*/, size_t nq, size_t qstride,
                    size_t k, uint32_t *ids /*[h|d]*/, float *dists /*[h|d] or NULL*/);
+/* replaces hnswlib::BruteforceSearch<int>::searchKnn (bruteforce.h:106-135) over hnswlib::L2SpaceI
+ * (space_l2.h:255-323, L2SqrI4x / L2SqrI: int sum of (a-b)^2 over unsigned bytes), batched. base [n] rows of dim
+ * bytes at bstride bytes, q [nq] rows at qstride bytes (host or device; copied per call when on the host).
+ * ids/dists [nq,k] ascending by (distance,id); integer arithmetic, so both are bit-exact. Unfilled slots (k > n):
+ * B200ANN_INVALID / INT32_MAX. dim <= 32768 (beyond it the reference's int accumulator can overflow). */
+int b200ann_bf_knn_u8(b200ann_handle_t h, const uint8_t *base /*[h|d]*/, size_t n, size_t dim, size_t bstride,
+                      const uint8_t *q /*[h|d]*/, size_t nq, size_t qstride, size_t k, uint32_t *ids /*[h|d]*/,
+                      int32_t *dists /*[h|d] or NULL*/);
 /* exact kNN graph of the index's own rows, self excluded: knn [n,K] ascending (distance,id).
  * The exact counterpart of IndexGraph::Build's output (index_graph.cpp:275-292). */
 int b200ann_knn_graph(b200ann_handle_t h, b200ann_index_t ix, size_t K, uint32_t *knn /*[h|d]*/);

@@ -305,6 +305,45 @@ EXPORT int orc_bf_knn(const float *base, size_t n, size_t dim, size_t stride, co
   return 0;
 }
 
+/* hnswlib::L2SqrI (space_l2.h:281-292; L2SqrI4x :255-279 is the same sum unrolled by 4): int accumulation of
+ * (a-b)^2 over unsigned bytes. Integer arithmetic: no rounding, no order dependence. */
+static int orc_l2sqr_u8(const uint8_t *a, const uint8_t *b, size_t dim) {
+  int res = 0;
+  for (size_t i = 0; i < dim; i++) { int d = (int)a[i] - (int)b[i]; res += d * d; }
+  return res;
+}
+
+/* hnswlib::BruteforceSearch<int>::searchKnn (bruteforce.h:106-135) over L2SpaceI, every query of a batch:
+ * the k smallest under (distance, id) (the reference's `dist <= lastdist` admission + pair max-heap eviction
+ * keeps the smaller label among equals), ascending. Unfilled slots: ORC_INVALID / INT32_MAX. */
+EXPORT int orc_bf_knn_u8(const uint8_t *base, size_t n, size_t dim, size_t stride, const uint8_t *q, size_t nq,
+                         size_t qstride, size_t k, uint32_t *ids, int32_t *dists) {
+  if (k == 0) return 0;
+#pragma omp parallel
+  {
+    int32_t *hd = (int32_t *)malloc(sizeof(int32_t) * k);
+    uint32_t *hi = (uint32_t *)malloc(sizeof(uint32_t) * k);
+#pragma omp for schedule(dynamic, 4)
+    for (long qi = 0; qi < (long)nq; qi++) {
+      const uint8_t *qv = q + (size_t)qi * qstride;
+      size_t m = 0;  /* sorted ascending list of the best m <= k, insertion from the back */
+      for (size_t i = 0; i < n; i++) {
+        int32_t d = orc_l2sqr_u8(qv, base + i * stride, dim);
+        if (m == k && !(d < hd[k - 1])) continue;  /* ids arrive ascending: an equal distance never displaces */
+        size_t j = m < k ? m++ : k - 1;
+        while (j > 0 && hd[j - 1] > d) { hd[j] = hd[j - 1]; hi[j] = hi[j - 1]; j--; }
+        hd[j] = d; hi[j] = (uint32_t)i;
+      }
+      for (size_t j = 0; j < k; j++) {
+        ids[(size_t)qi * k + j] = j < m ? hi[j] : ORC_INVALID;
+        dists[(size_t)qi * k + j] = j < m ? hd[j] : INT32_MAX;
+      }
+    }
+    free(hd); free(hi);
+  }
+  return 0;
+}
+
 /* ------------------------------------------------------------------ sorted pool (efanna Neighbor) */
 /* efanna2e::Neighbor (CNNS/include/nsg/neighbor.h:18-30) */
 typedef struct { uint32_t id; float distance; int flag; } orc_nb;

@@ -54,6 +54,28 @@ int ref_bf_knn(int metric, const float *base, size_t n, size_t dim, const float 
   return 0;
 }
 
+// BruteforceSearch<int> over L2SpaceI (space_l2.h:294-323): u8 rows, int distances.
+int ref_bf_knn_u8(const unsigned char *base, size_t n, size_t dim, const unsigned char *q, size_t nq, size_t k,
+                  unsigned long long *labels, int *dists, int threads) {
+  L2SpaceI space(dim);
+  BruteforceSearch<int> bf(&space, n);
+  for (size_t i = 0; i < n; i++) bf.addPoint(base + i * dim, i);
+  if (threads <= 0) threads = omp_get_max_threads();
+#pragma omp parallel for num_threads(threads) schedule(dynamic, 8)
+  for (long i = 0; i < (long)nq; i++) {
+    auto r = bf.searchKnn(q + i * dim, k);
+    size_t m = r.size();
+    for (size_t j = m; j < k; j++) { labels[i * k + j] = (unsigned long long)-1; dists[i * k + j] = -1; }
+    while (!r.empty()) {
+      --m;
+      labels[i * k + m] = r.top().second;
+      dists[i * k + m] = r.top().first;
+      r.pop();
+    }
+  }
+  return 0;
+}
+
 void *ref_hnsw_new(int metric, size_t dim, size_t max_elements, size_t M, size_t efc, size_t seed) {
   RefHnsw *h = new RefHnsw;
   h->dim = dim;

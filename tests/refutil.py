@@ -45,6 +45,8 @@ def oracle():
         lib.orc_seed_hash.argtypes = [C.c_uint32] * 3
         lib.orc_bf_knn.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, f32p, C.c_size_t, C.c_size_t,
                                    C.c_size_t, C.c_int, u32p, f32p]
+        lib.orc_bf_knn_u8.argtypes = [u8p, C.c_size_t, C.c_size_t, C.c_size_t, u8p, C.c_size_t, C.c_size_t,
+                                      C.c_size_t, u32p, i32p]
         lib.orc_insert_into_pool.argtypes = [u32p, f32p, i32p, C.c_uint, C.c_uint32, C.c_float]
         lib.orc_nsg_search.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, u32p, C.c_uint, C.c_uint32,
                                        f32p, C.c_size_t, C.c_size_t, C.c_uint, C.c_uint, C.c_int, C.c_int,
@@ -105,6 +107,15 @@ def orc_bf_knn(base, q, k, mode):
     ids = np.empty((nq, k), np.uint32)
     d = np.empty((nq, k), np.float32)
     oracle().orc_bf_knn(base, n, dim, base.shape[1], q, nq, q.shape[1], k, mode, ids, d)
+    return ids, d
+
+
+def orc_bf_knn_u8(base, q, k):
+    n, dim = base.shape
+    nq = q.shape[0]
+    ids = np.empty((nq, k), np.uint32)
+    d = np.empty((nq, k), np.int32)
+    oracle().orc_bf_knn_u8(base, n, dim, base.shape[1], q, nq, q.shape[1], k, ids, d)
     return ids, d
 
 
@@ -455,6 +466,7 @@ def reflib(name):
         lib.ref_dist.argtypes = [C.c_int, f32p, f32p, C.c_size_t]
         lib.ref_bf_knn.argtypes = [C.c_int, f32p, C.c_size_t, C.c_size_t, f32p, C.c_size_t, C.c_size_t, u64p,
                                    f32p, C.c_int]
+        lib.ref_bf_knn_u8.argtypes = [u8p, C.c_size_t, C.c_size_t, u8p, C.c_size_t, C.c_size_t, u64p, i32p, C.c_int]
         lib.ref_hnsw_new.restype = C.c_void_p
         lib.ref_hnsw_new.argtypes = [C.c_int] + [C.c_size_t] * 5
         lib.ref_hnsw_load.restype = C.c_void_p
@@ -519,6 +531,14 @@ def ref_bf_knn(base, q, k, metric, lib="hnsw", threads=0):
     lab = np.empty((q.shape[0], k), np.uint64)
     d = np.empty((q.shape[0], k), np.float32)
     reflib(lib).ref_bf_knn(metric, base, n, dim, q, q.shape[0], k, lab, d, threads)
+    return lab, d
+
+
+def ref_bf_knn_u8(base, q, k, lib="hnsw", threads=0):
+    n, dim = base.shape
+    lab = np.empty((q.shape[0], k), np.uint64)
+    d = np.empty((q.shape[0], k), np.int32)
+    reflib(lib).ref_bf_knn_u8(base, n, dim, q, q.shape[0], k, lab, d, threads)
     return lab, d
 
 

@@ -80,7 +80,7 @@ EXPORTS = [
     "b200ann_nsg_interinsert", "b200ann_nsg_finish", "b200ann_merge_topk", "b200ann_nsg_search_from",
     "b200ann_hybrid_search", "b200ann_set_knn_mode", "b200ann_knn_last_stats", "b200ann_nndescent",
     "b200ann_hnsw_build", "b200ann_index_hnsw_shape", "b200ann_index_get_hnsw", "b200ann_nsg_search_clustered",
-    "b200ann_set_async", "b200ann_cluster_search", "b200ann_bf_knn_u8",
+    "b200ann_set_async", "b200ann_cluster_search", "b200ann_bf_knn_u8", "b200ann_upload_u8", "b200ann_free_device",
 ]
 
 

@@ -354,6 +354,22 @@ int b200ann_bf_knn_u8(b200ann_handle_t h, const uint8_t *base, size_t n, size_t 
   return 0;
 }
 
+int b200ann_upload_u8(b200ann_handle_t h, const uint8_t *src, size_t bytes, uint8_t **out_dev) {
+  if (!h || !out_dev || (!src && bytes)) return B200ANN_ERR_ARG;
+  CU_CHECK(h, cudaSetDevice(h->device));
+  uint8_t *d = nullptr;
+  CU_CHECK(h, cudaMalloc((void **)&d, bytes ? bytes : 1));
+  cudaError_t e = cudaMemcpyAsync(d, src, bytes, cudaMemcpyHostToDevice, h->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+  if (e != cudaSuccess) { cudaFree(d); CU_CHECK(h, e); }
+  *out_dev = d;
+  return 0;
+}
+
+int b200ann_free_device(void *dev) {
+  return cudaFree(dev) == cudaSuccess ? 0 : B200ANN_ERR_CUDA;
+}
+
 int b200ann_knn_graph(b200ann_handle_t h, b200ann_index_t ix, size_t K, uint32_t *knn) {
   if (!h || !ix) return B200ANN_ERR_ARG;
   if (!knn || K == 0 || K >= ix->n) return set_err(h, B200ANN_ERR_ARG, "knn_graph: need 0 < K < n");

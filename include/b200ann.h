@@ -109,6 +109,10 @@ int b200ann_bf_knn(b200ann_handle_t h, b200ann_index_t ix, const float *q /*[h|d
 int b200ann_bf_knn_u8(b200ann_handle_t h, const uint8_t *base /*[h|d]*/, size_t n, size_t dim, size_t bstride,
                       const uint8_t *q /*[h|d]*/, size_t nq, size_t qstride, size_t k, uint32_t *ids /*[h|d]*/,
                       int32_t *dists /*[h|d] or NULL*/);
+/* a device-resident copy of host bytes for b200ann_bf_knn_u8's `base` (so repeated searches do not re-upload the rows);
+ * release with b200ann_free_device. */
+int b200ann_upload_u8(b200ann_handle_t h, const uint8_t *src /*[h]*/, size_t bytes, uint8_t **out_dev);
+int b200ann_free_device(void *dev);
 /* exact kNN graph of the index's own rows, self excluded: knn [n,K] ascending (distance,id).
  * The exact counterpart of IndexGraph::Build's output (index_graph.cpp:275-292). */
 int b200ann_knn_graph(b200ann_handle_t h, b200ann_index_t ix, size_t K, uint32_t *knn /*[h|d]*/);

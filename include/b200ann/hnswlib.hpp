@@ -95,6 +95,27 @@ class InnerProductSpace : public SpaceInterface<float> {
 };
 
 namespace detail {
+inline int l2i_host(const void *a, const void *b, const void *dimp) {
+  const unsigned char *x = (const unsigned char *)a, *y = (const unsigned char *)b;
+  size_t d = *(const size_t *)dimp;
+  int s = 0;
+  for (size_t i = 0; i < d; i++) { int t = (int)x[i] - (int)y[i]; s += t * t; }
+  return s;
+}
+}  // namespace detail
+
+// hnswlib::L2SpaceI (space_l2.h:294-323): unsigned-byte vectors, int squared L2. Served on the GPU by
+// BruteforceSearch<int> (b200ann_bf_knn_u8); HierarchicalNSW<int> is not built.
+class L2SpaceI : public SpaceInterface<int> {
+  size_t data_size_, dim_;
+ public:
+  explicit L2SpaceI(size_t dim) : data_size_(dim * sizeof(unsigned char)), dim_(dim) {}
+  size_t get_data_size() override { return data_size_; }
+  DISTFUNC<int> get_dist_func() override { return detail::l2i_host; }
+  void *get_dist_func_param() override { return &dim_; }
+};
+
+namespace detail {
 // metric + dim of a Space; anything but the two known spaces is rejected
 inline void space_info(SpaceInterface<float> *s, int &metric, size_t &dim) {
   if (dynamic_cast<L2Space *>(s)) metric = B200ANN_L2;
@@ -237,6 +258,128 @@ class BruteforceSearch : public AlgorithmInterface<dist_t> {
   std::vector<labeltype> labels_;
   std::unordered_map<labeltype, size_t> pos_;
   mutable b200ann_index_t ix_ = nullptr;
+  mutable bool dirty_ = true;
+  mutable std::mutex mu_;
+};
+
+// BruteforceSearch<int> over L2SpaceI: rows of dim unsigned bytes, int distances; same contract and file format
+// (bruteforce.h:138-171 with size_per_element = dim + sizeof(labeltype)) as the float class above. Distances and
+// labels are bit-identical to the reference's (integer arithmetic).
+template <>
+class BruteforceSearch<int> : public AlgorithmInterface<int> {
+ public:
+  size_t maxelements_, cur_element_count, dim_;
+
+  BruteforceSearch(SpaceInterface<int> *s, size_t maxElements, int device = 0) : maxelements_(maxElements), cur_element_count(0), gpu_(device) {
+    set_space(s);
+    data_.resize(maxElements * dim_);
+    labels_.resize(maxElements);
+  }
+  ~BruteforceSearch() { if (dev_) b200ann_free_device(dev_); }
+
+  void addPoint(const void *datapoint, labeltype label, bool = false) override {
+    std::unique_lock<std::mutex> lock(mu_);
+    size_t idx;
+    auto it = pos_.find(label);
+    if (it != pos_.end()) idx = it->second;
+    else {
+      if (cur_element_count >= maxelements_) throw std::runtime_error("The number of elements exceeds the specified limit\n");  // bruteforce.h:73-75
+      idx = cur_element_count++;
+      pos_[label] = idx;
+    }
+    labels_[idx] = label;
+    std::memcpy(&data_[idx * dim_], datapoint, dim_);
+    dirty_ = true;
+  }
+  void removePoint(labeltype label) {  // bruteforce.h:86-103
+    std::unique_lock<std::mutex> lock(mu_);
+    auto it = pos_.find(label);
+    if (it == pos_.end()) return;
+    size_t idx = it->second, last = cur_element_count - 1;
+    pos_.erase(it);
+    if (idx != last) {
+      std::memcpy(&data_[idx * dim_], &data_[last * dim_], dim_);
+      labels_[idx] = labels_[last];
+      pos_[labels_[idx]] = idx;
+    }
+    cur_element_count--;
+    dirty_ = true;
+  }
+
+  // [nq,k] rows ascending by (distance, insertion position)
+  void searchKnnBatch(const unsigned char *queries, size_t nq, size_t k, labeltype *labels, int *dists) const {
+    std::unique_lock<std::mutex> lock(mu_);
+    if (k > cur_element_count) throw std::runtime_error("BruteforceSearch: k > number of elements");  // assert at bruteforce.h:108
+    upload();
+    std::vector<uint32_t> ids(nq * k);
+    detail::check(gpu_.h, b200ann_bf_knn_u8(gpu_.h, dev_, cur_element_count, dim_, dim_, queries, nq, dim_, k, ids.data(), dists),
+                  "BruteforceSearch<int>::searchKnn");
+    for (size_t i = 0; i < nq * k; i++) labels[i] = labels_[ids[i]];
+  }
+  std::priority_queue<std::pair<int, labeltype>> searchKnn(const void *query_data, size_t k,
+                                                           BaseFilterFunctor *isIdAllowed = nullptr) const override {
+    std::priority_queue<std::pair<int, labeltype>> res;
+    if (cur_element_count == 0) return res;
+    size_t kk = k < cur_element_count ? k : cur_element_count;
+    for (;;) {
+      std::vector<labeltype> lab(kk);
+      std::vector<int> d(kk);
+      searchKnnBatch((const unsigned char *)query_data, 1, kk, lab.data(), d.data());
+      res = std::priority_queue<std::pair<int, labeltype>>();
+      for (size_t i = 0; i < kk && res.size() < k; i++)
+        if (!isIdAllowed || (*isIdAllowed)(lab[i])) res.emplace(d[i], lab[i]);
+      if (res.size() >= k || kk == cur_element_count || !isIdAllowed) break;
+      kk = kk * 4 < cur_element_count ? kk * 4 : cur_element_count;  // filtered: widen the exact scan
+    }
+    return res;
+  }
+
+  void saveIndex(const std::string &location) override {
+    std::ofstream out(location, std::ios::binary);
+    size_t spe = dim_ + sizeof(labeltype);
+    out.write((char *)&maxelements_, sizeof(size_t));
+    out.write((char *)&spe, sizeof(size_t));
+    out.write((char *)&cur_element_count, sizeof(size_t));
+    for (size_t i = 0; i < maxelements_; i++) {
+      out.write((const char *)&data_[i * dim_], dim_);
+      out.write((const char *)&labels_[i], sizeof(labeltype));
+    }
+  }
+  void loadIndex(const std::string &location, SpaceInterface<int> *s) {
+    std::ifstream in(location, std::ios::binary);
+    if (!in) throw std::runtime_error("Cannot open file");
+    set_space(s);
+    size_t spe;
+    in.read((char *)&maxelements_, sizeof(size_t));
+    in.read((char *)&spe, sizeof(size_t));
+    in.read((char *)&cur_element_count, sizeof(size_t));
+    data_.resize(maxelements_ * dim_);
+    labels_.resize(maxelements_);
+    pos_.clear();
+    for (size_t i = 0; i < maxelements_; i++) {
+      in.read((char *)&data_[i * dim_], dim_);
+      in.read((char *)&labels_[i], sizeof(labeltype));
+      if (i < cur_element_count) pos_[labels_[i]] = i;
+    }
+    dirty_ = true;
+  }
+
+ private:
+  void set_space(SpaceInterface<int> *s) {
+    if (!dynamic_cast<L2SpaceI *>(s)) throw std::runtime_error("b200ann: BruteforceSearch<int> needs L2SpaceI (a device kernel cannot call a host DISTFUNC)");
+    dim_ = *(size_t *)s->get_dist_func_param();
+  }
+  void upload() const {  // the rows stay resident on the device between searches
+    if (!dirty_ && dev_) return;
+    if (dev_) { b200ann_free_device(dev_); dev_ = nullptr; }
+    detail::check(gpu_.h, b200ann_upload_u8(gpu_.h, data_.data(), cur_element_count * dim_, &dev_), "b200ann_upload_u8");
+    dirty_ = false;
+  }
+  detail::Gpu gpu_;
+  std::vector<unsigned char> data_;
+  std::vector<labeltype> labels_;
+  std::unordered_map<labeltype, size_t> pos_;
+  mutable uint8_t *dev_ = nullptr;
   mutable bool dirty_ = true;
   mutable std::mutex mu_;
 };

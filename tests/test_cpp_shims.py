@@ -21,7 +21,7 @@ def _build(name, tmp):
     return exe
 
 
-@pytest.mark.parametrize("name", ["test_efanna_shim", "test_hnswlib_shim", "test_hybrid_shim"])
+@pytest.mark.parametrize("name", ["test_efanna_shim", "test_hnswlib_shim", "test_hybrid_shim", "test_l2spacei_shim"])
 def test_shims_compile_and_fail_loudly_without_gpu(tmp_path, name):
     exe = _build(name, tmp_path)
     try:
@@ -32,6 +32,15 @@ def test_shims_compile_and_fail_loudly_without_gpu(tmp_path, name):
     if not has_gpu:
         p = subprocess.run([exe, str(tmp_path)], capture_output=True, text=True)
         assert p.returncode != 0 and "no CUDA device" in (p.stderr + p.stdout)
+
+
+@pytest.mark.gpu
+def test_l2spacei_shim_driver(tmp_path):
+    """BruteforceSearch<int> over L2SpaceI (space_l2.h:294-323) through the shim: labels and int distances"""
+    exe = _build("test_l2spacei_shim", tmp_path)
+    p = subprocess.run([exe, str(tmp_path)], capture_output=True, text=True)
+    print(p.stdout, p.stderr)
+    assert p.returncode == 0 and "l2spacei shim ok" in p.stdout
 
 
 @pytest.mark.gpu

@@ -77,15 +77,33 @@ __device__ __forceinline__ void merge_pending(float pd, uint32_t pi, const volat
   thr_i = ((const volatile uint32_t *)dst_i)[k - 1];
 }
 
-__global__ void __launch_bounds__(NT) bf_knn_kernel(const BfParams p) {
+// running top-k state of the CTA's 64 queries (each owned by one warp)
+struct TopkSmem {
+  float pend_d[QT][PEND]; uint32_t pend_i[QT][PEND];
+  uint32_t pend_n[QT]; float thr_d[QT]; uint32_t thr_i[QT]; uint8_t curbuf[QT];
+};
+
+// Merge query ql's pending entries into its k-list. NOT inlined on purpose: the insertion pass is fully unrolled over
+// the 4x8 register tile and tests two queries per step; 64 inlined copies of the bitonic sort + merge made that pass
+// instruction-fetch bound (measured on the u8 twin of this kernel, bf_knn_u8.cu: 1.6x - 2x end to end).
+__device__ __noinline__ void flush_query(TopkSmem *st, float *l0d, float *l1d, uint32_t *l0i, uint32_t *l1i, size_t off,
+                                         uint32_t k, int ql, int lane) {
+  uint32_t cnt = st->pend_n[ql];
+  if (cnt == 0) return;
+  float pd = (uint32_t)lane < cnt ? st->pend_d[ql][lane] : INFINITY;
+  uint32_t pi = (uint32_t)lane < cnt ? st->pend_i[ql][lane] : INVALID_ID;
+  int c = st->curbuf[ql];
+  float td; uint32_t ti;
+  merge_pending(pd, pi, (c ? l1d : l0d) + off, (c ? l1i : l0i) + off, (c ? l0d : l1d) + off, (c ? l0i : l1i) + off, k,
+                lane, td, ti);
+  if (lane == 0) { st->curbuf[ql] = c ^ 1; st->pend_n[ql] = 0; st->thr_d[ql] = td; st->thr_i[ql] = ti; }
+  __syncwarp();
+}
+
+__global__ void __launch_bounds__(NT, 2) bf_knn_kernel(const BfParams p) {
   __shared__ __align__(16) float Qs[DK][QS];
   __shared__ __align__(16) float Bs[DK][BS];
-  __shared__ float pend_d[QT][PEND];
-  __shared__ uint32_t pend_i[QT][PEND];
-  __shared__ uint32_t pend_n[QT];
-  __shared__ float thr_d[QT];
-  __shared__ uint32_t thr_i[QT];
-  __shared__ uint8_t curbuf[QT];
+  __shared__ TopkSmem st;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int ty = tid >> 4, tx = tid & 15;
@@ -97,7 +115,7 @@ __global__ void __launch_bounds__(NT) bf_knn_kernel(const BfParams p) {
   const size_t lbase = ((size_t)split * p.nq) * p.k;
 
   for (int i = tid; i < QT; i += NT) {
-    pend_n[i] = 0; thr_d[i] = INFINITY; thr_i[i] = INVALID_ID; curbuf[i] = 0;
+    st.pend_n[i] = 0; st.thr_d[i] = INFINITY; st.thr_i[i] = INVALID_ID; st.curbuf[i] = 0;
   }
   // lists start as (+inf, INVALID)
   for (uint32_t qq = 0; qq < QT; qq++) {
@@ -111,18 +129,7 @@ __global__ void __launch_bounds__(NT) bf_knn_kernel(const BfParams p) {
   __syncthreads();
 
   auto flush = [&](int ql) {  // warp-cooperative; ql is warp-uniform and owned by this warp
-    uint32_t cnt = pend_n[ql];
-    if (cnt == 0) return;
-    uint32_t qg = q0 + ql;
-    float pd = (uint32_t)lane < cnt ? pend_d[ql][lane] : INFINITY;
-    uint32_t pi = (uint32_t)lane < cnt ? pend_i[ql][lane] : INVALID_ID;
-    int c = curbuf[ql];
-    size_t off = lbase + (size_t)qg * p.k;
-    float td; uint32_t ti;
-    merge_pending(pd, pi, p.list_d[c] + off, p.list_i[c] + off, p.list_d[c ^ 1] + off, p.list_i[c ^ 1] + off, p.k,
-                  lane, td, ti);
-    if (lane == 0) { curbuf[ql] = c ^ 1; pend_n[ql] = 0; thr_d[ql] = td; thr_i[ql] = ti; }
-    __syncwarp();
+    flush_query(&st, p.list_d[0], p.list_d[1], p.list_i[0], p.list_i[1], lbase + (size_t)(q0 + ql) * p.k, p.k, ql, lane);
   };
 
   for (uint32_t b0 = b_begin; b0 < b_end; b0 += BT) {
@@ -184,6 +191,23 @@ __global__ void __launch_bounds__(NT) bf_knn_kernel(const BfParams p) {
       const uint32_t qg = q0 + ty * 4 + i;
       self_id[i] = (p.self_ids && qg < p.nq) ? __ldg(p.self_ids + qg) : qg;
     }
+    // distances in place; a tile in which no lane of the warp beats its query's current k-th (the common case once
+    // the lists have warmed up: thresholds only tighten) skips the insertion pass altogether
+    bool any = false;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const int ql = ty * 4 + i;
+      const uint32_t qg = q0 + ql;
+      const float td = st.thr_d[ql]; const uint32_t ti = st.thr_i[ql];
+#pragma unroll
+      for (int j = 0; j < 8; j++) {
+        uint32_t bg = b0 + (j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4));
+        float d = p.ip ? 1.0f - acc[i][j] : acc[i][j];
+        acc[i][j] = d;
+        any |= qg < p.nq && bg < b_end && !(p.exclude_self && bg == self_id[i]) && lex_less(d, bg, td, ti);
+      }
+    }
+    if (!__any_sync(0xffffffffu, any)) continue;
 #pragma unroll
     for (int i = 0; i < 4; i++) {
       const int ql = ty * 4 + i;
@@ -192,15 +216,15 @@ __global__ void __launch_bounds__(NT) bf_knn_kernel(const BfParams p) {
       for (int j = 0; j < 8; j++) {
         // make room: at most 16 lanes push to one query per step
         int qa = (warp * 2) * 4 + i, qb = (warp * 2 + 1) * 4 + i;
-        if (pend_n[qa] > PEND - 16) flush(qa);
-        if (pend_n[qb] > PEND - 16) flush(qb);
+        if (st.pend_n[qa] > PEND - 16) flush(qa);
+        if (st.pend_n[qb] > PEND - 16) flush(qb);
         uint32_t bg = b0 + (j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4));
-        float d = p.ip ? 1.0f - acc[i][j] : acc[i][j];
+        float d = acc[i][j];
         bool pass = qg < p.nq && bg < b_end && !(p.exclude_self && bg == self_id[i]) &&
-                    lex_less(d, bg, thr_d[ql], thr_i[ql]);
+                    lex_less(d, bg, st.thr_d[ql], st.thr_i[ql]);
         if (pass) {
-          uint32_t s = atomicAdd(&pend_n[ql], 1u);
-          pend_d[ql][s] = d; pend_i[ql][s] = bg;
+          uint32_t s = atomicAdd(&st.pend_n[ql], 1u);
+          st.pend_d[ql][s] = d; st.pend_i[ql][s] = bg;
         }
         __syncwarp();
       }
@@ -214,7 +238,7 @@ __global__ void __launch_bounds__(NT) bf_knn_kernel(const BfParams p) {
   __syncwarp();
   for (int i = 0; i < 8; i++) {
     int ql = warp * 8 + i;
-    if (q0 + ql < p.nq && lane == 0) p.cur[(size_t)split * p.nq + q0 + ql] = curbuf[ql];
+    if (q0 + ql < p.nq && lane == 0) p.cur[(size_t)split * p.nq + q0 + ql] = st.curbuf[ql];
   }
 }
 
@@ -267,12 +291,19 @@ int launch_bf_knn(b200ann_handle *h, const b200ann_index *ix, const float *q, si
   p.q = q; p.qstride = qstride; p.nq = (uint32_t)nq; p.k = (uint32_t)k;
   p.ip = ix->metric == B200ANN_IP; p.exclude_self = exclude_self; p.self_ids = self_ids;
   uint32_t qtiles = (uint32_t)((nq + QT - 1) / QT);
-  uint32_t want = 2u * (uint32_t)h->sm_count;  // aim for >= 2 CTAs per SM
-  uint32_t splits = qtiles >= want ? 1u : (want + qtiles - 1) / qtiles;
-  uint32_t max_splits = (uint32_t)((ix->n + 4 * BT - 1) / (4 * BT));
-  if (splits > max_splits) splits = max_splits;
-  if (splits < 1) splits = 1;
-  if (splits > 64) splits = 64;
+  // 2 CTAs are resident per SM. A grid slightly above a whole number of waves wastes most of the last one, and every
+  // split pays its own top-k warm-up: pick the split count with the least time per CTA of useful work (bf_knn_u8.cu).
+  const uint32_t slots = 2u * (uint32_t)h->sm_count;
+  uint32_t cap = (uint32_t)((ix->n + 4 * BT - 1) / (4 * BT));
+  if (cap > 64) cap = 64;
+  if (cap < 1) cap = 1;
+  uint32_t splits = 1; double best_cost = 1e300;
+  for (uint32_t s = 1; s <= cap; s++) {
+    double ctas = (double)qtiles * s, waves = (double)((qtiles * (uint64_t)s + slots - 1) / slots);
+    double cost = waves / ctas * (1.0 + 0.02 * s);
+    if (cost < best_cost * 0.999) { best_cost = cost; splits = s; }
+  }
+  while (splits > 1 && (size_t)splits * nq * k * 16 > ((size_t)1 << 30)) splits--;  // <= 1 GiB of partial lists
   p.splits = splits;
   size_t cnt = (size_t)splits * nq * k;
   DevBuf<float> ld0, ld1; DevBuf<uint32_t> li0, li1; DevBuf<uint8_t> cur;

@@ -191,9 +191,9 @@ __global__ void __launch_bounds__(NT, 2) bf_knn_kernel(const BfParams p) {
       const uint32_t qg = q0 + ty * 4 + i;
       self_id[i] = (p.self_ids && qg < p.nq) ? __ldg(p.self_ids + qg) : qg;
     }
-    // distances in place; a tile in which no lane of the warp beats its query's current k-th (the common case once
-    // the lists have warmed up: thresholds only tighten) skips the insertion pass altogether
-    bool any = false;
+    // distances in place; a tile in which no lane of the warp beats its query's current k-th (thresholds only
+    // tighten) skips the insertion pass altogether
+    uint32_t mask = 0;  // bit i*8+j: this lane's tile entry (i,j) beats its query's current k-th
 #pragma unroll
     for (int i = 0; i < 4; i++) {
       const int ql = ty * 4 + i;
@@ -204,16 +204,20 @@ __global__ void __launch_bounds__(NT, 2) bf_knn_kernel(const BfParams p) {
         uint32_t bg = b0 + (j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4));
         float d = p.ip ? 1.0f - acc[i][j] : acc[i][j];
         acc[i][j] = d;
-        any |= qg < p.nq && bg < b_end && !(p.exclude_self && bg == self_id[i]) && lex_less(d, bg, td, ti);
+        if (qg < p.nq && bg < b_end && !(p.exclude_self && bg == self_id[i]) && lex_less(d, bg, td, ti)) mask |= 1u << (i * 8 + j);
       }
     }
-    if (!__any_sync(0xffffffffu, any)) continue;
+    // only the (i,j) steps in which some lane of the warp has an entry to insert are executed (warp-uniform test):
+    // the CTA barrier of the next tile waits for the slowest warp, so the cost of this pass is paid by all 8 warps
+    const uint32_t umask = __reduce_or_sync(0xffffffffu, mask);
+    if (umask == 0) continue;
 #pragma unroll
     for (int i = 0; i < 4; i++) {
       const int ql = ty * 4 + i;
       const uint32_t qg = q0 + ql;
 #pragma unroll
       for (int j = 0; j < 8; j++) {
+        if (!((umask >> (i * 8 + j)) & 1u)) continue;
         // make room: at most 16 lanes push to one query per step
         int qa = (warp * 2) * 4 + i, qb = (warp * 2 + 1) * 4 + i;
         if (st.pend_n[qa] > PEND - 16) flush(qa);

@@ -167,6 +167,27 @@ __global__ void __launch_bounds__(NT, 2) bf_knn_u8_kernel(const BfParams p) {
     flush_query(&st, p.list_d[0], p.list_d[1], p.list_i[0], p.list_i[1], lbase + (size_t)(q0 + ql) * p.k, p.k, ql, lane);
   };
 
+  // Register double buffer: the global loads of stage s+1 are issued before the arithmetic of stage s, so their
+  // latency hides behind 32 x 32 dp4a per thread instead of sitting in front of the CTA barrier (ncu of the
+  // single-buffered form: barrier = top stall, issue slots 30 % busy).
+  uint4 pq[2], pb[2][2];
+  auto fetch = [&](uint32_t fb0, uint32_t fc0) {  // 4 threads per row, two 16-byte chunks each
+#pragma unroll
+    for (int half = 0; half < 2; half++) {
+      const int r = tid >> 2, wc = ((tid & 3) + 4 * half) * 4;
+      const uint32_t qg = q0 + r;
+      pq[half] = make_uint4(0, 0, 0, 0);
+      if (qg < p.nq) pq[half] = load16(p.q + (size_t)qg * p.qstride, fc0 + wc * 4, p.dim, p.qvec);
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        const uint32_t bg = fb0 + r + h * 64;
+        pb[half][h] = make_uint4(0, 0, 0, 0);
+        if (bg < b_end) pb[half][h] = load16(p.base + (size_t)bg * p.bstride, fc0 + wc * 4, p.dim, p.bvec);
+      }
+    }
+  };
+  if (b_begin < b_end) fetch(b_begin, 0);
+
   for (uint32_t b0 = b_begin; b0 < b_end; b0 += BT) {
     dkey acc[4][8];
 #pragma unroll
@@ -175,25 +196,25 @@ __global__ void __launch_bounds__(NT, 2) bf_knn_u8_kernel(const BfParams p) {
       for (int j = 0; j < 8; j++) acc[i][j] = 0u;
 
     for (uint32_t c0 = 0; c0 < p.dim; c0 += DK * 4) {
-      // stage Q (64 rows x 128 bytes) and B (128 rows x 128 bytes) as packed u32 words, word-major;
-      // 4 threads per row, two 16-byte chunks each (chunk = (tid&3) + 4*half: neighbours load neighbours)
+      // stage Q (64 rows x 128 bytes) and B (128 rows x 128 bytes) as packed u32 words, word-major
 #pragma unroll
       for (int half = 0; half < 2; half++) {
-        int r = tid >> 2, wc = ((tid & 3) + 4 * half) * 4;
-        uint32_t qg = q0 + r;
-        uint4 v = make_uint4(0, 0, 0, 0);
-        if (qg < p.nq) v = load16(p.q + (size_t)qg * p.qstride, c0 + wc * 4, p.dim, p.qvec);
+        const int r = tid >> 2, wc = ((tid & 3) + 4 * half) * 4;
+        const uint4 v = pq[half];
         Qs[wc + 0][r] = v.x; Qs[wc + 1][r] = v.y; Qs[wc + 2][r] = v.z; Qs[wc + 3][r] = v.w;
 #pragma unroll
         for (int h = 0; h < 2; h++) {
-          int rb = r + h * 64;
-          uint32_t bg = b0 + rb;
-          uint4 w = make_uint4(0, 0, 0, 0);
-          if (bg < b_end) w = load16(p.base + (size_t)bg * p.bstride, c0 + wc * 4, p.dim, p.bvec);
+          const int rb = r + h * 64;
+          const uint4 w = pb[half][h];
           Bs[wc + 0][rb] = w.x; Bs[wc + 1][rb] = w.y; Bs[wc + 2][rb] = w.z; Bs[wc + 3][rb] = w.w;
         }
       }
       __syncthreads();
+      {
+        uint32_t nc0 = c0 + DK * 4, nb0 = b0;
+        if (nc0 >= p.dim) { nc0 = 0; nb0 = b0 + BT; }
+        if (nb0 < b_end) fetch(nb0, nc0);
+      }
 #pragma unroll
       for (int d = 0; d < DK; d++) {
         uint4 qv = *reinterpret_cast<const uint4 *>(&Qs[d][ty * 4]);
@@ -220,9 +241,9 @@ __global__ void __launch_bounds__(NT, 2) bf_knn_u8_kernel(const BfParams p) {
       uint32_t bg = b0 + (j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4));
       bn[j] = bg < b_end ? __ldg(p.bnorm + bg) : 0u;
     }
-    // distances in place; a tile in which no lane of the warp beats its query's current k-th (the common case once
-    // the lists have warmed up: thresholds only tighten) skips the insertion pass altogether
-    bool any = false;
+    // distances in place; a tile in which no lane of the warp beats its query's current k-th (thresholds only
+    // tighten) skips the insertion pass altogether
+    uint32_t mask = 0;  // bit i*8+j: this lane's tile entry (i,j) beats its query's current k-th
 #pragma unroll
     for (int i = 0; i < 4; i++) {
       const int ql = ty * 4 + i;
@@ -234,16 +255,20 @@ __global__ void __launch_bounds__(NT, 2) bf_knn_u8_kernel(const BfParams p) {
         // |a-b|^2 = |a|^2 + |b|^2 - 2 a.b, exact in u32 (2 a.b <= |a|^2 + |b|^2 <= 2 * 255^2 * 32768 < 2^32)
         dkey d = qn[i] + bn[j] - 2u * acc[i][j];
         acc[i][j] = d;
-        any |= qg < p.nq && bg < b_end && lex_less(d, bg, td, ti);
+        if (qg < p.nq && bg < b_end && lex_less(d, bg, td, ti)) mask |= 1u << (i * 8 + j);
       }
     }
-    if (!__any_sync(0xffffffffu, any)) continue;
+    // only the (i,j) steps in which some lane of the warp has an entry to insert are executed (warp-uniform test):
+    // the CTA barrier of the next tile waits for the slowest warp, so the cost of this pass is paid by all 8 warps
+    const uint32_t umask = __reduce_or_sync(0xffffffffu, mask);
+    if (umask == 0) continue;
 #pragma unroll
     for (int i = 0; i < 4; i++) {
       const int ql = ty * 4 + i;
       const uint32_t qg = q0 + ql;
 #pragma unroll
       for (int j = 0; j < 8; j++) {
+        if (!((umask >> (i * 8 + j)) & 1u)) continue;
         // make room: at most 16 lanes push to one query per step
         int qa = (warp * 2) * 4 + i, qb = (warp * 2 + 1) * 4 + i;
         if (st.pend_n[qa] > PEND - 16) flush(qa);

@@ -32,6 +32,7 @@ struct BfParams {
   uint32_t splits;          // base range splits (grid.y)
   dkey *list_d[2]; uint32_t *list_i[2];  // [splits, nq, k] ping-pong lists
   uint8_t *cur;             // [splits, nq] which list is current at exit
+  dkey *gthr;               // [nq] smallest k-th distance any split of the query has reached so far
 };
 
 // 16 bytes of a row starting at byte c0, zero past the row end (zero bytes add 0 to the distance)
@@ -116,13 +117,14 @@ __global__ void u8_norms_kernel(const uint8_t *rows, size_t stride, uint32_t n, 
 struct TopkSmem {
   dkey pend_d[QT][PEND]; uint32_t pend_i[QT][PEND];
   uint32_t pend_n[QT]; dkey thr_d[QT]; uint32_t thr_i[QT]; uint8_t curbuf[QT];
+  dkey gth[QT];  // copy of BfParams::gthr for the CTA's queries, refreshed every few tiles
 };
 
 // Merge query ql's pending entries into its k-list. NOT inlined on purpose: the insertion pass below is fully
 // unrolled over the 4x8 register tile and tests two queries per step, and 64 inlined copies of the bitonic sort +
 // merge made the pass instruction-fetch bound (1M x 128: 3x the cost of the tile's arithmetic).
 __device__ __noinline__ void flush_query(TopkSmem *st, dkey *l0d, dkey *l1d, uint32_t *l0i, uint32_t *l1i, size_t off,
-                                         uint32_t k, int ql, int lane) {
+                                         uint32_t k, int ql, int lane, dkey *gthr_q) {
   uint32_t cnt = st->pend_n[ql];
   if (cnt == 0) return;
   dkey pd = (uint32_t)lane < cnt ? st->pend_d[ql][lane] : DINF;
@@ -131,7 +133,10 @@ __device__ __noinline__ void flush_query(TopkSmem *st, dkey *l0d, dkey *l1d, uin
   dkey td; uint32_t ti;
   merge_pending(pd, pi, (c ? l1d : l0d) + off, (c ? l1i : l0i) + off, (c ? l0d : l1d) + off, (c ? l0i : l1i) + off, k,
                 lane, td, ti);
-  if (lane == 0) { st->curbuf[ql] = c ^ 1; st->pend_n[ql] = 0; st->thr_d[ql] = td; st->thr_i[ql] = ti; }
+  if (lane == 0) {
+    st->curbuf[ql] = c ^ 1; st->pend_n[ql] = 0; st->thr_d[ql] = td; st->thr_i[ql] = ti;
+    if (td < st->gth[ql]) { st->gth[ql] = td; atomicMin(gthr_q, td); }  // a full list: publish its k-th distance
+  }
   __syncwarp();
 }
 
@@ -150,7 +155,7 @@ __global__ void __launch_bounds__(NT, 2) bf_knn_u8_kernel(const BfParams p) {
   const size_t lbase = ((size_t)split * p.nq) * p.k;
 
   for (int i = tid; i < QT; i += NT) {
-    st.pend_n[i] = 0; st.thr_d[i] = DINF; st.thr_i[i] = INVALID_ID; st.curbuf[i] = 0;
+    st.gth[i] = DINF; st.pend_n[i] = 0; st.thr_d[i] = DINF; st.thr_i[i] = INVALID_ID; st.curbuf[i] = 0;
   }
   // lists start as (+inf, INVALID)
   for (uint32_t qq = 0; qq < QT; qq++) {
@@ -164,7 +169,8 @@ __global__ void __launch_bounds__(NT, 2) bf_knn_u8_kernel(const BfParams p) {
   __syncthreads();
 
   auto flush = [&](int ql) {  // warp-cooperative; ql is warp-uniform and owned by this warp
-    flush_query(&st, p.list_d[0], p.list_d[1], p.list_i[0], p.list_i[1], lbase + (size_t)(q0 + ql) * p.k, p.k, ql, lane);
+    flush_query(&st, p.list_d[0], p.list_d[1], p.list_i[0], p.list_i[1], lbase + (size_t)(q0 + ql) * p.k, p.k, ql, lane,
+                p.gthr + (q0 + ql));
   };
 
   // Register double buffer: the global loads of stage s+1 are issued before the arithmetic of stage s, so their
@@ -243,19 +249,34 @@ __global__ void __launch_bounds__(NT, 2) bf_knn_u8_kernel(const BfParams p) {
     }
     // distances in place; a tile in which no lane of the warp beats its query's current k-th (thresholds only
     // tighten) skips the insertion pass altogether
+    // Every split of a query keeps its own list, but an entry farther than the k-th distance ANY split has reached
+    // cannot be among the k nearest overall (equal distances still go through: the id decides), so the splits share
+    // that bound through global memory and only the first ones pay the full list warm-up. The merged result is the
+    // same exact top-k; which non-members a split happens to keep is the only thing that varies from run to run.
+    if ((((b0 - b_begin) / BT) & 3u) == 0) {
+      if (lane < 8) {
+        const int ql = warp * 8 + lane;
+        if (q0 + ql < p.nq) {
+          dkey g = *((volatile dkey *)(p.gthr + q0 + ql));
+          if (g < st.gth[ql]) st.gth[ql] = g;
+        }
+      }
+      __syncwarp();
+    }
     uint32_t mask = 0;  // bit i*8+j: this lane's tile entry (i,j) beats its query's current k-th
 #pragma unroll
     for (int i = 0; i < 4; i++) {
       const int ql = ty * 4 + i;
       const uint32_t qg = q0 + ql;
       const dkey td = st.thr_d[ql]; const uint32_t ti = st.thr_i[ql];
+      const dkey tg = st.gth[ql];
 #pragma unroll
       for (int j = 0; j < 8; j++) {
         uint32_t bg = b0 + (j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4));
         // |a-b|^2 = |a|^2 + |b|^2 - 2 a.b, exact in u32 (2 a.b <= |a|^2 + |b|^2 <= 2 * 255^2 * 32768 < 2^32)
         dkey d = qn[i] + bn[j] - 2u * acc[i][j];
         acc[i][j] = d;
-        if (qg < p.nq && bg < b_end && lex_less(d, bg, td, ti)) mask |= 1u << (i * 8 + j);
+        if (qg < p.nq && bg < b_end && d <= tg && lex_less(d, bg, td, ti)) mask |= 1u << (i * 8 + j);
       }
     }
     // only the (i,j) steps in which some lane of the warp has an entry to insert are executed (warp-uniform test):
@@ -275,7 +296,7 @@ __global__ void __launch_bounds__(NT, 2) bf_knn_u8_kernel(const BfParams p) {
         if (st.pend_n[qb] > PEND - 16) flush(qb);
         uint32_t bg = b0 + (j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4));
         dkey d = acc[i][j];
-        bool pass = qg < p.nq && bg < b_end && lex_less(d, bg, st.thr_d[ql], st.thr_i[ql]);
+        bool pass = qg < p.nq && bg < b_end && d <= st.gth[ql] && lex_less(d, bg, st.thr_d[ql], st.thr_i[ql]);
         if (pass) {
           uint32_t s = atomicAdd(&st.pend_n[ql], 1u);
           st.pend_d[ql][s] = d; st.pend_i[ql][s] = bg;
@@ -366,6 +387,10 @@ int launch_bf_knn_u8(b200ann_handle *h, const uint8_t *base, size_t n, size_t di
   CU_CHECK(h, ld0.alloc(cnt, h->stream)); CU_CHECK(h, ld1.alloc(cnt, h->stream));
   CU_CHECK(h, li0.alloc(cnt, h->stream)); CU_CHECK(h, li1.alloc(cnt, h->stream));
   CU_CHECK(h, cur.alloc((size_t)splits * nq, h->stream));
+  DevBuf<dkey> gthr;
+  CU_CHECK(h, gthr.alloc(nq, h->stream));
+  CU_CHECK(h, cudaMemsetAsync(gthr.p, 0x7F, nq * sizeof(dkey), h->stream));  // 0x7F7F7F7F > any distance, <= DINF
+  p.gthr = gthr.p;
   p.list_d[0] = ld0.p; p.list_d[1] = ld1.p; p.list_i[0] = li0.p; p.list_i[1] = li1.p; p.cur = cur.p;
   DevBuf<uint32_t> bnorm, qnorm;
   CU_CHECK(h, bnorm.alloc(n, h->stream)); CU_CHECK(h, qnorm.alloc(nq, h->stream));

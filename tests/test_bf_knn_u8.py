@@ -72,7 +72,8 @@ def H():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("n,dim,nq,k,ties", CASES + [(20000, 128, 300, 200, False), (5000, 21, 65, 10, True)])
+@pytest.mark.parametrize("n,dim,nq,k,ties", CASES + [(20000, 128, 300, 200, False), (5000, 21, 65, 10, True),
+                                                  (30000, 16, 100, 50, True), (60000, 8, 1000, 10, True)])  # many splits, heavy ties
 def test_gpu_u8_bit_exact_vs_oracle(H, n, dim, nq, k, ties):
     base, q = u8_data(n, dim, 5, ties), u8_data(nq, dim, 6, ties)
     gi, gd = H.bf_knn_u8(base, q, k)

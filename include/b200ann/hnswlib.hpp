@@ -20,6 +20,7 @@
 #include <mutex>
 #include <queue>
 #include <stdexcept>
+#include <set>
 #include <string>
 #include <unordered_map>
 #include <vector>
@@ -403,8 +404,8 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
 
   // construction ctor (hnswalg.h:89-144)
   HierarchicalNSW(SpaceInterface<dist_t> *s, size_t max_elements, size_t M = 16, size_t ef_construction = 200,
-                  size_t random_seed = 100, bool = false, int device = 0)
-      : gpu_(device) {
+                  size_t random_seed = 100, bool allow_replace_deleted = false, int device = 0)
+      : gpu_(device), allow_replace_deleted_(allow_replace_deleted) {
     detail::space_info(s, metric_, dim_);
     max_elements_ = max_elements;
     M_ = M <= 10000 ? M : 10000;                       // :98-104
@@ -414,8 +415,9 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     seed_ = random_seed;
   }
   // load ctor (hnswalg.h:78-86)
-  HierarchicalNSW(SpaceInterface<dist_t> *s, const std::string &location, bool = false, size_t max_elements = 0, bool = false, int device = 0)
-      : gpu_(device) {
+  HierarchicalNSW(SpaceInterface<dist_t> *s, const std::string &location, bool = false, size_t max_elements = 0,
+                  bool allow_replace_deleted = false, int device = 0)
+      : gpu_(device), allow_replace_deleted_(allow_replace_deleted) {
     detail::space_info(s, metric_, dim_);
     loadIndex(location, s, max_elements);
   }
@@ -438,11 +440,14 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     std::vector<char> blob(n * size_data_per_element);
     in.read(blob.data(), (std::streamsize)blob.size());
     vec_.resize(n * dim_); labels_.resize(n); links0_.assign(n * maxM0_, B200ANN_INVALID);
-    deleted_.assign(n, 0); num_deleted_ = 0;
+    deleted_.assign(n, 0); num_deleted_ = 0; deleted_set_.clear();
     for (size_t i = 0; i < n; i++) {
       const char *row = blob.data() + i * size_data_per_element;
       unsigned short cnt = *(const unsigned short *)(row + offsetLevel0);
-      if (*(const unsigned char *)(row + offsetLevel0 + 2) & DELETE_MARK) { deleted_[i] = 1; num_deleted_++; }  // :811-815
+      if (*(const unsigned char *)(row + offsetLevel0 + 2) & DELETE_MARK) {  // :811-815
+        deleted_[i] = 1; num_deleted_++;
+        if (allow_replace_deleted_) deleted_set_.insert((tableint)i);
+      }
       std::memcpy(&links0_[i * maxM0_], row + offsetLevel0 + 4, (size_t)cnt * 4);
       std::memcpy(&vec_[i * dim_], row + offsetData, dim_ * sizeof(float));
       labeltype lab;
@@ -514,10 +519,28 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
 
   // hnswalg.h:954-992 / :1153-1267. Thread-safe (the drivers call it from omp / ParallelFor loops); internal ids are
   // handed out in arrival order like cur_element_count++ (:1181).
-  void addPoint(const void *datapoint, labeltype label, bool = false) override {
+  // replace_deleted (:954-992, needs allow_replace_deleted in the ctor): the new point takes the slot (internal id,
+  // vector, label) of an element marked deleted instead of growing the index; with no deleted element it is a plain
+  // add. The reference takes *deleted_elements.begin() of an unordered_set (an unspecified one); here the smallest
+  // deleted internal id. The reference re-links the slot in place (updatePoint); here the graph is rebuilt on next use.
+  void addPoint(const void *datapoint, labeltype label, bool replace_deleted = false) override {
+    if (!allow_replace_deleted_ && replace_deleted) throw std::runtime_error("Replacement of deleted elements is disabled in constructor");  // :955-957
     std::unique_lock<std::mutex> lock(mu_);
+    if (replace_deleted && !deleted_set_.empty()) {
+      tableint id = *deleted_set_.begin();
+      deleted_set_.erase(deleted_set_.begin());
+      label_lookup_.erase(labels_[id]);      // :982-987
+      labels_[id] = label;
+      label_lookup_[label] = id;
+      deleted_[id] = 0; num_deleted_--;      // unmarkDeletedInternal :989
+      std::memcpy(&vec_[id * dim_], datapoint, dim_ * sizeof(float));
+      dirty_ = true;
+      return;
+    }
     auto it = label_lookup_.find(label);
     if (it != label_lookup_.end()) {
+      if (allow_replace_deleted_ && deleted_[it->second])  // :1163-1167
+        throw std::runtime_error("Can't use addPoint to update deleted elements if replacement of deleted elements is enabled.");
       if (deleted_[it->second]) { deleted_[it->second] = 0; num_deleted_--; }  // :1166-1168: an update un-deletes
       std::memcpy(&vec_[it->second * dim_], datapoint, dim_ * sizeof(float));
       dirty_ = true;
@@ -539,6 +562,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     if (it == label_lookup_.end()) throw std::runtime_error("Label not found");
     if (deleted_[it->second]) throw std::runtime_error("The requested to delete element is already deleted");
     deleted_[it->second] = 1; num_deleted_++;
+    if (allow_replace_deleted_) deleted_set_.insert((tableint)it->second);  // :879-882
   }
   void unmarkDelete(labeltype label) {
     std::unique_lock<std::mutex> lock(mu_);
@@ -546,6 +570,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     if (it == label_lookup_.end()) throw std::runtime_error("Label not found");
     if (!deleted_[it->second]) throw std::runtime_error("The requested to undelete element is not deleted");
     deleted_[it->second] = 0; num_deleted_--;
+    if (allow_replace_deleted_) deleted_set_.erase((tableint)it->second);  // :921-924
   }
   // hnswalg.h:640-675: only the capacity changes here (the staging vectors grow on demand)
   void resizeIndex(size_t new_max_elements) {
@@ -625,6 +650,8 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
   static const unsigned char DELETE_MARK = 0x01;  // hnswalg.h:21
   std::vector<unsigned char> deleted_;
   size_t num_deleted_ = 0;
+  bool allow_replace_deleted_ = false;
+  std::set<tableint> deleted_set_;  // internal ids marked deleted (kept only with allow_replace_deleted_, like :71)
   template <typename T> static void rd(std::istream &in, T &v) { in.read((char *)&v, sizeof(T)); }
   template <typename T> static void wr(std::ostream &out, const T &v) { out.write((const char *)&v, sizeof(T)); }
   void upload() {

@@ -21,7 +21,7 @@ def _build(name, tmp):
     return exe
 
 
-@pytest.mark.parametrize("name", ["test_efanna_shim", "test_hnswlib_shim", "test_hybrid_shim", "test_l2spacei_shim"])
+@pytest.mark.parametrize("name", ["test_efanna_shim", "test_hnswlib_shim", "test_hybrid_shim", "test_l2spacei_shim", "test_replace_deleted"])
 def test_shims_compile_and_fail_loudly_without_gpu(tmp_path, name):
     exe = _build(name, tmp_path)
     try:
@@ -41,6 +41,15 @@ def test_l2spacei_shim_driver(tmp_path):
     p = subprocess.run([exe, str(tmp_path)], capture_output=True, text=True)
     print(p.stdout, p.stderr)
     assert p.returncode == 0 and "l2spacei shim ok" in p.stdout
+
+
+@pytest.mark.gpu
+def test_replace_deleted_driver(tmp_path):
+    """allow_replace_deleted / addPoint(replace_deleted=True), hnswalg.h:954-992"""
+    exe = _build("test_replace_deleted", tmp_path)
+    p = subprocess.run([exe], capture_output=True, text=True)
+    print(p.stdout, p.stderr)
+    assert p.returncode == 0 and "replace_deleted ok" in p.stdout
 
 
 @pytest.mark.gpu

@@ -16,8 +16,8 @@ CUDA library every compute call raises.
 
 knn_query(filter=...) and mark_deleted / unmark_deleted run the reference's searchBaseLayerST<false> on the GPU
 (b200ann_hnsw_search_filtered): the Python callable is evaluated once per call over all labels into a bitmap.
-Not on the GPU path yet (raises NotImplementedError instead of answering differently from the reference):
-add_items(replace_deleted=True)."""
+add_items(replace_deleted=True) reuses the slots of deleted elements (hnswalg.h:954-992, needs
+init_index(allow_replace_deleted=True)); the graph is rebuilt on the next query."""
 import importlib
 import pickle  # noqa: F401  (Index/BFIndex define __getstate__/__setstate__)
 
@@ -212,8 +212,12 @@ class Index:
         """bindings.cpp:250-330. A label that is already present replaces that element's vector (the reference's
         updatePoint, hnswalg.h:1158-1175); the graph is rebuilt on the next query either way."""
         self._need_init()
-        if replace_deleted:
-            raise NotImplementedError("add_items(replace_deleted=True) is not on the GPU path yet")
+        if replace_deleted and not self._allow_replace:           # hnswalg.h:955-957
+            raise RuntimeError("Replacement of deleted elements is disabled in constructor")
+        # replace_deleted (hnswalg.h:954-992): a new point takes the slot (internal id, vector, label) of an element
+        # marked deleted; the reference picks an unspecified one (unordered_set::begin), here the smallest internal id
+        vacant = np.flatnonzero(self._deleted).tolist() if replace_deleted else []
+        vacant.reverse()
         rows = _as_rows(data, self.dim)
         labels = _as_ids(ids, len(rows), self._cur_l)
         self._cur_l += len(rows)                                  # :328
@@ -222,8 +226,19 @@ class Index:
         new_rows, new_labels = [], []
         try:
             for r, lab in enumerate(labels.tolist()):
+                if vacant:
+                    at = vacant.pop()
+                    self._lookup.pop(int(self._labels[at]), None)    # :982-987
+                    self._labels[at] = lab
+                    self._lookup[lab] = at
+                    self._deleted[at] = False                     # unmarkDeletedInternal, :989
+                    self._vec[at] = rows[r]
+                    continue
                 at = self._lookup.get(lab)
                 if at is not None:
+                    if self._allow_replace and at < len(self._vec) and self._deleted[at]:   # :1163-1167
+                        raise RuntimeError("Can't use addPoint to update deleted elements if replacement of deleted "
+                                           "elements is enabled.")
                     if at < len(self._vec):
                         self._vec[at] = rows[r]
                         self._deleted[at] = False                 # hnswalg.h:1166-1168: an update un-deletes

@@ -225,3 +225,60 @@ def test_filter_and_mark_deleted(hnswlib, tmp_path):
     assert np.mean(restored.reshape(-1) == np.arange(len(data1))) > 0.999
     for x in (p, p2, bf):
         x.close()
+
+
+def test_replace_deleted(hnswlib, tmp_path):
+    # bindings_test_replace.py:9-139 (dim 16, 4 batches, capacity = 2 batches, replace the deleted ones twice, with a
+    # save -> load(allow_replace_deleted=True) in between); smaller batches than the reference's 5000
+    dim, ne = 16, 2000
+    rng = np.random.default_rng(5)
+    data = [rng.random((ne, dim), dtype=np.float32) for _ in range(4)]
+    labels = [np.arange(b * ne, (b + 1) * ne) for b in range(4)]
+    ix = hnswlib.Index(space="l2", dim=dim)
+    ix.init_index(max_elements=2 * ne, ef_construction=200, M=16, allow_replace_deleted=True)
+    ix.set_ef(100)
+    ix.add_items(data[0], labels[0])
+    ix.add_items(data[1], labels[1])                       # the index is full
+    with pytest.raises(RuntimeError, match="exceeds the specified limit"):
+        ix.add_items(data[2][:1], labels[2][:1])
+    deleted = set(ix.knn_query(data[1], k=1)[0].flatten().tolist())
+    ndup = ne - len(deleted)
+    for lab in deleted:
+        ix.mark_deleted(lab)
+    with pytest.raises(RuntimeError, match="Can't use addPoint to update deleted elements"):
+        ix.add_items(data[1][:1], [next(iter(deleted))])
+    found1 = ix.knn_query(data[0], k=1)[0]
+    assert np.mean(np.abs(data[0] - ix.get_items(found1.flatten()))) < 1e-3
+    assert not (set(ix.knn_query(data[1], k=1)[0].flatten().tolist()) & deleted)
+    l3, d3 = labels[2][:ne - ndup], data[2][:ne - ndup]
+    ix.add_items(d3, l3, replace_deleted=True)             # fits only because the deleted slots are reused
+    assert ix.get_current_count() == 2 * ne
+    remaining = sorted((set(labels[0].tolist()) | set(labels[1].tolist())) - deleted)
+    comb = np.concatenate([data[0], data[1]])
+    assert (np.asarray(ix.get_items(remaining)) == comb[remaining]).all()
+    assert (np.asarray(ix.get_items(l3)) == d3).all()
+    got = ix.knn_query(d3, k=1)[0].flatten()
+    assert np.mean(got == l3) > 0.99                       # the replacing points are found under their new labels
+    for lab in deleted:                                    # the replaced labels are gone
+        with pytest.raises(RuntimeError):
+            ix.get_items([lab])
+        break
+    # serialisation: delete batch 3, save, load with replacement enabled, replace with batch 4
+    for lab in l3:
+        ix.mark_deleted(lab)
+    path = str(tmp_path / "replace.bin")
+    ix.save_index(path)
+    ix2 = hnswlib.Index(space="l2", dim=dim)
+    ix2.load_index(path, max_elements=2 * ne, allow_replace_deleted=True)
+    ix2.set_ef(100)
+    l4, d4 = labels[3][:len(l3)], data[3][:len(l3)]
+    ix2.add_items(d4, l4, replace_deleted=True)
+    assert ix2.get_current_count() == 2 * ne
+    got = ix2.knn_query(d4, k=1)[0].flatten()
+    assert np.mean(got == l4) > 0.99
+    assert not (set(ix2.knn_query(data[2], k=1)[0].flatten().tolist()) & set(l3.tolist()))
+    # replacement disabled -> the reference's exception
+    ix3 = hnswlib.Index(space="l2", dim=dim)
+    ix3.init_index(max_elements=10)
+    with pytest.raises(RuntimeError, match="Replacement of deleted elements is disabled in constructor"):
+        ix3.add_items(data[0][:2], [0, 1], replace_deleted=True)

@@ -130,7 +130,7 @@ def test_binding_host_logic_without_compute(tmp_path):
         p.resize_index(2)
     p.resize_index(9)
     assert p.max_elements == 9
-    with pytest.raises(NotImplementedError):
+    with pytest.raises(RuntimeError, match="Replacement of deleted elements is disabled in constructor"):  # hnswalg.h:955-957
         p.add_items(x[:1], replace_deleted=True)
     # markDelete bookkeeping and its error messages (hnswalg.h:853-922); an update un-deletes (:1166-1168)
     p.mark_deleted(7)
@@ -145,6 +145,25 @@ def test_binding_host_logic_without_compute(tmp_path):
     p.mark_deleted(9)
     p.add_items(x[:1], ids=[9])
     assert not p._deleted.any()
+    # replace_deleted bookkeeping (hnswalg.h:954-992, :1160-1167): deleted slots are reused smallest id first
+    r = hp.Index("l2", 4)
+    r.init_index(max_elements=4, allow_replace_deleted=True)
+    r.add_items(x[:4], ids=[10, 11, 12, 13])
+    r.mark_deleted(12)
+    r.mark_deleted(10)
+    with pytest.raises(RuntimeError, match="Can't use addPoint to update deleted elements"):
+        r.add_items(x[:1], ids=[12])
+    with pytest.raises(RuntimeError, match="exceeds the specified limit"):
+        r.add_items(x[4:5], ids=[50])
+    r.add_items(x[4:5] + 7, ids=[50], replace_deleted=True)
+    assert r.get_ids_list() == [50, 11, 12, 13] and r._deleted.tolist() == [False, False, True, False]
+    assert (r.get_items([50]) == x[4:5] + 7).all() and r.get_current_count() == 4
+    with pytest.raises(RuntimeError, match="Label not found"):
+        r.get_items([10])
+    r.add_items(x[0:1], ids=[60], replace_deleted=True)           # takes slot 2 (label 12)
+    assert r.get_ids_list() == [50, 11, 60, 13] and not r._deleted.any()
+    with pytest.raises(RuntimeError, match="exceeds the specified limit"):   # nothing vacant: a plain add
+        r.add_items(x[1:2], ids=[61], replace_deleted=True)
     c = hp.Index("cosine", 4)
     c.init_index(3)
     c.add_items(np.array([[3, 0, 4, 0]], np.float32))

@@ -330,6 +330,8 @@ class Index:
                 rows = [self._lookup[int(x)] for x in a.reshape(-1).tolist()]
             except KeyError:
                 raise RuntimeError("Label not found")             # hnswalg.h:831
+            if any(r < len(self._deleted) and self._deleted[r] for r in rows):
+                raise RuntimeError("Label not found")             # :832 a deleted element is not returned either
             out = self._vec[rows].copy()
         return out if return_type == "numpy" else out.tolist()
 

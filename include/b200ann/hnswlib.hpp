@@ -579,6 +579,15 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     max_elements_ = new_max_elements;
   }
   bool isMarkedDeleted(tableint internal_id) const { return deleted_[internal_id] != 0; }
+  // hnswalg.h:825-847: the stored vector of a label; unknown and deleted labels throw alike
+  template <typename data_t>
+  std::vector<data_t> getDataByLabel(labeltype label) const {
+    std::unique_lock<std::mutex> lock(mu_);
+    auto it = label_lookup_.find(label);
+    if (it == label_lookup_.end() || deleted_[it->second]) throw std::runtime_error("Label not found");
+    const data_t *p = (const data_t *)&vec_[it->second * dim_];
+    return std::vector<data_t>(p, p + dim_);
+  }
   size_t getDeletedCount() const { return num_deleted_; }
   size_t getCurrentElementCount() const { return cur_element_count; }
   size_t getMaxElements() const { return max_elements_; }

@@ -2,6 +2,7 @@
 // reference's contract (hnswlib/hnswlib/hnswalg.h:954-992, :1160-1167) and its test tests/python/bindings_test_replace.py:
 // deleted slots are reused, the index does not grow, replaced labels disappear, new labels are found.
 #include <b200ann/hnswlib.hpp>
+#include <algorithm>
 #include <cstdio>
 #include <random>
 #include <vector>
@@ -40,6 +41,11 @@ int main() {
     REQUIRE(ix.getDeletedCount() == 0 && ix.cur_element_count == n);
     // replaced labels are gone, new labels are their own nearest neighbour at distance 0
     REQUIRE(throws_with([&] { ix.markDelete(0); }, "Label not found"));
+    REQUIRE(throws_with([&] { ix.getDataByLabel<float>(0); }, "Label not found"));
+    {
+      std::vector<float> v = ix.getDataByLabel<float>(100000 + 7);
+      REQUIRE(v.size() == dim && std::equal(v.begin(), v.end(), &extra[7 * dim]));
+    }
     size_t miss_new = 0, miss_old = 0;  // graph search is approximate: allow a stray miss, never a replaced label
     for (size_t i = 0; i < ndel; i++) {
       auto r = ix.searchKnnCloserFirst(&extra[i * dim], 1);

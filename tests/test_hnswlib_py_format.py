@@ -141,6 +141,8 @@ def test_binding_host_logic_without_compute(tmp_path):
     with pytest.raises(RuntimeError, match="not deleted"):
         p.unmark_deleted(0)
     assert p._deleted.tolist() == [False, False, True, False, False]
+    with pytest.raises(RuntimeError, match="Label not found"):  # getDataByLabel refuses deleted elements, hnswalg.h:832
+        p.get_items([7])
     p.unmark_deleted(7)
     p.mark_deleted(9)
     p.add_items(x[:1], ids=[9])

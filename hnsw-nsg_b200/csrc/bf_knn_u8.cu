@@ -14,6 +14,7 @@
 // __vabsdiffu4 + __dp4a on the differences needed two instructions). Rows are fetched with 16-byte loads when
 // base and stride are 16-byte aligned; the tail of a row is zero filled (zero bytes add nothing to products
 // or norms). HBM traffic = n*dim bytes per 64-query tile; the kernel is bound by the integer pipe.
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace {
@@ -379,6 +380,10 @@ int launch_bf_knn_u8(b200ann_handle *h, const uint8_t *base, size_t n, size_t di
     double ctas = (double)qtiles * s, waves = (double)((qtiles * (uint64_t)s + slots - 1) / slots);
     double cost = waves / ctas * (1.0 + 0.02 * s);
     if (cost < best_cost * 0.999) { best_cost = cost; splits = s; }
+  }
+  if (const char *e = getenv("B200ANN_U8_SPLITS")) {  // A/B knob for the heuristic above
+    int v = atoi(e);
+    if (v >= 1 && (uint32_t)v <= cap) splits = (uint32_t)v;
   }
   while (splits > 1 && (size_t)splits * nq * k * 16 > ((size_t)1 << 30)) splits--;  // <= 1 GiB of partial lists
   p.splits = splits;

@@ -68,6 +68,9 @@ _lib.b200ann_set_async.argtypes = [_vp, C.c_int]
 _lib.b200ann_cluster_search.argtypes = [_vp, _vp, _vp, _sz, _vp, _vp, _vp, _sz, _vp, _vp, _sz, _sz, _sz, _sz, _sz, _sz, _u32,
                                         C.c_int, _vp, _vp, _vp]
 _lib.b200ann_knn_last_stats.argtypes = [_vp, _vp]
+_lib.b200ann_set_search_options.argtypes = [_vp, C.c_int, C.c_int, C.c_int]
+_lib.b200ann_set_query_order.argtypes = [_vp, _vp, _sz]
+_lib.b200ann_probe_gather.argtypes = [_vp, _vp, C.c_uint64, C.c_int, C.c_int, C.c_int, _u32, C.POINTER(C.c_float)]
 _lib.b200ann_nsg_finish.argtypes = [_vp, _vp, _vp, _vp, _sz, _u32, _sz, _u32, _sz, C.POINTER(_u32)]
 
 EXPORTS = [
@@ -80,6 +83,7 @@ EXPORTS = [
     "b200ann_nsg_interinsert", "b200ann_nsg_finish", "b200ann_merge_topk", "b200ann_nsg_search_from",
     "b200ann_hybrid_search", "b200ann_set_knn_mode", "b200ann_knn_last_stats", "b200ann_nndescent",
     "b200ann_hnsw_build", "b200ann_index_hnsw_shape", "b200ann_index_get_hnsw", "b200ann_nsg_search_clustered",
+    "b200ann_set_search_options", "b200ann_set_query_order", "b200ann_probe_gather",
     "b200ann_set_async", "b200ann_cluster_search", "b200ann_bf_knn_u8", "b200ann_upload_u8", "b200ann_free_device",
 ]
 
@@ -159,6 +163,16 @@ class Handle:
         """device-to-device nsg_search / merge_topk calls stop synchronizing the stream (see b200ann.h)"""
         self._check(_lib.b200ann_set_async(self._h, 1 if on else 0))
 
+    def set_search_options(self, prefetch=-1, visited_compact=-1, ctas_per_sm=-1):
+        """scheduling knobs of the search kernels (never change results); -1 = leave as is"""
+        self._check(_lib.b200ann_set_search_options(self._h, prefetch, visited_compact, ctas_per_sm))
+
+    def set_query_order(self, order):
+        """order: device u32/i32 permutation (torch tensor / raw pointer) or None; see b200ann.h"""
+        n = 0 if order is None else int(order.numel()) if hasattr(order, "numel") else int(len(order))
+        self._order_keepalive = order
+        self._check(_lib.b200ann_set_query_order(self._h, _ptr(order), n))
+
     def set_visited_bits(self, bits):
         self._check(_lib.b200ann_set_visited_bits(self._h, bits))
 
@@ -214,6 +228,13 @@ class Index:
             self._ix = None
 
     __del__ = close
+
+    def probe_gather(self, rows, inflight=2, warps_per_block=8, blocks_per_sm=8, seed=1):
+        """random whole-row gather rate of this index in GB/s (b200ann_probe_gather)"""
+        ms = C.c_float(0)
+        self.h._check(_lib.b200ann_probe_gather(self.h._h, self._ix, rows, inflight, warps_per_block, blocks_per_sm, seed,
+                                                C.byref(ms)))
+        return rows * self.dim * 4 / (ms.value * 1e-3) / 1e9, ms.value
 
     # ---- graphs
     def set_graph(self, graph, ep):

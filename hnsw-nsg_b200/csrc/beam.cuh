@@ -53,6 +53,10 @@ struct SearchParams {
   uint32_t cand_cap, pool_cap;  // words
   uint32_t *ids; uint64_t *labels_out; float *dists; uint32_t *stats;
   uint32_t *work;               // search kernels: queue counter (NULL = query index from the launch grid)
+  const uint32_t *order;        // search kernels: work item w -> query order[w] (NULL = identity); scheduling only
+  int vis16;                    // visited set entries: 0 = u32 ids (2^hbits slots), 1 = u16 tags (2^(hbits+1) slots)
+  int nbits;                    // vis16: ids are hashed as nbits-bit numbers (n <= 2^nbits)
+  int prefetch;                 // 1: expand_all prefetches the adjacency row of the next unexpanded pool entry
 };
 
 __device__ __forceinline__ uint32_t mix32(uint32_t x) {
@@ -84,6 +88,7 @@ struct Beam {
   float *pool_d; uint32_t *pool_i;   // [pool_cap]
   uint32_t *cand_i; float *cand_d;   // [cand_cap]
   uint32_t *tab; uint32_t hshift, hmask;
+  uint32_t nmask, rbits, rmask, smask;  // vis16 geometry
   float4 qreg[NCH];
   int lane, t, g;
   uint32_t np, cap;
@@ -99,6 +104,13 @@ struct Beam {
     tab = smem_base + 2 * p.pool_cap + 2 * p.cand_cap;
     hshift = 32 - p.hbits;
     hmask = (1u << p.hbits) - 1;
+    nmask = rbits = rmask = smask = 0;
+    if (p.vis16) {
+      nmask = p.nbits >= 32 ? 0xFFFFFFFFu : ((1u << p.nbits) - 1);
+      rbits = (uint32_t)(p.nbits - (p.hbits + 1));
+      rmask = (1u << rbits) - 1;
+      smask = (2u << p.hbits) - 1;
+    }
     lane = threadIdx.x & 31;
     t = lane % TEAM;
     g = lane / TEAM;
@@ -108,6 +120,21 @@ struct Beam {
 
   // visited set: true if `id` was already present, else inserts it
   __device__ __forceinline__ bool test_and_set(uint32_t id) {
+    if (p.vis16) {
+      const uint32_t x = (id * 0x9E3779B1u) & nmask;
+      const uint32_t s = x >> rbits;
+      const uint32_t tag = (x & rmask) << 3;
+      unsigned short *t16 = reinterpret_cast<unsigned short *>(tab);
+#pragma unroll 1
+      for (uint32_t pr = 0; pr < (uint32_t)PROBES; pr++) {
+        const unsigned short e = (unsigned short)(tag | pr);
+        unsigned short old = atomicCAS(&t16[(s + pr) & smask], (unsigned short)0xFFFFu, e);
+        if (old == 0xFFFFu) return false;
+        if (old == e) return true;
+      }
+      t16[s] = (unsigned short)tag;  // probe sequence full: forget the home slot's entry
+      return false;
+    }
     uint32_t s = slot(id);
 #pragma unroll 1
     for (int pr = 0; pr < PROBES; pr++) {
@@ -369,6 +396,24 @@ struct Beam {
     cap = Lq;
   }
 
+  // Speculative prefetch (the reference's _mm_prefetch of the next rows, index_nsg.cpp:627-632, hnswalg.h:370-383):
+  // while node pool[k] is expanded, the adjacency row of the next unexpanded pool entry - the node the loop turns to
+  // next unless a closer candidate arrives - is pulled into L2, so its load later costs an L2 hit instead of a DRAM
+  // round trip on the hop's critical path. Touches no state: results cannot change.
+  __device__ __forceinline__ void prefetch_next_row(uint32_t k) {
+    uint32_t nxt = INVALID_ID;
+    for (uint32_t j0 = k + 1; j0 < np; j0 += 32) {
+      uint32_t j = j0 + lane;
+      uint32_t e = j < np ? pool_i[j] : 0u;
+      unsigned m = __ballot_sync(0xffffffffu, (e & FLAG) != 0);
+      if (m) { nxt = __shfl_sync(0xffffffffu, e, __ffs(m) - 1) & ~FLAG; break; }
+    }
+    if (nxt != INVALID_ID) {
+      const uint32_t *row = p.graph + (size_t)nxt * p.gstride;
+      if ((uint32_t)lane * 32u < p.gstride) asm volatile("prefetch.global.L2 [%0];" ::"l"(row + lane * 32));
+    }
+  }
+
   // main loop (index_nsg.cpp:539-564 / hnswalg.h:342-436)
   template <class Rec>
   __device__ __forceinline__ void expand_all(Rec &rec) {
@@ -381,6 +426,7 @@ struct Beam {
         if (lane == 0) pool_i[k] = e & ~FLAG;
         uint32_t node = e & ~FLAG;
         n_hops++;
+        if (p.prefetch && !(HNSW && lvl > 0)) prefetch_next_row(k);
         const uint32_t *row = p.graph + (size_t)node * p.gstride;
         uint32_t rl = p.gstride;
         if (HNSW && lvl > 0) {

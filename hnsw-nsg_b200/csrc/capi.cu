@@ -71,6 +71,9 @@ int b200ann_create(int device, b200ann_handle_t *out) {
   }
   cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device);
   if (const char *e = getenv("B200ANN_PERSISTENT")) h->persistent = atoi(e);  // tuning knob: 0 = one launch slot per query
+  if (const char *e = getenv("B200ANN_SEARCH_PREFETCH")) h->search_prefetch = atoi(e);
+  if (const char *e = getenv("B200ANN_VISITED_COMPACT")) h->visited_compact = atoi(e);
+  if (const char *e = getenv("B200ANN_SEARCH_CTAS_PER_SM")) h->search_ctas_per_sm = atoi(e);
   {  // keep the stream-ordered scratch pool mapped between calls (default: released at every synchronize)
     cudaMemPool_t pool;
     if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
@@ -104,6 +107,36 @@ int b200ann_set_visited_bits(b200ann_handle_t h, int bits) {
   if (!h) return B200ANN_ERR_ARG;
   if (bits < 5 || bits > 14) return set_err(h, B200ANN_ERR_ARG, "visited_bits must be in [5,14]");
   h->visited_bits = bits;
+  return 0;
+}
+
+int b200ann_set_search_options(b200ann_handle_t h, int prefetch, int visited_compact, int ctas_per_sm) {
+  if (!h) return B200ANN_ERR_ARG;
+  if (prefetch >= 0) h->search_prefetch = prefetch != 0;
+  if (visited_compact >= 0) h->visited_compact = visited_compact != 0;
+  if (ctas_per_sm >= 0) h->search_ctas_per_sm = ctas_per_sm;
+  return 0;
+}
+
+int b200ann_set_query_order(b200ann_handle_t h, const uint32_t *order, size_t n) {
+  if (!h) return B200ANN_ERR_ARG;
+  if (order && !is_device_ptr(order)) return set_err(h, B200ANN_ERR_ARG, "set_query_order: order must be device memory");
+  h->query_order = order; h->query_order_n = order ? n : 0;
+  return 0;
+}
+
+int b200ann_probe_gather(b200ann_handle_t h, b200ann_index_t ix, uint64_t rows, int inflight, int warps_per_block,
+                         int blocks_per_sm, uint32_t seed, float *ms) {
+  if (!h || !ix || !ms) return B200ANN_ERR_ARG;
+  CU_CHECK(h, cudaSetDevice(h->device));
+  DevBuf<float> sink;
+  CU_CHECK(h, sink.alloc(1, h->stream));
+  CallTimer t(h);
+  int rc = launch_gather_probe(h, ix, rows, inflight, warps_per_block, blocks_per_sm, seed, sink.p);
+  t.stop();
+  if (rc) return rc;
+  CU_CHECK(h, t.sync());
+  *ms = h->last_ms;
   return 0;
 }
 

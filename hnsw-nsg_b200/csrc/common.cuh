@@ -27,6 +27,11 @@ struct b200ann_handle {
   uint64_t knn_stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   uint32_t *work = nullptr;  // device work-queue counter of the persistent search kernel (search.cu)
   int persistent = 1;        // 1: search warps pull queries from the queue; 0: one query per warp, one launch slot each
+  const uint32_t *query_order = nullptr;  // b200ann_set_query_order: device permutation of the next search's work items
+  size_t query_order_n = 0;
+  int search_prefetch = 1;   // beam.cuh prefetch_next_row (B200ANN_SEARCH_PREFETCH=0 turns it off for A/B runs)
+  int visited_compact = 1;   // 16-bit visited-set entries when n allows (B200ANN_VISITED_COMPACT=0: 32-bit ids)
+  int search_ctas_per_sm = 0;  // cap on resident blocks per SM of the persistent search kernel (0 = occupancy limit)
   bool async_mode = false;   // b200ann_set_async: device-to-device search / merge calls do not synchronize the stream
 };
 
@@ -145,6 +150,8 @@ int launch_nsg_search_clustered(b200ann_handle *h, const b200ann_index *ix, cons
                                 const uint32_t *size, uint32_t *ids, float *dists, uint32_t *stats);
 int launch_hnsw_search(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
                        size_t k, size_t ef, uint64_t *labels, float *dists, uint32_t *stats);
+int launch_gather_probe(b200ann_handle *h, const b200ann_index *ix, uint64_t rows, int inflight, int wpb, int bpsm,
+                        uint32_t seed, float *sink);
 int launch_hnsw_search_filtered(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
                                 size_t k, size_t ef, const uint32_t *allow_bits, size_t ccap, bool big,
                                 const uint8_t *only, uint64_t *labels, float *dists, uint32_t *stats, uint8_t *inexact,

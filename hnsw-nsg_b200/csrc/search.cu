@@ -31,6 +31,7 @@ __global__ void __launch_bounds__(WARPS * 32, (NCH <= 4 ? 6 : 1)) beam_search_ke
       qi = blockIdx.x * WARPS + warp;
     }
     if (qi >= p.nq) break;
+    if (p.order) qi = __ldg(p.order + qi);
     b.begin(p.q + (size_t)qi * p.qstride);
     if (HNSW) {
       b.descend_hnsw();
@@ -85,6 +86,12 @@ __global__ void __launch_bounds__(WARPS * 32, (NCH <= 4 ? 6 : 1)) beam_search_ke
 template <int TEAM, int NCH, bool IP, bool HNSW>
 int launch_t(b200ann_handle *h, const SearchParams &p0) {
   SearchParams p = p0;
+  p.order = (h->query_order && h->query_order_n == p.nq) ? h->query_order : nullptr;
+  p.prefetch = h->search_prefetch;
+  p.nbits = 1;
+  while (p.nbits < 32 && (1ull << p.nbits) < (unsigned long long)p.n) p.nbits++;
+  if (p.nbits < p.hbits + 1) p.nbits = p.hbits + 1;
+  p.vis16 = (h->visited_compact && p.nbits - (p.hbits + 1) <= 12) ? 1 : 0;
   size_t smem = (size_t)WARPS * smem_words(p.pool_cap, p.cand_cap, p.hbits) * 4;
   if (smem > 227 * 1024) return set_err(h, B200ANN_ERR_ARG, "search: L / degree / visited_bits need more than 227 KB shared memory per block");
   auto kern = beam_search_kernel<TEAM, NCH, IP, HNSW>;
@@ -94,6 +101,7 @@ int launch_t(b200ann_handle *h, const SearchParams &p0) {
   if (h->persistent) {
     int occ = 0;
     CU_CHECK(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, WARPS * 32, smem));
+    if (h->search_ctas_per_sm > 0 && h->search_ctas_per_sm < occ) occ = h->search_ctas_per_sm;
     size_t wave = (size_t)(occ > 0 ? occ : 1) * (size_t)h->sm_count;
     if (blocks > wave) {  // more than one wave of blocks: pull queries from a queue instead
       if (!h->work) CU_CHECK(h, cudaMalloc((void **)&h->work, sizeof(uint32_t)));
@@ -123,6 +131,73 @@ int launch_dim(b200ann_handle *h, const SearchParams &p) {
 }
 
 }  // namespace
+
+// ---------------------------------------------------------------- random-row gather probe
+// What HBM delivers for the access pattern of graph search itself: whole rows of the index at pseudo-random
+// positions, read with the search kernels' own loads (a team of 8 / 32 lanes per row, 16 bytes per lane and load,
+// `inflight` rows per team in flight), no dependence between rows. The measured rate is the ceiling a beam search
+// over this index can reach; bench.py reports it next to the streaming-copy peak.
+namespace {
+template <int TEAM, int NCH, int INFLIGHT>
+__global__ void __launch_bounds__(256) gather_probe_kernel(const float *vec, size_t stride, uint32_t n, int nch,
+                                                           uint64_t rows_total, uint32_t seed, float *sink) {
+  constexpr int TPW = 32 / TEAM;
+  const int lane = threadIdx.x & 31, t = lane % TEAM, g = lane / TEAM;
+  const uint64_t team_id = ((uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * TPW + g;
+  const uint64_t teams = (uint64_t)gridDim.x * (blockDim.x >> 5) * TPW;
+  float acc = 0.f;
+  for (uint64_t r0 = team_id * INFLIGHT; r0 < rows_total; r0 += teams * INFLIGHT) {
+    float4 v[INFLIGHT][NCH];
+#pragma unroll
+    for (int i = 0; i < INFLIGHT; i++) {
+      uint32_t row = seed_hash(seed, (uint32_t)(r0 + i), (uint32_t)((r0 + i) >> 32)) % n;
+      const float4 *rp = reinterpret_cast<const float4 *>(vec + (size_t)row * stride);
+#pragma unroll
+      for (int c = 0; c < NCH; c++) {
+        int ch = t + c * TEAM;
+        v[i][c] = ch < nch ? ld_row16(rp + ch) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < INFLIGHT; i++)
+#pragma unroll
+      for (int c = 0; c < NCH; c++) acc += v[i][c].x + v[i][c].y + v[i][c].z + v[i][c].w;
+  }
+  if (acc == 1.2345e-30f) sink[0] = acc;  // keeps the loads alive
+}
+
+template <int TEAM, int NCH>
+int probe_launch(b200ann_handle *h, const b200ann_index *ix, uint64_t rows, int inflight, int wpb, int bpsm,
+                 uint32_t seed, float *sink) {
+  dim3 grid((unsigned)(h->sm_count * bpsm)), block((unsigned)(wpb * 32));
+  const int nch = (int)((ix->dim + 3) / 4);
+#define PROBE_CASE(F)                                                                                              \
+  case F:                                                                                                          \
+    gather_probe_kernel<TEAM, NCH, F><<<grid, block, 0, h->stream>>>(ix->vec, ix->stride, (uint32_t)ix->n, nch, rows, seed, sink); \
+    break;
+  switch (inflight) {
+    PROBE_CASE(1) PROBE_CASE(2) PROBE_CASE(4)
+    default: return set_err(h, B200ANN_ERR_ARG, "probe_gather: rows in flight per team must be 1, 2 or 4");
+  }
+#undef PROBE_CASE
+  h->launches++;
+  CU_CHECK(h, cudaGetLastError());
+  return 0;
+}
+}  // namespace
+
+int launch_gather_probe(b200ann_handle *h, const b200ann_index *ix, uint64_t rows, int inflight, int wpb, int bpsm,
+                        uint32_t seed, float *sink) {
+  const int nch = (int)((ix->dim + 3) / 4);
+  if (wpb < 1 || wpb > 8 || bpsm < 1 || bpsm > 32) return set_err(h, B200ANN_ERR_ARG, "probe_gather: warps per block in [1,8], blocks per SM in [1,32]");
+  if (nch <= 8) return probe_launch<8, 1>(h, ix, rows, inflight, wpb, bpsm, seed, sink);
+  if (nch <= 16) return probe_launch<8, 2>(h, ix, rows, inflight, wpb, bpsm, seed, sink);
+  if (nch <= 32) return probe_launch<8, 4>(h, ix, rows, inflight, wpb, bpsm, seed, sink);
+  if (nch <= 64) return probe_launch<8, 8>(h, ix, rows, inflight, wpb, bpsm, seed, sink);
+  if (nch <= 128) return probe_launch<32, 4>(h, ix, rows, inflight, wpb, bpsm, seed, sink);
+  if (nch <= 256) return probe_launch<32, 8>(h, ix, rows, inflight, wpb, bpsm, seed, sink);
+  return set_err(h, B200ANN_ERR_ARG, "probe_gather: dim > 1024 is not supported");
+}
 
 int launch_nsg_search(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
                       size_t K, size_t L, uint32_t seed, uint32_t *ids, float *dists, uint32_t *stats,

@@ -241,6 +241,23 @@ int b200ann_merge_topk(b200ann_handle_t h, const float *d /*[h|d]*/, const uint3
  * the next synchronizing call. Calls with any host buffer still synchronize. Default off. */
 int b200ann_set_async(b200ann_handle_t h, int on);
 
+/* Scheduling / tuning knobs of the graph-search kernels; none of them changes a result (-1 = leave as is).
+ * prefetch: while a node is expanded, pull the adjacency row of the next unexpanded pool entry into L2 (the reference's
+ *   _mm_prefetch hints, index_nsg.cpp:627-632, hnswalg.h:370-383); default on.
+ * visited_compact: 16-bit visited-set entries (twice the slots in the same shared memory) when n allows; default on.
+ * ctas_per_sm: cap on resident blocks per SM of the persistent kernel (0 = what occupancy allows). */
+int b200ann_set_search_options(b200ann_handle_t h, int prefetch, int visited_compact, int ctas_per_sm);
+/* Work order of the following b200ann_*_search calls on this handle whose nq == n: work item w processes query
+ * order[w] (a permutation of 0..n-1 in DEVICE memory, borrowed until reset with NULL). Queries are independent, so the
+ * order only decides which queries run at the same time (queries that walk the same region of the graph share L2). */
+int b200ann_set_query_order(b200ann_handle_t h, const uint32_t *order /*[d] or NULL*/, size_t n);
+/* Measurement aid: reads `rows` whole rows of the index at pseudo-random positions with the search kernels' own loads
+ * (16 B per lane, a team of lanes per row, `inflight` in {1,2,4} rows per team in flight) and returns the device time.
+ * rows * dim*4 / ms = what HBM delivers for graph search's access pattern on this index (the random-gather ceiling
+ * bench.py reports next to the streaming-copy peak). */
+int b200ann_probe_gather(b200ann_handle_t h, b200ann_index_t ix, uint64_t rows, int inflight, int warps_per_block,
+                         int blocks_per_sm, uint32_t seed, float *ms /*[h]*/);
+
 /* tuning knob: log2 of the per-query visited-set size in shared memory (default 10). */
 int b200ann_set_visited_bits(b200ann_handle_t h, int bits);
 /* same for the per-node searches of b200ann_nsg_link / b200ann_hnsw_build. 0 (default) = auto: 9 (dim <= 128) or 10 for

@@ -65,10 +65,13 @@ class HNSW_NSG {
   }
 
   // :72-74 -> IndexNSG::Build (hnsw_nsg/src/index_nsg.cpp): "L", "R", "C", "nn_graph_path" (efanna .graph file).
-  // The NSG is built over the vectors the HNSW part holds (the same rows in the same order in every driver).
+  // The NSG is built over the vectors the HNSW part holds, renumbered so that internal id == label == row of `data`
+  // (the reference's driver adds points under omp parallel for, so arrival order is not row order).
   void Build_NSG(const float *data, Parameters &parameters) {
-    (void)data;
+    (void)data;  // == the rows addPoint copied, in label order after the renumbering below
     hnsw_.build();
+    hnsw_.relabel_to_labels();  // NSG ids are rows of `data` = labels (index_hnsw_nsg.h:145-150): internal id := label
+    checked_gen_ = hnsw_.generation();
     std::string path = parameters.template Get<std::string>("nn_graph_path");
     unsigned L = parameters.template Get<unsigned>("L"), R = parameters.template Get<unsigned>("R"),
              C = parameters.template Get<unsigned>("C");
@@ -154,6 +157,10 @@ class HNSW_NSG {
   // both graphs live in ONE device index; re-install the NSG when the HNSW part rebuilt its index
   void install() {
     hnsw_.build();
+    if (hnsw_.generation() != checked_gen_) {  // e.g. a reference-written file whose points were added in parallel
+      hnsw_.relabel_to_labels();
+      checked_gen_ = hnsw_.generation();
+    }
     b200ann_index_t ix = hnsw_.device_index();
     if (!ix) throw std::runtime_error("HNSW_NSG: empty index");
     if (hnsw_.generation() == installed_gen_) return;
@@ -166,6 +173,7 @@ class HNSW_NSG {
   size_t gs_ = 1;
   unsigned ep_ = 0, width_ = 0;
   size_t installed_gen_ = (size_t)-1;  // generation of the HNSW part's device index that holds the NSG graph
+  size_t checked_gen_ = (size_t)-1;    // generation whose internal ids were checked / renumbered to equal the labels
 };
 
 }  // namespace hnsw_nsg

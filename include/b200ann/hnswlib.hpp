@@ -434,16 +434,31 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     rd(in, offsetLevel0); rd(in, max_elements_); rd(in, cur_element_count); rd(in, size_data_per_element);
     rd(in, label_offset); rd(in, offsetData); rd(in, maxlevel_); rd(in, enterpoint_node_); rd(in, maxM_); rd(in, maxM0_);
     rd(in, M_); rd(in, mult_); rd(in, ef_construction_);
+    if (!in) throw std::runtime_error("Index seems to be corrupted or unsupported");
     if (max_elements_i > max_elements_) max_elements_ = max_elements_i;
-    if ((label_offset - offsetData) / sizeof(float) != dim_) throw std::runtime_error("index file dimension does not match the space");
+    if (label_offset < offsetData || (label_offset - offsetData) / sizeof(float) != dim_) throw std::runtime_error("index file dimension does not match the space");
     const size_t n = cur_element_count;
+    // the layout the reference writes (hnswalg.h:116-123) and the size check of its loader (:740-760)
+    if (maxM0_ == 0 || maxM_ == 0 || maxM0_ > (1u << 20) || maxM_ > (1u << 20) || n > max_elements_ || offsetLevel0 != 0 ||
+        offsetData != maxM0_ * 4 + 4 || size_data_per_element != label_offset + sizeof(labeltype) || (n > 0 && enterpoint_node_ >= n))
+      throw std::runtime_error("Index seems to be corrupted or unsupported");
+    {
+      const std::streampos here = in.tellg();
+      in.seekg(0, std::ios::end);
+      const std::streampos total = in.tellg();
+      in.seekg(here);
+      if ((unsigned long long)(total - here) < (unsigned long long)n * size_data_per_element + (unsigned long long)n * 4)
+        throw std::runtime_error("Index seems to be corrupted or unsupported");
+    }
     std::vector<char> blob(n * size_data_per_element);
     in.read(blob.data(), (std::streamsize)blob.size());
     vec_.resize(n * dim_); labels_.resize(n); links0_.assign(n * maxM0_, B200ANN_INVALID);
     deleted_.assign(n, 0); num_deleted_ = 0; deleted_set_.clear();
+    label_lookup_.clear();
     for (size_t i = 0; i < n; i++) {
       const char *row = blob.data() + i * size_data_per_element;
       unsigned short cnt = *(const unsigned short *)(row + offsetLevel0);
+      if (cnt > maxM0_) throw std::runtime_error("Index seems to be corrupted or unsupported");
       if (*(const unsigned char *)(row + offsetLevel0 + 2) & DELETE_MARK) {  // :811-815
         deleted_[i] = 1; num_deleted_++;
         if (allow_replace_deleted_) deleted_set_.insert((tableint)i);
@@ -460,20 +475,25 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     for (size_t i = 0; i < n; i++) {
       unsigned int sz;
       rd(in, sz);
+      if (!in) throw std::runtime_error("Index seems to be corrupted or unsupported");
       if (!sz) continue;
+      if (sz % slpe != 0 || sz / slpe > 64) throw std::runtime_error("Index seems to be corrupted or unsupported");
       int lv = (int)(sz / slpe);
       element_levels_[i] = lv;
       upper_ptr_[i] = (uint32_t)(upper_links_.size() / maxM_);
       std::vector<char> ll(sz);
       in.read(ll.data(), sz);
+      if (!in) throw std::runtime_error("Index seems to be corrupted or unsupported");
       for (int l = 0; l < lv; l++) {
         const char *p = ll.data() + (size_t)l * slpe;
         unsigned short cnt = *(const unsigned short *)p;
+        if (cnt > maxM_) throw std::runtime_error("Index seems to be corrupted or unsupported");
         size_t base = upper_links_.size();
         upper_links_.resize(base + maxM_, B200ANN_INVALID);
         std::memcpy(&upper_links_[base], p + 4, (size_t)cnt * 4);
       }
     }
+    dirty_ = false;
     upload();
   }
 
@@ -606,6 +626,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     std::vector<uint64_t> lab(nq * k);
     std::unique_lock<std::mutex> lock(mu_);
     build_locked(nullptr);
+    if (!ix_) throw std::runtime_error("HierarchicalNSW::searchKnnBatch: the index is empty");
     if (!num_deleted_ && !isIdAllowed) {  // :1306 bare_bone_search
       detail::check(gpu_.h, b200ann_hnsw_search(gpu_.h, ix_, queries, nq, dim_, k, ef_, lab.data(), dists, nullptr), "HierarchicalNSW::searchKnn");
     } else {
@@ -639,6 +660,46 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     for (size_t i = 0; i < k; i++)
       if (lab[i] != ~(uint64_t)0) res.emplace(d[i], (labeltype)lab[i]);
     return res;
+  }
+
+  // b200ann extension for the hybrid index: renumber the elements so that internal id == label. The reference's
+  // hybrid enters its NSG at getExternalLabel(node) and the NSG's ids are rows of the caller's `data`
+  // (index_hnsw_nsg.h:145-150), whatever order addPoint ran in - its driver adds under `omp parallel for`
+  // (hnsw_nsg/tests/test_hnsw_nsg_search.cpp:331-333), so internal id != label there. One device index holds both
+  // graphs here, so its rows must be in label order. Throws unless the labels are a permutation of 0..n-1 (the
+  // reference would read `data` out of bounds). Returns false when nothing had to move.
+  bool relabel_to_labels() {
+    std::unique_lock<std::mutex> lock(mu_);
+    build_locked(nullptr);
+    const size_t n = cur_element_count;
+    bool identity = true;
+    std::vector<unsigned char> seen(n, 0);
+    for (size_t i = 0; i < n; i++) {
+      const size_t l = labels_[i];
+      if (l >= n || seen[l]) throw std::runtime_error("HNSW_NSG: labels must be the row numbers 0..n-1 of the NSG's base set");
+      seen[l] = 1;
+      identity &= l == i;
+    }
+    if (identity) return false;
+    auto map = [&](uint32_t v) { return v == B200ANN_INVALID ? v : (uint32_t)labels_[v]; };
+    std::vector<float> vec(vec_.size());
+    std::vector<uint32_t> l0(links0_.size()), up(n);
+    std::vector<int> lv(n);
+    std::vector<unsigned char> del(n);
+    for (size_t i = 0; i < n; i++) {
+      const size_t t = labels_[i];
+      std::memcpy(&vec[t * dim_], &vec_[i * dim_], dim_ * sizeof(float));
+      for (size_t j = 0; j < maxM0_; j++) l0[t * maxM0_ + j] = map(links0_[i * maxM0_ + j]);
+      lv[t] = element_levels_[i]; up[t] = upper_ptr_[i]; del[t] = deleted_[i];
+    }
+    for (auto &v : upper_links_) v = map(v);
+    std::set<tableint> ds;
+    for (tableint d : deleted_set_) ds.insert((tableint)labels_[d]);
+    enterpoint_node_ = (tableint)labels_[enterpoint_node_];
+    vec_.swap(vec); links0_.swap(l0); upper_ptr_.swap(up); element_levels_.swap(lv); deleted_.swap(del); deleted_set_.swap(ds);
+    for (size_t i = 0; i < n; i++) { labels_[i] = i; label_lookup_[i] = i; }
+    upload();
+    return true;
   }
 
   labeltype getExternalLabel(tableint internal_id) const { return labels_[internal_id]; }

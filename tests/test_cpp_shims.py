@@ -21,7 +21,8 @@ def _build(name, tmp):
     return exe
 
 
-@pytest.mark.parametrize("name", ["test_efanna_shim", "test_hnswlib_shim", "test_hybrid_shim", "test_l2spacei_shim", "test_replace_deleted"])
+@pytest.mark.parametrize("name", ["test_efanna_shim", "test_hnswlib_shim", "test_hybrid_shim", "test_l2spacei_shim", "test_replace_deleted",
+                                  "test_hybrid_order"])
 def test_shims_compile_and_fail_loudly_without_gpu(tmp_path, name):
     exe = _build(name, tmp_path)
     try:
@@ -119,3 +120,44 @@ def test_hybrid_shim_driver(tmp_path):
         hy = R.RefHybrid(base, prefix, 60)
         ids = hy.search(q, 10, 10, seed=1)
         assert R.recall(ids[:, :10], truth) > 0.9
+
+
+@pytest.mark.gpu
+def test_hybrid_order_driver(tmp_path):
+    """addPoint in shuffled / parallel order: the hybrid shim still answers in data-row ids"""
+    exe = _build("test_hybrid_order", tmp_path)
+    p = subprocess.run([exe, "build", str(tmp_path)], capture_output=True, text=True)
+    print(p.stdout, p.stderr)
+    assert p.returncode == 0 and "hybrid order ok" in p.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not R.have_ref(), reason="needs oracle/_ref to build a reference hybrid index with several threads")
+def test_hybrid_shim_loads_parallel_built_reference_index(tmp_path):
+    """the UNMODIFIED reference builds the pair of files with 4 addPoint threads (internal id != label); the shim's load
+    ctor answers with the same data-row ids the reference returns on those files"""
+    n, dim, nq, k, L = 5000, 32, 300, 10, 40
+    base = R.data_sift_like(n, dim, 3)      # integer-valued: every summation order is exact
+    q = R.data_sift_like(nq, dim, 4)
+    kpath = str(tmp_path / "k.graph")
+    knn, _ = R.orc_bf_knn(base, base, 41, R.L2_SCALAR)
+    knn = np.stack([row[row != i][:40] for i, row in enumerate(knn)]).astype(np.uint32)
+    R.write_knn_graph(kpath, knn)
+    prefix = str(tmp_path / "refhy")
+    R.ref_hybrid_build(base, kpath, 40, 30, 300, 16, 100, prefix, seed=1, threads=4)
+    Hb = R.parse_hnsw(prefix + "_hnsw.bin")
+    assert (Hb["labels"] != np.arange(n)).any(), "the parallel build happened to add in order; nothing is tested"
+    hy = R.RefHybrid(base, prefix, L)
+    want = hy.search(q, k, k, seed=1)
+    base.tofile(str(tmp_path / "base.f32")); q.tofile(str(tmp_path / "q.f32"))
+    exe = _build("test_hybrid_order", tmp_path)
+    out = str(tmp_path / "ids.u32")
+    p = subprocess.run([exe, "load", prefix, str(tmp_path / "base.f32"), str(n), str(dim), str(tmp_path / "q.f32"), str(nq),
+                        str(L), str(k), out], capture_output=True, text=True)
+    print(p.stdout, p.stderr)
+    assert p.returncode == 0
+    got = np.fromfile(out, np.uint32).reshape(nq, k)
+    truth, _ = R.orc_bf_knn(base, q, k, R.L2_SCALAR)
+    assert abs(R.recall(got, truth) - R.recall(want[:, :k], truth)) <= 0.005
+    same = np.mean([set(a.tolist()) == set(b.tolist()) for a, b in zip(got, want[:, :k])])
+    assert same > 0.97, same

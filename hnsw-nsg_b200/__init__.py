@@ -70,6 +70,8 @@ _lib.b200ann_cluster_search.argtypes = [_vp, _vp, _vp, _sz, _vp, _vp, _vp, _sz, 
 _lib.b200ann_knn_last_stats.argtypes = [_vp, _vp]
 _lib.b200ann_set_search_options.argtypes = [_vp, C.c_int, C.c_int, C.c_int]
 _lib.b200ann_set_query_order.argtypes = [_vp, _vp, _sz]
+_lib.b200ann_set_search_kernel.argtypes = [_vp, C.c_int, C.c_int, C.c_int]
+_lib.b200ann_set_id_base.argtypes = [_vp, _u32]
 _lib.b200ann_probe_gather.argtypes = [_vp, _vp, C.c_uint64, C.c_int, C.c_int, C.c_int, _u32, C.POINTER(C.c_float)]
 _lib.b200ann_nsg_finish.argtypes = [_vp, _vp, _vp, _vp, _sz, _u32, _sz, _u32, _sz, C.POINTER(_u32)]
 
@@ -83,7 +85,7 @@ EXPORTS = [
     "b200ann_nsg_interinsert", "b200ann_nsg_finish", "b200ann_merge_topk", "b200ann_nsg_search_from",
     "b200ann_hybrid_search", "b200ann_set_knn_mode", "b200ann_knn_last_stats", "b200ann_nndescent",
     "b200ann_hnsw_build", "b200ann_index_hnsw_shape", "b200ann_index_get_hnsw", "b200ann_nsg_search_clustered",
-    "b200ann_set_search_options", "b200ann_set_query_order", "b200ann_probe_gather",
+    "b200ann_set_search_options", "b200ann_set_search_kernel", "b200ann_set_id_base", "b200ann_set_query_order", "b200ann_probe_gather",
     "b200ann_set_async", "b200ann_cluster_search", "b200ann_bf_knn_u8", "b200ann_upload_u8", "b200ann_free_device",
 ]
 
@@ -166,6 +168,15 @@ class Handle:
     def set_search_options(self, prefetch=-1, visited_compact=-1, ctas_per_sm=-1):
         """scheduling knobs of the search kernels (never change results); -1 = leave as is"""
         self._check(_lib.b200ann_set_search_options(self._h, prefetch, visited_compact, ctas_per_sm))
+
+    def set_search_kernel(self, version=-1, ring_stages=-1, mode=-1):
+        """version 2 = TMA row ring + register pool (default), 1 = round-1 kernel; mode 0 auto / 1 query per warp /
+        2 query per block; results are identical"""
+        self._check(_lib.b200ann_set_search_kernel(self._h, version, ring_stages, mode))
+
+    def set_id_base(self, id_base):
+        """added to every valid id of the NSG-family searches (row shards: local -> global rows)"""
+        self._check(_lib.b200ann_set_id_base(self._h, id_base))
 
     def set_query_order(self, order):
         """order: device u32/i32 permutation (torch tensor / raw pointer) or None; see b200ann.h"""

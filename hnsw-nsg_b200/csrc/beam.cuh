@@ -42,6 +42,7 @@ struct SearchParams {
   const float *q; size_t qstride; uint32_t nq; uint32_t dim;
   uint32_t K, L, seed; int hbits;
   uint32_t qidx_base;           // query index fed to the seed hash = qidx_base + query
+  uint32_t id_base;             // added to every valid result id (row shards: local -> global row numbers)
   int mode;                     // non-HNSW kernels: 0 = Search from ep, 2 = hybrid (HNSW descent, then
                                 // SearchFromEnterpoint), 3 = SearchFromEnterpoint from entry[query],
                                 // 4 = Search inside one cluster per query (block-diagonal graph):
@@ -57,6 +58,8 @@ struct SearchParams {
   int vis16;                    // visited set entries: 0 = u32 ids (2^hbits slots), 1 = u16 tags (2^(hbits+1) slots)
   int nbits;                    // vis16: ids are hashed as nbits-bit numbers (n <= 2^nbits)
   int prefetch;                 // 1: expand_all prefetches the adjacency row of the next unexpanded pool entry
+  uint32_t nst;                 // search core v2 (beam2.cuh): stages of the per-warp row ring
+  uint32_t q1;                  // search core v2: work items [0, q1) run one per warp, [q1, nq) one per block; work[0..1] = the two queues
 };
 
 __device__ __forceinline__ uint32_t mix32(uint32_t x) {

@@ -71,8 +71,13 @@ int b200ann_create(int device, b200ann_handle_t *out) {
   }
   cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device);
   if (const char *e = getenv("B200ANN_PERSISTENT")) h->persistent = atoi(e);  // tuning knob: 0 = one launch slot per query
+  if (const char *e = getenv("B200ANN_SEARCH_VERSION")) h->search_version = atoi(e);
+  if (const char *e = getenv("B200ANN_RING_STAGES")) h->ring_stages = atoi(e);
+  if (const char *e = getenv("B200ANN_SEARCH_MODE")) h->search_mode = atoi(e);
+  if (const char *e = getenv("B200ANN_SEARCH_TAIL")) h->search_tail = atoi(e);
   if (const char *e = getenv("B200ANN_SEARCH_PREFETCH")) h->search_prefetch = atoi(e);
   if (const char *e = getenv("B200ANN_VISITED_COMPACT")) h->visited_compact = atoi(e);
+  if (const char *e = getenv("B200ANN_VISITED_BITS")) { h->visited_bits = atoi(e); h->visited_bits_auto = false; }
   if (const char *e = getenv("B200ANN_SEARCH_CTAS_PER_SM")) h->search_ctas_per_sm = atoi(e);
   {  // keep the stream-ordered scratch pool mapped between calls (default: released at every synchronize)
     cudaMemPool_t pool;
@@ -105,8 +110,9 @@ float b200ann_last_kernel_ms(b200ann_handle_t h) { return h ? h->last_ms : 0.f; 
 
 int b200ann_set_visited_bits(b200ann_handle_t h, int bits) {
   if (!h) return B200ANN_ERR_ARG;
-  if (bits < 5 || bits > 14) return set_err(h, B200ANN_ERR_ARG, "visited_bits must be in [5,14]");
-  h->visited_bits = bits;
+  if (bits == 0) { h->visited_bits = 10; h->visited_bits_auto = true; return 0; }
+  if (bits < 5 || bits > 14) return set_err(h, B200ANN_ERR_ARG, "visited_bits must be 0 (auto) or in [5,14]");
+  h->visited_bits = bits; h->visited_bits_auto = false;
   return 0;
 }
 
@@ -115,6 +121,29 @@ int b200ann_set_search_options(b200ann_handle_t h, int prefetch, int visited_com
   if (prefetch >= 0) h->search_prefetch = prefetch != 0;
   if (visited_compact >= 0) h->visited_compact = visited_compact != 0;
   if (ctas_per_sm >= 0) h->search_ctas_per_sm = ctas_per_sm;
+  return 0;
+}
+
+int b200ann_set_search_kernel(b200ann_handle_t h, int version, int ring_stages, int mode) {
+  if (!h) return B200ANN_ERR_ARG;
+  if (mode >= 0) {
+    if (mode > 2) return set_err(h, B200ANN_ERR_ARG, "set_search_kernel: mode must be 0 (auto), 1 (query per warp) or 2 (query per block)");
+    h->search_mode = mode;
+  }
+  if (version >= 0) {
+    if (version != 1 && version != 2) return set_err(h, B200ANN_ERR_ARG, "set_search_kernel: version must be 1 or 2");
+    h->search_version = version;
+  }
+  if (ring_stages >= 0) {
+    if (ring_stages > 8) return set_err(h, B200ANN_ERR_ARG, "set_search_kernel: ring_stages must be in [0,8]");
+    h->ring_stages = ring_stages;
+  }
+  return 0;
+}
+
+int b200ann_set_id_base(b200ann_handle_t h, uint32_t id_base) {
+  if (!h) return B200ANN_ERR_ARG;
+  h->id_base = id_base;
   return 0;
 }
 

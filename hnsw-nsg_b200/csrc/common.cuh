@@ -18,6 +18,7 @@ struct b200ann_handle {
   uint64_t launches = 0;
   float last_ms = 0.f;
   int visited_bits = 10;
+  bool visited_bits_auto = true;  // search v2 sizes the table itself until b200ann_set_visited_bits is called (0 = auto again)
   int link_visited_bits = 0;    // 0 = auto. NSG Link is occupancy-bound by shared memory: 1M x 128 K=200 L=40 C=500 takes
                                 // 1.45 / 1.30 / 1.23 / 1.28 s with 2^11 / 2^10 / 2^9 / 2^8 slots (more warps per SM against more
                                 // re-evaluations); at dim 960 2^10 wins. auto = 2^9 for dim <= 128, else 2^10; HNSW build 2^11
@@ -30,7 +31,13 @@ struct b200ann_handle {
   const uint32_t *query_order = nullptr;  // b200ann_set_query_order: device permutation of the next search's work items
   size_t query_order_n = 0;
   int search_prefetch = 1;   // beam.cuh prefetch_next_row (B200ANN_SEARCH_PREFETCH=0 turns it off for A/B runs)
-  int visited_compact = 1;   // 16-bit visited-set entries when n allows (B200ANN_VISITED_COMPACT=0: 32-bit ids)
+  int visited_compact = 0;   // 1: 16-bit visited-set entries when n allows - twice the slots in the same shared memory, but ~3x the
+                             // instructions per probe; measured slower than 32-bit ids with a few % more re-evaluations (B200ANN_VISITED_COMPACT)
+  int search_version = 2;    // 2: beam2.cuh (TMA row ring, register pool); 1: round-1 kernel (B200ANN_SEARCH_VERSION)
+  int search_mode = 0;       // v2: 0 = auto split between one query per warp / per block, 1 = per warp only, 2 = per block only (B200ANN_SEARCH_MODE)
+  int search_tail = -1;      // v2 experiments: queries run one per block at the end of a batch (-1 = the launcher's rule; B200ANN_SEARCH_TAIL)
+  int ring_stages = 0;       // v2: stages of the per-warp row ring (0 = default 3; B200ANN_RING_STAGES)
+  uint32_t id_base = 0;      // b200ann_set_id_base: added to every result id of the NSG-family searches (row shards)
   int search_ctas_per_sm = 0;  // cap on resident blocks per SM of the persistent search kernel (0 = occupancy limit)
   bool async_mode = false;   // b200ann_set_async: device-to-device search / merge calls do not synchronize the stream
 };

@@ -7,6 +7,10 @@
 
 using namespace beam;
 
+int launch_search2_pr0(b200ann_handle *h, const SearchParams &p, bool ip, bool hnsw);
+int launch_search2_pr1(b200ann_handle *h, const SearchParams &p, bool ip, bool hnsw);
+int launch_search2_pr2(b200ann_handle *h, const SearchParams &p, bool ip, bool hnsw);
+
 namespace {
 
 constexpr int WARPS = 4;
@@ -71,7 +75,7 @@ __global__ void __launch_bounds__(WARPS * 32, (NCH <= 4 ? 6 : 1)) beam_search_ke
       if (HNSW) {
         p.labels_out[(size_t)qi * p.K + i] = ok ? (p.labels ? __ldg(p.labels + id) : (uint64_t)id) : ~(uint64_t)0;
       } else {
-        p.ids[(size_t)qi * p.K + i] = id;
+        p.ids[(size_t)qi * p.K + i] = id + (ok ? p.id_base : 0u);
       }
       if (p.dists) p.dists[(size_t)qi * p.K + i] = d;
     }
@@ -86,12 +90,6 @@ __global__ void __launch_bounds__(WARPS * 32, (NCH <= 4 ? 6 : 1)) beam_search_ke
 template <int TEAM, int NCH, bool IP, bool HNSW>
 int launch_t(b200ann_handle *h, const SearchParams &p0) {
   SearchParams p = p0;
-  p.order = (h->query_order && h->query_order_n == p.nq) ? h->query_order : nullptr;
-  p.prefetch = h->search_prefetch;
-  p.nbits = 1;
-  while (p.nbits < 32 && (1ull << p.nbits) < (unsigned long long)p.n) p.nbits++;
-  if (p.nbits < p.hbits + 1) p.nbits = p.hbits + 1;
-  p.vis16 = (h->visited_compact && p.nbits - (p.hbits + 1) <= 12) ? 1 : 0;
   size_t smem = (size_t)WARPS * smem_words(p.pool_cap, p.cand_cap, p.hbits) * 4;
   if (smem > 227 * 1024) return set_err(h, B200ANN_ERR_ARG, "search: L / degree / visited_bits need more than 227 KB shared memory per block");
   auto kern = beam_search_kernel<TEAM, NCH, IP, HNSW>;
@@ -104,7 +102,7 @@ int launch_t(b200ann_handle *h, const SearchParams &p0) {
     if (h->search_ctas_per_sm > 0 && h->search_ctas_per_sm < occ) occ = h->search_ctas_per_sm;
     size_t wave = (size_t)(occ > 0 ? occ : 1) * (size_t)h->sm_count;
     if (blocks > wave) {  // more than one wave of blocks: pull queries from a queue instead
-      if (!h->work) CU_CHECK(h, cudaMalloc((void **)&h->work, sizeof(uint32_t)));
+      if (!h->work) CU_CHECK(h, cudaMalloc((void **)&h->work, 2 * sizeof(uint32_t)));
       CU_CHECK(h, cudaMemsetAsync(h->work, 0, sizeof(uint32_t), h->stream));
       p.work = h->work;
       blocks = wave;
@@ -118,7 +116,20 @@ int launch_t(b200ann_handle *h, const SearchParams &p0) {
 }
 
 template <bool IP, bool HNSW>
-int launch_dim(b200ann_handle *h, const SearchParams &p) {
+int launch_dim(b200ann_handle *h, const SearchParams &p0) {
+  SearchParams p = p0;
+  p.order = (h->query_order && h->query_order_n == p.nq) ? h->query_order : nullptr;
+  p.prefetch = h->search_prefetch;
+  p.id_base = h->id_base;
+  p.nbits = 1;
+  while (p.nbits < 32 && (1ull << p.nbits) < (unsigned long long)p.n) p.nbits++;
+  if (p.nbits < p.hbits + 1) p.nbits = p.hbits + 1;
+  p.vis16 = (h->visited_compact && p.nbits - (p.hbits + 1) <= 12) ? 1 : 0;
+  if (h->search_version != 1) {  // v2: TMA row ring + register pool (beam2.cuh); B200ANN_SEARCH_VERSION=1 keeps v1 for A/B runs
+    if (p.L <= 32) return launch_search2_pr1(h, p, IP, HNSW);
+    if (p.L <= 64) return launch_search2_pr2(h, p, IP, HNSW);
+    return launch_search2_pr0(h, p, IP, HNSW);
+  }
   int nch = p.nch;
   if (nch <= 8) return launch_t<8, 1, IP, HNSW>(h, p);
   if (nch <= 16) return launch_t<8, 2, IP, HNSW>(h, p);

@@ -244,9 +244,21 @@ int b200ann_set_async(b200ann_handle_t h, int on);
 /* Scheduling / tuning knobs of the graph-search kernels; none of them changes a result (-1 = leave as is).
  * prefetch: while a node is expanded, pull the adjacency row of the next unexpanded pool entry into L2 (the reference's
  *   _mm_prefetch hints, index_nsg.cpp:627-632, hnswalg.h:370-383); default on.
- * visited_compact: 16-bit visited-set entries (twice the slots in the same shared memory) when n allows; default on.
+ * visited_compact: 16-bit visited-set entries (twice the slots in the same shared memory) when n allows; default off
+ *   (a probe costs ~3x the instructions of a 32-bit atomicCAS; measured slower despite fewer re-evaluations).
  * ctas_per_sm: cap on resident blocks per SM of the persistent kernel (0 = what occupancy allows). */
 int b200ann_set_search_options(b200ann_handle_t h, int prefetch, int visited_compact, int ctas_per_sm);
+/* Which graph-search kernel runs (results are bit-identical): version 2 (default) = rows through the TMA bulk-copy
+ * engine into a per-warp shared-memory ring of `ring_stages` stages (0 = default 1) with the pool in registers for
+ * L <= 64 (csrc/beam2.cuh); version 1 = the round-1 register-load kernel (csrc/beam.cuh), kept for A/B measurements.
+ * mode (version 2): 0 (default) = full rounds of the resident warps run one query per warp, a remainder of at most one
+ * round of blocks runs one query per block of 4 warps; 1 = one query per warp only; 2 = one query per block only.
+ * -1 leaves a value as it is. */
+int b200ann_set_search_kernel(b200ann_handle_t h, int version, int ring_stages, int mode);
+/* Row shards (multi-GPU search): id_base is added to every valid id the NSG-family searches of this handle write
+ * (b200ann_nsg_search, _nsg_search_from, _hybrid_search, _nsg_search_clustered), i.e. local row -> global row number
+ * in the kernel's own epilogue. Default 0. */
+int b200ann_set_id_base(b200ann_handle_t h, uint32_t id_base);
 /* Work order of the following b200ann_*_search calls on this handle whose nq == n: work item w processes query
  * order[w] (a permutation of 0..n-1 in DEVICE memory, borrowed until reset with NULL). Queries are independent, so the
  * order only decides which queries run at the same time (queries that walk the same region of the graph share L2). */
@@ -258,7 +270,9 @@ int b200ann_set_query_order(b200ann_handle_t h, const uint32_t *order /*[d] or N
 int b200ann_probe_gather(b200ann_handle_t h, b200ann_index_t ix, uint64_t rows, int inflight, int warps_per_block,
                          int blocks_per_sm, uint32_t seed, float *ms /*[h]*/);
 
-/* tuning knob: log2 of the per-query visited-set size in shared memory (default 10). */
+/* tuning knob: log2 of the per-query visited-set size in shared-memory words. 0 (default) = auto: search kernel v2
+ * takes 2^9 .. 2^11, whatever keeps the most warps resident; v1 and the build kernels use 2^10. Results never depend
+ * on it (a forgotten node is re-evaluated and rejected again). */
 int b200ann_set_visited_bits(b200ann_handle_t h, int bits);
 /* same for the per-node searches of b200ann_nsg_link / b200ann_hnsw_build. 0 (default) = auto: 9 (dim <= 128) or 10 for
  * NSG Link, which is bound by shared-memory occupancy, 11 for the HNSW build. Results do not depend on it. */

@@ -67,7 +67,7 @@ def main():
         print("ncu target launches done: L=%d, %.3f ms" % (L, h.last_kernel_ms), flush=True)
         return
 
-    def run(tag, reps=7, **kw):
+    def run(tag, reps=5, **kw):
         ix.nsg_search_raw(q_dev, nq, dim, 10, L, 1, ids_dev, None, st_dev)
         ids = ids_dev.cpu().numpy().view(np.uint32).copy()
         st = st_dev.cpu().numpy().astype(np.int64)
@@ -81,74 +81,58 @@ def main():
         res["runs"].append(r)
         return ids
 
-    # ---- baseline = round-1 configuration
+    if args.only == "quick":
+        for stages in (1, 2):
+            h.set_search_kernel(version=2, ring_stages=stages, mode=0)
+            run("v2 quick", stages=stages)
+        return
+    # ---- baseline = round-1 kernel and configuration
+    h.set_search_kernel(version=1)
     h.set_search_options(prefetch=0, visited_compact=0, ctas_per_sm=0)
     h.set_visited_bits(10)
-    ref_ids = run("r1_baseline: hbits10 u32, no prefetch")
+    ref_ids = run("v1 r1_baseline: hbits10 u32, no prefetch")
     res["recall"] = recall(ref_ids)
     print("L=%d recall=%.4f" % (L, res["recall"]), flush=True)
 
     def check(ids, tag):
         assert (ids == ref_ids).all(), "ids changed under " + tag
 
-    # ---- visited table sweep (exact count = the largest table)
-    for bits in (9, 10, 11, 12, 13):
-        for comp in (0, 1):
-            h.set_visited_bits(bits)
-            h.set_search_options(prefetch=0, visited_compact=comp)
-            check(run("visited", bits=bits, compact=comp), "visited %d/%d" % (bits, comp))
-    # ---- prefetch
-    for bits, comp in ((10, 0), (10, 1), (11, 1)):
+    # ---- v2: mode x ring depth
+    h.set_visited_bits(0)
+    h.set_search_options(prefetch=0, visited_compact=1)
+    for mode in (1, 0, 2):
+        for stages in (1, 2):
+            h.set_search_kernel(version=2, ring_stages=stages, mode=mode)
+            check(run("v2", stages=stages, mode=mode), "v2 %d %d" % (stages, mode))
+    for comp, bits in ((0, 0), (1, 9), (0, 9), (0, 10)):
+        h.set_search_kernel(version=2, ring_stages=1, mode=0)
         h.set_visited_bits(bits)
-        h.set_search_options(prefetch=1, visited_compact=comp)
-        check(run("prefetch", bits=bits, compact=comp, prefetch=1), "prefetch")
-    # ---- resident blocks per SM
-    h.set_visited_bits(10)
-    for c in (2, 3, 4, 5, 6):
-        h.set_search_options(prefetch=1, visited_compact=1, ctas_per_sm=c)
-        check(run("ctas_per_sm", ctas=c), "ctas %d" % c)
-    h.set_search_options(ctas_per_sm=0)
-    # ---- query order: queries sorted by their nearest pivot (P random base rows)
-    rng = np.random.default_rng(5)
-    for P in (16, 64, 256, 1024, 4096):
-        piv = base[rng.choice(n, P, replace=False)]
-        pix = B.Index(h, piv, B.L2)
-        near, _ = pix.bf_knn(q, 2 if P > 2 else 1)
-        pix.close()
-        key = near[:, 0].astype(np.int64) * P + near[:, 1].astype(np.int64)
-        order = torch.from_numpy(np.argsort(key, kind="stable").astype(np.int32)).cuda()
-        h.set_query_order(order)
-        for c in (0, 3):
-            h.set_search_options(ctas_per_sm=c)
-            check(run("order_by_pivot", P=P, ctas=c), "order P=%d" % P)
-        h.set_query_order(None)
-    h.set_search_options(ctas_per_sm=0)
-    # ---- order by the exact nearest neighbour's position in a pivot ordering of the BASE (upper bound of locality)
-    order = torch.from_numpy(np.argsort(gt[:, 0], kind="stable").astype(np.int32)).cuda()
-    h.set_query_order(order)
-    check(run("order_by_gt_id"), "order gt")
-    h.set_query_order(None)
-    # ---- random-gather probe
-    res["probe"] = []
-    rows = 16 << 20
-    for infl in (1, 2, 4):
-        for bps in (4, 8):
-            gbs, ms = ix.probe_gather(rows, infl, 8, bps)
-            gbs, ms = ix.probe_gather(rows, infl, 8, bps)
-            r = dict(dim=dim, inflight=infl, blocks_per_sm=bps, warps_per_block=8, GBps=gbs, ms=ms)
-            print(json.dumps(r), flush=True)
-            res["probe"].append(r)
+        h.set_search_options(visited_compact=comp)
+        check(run("v2", stages=1, mode=0, bits=bits, compact=comp), "v2 table")
+    h.set_visited_bits(0)
+    h.set_search_options(prefetch=1, visited_compact=1)
+    check(run("v2", stages=1, mode=0, prefetch=1), "v2 prefetch")
+    h.set_search_options(prefetch=0)
+    # ---- batch size: the tail of a batch (slots = 148 SMs x 8 blocks x 4 warps = 4736)
+    nq_keep = nq
+    for nq2 in (1184, 2368, 4736, 5920, 9472, 10000):
+        nq = nq2
+        for ver, mode in ((1, 0), (2, 1), (2, 0), (2, 2)):
+            h.set_search_kernel(version=ver, ring_stages=1, mode=mode)
+            run("nq sweep", ver=ver, mode=mode, nq=nq2)
+    nq = nq_keep
+    h.set_search_kernel(version=2, ring_stages=1, mode=0)
+    # ---- other L (pool forms) v1 vs v2
+    for L2 in (16, 48, 100):
+        L_keep = L
+        L = L2
+        h.set_search_kernel(version=1)
+        a = run("v1 L", L=L2)
+        h.set_search_kernel(version=2, ring_stages=0)
+        b_ = run("v2 L", L=L2)
+        assert (a == b_).all(), "v1 != v2 at L=%d" % L2
+        L = L_keep
     ix.close()
-    for d2, n2 in ((96, 1250000), (960, 250000), (32, 4000000)):
-        b2 = np.zeros((n2, d2), np.float32)
-        ix2 = B.Index(h, b2, B.L2)
-        for infl in (2, 4):
-            gbs, ms = ix2.probe_gather((8 << 30) // (d2 * 4), infl, 8, 8)
-            gbs, ms = ix2.probe_gather((8 << 30) // (d2 * 4), infl, 8, 8)
-            r = dict(dim=d2, n=n2, inflight=infl, blocks_per_sm=8, warps_per_block=8, GBps=gbs, ms=ms)
-            print(json.dumps(r), flush=True)
-            res["probe"].append(r)
-        ix2.close()
     os.makedirs(os.path.dirname(args.out), exist_ok=True)
     json.dump(res, open(args.out, "w"), indent=1)
 

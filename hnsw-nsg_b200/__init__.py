@@ -45,6 +45,7 @@ _lib.b200ann_index_get_graph.argtypes = [_vp, _vp, _sz, C.POINTER(C.c_uint32), C
 _lib.b200ann_index_set_hnsw.argtypes = [_vp, _vp, _sz, _vp, _vp, _vp, _sz, _sz, _vp, C.c_uint32, C.c_int]
 _lib.b200ann_bf_knn.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _vp, _vp]
 _lib.b200ann_knn_graph.argtypes = [_vp, _vp, _sz, _vp]
+_lib.b200ann_knn_graph_rows.argtypes = [_vp, _vp, _sz, _sz, _sz, _vp]
 _lib.b200ann_bf_knn_u8.argtypes = [_vp, _vp, _sz, _sz, _sz, _vp, _sz, _sz, _sz, _vp, _vp]
 _lib.b200ann_hnsw_build.argtypes = [_vp, _vp, _sz, _sz, C.c_uint32, _sz, _sz, _vp, _vp]
 _lib.b200ann_index_hnsw_shape.argtypes = [_vp, _vp]
@@ -63,6 +64,7 @@ _lib.b200ann_nsg_init_ep.argtypes = [_vp, _vp, _vp, _sz, _sz, _u32, _u32, C.POIN
 _lib.b200ann_nsg_link.argtypes = [_vp, _vp, _vp, _sz, _u32, _sz, _sz, _sz, _u32, _vp, _vp, _vp]
 _lib.b200ann_nsg_interinsert.argtypes = [_vp, _vp, _sz, _vp, _vp, C.POINTER(C.c_uint64)]
 _lib.b200ann_merge_topk.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _vp, _vp]
+_lib.b200ann_merge_topk_gathered.argtypes = [_vp, _vp, _sz, _sz, _sz, _sz, _sz, _vp, _vp]
 _lib.b200ann_set_knn_mode.argtypes = [_vp, C.c_int, C.c_int]
 _lib.b200ann_set_async.argtypes = [_vp, C.c_int]
 _lib.b200ann_cluster_search.argtypes = [_vp, _vp, _vp, _sz, _vp, _vp, _vp, _sz, _vp, _vp, _sz, _sz, _sz, _sz, _sz, _sz, _u32,
@@ -85,7 +87,7 @@ EXPORTS = [
     "b200ann_nsg_interinsert", "b200ann_nsg_finish", "b200ann_merge_topk", "b200ann_nsg_search_from",
     "b200ann_hybrid_search", "b200ann_set_knn_mode", "b200ann_knn_last_stats", "b200ann_nndescent",
     "b200ann_hnsw_build", "b200ann_index_hnsw_shape", "b200ann_index_get_hnsw", "b200ann_nsg_search_clustered",
-    "b200ann_set_search_options", "b200ann_set_search_kernel", "b200ann_set_id_base", "b200ann_set_query_order", "b200ann_probe_gather",
+    "b200ann_knn_graph_rows", "b200ann_merge_topk_gathered", "b200ann_set_search_options", "b200ann_set_search_kernel", "b200ann_set_id_base", "b200ann_set_query_order", "b200ann_probe_gather",
     "b200ann_set_async", "b200ann_cluster_search", "b200ann_bf_knn_u8", "b200ann_upload_u8", "b200ann_free_device",
 ]
 
@@ -200,6 +202,10 @@ class Handle:
     def merge_topk_raw(self, d, ids, parts, nq, k, kout, out_d, out_i):
         self._check(_lib.b200ann_merge_topk(self._h, _ptr(d), _ptr(ids), parts, nq, k, kout, _ptr(out_d), _ptr(out_i)))
 
+    def merge_topk_gathered(self, buf, world, lp, nq, k, kout, out_d, out_i):
+        """buf: device buffer filled by one all-gather of per-rank blocks [d: lp x nq x k][ids: lp x nq x k]"""
+        self._check(_lib.b200ann_merge_topk_gathered(self._h, _ptr(buf), world, lp, nq, k, kout, _ptr(out_d), _ptr(out_i)))
+
     def bf_knn_u8(self, base, q, k):
         """exact kNN over u8 rows with int squared-L2 (hnswlib L2SpaceI + BruteforceSearch<int>);
         base [n,dim], q [nq,dim] uint8 numpy -> (ids u32 [nq,k], dists i32 [nq,k])"""
@@ -282,6 +288,12 @@ class Index:
     def knn_graph(self, K):
         knn = np.empty((self.n, K), np.uint32)
         self.h._check(_lib.b200ann_knn_graph(self.h._h, self._ix, K, _ptr(knn)))
+        return knn
+
+    def knn_graph_rows(self, row0, nrows, K, out=None):
+        """rows [row0, row0+nrows) of the exact kNN graph; out: optional device buffer [nrows,K]"""
+        knn = out if out is not None else np.empty((nrows, K), np.uint32)
+        self.h._check(_lib.b200ann_knn_graph_rows(self.h._h, self._ix, row0, nrows, K, _ptr(knn)))
         return knn
 
     def knn_graph_raw(self, K, out):

@@ -23,6 +23,7 @@ struct BfParams {
   const float *q; size_t qstride; uint32_t nq;
   uint32_t k; int ip; int exclude_self;
   const uint32_t *self_ids;  // optional: the id query i must skip (exclude_self with gathered queries)
+  uint32_t self_base;        // added to the id to skip (queries = a block of base rows starting at self_base)
   uint32_t splits;          // base range splits (grid.y)
   float *list_d[2]; uint32_t *list_i[2];  // [splits, nq, k] ping-pong lists
   uint8_t *cur;             // [splits, nq] which list is current at exit
@@ -189,7 +190,7 @@ __global__ void __launch_bounds__(NT, 2) bf_knn_kernel(const BfParams p) {
 #pragma unroll
     for (int i = 0; i < 4; i++) {
       const uint32_t qg = q0 + ty * 4 + i;
-      self_id[i] = (p.self_ids && qg < p.nq) ? __ldg(p.self_ids + qg) : qg;
+      self_id[i] = ((p.self_ids && qg < p.nq) ? __ldg(p.self_ids + qg) : qg) + p.self_base;
     }
     // distances in place; a tile in which no lane of the warp beats its query's current k-th (thresholds only
     // tighten) skips the insertion pass altogether
@@ -288,12 +289,12 @@ __global__ void bf_finalize_kernel(const BfParams p, uint32_t *out_i, float *out
 }  // namespace
 
 int launch_bf_knn(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
-                  size_t k, bool exclude_self, uint32_t *ids, float *dists, const uint32_t *self_ids) {
+                  size_t k, bool exclude_self, uint32_t *ids, float *dists, const uint32_t *self_ids, uint32_t self_base) {
   if (nq == 0) return 0;
   BfParams p = {};
   p.base = ix->vec; p.bstride = ix->stride; p.n = (uint32_t)ix->n; p.dim = (uint32_t)ix->dim;
   p.q = q; p.qstride = qstride; p.nq = (uint32_t)nq; p.k = (uint32_t)k;
-  p.ip = ix->metric == B200ANN_IP; p.exclude_self = exclude_self; p.self_ids = self_ids;
+  p.ip = ix->metric == B200ANN_IP; p.exclude_self = exclude_self; p.self_ids = self_ids; p.self_base = self_base;
   uint32_t qtiles = (uint32_t)((nq + QT - 1) / QT);
   // 2 CTAs are resident per SM. A grid slightly above a whole number of waves wastes most of the last one, and every
   // split pays its own top-k warm-up: pick the split count with the least time per CTA of useful work (bf_knn_u8.cu).

@@ -340,7 +340,7 @@ int b200ann_index_get_hnsw(b200ann_index_t ix, uint32_t *links0, int32_t *levels
 
 // tensor cores when the problem is big enough to fill them (or when forced), else the fp32 SIMT kernel
 static int knn_dispatch(b200ann_handle *h, b200ann_index *ix, const float *q, size_t nq, size_t qstride, size_t k,
-                        bool exclude_self, uint32_t *ids, float *dists) {
+                        bool exclude_self, uint32_t *ids, float *dists, uint32_t self_base = 0) {
   bool tcp = false;
   if (h->knn_mode == 2) {
     if (!knn_tc_supported(ix, nq, k)) return set_err(h, B200ANN_ERR_ARG, "knn: tensor path forced but unsupported (k > 1024, dim > 4096 or no driver entry point)");
@@ -349,8 +349,8 @@ static int knn_dispatch(b200ann_handle *h, b200ann_index *ix, const float *q, si
     tcp = knn_tc_supported(ix, nq, k) && ix->n >= 4096 && (double)nq * (double)ix->n >= (double)(1 << 24);
   }
   memset(h->knn_stats, 0, sizeof h->knn_stats);
-  if (tcp) return launch_knn_tc(h, ix, q, nq, qstride, k, exclude_self, ids, dists);
-  return launch_bf_knn(h, ix, q, nq, qstride, k, exclude_self, ids, dists);
+  if (tcp) return launch_knn_tc(h, ix, q, nq, qstride, k, exclude_self, ids, dists, self_base);
+  return launch_bf_knn(h, ix, q, nq, qstride, k, exclude_self, ids, dists, nullptr, self_base);
 }
 
 int b200ann_set_async(b200ann_handle_t h, int on) {
@@ -440,6 +440,22 @@ int b200ann_knn_graph(b200ann_handle_t h, b200ann_index_t ix, size_t K, uint32_t
   CU_CHECK(h, oi.stage(knn, ix->n * K, h->stream));
   CallTimer t(h);
   int rc = knn_dispatch(h, ix, ix->vec, ix->n, ix->stride, K, true, oi.d, nullptr);
+  t.stop();
+  if (rc) return rc;
+  CU_CHECK(h, oi.finish(h->stream));
+  CU_CHECK(h, t.sync());
+  return 0;
+}
+
+int b200ann_knn_graph_rows(b200ann_handle_t h, b200ann_index_t ix, size_t row0, size_t nrows, size_t K, uint32_t *knn) {
+  if (!h || !ix) return B200ANN_ERR_ARG;
+  if (!knn || K == 0 || K >= ix->n || row0 + nrows > ix->n) return set_err(h, B200ANN_ERR_ARG, "knn_graph_rows: need 0 < K < n and row0 + nrows <= n");
+  if (nrows == 0) return 0;
+  CU_CHECK(h, cudaSetDevice(h->device));
+  OutArg<uint32_t> oi;
+  CU_CHECK(h, oi.stage(knn, nrows * K, h->stream));
+  CallTimer t(h);
+  int rc = knn_dispatch(h, ix, ix->vec + row0 * ix->stride, nrows, ix->stride, K, true, oi.d, nullptr, (uint32_t)row0);
   t.stop();
   if (rc) return rc;
   CU_CHECK(h, oi.finish(h->stream));

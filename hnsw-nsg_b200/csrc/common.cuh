@@ -166,13 +166,14 @@ int launch_hnsw_search_filtered(b200ann_handle *h, const b200ann_index *ix, cons
 int launch_merge_topk(b200ann_handle *h, const float *d, const uint32_t *ids, size_t parts, size_t nq, size_t k, size_t kout,
                       float *out_d, uint32_t *out_i);
 int launch_bf_knn(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
-                  size_t k, bool exclude_self, uint32_t *ids, float *dists, const uint32_t *self_ids = nullptr);
+                  size_t k, bool exclude_self, uint32_t *ids, float *dists, const uint32_t *self_ids = nullptr,
+                  uint32_t self_base = 0);
 // u8 rows, integer squared L2 (bf_knn_u8.cu); device pointers only
 int launch_bf_knn_u8(b200ann_handle *h, const uint8_t *base, size_t n, size_t dim, size_t bstride, const uint8_t *q,
                      size_t nq, size_t qstride, size_t k, uint32_t *ids, int32_t *dists);
 // tensor-core path (knn_tc.cu); same contract. knn_dispatch picks the path from h->knn_mode.
 int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t nq, size_t qstride, size_t k,
-                  bool exclude_self, uint32_t *ids, float *dists);
+                  bool exclude_self, uint32_t *ids, float *dists, uint32_t self_base = 0);
 bool knn_tc_supported(const b200ann_index *ix, size_t nq, size_t k);
 void knn_tc_free(b200ann_index *ix);
 

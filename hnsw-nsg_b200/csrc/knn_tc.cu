@@ -141,7 +141,8 @@ __global__ void prep_kernel(const float *src, size_t sstride, uint32_t n, uint32
 // ---------------------------------------------------------------- sweep kernel
 struct SweepParams {
   uint32_t nq_rows;   // query rows of this launch
-  uint32_t q_row0;    // row of the query bf16 arrays the launch starts at (also the self id of local row 0)
+  uint32_t q_row0;    // row of the query bf16 arrays the launch starts at
+  uint32_t self_base; // exclude_self: query row i is base row self_base + i (0 when the queries are the whole base)
   uint32_t n;         // base rows
   uint32_t nkb;       // K-blocks per pass = dpad / 64
   uint32_t passes;    // 1 (bf16-exact data) or 3 (hi*hi + hi*lo + lo*hi)
@@ -409,7 +410,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap mA_hi, const __grid_constant__ 
     const int rowi = q * 32 + lane;  // row within the CTA
     const uint32_t row_local = blockIdx.x * BM + rowi;
     const bool row_valid = row_local < p.nq_rows;
-    const uint32_t self = p.exclude_self ? p.q_row0 + row_local : INVALID_ID;
+    const uint32_t self = p.exclude_self ? p.self_base + p.q_row0 + row_local : INVALID_ID;
     const size_t sr0 = (size_t)blockIdx.y * p.rows_pad + blockIdx.x * BM + q * 32;  // scratch row of lane 0
     float *cd = p.cand_d + (sr0 + lane) * p.cap;
     uint32_t *ci = p.cand_i + (sr0 + lane) * p.cap;
@@ -768,7 +769,7 @@ bool knn_tc_supported(const b200ann_index *ix, size_t nq, size_t k) {
 }
 
 int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t nq, size_t qstride, size_t k,
-                  bool exclude_self, uint32_t *ids, float *dists) {
+                  bool exclude_self, uint32_t *ids, float *dists, uint32_t self_base) {
   if (nq == 0) return 0;
   if (!knn_tc_supported(ix, nq, k)) return set_err(h, B200ANN_ERR_ARG, "knn (tensor path): unsupported k/dim or no cuTensorMapEncodeTiled");
   const size_t n = ix->n, dim = ix->dim;
@@ -784,10 +785,15 @@ int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t n
     ix->tc_inexact = b.inexact; ix->tc_ny_max = b.nmax;
   }
   Bf16Set qs;
-  const bool self_queries = (q == ix->vec && nq == n);
+  // queries that are rows of the index itself (the whole base, or a block of rows of it: b200ann_knn_graph_rows) use
+  // the cached bf16 copies
+  const bool self_queries = q >= ix->vec && q < ix->vec + n * ix->stride && qstride == ix->stride &&
+                            (size_t)(q - ix->vec) % ix->stride == 0 && (size_t)(q - ix->vec) / ix->stride + nq <= n;
   struct QGuard { Bf16Set *s; bool own; ~QGuard() { if (own) free_set(s); } } qguard{&qs, !self_queries};
   if (self_queries) {
-    qs.hi = ix->tc_hi; qs.lo = ix->tc_lo; qs.norms = ix->tc_norms; qs.inexact = ix->tc_inexact; qs.nmax = ix->tc_ny_max;
+    const size_t r0 = (size_t)(q - ix->vec) / ix->stride;
+    qs.hi = (char *)ix->tc_hi + r0 * dpad * 2; qs.lo = ix->tc_lo ? (char *)ix->tc_lo + r0 * dpad * 2 : nullptr;
+    qs.norms = ix->tc_norms + r0; qs.inexact = ix->tc_inexact; qs.nmax = ix->tc_ny_max;
   } else {
     int rc = prep_rows(h, q, qstride, nq, dim, dpad, &qs);
     if (rc) return rc;
@@ -867,7 +873,7 @@ int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t n
     tc::SweepParams sp = {};
     sp.nq_rows = rows; sp.q_row0 = (uint32_t)r0; sp.n = (uint32_t)n; sp.nkb = nkb; sp.passes = passes; sp.a_resident = a_res; sp.a_slots = a_slots; sp.nstage = nstage;
     sp.ntiles = ntiles; sp.tiles_per_split = tiles_per_split; sp.ny = ip ? nullptr : ix->tc_norms;
-    sp.exclude_self = exclude_self; sp.Kp = Kp; sp.cap = cap; sp.rows_pad = rows_pad;
+    sp.exclude_self = exclude_self; sp.self_base = self_base; sp.Kp = Kp; sp.cap = cap; sp.rows_pad = rows_pad;
     sp.cand_d = cand_d.p; sp.cand_i = cand_i.p; sp.cand_n = cand_n.p; sp.cand_tau = cand_tau.p;
     sp.prof = want_prof ? prof.p : nullptr;
     tc::sweep_kernel<<<dim3(mtiles, splits), tc::NTHREADS, sweep_smem, h->stream>>>(mA_hi, mA_lo, mB_hi, mB_lo, sp);
@@ -909,7 +915,7 @@ int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t n
     size_t tot = (size_t)nf * dim;
     tc::gather_rows_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, h->stream>>>(fail.p + 1, nf, q, qstride, (uint32_t)dim, fq.p);
     h->launches++;
-    int rc = launch_bf_knn(h, ix, fq.p, nf, dim, k, exclude_self, fi.p, fd.p, fail.p + 1);
+    int rc = launch_bf_knn(h, ix, fq.p, nf, dim, k, exclude_self, fi.p, fd.p, fail.p + 1, self_base);
     if (rc) return rc;
     tot = (size_t)nf * k;
     tc::scatter_rows_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, h->stream>>>(fail.p + 1, nf, (uint32_t)k, fi.p, fd.p, ids, dists);

@@ -1,30 +1,46 @@
-"""Row-sharded search across ranks (one process per GPU): every rank searches its own sub-index,
-per-shard [nq,k] (distance, global id) lists are exchanged with ONE all-gather and merged.
-Backend agnostic (`nccl` on GPUs, `gloo` in the CPU tests); the merge itself is injected:
-on a GPU it is Handle.merge_topk_raw (csrc/merge.cu).
+"""Row-sharded search across ranks (one process per GPU): the base is cut into `shards` row blocks, rank r owns the
+lp = shards / world consecutive shards r*lp .. r*lp + lp - 1 (so block order == shard order == row order and the merged
+result, ties included, is the same for every world size); every rank searches the same query batch on the shards it owns, writing (distance, global id)
+lists straight into its BLOCK of a send buffer; ONE all-gather exchanges the blocks and every rank merges them.
+
+Block layout (32-bit words): [distances: lp x nq x k float32][ids: lp x nq x k uint32], lp = shards per rank - what
+b200ann_merge_topk_gathered (csrc/merge.cu) reads after the collective. Backend agnostic (`nccl` on GPUs, `gloo` in
+the CPU tests). The merged result does not depend on the number of ranks the shards are spread over.
 Reference analogue: the per-cluster search + host merge of CNNS/tests/cluster_hnsw_nsg_search.cpp:189-270."""
 import torch
 import torch.distributed as dist
 
 
-def to_global(local_ids, rank, rows_per_rank, invalid=-1):
-    """local row ids (int32 bit pattern of u32) -> global ids; INVALID (0xFFFFFFFF == -1) stays INVALID"""
-    return torch.where(local_ids == invalid, local_ids, local_ids + rank * rows_per_rank)
+def owned_shards(rank, world, shards):
+    """shards of rank `rank`: rank*lp .. rank*lp + lp - 1 with lp = shards / world (shards % world must be 0)"""
+    assert shards % world == 0, "the shard count must be a multiple of the world size"
+    lp = shards // world
+    return list(range(rank * lp, (rank + 1) * lp))
 
 
-def gather_lists(d, ids):
-    """d, ids [nq,k] on every rank -> ([world,nq,k], [world,nq,k]) on every rank, part r = rank r"""
-    world = dist.get_world_size()
-    nq = d.shape[0]
-    gd = torch.empty((world * nq,) + tuple(d.shape[1:]), dtype=d.dtype, device=d.device)
-    gi = torch.empty((world * nq,) + tuple(ids.shape[1:]), dtype=ids.dtype, device=ids.device)
-    dist.all_gather_into_tensor(gd, d.contiguous())   # concatenation along dim 0 == [world, nq, k]
-    dist.all_gather_into_tensor(gi, ids.contiguous())
-    return gd.view((world,) + tuple(d.shape)), gi.view((world,) + tuple(ids.shape))
+def alloc_block(lp, nq, k, device):
+    """-> (block int32 [2*lp*nq*k], d float32 view [lp,nq,k], ids int32 view [lp,nq,k] (u32 bit patterns))"""
+    block = torch.empty(2 * lp * nq * k, dtype=torch.int32, device=device)
+    half = lp * nq * k
+    d = block[:half].view(torch.float32).view(lp, nq, k)
+    ids = block[half:].view(lp, nq, k)
+    return block, d, ids
 
 
-def sharded_topk(d, local_ids, rank, rows_per_rank, kout, merge):
-    """merge(gd, gi, kout) -> (out_d, out_i): the kout smallest (distance,id) of the union per query"""
-    gi_local = to_global(local_ids, rank, rows_per_rank)
-    gd, gi = gather_lists(d, gi_local)
-    return merge(gd, gi, kout)
+def exchange(block, world, out=None):
+    """all-gather of every rank's block -> [world, len(block)] (world == 1: the block itself, no collective)"""
+    if world == 1:
+        return block.view(1, -1)
+    if out is None:
+        out = torch.empty((world, block.numel()), dtype=block.dtype, device=block.device)
+    dist.all_gather_into_tensor(out.view(-1), block)
+    return out
+
+
+def split_gathered(g, lp, nq, k):
+    """gathered blocks [world, 2*lp*nq*k] -> (d [world*lp,nq,k] float32, ids [world*lp,nq,k] int32), part = rank*lp + l"""
+    world = g.shape[0]
+    half = lp * nq * k
+    d = g[:, :half].contiguous().view(torch.float32).view(world * lp, nq, k)
+    ids = g[:, half:].contiguous().view(world * lp, nq, k)
+    return d, ids

@@ -117,6 +117,13 @@ int b200ann_free_device(void *dev);
  * The exact counterpart of IndexGraph::Build's output (index_graph.cpp:275-292). */
 int b200ann_knn_graph(b200ann_handle_t h, b200ann_index_t ix, size_t K, uint32_t *knn /*[h|d]*/);
 
+/* rows [row0, row0 + nrows) of the same graph: knn [nrows,K]. The row-block partition of the kNN-graph build across
+ * GPUs (BASELINE north_star "graph build is partitioned by row blocks"): every GPU holds the base, computes the rows
+ * of its block and the blocks are exchanged with one all-gather; the union equals b200ann_knn_graph's output bit for
+ * bit. */
+int b200ann_knn_graph_rows(b200ann_handle_t h, b200ann_index_t ix, size_t row0, size_t nrows, size_t K,
+                           uint32_t *knn /*[h|d]*/);
+
 /* replaces efanna2e::IndexGraph::Build with the IndexRandom initializer (CNNS/efanna_graph/src/index_graph.cpp:
  * 265-294: InitializeGraph :175-201, NNDescent :122-136 = iter x {join :22-33, update :34-120}, top-K extraction
  * :275-291; index_random.cpp:24-27). K, L, iter, S, R are the reference's parameters of the same names. L2 indexes
@@ -226,13 +233,21 @@ int b200ann_cluster_search(b200ann_handle_t h, b200ann_index_t ix, b200ann_index
                            uint32_t *searched /*[h|d] or NULL*/);
 
 /* ---- shard-result merge (multi-GPU search) ---------------------------------------------------- */
-/* d/ids [parts, nq, k]: per-shard result lists, each row ascending by (distance,id), ids global,
- * unfilled slots +inf / B200ANN_INVALID. out_d (may be NULL) / out_i [nq, kout] = the kout smallest
- * of the union, ascending (distance,id). GPU counterpart of the reference's per-cluster result merge
+/* d/ids [parts, nq, k]: per-shard result lists, each row ascending by distance (what every search of this library
+ * writes), ids global, unfilled slots +inf / B200ANN_INVALID. out_d (may be NULL) / out_i [nq, kout] = the kout
+ * smallest of the union, ascending by distance; equal distances keep (part, position) order - with row shards and
+ * (distance,id)-sorted lists that is (distance,id) order. GPU counterpart of the reference's per-cluster result merge
  * (CNNS/tests/cluster_hnsw_nsg_search.cpp:189-270; merge_topk_queue, ..._pipeline.cpp:195-212);
  * the lists come from one NCCL all-gather of every rank's b200ann_nsg_search / _hnsw_search output. */
 int b200ann_merge_topk(b200ann_handle_t h, const float *d /*[h|d]*/, const uint32_t *ids /*[h|d]*/, size_t parts,
                        size_t nq, size_t k, size_t kout, float *out_d /*[h|d]*/, uint32_t *out_i /*[h|d]*/);
+
+/* the same merge over the buffer ONE all-gather fills: buf = world blocks, block r = what rank r sent:
+ * [distances: lp x nq x k floats][ids: lp x nq x k u32] (lp lists per rank: the shards it owns). The searches write
+ * straight into the rank's block (ids already global through b200ann_set_id_base), so a multi-GPU step is
+ * lp searches -> one ncclAllGather -> this kernel. Device memory only. */
+int b200ann_merge_topk_gathered(b200ann_handle_t h, const void *buf /*[d]*/, size_t world, size_t lp, size_t nq, size_t k,
+                                size_t kout, float *out_d /*[d] or NULL*/, uint32_t *out_i /*[d]*/);
 
 /* Stream-ordered mode for pipelines that keep everything on the device (multi-GPU search: search -> all-gather ->
  * merge): when on, b200ann_nsg_search and b200ann_merge_topk calls whose inputs AND outputs are all device memory

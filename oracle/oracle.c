@@ -1300,21 +1300,30 @@ EXPORT long orc_nsg_tree_grow(const float *data, size_t n, size_t dim, size_t st
 
 /* ================================================================== shard-result merge */
 /* per query: `parts` ascending lists of k (distance,id) -> the kout smallest of the union, ascending
- * (distance,id). What the reference's cluster drivers do on the host with an unordered_map +
+ * distance. What the reference's cluster drivers do on the host with an unordered_map +
  * partial_sort (CNNS/tests/cluster_hnsw_nsg_search.cpp:228-262): ids are global and unique across
  * shards, so no dedup is needed. d/ids [parts,nq,k]. */
+typedef struct { float d; uint32_t id; uint32_t ord; } orc_mpair;
+static int mpair_cmp(const void *a, const void *b) {
+  const orc_mpair *x = (const orc_mpair *)a, *y = (const orc_mpair *)b;
+  if (x->d < y->d) return -1;
+  if (x->d > y->d) return 1;
+  return x->ord < y->ord ? -1 : (x->ord > y->ord ? 1 : 0);
+}
+/* order: (distance, part, position in the part) - a stable merge of lists that are ascending by distance. With row
+ * shards (ids ascending with the part) and (distance,id)-sorted lists this is the (distance,id) order. */
 EXPORT int orc_merge_topk(const float *d, const uint32_t *ids, size_t parts, size_t nq, size_t k, size_t kout,
                           float *out_d, uint32_t *out_i) {
-  orc_pair *tmp = (orc_pair *)malloc(sizeof(orc_pair) * parts * k);
+  orc_mpair *tmp = (orc_mpair *)malloc(sizeof(orc_mpair) * parts * k);
   for (size_t q = 0; q < nq; q++) {
     size_t m = 0;
     for (size_t s = 0; s < parts; s++)
       for (size_t j = 0; j < k; j++) {
         size_t off = (s * nq + q) * k + j;
         if (ids[off] == ORC_INVALID) continue;
-        tmp[m].d = d[off]; tmp[m].id = ids[off]; m++;
+        tmp[m].d = d[off]; tmp[m].id = ids[off]; tmp[m].ord = (uint32_t)(s * k + j); m++;
       }
-    qsort(tmp, m, sizeof(orc_pair), pair_cmp);
+    qsort(tmp, m, sizeof(orc_mpair), mpair_cmp);
     for (size_t j = 0; j < kout; j++) {
       out_i[q * kout + j] = j < m ? tmp[j].id : ORC_INVALID;
       if (out_d) out_d[q * kout + j] = j < m ? tmp[j].d : INFINITY;

@@ -102,3 +102,18 @@ def test_knn_tc_equals_simt_at_scale(B):
     assert (knn[rows] == want).all()
     ix.close()
     h.close()
+
+
+@pytest.mark.parametrize("mode,n,dim,K", [(2, 9000, 64, 24), (1, 3000, 40, 10), (0, 20000, 128, 50)])
+def test_knn_graph_rows_union_equals_whole(B, H, mode, n, dim, K):
+    """row-block partition of the kNN-graph build (multi-GPU build): the blocks' union is the whole graph, bit for bit"""
+    base = R.data_sift_like(n, dim, 7) if mode != 1 else R.data_uniform(n, dim, 7)
+    ix = B.Index(H, base, 0)
+    H.set_knn_mode(mode)
+    try:
+        whole = ix.knn_graph(K)
+        cuts = [0, n // 3 + 5, n // 3 + 6, n - 1000, n]
+        parts = [ix.knn_graph_rows(a, b - a, K) for a, b in zip(cuts[:-1], cuts[1:])]
+        assert (np.concatenate(parts) == whole).all()
+    finally:
+        H.set_knn_mode(0)

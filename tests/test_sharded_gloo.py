@@ -21,37 +21,55 @@ def _sharded():
     return m
 
 
+SHARDS = 4
+
+
+def _run(rank, world, n_per, dim, nq, k):
+    """the sharded search of bench.py's C5 step with the oracle in place of the kernels: -> (out_d, out_i)"""
+    S = _sharded()
+    base = R.data_uniform(n_per * SHARDS, dim, 1)
+    q = R.data_uniform(nq, dim, 2)
+    own = S.owned_shards(rank, world, SHARDS)
+    lp = len(own)
+    block, bd, bi = S.alloc_block(lp, nq, k, "cpu")
+    for l, s in enumerate(own):
+        shard = np.ascontiguousarray(base[s * n_per:(s + 1) * n_per])
+        ids, d = R.orc_bf_knn(shard, q, k, R.L2_SCALAR)          # local ids of this shard
+        ids = ids.astype(np.int64) + s * n_per                    # what b200ann_set_id_base does in the kernel epilogue
+        if s == 1:
+            ids[0, -1] = R.INVALID; d[0, -1] = np.inf             # an unfilled slot must stay INVALID
+        bd[l] = torch.from_numpy(d)
+        bi[l] = torch.from_numpy(ids.astype(np.uint32).view(np.int32))
+    g = S.exchange(block, world)
+    gd, gi = S.split_gathered(g, lp, nq, k)
+    od, oi = R.orc_merge_topk(gd.numpy(), gi.numpy().view(np.uint32), k)
+    return base, q, od, oi
+
+
 def _worker(rank, world, port, n_per, dim, nq, k, out):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
-    S = _sharded()
-    base = R.data_uniform(n_per * world, dim, 1)
-    q = R.data_uniform(nq, dim, 2)
-    shard = np.ascontiguousarray(base[rank * n_per:(rank + 1) * n_per])
-    ids, d = R.orc_bf_knn(shard, q, k, R.L2_SCALAR)            # local ids of this shard
-    if rank == 1:
-        ids[0, -1] = R.INVALID; d[0, -1] = np.inf                # an unfilled slot must stay INVALID
-
-    def merge(gd, gi, kout):
-        od, oi = R.orc_merge_topk(gd.numpy(), gi.numpy().view(np.uint32), kout)
-        return od, oi
-
-    od, oi = S.sharded_topk(torch.from_numpy(d), torch.from_numpy(ids.view(np.int32)), rank, n_per, k, merge)
+    base, q, od, oi = _run(rank, world, n_per, dim, nq, k)
     tid, td = R.orc_bf_knn(base, q, k, R.L2_SCALAR)
     ok = (oi[1:] == tid[1:]).all() and (od[1:] == td[1:]).all() and R.INVALID not in oi
-    out[rank] = bool(ok)
+    out[rank] = (bool(ok), oi.tobytes(), od.tobytes())
     dist.barrier()
     dist.destroy_process_group()
 
 
-def test_sharded_topk_world2():
+def test_sharded_topk_world2_equals_world1():
+    """4 shards over 2 ranks (gloo): the merged lists equal brute force over the whole base AND the lists one rank
+    holding all 4 shards produces - the result does not depend on how many GPUs the shards are spread over"""
     world = 2
     with mp.Manager() as mgr:
         out = mgr.dict()
         port = 29500 + (os.getpid() % 2000)
-        mp.spawn(_worker, args=(world, port, 1500, 16, 40, 10, out), nprocs=world, join=True)
-        assert out[0] and out[1]
+        mp.spawn(_worker, args=(world, port, 900, 16, 40, 10, out), nprocs=world, join=True)
+        assert out[0][0] and out[1][0]
+        assert out[0][1] == out[1][1] and out[0][2] == out[1][2]
+        _, _, od, oi = _run(0, 1, 900, 16, 40, 10)
+        assert oi.tobytes() == out[0][1] and od.tobytes() == out[0][2]
 
 
 def test_merge_oracle_matches_numpy():
@@ -62,5 +80,5 @@ def test_merge_oracle_matches_numpy():
     od, oi = R.orc_merge_topk(d, ids, 10)
     for q in range(nq):
         alld = d[:, q].ravel(); alli = ids[:, q].ravel()
-        o = np.lexsort((alli, alld))[:10]
+        o = np.argsort(alld, kind="stable")[:10]   # (distance, part, position)
         assert (oi[q] == alli[o]).all() and (od[q] == alld[o]).all()

@@ -559,6 +559,8 @@ static int search_from_common(b200ann_handle_t h, b200ann_index_t ix, const floa
   CU_CHECK(h, od.finish(h->stream));
   CU_CHECK(h, os.finish(h->stream));
   CU_CHECK(h, oe.finish(h->stream));
+  if (h->async_mode && !oi.host && !od.host && !os.host && !oe.host && is_device_ptr(q) && (hybrid || is_device_ptr(entry)))
+    return 0;  // stream-ordered, no host sync
   CU_CHECK(h, t.sync());
   return 0;
 }

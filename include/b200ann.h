@@ -250,7 +250,7 @@ int b200ann_merge_topk_gathered(b200ann_handle_t h, const void *buf /*[d]*/, siz
                                 size_t kout, float *out_d /*[d] or NULL*/, uint32_t *out_i /*[d]*/);
 
 /* Stream-ordered mode for pipelines that keep everything on the device (multi-GPU search: search -> all-gather ->
- * merge): when on, b200ann_nsg_search and b200ann_merge_topk calls whose inputs AND outputs are all device memory
+ * merge): when on, b200ann_nsg_search, _nsg_search_from, _hybrid_search and b200ann_merge_topk(_gathered) calls whose inputs AND outputs are all device memory
  * return as soon as their kernels are enqueued on the handle's stream (b200ann_stream); the caller orders later work
  * on that stream or synchronizes it. b200ann_last_kernel_ms is not updated by such calls; a kernel fault surfaces at
  * the next synchronizing call. Calls with any host buffer still synchronize. Default off. */

@@ -48,6 +48,7 @@ _lib.b200ann_knn_graph.argtypes = [_vp, _vp, _sz, _vp]
 _lib.b200ann_knn_graph_rows.argtypes = [_vp, _vp, _sz, _sz, _sz, _vp]
 _lib.b200ann_bf_knn_u8.argtypes = [_vp, _vp, _sz, _sz, _sz, _vp, _sz, _sz, _sz, _vp, _vp]
 _lib.b200ann_hnsw_build.argtypes = [_vp, _vp, _sz, _sz, C.c_uint32, _sz, _sz, _vp, _vp]
+_lib.b200ann_hnsw_insert_batch.argtypes = [_vp, _vp, _vp, _sz, _vp, _sz, _sz, _vp]
 _lib.b200ann_index_hnsw_shape.argtypes = [_vp, _vp]
 _lib.b200ann_index_get_hnsw.argtypes = [_vp, _vp, _vp, _vp, _vp, _vp]
 _lib.b200ann_nndescent.argtypes = [_vp, _vp, _sz, _sz, _sz, _sz, _sz, C.c_uint32, _vp, _vp, _vp]
@@ -87,7 +88,7 @@ EXPORTS = [
     "b200ann_nsg_interinsert", "b200ann_nsg_finish", "b200ann_merge_topk", "b200ann_nsg_search_from",
     "b200ann_hybrid_search", "b200ann_set_knn_mode", "b200ann_knn_last_stats", "b200ann_nndescent",
     "b200ann_hnsw_build", "b200ann_index_hnsw_shape", "b200ann_index_get_hnsw", "b200ann_nsg_search_clustered",
-    "b200ann_knn_graph_rows", "b200ann_merge_topk_gathered", "b200ann_set_search_options", "b200ann_set_search_kernel", "b200ann_set_id_base", "b200ann_set_query_order", "b200ann_probe_gather",
+    "b200ann_knn_graph_rows", "b200ann_hnsw_insert_batch", "b200ann_merge_topk_gathered", "b200ann_set_search_options", "b200ann_set_search_kernel", "b200ann_set_id_base", "b200ann_set_query_order", "b200ann_probe_gather",
     "b200ann_set_async", "b200ann_cluster_search", "b200ann_bf_knn_u8", "b200ann_upload_u8", "b200ann_free_device",
 ]
 
@@ -305,6 +306,17 @@ class Index:
         info = np.zeros(8, np.uint64)
         lab = None if labels is None else np.ascontiguousarray(labels, np.uint64)
         self.h._check(_lib.b200ann_hnsw_build(self.h._h, self._ix, M, efc, seed, ratio, bmax, _ptr(lab), _ptr(info)))
+        keys = ("beam_evals", "hops", "heuristic_evals", "batches", "upper_rows", "maxlevel", "ep", "largest_group")
+        return dict(zip(keys, (int(x) for x in info)))
+
+    def hnsw_insert_batch(self, data, labels=None, efc=0):
+        """nb addPoint calls on the live graph: appends the rows of `data` and links them in place"""
+        data = np.ascontiguousarray(data, np.float32)
+        info = np.zeros(8, np.uint64)
+        lab = None if labels is None else np.ascontiguousarray(labels, np.uint64)
+        self.h._check(_lib.b200ann_hnsw_insert_batch(self.h._h, self._ix, _ptr(data), data.shape[1], _ptr(lab), data.shape[0],
+                                                     efc, _ptr(info)))
+        self.n += data.shape[0]
         keys = ("beam_evals", "hops", "heuristic_evals", "batches", "upper_rows", "maxlevel", "ep", "largest_group")
         return dict(zip(keys, (int(x) for x in info)))
 

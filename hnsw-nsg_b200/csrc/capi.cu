@@ -212,6 +212,9 @@ static void free_hnsw(b200ann_index *ix) {
   if (ix->upper_ptr) cudaFree(ix->upper_ptr);
   if (ix->upper_links) cudaFree(ix->upper_links);
   if (ix->labels) cudaFree(ix->labels);
+  if (ix->upper_owner) cudaFree(ix->upper_owner);
+  ix->upper_owner = nullptr;
+  ix->cap_links0 = ix->cap_levels = ix->cap_uptr = ix->cap_upper = ix->cap_owner = ix->cap_labels = 0;
   ix->links0 = ix->upper_ptr = ix->upper_links = nullptr;
   ix->levels = nullptr; ix->labels = nullptr; ix->has_hnsw = false;
 }
@@ -290,6 +293,8 @@ int b200ann_index_set_hnsw(b200ann_index_t ix, const uint32_t *links0, size_t ma
   CU_CHECK(h, cudaStreamSynchronize(h->stream));
   ix->maxM0 = maxM0; ix->maxM = maxM ? maxM : 1; ix->upper_rows = upper_rows;
   ix->hnsw_ep = ep; ix->maxlevel = maxlevel; ix->has_hnsw = true;
+  ix->hnsw_M = ix->maxM; ix->hnsw_efc = 0;
+  ix->level_rng.seed(100);  // a loaded index draws new levels from a fresh generator (hnswalg.h:78-86 load ctor, random_seed = 100)
   return 0;
 }
 
@@ -300,6 +305,23 @@ int b200ann_hnsw_build(b200ann_handle_t h, b200ann_index_t ix, size_t M, size_t 
   free_hnsw(ix);
   CallTimer t(h);
   int rc = hnsw_build_launch(h, ix, M, efc, seed, ratio, bmax, labels, info);
+  t.stop();
+  if (rc) return rc;
+  CU_CHECK(h, t.sync());
+  return 0;
+}
+
+int b200ann_hnsw_insert_batch(b200ann_handle_t h, b200ann_index_t ix, const float *data, size_t stride, const uint64_t *labels,
+                              size_t nb, size_t ef_construction, uint64_t *info) {
+  if (!h || !ix) return B200ANN_ERR_ARG;
+  if (!data || stride < ix->dim) return set_err(h, B200ANN_ERR_ARG, "hnsw_insert_batch: bad data / stride");
+  if (nb == 0) return 0;
+  CU_CHECK(h, cudaSetDevice(h->device));
+  if (ef_construction) ix->hnsw_efc = ef_construction > ix->maxM ? ef_construction : ix->maxM;
+  InArg<float> din;
+  CU_CHECK(h, din.stage(data, nb * stride, h->stream));
+  CallTimer t(h);
+  int rc = hnsw_insert_launch(h, ix, din.d, stride, nb, labels, 0, 0, info);
   t.stop();
   if (rc) return rc;
   CU_CHECK(h, t.sync());

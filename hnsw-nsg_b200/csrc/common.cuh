@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <random>
 #include <string>
 #include <vector>
 #include "../../include/b200ann.h"
@@ -61,6 +62,12 @@ struct b200ann_index {
   uint32_t hnsw_ep = 0;
   int maxlevel = -1;
   bool has_hnsw = false;
+  // in-place growth (b200ann_hnsw_insert_batch): capacities in elements (0 = exactly what the size needs), the owner of
+  // every upper row, the level generator that continues across appends (hnswalg.h:122 level_generator_), M / efC
+  size_t cap_vec = 0, cap_links0 = 0, cap_levels = 0, cap_uptr = 0, cap_upper = 0, cap_owner = 0, cap_labels = 0;
+  uint32_t *upper_owner = nullptr;
+  std::default_random_engine level_rng{100};
+  size_t hnsw_M = 0, hnsw_efc = 0;
   // tensor-core kNN cache (knn_tc.cu): bf16 hi/lo copies [n, tc_dpad], fp32 row norms
   void *tc_hi = nullptr, *tc_lo = nullptr;
   float *tc_norms = nullptr;
@@ -180,6 +187,8 @@ void knn_tc_free(b200ann_index *ix);
 // HNSW construction (hnsw_build.cu): builds and installs the graph in the index
 int hnsw_build_launch(b200ann_handle *h, b200ann_index *ix, size_t M, size_t efc, uint32_t seed, size_t ratio, size_t bmax,
                       const uint64_t *labels_host_or_dev, uint64_t *info8);
+int hnsw_insert_launch(b200ann_handle *h, b200ann_index *ix, const float *data, size_t dstride, size_t nb,
+                       const uint64_t *labels_host_or_dev, size_t ratio, size_t bmax, uint64_t *info8);
 
 // NN-descent (nndescent.cu); device pointers only
 int nndescent_launch(b200ann_handle *h, const b200ann_index *ix, size_t K, size_t L, size_t iter, size_t S, size_t R,

@@ -20,6 +20,7 @@
 // reference (this file is compiled against the same libstdc++), so level assignment is identical to it.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <random>
 #include <vector>
 #include "beam.cuh"
@@ -275,16 +276,199 @@ __global__ void fill_u32_kernel(uint32_t *p, size_t count, uint32_t v) {
 
 }  // namespace
 
-// HierarchicalNSW::getRandomLevel (hnswalg.h:206-210) for rows 0..n-1 in insertion order
-static void draw_levels(size_t n, size_t M, uint32_t seed, std::vector<int32_t> &levels) {
-  std::default_random_engine level_generator(seed);            // hnswalg.h:122
+// HierarchicalNSW::getRandomLevel (hnswalg.h:206-210): the next `count` draws of the index's level generator
+// (std::default_random_engine seeded once, :122 / the load ctor; the sequence continues across calls like the
+// reference's member generator does across addPoint calls)
+static void draw_levels(b200ann_index *ix, size_t count, size_t M, std::vector<int32_t> &levels) {
   const double mult = 1 / std::log(1.0 * (double)M);          // :114
-  levels.resize(n);
-  for (size_t i = 0; i < n; i++) {
+  levels.resize(count);
+  for (size_t i = 0; i < count; i++) {
     std::uniform_real_distribution<double> distribution(0.0, 1.0);
-    double r = -std::log(distribution(level_generator)) * mult;
+    double r = -std::log(distribution(ix->level_rng)) * mult;
     levels[i] = (int)r;
   }
+}
+
+// undo of a batch whose reverse pass cannot run (see hnsw_run_batches): forget the reverse-edge counts it recorded
+__global__ void rev_reset_kernel(const uint32_t *touched, uint32_t ntouched, uint32_t *rcount) {
+  uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < ntouched) rcount[touched[t]] = 0;
+}
+
+__global__ void iota_u64_kernel(uint64_t *p, size_t from, size_t to) {
+  size_t i = from + blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i < to) p[i] = i;
+}
+
+// grow a device array to hold `need` elements, keeping the first `keep` (capacity doubles: appends are amortised)
+template <typename T>
+static cudaError_t grow(T **p, size_t keep, size_t need, size_t *cap, cudaStream_t st) {
+  if (need <= *cap && *p) return cudaSuccess;
+  size_t nc = *cap * 2 > need ? *cap * 2 : need;
+  T *q = nullptr;
+  cudaError_t e = cudaMalloc((void **)&q, (nc ? nc : 1) * sizeof(T));
+  if (e != cudaSuccess) return e;
+  if (*p && keep) e = cudaMemcpyAsync(q, *p, keep * sizeof(T), cudaMemcpyDeviceToDevice, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  if (*p) cudaFree(*p);
+  *p = q; *cap = nc;
+  return e;
+}
+
+// Inserts rows [s0, n) of the index (vectors, levels, upper_ptr and the INVALID-filled link rows are in place) into
+// the HNSW graph held by the index, batch by batch; updates the entry point / top level. levels = host levels of
+// rows [s0, n). stats4 += {beam evaluations, hops, heuristic evaluations, 0}.
+static int hnsw_run_batches(b200ann_handle *h, b200ann_index *ix, size_t s0, const std::vector<int32_t> &lv, size_t M, size_t efc,
+                            size_t ratio, size_t bmax, unsigned long long *stats4, uint64_t *batches_out, uint64_t *biggest_out) {
+  const size_t n = ix->n, rows = ix->upper_rows, maxM0 = ix->maxM0, maxM = ix->maxM;
+  cudaStream_t st = h->stream;
+  auto level_of = [&](size_t i) { return lv[i - s0]; };
+  int toplevel = ix->maxlevel;
+  for (size_t i = s0; i < n; i++) toplevel = std::max(toplevel, (int)level_of(i));
+  std::vector<size_t> uprow(n - s0 + 1);   // first upper row of point i (the arrays were extended before this call)
+  {
+    size_t tot = 0;
+    for (size_t i = s0; i < n; i++) tot += (size_t)level_of(i);
+    size_t acc = rows - tot;
+    for (size_t i = s0; i < n; i++) { uprow[i - s0] = acc; acc += (size_t)level_of(i); }
+    uprow[n - s0] = acc;
+  }
+  const uint32_t nlev = (uint32_t)toplevel + 1;
+  if (bmax > n - s0) bmax = n - s0 ? n - s0 : 1;
+  DevBuf<uint32_t> rstate, touched, counters, rev_row, rev_src, g_src;
+  DevBuf<float> rev_d, g_d;
+  DevBuf<unsigned long long> stats;
+  const size_t nr = n + rows, ecap = bmax * nlev * M;
+  CU_CHECK(h, rstate.alloc(3 * nr, st));          // rcount | rfill | roff
+  CU_CHECK(h, touched.alloc(nr, st));
+  CU_CHECK(h, counters.alloc(4, st));
+  CU_CHECK(h, rev_row.alloc(ecap, st)); CU_CHECK(h, rev_src.alloc(ecap, st)); CU_CHECK(h, rev_d.alloc(ecap, st));
+  CU_CHECK(h, g_src.alloc(ecap, st)); CU_CHECK(h, g_d.alloc(ecap, st));
+  CU_CHECK(h, stats.alloc(4, st));
+  CU_CHECK(h, cudaMemsetAsync(rstate.p, 0, 3 * nr * 4, st));
+  CU_CHECK(h, cudaMemsetAsync(stats.p, 0, 4 * sizeof(unsigned long long), st));
+  uint32_t *rcount = rstate.p, *rfill = rstate.p + nr, *roff = rstate.p + 2 * nr;
+
+  const bool ipm = ix->metric == B200ANN_IP;
+  InsertParams ip = {};
+  ip.sp.vec = ix->vec; ip.sp.stride = ix->stride; ip.sp.n = (uint32_t)n; ip.sp.nch = (int)((ix->dim + 3) / 4);
+  ip.sp.dim = (uint32_t)ix->dim;
+  ip.sp.graph = ix->links0; ip.sp.gstride = (uint32_t)maxM0;
+  ip.sp.upper_links = ix->upper_links; ip.sp.upper_ptr = ix->upper_ptr; ip.sp.maxM = (uint32_t)maxM;
+  ip.sp.L = (uint32_t)efc; ip.sp.K = (uint32_t)M;
+  // visited hash of 2^11 slots per warp: measured on 1M x 128, M=16, efC=200: 2^10 1.68 s, 2^11 1.64 s, 2^12 2.10 s,
+  // 2^13 3.2 s (a smaller table re-evaluates ~5 % more rows but doubles the resident warps)
+  ip.sp.hbits = (h->link_visited_bits && h->link_visited_bits < 11) ? h->link_visited_bits : 11;
+  ip.sp.pool_cap = round_up((uint32_t)efc + 1, 32);
+  ip.sp.cand_cap = round_up((uint32_t)maxM0, 32);
+  ip.M = (uint32_t)M; ip.nlev = nlev; ip.levels = ix->levels; ip.links0 = ix->links0; ip.upper_links = ix->upper_links;
+  ip.rev_row = rev_row.p; ip.rev_src = rev_src.p; ip.rev_d = rev_d.p;
+  ip.rcount = rcount; ip.touched = touched.p; ip.counters = counters.p; ip.stats = stats.p;
+  ReverseParams rp = {};
+  rp.sp = ip.sp; rp.sp.pool_cap = 32; rp.sp.hbits = 5;
+  rp.links0 = ix->links0; rp.upper_links = ix->upper_links; rp.row_owner = ix->upper_owner;
+  rp.touched = touched.p; rp.counters = counters.p; rp.roff = roff; rp.g_src = g_src.p; rp.g_d = g_d.p;
+  rp.rcount = rcount; rp.rfill = rfill; rp.stats = stats.p;
+
+  uint32_t ep = ix->hnsw_ep;
+  int maxlevel = ix->maxlevel;
+  uint64_t batches = 0, biggest = 0;
+  size_t s = s0;
+  int rc = 0;
+  if (s == 0) {  // first element: entry point, nothing to link (:1255-1258)
+    ep = 0; maxlevel = level_of(0); s = 1; batches = 1;
+  }
+  // a warp of the reverse pass holds one touched row's old links + ALL reverse edges the batch adds to it in shared
+  // memory; a hub (duplicate-heavy data, inner product) can collect more than fits. Such a batch is undone - nothing
+  // but the new points' own rows was written - and re-run at half the size.
+  size_t max_group = (227 * 1024 / (WARPS * 4) - smem_words(32, round_up((uint32_t)maxM0, 32), 5) - 2 * maxM0) / 4 - maxM0 - 32;
+  if (const char *e = getenv("B200ANN_HNSW_MAX_GROUP")) max_group = std::min<size_t>(max_group, (size_t)atol(e));  // tests
+  size_t bcap = bmax;
+  while (s < n && rc == 0) {
+    size_t e;
+    if (level_of(s) > maxlevel) e = s + 1;
+    else {
+      size_t b = std::min(std::min(bmax, bcap), std::max<size_t>(1, s / ratio));
+      e = std::min(n, s + b);
+      for (size_t i = s + 1; i < e; i++)
+        if (level_of(i) > maxlevel) { e = i; break; }
+    }
+    batches++;
+    const size_t total = (e - s) * nlev * M;
+    cudaMemsetAsync(rev_row.p, 0xFF, total * 4, st);
+    cudaMemsetAsync(counters.p, 0, 4 * 4, st);
+    ip.s = (uint32_t)s; ip.e = (uint32_t)e; ip.sp.ep = ep; ip.sp.maxlevel = maxlevel;
+    rc = launch_insert(h, ip, ipm);
+    if (rc) break;
+    uint32_t hc[4];
+    cudaMemcpyAsync(hc, counters.p, sizeof hc, cudaMemcpyDeviceToHost, st);
+    cudaError_t ce = cudaStreamSynchronize(st);
+    if (ce != cudaSuccess) { rc = set_err(h, B200ANN_ERR_CUDA, std::string("hnsw insert: ") + cudaGetErrorString(ce)); break; }
+    if (hc[0] && hc[1] > max_group && e - s > 1) {
+      rev_reset_kernel<<<(hc[0] + 255) / 256, 256, 0, st>>>(touched.p, hc[0], rcount);
+      fill_u32_kernel<<<h->sm_count, 256, 0, st>>>(ix->links0 + s * maxM0, (e - s) * maxM0, INVALID_ID);
+      const size_t ur0 = uprow[s - s0], ur1 = uprow[e - s0];   // the upper rows of the batch's points are contiguous
+      if (ur1 > ur0) fill_u32_kernel<<<h->sm_count, 256, 0, st>>>(ix->upper_links + ur0 * maxM, (ur1 - ur0) * maxM, INVALID_ID);
+      h->launches += 2;
+      bcap = (e - s) / 2;
+      batches--;
+      continue;
+    }
+    if (hc[0]) {
+      biggest = std::max<uint64_t>(biggest, hc[1]);
+      rev_offsets_kernel<<<(hc[0] + 255) / 256, 256, 0, st>>>(touched.p, counters.p, rcount, roff, counters.p + 2);
+      rev_group_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(rev_row.p, rev_src.p, rev_d.p, total, roff, rfill, g_src.p, g_d.p);
+      h->launches += 2;
+      rp.mcap = round_up((uint32_t)maxM0 + hc[1], 32);
+      rc = launch_reverse(h, rp, hc[0], ipm);
+      if (rc) break;
+    }
+    for (size_t i = s; i < e; i++)
+      if (level_of(i) > maxlevel) { maxlevel = level_of(i); ep = (uint32_t)i; }   // :1262-1265
+    s = e;
+    if (bcap < bmax) bcap = std::min(bmax, bcap * 2);
+  }
+  unsigned long long hs[4] = {0, 0, 0, 0};
+  if (rc == 0) {
+    cudaMemcpyAsync(hs, stats.p, sizeof hs, cudaMemcpyDeviceToHost, st);
+    cudaError_t ce = cudaStreamSynchronize(st);
+    if (ce == cudaSuccess) ce = cudaGetLastError();
+    if (ce != cudaSuccess) rc = set_err(h, B200ANN_ERR_CUDA, std::string("hnsw insert: ") + cudaGetErrorString(ce));
+  }
+  if (rc) return rc;
+  ix->hnsw_ep = ep; ix->maxlevel = maxlevel;
+  for (int i = 0; i < 4; i++) stats4[i] += hs[i];
+  *batches_out += batches;
+  *biggest_out = std::max<uint64_t>(*biggest_out, biggest);
+  return 0;
+}
+
+// rows [n_old, n) get their levels, upper rows (INVALID-filled) and owners; the arrays grow as needed
+static int hnsw_extend_arrays(b200ann_handle *h, b200ann_index *ix, size_t n_old, const std::vector<int32_t> &lv) {
+  cudaStream_t st = h->stream;
+  const size_t n = ix->n, maxM0 = ix->maxM0, maxM = ix->maxM;
+  std::vector<uint32_t> uptr(n - n_old), owner;
+  size_t rows = ix->upper_rows;
+  for (size_t i = n_old; i < n; i++) {
+    uptr[i - n_old] = (uint32_t)rows;
+    for (int l = 0; l < lv[i - n_old]; l++) owner.push_back((uint32_t)i);
+    rows += (size_t)lv[i - n_old];
+  }
+  const size_t rows_old = ix->upper_rows;
+  size_t c;
+  c = ix->cap_links0; CU_CHECK(h, grow(&ix->links0, n_old * maxM0, n * maxM0, &c, st)); ix->cap_links0 = c;
+  c = ix->cap_levels; CU_CHECK(h, grow(&ix->levels, n_old, n, &c, st)); ix->cap_levels = c;
+  c = ix->cap_uptr; CU_CHECK(h, grow(&ix->upper_ptr, n_old, n, &c, st)); ix->cap_uptr = c;
+  c = ix->cap_upper; CU_CHECK(h, grow(&ix->upper_links, rows_old * maxM, (rows ? rows : 1) * maxM, &c, st)); ix->cap_upper = c;
+  c = ix->cap_owner; CU_CHECK(h, grow(&ix->upper_owner, rows_old, rows ? rows : 1, &c, st)); ix->cap_owner = c;
+  CU_CHECK(h, cudaMemcpyAsync(ix->levels + n_old, lv.data(), (n - n_old) * 4, cudaMemcpyHostToDevice, st));
+  CU_CHECK(h, cudaMemcpyAsync(ix->upper_ptr + n_old, uptr.data(), (n - n_old) * 4, cudaMemcpyHostToDevice, st));
+  if (rows > rows_old) CU_CHECK(h, cudaMemcpyAsync(ix->upper_owner + rows_old, owner.data(), (rows - rows_old) * 4, cudaMemcpyHostToDevice, st));
+  fill_u32_kernel<<<h->sm_count * 8, 256, 0, st>>>(ix->links0 + n_old * maxM0, (n - n_old) * maxM0, INVALID_ID);
+  if (rows > rows_old) fill_u32_kernel<<<h->sm_count * 8, 256, 0, st>>>(ix->upper_links + rows_old * maxM, (rows - rows_old) * maxM, INVALID_ID);
+  CU_CHECK(h, cudaStreamSynchronize(st));   // the host staging vectors go out of scope
+  ix->upper_rows = rows;
+  return 0;
 }
 
 // Builds the HNSW graph of the index's rows (inserted in row order) and installs it in the index.
@@ -298,133 +482,93 @@ int hnsw_build_launch(b200ann_handle *h, b200ann_index *ix, size_t M, size_t efc
   if (efc < M) efc = M;                                        // hnswalg.h:107
   if (ratio == 0) ratio = 64;
   if (bmax == 0) bmax = 8192;
-  const size_t maxM = M, maxM0 = 2 * M;
   cudaStream_t st = h->stream;
+  // the caller freed any previous HNSW graph: start from empty arrays
+  ix->maxM = M; ix->maxM0 = 2 * M; ix->upper_rows = 0; ix->hnsw_ep = 0; ix->maxlevel = -1;
+  ix->cap_links0 = ix->cap_levels = ix->cap_uptr = ix->cap_upper = ix->cap_owner = ix->cap_labels = 0;
+  ix->level_rng.seed(seed); ix->hnsw_M = M; ix->hnsw_efc = efc;
   std::vector<int32_t> levels;
-  draw_levels(n, M, seed, levels);
-  std::vector<uint32_t> upper_ptr(n), row_owner;
-  size_t rows = 0;
-  int toplevel = 0;
-  for (size_t i = 0; i < n; i++) {
-    upper_ptr[i] = (uint32_t)rows;
-    for (int l = 0; l < levels[i]; l++) row_owner.push_back((uint32_t)i);
-    rows += (size_t)levels[i];
-    toplevel = std::max(toplevel, (int)levels[i]);
-  }
-  const uint32_t nlev = (uint32_t)toplevel + 1;
-
-  // the graph arrays become the index's (freed by b200ann_index_destroy / a later set_hnsw)
-  uint32_t *links0 = nullptr, *upper_links = nullptr, *d_upper_ptr = nullptr;
-  int32_t *d_levels = nullptr;
-  uint64_t *d_labels = nullptr;
-  struct Guard {  // frees the graph arrays unless the build succeeded and handed them to the index
-    uint32_t *&a, *&b, *&c; int32_t *&d; uint64_t *&e; bool keep = false;
-    ~Guard() { if (!keep) { cudaFree(a); cudaFree(b); cudaFree(c); cudaFree(d); cudaFree(e); } }
-  } guard{links0, upper_links, d_upper_ptr, d_levels, d_labels};
-  CU_CHECK(h, cudaMalloc((void **)&links0, n * maxM0 * 4));
-  CU_CHECK(h, cudaMalloc((void **)&upper_links, (rows ? rows : 1) * maxM * 4));
-  CU_CHECK(h, cudaMalloc((void **)&d_upper_ptr, n * 4));
-  CU_CHECK(h, cudaMalloc((void **)&d_levels, n * 4));
-  CU_CHECK(h, cudaMemcpyAsync(d_upper_ptr, upper_ptr.data(), n * 4, cudaMemcpyHostToDevice, st));
-  CU_CHECK(h, cudaMemcpyAsync(d_levels, levels.data(), n * 4, cudaMemcpyHostToDevice, st));
+  draw_levels(ix, n, M, levels);
+  int rc = hnsw_extend_arrays(h, ix, 0, levels);
+  if (rc) return rc;
   if (labels_host_or_dev) {
-    CU_CHECK(h, cudaMalloc((void **)&d_labels, n * 8));
-    CU_CHECK(h, cudaMemcpyAsync(d_labels, labels_host_or_dev, n * 8, cudaMemcpyDefault, st));
-  }
-  fill_u32_kernel<<<h->sm_count * 8, 256, 0, st>>>(links0, n * maxM0, INVALID_ID);
-  fill_u32_kernel<<<h->sm_count * 8, 256, 0, st>>>(upper_links, (rows ? rows : 1) * maxM, INVALID_ID);
-
-  DevBuf<uint32_t> owner, rstate, touched, counters, rev_row, rev_src, g_src;
-  DevBuf<float> rev_d, g_d;
-  DevBuf<unsigned long long> stats;
-  const size_t nr = n + rows, ecap = bmax * nlev * M;
-  CU_CHECK(h, owner.alloc(rows, st));
-  CU_CHECK(h, rstate.alloc(3 * nr, st));          // rcount | rfill | roff
-  CU_CHECK(h, touched.alloc(nr, st));
-  CU_CHECK(h, counters.alloc(4, st));
-  CU_CHECK(h, rev_row.alloc(ecap, st)); CU_CHECK(h, rev_src.alloc(ecap, st)); CU_CHECK(h, rev_d.alloc(ecap, st));
-  CU_CHECK(h, g_src.alloc(ecap, st)); CU_CHECK(h, g_d.alloc(ecap, st));
-  CU_CHECK(h, stats.alloc(4, st));
-  if (rows) CU_CHECK(h, cudaMemcpyAsync(owner.p, row_owner.data(), rows * 4, cudaMemcpyHostToDevice, st));
-  CU_CHECK(h, cudaMemsetAsync(rstate.p, 0, 3 * nr * 4, st));
-  CU_CHECK(h, cudaMemsetAsync(stats.p, 0, 4 * sizeof(unsigned long long), st));
-  uint32_t *rcount = rstate.p, *rfill = rstate.p + nr, *roff = rstate.p + 2 * nr;
-
-  const bool ipm = ix->metric == B200ANN_IP;
-  InsertParams ip = {};
-  ip.sp.vec = ix->vec; ip.sp.stride = ix->stride; ip.sp.n = (uint32_t)n; ip.sp.nch = (int)((ix->dim + 3) / 4);
-  ip.sp.dim = (uint32_t)ix->dim;
-  ip.sp.graph = links0; ip.sp.gstride = (uint32_t)maxM0;
-  ip.sp.upper_links = upper_links; ip.sp.upper_ptr = d_upper_ptr; ip.sp.maxM = (uint32_t)maxM;
-  ip.sp.L = (uint32_t)efc; ip.sp.K = (uint32_t)M;
-  // visited hash of 2^11 slots per warp: measured on 1M x 128, M=16, efC=200: 2^10 1.68 s, 2^11 1.64 s, 2^12 2.10 s,
-  // 2^13 3.2 s (a smaller table re-evaluates ~5 % more rows but doubles the resident warps)
-  ip.sp.hbits = (h->link_visited_bits && h->link_visited_bits < 11) ? h->link_visited_bits : 11;
-  ip.sp.pool_cap = round_up((uint32_t)efc + 1, 32);
-  ip.sp.cand_cap = round_up((uint32_t)maxM0, 32);
-  ip.M = (uint32_t)M; ip.nlev = nlev; ip.levels = d_levels; ip.links0 = links0; ip.upper_links = upper_links;
-  ip.rev_row = rev_row.p; ip.rev_src = rev_src.p; ip.rev_d = rev_d.p;
-  ip.rcount = rcount; ip.touched = touched.p; ip.counters = counters.p; ip.stats = stats.p;
-  ReverseParams rp = {};
-  rp.sp = ip.sp; rp.sp.pool_cap = 32; rp.sp.hbits = 5;
-  rp.links0 = links0; rp.upper_links = upper_links; rp.row_owner = owner.p;
-  rp.touched = touched.p; rp.counters = counters.p; rp.roff = roff; rp.g_src = g_src.p; rp.g_d = g_d.p;
-  rp.rcount = rcount; rp.rfill = rfill; rp.stats = stats.p;
-
-  uint32_t ep = 0;
-  int maxlevel = levels[0];                                    // first element: entry point, nothing to link (:1255-1258)
-  uint64_t batches = 1, biggest = 0;
-  size_t s = 1;
-  int rc = 0;
-  while (s < n && rc == 0) {
-    size_t e;
-    if (levels[s] > maxlevel) e = s + 1;
-    else {
-      size_t b = std::min(bmax, std::max<size_t>(1, s / ratio));
-      e = std::min(n, s + b);
-      for (size_t i = s + 1; i < e; i++)
-        if (levels[i] > maxlevel) { e = i; break; }
-    }
-    batches++;
-    const size_t total = (e - s) * nlev * M;
-    cudaMemsetAsync(rev_row.p, 0xFF, total * 4, st);
-    cudaMemsetAsync(counters.p, 0, 4 * 4, st);
-    ip.s = (uint32_t)s; ip.e = (uint32_t)e; ip.sp.ep = ep; ip.sp.maxlevel = maxlevel;
-    rc = launch_insert(h, ip, ipm);
-    if (rc) break;
-    uint32_t hc[4];
-    cudaMemcpyAsync(hc, counters.p, sizeof hc, cudaMemcpyDeviceToHost, st);
-    cudaError_t ce = cudaStreamSynchronize(st);
-    if (ce != cudaSuccess) { rc = set_err(h, B200ANN_ERR_CUDA, std::string("hnsw_build: ") + cudaGetErrorString(ce)); break; }
-    if (hc[0]) {
-      biggest = std::max<uint64_t>(biggest, hc[1]);
-      rev_offsets_kernel<<<(hc[0] + 255) / 256, 256, 0, st>>>(touched.p, counters.p, rcount, roff, counters.p + 2);
-      rev_group_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(rev_row.p, rev_src.p, rev_d.p, total, roff, rfill, g_src.p, g_d.p);
-      h->launches += 2;
-      rp.mcap = round_up((uint32_t)maxM0 + hc[1], 32);
-      rc = launch_reverse(h, rp, hc[0], ipm);
-      if (rc) break;
-    }
-    for (size_t i = s; i < e; i++)
-      if (levels[i] > maxlevel) { maxlevel = levels[i]; ep = (uint32_t)i; }   // :1262-1265
-    s = e;
+    CU_CHECK(h, cudaMalloc((void **)&ix->labels, n * 8));
+    ix->cap_labels = n;
+    CU_CHECK(h, cudaMemcpyAsync(ix->labels, labels_host_or_dev, n * 8, cudaMemcpyDefault, st));
   }
   unsigned long long hs[4] = {0, 0, 0, 0};
-  if (rc == 0) {
-    cudaMemcpyAsync(hs, stats.p, sizeof hs, cudaMemcpyDeviceToHost, st);
-    cudaError_t ce = cudaStreamSynchronize(st);
-    if (ce == cudaSuccess) ce = cudaGetLastError();
-    if (ce != cudaSuccess) rc = set_err(h, B200ANN_ERR_CUDA, std::string("hnsw_build: ") + cudaGetErrorString(ce));
-  }
+  uint64_t batches = 0, biggest = 0;
+  rc = hnsw_run_batches(h, ix, 0, levels, M, efc, ratio, bmax, hs, &batches, &biggest);
   if (rc) return rc;
-  guard.keep = true;
-  // install (the caller freed any previous HNSW graph)
-  ix->links0 = links0; ix->maxM0 = maxM0; ix->levels = d_levels; ix->upper_ptr = d_upper_ptr;
-  ix->upper_links = upper_links; ix->upper_rows = rows; ix->maxM = maxM; ix->labels = d_labels;
-  ix->hnsw_ep = ep; ix->maxlevel = maxlevel; ix->has_hnsw = true;
+  ix->has_hnsw = true;
   if (info8) {
-    info8[0] = hs[0]; info8[1] = hs[1]; info8[2] = hs[2]; info8[3] = batches; info8[4] = rows;
-    info8[5] = (uint64_t)maxlevel; info8[6] = ep; info8[7] = biggest;
+    info8[0] = hs[0]; info8[1] = hs[1]; info8[2] = hs[2]; info8[3] = batches; info8[4] = ix->upper_rows;
+    info8[5] = (uint64_t)ix->maxlevel; info8[6] = ix->hnsw_ep; info8[7] = biggest;
+  }
+  return 0;
+}
+
+// Appends nb rows to the index and links them into its HNSW graph in place: what nb addPoint calls do to a live
+// hnswlib index (hnswalg.h:1153-1267). data [nb, dstride] device memory. The level generator continues where the
+// build (or the previous append) left it. Any NSG graph / tensor-core cache of the index is dropped (their row set
+// changed). info8 as hnsw_build_launch (counters of this call).
+int hnsw_insert_launch(b200ann_handle *h, b200ann_index *ix, const float *data, size_t dstride, size_t nb,
+                       const uint64_t *labels_host_or_dev, size_t ratio, size_t bmax, uint64_t *info8) {
+  if (!ix->has_hnsw) return set_err(h, B200ANN_ERR_STATE, "hnsw_insert_batch: index has no HNSW graph (hnsw_build / set_hnsw first)");
+  if (ix->n + nb >= (1ull << 31)) return set_err(h, B200ANN_ERR_ARG, "hnsw_insert_batch: too many rows");
+  if (ratio == 0) ratio = 64;
+  if (bmax == 0) bmax = 8192;
+  cudaStream_t st = h->stream;
+  const size_t n_old = ix->n, n = n_old + nb;
+  const size_t M = ix->hnsw_M ? ix->hnsw_M : ix->maxM;
+  const size_t efc = ix->hnsw_efc ? ix->hnsw_efc : 200;
+  // vectors
+  {
+    size_t c = ix->cap_vec ? ix->cap_vec : n_old * ix->stride;
+    CU_CHECK(h, grow(&ix->vec, n_old * ix->stride, n * ix->stride, &c, st));
+    ix->cap_vec = c;
+    if (ix->stride != ix->dim) CU_CHECK(h, cudaMemsetAsync(ix->vec + n_old * ix->stride, 0, nb * ix->stride * 4, st));
+    CU_CHECK(h, cudaMemcpy2DAsync(ix->vec + n_old * ix->stride, ix->stride * 4, data, dstride * 4, ix->dim * 4, nb, cudaMemcpyDefault, st));
+  }
+  if (ix->graph) { cudaFree(ix->graph); ix->graph = nullptr; }
+  knn_tc_free(ix);
+  // labels: an index without a label array has label == row number
+  if (labels_host_or_dev || ix->labels) {
+    const bool had = ix->labels != nullptr;
+    size_t c = ix->cap_labels ? ix->cap_labels : (had ? n_old : 0);
+    CU_CHECK(h, grow(&ix->labels, had ? n_old : 0, n, &c, st));
+    ix->cap_labels = c;
+    if (!had) iota_u64_kernel<<<(unsigned)((n_old + 255) / 256), 256, 0, st>>>(ix->labels, 0, n_old);
+    if (labels_host_or_dev) CU_CHECK(h, cudaMemcpyAsync(ix->labels + n_old, labels_host_or_dev, nb * 8, cudaMemcpyDefault, st));
+    else iota_u64_kernel<<<(unsigned)((nb + 255) / 256), 256, 0, st>>>(ix->labels, n_old, n);
+  }
+  // capacities of arrays installed by b200ann_index_set_hnsw (exact fit)
+  if (!ix->cap_links0) { ix->cap_links0 = n_old * ix->maxM0; ix->cap_levels = n_old; ix->cap_uptr = n_old;
+                         ix->cap_upper = (ix->upper_rows ? ix->upper_rows : 1) * ix->maxM; }
+  if (!ix->upper_owner) {  // set_hnsw path: rebuild the owner of every upper row from the levels
+    std::vector<int32_t> lv(n_old);
+    CU_CHECK(h, cudaMemcpy(lv.data(), ix->levels, n_old * 4, cudaMemcpyDeviceToHost));
+    std::vector<uint32_t> up(n_old);
+    CU_CHECK(h, cudaMemcpy(up.data(), ix->upper_ptr, n_old * 4, cudaMemcpyDeviceToHost));
+    std::vector<uint32_t> owner(ix->upper_rows ? ix->upper_rows : 1, 0);
+    for (size_t i = 0; i < n_old; i++)
+      for (int l = 0; l < lv[i]; l++) owner[up[i] + l] = (uint32_t)i;
+    CU_CHECK(h, cudaMalloc((void **)&ix->upper_owner, owner.size() * 4));
+    ix->cap_owner = owner.size();
+    CU_CHECK(h, cudaMemcpy(ix->upper_owner, owner.data(), owner.size() * 4, cudaMemcpyHostToDevice));
+  }
+  ix->n = n;
+  std::vector<int32_t> levels;
+  draw_levels(ix, nb, M, levels);
+  int rc = hnsw_extend_arrays(h, ix, n_old, levels);
+  if (rc) { ix->n = n_old; return rc; }
+  unsigned long long hs[4] = {0, 0, 0, 0};
+  uint64_t batches = 0, biggest = 0;
+  rc = hnsw_run_batches(h, ix, n_old, levels, M, efc, ratio, bmax, hs, &batches, &biggest);
+  if (rc) return rc;
+  if (info8) {
+    info8[0] = hs[0]; info8[1] = hs[1]; info8[2] = hs[2]; info8[3] = batches; info8[4] = ix->upper_rows;
+    info8[5] = (uint64_t)ix->maxlevel; info8[6] = ix->hnsw_ep; info8[7] = biggest;
   }
   return 0;
 }

@@ -293,7 +293,12 @@ class Index:
         if self._ix is None or k > len(self._labels):
             raise RuntimeError(short)
         if filter is None and not self._deleted.any():            # hnswalg.h:1306 bare_bone_search
-            lab, d = self._ix.hnsw_search(q, k, max(self._ef, k))  # searchKnn uses max(ef_, k), :1309
+            try:
+                lab, d = self._ix.hnsw_search(q, k, max(self._ef, k))  # searchKnn uses max(ef_, k), :1309
+            except _B().B200AnnError as e:
+                if e.code == -4:                                  # B200ANN_ERR_FEWER: the reference's message, :646-648
+                    raise RuntimeError(short)
+                raise
         else:
             allow = ~self._deleted
             if filter is not None:                                # CustomFilterFunctor, bindings.cpp:129-142
@@ -419,6 +424,7 @@ class Index:
         if self._inited:
             self._build()
             st.update(cur_l=self._cur_l, max=self._max, M=self._M, efc=self._efc, seed=self._seed, vec=self._vec, labels=self._labels, deleted=self._deleted,
+                      allow_replace_deleted=self._allow_replace,   # bindings.cpp:491, :567 pickle it too
                       graph=self._ix.get_hnsw() if self._ix is not None else None)
         return st
 
@@ -426,7 +432,7 @@ class Index:
         Index.__init__(self, st["space"], st["dim"], st["device"])
         self._ef, self.num_threads = st["ef"], st["num_threads"]
         if st["inited"]:
-            self.init_index(st["max"], st["M"], st["efc"], st["seed"])
+            self.init_index(st["max"], st["M"], st["efc"], st["seed"], st.get("allow_replace_deleted", False))
             self._vec, self._labels, self._deleted = st["vec"], st["labels"], st["deleted"]
             self._lookup = {int(l): i for i, l in enumerate(self._labels.tolist())}
             self._graph = st["graph"]

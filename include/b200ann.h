@@ -86,6 +86,17 @@ int b200ann_index_set_hnsw(b200ann_index_t ix, const uint32_t *links0, size_t ma
  * upper rows, maxlevel, entry point, largest reverse-link group}. */
 int b200ann_hnsw_build(b200ann_handle_t h, b200ann_index_t ix, size_t M, size_t ef_construction, uint32_t random_seed,
                        size_t ratio, size_t bmax, const uint64_t *labels /*[h|d] or NULL*/, uint64_t *info /*[h]*/);
+/* replaces nb addPoint calls on a LIVE hnswlib index (hnswalg.h:954-992 / :1153-1267): appends nb rows (data [nb,
+ * stride], labels [nb] or NULL = row numbers) to the index and links them into the HNSW graph it already holds, in
+ * place - the device arrays grow with doubling capacity, the rows already linked are not touched except through the
+ * reverse links the new points add, and the level generator continues where the build / the previous append left it
+ * (a graph installed with b200ann_index_set_hnsw starts a fresh generator with seed 100 like the reference's load
+ * ctor). The new rows are inserted with the batch schedule of b200ann_hnsw_build (one batch for nb <= n/64).
+ * ef_construction: 0 = the value of the build (200 for an installed graph). Any NSG graph of the index is dropped.
+ * b200ann_index_size grows by nb. info (optional, 8 x u64): as b200ann_hnsw_build, counters of this call. */
+int b200ann_hnsw_insert_batch(b200ann_handle_t h, b200ann_index_t ix, const float *data /*[h|d]*/, size_t stride,
+                              const uint64_t *labels /*[h|d] or NULL*/, size_t nb, size_t ef_construction,
+                              uint64_t *info /*[h]*/);
 /* sizes of the index's HNSW graph: {maxM0, maxM, upper_rows, maxlevel, entry point} */
 int b200ann_index_hnsw_shape(b200ann_index_t ix, uint64_t *out5 /*[h]*/);
 /* copy the HNSW graph back in the layout b200ann_index_set_hnsw takes (what HierarchicalNSW::saveIndex

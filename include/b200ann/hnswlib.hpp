@@ -13,6 +13,7 @@
 //   has fewer than k results, bindings.cpp:646-648)
 #ifndef B200ANN_HNSWLIB_HPP
 #define B200ANN_HNSWLIB_HPP
+#include <atomic>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -389,9 +390,10 @@ class BruteforceSearch<int> : public AlgorithmInterface<int> {
 // written by HierarchicalNSW::saveIndex (:685-713); search it on the GPU; write it back in the same format.
 // addPoint copies the vector (like :1204) into a host staging area; the graph is built on the GPU
 // (b200ann_hnsw_build: same level sequence as the reference, batched insertion) by build(), or lazily by the
-// first searchKnn / saveIndex after an addPoint. Adding a point to a built index rebuilds it on the next use:
-// add in bulk, then search. addPoint with an existing label replaces that element's vector (the reference's
-// updatePoint, :1158-1175, re-links in place).
+// first searchKnn / saveIndex after an addPoint. Points added to a built index are linked into the live device graph
+// in place on the next use (b200ann_hnsw_insert_batch: what addPoint does to a live hnswlib index, :1153-1267).
+// addPoint with an existing label replaces that element's vector (the reference's updatePoint, :1158-1175, re-links
+// in place; here an update or a replaced deleted slot re-links everything on the next use).
 template <typename dist_t>
 class HierarchicalNSW : public AlgorithmInterface<dist_t> {
  public:
@@ -400,7 +402,10 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
   double mult_ = 0;
   int maxlevel_ = -1;
   tableint enterpoint_node_ = 0;
-  std::vector<int> element_levels_;
+  std::vector<int> element_levels_;   // valid after saveIndex / loadIndex (the graph lives on the device)
+  // hnswalg.h:65-66: distance evaluations and expanded nodes of every search so far
+  mutable std::atomic<long> metric_distance_computations{0};
+  mutable std::atomic<long> metric_hops{0};
 
   // construction ctor (hnswalg.h:89-144)
   HierarchicalNSW(SpaceInterface<dist_t> *s, size_t max_elements, size_t M = 16, size_t ef_construction = 200,
@@ -493,13 +498,15 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
         std::memcpy(&upper_links_[base], p + 4, (size_t)cnt * 4);
       }
     }
-    dirty_ = false;
+    needs_rebuild_ = false;
+    built_count_ = n;
+    host_graph_valid_ = true;
     upload();
   }
 
   // hnswalg.h:685-713, byte-compatible with the reference's loader
   void saveIndex(const std::string &location) override {
-    { std::unique_lock<std::mutex> lock(mu_); build_locked(nullptr); }
+    { std::unique_lock<std::mutex> lock(mu_); build_locked(nullptr); sync_host_graph_locked(); }
     std::ofstream out(location, std::ios::binary);
     const size_t n = cur_element_count;
     size_t size_links_level0 = maxM0_ * 4 + 4, data_size = dim_ * sizeof(float);
@@ -554,7 +561,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
       label_lookup_[label] = id;
       deleted_[id] = 0; num_deleted_--;      // unmarkDeletedInternal :989
       std::memcpy(&vec_[id * dim_], datapoint, dim_ * sizeof(float));
-      dirty_ = true;
+      needs_rebuild_ = true;
       return;
     }
     auto it = label_lookup_.find(label);
@@ -563,7 +570,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
         throw std::runtime_error("Can't use addPoint to update deleted elements if replacement of deleted elements is enabled.");
       if (deleted_[it->second]) { deleted_[it->second] = 0; num_deleted_--; }  // :1166-1168: an update un-deletes
       std::memcpy(&vec_[it->second * dim_], datapoint, dim_ * sizeof(float));
-      dirty_ = true;
+      if (it->second < built_count_) needs_rebuild_ = true;  // a linked element moved: re-link (updatePoint)
       return;
     }
     if (cur_element_count >= max_elements_) throw std::runtime_error("The number of elements exceeds the specified limit");  // :1178
@@ -571,8 +578,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     vec_.insert(vec_.end(), (const float *)datapoint, (const float *)datapoint + dim_);
     labels_.push_back(label);
     deleted_.push_back(0);
-    cur_element_count++;
-    dirty_ = true;
+    cur_element_count++;   // linked into the device graph by the next build_locked()
   }
   // hnswalg.h:853-911 markDelete / :893-922 unmarkDelete: the element stays in the graph and is walked through, but is
   // never returned (searchBaseLayerST<false>); same exceptions as the reference
@@ -627,13 +633,15 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     std::unique_lock<std::mutex> lock(mu_);
     build_locked(nullptr);
     if (!ix_) throw std::runtime_error("HierarchicalNSW::searchKnnBatch: the index is empty");
+    std::vector<uint32_t> st(nq * 2, 0u);
     if (!num_deleted_ && !isIdAllowed) {  // :1306 bare_bone_search
-      detail::check(gpu_.h, b200ann_hnsw_search(gpu_.h, ix_, queries, nq, dim_, k, ef_, lab.data(), dists, nullptr), "HierarchicalNSW::searchKnn");
+      detail::check(gpu_.h, b200ann_hnsw_search(gpu_.h, ix_, queries, nq, dim_, k, ef_, lab.data(), dists, st.data()), "HierarchicalNSW::searchKnn");
     } else {
       std::vector<uint32_t> allow = allow_bitmap(isIdAllowed);
       detail::check(gpu_.h, b200ann_hnsw_search_filtered(gpu_.h, ix_, queries, nq, dim_, k, ef_, allow.data(), lab.data(), dists,
-                                                         nullptr, nullptr), "HierarchicalNSW::searchKnn (filtered)");
+                                                         st.data(), nullptr), "HierarchicalNSW::searchKnn (filtered)");
     }
+    count_metrics(st);
     for (size_t i = 0; i < nq * k; i++) labels[i] = (labeltype)lab[i];
   }
   // hnswalg.h:1270-1324: max-heap of (distance,label), at most k entries; no exception when fewer than k exist
@@ -643,20 +651,22 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     if (cur_element_count == 0) return res;
     std::vector<uint64_t> lab(k);
     std::vector<dist_t> d(k);
+    std::vector<uint32_t> st(2, 0u);
     {
       std::unique_lock<std::mutex> lock(mu_);
       build_locked(nullptr);
       if (!num_deleted_ && !isIdAllowed) {
         size_t kk = k < cur_element_count ? k : cur_element_count;
-        int rc = b200ann_hnsw_search(gpu_.h, ix_, (const float *)query_data, 1, dim_, kk, ef_, lab.data(), d.data(), nullptr);
+        int rc = b200ann_hnsw_search(gpu_.h, ix_, (const float *)query_data, 1, dim_, kk, ef_, lab.data(), d.data(), st.data());
         if (rc != 0 && rc != B200ANN_ERR_FEWER) detail::check(gpu_.h, rc, "HierarchicalNSW::searchKnn");
         for (size_t i = kk; i < k; i++) lab[i] = ~(uint64_t)0;
       } else {
         std::vector<uint32_t> allow = allow_bitmap(isIdAllowed);
         detail::check(gpu_.h, b200ann_hnsw_search_filtered(gpu_.h, ix_, (const float *)query_data, 1, dim_, k, ef_, allow.data(),
-                                                           lab.data(), d.data(), nullptr, nullptr), "HierarchicalNSW::searchKnn (filtered)");
+                                                           lab.data(), d.data(), st.data(), nullptr), "HierarchicalNSW::searchKnn (filtered)");
       }
     }
+    count_metrics(st);
     for (size_t i = 0; i < k; i++)
       if (lab[i] != ~(uint64_t)0) res.emplace(d[i], (labeltype)lab[i]);
     return res;
@@ -673,6 +683,10 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     build_locked(nullptr);
     const size_t n = cur_element_count;
     bool identity = true;
+    for (size_t i = 0; i < n && identity; i++) identity = labels_[i] == i;
+    if (identity) return false;
+    sync_host_graph_locked();
+    identity = true;
     std::vector<unsigned char> seen(n, 0);
     for (size_t i = 0; i < n; i++) {
       const size_t l = labels_[i];
@@ -736,17 +750,45 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
                                                  upper_links_.empty() ? nullptr : upper_links_.data(), upper_links_.size() / (maxM_ ? maxM_ : 1),
                                                  maxM_, lab.data(), enterpoint_node_, maxlevel_), "b200ann_index_set_hnsw");
   }
-  // GPU construction of the staged points; caller holds mu_
+  void count_metrics(const std::vector<uint32_t> &st) const {
+    long nd = 0, nh = 0;
+    for (size_t i = 0; i + 1 < st.size(); i += 2) { nd += st[i]; nh += st[i + 1]; }
+    metric_distance_computations += nd;
+    metric_hops += nh;
+  }
+  // Brings the device graph up to date with the staged points; caller holds mu_. Points appended since the last call
+  // are linked into the live graph in place (b200ann_hnsw_insert_batch); an updated vector or a replaced deleted
+  // slot re-links everything (b200ann_hnsw_build).
   void build_locked(uint64_t *info8) const {
-    if (!dirty_) return;
     HierarchicalNSW *self = const_cast<HierarchicalNSW *>(this);
-    if (self->ix_) { b200ann_index_destroy(self->ix_); self->ix_ = nullptr; }
     const size_t n = cur_element_count;
-    if (n == 0) { dirty_ = false; return; }
-    detail::check(gpu_.h, b200ann_index_create(gpu_.h, vec_.data(), n, dim_, dim_, metric_, &self->ix_), "b200ann_index_create");
-    std::vector<uint64_t> lab(labels_.begin(), labels_.end());
-    detail::check(gpu_.h, b200ann_hnsw_build(gpu_.h, ix_, M_, ef_construction_, (uint32_t)seed_, 0, 0, lab.data(), info8),
-                  "HierarchicalNSW::addPoint (b200ann_hnsw_build)");
+    if (n == 0) return;
+    if (ix_ && !needs_rebuild_ && built_count_ == n) return;
+    if (ix_ && !needs_rebuild_ && built_count_ > 0 && built_count_ < n) {
+      std::vector<uint64_t> lab(labels_.begin() + built_count_, labels_.end());
+      detail::check(gpu_.h, b200ann_hnsw_insert_batch(gpu_.h, ix_, &vec_[built_count_ * dim_], dim_, lab.data(), n - built_count_,
+                                                      ef_construction_, info8), "HierarchicalNSW::addPoint (b200ann_hnsw_insert_batch)");
+    } else {
+      if (self->ix_) { b200ann_index_destroy(self->ix_); self->ix_ = nullptr; }
+      detail::check(gpu_.h, b200ann_index_create(gpu_.h, vec_.data(), n, dim_, dim_, metric_, &self->ix_), "b200ann_index_create");
+      std::vector<uint64_t> lab(labels_.begin(), labels_.end());
+      detail::check(gpu_.h, b200ann_hnsw_build(gpu_.h, ix_, M_, ef_construction_, (uint32_t)seed_, 0, 0, lab.data(), info8),
+                    "HierarchicalNSW::addPoint (b200ann_hnsw_build)");
+    }
+    uint64_t shape[5];
+    detail::check(gpu_.h, b200ann_index_hnsw_shape(ix_, shape), "b200ann_index_hnsw_shape");
+    self->maxlevel_ = (int)shape[3];
+    self->enterpoint_node_ = (tableint)shape[4];
+    self->gen_++;
+    self->built_count_ = n;
+    self->needs_rebuild_ = false;
+    self->host_graph_valid_ = false;
+  }
+  // host copy of the graph (saveIndex, relabel_to_labels): fetched from the device only when needed; caller holds mu_
+  void sync_host_graph_locked() const {
+    if (host_graph_valid_ || !ix_) return;
+    HierarchicalNSW *self = const_cast<HierarchicalNSW *>(this);
+    const size_t n = cur_element_count;
     uint64_t shape[5];
     detail::check(gpu_.h, b200ann_index_hnsw_shape(ix_, shape), "b200ann_index_hnsw_shape");
     self->links0_.assign(n * maxM0_, B200ANN_INVALID);
@@ -756,10 +798,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     detail::check(gpu_.h, b200ann_index_get_hnsw(ix_, self->links0_.data(), lv.data(), self->upper_ptr_.data(),
                                                  shape[2] ? self->upper_links_.data() : nullptr, nullptr), "b200ann_index_get_hnsw");
     self->element_levels_.assign(lv.begin(), lv.end());
-    self->maxlevel_ = (int)shape[3];
-    self->enterpoint_node_ = (tableint)shape[4];
-    self->gen_++;
-    dirty_ = false;
+    self->host_graph_valid_ = true;
   }
   detail::Gpu gpu_;
   int metric_ = 0;
@@ -771,7 +810,9 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
   std::unordered_map<labeltype, size_t> label_lookup_;
   std::vector<uint32_t> links0_, upper_ptr_, upper_links_;
   b200ann_index_t ix_ = nullptr;
-  mutable bool dirty_ = false;
+  mutable size_t built_count_ = 0;        // elements linked into the device graph
+  mutable bool needs_rebuild_ = false;    // an existing element's vector changed since the graph was built
+  mutable bool host_graph_valid_ = false; // links0_ / upper_* / element_levels_ mirror the device graph
   mutable std::mutex mu_;
 };
 

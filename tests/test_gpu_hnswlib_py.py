@@ -272,6 +272,7 @@ def test_replace_deleted(hnswlib, tmp_path):
     ix2.load_index(path, max_elements=2 * ne, allow_replace_deleted=True)
     ix2.set_ef(100)
     l4, d4 = labels[3][:len(l3)], data[3][:len(l3)]
+    ix2 = pickle.loads(pickle.dumps(ix2))               # allow_replace_deleted survives pickling (bindings.cpp:491, :567)
     ix2.add_items(d4, l4, replace_deleted=True)
     assert ix2.get_current_count() == 2 * ne
     got = ix2.knn_query(d4, k=1)[0].flatten()

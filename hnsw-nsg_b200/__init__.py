@@ -55,6 +55,8 @@ _lib.b200ann_nndescent.argtypes = [_vp, _vp, _sz, _sz, _sz, _sz, _sz, C.c_uint32
 _lib.b200ann_nsg_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, C.c_uint32, _vp, _vp, _vp]
 _lib.b200ann_hnsw_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _vp, _vp, _vp]
 _lib.b200ann_hnsw_search_filtered.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _vp, _vp, _vp, _vp, _vp]
+_lib.b200ann_hnsw_search_epsilon.argtypes = [_vp, _vp, _vp, _sz, _sz, C.c_float, _sz, _sz, _vp, C.c_int, _vp, _vp,
+                                             _vp, _vp]
 _u32 = C.c_uint32
 _lib.b200ann_nsg_search_from.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _u32, _vp, _vp, _vp, _vp]
 _lib.b200ann_nsg_search_clustered.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _u32, _vp, _vp, _vp, _vp, _vp, _vp]
@@ -84,6 +86,7 @@ EXPORTS = [
     "b200ann_index_size", "b200ann_index_dim", "b200ann_index_set_graph", "b200ann_index_get_graph",
     "b200ann_index_set_hnsw", "b200ann_bf_knn", "b200ann_knn_graph", "b200ann_nsg_search", "b200ann_hnsw_search",
     "b200ann_hnsw_search_filtered",
+    "b200ann_hnsw_search_epsilon",
     "b200ann_set_link_visited_bits", "b200ann_nsg_build", "b200ann_nsg_init_ep", "b200ann_nsg_link",
     "b200ann_nsg_interinsert", "b200ann_nsg_finish", "b200ann_merge_topk", "b200ann_nsg_search_from",
     "b200ann_hybrid_search", "b200ann_set_knn_mode", "b200ann_knn_last_stats", "b200ann_nndescent",
@@ -424,6 +427,31 @@ class Index:
         self.h._check(_lib.b200ann_hnsw_search_filtered(self.h._h, self._ix, _ptr(q), q.shape[0], q.shape[1], k, ef,
                                                         _ptr(words), _ptr(lab), _ptr(d), _ptr(st), _ptr(bad)))
         return (lab, d, bad, st) if want_stats else (lab, d, bad)
+
+    def hnsw_search_epsilon(self, q, epsilon, min_num_candidates, max_num_candidates, allow=None, internal_ids=False,
+                            want_stats=False):
+        """searchStopConditionClosest(query, EpsilonSearchStopCondition(epsilon, min, max), filter) batched
+        (hnswalg.h:1327-1378, stop_condition.h:219-275). -> (labels [nq,max], dists [nq,max], counts [nq][, stats]);
+        row q holds counts[q] results ascending by distance, all within epsilon; the rest is ~0 / inf.
+        internal_ids=True returns internal ids like the reference does."""
+        q = np.ascontiguousarray(q, np.float32)
+        words = None
+        if allow is not None:
+            a = np.asarray(allow).astype(bool)
+            assert a.shape == (self.n,)
+            bits = np.packbits(a, bitorder="little")
+            words = np.zeros(((self.n + 31) // 32) * 4, np.uint8)
+            words[:len(bits)] = bits
+            words = words.view(np.uint32)
+        mx = int(max_num_candidates)
+        lab = np.empty((q.shape[0], mx), np.uint64)
+        d = np.empty((q.shape[0], mx), np.float32)
+        cnt = np.zeros(q.shape[0], np.uint32)
+        st = np.zeros((q.shape[0], 2), np.uint32) if want_stats else None
+        self.h._check(_lib.b200ann_hnsw_search_epsilon(self.h._h, self._ix, _ptr(q), q.shape[0], q.shape[1],
+                                                       float(epsilon), int(min_num_candidates), mx, _ptr(words),
+                                                       1 if internal_ids else 0, _ptr(lab), _ptr(d), _ptr(cnt), _ptr(st)))
+        return (lab, d, cnt, st) if want_stats else (lab, d, cnt)
 
     def nsg_search_from(self, q, entry, K, L, seed=0, want_stats=False):
         """IndexNSG::SearchFromEnterpoint batched: query i starts at entry[i]"""

@@ -627,30 +627,37 @@ int b200ann_hnsw_search(b200ann_handle_t h, b200ann_index_t ix, const float *q, 
   return 0;
 }
 
-int b200ann_hnsw_search_filtered(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_t nq, size_t qstride, size_t k,
-                                 size_t ef, const uint32_t *allow, uint64_t *labels, float *dists, uint32_t *stats,
-                                 uint8_t *inexact) {
-  if (!h || !ix) return B200ANN_ERR_ARG;
-  if (!ix->has_hnsw) return set_err(h, B200ANN_ERR_STATE, "hnsw_search_filtered: index has no HNSW graph (set_hnsw / hnsw_build first)");
-  if (!q || !allow || !labels || !dists || k == 0 || qstride < ix->dim)
-    return set_err(h, B200ANN_ERR_ARG, "hnsw_search_filtered: need q, allow, labels, dists, k > 0, qstride >= dim");
-  if (inexact && is_device_ptr(inexact)) return set_err(h, B200ANN_ERR_ARG, "hnsw_search_filtered: inexact must be host memory");
-  if (nq == 0) return 0;
+// shared by the filtered and the epsilon entry points: two passes (shared-memory heaps, then global-memory heaps for the
+// queries the first pass could not prove exact). allow == NULL: every element may be returned.
+static int filtered_common(b200ann_handle_t h, b200ann_index_t ix, const char *who, const float *q, size_t nq, size_t qstride,
+                           size_t k, size_t ef, const uint32_t *allow, uint64_t *labels, float *dists, uint32_t *stats,
+                           uint8_t *inexact, float eps, size_t min_cand, uint32_t *counts, bool internal_ids) {
   CU_CHECK(h, cudaSetDevice(h->device));
-  InArg<float> qin; InArg<uint32_t> ain; OutArg<uint64_t> ol; OutArg<float> od; OutArg<uint32_t> os;
+  InArg<float> qin; InArg<uint32_t> ain; OutArg<uint64_t> ol; OutArg<float> od; OutArg<uint32_t> os, oc;
   DevBuf<uint8_t> flags;
+  DevBuf<uint32_t> ones;
+  const size_t awords = (ix->n + 31) / 32;
   CU_CHECK(h, qin.stage(q, nq * qstride, h->stream));
-  CU_CHECK(h, ain.stage(allow, (ix->n + 31) / 32, h->stream));
+  const uint32_t *adev;
+  if (allow) {
+    CU_CHECK(h, ain.stage(allow, awords, h->stream));
+    adev = ain.d;
+  } else {
+    CU_CHECK(h, ones.alloc(awords, h->stream));
+    CU_CHECK(h, cudaMemsetAsync(ones.p, 0xff, awords * 4, h->stream));
+    adev = ones.p;
+  }
   CU_CHECK(h, ol.stage(labels, nq * k, h->stream));
   CU_CHECK(h, od.stage(dists, nq * k, h->stream));
   CU_CHECK(h, os.stage(stats, nq * 2, h->stream));
+  CU_CHECK(h, oc.stage(counts, nq, h->stream));
   CU_CHECK(h, flags.alloc(nq, h->stream));
   std::vector<uint8_t> hf(nq);
   CallTimer t(h);
   size_t left = 0;
   for (int pass = 0; pass < 2; pass++) {
-    int rc = launch_hnsw_search_filtered(h, ix, qin.d, nq, qstride, k, ef, ain.d, 0, pass == 1, pass ? flags.p : nullptr,
-                                         ol.d, od.d, os.d, flags.p, nullptr);
+    int rc = launch_hnsw_search_filtered(h, ix, qin.d, nq, qstride, k, ef, adev, 0, pass == 1, pass ? flags.p : nullptr,
+                                         ol.d, od.d, os.d, flags.p, nullptr, eps, min_cand, oc.d, internal_ids);
     if (rc) return rc;
     CU_CHECK(h, cudaMemcpyAsync(hf.data(), flags.p, nq, cudaMemcpyDeviceToHost, h->stream));
     CU_CHECK(h, cudaStreamSynchronize(h->stream));
@@ -662,12 +669,43 @@ int b200ann_hnsw_search_filtered(b200ann_handle_t h, b200ann_index_t ix, const f
   CU_CHECK(h, ol.finish(h->stream));
   CU_CHECK(h, od.finish(h->stream));
   CU_CHECK(h, os.finish(h->stream));
+  CU_CHECK(h, oc.finish(h->stream));
   CU_CHECK(h, t.sync());
   if (inexact) std::memcpy(inexact, hf.data(), nq);
-  else if (left)
-    return set_err(h, B200ANN_ERR_CAPACITY, "hnsw_search_filtered: the filter is too selective for the graph walk on some queries "
-                                            "(candidate set overflow); pass `inexact` to see which, or scan the allowed rows with bf_knn");
+  else if (left) {
+    std::string m = std::string(who) + ": the filter is too selective for the graph walk on some queries "
+                    "(candidate set overflow); pass `inexact` to see which, or scan the allowed rows with bf_knn";
+    return set_err(h, B200ANN_ERR_CAPACITY, m.c_str());
+  }
   return 0;
+}
+
+int b200ann_hnsw_search_filtered(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_t nq, size_t qstride, size_t k,
+                                 size_t ef, const uint32_t *allow, uint64_t *labels, float *dists, uint32_t *stats,
+                                 uint8_t *inexact) {
+  if (!h || !ix) return B200ANN_ERR_ARG;
+  if (!ix->has_hnsw) return set_err(h, B200ANN_ERR_STATE, "hnsw_search_filtered: index has no HNSW graph (set_hnsw / hnsw_build first)");
+  if (!q || !allow || !labels || !dists || k == 0 || qstride < ix->dim)
+    return set_err(h, B200ANN_ERR_ARG, "hnsw_search_filtered: need q, allow, labels, dists, k > 0, qstride >= dim");
+  if (inexact && is_device_ptr(inexact)) return set_err(h, B200ANN_ERR_ARG, "hnsw_search_filtered: inexact must be host memory");
+  if (nq == 0) return 0;
+  return filtered_common(h, ix, "hnsw_search_filtered", q, nq, qstride, k, ef, allow, labels, dists, stats, inexact, INFINITY, 0,
+                         nullptr, false);
+}
+
+int b200ann_hnsw_search_epsilon(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_t nq, size_t qstride, float epsilon,
+                                size_t min_num_candidates, size_t max_num_candidates, const uint32_t *allow, int internal_ids,
+                                uint64_t *labels, float *dists, uint32_t *counts, uint32_t *stats) {
+  if (!h || !ix) return B200ANN_ERR_ARG;
+  if (!ix->has_hnsw) return set_err(h, B200ANN_ERR_STATE, "hnsw_search_epsilon: index has no HNSW graph (set_hnsw / hnsw_build first)");
+  if (!q || !labels || !dists || !counts || max_num_candidates == 0 || qstride < ix->dim)
+    return set_err(h, B200ANN_ERR_ARG, "hnsw_search_epsilon: need q, labels, dists, counts, max_num_candidates > 0, qstride >= dim");
+  if (min_num_candidates > max_num_candidates)  // the reference asserts this (stop_condition.h:227)
+    return set_err(h, B200ANN_ERR_ARG, "hnsw_search_epsilon: min_num_candidates > max_num_candidates");
+  if (epsilon != epsilon) return set_err(h, B200ANN_ERR_ARG, "hnsw_search_epsilon: epsilon is NaN");
+  if (nq == 0) return 0;
+  return filtered_common(h, ix, "hnsw_search_epsilon", q, nq, qstride, max_num_candidates, max_num_candidates, allow, labels, dists,
+                         stats, nullptr, epsilon, min_num_candidates, counts, internal_ids != 0);
 }
 
 }  // extern "C"

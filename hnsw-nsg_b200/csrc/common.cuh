@@ -169,7 +169,8 @@ int launch_gather_probe(b200ann_handle *h, const b200ann_index *ix, uint64_t row
 int launch_hnsw_search_filtered(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
                                 size_t k, size_t ef, const uint32_t *allow_bits, size_t ccap, bool big,
                                 const uint8_t *only, uint64_t *labels, float *dists, uint32_t *stats, uint8_t *inexact,
-                                size_t *ccap_used);
+                                size_t *ccap_used, float eps = INFINITY, size_t min_cand = 0, uint32_t *counts = nullptr,
+                                bool internal_ids = false);
 int launch_merge_topk(b200ann_handle *h, const float *d, const uint32_t *ids, size_t parts, size_t nq, size_t k, size_t kout,
                       float *out_d, uint32_t *out_i);
 int launch_bf_knn(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,

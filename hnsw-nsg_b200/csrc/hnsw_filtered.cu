@@ -34,6 +34,11 @@ struct FilterParams {
   uint32_t *gheap_i;
   uint8_t *inexact;        // [nq]
   const uint8_t *only;     // NULL, or [nq]: search only the queries with only[q] != 0 (retry pass)
+  // EpsilonSearchStopCondition (stop_condition.h:219-275) with max_num_candidates = ef: eps = +inf, min_cand = 0
+  // switches it off (the plain filtered search). counts [nq] = results left by filter_results, or NULL.
+  float eps;
+  uint32_t min_cand;
+  uint32_t *counts;
 };
 
 __host__ __device__ inline uint32_t fsmem_words(const FilterParams &p) {
@@ -163,9 +168,11 @@ __global__ void __launch_bounds__(FW * 32) hnsw_filtered_kernel(const FilterPara
 
     for (;;) {
       const float c0d = nc ? cd[0] : INFINITY;
-      if (dmin < INFINITY && (nc == 0 || dmin <= c0d) && !(dmin > LB && nt == ef)) bad = true;
+      if (dmin < INFINITY && (nc == 0 || dmin <= c0d) && !(dmin > LB && nt == ef) &&
+          !(dmin > fp.eps && nt >= fp.min_cand)) bad = true;
       if (nc == 0) break;
-      if (c0d > LB && nt == ef) break;  // :355
+      if (c0d > LB && nt == ef) break;  // :355, stop_condition.h:243
+      if (c0d > fp.eps && nt >= fp.min_cand) break;  // stop_condition.h:247: out of the epsilon ball, enough seen
       const uint32_t node = ci[0];
       __syncwarp();
       if (lane == 0) heap_pop(cd, ci, nc);
@@ -232,14 +239,22 @@ __global__ void __launch_bounds__(FW * 32) hnsw_filtered_kernel(const FilterPara
       }
     }
 
+    // filter_results (stop_condition.h:265-272): the list is ascending, so dropping the tail beyond epsilon leaves
+    // the entries with distance <= epsilon (NaN-free data); nt <= ef = max_num_candidates already
+    uint32_t nres = 0;
+    for (uint32_t i0 = 0; i0 < nt; i0 += 32) {
+      uint32_t i = i0 + lane;
+      nres += __popc(__ballot_sync(0xffffffffu, i < nt && !(b.pool_d[i] > fp.eps)));
+    }
     for (uint32_t i = lane; i < p.K; i += 32) {
-      bool ok = i < nt;
+      bool ok = i < nres;
       uint32_t id = ok ? b.pool_i[i] : INVALID_ID;
       p.labels_out[(size_t)qi * p.K + i] = ok ? (p.labels ? __ldg(p.labels + id) : (uint64_t)id) : ~(uint64_t)0;
       if (p.dists) p.dists[(size_t)qi * p.K + i] = ok ? b.pool_d[i] : INFINITY;
     }
     if (lane == 0) {
       fp.inexact[qi] = bad ? 1 : 0;
+      if (fp.counts) fp.counts[qi] = nres < p.K ? nres : p.K;
       if (p.stats) { p.stats[2 * (size_t)qi] = b.n_dist; p.stats[2 * (size_t)qi + 1] = b.n_hops; }
     }
     __syncwarp();
@@ -280,14 +295,18 @@ int launch_fdim(b200ann_handle *h, FilterParams &fp) {
 int launch_hnsw_search_filtered(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
                                 size_t k, size_t ef, const uint32_t *allow_bits, size_t ccap, bool big,
                                 const uint8_t *only, uint64_t *labels, float *dists, uint32_t *stats, uint8_t *inexact,
-                                size_t *ccap_used) {
+                                size_t *ccap_used, float eps, size_t min_cand, uint32_t *counts, bool internal_ids) {
   FilterParams fp = {};
+  fp.eps = eps; fp.min_cand = (uint32_t)min_cand; fp.counts = counts;
   SearchParams &p = fp.s;
+  // epsilon mode (counts given): k is only the row stride of the outputs, the walk keeps ef = max_num_candidates
+  // results; more than n + 1 can never be held, and with n + 1 slots "nt == ef" stays false like in the reference
   size_t L = ef > k ? ef : k;
+  if (counts) L = ef < ix->n + 1 ? ef : ix->n + 1;
   p.vec = ix->vec; p.stride = ix->stride; p.n = (uint32_t)ix->n; p.nch = (int)((ix->dim + 3) / 4);
   p.graph = ix->links0; p.gstride = (uint32_t)ix->maxM0; p.ep = ix->hnsw_ep;
   p.upper_links = ix->upper_links; p.upper_ptr = ix->upper_ptr; p.maxM = (uint32_t)ix->maxM;
-  p.maxlevel = ix->maxlevel; p.labels = ix->labels;
+  p.maxlevel = ix->maxlevel; p.labels = internal_ids ? nullptr : ix->labels;
   p.q = q; p.qstride = qstride; p.nq = (uint32_t)nq; p.dim = (uint32_t)ix->dim;
   p.K = (uint32_t)k; p.L = (uint32_t)L; p.seed = 0; p.hbits = 0;
   size_t cc = ix->maxM0 > ix->maxM ? ix->maxM0 : ix->maxM;
@@ -295,11 +314,16 @@ int launch_hnsw_search_filtered(b200ann_handle *h, const b200ann_index *ix, cons
   p.pool_cap = round_up((uint32_t)L + 1, 32);
   p.labels_out = labels; p.dists = dists; p.stats = stats;
   fp.allow = allow_bits; fp.inexact = inexact; fp.only = only;
-  fp.wpb = FW;
   fp.vwords = round_up((uint32_t)((ix->n + 31) / 32), 4);
   const size_t fixed = smem_words(p.pool_cap, p.cand_cap, 0);
+  // warps per block: FW, fewer when one warp's result list is large (an epsilon search with max_num_candidates in the
+  // thousands), so that the list plus a candidate heap of >= 512 entries still fits the block's 227 KB
+  fp.wpb = FW;
+  while (fp.wpb > 1 && fixed + 2 * 512 > 227 * 1024 / 4 / fp.wpb) fp.wpb >>= 1;
   const size_t budget = 227 * 1024 / 4 / fp.wpb;
-  if (fixed + 2 * 64 > budget) return set_err(h, B200ANN_ERR_ARG, "hnsw_search_filtered: ef / degree need more than 227 KB shared memory per block");
+  if (fixed + 2 * 64 > budget)
+    return set_err(h, B200ANN_ERR_ARG, "hnsw_search_filtered / epsilon: ef (max_num_candidates) / degree need more than 227 KB "
+                                       "shared memory per query (about 28000 results)");
   size_t warps;
   DevBuf<float> gd; DevBuf<uint32_t> gi;
   if (!big) {

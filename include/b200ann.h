@@ -194,6 +194,23 @@ int b200ann_hnsw_search_filtered(b200ann_handle_t h, b200ann_index_t ix, const f
                                  uint64_t *labels /*[h|d]*/, float *dists /*[h|d]*/, uint32_t *stats /*[h|d]*/,
                                  uint8_t *inexact /*[h] or NULL*/);
 
+/* replaces hnswlib::HierarchicalNSW::searchStopConditionClosest(query, EpsilonSearchStopCondition(epsilon, min, max),
+ * isIdAllowed) for a batch of queries (hnswalg.h:1327-1378 -> searchBaseLayerST<false>(.., ef = 0, filter, stop
+ * condition) :309-440; stop_condition.h:219-275): a range search that walks like a search with ef =
+ * max_num_candidates and also stops once the closest open candidate lies outside the epsilon ball and at least
+ * min_num_candidates results are held; afterwards results farther than epsilon are dropped (filter_results).
+ * epsilon is in the index's distance (squared L2, or 1 - inner product). allow = the bitmap of
+ * b200ann_hnsw_search_filtered, or NULL (no filter functor, nothing deleted). Output rows have max_num_candidates
+ * slots, ascending by distance, counts[q] of them valid, the rest ~0 / +inf. internal_ids != 0 returns internal ids
+ * instead of labels - what the reference does (it copies the (dist, tableint) pairs of top_candidates into the
+ * result without getExternalLabel, hnswalg.h:1368-1371); 0 returns labels. A query the bounded first pass could not
+ * prove exact is searched again like in b200ann_hnsw_search_filtered; B200ANN_ERR_CAPACITY if one stayed unproven. */
+int b200ann_hnsw_search_epsilon(b200ann_handle_t h, b200ann_index_t ix, const float *q /*[h|d]*/, size_t nq,
+                                size_t qstride, float epsilon, size_t min_num_candidates, size_t max_num_candidates,
+                                const uint32_t *allow /*[h|d] or NULL*/, int internal_ids,
+                                uint64_t *labels /*[h|d] [nq,max]*/, float *dists /*[h|d] [nq,max]*/,
+                                uint32_t *counts /*[h|d] [nq]*/, uint32_t *stats /*[h|d] or NULL*/);
+
 /* replaces hnsw_nsg::IndexNSG::SearchFromEnterpoint (hnsw_nsg/src/index_nsg.cpp:703-782) for a batch:
  * like b200ann_nsg_search, but query i starts from entry[i] instead of the navigating node. The
  * reference's seed rules are kept: the entry point itself is marked visited and never

@@ -39,6 +39,53 @@ class BaseFilterFunctor {
   virtual ~BaseFilterFunctor() {}
 };
 
+// hnswlib.h:134-150: the stop-condition interface. The walk runs on the GPU, which knows ONE condition, the epsilon
+// range search below; the virtual hooks are kept so that reference code compiles and a host-side caller can still
+// drive a condition by hand.
+template <typename dist_t>
+class BaseSearchStopCondition {
+ public:
+  virtual void add_point_to_result(labeltype label, const void *datapoint, dist_t dist) = 0;
+  virtual void remove_point_from_result(labeltype label, const void *datapoint, dist_t dist) = 0;
+  virtual bool should_stop_search(dist_t candidate_dist, dist_t lowerBound) = 0;
+  virtual bool should_consider_candidate(dist_t candidate_dist, dist_t lowerBound) = 0;
+  virtual bool should_remove_extra() = 0;
+  virtual void filter_results(std::vector<std::pair<dist_t, labeltype>> &candidates) = 0;
+  virtual ~BaseSearchStopCondition() {}
+};
+
+// stop_condition.h:218-275, same constructor and hooks; epsilon() / min_num_candidates() / max_num_candidates() are
+// what HierarchicalNSW::searchStopConditionClosest hands to b200ann_hnsw_search_epsilon.
+template <typename dist_t>
+class EpsilonSearchStopCondition : public BaseSearchStopCondition<dist_t> {
+  float epsilon_;
+  size_t min_num_candidates_, max_num_candidates_, curr_num_items_;
+
+ public:
+  EpsilonSearchStopCondition(float epsilon, size_t min_num_candidates, size_t max_num_candidates)
+      : epsilon_(epsilon), min_num_candidates_(min_num_candidates), max_num_candidates_(max_num_candidates), curr_num_items_(0) {
+    if (min_num_candidates > max_num_candidates)  // an assert in the reference (:227)
+      throw std::runtime_error("EpsilonSearchStopCondition: min_num_candidates > max_num_candidates");
+  }
+  float epsilon() const { return epsilon_; }
+  size_t min_num_candidates() const { return min_num_candidates_; }
+  size_t max_num_candidates() const { return max_num_candidates_; }
+  void add_point_to_result(labeltype, const void *, dist_t) override { curr_num_items_ += 1; }
+  void remove_point_from_result(labeltype, const void *, dist_t) override { curr_num_items_ -= 1; }
+  bool should_stop_search(dist_t candidate_dist, dist_t lowerBound) override {
+    if (candidate_dist > lowerBound && curr_num_items_ == max_num_candidates_) return true;
+    return candidate_dist > epsilon_ && curr_num_items_ >= min_num_candidates_;
+  }
+  bool should_consider_candidate(dist_t candidate_dist, dist_t lowerBound) override {
+    return curr_num_items_ < max_num_candidates_ || lowerBound > candidate_dist;
+  }
+  bool should_remove_extra() override { return curr_num_items_ > max_num_candidates_; }
+  void filter_results(std::vector<std::pair<dist_t, labeltype>> &candidates) override {
+    while (!candidates.empty() && candidates.back().first > epsilon_) candidates.pop_back();
+    while (candidates.size() > max_num_candidates_) candidates.pop_back();
+  }
+};
+
 template <typename MTYPE>
 using DISTFUNC = MTYPE (*)(const void *, const void *, const void *);
 
@@ -670,6 +717,49 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     for (size_t i = 0; i < k; i++)
       if (lab[i] != ~(uint64_t)0) res.emplace(d[i], (labeltype)lab[i]);
     return res;
+  }
+
+  // hnswalg.h:1327-1378 with an EpsilonSearchStopCondition: (distance, id) pairs, closest first, every distance <=
+  // epsilon, at most max_num_candidates of them. Like the reference, .second is the INTERNAL id (it copies
+  // top_candidates' pairs without getExternalLabel, :1368-1371); searchEpsilonBatch(..., internal_ids = false) gives
+  // labels. Any other condition (the multi-vector one) has no GPU form and throws.
+  std::vector<std::pair<dist_t, labeltype>> searchStopConditionClosest(const void *query_data,
+                                                                       BaseSearchStopCondition<dist_t> &stop_condition,
+                                                                       BaseFilterFunctor *isIdAllowed = nullptr) const {
+    std::vector<std::pair<dist_t, labeltype>> result;
+    if (cur_element_count == 0) return result;
+    auto *eps = dynamic_cast<EpsilonSearchStopCondition<dist_t> *>(&stop_condition);
+    if (!eps) throw std::runtime_error("searchStopConditionClosest: only EpsilonSearchStopCondition runs on the GPU");
+    const size_t mx = eps->max_num_candidates();
+    if (mx == 0) return result;
+    std::vector<labeltype> ids(mx);
+    std::vector<dist_t> d(mx);
+    unsigned cnt = 0;
+    searchEpsilonBatch((const float *)query_data, 1, eps->epsilon(), eps->min_num_candidates(), mx, ids.data(), d.data(), &cnt,
+                       isIdAllowed, true);
+    result.resize(cnt);
+    for (unsigned i = 0; i < cnt; i++) result[i] = std::make_pair(d[i], ids[i]);
+    return result;
+  }
+  // batched form: ids / dists [nq, max_num_candidates] ascending, counts[q] valid entries per row, the rest ~0 / +inf
+  void searchEpsilonBatch(const float *queries, size_t nq, float epsilon, size_t min_num_candidates, size_t max_num_candidates,
+                          labeltype *ids, dist_t *dists, unsigned *counts, BaseFilterFunctor *isIdAllowed = nullptr,
+                          bool internal_ids = false) const {
+    std::vector<uint64_t> lab(nq * max_num_candidates);
+    std::vector<uint32_t> st(nq * 2, 0u), cnt(nq, 0u);
+    std::unique_lock<std::mutex> lock(mu_);
+    build_locked(nullptr);
+    if (!ix_) throw std::runtime_error("HierarchicalNSW::searchStopConditionClosest: the index is empty");
+    std::vector<uint32_t> allow;
+    const bool filtered = num_deleted_ || isIdAllowed;
+    if (filtered) allow = allow_bitmap(isIdAllowed);
+    detail::check(gpu_.h, b200ann_hnsw_search_epsilon(gpu_.h, ix_, queries, nq, dim_, epsilon, min_num_candidates, max_num_candidates,
+                                                      filtered ? allow.data() : nullptr, internal_ids ? 1 : 0, lab.data(), dists,
+                                                      cnt.data(), st.data()),
+                  "HierarchicalNSW::searchStopConditionClosest");
+    count_metrics(st);
+    for (size_t i = 0; i < lab.size(); i++) ids[i] = (labeltype)lab[i];
+    for (size_t i = 0; i < nq; i++) counts[i] = cnt[i];
   }
 
   // b200ann extension for the hybrid index: renumber the elements so that internal id == label. The reference's

@@ -724,9 +724,12 @@ EXPORT int orc_hnsw_search(const float *data, size_t n, size_t dim, size_t strid
  * !isMarkedDeleted(id) && (*isIdAllowed)(getExternalLabel(id)) (:325-326, :406-407). Two heaps exactly as the
  * reference: every considered element goes to candidate_set, only allowed ones to top_candidates; the entry point
  * of a disallowed start is queued at FLT_MAX without a distance evaluation (:334-337). */
+/* eps / min_cand: the second stop rule of EpsilonSearchStopCondition::should_stop_search (stop_condition.h:247-251)
+ * with max_num_candidates_ = ef, for which should_consider_candidate (:255-258) and should_remove_extra (:260-263)
+ * are the plain rules below; eps = INFINITY, min_cand = 0 never fires = the search without a stop condition. */
 static size_t hnsw_base_twoheap_filtered(const orc_hnsw *ix, uint32_t ep, const float *q, size_t ef,
                                          const uint8_t *allow, uint8_t *visited, orc_pair *top, orc_pair *cand,
-                                         uint64_t *stats) {
+                                         uint64_t *stats, float eps, size_t min_cand) {
   size_t nt = 0, nc = 0;
   float lowerBound;
   if (allow[ep]) {
@@ -744,7 +747,8 @@ static size_t hnsw_base_twoheap_filtered(const orc_hnsw *ix, uint32_t ep, const 
   visited[ep] = 1;
   while (nc) {
     orc_pair cur = cand[0];
-    if (cur.d > lowerBound && nt == ef) break; /* :355 */
+    if (cur.d > lowerBound && nt == ef) break; /* :355, stop_condition.h:243 */
+    if (cur.d > eps && nt >= min_cand) break;  /* stop_condition.h:247 */
     hpop(cand, &nc, -1);
     const uint32_t *row = ix->links0 + (size_t)cur.id * ix->maxM0;
     if (stats) stats[1]++;
@@ -863,7 +867,7 @@ EXPORT int orc_hnsw_search_filtered(const float *data, size_t n, size_t dim, siz
         uint64_t *st = stats ? stats + 2 * qi : NULL;
         uint32_t cur = hnsw_descend(&ix, qv, &cd, st);
         if (st && allow[cur]) st[0]--; /* an allowed entry point is evaluated again by the base layer; count it once */
-        m = variant == 0 ? hnsw_base_twoheap_filtered(&ix, cur, qv, efk, allow, visited, top, cand, st)
+        m = variant == 0 ? hnsw_base_twoheap_filtered(&ix, cur, qv, efk, allow, visited, top, cand, st, INFINITY, 0)
                          : hnsw_base_pools_filtered(&ix, cur, qv, efk, allow, ccap, visited, top, cand, st, &bad);
       }
       if (inexact) inexact[qi] = (uint8_t)bad;
@@ -874,6 +878,58 @@ EXPORT int orc_hnsw_search_filtered(const float *data, size_t n, size_t dim, siz
     }
     free(visited); free(top); free(cand);
   }
+  return 0;
+}
+
+/* HierarchicalNSW::searchStopConditionClosest(query, EpsilonSearchStopCondition(epsilon, min, max), isIdAllowed)
+ * batched (hnswalg.h:1327-1378): greedy descent, searchBaseLayerST<false>(ep, q, 0, filter, &stop) with the stop
+ * condition's counters (max plays the part of ef), ascending list, filter_results (stop_condition.h:265-272: drop the
+ * tail beyond epsilon, truncate to max). allow [n] by internal id or NULL (everything allowed). The reference puts
+ * INTERNAL ids into the result (:1368-1371 copies top_candidates' (dist, tableint) pairs); labels != NULL maps them
+ * to labels instead. out_* [nq, max] padded with ~0 / inf, counts [nq]. */
+EXPORT int orc_hnsw_search_epsilon(const float *data, size_t n, size_t dim, size_t stride, const uint32_t *links0,
+                                   unsigned maxM0, const int32_t *levels, const uint32_t *upper_ptr,
+                                   const uint32_t *upper_links, unsigned maxM, const uint64_t *labels, uint32_t ep,
+                                   int maxlevel, const uint8_t *allow, const float *q, size_t nq, size_t qstride,
+                                   float epsilon, size_t min_cand, size_t max_cand, int mode, uint64_t *out_labels,
+                                   float *out_dists, uint32_t *counts, uint64_t *stats) {
+  orc_hnsw ix = {data, n, dim, stride, links0, maxM0, levels, upper_ptr, upper_links, maxM, ep, maxlevel, mode};
+  if (stats) memset(stats, 0, sizeof(uint64_t) * 2 * nq);
+  if (min_cand > max_cand || max_cand == 0) return -1; /* stop_condition.h:227 asserts */
+  uint8_t *all = NULL;
+  if (!allow) {
+    all = (uint8_t *)malloc(n ? n : 1);
+    memset(all, 1, n);
+    allow = all;
+  }
+#pragma omp parallel
+  {
+    uint8_t *visited = (uint8_t *)malloc(n ? n : 1);
+    orc_pair *top = (orc_pair *)malloc(sizeof(orc_pair) * (max_cand + 2));
+    orc_pair *cand = (orc_pair *)malloc(sizeof(orc_pair) * (n + 2));
+#pragma omp for schedule(dynamic, 8)
+    for (long qi = 0; qi < (long)nq; qi++) {
+      const float *qv = q + (size_t)qi * qstride;
+      size_t m = 0;
+      if (n) {
+        memset(visited, 0, n);
+        float cd;
+        uint64_t *st = stats ? stats + 2 * qi : NULL;
+        uint32_t cur = hnsw_descend(&ix, qv, &cd, st);
+        if (st && allow[cur]) st[0]--;
+        m = hnsw_base_twoheap_filtered(&ix, cur, qv, max_cand, allow, visited, top, cand, st, epsilon, min_cand);
+        while (m && top[m - 1].d > epsilon) m--; /* filter_results */
+        if (m > max_cand) m = max_cand;
+      }
+      counts[qi] = (uint32_t)m;
+      for (size_t j = 0; j < max_cand; j++) {
+        out_labels[(size_t)qi * max_cand + j] = j < m ? (labels ? labels[top[j].id] : top[j].id) : ~(uint64_t)0;
+        out_dists[(size_t)qi * max_cand + j] = j < m ? top[j].d : INFINITY;
+      }
+    }
+    free(visited); free(top); free(cand);
+  }
+  free(all);
   return 0;
 }
 

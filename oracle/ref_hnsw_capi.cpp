@@ -165,6 +165,27 @@ int ref_hnsw_search_filtered(void *p, const float *q, size_t nq, size_t k, size_
   }
   return 0;
 }
+// searchStopConditionClosest(query, EpsilonSearchStopCondition(eps, min, max), isIdAllowed) (hnswalg.h:1327-1378,
+// stop_condition.h:219-275), the UNMODIFIED reference. ids [nq, max] = what the reference returns in .second (internal
+// ids, :1368-1371), padded with ~0 / -1; counts [nq]. allow by LABEL or NULL.
+int ref_hnsw_search_epsilon(void *p, const float *q, size_t nq, float eps, size_t min_cand, size_t max_cand,
+                            const unsigned char *allow, unsigned long long *ids, float *dists, unsigned *counts, int threads) {
+  RefHnsw *h = (RefHnsw *)p;
+  if (threads <= 0) threads = omp_get_max_threads();
+#pragma omp parallel for num_threads(threads) schedule(dynamic, 16)
+  for (long i = 0; i < (long)nq; i++) {
+    BitmapFilter f(allow);
+    hnswlib::EpsilonSearchStopCondition<float> stop(eps, min_cand, max_cand);
+    auto r = h->index->searchStopConditionClosest(q + i * h->dim, stop, allow ? &f : nullptr);
+    size_t m = r.size();
+    counts[i] = (unsigned)m;
+    for (size_t j = 0; j < max_cand; j++) {
+      ids[i * max_cand + j] = j < m ? (unsigned long long)r[j].second : (unsigned long long)-1;
+      dists[i * max_cand + j] = j < m ? r[j].first : -1.f;
+    }
+  }
+  return 0;
+}
 // markDelete / unmarkDelete (hnswalg.h:853-911)
 int ref_hnsw_mark_deleted(void *p, size_t label, int on) {
   RefHnsw *h = (RefHnsw *)p;

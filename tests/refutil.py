@@ -86,6 +86,10 @@ def oracle():
                                                  u32p, C.c_uint, C.c_void_p, C.c_uint32, C.c_int, u8p, f32p,
                                                  C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int,
                                                  C.c_int, u64p, f32p, C.c_void_p, C.c_void_p]
+        lib.orc_hnsw_search_epsilon.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, u32p, C.c_uint, i32p, u32p,
+                                                u32p, C.c_uint, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, f32p,
+                                                C.c_size_t, C.c_size_t, C.c_float, C.c_size_t, C.c_size_t, C.c_int,
+                                                u64p, f32p, u32p, C.c_void_p]
         lib.orc_hnsw_levels.argtypes = [C.c_size_t, C.c_uint, C.c_uint32, i32p]
         lib.orc_hnsw_batch_end.restype = C.c_size_t
         lib.orc_hnsw_batch_end.argtypes = [C.c_size_t, C.c_size_t, i32p, C.c_int, C.c_uint, C.c_uint]
@@ -165,6 +169,27 @@ def orc_hnsw_search_filtered(base, h, allow, q, k, ef, mode, variant=0, ccap=0, 
                                            variant, lab, d, _vp(st), _vp(bad))
     assert rc == 0
     return (lab, d, bad, st) if want_stats else (lab, d, bad)
+
+
+def orc_hnsw_search_epsilon(base, h, q, eps, min_cand, max_cand, mode, allow=None, internal_ids=True, want_stats=False):
+    """searchStopConditionClosest with EpsilonSearchStopCondition; allow [n] u8 by internal id or None.
+    Returns (ids or labels [nq,max], d, counts[, stats])."""
+    n, dim = base.shape
+    nq = q.shape[0]
+    lab = np.empty((nq, max_cand), np.uint64)
+    d = np.empty((nq, max_cand), np.float32)
+    cnt = np.zeros(nq, np.uint32)
+    st = np.zeros((nq, 2), np.uint64) if want_stats else None
+    up = h["upper_links"]
+    if up.size == 0:
+        up = np.full((1, max(1, h["maxM"])), INVALID, np.uint32)
+    a = None if allow is None else np.ascontiguousarray(allow, np.uint8)
+    rc = oracle().orc_hnsw_search_epsilon(base, n, dim, dim, h["links0"], h["links0"].shape[1], h["levels"],
+                                          h["upper_ptr"], up, up.shape[1], None if internal_ids else _vp(h["labels"]),
+                                          h["ep"], h["maxlevel"], _vp(a), q, nq, q.shape[1], eps, min_cand, max_cand,
+                                          mode, lab, d, cnt, _vp(st))
+    assert rc == 0
+    return (lab, d, cnt, st) if want_stats else (lab, d, cnt)
 
 
 def orc_nsg_search_from(base, graph, entry, q, K, L, mode, rng_mode=1, seed=0, want_stats=False):
@@ -479,6 +504,8 @@ def reflib(name):
         lib.ref_hnsw_search_filtered.argtypes = [C.c_void_p, f32p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_void_p, u64p,
                                                  f32p, C.c_int]
         lib.ref_hnsw_mark_deleted.argtypes = [C.c_void_p, C.c_size_t, C.c_int]
+        lib.ref_hnsw_search_epsilon.argtypes = [C.c_void_p, f32p, C.c_size_t, C.c_float, C.c_size_t, C.c_size_t,
+                                                C.c_void_p, u64p, f32p, u32p, C.c_int]
     elif name.startswith("nsg"):
         lib.ref_nsg_dist_l2.restype = C.c_float
         lib.ref_nsg_dist_l2.argtypes = [f32p, f32p, C.c_uint]
@@ -568,6 +595,15 @@ class RefHnsw:
         a = None if allow_by_label is None else np.ascontiguousarray(allow_by_label, np.uint8)
         self.lib.ref_hnsw_search_filtered(self.h, q, q.shape[0], k, ef, _vp(a), lab, d, threads)
         return lab, d
+
+    def search_epsilon(self, q, eps, min_cand, max_cand, allow_by_label=None, threads=0):
+        """searchStopConditionClosest(q, EpsilonSearchStopCondition(eps, min, max), filter): (internal ids, d, counts)"""
+        ids = np.empty((q.shape[0], max_cand), np.uint64)
+        d = np.empty((q.shape[0], max_cand), np.float32)
+        cnt = np.zeros(q.shape[0], np.uint32)
+        a = None if allow_by_label is None else np.ascontiguousarray(allow_by_label, np.uint8)
+        self.lib.ref_hnsw_search_epsilon(self.h, q, q.shape[0], eps, min_cand, max_cand, _vp(a), ids, d, cnt, threads)
+        return ids, d, cnt
 
     def mark_deleted(self, label, on=True):
         assert self.lib.ref_hnsw_mark_deleted(self.h, int(label), 1 if on else 0) == 0

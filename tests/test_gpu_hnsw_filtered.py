@@ -115,3 +115,53 @@ def test_filtered_ip_labels_and_device_buffers(B, H):
     assert rc == 0
     assert (tl.cpu().numpy().view(np.uint64) == rl).all()
     ix.close()
+
+
+@pytest.mark.parametrize("kth,mn,mx,keep", [(5, 0, 50, 1.0), (20, 10, 100, 1.0), (3, 30, 30, 1.0), (40, 0, 20, 1.0),
+                                            (10, 5, 60, 0.3), (10, 0, 64, 0.02), (0, 0, 10, 1.0), (30, 200, 400, 0.004), (10, 500, 25000, 1.0)])
+def test_epsilon_search_vs_oracle(B, case, kth, mn, mx, keep):
+    """b200ann_hnsw_search_epsilon == the oracle's searchStopConditionClosest / EpsilonSearchStopCondition restatement
+    (pinned bit for bit to the compiled reference in test_oracle_pinning.py): ids, distances, per-query result counts
+    and work counters. eps = the median distance to the kth neighbour (kth = 0: smaller than every distance)."""
+    base, ix, G, q = case
+    n = len(base)
+    _, d50 = ix.hnsw_search(q, 50, 200)
+    eps = float(np.median(d50[:, kth])) if kth else float(d50.min()) * 0.5
+    allow = None if keep == 1.0 else (np.random.default_rng(kth + mx).random(n) < keep)
+    ol, od, oc, os_ = R.orc_hnsw_search_epsilon(base, G, q, eps, mn, mx, R.L2_GPU, allow=allow, want_stats=True)
+    lab, d, cnt, st = ix.hnsw_search_epsilon(q, eps, mn, mx, allow=allow, internal_ids=True, want_stats=True)
+    assert (cnt == oc).all()
+    assert (lab == ol).all() and np.array_equal(d, od)
+    assert (st.astype(np.uint64) == os_).all()
+    valid = np.arange(mx)[None, :] < cnt[:, None]
+    assert (d[valid] <= eps).all() and (lab[~valid] == NOLAB).all() and np.isinf(d[~valid]).all()
+    if allow is not None:
+        assert allow[lab[valid].astype(np.int64)].all()
+    if kth == 0:
+        assert (cnt == 0).all()
+    elif keep == 1.0 and mx >= 50:
+        assert cnt.min() < cnt.max()
+
+
+def test_epsilon_search_labels_ip_and_errors(B, H):
+    n, dim = 6000, 100
+    base = R.data_glove_like(n, dim, 41)
+    labels = np.arange(n, dtype=np.uint64) * np.uint64(3) + np.uint64(7)
+    ix = B.Index(H, base, B.IP)
+    ix.hnsw_build(8, 40, seed=100, labels=labels)
+    G = ix.get_hnsw()
+    q = R.data_glove_like(64, dim, 42)
+    R.oracle().orc_set_gpu_team(B.dist_team(dim))
+    _, d20 = ix.hnsw_search(q, 20, 100)
+    eps = float(np.median(d20[:, 8]))
+    ol, od, oc = R.orc_hnsw_search_epsilon(base, G, q, eps, 2, 40, R.IP_GPU, internal_ids=False)
+    lab, d, cnt = ix.hnsw_search_epsilon(q, eps, 2, 40)                       # labels, not internal ids
+    assert (cnt == oc).all() and (lab == ol).all() and np.allclose(d, od, rtol=1e-5, atol=0)
+    ii, _, _ = ix.hnsw_search_epsilon(q, eps, 2, 40, internal_ids=True)
+    valid = np.arange(40)[None, :] < cnt[:, None]
+    assert (labels[ii[valid].astype(np.int64)] == lab[valid]).all()
+    with pytest.raises(Exception, match="min_num_candidates"):
+        ix.hnsw_search_epsilon(q, eps, 41, 40)
+    with pytest.raises(Exception, match="NaN"):
+        ix.hnsw_search_epsilon(q, float("nan"), 0, 40)
+    ix.close()

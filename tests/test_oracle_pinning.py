@@ -182,6 +182,32 @@ def test_hnsw_filtered_search_vs_reference(hnsw_case, keep, ef):
         assert bad.any()
 
 
+@needs_ref
+@pytest.mark.parametrize("kth,mn,mx,keep", [(5, 0, 50, 1.0), (20, 10, 100, 1.0), (3, 30, 30, 1.0), (40, 0, 20, 1.0),
+                                            (10, 5, 60, 0.3), (10, 0, 60, 0.05), (0, 0, 10, 1.0)])
+def test_hnsw_epsilon_search_vs_reference(hnsw_case, kth, mn, mx, keep):
+    """oracle epsilon search == HierarchicalNSW::searchStopConditionClosest(q, EpsilonSearchStopCondition(eps, min, max),
+    filter), bit for bit (internal ids, distances, result counts); eps = the median distance to the kth neighbour
+    (kth = 0: an epsilon smaller than every distance - nothing is returned)"""
+    base, q, h, H = hnsw_case
+    n = len(base)
+    _, d50 = h.search(q, 50, 200, threads=1)
+    eps = float(np.median(d50[:, kth])) if kth else float(d50.min()) * 0.5
+    allow = None
+    if keep < 1.0:
+        allow = (np.random.default_rng(kth + mx).random(n) < keep).astype(np.uint8)
+    ri, rd, rc = h.search_epsilon(q, eps, mn, mx, allow, threads=1)   # labels == internal ids here (added in order)
+    oi, od, oc = R.orc_hnsw_search_epsilon(base, H, q, eps, mn, mx, R.L2_SCALAR, allow=allow)
+    rd = np.where(ri == np.uint64(0xFFFFFFFFFFFFFFFF), np.float32(np.inf), rd)
+    assert (rc == oc).all() and (ri == oi).all() and (rd == od).all()
+    valid = np.arange(mx)[None, :] < oc[:, None]
+    assert (od[valid] <= eps).all()
+    if kth == 0:
+        assert (oc == 0).all()
+    elif keep == 1.0 and mx >= 50:
+        assert oc.min() < oc.max()   # a real range search: the count varies with the query
+
+
 @pytest.fixture(scope="module")
 def nsg_case(tmp_path_factory):
     n, dim = 3000, 24

@@ -54,6 +54,8 @@ _lib.b200ann_index_get_hnsw.argtypes = [_vp, _vp, _vp, _vp, _vp, _vp]
 _lib.b200ann_nndescent.argtypes = [_vp, _vp, _sz, _sz, _sz, _sz, _sz, C.c_uint32, _vp, _vp, _vp]
 _lib.b200ann_nsg_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, C.c_uint32, _vp, _vp, _vp]
 _lib.b200ann_hnsw_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _vp, _vp, _vp]
+_lib.b200ann_bf_knn_noalloc.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _vp, _vp]
+NOALLOC_SCRATCH_BYTES = 16 << 20   # B200ANN_NOALLOC_SCRATCH_BYTES, include/b200ann.h
 _lib.b200ann_hnsw_search_filtered.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _vp, _vp, _vp, _vp, _vp]
 _lib.b200ann_hnsw_search_epsilon.argtypes = [_vp, _vp, _vp, _sz, _sz, C.c_float, _sz, _sz, _vp, C.c_int, _vp, _vp,
                                              _vp, _vp]
@@ -86,6 +88,7 @@ EXPORTS = [
     "b200ann_index_size", "b200ann_index_dim", "b200ann_index_set_graph", "b200ann_index_get_graph",
     "b200ann_index_set_hnsw", "b200ann_bf_knn", "b200ann_knn_graph", "b200ann_nsg_search", "b200ann_hnsw_search",
     "b200ann_hnsw_search_filtered",
+    "b200ann_bf_knn_noalloc",
     "b200ann_hnsw_search_epsilon",
     "b200ann_set_link_visited_bits", "b200ann_nsg_build", "b200ann_nsg_init_ep", "b200ann_nsg_link",
     "b200ann_nsg_interinsert", "b200ann_nsg_finish", "b200ann_merge_topk", "b200ann_nsg_search_from",

@@ -11,6 +11,7 @@
 // top-k needs no block-level synchronisation: candidates below the query's current k-th
 // (distance,id) go to a 32-entry shared-memory pending buffer; a full buffer is bitonic-sorted across
 // the warp and merged into the query's sorted k-list in global memory (ping-pong between two lists).
+#include <mutex>
 #include "common.cuh"
 
 namespace {
@@ -323,5 +324,99 @@ int launch_bf_knn(b200ann_handle *h, const b200ann_index *ix, const float *q, si
   bf_finalize_kernel<<<(unsigned)((nq + 3) / 4), 128, 0, h->stream>>>(p, ids, dists);
   h->launches++;
   CU_CHECK(h, cudaGetLastError());
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// b200ann_bf_knn_noalloc: the SIMT kernel pair above for callers that cannot allocate (CUDA graph capture, tight
+// serving loops, harnesses that forbid cudaMalloc). No counterpart in the reference.
+// The per-split partial lists and the "current list" flags, which launch_bf_knn takes from the stream
+// ordered allocator, live in ONE file-scope device array of B200ANN_NOALLOC_SCRATCH_BYTES (16 MiB) that every GPU
+// loading the library holds until exit. Every call shares it and finds the previous call's contents in it: the part
+// a call uses is cleared first, and calls that overlap on the GPU (two streams, two handles, two host threads) race.
+namespace {
+constexpr size_t NOALLOC_BYTES = B200ANN_NOALLOC_SCRATCH_BYTES;
+static __device__ __align__(256) unsigned char bf_noalloc_scratch[NOALLOC_BYTES];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex noalloc_mu;
+unsigned char *noalloc_ptr[NOALLOC_MAX_DEVICES];  // device address of bf_noalloc_scratch on device i (0 = not asked yet)
+
+// In host code `bf_noalloc_scratch` is only a stand-in for the symbol, not a device address: the address a kernel
+// can use comes from cudaGetSymbolAddress, asked once per device with that device current.
+int noalloc_scratch(b200ann_handle *h, unsigned char **out) {
+  if (h->device < 0 || h->device >= NOALLOC_MAX_DEVICES) return set_err(h, B200ANN_ERR_ARG, "bf_knn_noalloc: device index >= 64");
+  std::lock_guard<std::mutex> lock(noalloc_mu);
+  if (!noalloc_ptr[h->device]) {
+    int cur = -1;
+    CU_CHECK(h, cudaGetDevice(&cur));
+    if (cur != h->device) return set_err(h, B200ANN_ERR_STATE, "bf_knn_noalloc: the handle's device is not current");
+    unsigned char *p = nullptr;
+    CU_CHECK(h, cudaGetSymbolAddress((void **)&p, bf_noalloc_scratch));
+    if (!p) return set_err(h, B200ANN_ERR_CUDA, "bf_knn_noalloc: cudaGetSymbolAddress returned a null address");
+    noalloc_ptr[h->device] = p;
+  }
+  *out = noalloc_ptr[h->device];
+  return 0;
+}
+}  // namespace
+
+extern "C" int b200ann_bf_knn_noalloc(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_t nq, size_t qstride,
+                                      size_t k, uint32_t *ids, float *dists) {
+  if (!h || !ix) return B200ANN_ERR_ARG;
+  if (!q || !ids || k == 0 || qstride < ix->dim) return set_err(h, B200ANN_ERR_ARG, "bf_knn_noalloc: bad q/ids/k/qstride");
+  if (nq == 0) return 0;
+  if (nq >= 0xFFFFFFFFull || k >= 0xFFFFFFFFull) return set_err(h, B200ANN_ERR_ARG, "bf_knn_noalloc: nq / k must fit 32 bits");
+  CU_CHECK(h, cudaSetDevice(h->device));
+  // host buffers would need staging copies, i.e. allocations
+  if (!is_device_ptr(q) || !is_device_ptr(ids) || (dists && !is_device_ptr(dists)))
+    return set_err(h, B200ANN_ERR_ARG, "bf_knn_noalloc: q, ids and dists must be device memory (host buffers need staging allocations; use b200ann_bf_knn)");
+  // scratch per split: two (distance, id) list pairs of nq*k entries + nq flag bytes (rounded to 16)
+  const size_t per_split = nq * k * 16 + (nq + 15) / 16 * 16;
+  if (per_split > NOALLOC_BYTES) {
+    char b[256];
+    snprintf(b, sizeof b, "bf_knn_noalloc: nq * k * 16 + nq = %zu bytes of partial lists exceed the %zu-byte static scratch "
+             "(lower nq or k, or use b200ann_bf_knn)", per_split, NOALLOC_BYTES);
+    return set_err(h, B200ANN_ERR_ARG, b);
+  }
+  unsigned char *scratch = nullptr;
+  int rc = noalloc_scratch(h, &scratch);
+  if (rc) return rc;
+
+  BfParams p = {};
+  p.base = ix->vec; p.bstride = ix->stride; p.n = (uint32_t)ix->n; p.dim = (uint32_t)ix->dim;
+  p.q = q; p.qstride = qstride; p.nq = (uint32_t)nq; p.k = (uint32_t)k;
+  p.ip = ix->metric == B200ANN_IP; p.exclude_self = 0; p.self_ids = nullptr; p.self_base = 0;
+  const uint32_t qtiles = (uint32_t)((nq + QT - 1) / QT);
+  const uint32_t slots = 2u * (uint32_t)h->sm_count;  // launch_bf_knn's split rule, then as many splits as the array holds
+  uint32_t cap = (uint32_t)((ix->n + 4 * BT - 1) / (4 * BT));
+  if (cap > 64) cap = 64;
+  if (cap < 1) cap = 1;
+  uint32_t splits = 1; double best_cost = 1e300;
+  for (uint32_t s = 1; s <= cap; s++) {
+    double ctas = (double)qtiles * s, waves = (double)((qtiles * (uint64_t)s + slots - 1) / slots);
+    double cost = waves / ctas * (1.0 + 0.02 * s);
+    if (cost < best_cost * 0.999) { best_cost = cost; splits = s; }
+  }
+  while (splits > 1 && (size_t)splits * per_split > NOALLOC_BYTES) splits--;
+  p.splits = splits;
+  const size_t cnt = (size_t)splits * nq * k;  // entries per list (4-byte entries: every section is aligned for its type)
+  p.list_d[0] = reinterpret_cast<float *>(scratch);
+  p.list_d[1] = p.list_d[0] + cnt;
+  p.list_i[0] = reinterpret_cast<uint32_t *>(p.list_d[1] + cnt);
+  p.list_i[1] = p.list_i[0] + cnt;
+  p.cur = reinterpret_cast<uint8_t *>(p.list_i[1] + cnt);
+  // the array still holds the last call's lists and flags: clear what this call uses
+  CU_CHECK(h, cudaMemsetAsync(scratch, 0, cnt * 16 + (size_t)splits * nq, h->stream));
+  dim3 grid(qtiles, splits);
+  bf_knn_kernel<<<grid, NT, 0, h->stream>>>(p);
+  h->launches++;
+  CU_CHECK(h, cudaGetLastError());
+  bf_finalize_kernel<<<(unsigned)((nq + 3) / 4), 128, 0, h->stream>>>(p, ids, dists);
+  h->launches++;
+  CU_CHECK(h, cudaGetLastError());
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  CU_CHECK(h, cudaStreamIsCapturing(h->stream, &cs));
+  if (cs == cudaStreamCaptureStatusNone && !h->async_mode) CU_CHECK(h, cudaStreamSynchronize(h->stream));
   return 0;
 }

@@ -112,6 +112,21 @@ int b200ann_index_get_hnsw(b200ann_index_t ix, uint32_t *links0 /*[h|d]*/, int32
  * B200ANN_INVALID / +inf. */
 int b200ann_bf_knn(b200ann_handle_t h, b200ann_index_t ix, const float *q /*[h|d]*/, size_t nq, size_t qstride,
                    size_t k, uint32_t *ids /*[h|d]*/, float *dists /*[h|d] or NULL*/);
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it). b200ann_bf_knn on the
+ * fp32 SIMT kernel pair (csrc/bf_knn.cu) with NO allocation of any kind: the per-split partial lists, which
+ * b200ann_bf_knn takes from the stream-ordered allocator, live in one static device array of
+ * B200ANN_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit. q, ids and dists must be DEVICE
+ * memory (host buffers would need staging allocations -> B200ANN_ERR_ARG). Needs nq * k * 16 + nq bytes <=
+ * B200ANN_NOALLOC_SCRATCH_BYTES (e.g. 1000 queries x k = 1000, or 100000 x k = 10), else B200ANN_ERR_ARG with the
+ * sizes in the message; within the limit the base range is split over as many CTAs as the array holds lists for.
+ * Results are those of b200ann_bf_knn, bit for bit. Every call shares the array (the part a call uses is cleared
+ * first): calls that overlap on the GPU - two streams, two handles, two host threads - race; serialise them. Runs on
+ * the handle's stream and synchronises it before returning unless the stream is being captured or b200ann_set_async
+ * is on. */
+#define B200ANN_NOALLOC_SCRATCH_BYTES ((size_t)16 << 20)
+int b200ann_bf_knn_noalloc(b200ann_handle_t h, b200ann_index_t ix, const float *q /*[d]*/, size_t nq, size_t qstride,
+                           size_t k, uint32_t *ids /*[d]*/, float *dists /*[d] or NULL*/);
 /* replaces hnswlib::BruteforceSearch<int>::searchKnn (bruteforce.h:106-135) over hnswlib::L2SpaceI
  * (space_l2.h:255-323, L2SqrI4x / L2SqrI: int sum of (a-b)^2 over unsigned bytes), batched. base [n] rows of dim
  * bytes at bstride bytes, q [nq] rows at qstride bytes (host or device; copied per call when on the host).

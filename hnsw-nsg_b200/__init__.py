@@ -13,7 +13,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200ann.so")
 INVALID = 0xFFFFFFFF
-L2, IP = 0, 1
+L2, IP, L2_U8 = 0, 1, 2   # L2_U8: unsigned-byte rows, int squared L2 (hnswlib L2SpaceI); HNSW entry points only
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(
@@ -54,6 +54,7 @@ _lib.b200ann_index_get_hnsw.argtypes = [_vp, _vp, _vp, _vp, _vp, _vp]
 _lib.b200ann_nndescent.argtypes = [_vp, _vp, _sz, _sz, _sz, _sz, _sz, C.c_uint32, _vp, _vp, _vp]
 _lib.b200ann_nsg_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, C.c_uint32, _vp, _vp, _vp]
 _lib.b200ann_hnsw_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _vp, _vp, _vp]
+_lib.b200ann_index_create_u8.argtypes = [_vp, _vp, _sz, _sz, _sz, _vp]
 _lib.b200ann_bf_knn_noalloc.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _vp, _vp]
 NOALLOC_SCRATCH_BYTES = 16 << 20   # B200ANN_NOALLOC_SCRATCH_BYTES, include/b200ann.h
 _lib.b200ann_hnsw_search_filtered.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _vp, _vp, _vp, _vp, _vp]
@@ -89,6 +90,7 @@ EXPORTS = [
     "b200ann_index_set_hnsw", "b200ann_bf_knn", "b200ann_knn_graph", "b200ann_nsg_search", "b200ann_hnsw_search",
     "b200ann_hnsw_search_filtered",
     "b200ann_bf_knn_noalloc",
+    "b200ann_index_create_u8",
     "b200ann_hnsw_search_epsilon",
     "b200ann_set_link_visited_bits", "b200ann_nsg_build", "b200ann_nsg_init_ep", "b200ann_nsg_link",
     "b200ann_nsg_interinsert", "b200ann_nsg_finish", "b200ann_merge_topk", "b200ann_nsg_search_from",
@@ -242,9 +244,14 @@ class Index:
             n, dim = data.shape
             stride = dim
         ix = _vp()
-        handle._check(_lib.b200ann_index_create(handle._h, _ptr(data), n, dim, stride, metric, C.byref(ix)))
+        if metric == L2_U8:   # data: uint8 rows, stride in bytes
+            handle._check(_lib.b200ann_index_create_u8(handle._h, _ptr(data), n, dim, stride, C.byref(ix)))
+        else:
+            handle._check(_lib.b200ann_index_create(handle._h, _ptr(data), n, dim, stride, metric, C.byref(ix)))
         self._ix = ix
         self.n, self.dim, self.metric = n, dim, metric
+        self._qt = np.uint8 if metric == L2_U8 else np.float32    # element type of rows and queries
+        self._dt = np.int32 if metric == L2_U8 else np.float32    # type of the distances the searches return
 
     def close(self):
         if getattr(self, "_ix", None):
@@ -317,7 +324,7 @@ class Index:
 
     def hnsw_insert_batch(self, data, labels=None, efc=0):
         """nb addPoint calls on the live graph: appends the rows of `data` and links them in place"""
-        data = np.ascontiguousarray(data, np.float32)
+        data = np.ascontiguousarray(data, self._qt)
         info = np.zeros(8, np.uint64)
         lab = None if labels is None else np.ascontiguousarray(labels, np.uint64)
         self.h._check(_lib.b200ann_hnsw_insert_batch(self.h._h, self._ix, _ptr(data), data.shape[1], _ptr(lab), data.shape[0],
@@ -404,9 +411,9 @@ class Index:
         return (ids, d, st) if want_stats else (ids, d)
 
     def hnsw_search(self, q, k, ef, want_stats=False):
-        q = np.ascontiguousarray(q, np.float32)
+        q = np.ascontiguousarray(q, self._qt)
         lab = np.empty((q.shape[0], k), np.uint64)
-        d = np.empty((q.shape[0], k), np.float32)
+        d = np.empty((q.shape[0], k), self._dt)
         st = np.zeros((q.shape[0], 2), np.uint32) if want_stats else None
         self.h._check(_lib.b200ann_hnsw_search(self.h._h, self._ix, _ptr(q), q.shape[0], q.shape[1], k, ef, _ptr(lab),
                                                _ptr(d), _ptr(st)))
@@ -416,7 +423,7 @@ class Index:
         """searchKnn(query, k, isIdAllowed) batched. allow: bool / 0-1 array [n] by internal id (row), True = the
         element may be returned (passes the filter and is not deleted). -> (labels, dists, inexact[, stats]); short
         rows are padded with ~0 / inf; inexact[q] = 1: the bounded candidate set overflowed for that query."""
-        q = np.ascontiguousarray(q, np.float32)
+        q = np.ascontiguousarray(q, self._qt)
         a = np.asarray(allow).astype(bool)
         assert a.shape == (self.n,)
         bits = np.packbits(a, bitorder="little")
@@ -424,7 +431,7 @@ class Index:
         words[:len(bits)] = bits
         words = words.view(np.uint32)
         lab = np.empty((q.shape[0], k), np.uint64)
-        d = np.empty((q.shape[0], k), np.float32)
+        d = np.empty((q.shape[0], k), self._dt)
         bad = np.zeros(q.shape[0], np.uint8)
         st = np.zeros((q.shape[0], 2), np.uint32) if want_stats else None
         self.h._check(_lib.b200ann_hnsw_search_filtered(self.h._h, self._ix, _ptr(q), q.shape[0], q.shape[1], k, ef,
@@ -437,7 +444,7 @@ class Index:
         (hnswalg.h:1327-1378, stop_condition.h:219-275). -> (labels [nq,max], dists [nq,max], counts [nq][, stats]);
         row q holds counts[q] results ascending by distance, all within epsilon; the rest is ~0 / inf.
         internal_ids=True returns internal ids like the reference does."""
-        q = np.ascontiguousarray(q, np.float32)
+        q = np.ascontiguousarray(q, self._qt)
         words = None
         if allow is not None:
             a = np.asarray(allow).astype(bool)
@@ -448,7 +455,7 @@ class Index:
             words = words.view(np.uint32)
         mx = int(max_num_candidates)
         lab = np.empty((q.shape[0], mx), np.uint64)
-        d = np.empty((q.shape[0], mx), np.float32)
+        d = np.empty((q.shape[0], mx), self._dt)
         cnt = np.zeros(q.shape[0], np.uint32)
         st = np.zeros((q.shape[0], 2), np.uint32) if want_stats else None
         self.h._check(_lib.b200ann_hnsw_search_epsilon(self.h._h, self._ix, _ptr(q), q.shape[0], q.shape[1],

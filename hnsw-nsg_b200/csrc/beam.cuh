@@ -82,11 +82,11 @@ __host__ __device__ inline uint32_t smem_words(uint32_t pool_cap, uint32_t cand_
 
 // COHERENT: adjacency rows are read with ordinary (L2-coherent) loads instead of the read-only path,
 // for kernels that append edges while they search (tree_grow).
-template <int TEAM, int NCH, bool IP, bool HNSW, bool COHERENT = false>
+template <int TEAM, int NCH, int IP, bool HNSW, bool COHERENT = false>
 struct Beam {
   static constexpr int TPW = 32 / TEAM;
   static constexpr int TEAMSZ = TEAM, NCHUNK = NCH;
-  static constexpr bool IS_IP = IP;
+  static constexpr int IS_IP = IP;  // the metric: MET_L2 / MET_IP / MET_U8 (dist.cuh)
   const SearchParams &p;
   float *pool_d; uint32_t *pool_i;   // [pool_cap]
   uint32_t *cand_i; float *cand_d;   // [cand_cap]
@@ -150,13 +150,32 @@ struct Beam {
   }
 
   __device__ __forceinline__ void load_query(const float *qv) {
+    if constexpr (IP == MET_U8) {  // qv = p.dim unsigned bytes (any alignment); bytes past dim read as 0
+      const unsigned char *qb = reinterpret_cast<const unsigned char *>(qv);
 #pragma unroll
-    for (int c = 0; c < NCH; c++) {
-      uint32_t b = (uint32_t)(t + c * TEAM) * 4;
-      qreg[c].x = b + 0 < p.dim ? __ldg(qv + b + 0) : 0.f;
-      qreg[c].y = b + 1 < p.dim ? __ldg(qv + b + 1) : 0.f;
-      qreg[c].z = b + 2 < p.dim ? __ldg(qv + b + 2) : 0.f;
-      qreg[c].w = b + 3 < p.dim ? __ldg(qv + b + 3) : 0.f;
+      for (int c = 0; c < NCH; c++) {
+        const uint32_t b = (uint32_t)(t + c * TEAM) * 16;
+        uint32_t w[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          w[j] = 0;
+#pragma unroll
+          for (int k = 0; k < 4; k++) {
+            const uint32_t i = b + 4 * j + k;
+            if (i < p.dim) w[j] |= (uint32_t)__ldg(qb + i) << (8 * k);
+          }
+        }
+        qreg[c] = make_float4(__uint_as_float(w[0]), __uint_as_float(w[1]), __uint_as_float(w[2]), __uint_as_float(w[3]));
+      }
+    } else {
+#pragma unroll
+      for (int c = 0; c < NCH; c++) {
+        uint32_t b = (uint32_t)(t + c * TEAM) * 4;
+        qreg[c].x = b + 0 < p.dim ? __ldg(qv + b + 0) : 0.f;
+        qreg[c].y = b + 1 < p.dim ? __ldg(qv + b + 1) : 0.f;
+        qreg[c].z = b + 2 < p.dim ? __ldg(qv + b + 2) : 0.f;
+        qreg[c].w = b + 3 < p.dim ? __ldg(qv + b + 3) : 0.f;
+      }
     }
   }
 

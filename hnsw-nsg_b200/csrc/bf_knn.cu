@@ -363,6 +363,7 @@ int noalloc_scratch(b200ann_handle *h, unsigned char **out) {
 
 extern "C" int b200ann_bf_knn_noalloc(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_t nq, size_t qstride,
                                       size_t k, uint32_t *ids, float *dists) {
+  FLOAT_ONLY(h, ix, "bf_knn_noalloc");
   if (!h || !ix) return B200ANN_ERR_ARG;
   if (!q || !ids || k == 0 || qstride < ix->dim) return set_err(h, B200ANN_ERR_ARG, "bf_knn_noalloc: bad q/ids/k/qstride");
   if (nq == 0) return 0;

@@ -36,6 +36,14 @@ __global__ void pad_rows_kernel(const float *src, size_t sstride, float *dst, si
   }
 }
 
+// u8 indexes: distances are int32 bit patterns in the float-typed output; an unfilled slot holds the kernels' +inf
+// pattern and becomes INT32_MAX like b200ann_bf_knn_u8's
+__global__ void u8_pad_kernel(float *d, size_t count) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  for (; i < count; i += (size_t)gridDim.x * blockDim.x)
+    if (__float_as_uint(d[i]) == 0x7F800000u) d[i] = __uint_as_float(0x7FFFFFFFu);
+}
+
 __global__ void regraph_kernel(const uint32_t *src, size_t sstride, uint32_t *dst, size_t dstride, size_t n,
                                uint32_t *width) {
   size_t r = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
@@ -51,6 +59,36 @@ __global__ void regraph_kernel(const uint32_t *src, size_t sstride, uint32_t *ds
 }
 
 }  // namespace
+
+// Query rows of a search call. Float index: [nq, qstride] floats, staged like any input. u8 index: q points at
+// unsigned-byte rows qstride BYTES apart; the kernels address rows in 4-byte units, so rows that are on the host,
+// unaligned or at an odd stride are copied to a device buffer with a 4-byte aligned pitch.
+struct QueryArg {
+  InArg<float> f;
+  DevBuf<uint8_t> b;
+  const float *d = nullptr;
+  size_t qstride = 0;  // in 4-byte units
+  cudaError_t stage(const b200ann_index *ix, const float *q, size_t nq, size_t qs, cudaStream_t st) {
+    if (!ix_u8(ix)) {
+      cudaError_t e = f.stage(q, nq * qs, st);
+      d = f.d; qstride = qs;
+      return e;
+    }
+    if (is_device_ptr(q) && qs % 4 == 0 && ((uintptr_t)q & 3) == 0) { d = q; qstride = qs / 4; return cudaSuccess; }
+    const size_t pitch = (ix->dim + 3) / 4 * 4;
+    cudaError_t e = b.alloc(nq * pitch, st);
+    if (e != cudaSuccess) return e;
+    d = (const float *)b.p; qstride = pitch / 4;
+    return cudaMemcpy2DAsync(b.p, pitch, q, qs, ix->dim, nq, cudaMemcpyDefault, st);
+  }
+};
+static int u8_fix_pad(b200ann_handle *h, const b200ann_index *ix, float *dists_dev, size_t count) {
+  if (!ix_u8(ix) || !dists_dev || !count) return 0;
+  u8_pad_kernel<<<(unsigned)((count + 255) / 256 < 4096 ? (count + 255) / 256 : 4096), 256, 0, h->stream>>>(dists_dev, count);
+  h->launches++;
+  CU_CHECK(h, cudaGetLastError());
+  return 0;
+}
 
 extern "C" {
 
@@ -156,6 +194,7 @@ int b200ann_set_query_order(b200ann_handle_t h, const uint32_t *order, size_t n)
 
 int b200ann_probe_gather(b200ann_handle_t h, b200ann_index_t ix, uint64_t rows, int inflight, int warps_per_block,
                          int blocks_per_sm, uint32_t seed, float *ms) {
+  FLOAT_ONLY(h, ix, "probe_gather");
   if (!h || !ix || !ms) return B200ANN_ERR_ARG;
   CU_CHECK(h, cudaSetDevice(h->device));
   DevBuf<float> sink;
@@ -197,6 +236,29 @@ int b200ann_index_create(b200ann_handle_t h, const float *data, size_t n, size_t
     if (ix->vec) cudaFree(ix->vec);
     delete ix;
     return set_err(h, B200ANN_ERR_CUDA, std::string("index_create: ") + cudaGetErrorString(e));
+  }
+  *out = ix;
+  return 0;
+}
+
+int b200ann_index_create_u8(b200ann_handle_t h, const uint8_t *data, size_t n, size_t dim, size_t stride, b200ann_index_t *out) {
+  if (!h || !out) return B200ANN_ERR_ARG;
+  *out = nullptr;
+  if (!data || n == 0 || dim == 0 || stride < dim) return set_err(h, B200ANN_ERR_ARG, "index_create_u8: bad data/n/dim/stride");
+  if (n >= 0x7fffffffu) return set_err(h, B200ANN_ERR_ARG, "index_create_u8: n must be < 2^31");
+  if (dim > 8192) return set_err(h, B200ANN_ERR_ARG, "index_create_u8: dim > 8192 is not supported");
+  CU_CHECK(h, cudaSetDevice(h->device));
+  b200ann_index *ix = new b200ann_index;
+  const size_t rowbytes = (dim + 15) / 16 * 16;
+  ix->h = h; ix->n = n; ix->dim = dim; ix->stride = rowbytes / 4; ix->metric = B200ANN_L2_U8;
+  cudaError_t e = cudaMalloc((void **)&ix->vec, n * rowbytes);
+  if (e == cudaSuccess && rowbytes != dim) e = cudaMemsetAsync(ix->vec, 0, n * rowbytes, h->stream);
+  if (e == cudaSuccess) e = cudaMemcpy2DAsync(ix->vec, rowbytes, data, stride, dim, n, cudaMemcpyDefault, h->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+  if (e != cudaSuccess) {
+    if (ix->vec) cudaFree(ix->vec);
+    delete ix;
+    return set_err(h, B200ANN_ERR_CUDA, std::string("index_create_u8: ") + cudaGetErrorString(e));
   }
   *out = ix;
   return 0;
@@ -318,10 +380,12 @@ int b200ann_hnsw_insert_batch(b200ann_handle_t h, b200ann_index_t ix, const floa
   if (nb == 0) return 0;
   CU_CHECK(h, cudaSetDevice(h->device));
   if (ef_construction) ix->hnsw_efc = ef_construction > ix->maxM ? ef_construction : ix->maxM;
-  InArg<float> din;
-  CU_CHECK(h, din.stage(data, nb * stride, h->stream));
+  // a u8 index takes unsigned-byte rows, stride in bytes
+  const size_t esz = ix_u8(ix) ? 1 : 4;
+  InArg<uint8_t> din;
+  CU_CHECK(h, din.stage((const uint8_t *)data, nb * stride * esz, h->stream));
   CallTimer t(h);
-  int rc = hnsw_insert_launch(h, ix, din.d, stride, nb, labels, 0, 0, info);
+  int rc = hnsw_insert_launch(h, ix, din.d, stride * esz, nb, labels, 0, 0, info);
   t.stop();
   if (rc) return rc;
   CU_CHECK(h, t.sync());
@@ -396,6 +460,7 @@ int b200ann_knn_last_stats(b200ann_handle_t h, uint64_t *out8) {
 
 int b200ann_bf_knn(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_t nq, size_t qstride, size_t k,
                    uint32_t *ids, float *dists) {
+  FLOAT_ONLY(h, ix, "bf_knn");
   if (!h || !ix) return B200ANN_ERR_ARG;
   if (!q || !ids || k == 0 || qstride < ix->dim) return set_err(h, B200ANN_ERR_ARG, "bf_knn: bad q/ids/k/qstride");
   if (nq == 0) return 0;
@@ -455,6 +520,7 @@ int b200ann_free_device(void *dev) {
 }
 
 int b200ann_knn_graph(b200ann_handle_t h, b200ann_index_t ix, size_t K, uint32_t *knn) {
+  FLOAT_ONLY(h, ix, "knn_graph");
   if (!h || !ix) return B200ANN_ERR_ARG;
   if (!knn || K == 0 || K >= ix->n) return set_err(h, B200ANN_ERR_ARG, "knn_graph: need 0 < K < n");
   CU_CHECK(h, cudaSetDevice(h->device));
@@ -470,6 +536,7 @@ int b200ann_knn_graph(b200ann_handle_t h, b200ann_index_t ix, size_t K, uint32_t
 }
 
 int b200ann_knn_graph_rows(b200ann_handle_t h, b200ann_index_t ix, size_t row0, size_t nrows, size_t K, uint32_t *knn) {
+  FLOAT_ONLY(h, ix, "knn_graph_rows");
   if (!h || !ix) return B200ANN_ERR_ARG;
   if (!knn || K == 0 || K >= ix->n || row0 + nrows > ix->n) return set_err(h, B200ANN_ERR_ARG, "knn_graph_rows: need 0 < K < n and row0 + nrows <= n");
   if (nrows == 0) return 0;
@@ -487,6 +554,7 @@ int b200ann_knn_graph_rows(b200ann_handle_t h, b200ann_index_t ix, size_t row0, 
 
 int b200ann_nndescent(b200ann_handle_t h, b200ann_index_t ix, size_t K, size_t L, size_t iter, size_t S, size_t R,
                       uint32_t seed, uint32_t *knn, float *dists, uint64_t *info) {
+  FLOAT_ONLY(h, ix, "nndescent");
   if (!h || !ix) return B200ANN_ERR_ARG;
   if (!knn) return set_err(h, B200ANN_ERR_ARG, "nndescent: knn output is NULL");
   CU_CHECK(h, cudaSetDevice(h->device));
@@ -505,6 +573,7 @@ int b200ann_nndescent(b200ann_handle_t h, b200ann_index_t ix, size_t K, size_t L
 
 int b200ann_nsg_search(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_t nq, size_t qstride, size_t K,
                        size_t L, uint32_t seed, uint32_t *ids, float *dists, uint32_t *stats) {
+  FLOAT_ONLY(h, ix, "nsg_search");
   if (!h || !ix) return B200ANN_ERR_ARG;
   if (!ix->graph) return set_err(h, B200ANN_ERR_STATE, "nsg_search: index has no graph (set_graph / nsg_build first)");
   if (!q || !ids || K == 0 || L < K || L > ix->n || qstride < ix->dim)
@@ -531,6 +600,7 @@ int b200ann_nsg_search(b200ann_handle_t h, b200ann_index_t ix, const float *q, s
 int b200ann_nsg_search_clustered(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_t nq, size_t qstride,
                                  size_t K, size_t L, uint32_t seed, const uint32_t *ep, const uint32_t *base,
                                  const uint32_t *size, uint32_t *ids, float *dists, uint32_t *stats) {
+  FLOAT_ONLY(h, ix, "nsg_search_clustered");
   if (!h || !ix) return B200ANN_ERR_ARG;
   if (!ix->graph) return set_err(h, B200ANN_ERR_STATE, "nsg_search_clustered: index has no graph (set_graph first)");
   if (!q || !ids || !ep || !base || !size || K == 0 || L < K || qstride < ix->dim)
@@ -559,6 +629,7 @@ int b200ann_nsg_search_clustered(b200ann_handle_t h, b200ann_index_t ix, const f
 static int search_from_common(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_t nq, size_t qstride,
                               size_t K, size_t L, uint32_t seed, const uint32_t *entry, bool hybrid, uint32_t *ids,
                               float *dists, uint32_t *entry_out, uint32_t *stats, const char *who) {
+  FLOAT_ONLY(h, ix, "nsg_search_from / hybrid_search");
   if (!h || !ix) return B200ANN_ERR_ARG;
   if (!ix->graph) return set_err(h, B200ANN_ERR_STATE, std::string(who) + ": index has no NSG graph (set_graph / nsg_build first)");
   if (hybrid && !ix->has_hnsw) return set_err(h, B200ANN_ERR_STATE, std::string(who) + ": index has no HNSW levels (set_hnsw first)");
@@ -606,13 +677,14 @@ int b200ann_hnsw_search(b200ann_handle_t h, b200ann_index_t ix, const float *q, 
     return set_err(h, B200ANN_ERR_ARG, "hnsw_search: need q, labels, dists, k > 0, qstride >= dim");
   if (nq == 0) return 0;
   CU_CHECK(h, cudaSetDevice(h->device));
-  InArg<float> qin; OutArg<uint64_t> ol; OutArg<float> od; OutArg<uint32_t> os;
-  CU_CHECK(h, qin.stage(q, nq * qstride, h->stream));
+  QueryArg qin; OutArg<uint64_t> ol; OutArg<float> od; OutArg<uint32_t> os;
+  CU_CHECK(h, qin.stage(ix, q, nq, qstride, h->stream));
   CU_CHECK(h, ol.stage(labels, nq * k, h->stream));
   CU_CHECK(h, od.stage(dists, nq * k, h->stream));
   CU_CHECK(h, os.stage(stats, nq * 2, h->stream));
   CallTimer t(h);
-  int rc = launch_hnsw_search(h, ix, qin.d, nq, qstride, k, ef, ol.d, od.d, os.d);
+  int rc = launch_hnsw_search(h, ix, qin.d, nq, qin.qstride, k, ef, ol.d, od.d, os.d);
+  if (!rc) rc = u8_fix_pad(h, ix, od.d, nq * k);
   t.stop();
   if (rc) return rc;
   CU_CHECK(h, ol.finish(h->stream));
@@ -633,11 +705,11 @@ static int filtered_common(b200ann_handle_t h, b200ann_index_t ix, const char *w
                            size_t k, size_t ef, const uint32_t *allow, uint64_t *labels, float *dists, uint32_t *stats,
                            uint8_t *inexact, float eps, size_t min_cand, uint32_t *counts, bool internal_ids) {
   CU_CHECK(h, cudaSetDevice(h->device));
-  InArg<float> qin; InArg<uint32_t> ain; OutArg<uint64_t> ol; OutArg<float> od; OutArg<uint32_t> os, oc;
+  QueryArg qin; InArg<uint32_t> ain; OutArg<uint64_t> ol; OutArg<float> od; OutArg<uint32_t> os, oc;
   DevBuf<uint8_t> flags;
   DevBuf<uint32_t> ones;
   const size_t awords = (ix->n + 31) / 32;
-  CU_CHECK(h, qin.stage(q, nq * qstride, h->stream));
+  CU_CHECK(h, qin.stage(ix, q, nq, qstride, h->stream));
   const uint32_t *adev;
   if (allow) {
     CU_CHECK(h, ain.stage(allow, awords, h->stream));
@@ -656,7 +728,7 @@ static int filtered_common(b200ann_handle_t h, b200ann_index_t ix, const char *w
   CallTimer t(h);
   size_t left = 0;
   for (int pass = 0; pass < 2; pass++) {
-    int rc = launch_hnsw_search_filtered(h, ix, qin.d, nq, qstride, k, ef, adev, 0, pass == 1, pass ? flags.p : nullptr,
+    int rc = launch_hnsw_search_filtered(h, ix, qin.d, nq, qin.qstride, k, ef, adev, 0, pass == 1, pass ? flags.p : nullptr,
                                          ol.d, od.d, os.d, flags.p, nullptr, eps, min_cand, oc.d, internal_ids);
     if (rc) return rc;
     CU_CHECK(h, cudaMemcpyAsync(hf.data(), flags.p, nq, cudaMemcpyDeviceToHost, h->stream));
@@ -665,6 +737,7 @@ static int filtered_common(b200ann_handle_t h, b200ann_index_t ix, const char *w
     for (size_t i = 0; i < nq; i++) left += hf[i] != 0;
     if (!left) break;  // pass 1 searches only the queries pass 0 reported
   }
+  { int rc = u8_fix_pad(h, ix, od.d, nq * k); if (rc) return rc; }
   t.stop();
   CU_CHECK(h, ol.finish(h->stream));
   CU_CHECK(h, od.finish(h->stream));

@@ -137,6 +137,7 @@ extern "C" int b200ann_cluster_search(b200ann_handle_t h, b200ann_index_t ix, b2
                                       size_t n_clusters, const uint32_t *perm, const float *q, size_t nq, size_t qstride,
                                       size_t k, size_t nprobe, size_t search_K, size_t L, uint32_t seed, int early_stop,
                                       uint32_t *ids, float *dists, uint32_t *searched) {
+  FLOAT_ONLY(h, ix, "cluster_search");
   if (!h || !ix || !route_ix) return B200ANN_ERR_ARG;
   if (!ix->graph) return set_err(h, B200ANN_ERR_STATE, "cluster_search: index has no graph (set_graph first)");
   if (!q || !ids || !cl_ep || !cl_base || !cl_size || per_cluster == 0 || n_clusters == 0 || k == 0 || search_K == 0 ||

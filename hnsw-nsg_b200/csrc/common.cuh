@@ -76,10 +76,23 @@ struct b200ann_index {
   float tc_ny_max = 0.f;
 };
 
+// B200ANN_L2_U8 indexes (unsigned-byte rows, int squared L2 = hnswlib::L2SpaceI): rows are padded to 16 bytes,
+// `stride` stays in 4-byte units so that `vec + id * stride` addresses a row for both element types
+inline bool ix_u8(const b200ann_index *ix) { return ix->metric == B200ANN_L2_U8; }
+inline int ix_nch(const b200ann_index *ix) { return (int)(ix_u8(ix) ? (ix->dim + 15) / 16 : (ix->dim + 3) / 4); }  // 16-byte chunks per row
+inline size_t ix_row_bytes(const b200ann_index *ix) { return ix_u8(ix) ? ix->dim : ix->dim * 4; }               // payload bytes per row
+
 inline int set_err(b200ann_handle *h, int code, const std::string &msg) {
   if (h) h->err = msg;
   return code;
 }
+
+// entry points that only exist for float rows
+#define FLOAT_ONLY(h, ix, name)                                                                                        \
+  do {                                                                                                                 \
+    if ((ix) && (ix)->metric == B200ANN_L2_U8)                                                                         \
+      return set_err(h, B200ANN_ERR_ARG, name ": the index holds unsigned-byte rows (b200ann_index_create_u8); only the HNSW build / search entry points take it"); \
+  } while (0)
 
 #define CU_CHECK(h, call)                                                                         \
   do {                                                                                            \
@@ -188,7 +201,7 @@ void knn_tc_free(b200ann_index *ix);
 // HNSW construction (hnsw_build.cu): builds and installs the graph in the index
 int hnsw_build_launch(b200ann_handle *h, b200ann_index *ix, size_t M, size_t efc, uint32_t seed, size_t ratio, size_t bmax,
                       const uint64_t *labels_host_or_dev, uint64_t *info8);
-int hnsw_insert_launch(b200ann_handle *h, b200ann_index *ix, const float *data, size_t dstride, size_t nb,
+int hnsw_insert_launch(b200ann_handle *h, b200ann_index *ix, const void *data, size_t dstride_bytes, size_t nb,
                        const uint64_t *labels_host_or_dev, size_t ratio, size_t bmax, uint64_t *info8);
 
 // NN-descent (nndescent.cu); device pointers only

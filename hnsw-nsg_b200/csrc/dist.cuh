@@ -26,9 +26,26 @@ __device__ __forceinline__ float4 ld_row16(const float4 *p) {
 // cached 16-byte load: rows that are re-read soon (the kept set of the occlusion prune) stay in L1
 __device__ __forceinline__ float4 ld_row16_ca(const float4 *p) { return __ldg(p); }
 
-template <bool IP>
+// MET (the `IP` template argument of the kernels; a bool converts to 0 / 1): 0 = squared L2, 1 = inner product
+// (1 - <a,b>), 2 = squared L2 over UNSIGNED BYTES: a 16-byte chunk holds 16 dimensions, the distance is the
+// reference's int sum of (a-b)^2 (hnswlib L2SqrI / L2SqrI4x, space_l2.h:255-292), exact in any order. It travels
+// through the float-typed plumbing as its bit pattern: non-negative ints below 0x7F800000 order like the floats
+// with the same bits (denormals included; nothing here is compiled with -ftz), +inf stays above all of them, and no
+// kernel does arithmetic on a distance - only comparisons.
+constexpr int MET_L2 = 0, MET_IP = 1, MET_U8 = 2;
+
+__device__ __forceinline__ uint32_t acc16_u8(uint32_t acc, const float4 &q, const float4 &v) {
+  uint32_t d;
+  d = __vabsdiffu4(__float_as_uint(q.x), __float_as_uint(v.x)); acc = __dp4a(d, d, acc);
+  d = __vabsdiffu4(__float_as_uint(q.y), __float_as_uint(v.y)); acc = __dp4a(d, d, acc);
+  d = __vabsdiffu4(__float_as_uint(q.z), __float_as_uint(v.z)); acc = __dp4a(d, d, acc);
+  d = __vabsdiffu4(__float_as_uint(q.w), __float_as_uint(v.w)); acc = __dp4a(d, d, acc);
+  return acc;
+}
+
+template <int IP>
 __device__ __forceinline__ float acc4(float acc, const float4 &q, const float4 &v) {
-  if (IP) {
+  if (IP == MET_IP) {
     acc = fmaf(q.x, v.x, acc);
     acc = fmaf(q.y, v.y, acc);
     acc = fmaf(q.z, v.z, acc);
@@ -52,7 +69,7 @@ __device__ __forceinline__ float team_reduce(float acc) {
 
 // Distances of two rows per team in one go (2*NCH independent 16-byte loads in flight per lane).
 // r0/r1 may be nullptr (no row): the result is then unspecified and must be ignored by the caller.
-template <int TEAM, int NCH, bool IP, bool CACHE = false>
+template <int TEAM, int NCH, int IP, bool CACHE = false>
 __device__ __forceinline__ void team_dist2(const float4 *r0, const float4 *r1, const float4 (&q)[NCH], int t,
                                            int nch, float &d0, float &d1) {
   float4 v0[NCH], v1[NCH];
@@ -67,19 +84,38 @@ __device__ __forceinline__ void team_dist2(const float4 *r0, const float4 *r1, c
     int ch = t + c * TEAM;
     v1[c] = (r1 != nullptr && ch < nch) ? (CACHE ? ld_row16_ca(r1 + ch) : ld_row16(r1 + ch)) : z;
   }
-  float a0 = 0.f, a1 = 0.f;
+  if constexpr (IP == MET_U8) {
+    uint32_t u0 = 0, u1 = 0;
 #pragma unroll
-  for (int c = 0; c < NCH; c++) {
-    int ch = t + c * TEAM;
-    if (ch < nch) {
-      a0 = acc4<IP>(a0, q[c], v0[c]);
-      a1 = acc4<IP>(a1, q[c], v1[c]);
+    for (int c = 0; c < NCH; c++) {
+      int ch = t + c * TEAM;
+      if (ch < nch) {
+        u0 = acc16_u8(u0, q[c], v0[c]);
+        u1 = acc16_u8(u1, q[c], v1[c]);
+      }
     }
+#pragma unroll
+    for (int off = TEAM / 2; off >= 1; off >>= 1) {
+      u0 += __shfl_xor_sync(0xffffffffu, u0, off);
+      u1 += __shfl_xor_sync(0xffffffffu, u1, off);
+    }
+    d0 = __uint_as_float(u0);
+    d1 = __uint_as_float(u1);
+  } else {
+    float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+    for (int c = 0; c < NCH; c++) {
+      int ch = t + c * TEAM;
+      if (ch < nch) {
+        a0 = acc4<IP>(a0, q[c], v0[c]);
+        a1 = acc4<IP>(a1, q[c], v1[c]);
+      }
+    }
+    a0 = team_reduce<TEAM>(a0);
+    a1 = team_reduce<TEAM>(a1);
+    d0 = IP == MET_IP ? 1.0f - a0 : a0;
+    d1 = IP == MET_IP ? 1.0f - a1 : a1;
   }
-  a0 = team_reduce<TEAM>(a0);
-  a1 = team_reduce<TEAM>(a1);
-  d0 = IP ? 1.0f - a0 : a0;
-  d1 = IP ? 1.0f - a1 : a1;
 }
 
 // team size / chunks-per-lane rule shared by all launchers (and restated in tests via b200ann_dist_team)

@@ -46,7 +46,7 @@ __host__ __device__ inline uint32_t insert_smem_words(const InsertParams &ip) {
   return smem_words(ip.sp.pool_cap, ip.sp.cand_cap, ip.sp.hbits) + 2 * ip.sp.gstride;
 }
 
-template <int TEAM, int NCH, bool IP>
+template <int TEAM, int NCH, int IP>
 __global__ void __launch_bounds__(WARPS * 32) hnsw_insert_kernel(const InsertParams ip) {
   extern __shared__ uint32_t smem[];
   const SearchParams &p = ip.sp;
@@ -147,7 +147,7 @@ __host__ __device__ inline uint32_t reverse_smem_words(const ReverseParams &rp) 
   return smem_words(rp.sp.pool_cap, rp.sp.cand_cap, rp.sp.hbits) + 4 * rp.mcap + 2 * rp.sp.gstride;
 }
 
-template <int TEAM, int NCH, bool IP>
+template <int TEAM, int NCH, int IP>
 __global__ void __launch_bounds__(WARPS * 32) hnsw_reverse_kernel(const ReverseParams rp) {
   extern __shared__ uint32_t smem[];
   const SearchParams &p = rp.sp;
@@ -217,7 +217,7 @@ __global__ void __launch_bounds__(WARPS * 32) hnsw_reverse_kernel(const ReverseP
   }
 }
 
-template <int TEAM, int NCH, bool IP>
+template <int TEAM, int NCH, int IP>
 int launch_insert_t(b200ann_handle *h, const InsertParams &ip) {
   size_t smem = (size_t)WARPS * insert_smem_words(ip) * 4;
   if (smem > 227 * 1024) return set_err(h, B200ANN_ERR_ARG, "hnsw_build: ef_construction / M need more than 227 KB shared memory per block");
@@ -227,7 +227,7 @@ int launch_insert_t(b200ann_handle *h, const InsertParams &ip) {
   h->launches++;
   return 0;
 }
-template <int TEAM, int NCH, bool IP>
+template <int TEAM, int NCH, int IP>
 int launch_reverse_t(b200ann_handle *h, const ReverseParams &rp, uint32_t ntouched) {
   size_t smem = (size_t)WARPS * reverse_smem_words(rp) * 4;
   if (smem > 227 * 1024) return set_err(h, B200ANN_ERR_ARG, "hnsw_build: a reverse-link group needs more than 227 KB shared memory (lower bmax)");
@@ -238,33 +238,30 @@ int launch_reverse_t(b200ann_handle *h, const ReverseParams &rp, uint32_t ntouch
   return 0;
 }
 
-#define HB_DISPATCH(FN, ...)                                                                   \
-  do {                                                                                         \
-    if (nch > 512) return set_err(h, B200ANN_ERR_ARG, "dim > 2048 is not supported");          \
-    if (ip_metric) {                                                                           \
-      if (nch <= 8) return FN<8, 1, true>(__VA_ARGS__);                                        \
-      if (nch <= 16) return FN<8, 2, true>(__VA_ARGS__);                                       \
-      if (nch <= 32) return FN<8, 4, true>(__VA_ARGS__);                                       \
-      if (nch <= 64) return FN<8, 8, true>(__VA_ARGS__);                                       \
-      if (nch <= 128) return FN<32, 4, true>(__VA_ARGS__);                                     \
-      if (nch <= 256) return FN<32, 8, true>(__VA_ARGS__);                                     \
-      return FN<32, 16, true>(__VA_ARGS__);                                                    \
-    } else {                                                                                   \
-      if (nch <= 8) return FN<8, 1, false>(__VA_ARGS__);                                       \
-      if (nch <= 16) return FN<8, 2, false>(__VA_ARGS__);                                      \
-      if (nch <= 32) return FN<8, 4, false>(__VA_ARGS__);                                      \
-      if (nch <= 64) return FN<8, 8, false>(__VA_ARGS__);                                      \
-      if (nch <= 128) return FN<32, 4, false>(__VA_ARGS__);                                    \
-      if (nch <= 256) return FN<32, 8, false>(__VA_ARGS__);                                    \
-      return FN<32, 16, false>(__VA_ARGS__);                                                   \
-    }                                                                                          \
+#define HB_NCH(FN, MET, ...)                                  \
+  do {                                                        \
+    if (nch <= 8) return FN<8, 1, MET>(__VA_ARGS__);          \
+    if (nch <= 16) return FN<8, 2, MET>(__VA_ARGS__);         \
+    if (nch <= 32) return FN<8, 4, MET>(__VA_ARGS__);         \
+    if (nch <= 64) return FN<8, 8, MET>(__VA_ARGS__);         \
+    if (nch <= 128) return FN<32, 4, MET>(__VA_ARGS__);       \
+    if (nch <= 256) return FN<32, 8, MET>(__VA_ARGS__);       \
+    return FN<32, 16, MET>(__VA_ARGS__);                      \
+  } while (0)
+// met: MET_L2 / MET_IP / MET_U8 (dist.cuh); nch = 16-byte chunks per row (4 floats or 16 bytes each)
+#define HB_DISPATCH(FN, ...)                                                                                  \
+  do {                                                                                                        \
+    if (nch > 512) return set_err(h, B200ANN_ERR_ARG, "dim > 2048 (8192 for byte rows) is not supported");    \
+    if (met == MET_IP) HB_NCH(FN, MET_IP, __VA_ARGS__);                                                       \
+    else if (met == MET_U8) HB_NCH(FN, MET_U8, __VA_ARGS__);                                                  \
+    else HB_NCH(FN, MET_L2, __VA_ARGS__);                                                                     \
   } while (0)
 
-int launch_insert(b200ann_handle *h, const InsertParams &ip, bool ip_metric) {
+int launch_insert(b200ann_handle *h, const InsertParams &ip, int met) {
   int nch = ip.sp.nch;
   HB_DISPATCH(launch_insert_t, h, ip);
 }
-int launch_reverse(b200ann_handle *h, const ReverseParams &rp, uint32_t ntouched, bool ip_metric) {
+int launch_reverse(b200ann_handle *h, const ReverseParams &rp, uint32_t ntouched, int met) {
   int nch = rp.sp.nch;
   HB_DISPATCH(launch_reverse_t, h, rp, ntouched);
 }
@@ -349,9 +346,9 @@ static int hnsw_run_batches(b200ann_handle *h, b200ann_index *ix, size_t s0, con
   CU_CHECK(h, cudaMemsetAsync(stats.p, 0, 4 * sizeof(unsigned long long), st));
   uint32_t *rcount = rstate.p, *rfill = rstate.p + nr, *roff = rstate.p + 2 * nr;
 
-  const bool ipm = ix->metric == B200ANN_IP;
+  const int ipm = ix->metric == B200ANN_IP ? MET_IP : (ix_u8(ix) ? MET_U8 : MET_L2);
   InsertParams ip = {};
-  ip.sp.vec = ix->vec; ip.sp.stride = ix->stride; ip.sp.n = (uint32_t)n; ip.sp.nch = (int)((ix->dim + 3) / 4);
+  ip.sp.vec = ix->vec; ip.sp.stride = ix->stride; ip.sp.n = (uint32_t)n; ip.sp.nch = ix_nch(ix);
   ip.sp.dim = (uint32_t)ix->dim;
   ip.sp.graph = ix->links0; ip.sp.gstride = (uint32_t)maxM0;
   ip.sp.upper_links = ix->upper_links; ip.sp.upper_ptr = ix->upper_ptr; ip.sp.maxM = (uint32_t)maxM;
@@ -509,10 +506,10 @@ int hnsw_build_launch(b200ann_handle *h, b200ann_index *ix, size_t M, size_t efc
 }
 
 // Appends nb rows to the index and links them into its HNSW graph in place: what nb addPoint calls do to a live
-// hnswlib index (hnswalg.h:1153-1267). data [nb, dstride] device memory. The level generator continues where the
+// hnswlib index (hnswalg.h:1153-1267). data = nb rows dstride_bytes apart (floats, or bytes for a u8 index), device memory. The level generator continues where the
 // build (or the previous append) left it. Any NSG graph / tensor-core cache of the index is dropped (their row set
 // changed). info8 as hnsw_build_launch (counters of this call).
-int hnsw_insert_launch(b200ann_handle *h, b200ann_index *ix, const float *data, size_t dstride, size_t nb,
+int hnsw_insert_launch(b200ann_handle *h, b200ann_index *ix, const void *data, size_t dstride_bytes, size_t nb,
                        const uint64_t *labels_host_or_dev, size_t ratio, size_t bmax, uint64_t *info8) {
   if (!ix->has_hnsw) return set_err(h, B200ANN_ERR_STATE, "hnsw_insert_batch: index has no HNSW graph (hnsw_build / set_hnsw first)");
   if (ix->n + nb >= (1ull << 31)) return set_err(h, B200ANN_ERR_ARG, "hnsw_insert_batch: too many rows");
@@ -527,8 +524,9 @@ int hnsw_insert_launch(b200ann_handle *h, b200ann_index *ix, const float *data, 
     size_t c = ix->cap_vec ? ix->cap_vec : n_old * ix->stride;
     CU_CHECK(h, grow(&ix->vec, n_old * ix->stride, n * ix->stride, &c, st));
     ix->cap_vec = c;
-    if (ix->stride != ix->dim) CU_CHECK(h, cudaMemsetAsync(ix->vec + n_old * ix->stride, 0, nb * ix->stride * 4, st));
-    CU_CHECK(h, cudaMemcpy2DAsync(ix->vec + n_old * ix->stride, ix->stride * 4, data, dstride * 4, ix->dim * 4, nb, cudaMemcpyDefault, st));
+    const size_t rb = ix_row_bytes(ix);
+    if (ix->stride * 4 != rb) CU_CHECK(h, cudaMemsetAsync(ix->vec + n_old * ix->stride, 0, nb * ix->stride * 4, st));
+    CU_CHECK(h, cudaMemcpy2DAsync(ix->vec + n_old * ix->stride, ix->stride * 4, data, dstride_bytes, rb, nb, cudaMemcpyDefault, st));
   }
   if (ix->graph) { cudaFree(ix->graph); ix->graph = nullptr; }
   knn_tc_free(ix);

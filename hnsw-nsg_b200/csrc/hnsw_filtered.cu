@@ -14,6 +14,7 @@
 // for bit. Reported queries are searched again (retry pass) with the heap in global memory and room for all n
 // elements, which cannot overflow. The visited set is exact (the reference's per-query tag array,
 // visited_list_pool.h:10-31): one bitmap of n bits per resident warp in global memory, cleared per query.
+#include <string.h>
 #include "beam.cuh"
 
 using namespace beam;
@@ -122,7 +123,7 @@ __device__ __forceinline__ uint32_t heap_argmax(const float *hd, const uint32_t 
   return bs;
 }
 
-template <int TEAM, int NCH, bool IP>
+template <int TEAM, int NCH, int IP>
 __global__ void __launch_bounds__(FW * 32) hnsw_filtered_kernel(const FilterParams fp) {
   extern __shared__ uint32_t smem[];
   const SearchParams &p = fp.s;
@@ -261,7 +262,7 @@ __global__ void __launch_bounds__(FW * 32) hnsw_filtered_kernel(const FilterPara
   }
 }
 
-template <int TEAM, int NCH, bool IP>
+template <int TEAM, int NCH, int IP>
 int launch_ft(b200ann_handle *h, FilterParams &fp) {
   size_t smem = (size_t)fp.wpb * fsmem_words(fp) * 4;
   auto kern = hnsw_filtered_kernel<TEAM, NCH, IP>;
@@ -273,7 +274,7 @@ int launch_ft(b200ann_handle *h, FilterParams &fp) {
   return 0;
 }
 
-template <bool IP>
+template <int IP>
 int launch_fdim(b200ann_handle *h, FilterParams &fp) {
   int nch = fp.s.nch;
   if (nch <= 8) return launch_ft<8, 1, IP>(h, fp);
@@ -283,7 +284,7 @@ int launch_fdim(b200ann_handle *h, FilterParams &fp) {
   if (nch <= 128) return launch_ft<32, 4, IP>(h, fp);
   if (nch <= 256) return launch_ft<32, 8, IP>(h, fp);
   if (nch <= 512) return launch_ft<32, 16, IP>(h, fp);
-  return set_err(h, B200ANN_ERR_ARG, "hnsw_search_filtered: dim > 2048 is not supported");
+  return set_err(h, B200ANN_ERR_ARG, "hnsw_search_filtered: dim > 2048 (8192 for byte rows) is not supported");
 }
 
 }  // namespace
@@ -298,12 +299,18 @@ int launch_hnsw_search_filtered(b200ann_handle *h, const b200ann_index *ix, cons
                                 size_t *ccap_used, float eps, size_t min_cand, uint32_t *counts, bool internal_ids) {
   FilterParams fp = {};
   fp.eps = eps; fp.min_cand = (uint32_t)min_cand; fp.counts = counts;
+  if (ix_u8(ix) && eps < INFINITY)  // int distances travel as bit patterns (dist.cuh): d > eps <=> bits(d) > bits(floor(eps))
+  {
+    const int e = (int)fminf(floorf(eps), 2139095039.f);
+    fp.eps = -1.0f;
+    if (eps >= 0.f) memcpy(&fp.eps, &e, 4);
+  }
   SearchParams &p = fp.s;
   // epsilon mode (counts given): k is only the row stride of the outputs, the walk keeps ef = max_num_candidates
   // results; more than n + 1 can never be held, and with n + 1 slots "nt == ef" stays false like in the reference
   size_t L = ef > k ? ef : k;
   if (counts) L = ef < ix->n + 1 ? ef : ix->n + 1;
-  p.vec = ix->vec; p.stride = ix->stride; p.n = (uint32_t)ix->n; p.nch = (int)((ix->dim + 3) / 4);
+  p.vec = ix->vec; p.stride = ix->stride; p.n = (uint32_t)ix->n; p.nch = ix_nch(ix);
   p.graph = ix->links0; p.gstride = (uint32_t)ix->maxM0; p.ep = ix->hnsw_ep;
   p.upper_links = ix->upper_links; p.upper_ptr = ix->upper_ptr; p.maxM = (uint32_t)ix->maxM;
   p.maxlevel = ix->maxlevel; p.labels = internal_ids ? nullptr : ix->labels;
@@ -360,5 +367,6 @@ int launch_hnsw_search_filtered(b200ann_handle *h, const b200ann_index *ix, cons
   DevBuf<uint32_t> vis;
   CU_CHECK(h, vis.alloc((size_t)fp.total_warps * fp.vwords, h->stream));
   fp.visited = vis.p;
-  return ix->metric == B200ANN_IP ? launch_fdim<true>(h, fp) : launch_fdim<false>(h, fp);
+  if (ix_u8(ix)) return launch_fdim<MET_U8>(h, fp);
+  return ix->metric == B200ANN_IP ? launch_fdim<MET_IP>(h, fp) : launch_fdim<MET_L2>(h, fp);
 }

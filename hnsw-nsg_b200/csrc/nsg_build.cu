@@ -763,6 +763,7 @@ int b200ann_set_link_visited_bits(b200ann_handle_t h, int bits) {
 
 int b200ann_nsg_init_ep(b200ann_handle_t h, b200ann_index_t ix, const uint32_t *knn, size_t kstride, size_t L,
                         uint32_t seed, uint32_t ep0, uint32_t *ep_out, float *center_out) {
+  FLOAT_ONLY(h, ix, "nsg_init_ep");
   if (!h || !ix || !ep_out) return B200ANN_ERR_ARG;
   int rc = check_build_args(h, ix, knn, kstride, L, 1, 1);
   if (rc) return rc;
@@ -782,6 +783,7 @@ int b200ann_nsg_init_ep(b200ann_handle_t h, b200ann_index_t ix, const uint32_t *
 
 int b200ann_nsg_link(b200ann_handle_t h, b200ann_index_t ix, const uint32_t *knn, size_t kstride, uint32_t ep, size_t L,
                      size_t R, size_t C, uint32_t seed, uint32_t *cut_ids, float *cut_d, uint32_t *stats) {
+  FLOAT_ONLY(h, ix, "nsg_link");
   if (!h || !ix) return B200ANN_ERR_ARG;
   int rc = check_build_args(h, ix, knn, kstride, L, R, C);
   if (rc) return rc;
@@ -803,6 +805,7 @@ int b200ann_nsg_link(b200ann_handle_t h, b200ann_index_t ix, const uint32_t *knn
 
 int b200ann_nsg_interinsert(b200ann_handle_t h, b200ann_index_t ix, size_t R, uint32_t *cut_ids, float *cut_d,
                             uint64_t *n_eval) {
+  FLOAT_ONLY(h, ix, "nsg_interinsert");
   if (!h || !ix) return B200ANN_ERR_ARG;
   if (!cut_ids || !cut_d || R == 0) return set_err(h, B200ANN_ERR_ARG, "nsg_interinsert: need cut_ids, cut_d, R > 0");
   CU_CHECK(h, cudaSetDevice(h->device));
@@ -835,6 +838,7 @@ int b200ann_nsg_interinsert(b200ann_handle_t h, b200ann_index_t ix, size_t R, ui
 
 int b200ann_nsg_finish(b200ann_handle_t h, b200ann_index_t ix, const uint32_t *cut_ids, const float *cut_d, size_t R,
                        uint32_t ep, size_t L, uint32_t seed, size_t slack, uint32_t *added) {
+  FLOAT_ONLY(h, ix, "nsg_finish");
   if (!h || !ix) return B200ANN_ERR_ARG;
   if (!cut_ids || !cut_d || R == 0 || ep >= ix->n || L == 0 || L > ix->n)
     return set_err(h, B200ANN_ERR_ARG, "nsg_finish: need cut_ids, cut_d, R > 0, ep < n, 0 < L <= n");
@@ -847,6 +851,7 @@ int b200ann_nsg_finish(b200ann_handle_t h, b200ann_index_t ix, const uint32_t *c
 
 int b200ann_nsg_build(b200ann_handle_t h, b200ann_index_t ix, const uint32_t *knn, size_t kstride, size_t L, size_t R,
                       size_t C, uint32_t seed, uint32_t ep0, uint64_t *info) {
+  FLOAT_ONLY(h, ix, "nsg_build");
   if (!h || !ix) return B200ANN_ERR_ARG;
   int rc = check_build_args(h, ix, knn, kstride, L, R, C);
   if (rc) return rc;

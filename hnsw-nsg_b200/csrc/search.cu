@@ -18,7 +18,7 @@ constexpr int WARPS = 4;
 // Persistent form (p.work != NULL): the grid is one resident wave and every WARP pulls its next query from an
 // atomic counter, so a warp whose query ends early starts another one instead of idling until the slowest warp of
 // its block (and the last partial wave) is done. Results do not depend on which warp ran which query.
-template <int TEAM, int NCH, bool IP, bool HNSW>
+template <int TEAM, int NCH, int IP, bool HNSW>
 __global__ void __launch_bounds__(WARPS * 32, (NCH <= 4 ? 6 : 1)) beam_search_kernel(const SearchParams p) {
   extern __shared__ uint32_t smem[];
   const int warp = threadIdx.x >> 5;
@@ -87,7 +87,7 @@ __global__ void __launch_bounds__(WARPS * 32, (NCH <= 4 ? 6 : 1)) beam_search_ke
   }
 }
 
-template <int TEAM, int NCH, bool IP, bool HNSW>
+template <int TEAM, int NCH, int IP, bool HNSW>
 int launch_t(b200ann_handle *h, const SearchParams &p0) {
   SearchParams p = p0;
   size_t smem = (size_t)WARPS * smem_words(p.pool_cap, p.cand_cap, p.hbits) * 4;
@@ -115,7 +115,7 @@ int launch_t(b200ann_handle *h, const SearchParams &p0) {
   return 0;
 }
 
-template <bool IP, bool HNSW>
+template <int IP, bool HNSW>
 int launch_dim(b200ann_handle *h, const SearchParams &p0) {
   SearchParams p = p0;
   p.order = (h->query_order && h->query_order_n == p.nq) ? h->query_order : nullptr;
@@ -125,10 +125,10 @@ int launch_dim(b200ann_handle *h, const SearchParams &p0) {
   while (p.nbits < 32 && (1ull << p.nbits) < (unsigned long long)p.n) p.nbits++;
   if (p.nbits < p.hbits + 1) p.nbits = p.hbits + 1;
   p.vis16 = (h->visited_compact && p.nbits - (p.hbits + 1) <= 12) ? 1 : 0;
-  if (h->search_version != 1) {  // v2: TMA row ring + register pool (beam2.cuh); B200ANN_SEARCH_VERSION=1 keeps v1 for A/B runs
-    if (p.L <= 32) return launch_search2_pr1(h, p, IP, HNSW);
-    if (p.L <= 64) return launch_search2_pr2(h, p, IP, HNSW);
-    return launch_search2_pr0(h, p, IP, HNSW);
+  if (h->search_version != 1 && IP != MET_U8) {  // byte rows (MET_U8) run on the v1 kernel; v2: TMA row ring + register pool (beam2.cuh); B200ANN_SEARCH_VERSION=1 keeps v1 for A/B runs
+    if (p.L <= 32) return launch_search2_pr1(h, p, IP == MET_IP, HNSW);
+    if (p.L <= 64) return launch_search2_pr2(h, p, IP == MET_IP, HNSW);
+    return launch_search2_pr0(h, p, IP == MET_IP, HNSW);
   }
   int nch = p.nch;
   if (nch <= 8) return launch_t<8, 1, IP, HNSW>(h, p);
@@ -138,7 +138,7 @@ int launch_dim(b200ann_handle *h, const SearchParams &p0) {
   if (nch <= 128) return launch_t<32, 4, IP, HNSW>(h, p);
   if (nch <= 256) return launch_t<32, 8, IP, HNSW>(h, p);
   if (nch <= 512) return launch_t<32, 16, IP, HNSW>(h, p);
-  return set_err(h, B200ANN_ERR_ARG, "search: dim > 2048 is not supported");
+  return set_err(h, B200ANN_ERR_ARG, "search: dim > 2048 (8192 for byte rows) is not supported");
 }
 
 }  // namespace
@@ -269,15 +269,16 @@ int launch_hnsw_search(b200ann_handle *h, const b200ann_index *ix, const float *
                        size_t k, size_t ef, uint64_t *labels, float *dists, uint32_t *stats) {
   SearchParams p = {};
   size_t L = ef > k ? ef : k;  // hnswalg.h:1309 std::max(ef_, k)
-  p.vec = ix->vec; p.stride = ix->stride; p.n = (uint32_t)ix->n; p.nch = (int)((ix->dim + 3) / 4);
+  p.vec = ix->vec; p.stride = ix->stride; p.n = (uint32_t)ix->n; p.nch = ix_nch(ix);
   p.graph = ix->links0; p.gstride = (uint32_t)ix->maxM0; p.ep = ix->hnsw_ep;
   p.upper_links = ix->upper_links; p.upper_ptr = ix->upper_ptr; p.maxM = (uint32_t)ix->maxM;
   p.maxlevel = ix->maxlevel; p.labels = ix->labels;
-  p.q = q; p.qstride = qstride; p.nq = (uint32_t)nq; p.dim = (uint32_t)ix->dim;
+  p.q = q; p.qstride = qstride; p.nq = (uint32_t)nq; p.dim = (uint32_t)ix->dim;  // u8 index: q = byte rows, qstride in 4-byte units
   p.K = (uint32_t)k; p.L = (uint32_t)L; p.seed = 0; p.hbits = h->visited_bits;
   size_t cc = ix->maxM0 > ix->maxM ? ix->maxM0 : ix->maxM;
   p.cand_cap = round_up((uint32_t)cc, 32);
   p.pool_cap = round_up((uint32_t)L + 1, 32);
   p.labels_out = labels; p.dists = dists; p.stats = stats;
-  return ix->metric == B200ANN_IP ? launch_dim<true, true>(h, p) : launch_dim<false, true>(h, p);
+  if (ix_u8(ix)) return launch_dim<MET_U8, true>(h, p);
+  return ix->metric == B200ANN_IP ? launch_dim<MET_IP, true>(h, p) : launch_dim<MET_L2, true>(h, p);
 }

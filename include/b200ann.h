@@ -27,7 +27,11 @@ extern "C" {
 
 #define B200ANN_INVALID 0xFFFFFFFFu
 
-enum { B200ANN_L2 = 0, B200ANN_IP = 1 }; /* L2Space / InnerProductSpace (1 - <a,b>) */
+enum {
+  B200ANN_L2 = 0,   /* hnswlib::L2Space */
+  B200ANN_IP = 1,   /* hnswlib::InnerProductSpace (1 - <a,b>) */
+  B200ANN_L2_U8 = 2 /* hnswlib::L2SpaceI: unsigned-byte rows, int squared L2 (b200ann_index_create_u8 only) */
+};
 
 enum {
   B200ANN_OK = 0,
@@ -57,6 +61,17 @@ float b200ann_last_kernel_ms(b200ann_handle_t h);
  * the borrowed `data_` of efanna2e::IndexNSG (CNNS/src/nsg/index_nsg.cpp:469,509) */
 int b200ann_index_create(b200ann_handle_t h, const float *data /*[h|d]*/, size_t n, size_t dim, size_t stride,
                          int metric, b200ann_index_t *out);
+/* replaces the data ownership of hnswlib::HierarchicalNSW<int> over hnswlib::L2SpaceI (space_l2.h:255-323: elements
+ * are dim unsigned bytes, the distance is the int sum of (a-b)^2, L2SqrI4x / L2SqrI): data = n rows of dim bytes,
+ * stride BYTES apart; rows live in HBM padded to 16 bytes - a quarter of the float index's bytes per hop of a
+ * bandwidth-bound walk. dim <= 8192. Such an index is taken by the HNSW entry points only (b200ann_hnsw_build,
+ * b200ann_hnsw_insert_batch with byte rows and a byte stride, b200ann_index_set_hnsw / get_hnsw,
+ * b200ann_hnsw_search, _filtered, _epsilon); there `q` points at unsigned-byte query rows, `qstride` is in BYTES,
+ * and the `dists` array holds int32 values (the reference's dist_t = int; unfilled slots INT32_MAX), bit-exact -
+ * integer sums do not depend on the summation order. epsilon of the range search is compared as an integer.
+ * Every other entry point returns B200ANN_ERR_ARG for it. */
+int b200ann_index_create_u8(b200ann_handle_t h, const uint8_t *data /*[h|d]*/, size_t n, size_t dim, size_t stride,
+                            b200ann_index_t *out);
 int b200ann_index_destroy(b200ann_index_t ix);
 size_t b200ann_index_size(b200ann_index_t ix);
 size_t b200ann_index_dim(b200ann_index_t ix);

@@ -172,6 +172,12 @@ inline void space_info(SpaceInterface<float> *s, int &metric, size_t &dim) {
   else throw std::runtime_error("b200ann: only L2Space and InnerProductSpace run on the GPU (a device kernel cannot call a host DISTFUNC)");
   dim = *(size_t *)s->get_dist_func_param();
 }
+// HierarchicalNSW<int>: L2SpaceI (unsigned-byte rows, int squared L2) -> a B200ANN_L2_U8 index
+inline void space_info(SpaceInterface<int> *s, int &metric, size_t &dim) {
+  if (!dynamic_cast<L2SpaceI *>(s)) throw std::runtime_error("b200ann: L2SpaceI is the only SpaceInterface<int> that runs on the GPU");
+  metric = B200ANN_L2_U8;
+  dim = *(size_t *)s->get_dist_func_param();
+}
 }  // namespace detail
 
 template <typename dist_t>
@@ -458,7 +464,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
   HierarchicalNSW(SpaceInterface<dist_t> *s, size_t max_elements, size_t M = 16, size_t ef_construction = 200,
                   size_t random_seed = 100, bool allow_replace_deleted = false, int device = 0)
       : gpu_(device), allow_replace_deleted_(allow_replace_deleted) {
-    detail::space_info(s, metric_, dim_);
+    detail::space_info(s, metric_, dim_); set_geometry();
     max_elements_ = max_elements;
     M_ = M <= 10000 ? M : 10000;                       // :98-104
     maxM_ = M_; maxM0_ = M_ * 2;
@@ -470,7 +476,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
   HierarchicalNSW(SpaceInterface<dist_t> *s, const std::string &location, bool = false, size_t max_elements = 0,
                   bool allow_replace_deleted = false, int device = 0)
       : gpu_(device), allow_replace_deleted_(allow_replace_deleted) {
-    detail::space_info(s, metric_, dim_);
+    detail::space_info(s, metric_, dim_); set_geometry();
     loadIndex(location, s, max_elements);
   }
   ~HierarchicalNSW() { if (ix_) b200ann_index_destroy(ix_); }
@@ -481,14 +487,14 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
   void loadIndex(const std::string &location, SpaceInterface<dist_t> *s, size_t max_elements_i = 0) {
     std::ifstream in(location, std::ios::binary);
     if (!in.is_open()) throw std::runtime_error("Cannot open file");
-    detail::space_info(s, metric_, dim_);
+    detail::space_info(s, metric_, dim_); set_geometry();
     size_t offsetLevel0, size_data_per_element, label_offset, offsetData;
     rd(in, offsetLevel0); rd(in, max_elements_); rd(in, cur_element_count); rd(in, size_data_per_element);
     rd(in, label_offset); rd(in, offsetData); rd(in, maxlevel_); rd(in, enterpoint_node_); rd(in, maxM_); rd(in, maxM0_);
     rd(in, M_); rd(in, mult_); rd(in, ef_construction_);
     if (!in) throw std::runtime_error("Index seems to be corrupted or unsupported");
     if (max_elements_i > max_elements_) max_elements_ = max_elements_i;
-    if (label_offset < offsetData || (label_offset - offsetData) / sizeof(float) != dim_) throw std::runtime_error("index file dimension does not match the space");
+    if (label_offset < offsetData || label_offset - offsetData != data_size_) throw std::runtime_error("index file dimension does not match the space");
     const size_t n = cur_element_count;
     // the layout the reference writes (hnswalg.h:116-123) and the size check of its loader (:740-760)
     if (maxM0_ == 0 || maxM_ == 0 || maxM0_ > (1u << 20) || maxM_ > (1u << 20) || n > max_elements_ || offsetLevel0 != 0 ||
@@ -504,7 +510,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     }
     std::vector<char> blob(n * size_data_per_element);
     in.read(blob.data(), (std::streamsize)blob.size());
-    vec_.resize(n * dim_); labels_.resize(n); links0_.assign(n * maxM0_, B200ANN_INVALID);
+    vec_.resize(n * rw_); labels_.resize(n); links0_.assign(n * maxM0_, B200ANN_INVALID);
     deleted_.assign(n, 0); num_deleted_ = 0; deleted_set_.clear();
     label_lookup_.clear();
     for (size_t i = 0; i < n; i++) {
@@ -516,7 +522,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
         if (allow_replace_deleted_) deleted_set_.insert((tableint)i);
       }
       std::memcpy(&links0_[i * maxM0_], row + offsetLevel0 + 4, (size_t)cnt * 4);
-      std::memcpy(&vec_[i * dim_], row + offsetData, dim_ * sizeof(float));
+      std::memcpy(&vec_[i * rw_], row + offsetData, data_size_);
       labeltype lab;
       std::memcpy(&lab, row + label_offset, sizeof(labeltype));
       labels_[i] = lab;
@@ -556,7 +562,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     { std::unique_lock<std::mutex> lock(mu_); build_locked(nullptr); sync_host_graph_locked(); }
     std::ofstream out(location, std::ios::binary);
     const size_t n = cur_element_count;
-    size_t size_links_level0 = maxM0_ * 4 + 4, data_size = dim_ * sizeof(float);
+    size_t size_links_level0 = maxM0_ * 4 + 4, data_size = data_size_;
     size_t size_data_per_element = size_links_level0 + data_size + sizeof(labeltype);
     size_t offsetLevel0 = 0, offsetData = size_links_level0, label_offset = size_links_level0 + data_size;
     wr(out, offsetLevel0); wr(out, max_elements_); wr(out, cur_element_count); wr(out, size_data_per_element);
@@ -570,7 +576,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
       std::memcpy(row.data(), &cnt, 2);
       if (deleted_[i]) row[2] = (char)DELETE_MARK;  // the mark lives in the upper half of the list-size word (:864-878)
       std::memcpy(row.data() + 4, &links0_[i * maxM0_], (size_t)cnt * 4);
-      std::memcpy(row.data() + offsetData, &vec_[i * dim_], data_size);
+      std::memcpy(row.data() + offsetData, &vec_[i * rw_], data_size);
       labeltype lab = labels_[i];
       std::memcpy(row.data() + label_offset, &lab, sizeof(labeltype));
       out.write(row.data(), (std::streamsize)row.size());
@@ -607,7 +613,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
       labels_[id] = label;
       label_lookup_[label] = id;
       deleted_[id] = 0; num_deleted_--;      // unmarkDeletedInternal :989
-      std::memcpy(&vec_[id * dim_], datapoint, dim_ * sizeof(float));
+      std::memcpy(&vec_[id * rw_], datapoint, data_size_);
       needs_rebuild_ = true;
       return;
     }
@@ -616,13 +622,14 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
       if (allow_replace_deleted_ && deleted_[it->second])  // :1163-1167
         throw std::runtime_error("Can't use addPoint to update deleted elements if replacement of deleted elements is enabled.");
       if (deleted_[it->second]) { deleted_[it->second] = 0; num_deleted_--; }  // :1166-1168: an update un-deletes
-      std::memcpy(&vec_[it->second * dim_], datapoint, dim_ * sizeof(float));
+      std::memcpy(&vec_[it->second * rw_], datapoint, data_size_);
       if (it->second < built_count_) needs_rebuild_ = true;  // a linked element moved: re-link (updatePoint)
       return;
     }
     if (cur_element_count >= max_elements_) throw std::runtime_error("The number of elements exceeds the specified limit");  // :1178
     label_lookup_[label] = cur_element_count;
-    vec_.insert(vec_.end(), (const float *)datapoint, (const float *)datapoint + dim_);
+    vec_.resize(vec_.size() + rw_, 0.f);
+    std::memcpy(&vec_[vec_.size() - rw_], datapoint, data_size_);
     labels_.push_back(label);
     deleted_.push_back(0);
     cur_element_count++;   // linked into the device graph by the next build_locked()
@@ -658,8 +665,8 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     std::unique_lock<std::mutex> lock(mu_);
     auto it = label_lookup_.find(label);
     if (it == label_lookup_.end() || deleted_[it->second]) throw std::runtime_error("Label not found");
-    const data_t *p = (const data_t *)&vec_[it->second * dim_];
-    return std::vector<data_t>(p, p + dim_);
+    const data_t *p = (const data_t *)&vec_[it->second * rw_];
+    return std::vector<data_t>(p, p + data_size_ / sizeof(data_t));
   }
   size_t getDeletedCount() const { return num_deleted_; }
   size_t getCurrentElementCount() const { return cur_element_count; }
@@ -674,7 +681,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
   // some row has fewer than k results, bindings.cpp:646-648). Otherwise searchBaseLayerST<false> on the GPU
   // (b200ann_hnsw_search_filtered): the functor is evaluated ONCE per batch over all labels into a bitmap; short
   // rows are padded with ~0 / +inf.
-  void searchKnnBatch(const float *queries, size_t nq, size_t k, labeltype *labels, dist_t *dists,
+  void searchKnnBatch(const void *queries, size_t nq, size_t k, labeltype *labels, dist_t *dists,
                       BaseFilterFunctor *isIdAllowed = nullptr) const {
     std::vector<uint64_t> lab(nq * k);
     std::unique_lock<std::mutex> lock(mu_);
@@ -682,10 +689,10 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     if (!ix_) throw std::runtime_error("HierarchicalNSW::searchKnnBatch: the index is empty");
     std::vector<uint32_t> st(nq * 2, 0u);
     if (!num_deleted_ && !isIdAllowed) {  // :1306 bare_bone_search
-      detail::check(gpu_.h, b200ann_hnsw_search(gpu_.h, ix_, queries, nq, dim_, k, ef_, lab.data(), dists, st.data()), "HierarchicalNSW::searchKnn");
+      detail::check(gpu_.h, b200ann_hnsw_search(gpu_.h, ix_, (const float *)queries, nq, dim_, k, ef_, lab.data(), (float *)dists, st.data()), "HierarchicalNSW::searchKnn");
     } else {
       std::vector<uint32_t> allow = allow_bitmap(isIdAllowed);
-      detail::check(gpu_.h, b200ann_hnsw_search_filtered(gpu_.h, ix_, queries, nq, dim_, k, ef_, allow.data(), lab.data(), dists,
+      detail::check(gpu_.h, b200ann_hnsw_search_filtered(gpu_.h, ix_, (const float *)queries, nq, dim_, k, ef_, allow.data(), lab.data(), (float *)dists,
                                                          st.data(), nullptr), "HierarchicalNSW::searchKnn (filtered)");
     }
     count_metrics(st);
@@ -704,13 +711,13 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
       build_locked(nullptr);
       if (!num_deleted_ && !isIdAllowed) {
         size_t kk = k < cur_element_count ? k : cur_element_count;
-        int rc = b200ann_hnsw_search(gpu_.h, ix_, (const float *)query_data, 1, dim_, kk, ef_, lab.data(), d.data(), st.data());
+        int rc = b200ann_hnsw_search(gpu_.h, ix_, (const float *)query_data, 1, dim_, kk, ef_, lab.data(), (float *)d.data(), st.data());
         if (rc != 0 && rc != B200ANN_ERR_FEWER) detail::check(gpu_.h, rc, "HierarchicalNSW::searchKnn");
         for (size_t i = kk; i < k; i++) lab[i] = ~(uint64_t)0;
       } else {
         std::vector<uint32_t> allow = allow_bitmap(isIdAllowed);
         detail::check(gpu_.h, b200ann_hnsw_search_filtered(gpu_.h, ix_, (const float *)query_data, 1, dim_, k, ef_, allow.data(),
-                                                           lab.data(), d.data(), st.data(), nullptr), "HierarchicalNSW::searchKnn (filtered)");
+                                                           lab.data(), (float *)d.data(), st.data(), nullptr), "HierarchicalNSW::searchKnn (filtered)");
       }
     }
     count_metrics(st);
@@ -735,14 +742,14 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     std::vector<labeltype> ids(mx);
     std::vector<dist_t> d(mx);
     unsigned cnt = 0;
-    searchEpsilonBatch((const float *)query_data, 1, eps->epsilon(), eps->min_num_candidates(), mx, ids.data(), d.data(), &cnt,
+    searchEpsilonBatch(query_data, 1, eps->epsilon(), eps->min_num_candidates(), mx, ids.data(), d.data(), &cnt,
                        isIdAllowed, true);
     result.resize(cnt);
     for (unsigned i = 0; i < cnt; i++) result[i] = std::make_pair(d[i], ids[i]);
     return result;
   }
   // batched form: ids / dists [nq, max_num_candidates] ascending, counts[q] valid entries per row, the rest ~0 / +inf
-  void searchEpsilonBatch(const float *queries, size_t nq, float epsilon, size_t min_num_candidates, size_t max_num_candidates,
+  void searchEpsilonBatch(const void *queries, size_t nq, float epsilon, size_t min_num_candidates, size_t max_num_candidates,
                           labeltype *ids, dist_t *dists, unsigned *counts, BaseFilterFunctor *isIdAllowed = nullptr,
                           bool internal_ids = false) const {
     std::vector<uint64_t> lab(nq * max_num_candidates);
@@ -753,8 +760,8 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     std::vector<uint32_t> allow;
     const bool filtered = num_deleted_ || isIdAllowed;
     if (filtered) allow = allow_bitmap(isIdAllowed);
-    detail::check(gpu_.h, b200ann_hnsw_search_epsilon(gpu_.h, ix_, queries, nq, dim_, epsilon, min_num_candidates, max_num_candidates,
-                                                      filtered ? allow.data() : nullptr, internal_ids ? 1 : 0, lab.data(), dists,
+    detail::check(gpu_.h, b200ann_hnsw_search_epsilon(gpu_.h, ix_, (const float *)queries, nq, dim_, epsilon, min_num_candidates, max_num_candidates,
+                                                      filtered ? allow.data() : nullptr, internal_ids ? 1 : 0, lab.data(), (float *)dists,
                                                       cnt.data(), st.data()),
                   "HierarchicalNSW::searchStopConditionClosest");
     count_metrics(st);
@@ -792,7 +799,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     std::vector<unsigned char> del(n);
     for (size_t i = 0; i < n; i++) {
       const size_t t = labels_[i];
-      std::memcpy(&vec[t * dim_], &vec_[i * dim_], dim_ * sizeof(float));
+      std::memcpy(&vec[t * rw_], &vec_[i * rw_], rw_ * sizeof(float));
       for (size_t j = 0; j < maxM0_; j++) l0[t * maxM0_ + j] = map(links0_[i * maxM0_ + j]);
       lv[t] = element_levels_[i]; up[t] = upper_ptr_[i]; del[t] = deleted_[i];
     }
@@ -807,7 +814,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
   }
 
   labeltype getExternalLabel(tableint internal_id) const { return labels_[internal_id]; }
-  const float *getDataByInternalId(tableint internal_id) const { return &vec_[(size_t)internal_id * dim_]; }
+  const float *getDataByInternalId(tableint internal_id) const { return &vec_[(size_t)internal_id * rw_]; }  // byte rows for <int>
   b200ann_handle_t handle() const { return gpu_.h; }
   b200ann_index_t device_index() const { return ix_; }
   size_t generation() const { return gen_; }  // bumped whenever the device index is re-created
@@ -833,7 +840,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     if (ix_) { b200ann_index_destroy(ix_); ix_ = nullptr; }
     const size_t n = cur_element_count;
     if (n == 0) return;
-    detail::check(gpu_.h, b200ann_index_create(gpu_.h, vec_.data(), n, dim_, dim_, metric_, &ix_), "b200ann_index_create");
+    detail::check(gpu_.h, create_index(n, &ix_), "b200ann_index_create");
     std::vector<int32_t> lv(element_levels_.begin(), element_levels_.end());
     std::vector<uint64_t> lab(labels_.begin(), labels_.end());
     detail::check(gpu_.h, b200ann_index_set_hnsw(ix_, links0_.data(), maxM0_, lv.data(), upper_ptr_.data(),
@@ -856,11 +863,11 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     if (ix_ && !needs_rebuild_ && built_count_ == n) return;
     if (ix_ && !needs_rebuild_ && built_count_ > 0 && built_count_ < n) {
       std::vector<uint64_t> lab(labels_.begin() + built_count_, labels_.end());
-      detail::check(gpu_.h, b200ann_hnsw_insert_batch(gpu_.h, ix_, &vec_[built_count_ * dim_], dim_, lab.data(), n - built_count_,
+      detail::check(gpu_.h, b200ann_hnsw_insert_batch(gpu_.h, ix_, &vec_[built_count_ * rw_], row_stride(), lab.data(), n - built_count_,
                                                       ef_construction_, info8), "HierarchicalNSW::addPoint (b200ann_hnsw_insert_batch)");
     } else {
       if (self->ix_) { b200ann_index_destroy(self->ix_); self->ix_ = nullptr; }
-      detail::check(gpu_.h, b200ann_index_create(gpu_.h, vec_.data(), n, dim_, dim_, metric_, &self->ix_), "b200ann_index_create");
+      detail::check(gpu_.h, create_index(n, &self->ix_), "b200ann_index_create");
       std::vector<uint64_t> lab(labels_.begin(), labels_.end());
       detail::check(gpu_.h, b200ann_hnsw_build(gpu_.h, ix_, M_, ef_construction_, (uint32_t)seed_, 0, 0, lab.data(), info8),
                     "HierarchicalNSW::addPoint (b200ann_hnsw_build)");
@@ -893,6 +900,18 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
   detail::Gpu gpu_;
   int metric_ = 0;
   size_t dim_ = 0;
+  size_t data_size_ = 0;  // bytes per element: dim floats, or dim unsigned bytes for HierarchicalNSW<int> / L2SpaceI
+  size_t rw_ = 0;         // floats of vec_ one row occupies (byte rows are padded to 4 bytes)
+  void set_geometry() {
+    const bool u8 = metric_ == B200ANN_L2_U8;
+    data_size_ = u8 ? dim_ : dim_ * sizeof(float);
+    rw_ = u8 ? (dim_ + 3) / 4 : dim_;
+  }
+  size_t row_stride() const { return metric_ == B200ANN_L2_U8 ? rw_ * 4 : dim_; }  // elements between rows of vec_
+  int create_index(size_t n, b200ann_index_t *out) const {
+    if (metric_ == B200ANN_L2_U8) return b200ann_index_create_u8(gpu_.h, (const uint8_t *)vec_.data(), n, dim_, rw_ * 4, out);
+    return b200ann_index_create(gpu_.h, vec_.data(), n, dim_, dim_, metric_, out);
+  }
   size_t seed_ = 100;
   size_t gen_ = 0;
   std::vector<float> vec_;

@@ -42,7 +42,8 @@ enum {
   ORC_FASTL2_EFANNA_AVX = 7, /* ||x||^2 - 2<q,x>, DistanceFastL2, distance.h:232-322 */
   ORC_L2_SEQ_FMA = 8,    /* order of csrc/bf_knn.cu: sequential over the dimension with fmaf */
   ORC_IP_SEQ_FMA = 9,
-  ORC_L2_HYBRID_AVX = 10 /* hnsw_nsg::DistanceL2AVX::compare, hnsw_nsg/include/nsg/distance.h:325-346 */
+  ORC_L2_HYBRID_AVX = 10, /* hnsw_nsg::DistanceL2AVX::compare, hnsw_nsg/include/nsg/distance.h:325-346 */
+  ORC_L2_U8 = 11         /* hnswlib L2SqrI / L2SqrI4x over unsigned bytes, space_l2.h:255-292 (see l2_u8 below) */
 };
 
 /* space_l2.h:6-20 — sequential, multiply then add (no FMA: built with -ffp-contract=off) */
@@ -229,8 +230,23 @@ static float seq_fma(const float *a, const float *b, size_t dim, int ip) {
 
 EXPORT void orc_set_gpu_team(int team) { g_gpu_team = team; }
 
+/* space_l2.h:255-292 (L2SqrI4x unrolls by 4, L2SqrI is the plain loop; int sums, so both give the same value): the
+ * rows are dim unsigned bytes behind the float pointers, the distance is an int. It is returned as the float with
+ * the same bit pattern: for non-negative ints below 0x7F800000 float order == int order (denormals included; this
+ * file is not built with fast-math), +inf stays above every distance, and the HNSW restatements below only ever
+ * COMPARE distances - so they serve HierarchicalNSW<int> unchanged. Row strides stay in 4-byte units. */
+static float l2_u8(const float *a, const float *b, size_t dim) {
+  const unsigned char *x = (const unsigned char *)a, *y = (const unsigned char *)b;
+  int res = 0;
+  for (size_t i = 0; i < dim; i++) { int d = (int)x[i] - (int)y[i]; res += d * d; }
+  float f;
+  memcpy(&f, &res, 4);
+  return f;
+}
+
 EXPORT float orc_dist(int mode, const float *a, const float *b, size_t dim) {
   switch (mode) {
+    case ORC_L2_U8: return l2_u8(a, b, dim);
     case ORC_L2_SCALAR: return l2_scalar(a, b, dim);
     case ORC_IP_SCALAR: return 1.0f - dot_scalar(a, b, dim);
     case ORC_L2_HNSW_AVX: return l2_hnsw_avx(a, b, dim);

@@ -223,3 +223,86 @@ int ref_hnsw_links(void *p, size_t id, int level, unsigned *out) {
   return cnt;
 }
 }
+
+// ---- HierarchicalNSW<int> over L2SpaceI (space_l2.h:255-323): unsigned-byte rows, int distances. Same drivers as
+// the float wrappers above, on the UNMODIFIED reference templates instantiated with dist_t = int.
+struct RefHnswI {
+  L2SpaceI *space;
+  HierarchicalNSW<int> *index;
+  size_t dim;
+};
+extern "C" {
+void *ref_hnswi_new(size_t dim, size_t max_elements, size_t M, size_t efc, size_t seed) {
+  RefHnswI *h = new RefHnswI;
+  h->dim = dim;
+  h->space = new L2SpaceI(dim);
+  h->index = new HierarchicalNSW<int>(h->space, max_elements, M, efc, seed);
+  return h;
+}
+void ref_hnswi_free(void *p) {
+  RefHnswI *h = (RefHnswI *)p;
+  delete h->index; delete h->space; delete h;
+}
+int ref_hnswi_add(void *p, const unsigned char *data, size_t n, size_t label0, int threads) {
+  RefHnswI *h = (RefHnswI *)p;
+  if (threads <= 0) threads = omp_get_max_threads();
+  size_t start = 0;
+  if (h->index->cur_element_count == 0 && n > 0) { h->index->addPoint(data, label0); start = 1; }
+#pragma omp parallel for num_threads(threads) schedule(dynamic, 64)
+  for (long i = (long)start; i < (long)n; i++) h->index->addPoint(data + i * h->dim, label0 + i);
+  return 0;
+}
+// allow by LABEL or NULL (then plain searchKnn, the bare-bone path)
+int ref_hnswi_search(void *p, const unsigned char *q, size_t nq, size_t k, size_t ef, const unsigned char *allow,
+                     unsigned long long *labels, int *dists, int threads) {
+  RefHnswI *h = (RefHnswI *)p;
+  h->index->setEf(ef);
+  if (threads <= 0) threads = omp_get_max_threads();
+#pragma omp parallel for num_threads(threads) schedule(dynamic, 16)
+  for (long i = 0; i < (long)nq; i++) {
+    BitmapFilter f(allow);
+    auto r = h->index->searchKnn(q + i * h->dim, k, allow ? &f : nullptr);
+    size_t m = r.size();
+    for (size_t j = m; j < k; j++) { labels[i * k + j] = (unsigned long long)-1; dists[i * k + j] = 0x7FFFFFFF; }
+    while (!r.empty()) {
+      --m;
+      labels[i * k + m] = r.top().second;
+      dists[i * k + m] = r.top().first;
+      r.pop();
+    }
+  }
+  return 0;
+}
+int ref_hnswi_search_epsilon(void *p, const unsigned char *q, size_t nq, float eps, size_t min_cand, size_t max_cand,
+                             unsigned long long *ids, int *dists, unsigned *counts, int threads) {
+  RefHnswI *h = (RefHnswI *)p;
+  if (threads <= 0) threads = omp_get_max_threads();
+#pragma omp parallel for num_threads(threads) schedule(dynamic, 16)
+  for (long i = 0; i < (long)nq; i++) {
+    EpsilonSearchStopCondition<int> stop(eps, min_cand, max_cand);
+    auto r = h->index->searchStopConditionClosest(q + i * h->dim, stop, nullptr);
+    size_t m = r.size();
+    counts[i] = (unsigned)m;
+    for (size_t j = 0; j < max_cand; j++) {
+      ids[i * max_cand + j] = j < m ? (unsigned long long)r[j].second : (unsigned long long)-1;
+      dists[i * max_cand + j] = j < m ? r[j].first : 0x7FFFFFFF;
+    }
+  }
+  return 0;
+}
+int ref_hnswi_save(void *p, const char *path) {
+  try { ((RefHnswI *)p)->index->saveIndex(path); } catch (std::exception &e) { return -1; }
+  return 0;
+}
+void *ref_hnswi_load(size_t dim, const char *path) {
+  RefHnswI *h = new RefHnswI;
+  h->dim = dim;
+  h->space = new L2SpaceI(dim);
+  try {
+    h->index = new HierarchicalNSW<int>(h->space, std::string(path));
+  } catch (std::exception &e) {
+    delete h->space; delete h; return nullptr;
+  }
+  return h;
+}
+}

@@ -14,7 +14,7 @@ INVALID = 0xFFFFFFFF
 
 # oracle distance modes (oracle/oracle.c)
 (L2_SCALAR, IP_SCALAR, L2_HNSW_AVX, IP_HNSW_AVX, L2_EFANNA_AVX, L2_GPU, IP_GPU, FASTL2_EFANNA_AVX, L2_SEQ_FMA,
- IP_SEQ_FMA, L2_HYBRID_AVX) = range(11)
+ IP_SEQ_FMA, L2_HYBRID_AVX, L2_U8) = range(12)
 
 f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
 u32p = np.ctypeslib.ndpointer(np.uint32, flags="C_CONTIGUOUS")
@@ -135,9 +135,22 @@ def orc_nsg_search(base, graph, ep, q, K, L, mode, rng_mode=1, seed=0, want_stat
     return (ids, d, st) if want_stats else (ids, d)
 
 
-def orc_hnsw_search(base, h, q, k, ef, mode, variant=1, want_stats=False):
+def u8_rows(a):
+    """[n, dim] uint8 -> float32 view [n, ceil(dim/4)] of the rows zero-padded to 4 bytes: how the oracle takes byte
+    rows in mode L2_U8 (strides in 4-byte units; pass dim=<byte dim> to the orc_hnsw_* wrappers). Distances come back
+    as int32 bit patterns in the float32 arrays (.view(np.int32))."""
+    a = np.ascontiguousarray(a, np.uint8)
+    n, dim = a.shape
+    rb = (dim + 3) // 4 * 4
+    out = np.zeros((n, rb), np.uint8)
+    out[:, :dim] = a
+    return out.view(np.float32)
+
+
+def orc_hnsw_search(base, h, q, k, ef, mode, variant=1, want_stats=False, dim=None):
     """h: dict with links0, levels, upper_ptr, upper_links, labels, ep, maxlevel (see parse_hnsw)."""
-    n, dim = base.shape
+    n, sdim = base.shape
+    dim = dim or sdim
     nq = q.shape[0]
     lab = np.empty((nq, k), np.uint64)
     d = np.empty((nq, k), np.float32)
@@ -145,16 +158,17 @@ def orc_hnsw_search(base, h, q, k, ef, mode, variant=1, want_stats=False):
     up = h["upper_links"]
     if up.size == 0:
         up = np.full((1, max(1, h["maxM"])), INVALID, np.uint32)
-    oracle().orc_hnsw_search(base, n, dim, dim, h["links0"], h["links0"].shape[1], h["levels"], h["upper_ptr"],
+    oracle().orc_hnsw_search(base, n, dim, sdim, h["links0"], h["links0"].shape[1], h["levels"], h["upper_ptr"],
                              up, up.shape[1], _vp(h["labels"]), h["ep"], h["maxlevel"], q, nq, q.shape[1], k, ef,
                              mode, variant, lab, d, _vp(st))
     return (lab, d, st) if want_stats else (lab, d)
 
 
-def orc_hnsw_search_filtered(base, h, allow, q, k, ef, mode, variant=0, ccap=0, want_stats=False):
+def orc_hnsw_search_filtered(base, h, allow, q, k, ef, mode, variant=0, ccap=0, want_stats=False, dim=None):
     """allow [n] u8 by internal id (0 = filtered out or deleted). variant 0 = the reference's two heaps, 1 = the CUDA
     kernel's bounded arrays (ccap). Returns (labels, d, inexact[, stats])."""
-    n, dim = base.shape
+    n, sdim = base.shape
+    dim = dim or sdim
     nq = q.shape[0]
     lab = np.empty((nq, k), np.uint64)
     d = np.empty((nq, k), np.float32)
@@ -163,7 +177,7 @@ def orc_hnsw_search_filtered(base, h, allow, q, k, ef, mode, variant=0, ccap=0, 
     up = h["upper_links"]
     if up.size == 0:
         up = np.full((1, max(1, h["maxM"])), INVALID, np.uint32)
-    rc = oracle().orc_hnsw_search_filtered(base, n, dim, dim, h["links0"], h["links0"].shape[1], h["levels"],
+    rc = oracle().orc_hnsw_search_filtered(base, n, dim, sdim, h["links0"], h["links0"].shape[1], h["levels"],
                                            h["upper_ptr"], up, up.shape[1], _vp(h["labels"]), h["ep"], h["maxlevel"],
                                            np.ascontiguousarray(allow, np.uint8), q, nq, q.shape[1], k, ef, ccap, mode,
                                            variant, lab, d, _vp(st), _vp(bad))
@@ -171,10 +185,12 @@ def orc_hnsw_search_filtered(base, h, allow, q, k, ef, mode, variant=0, ccap=0, 
     return (lab, d, bad, st) if want_stats else (lab, d, bad)
 
 
-def orc_hnsw_search_epsilon(base, h, q, eps, min_cand, max_cand, mode, allow=None, internal_ids=True, want_stats=False):
+def orc_hnsw_search_epsilon(base, h, q, eps, min_cand, max_cand, mode, allow=None, internal_ids=True, want_stats=False,
+                            dim=None):
     """searchStopConditionClosest with EpsilonSearchStopCondition; allow [n] u8 by internal id or None.
     Returns (ids or labels [nq,max], d, counts[, stats])."""
-    n, dim = base.shape
+    n, sdim = base.shape
+    dim = dim or sdim
     nq = q.shape[0]
     lab = np.empty((nq, max_cand), np.uint64)
     d = np.empty((nq, max_cand), np.float32)
@@ -184,7 +200,7 @@ def orc_hnsw_search_epsilon(base, h, q, eps, min_cand, max_cand, mode, allow=Non
     if up.size == 0:
         up = np.full((1, max(1, h["maxM"])), INVALID, np.uint32)
     a = None if allow is None else np.ascontiguousarray(allow, np.uint8)
-    rc = oracle().orc_hnsw_search_epsilon(base, n, dim, dim, h["links0"], h["links0"].shape[1], h["levels"],
+    rc = oracle().orc_hnsw_search_epsilon(base, n, dim, sdim, h["links0"], h["links0"].shape[1], h["levels"],
                                           h["upper_ptr"], up, up.shape[1], None if internal_ids else _vp(h["labels"]),
                                           h["ep"], h["maxlevel"], _vp(a), q, nq, q.shape[1], eps, min_cand, max_cand,
                                           mode, lab, d, cnt, _vp(st))
@@ -310,10 +326,11 @@ def orc_hnsw_levels(n, M, seed=100):
     return lv
 
 
-def orc_hnsw_build(base, M, efc, mode, variant, ratio=16, bmax=4096, seed=100, label0=0):
+def orc_hnsw_build(base, M, efc, mode, variant, ratio=16, bmax=4096, seed=100, label0=0, dim=None):
     """hnswlib addPoint loop over rows 0..n-1 -> the flat dict parse_hnsw returns. variant 0 = the reference one
     point at a time, 1 = the CUDA path's batch form."""
-    n, dim = base.shape
+    n, sdim = base.shape
+    dim = dim or sdim
     lv = orc_hnsw_levels(n, M, seed)
     rows = int(lv.sum())
     links0 = np.zeros((n, 2 * M), np.uint32)
@@ -321,7 +338,7 @@ def orc_hnsw_build(base, M, efc, mode, variant, ratio=16, bmax=4096, seed=100, l
     upper = np.zeros((max(rows, 1), M), np.uint32)
     ep, ml = C.c_uint32(0), C.c_int(0)
     info = np.zeros(4, np.uint64)
-    rc = oracle().orc_hnsw_build(base, n, dim, dim, M, efc, mode, variant, ratio, bmax, lv, links0, upper_ptr, upper,
+    rc = oracle().orc_hnsw_build(base, n, dim, sdim, M, efc, mode, variant, ratio, bmax, lv, links0, upper_ptr, upper,
                                  C.byref(ep), C.byref(ml), _vp(info))
     assert rc == 0
     return dict(n=n, dim=dim, M=M, maxM=M, maxM0=2 * M, efc=max(efc, M), ep=ep.value, maxlevel=ml.value, links0=links0,
@@ -342,8 +359,9 @@ def libc():
 
 
 # ------------------------------------------------------------------ reference on-disk formats
-def parse_hnsw(path):
-    """hnswlib saveIndex blob (hnswlib/hnswlib/hnswalg.h:685-713) -> flat arrays (oracle.c layout)."""
+def parse_hnsw(path, elem="f32"):
+    """hnswlib saveIndex blob (hnswlib/hnswlib/hnswalg.h:685-713) -> flat arrays (oracle.c layout).
+    elem = "u8": a HierarchicalNSW<int> / L2SpaceI file (rows of dim unsigned bytes)."""
     raw = np.fromfile(path, np.uint8)
     hdr = raw[:96]
     q = lambda off: int(hdr[off:off + 8].view(np.uint64)[0])
@@ -357,8 +375,12 @@ def parse_hnsw(path):
     cnt = blob[:, offL0:offL0 + 2].copy().view(np.uint16).reshape(n).astype(np.int64)
     l0 = blob[:, offL0 + 4:offL0 + 4 + 4 * maxM0].copy().view(np.uint32).reshape(n, maxM0)
     links0 = np.where(np.arange(maxM0)[None, :] < cnt[:, None], l0, INVALID).astype(np.uint32)
-    dim = (label_off - off_data) // 4
-    vec = blob[:, off_data:off_data + 4 * dim].copy().view(np.float32).reshape(n, dim)
+    if elem == "u8":
+        dim = label_off - off_data
+        vec = blob[:, off_data:off_data + dim].copy()
+    else:
+        dim = (label_off - off_data) // 4
+        vec = blob[:, off_data:off_data + 4 * dim].copy().view(np.float32).reshape(n, dim)
     labels = blob[:, label_off:label_off + 8].copy().view(np.uint64).reshape(n)
     pos = 96 + n * sdpe
     levels = np.zeros(n, np.int32)
@@ -506,6 +528,16 @@ def reflib(name):
         lib.ref_hnsw_mark_deleted.argtypes = [C.c_void_p, C.c_size_t, C.c_int]
         lib.ref_hnsw_search_epsilon.argtypes = [C.c_void_p, f32p, C.c_size_t, C.c_float, C.c_size_t, C.c_size_t,
                                                 C.c_void_p, u64p, f32p, u32p, C.c_int]
+        lib.ref_hnswi_new.restype = C.c_void_p
+        lib.ref_hnswi_new.argtypes = [C.c_size_t] * 5
+        lib.ref_hnswi_load.restype = C.c_void_p
+        lib.ref_hnswi_load.argtypes = [C.c_size_t, C.c_char_p]
+        lib.ref_hnswi_free.argtypes = [C.c_void_p]
+        lib.ref_hnswi_add.argtypes = [C.c_void_p, u8p, C.c_size_t, C.c_size_t, C.c_int]
+        lib.ref_hnswi_search.argtypes = [C.c_void_p, u8p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_void_p, u64p, i32p, C.c_int]
+        lib.ref_hnswi_search_epsilon.argtypes = [C.c_void_p, u8p, C.c_size_t, C.c_float, C.c_size_t, C.c_size_t, u64p, i32p,
+                                                 u32p, C.c_int]
+        lib.ref_hnswi_save.argtypes = [C.c_void_p, C.c_char_p]
     elif name.startswith("nsg"):
         lib.ref_nsg_dist_l2.restype = C.c_float
         lib.ref_nsg_dist_l2.argtypes = [f32p, f32p, C.c_uint]
@@ -567,6 +599,44 @@ def ref_bf_knn_u8(base, q, k, lib="hnsw", threads=0):
     d = np.empty((q.shape[0], k), np.int32)
     reflib(lib).ref_bf_knn_u8(base, n, dim, q, q.shape[0], k, lab, d, threads)
     return lab, d
+
+
+class RefHnswI:
+    """the unmodified HierarchicalNSW<int> over L2SpaceI (oracle/ref_hnsw_capi.cpp ref_hnswi_*)"""
+
+    def __init__(self, dim, max_elements=0, M=16, efc=200, seed=100, path=None):
+        self.lib = reflib("hnsw")
+        self.dim = dim
+        self.h = self.lib.ref_hnswi_new(dim, max_elements, M, efc, seed) if path is None else self.lib.ref_hnswi_load(dim, path.encode())
+        assert self.h
+
+    def add(self, data, label0=0, threads=1):
+        data = np.ascontiguousarray(data, np.uint8)
+        self.lib.ref_hnswi_add(self.h, data, data.shape[0], label0, threads)
+
+    def search(self, q, k, ef, allow_by_label=None, threads=0):
+        q = np.ascontiguousarray(q, np.uint8)
+        lab = np.empty((q.shape[0], k), np.uint64)
+        d = np.empty((q.shape[0], k), np.int32)
+        a = None if allow_by_label is None else np.ascontiguousarray(allow_by_label, np.uint8)
+        self.lib.ref_hnswi_search(self.h, q, q.shape[0], k, ef, _vp(a), lab, d, threads)
+        return lab, d
+
+    def search_epsilon(self, q, eps, min_cand, max_cand, threads=0):
+        q = np.ascontiguousarray(q, np.uint8)
+        ids = np.empty((q.shape[0], max_cand), np.uint64)
+        d = np.empty((q.shape[0], max_cand), np.int32)
+        cnt = np.zeros(q.shape[0], np.uint32)
+        self.lib.ref_hnswi_search_epsilon(self.h, q, q.shape[0], eps, min_cand, max_cand, ids, d, cnt, threads)
+        return ids, d, cnt
+
+    def save(self, path):
+        assert self.lib.ref_hnswi_save(self.h, path.encode()) == 0
+
+    def close(self):
+        if self.h:
+            self.lib.ref_hnswi_free(self.h)
+            self.h = None
 
 
 class RefHnsw:

@@ -22,7 +22,7 @@ def _build(name, tmp):
 
 
 @pytest.mark.parametrize("name", ["test_efanna_shim", "test_hnswlib_shim", "test_hybrid_shim", "test_l2spacei_shim", "test_replace_deleted",
-                                  "test_hybrid_order", "test_epsilon_search"])
+                                  "test_hybrid_order", "test_epsilon_search", "test_hnswlib_int"])
 def test_shims_compile_and_fail_loudly_without_gpu(tmp_path, name):
     exe = _build(name, tmp_path)
     try:
@@ -60,6 +60,33 @@ def test_epsilon_search_driver(tmp_path):
     p = subprocess.run([exe], capture_output=True, text=True)
     print(p.stdout, p.stderr)
     assert p.returncode == 0 and "epsilon search ok" in p.stdout
+
+
+@pytest.mark.gpu
+def test_hnswlib_int_driver(tmp_path):
+    """HierarchicalNSW<int> over L2SpaceI: GPU build, recall vs BruteforceSearch<int>, save/load, filter, delete, epsilon,
+    append; then (with oracle/_ref) an index file written by the unmodified reference, searched through the shim"""
+    exe = _build("test_hnswlib_int", tmp_path)
+    p = subprocess.run([exe, str(tmp_path)], capture_output=True, text=True)
+    print(p.stdout, p.stderr)
+    assert p.returncode == 0 and "hnswlib<int> shim ok" in p.stdout
+    if not R.have_ref():
+        return
+    rng = np.random.default_rng(3)
+    n, dim, nq, k, ef = 5000, 96, 200, 10, 50
+    base = np.minimum(255, rng.gamma(1.2, 24.0, (n, dim))).astype(np.uint8)
+    q = np.minimum(255, rng.gamma(1.2, 24.0, (nq, dim))).astype(np.uint8)
+    ref = R.RefHnswI(dim, n, 16, 100)
+    ref.add(base, label0=300, threads=1)
+    path = str(tmp_path / "ref_hnswi.bin")
+    ref.save(path)
+    lab, d = ref.search(q, k, ef, threads=1)
+    with open(str(tmp_path / "expect.bin"), "wb") as f:
+        np.array([nq, k, ef], np.uint64).tofile(f)
+        q.tofile(f); lab.tofile(f); d.tofile(f)
+    p = subprocess.run([exe, path, str(dim), str(tmp_path / "expect.bin")], capture_output=True, text=True)
+    print(p.stdout, p.stderr)
+    assert p.returncode == 0 and "vs reference file ok" in p.stdout
 
 
 @pytest.mark.gpu

@@ -117,6 +117,82 @@ def test_bruteforce_ties_vs_reference():
 
 
 @pytest.fixture(scope="module")
+def hnsw_u8_case(tmp_path_factory):
+    rng = np.random.default_rng(5)
+    n, dim = 4000, 50          # dim not a multiple of 4: L2SqrI, not L2SqrI4x (space_l2.h:302-306)
+    base = np.minimum(255, rng.gamma(1.2, 24.0, (n, dim))).astype(np.uint8)
+    q = np.minimum(255, rng.gamma(1.2, 24.0, (100, dim))).astype(np.uint8)
+    h = R.RefHnswI(dim, n, 16, 200)
+    h.add(base, threads=1)
+    p = str(tmp_path_factory.mktemp("hnswi") / "h.bin")
+    h.save(p)
+    return base, q, h, R.parse_hnsw(p, elem="u8")
+
+
+def _oi(d):
+    i = d.view(np.int32).copy()
+    i[np.isinf(d)] = 0x7FFFFFFF
+    return i
+
+
+def _same_up_to_ties(base, q, rl, rd, ol, od):
+    """distances identical; labels identical except where two elements tie on the int distance (the reference's heaps
+    order equal distances by their own history, the oracle by id): a differing label must carry the same distance"""
+    oi = _oi(od)
+    assert (rd == oi).all()
+    for r, c in zip(*np.nonzero(rl != ol)):
+        a = base[int(rl[r, c])].astype(np.int64) - q[r].astype(np.int64)
+        assert int((a * a).sum()) == int(oi[r, c])
+    assert (rl != ol).mean() < 0.005
+
+
+@needs_ref
+def test_hnsw_u8_vs_reference(hnsw_u8_case):
+    """oracle mode L2_U8 == the unmodified HierarchicalNSW<int> over L2SpaceI, bit for bit: searchKnn (both
+    formulations), searchKnn with a label filter, searchStopConditionClosest with EpsilonSearchStopCondition<int>"""
+    base, q, h, H = hnsw_u8_case
+    n, dim = base.shape
+    assert (H["vectors"] == base).all()
+    bf, qf = R.u8_rows(base), R.u8_rows(q)
+    for ef in (10, 40, 200):
+        rl, rd = h.search(q, 10, ef, threads=1)
+        for variant in (0, 1):
+            ol, od = R.orc_hnsw_search(bf, H, qf, 10, ef, R.L2_U8, variant=variant, dim=dim)
+            _same_up_to_ties(base, q, rl, rd, ol, od)
+    for keep, ef in ((0.5, 40), (0.05, 30)):
+        allow = (np.random.default_rng(ef).random(n) < keep).astype(np.uint8)
+        rl, rd = h.search(q, 10, ef, allow_by_label=allow, threads=1)
+        ol, od, _ = R.orc_hnsw_search_filtered(bf, H, allow, qf, 10, ef, R.L2_U8, variant=0, dim=dim)
+        _same_up_to_ties(base, q, rl, rd, ol, od)
+    _, d50 = h.search(q, 50, 200, threads=1)
+    for kth, mn, mx in ((5, 0, 50), (20, 10, 100), (3, 30, 30)):
+        eps = float(np.median(d50[:, kth])) + 0.5
+        ri, rd, rc = h.search_epsilon(q, eps, mn, mx, threads=1)
+        oi, od, oc = R.orc_hnsw_search_epsilon(bf, H, qf, np.int32(np.floor(eps)).view(np.float32), mn, mx, R.L2_U8, dim=dim)
+        assert (rc == oc).all()
+        _same_up_to_ties(base, q, np.where(ri == np.uint64(0xFFFFFFFFFFFFFFFF), 0, ri), rd, np.where(oi == np.uint64(0xFFFFFFFFFFFFFFFF), 0, oi), od)
+
+
+@needs_ref
+def test_hnsw_u8_build_vs_reference():
+    """oracle addPoint restatement (variant 0, one point at a time) in mode L2_U8 == the graph the unmodified
+    HierarchicalNSW<int> builds single-threaded"""
+    import tempfile, os
+    rng = np.random.default_rng(9)
+    n, dim, M, efc = 1500, 32, 8, 60
+    base = np.minimum(255, rng.gamma(1.2, 24.0, (n, dim))).astype(np.uint8)
+    h = R.RefHnswI(dim, n, M, efc)
+    h.add(base, threads=1)
+    p = os.path.join(tempfile.mkdtemp(), "h.bin")
+    h.save(p)
+    Hr = R.parse_hnsw(p, elem="u8")
+    O = R.orc_hnsw_build(R.u8_rows(base), M, efc, R.L2_U8, 0, dim=dim)
+    assert (O["levels"] == Hr["levels"]).all() and O["ep"] == Hr["ep"] and O["maxlevel"] == Hr["maxlevel"]
+    same = (np.sort(O["links0"], axis=1) == np.sort(Hr["links0"], axis=1)).all(axis=1).mean()
+    assert same > 0.99, same   # integer distances tie often; the reference's heap order among equal distances is its own
+
+
+@pytest.fixture(scope="module")
 def hnsw_case(tmp_path_factory):
     base = R.data_uniform(4000, 32, 1)
     q = R.data_uniform(100, 32, 2)

@@ -54,6 +54,8 @@ _lib.b200ann_index_get_hnsw.argtypes = [_vp, _vp, _vp, _vp, _vp, _vp]
 _lib.b200ann_nndescent.argtypes = [_vp, _vp, _sz, _sz, _sz, _sz, _sz, C.c_uint32, _vp, _vp, _vp]
 _lib.b200ann_nsg_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, C.c_uint32, _vp, _vp, _vp]
 _lib.b200ann_hnsw_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _vp, _vp, _vp]
+_lib.b200ann_index_set_labels.argtypes = [_vp, _vp, _vp, _sz]
+_lib.b200ann_hnsw_update_batch.argtypes = [_vp, _vp, _vp, _vp, _sz, _sz, _vp]
 _lib.b200ann_index_create_u8.argtypes = [_vp, _vp, _sz, _sz, _sz, _vp]
 _lib.b200ann_bf_knn_noalloc.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _vp, _vp]
 NOALLOC_SCRATCH_BYTES = 16 << 20   # B200ANN_NOALLOC_SCRATCH_BYTES, include/b200ann.h
@@ -91,6 +93,8 @@ EXPORTS = [
     "b200ann_hnsw_search_filtered",
     "b200ann_bf_knn_noalloc",
     "b200ann_index_create_u8",
+    "b200ann_hnsw_update_batch",
+    "b200ann_index_set_labels",
     "b200ann_hnsw_search_epsilon",
     "b200ann_set_link_visited_bits", "b200ann_nsg_build", "b200ann_nsg_init_ep", "b200ann_nsg_link",
     "b200ann_nsg_interinsert", "b200ann_nsg_finish", "b200ann_merge_topk", "b200ann_nsg_search_from",
@@ -181,8 +185,8 @@ class Handle:
         self._check(_lib.b200ann_set_search_options(self._h, prefetch, visited_compact, ctas_per_sm))
 
     def set_search_kernel(self, version=-1, ring_stages=-1, mode=-1):
-        """version 2 = TMA row ring + register pool (default), 1 = round-1 kernel; mode 0 auto / 1 query per warp /
-        2 query per block; results are identical"""
+        """version 0 = auto (default: 2 for L <= 64, else 1), 2 = TMA row ring + register pool, 1 = round-1 kernel;
+        mode 0 auto / 1 query per warp / 2 query per block; results are identical"""
         self._check(_lib.b200ann_set_search_kernel(self._h, version, ring_stages, mode))
 
     def set_id_base(self, id_base):
@@ -332,6 +336,23 @@ class Index:
         self.n += data.shape[0]
         keys = ("beam_evals", "hops", "heuristic_evals", "batches", "upper_rows", "maxlevel", "ep", "largest_group")
         return dict(zip(keys, (int(x) for x in info)))
+
+    def hnsw_update_batch(self, ids, data):
+        """updatePoint for the elements `ids` (distinct internal ids) with the new vectors `data`, in place"""
+        ids = np.ascontiguousarray(ids, np.uint32)
+        data = np.ascontiguousarray(data, self._qt)
+        assert data.shape[0] == ids.shape[0]
+        info = np.zeros(8, np.uint64)
+        self.h._check(_lib.b200ann_hnsw_update_batch(self.h._h, self._ix, _ptr(ids), _ptr(data), data.shape[1], ids.shape[0],
+                                                     _ptr(info)))
+        keys = ("dist_evals", "hops", "heuristic_evals", "chunks", "lists_rewritten", "maxlevel", "ep", "largest_group")
+        return dict(zip(keys, (int(x) for x in info)))
+
+    def set_labels(self, ids, labels):
+        """new labels for single elements (internal ids) of an index that holds an HNSW graph"""
+        ids = np.ascontiguousarray(ids, np.uint32)
+        labels = np.ascontiguousarray(labels, np.uint64)
+        self.h._check(_lib.b200ann_index_set_labels(self._ix, _ptr(ids), _ptr(labels), ids.shape[0]))
 
     def get_hnsw(self):
         """the HNSW graph in the flat layout set_hnsw takes (dict like tests/refutil.parse_hnsw)"""

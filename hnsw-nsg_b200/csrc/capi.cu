@@ -4,6 +4,7 @@
 #include <string.h>
 #include <stdlib.h>
 #include <cstring>
+#include <algorithm>
 #include <vector>
 #include "common.cuh"
 
@@ -42,6 +43,16 @@ __global__ void u8_pad_kernel(float *d, size_t count) {
   size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   for (; i < count; i += (size_t)gridDim.x * blockDim.x)
     if (__float_as_uint(d[i]) == 0x7F800000u) d[i] = __uint_as_float(0x7FFFFFFFu);
+}
+
+// labels of single elements (a replaced deleted slot gets a new label, hnswalg.h:982-987)
+__global__ void set_labels_kernel(uint64_t *labels, const uint32_t *ids, const uint64_t *lab, size_t nb) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i < nb) labels[ids[i]] = lab[i];
+}
+__global__ void iota_labels_kernel(uint64_t *p, size_t n) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i < n) p[i] = i;
 }
 
 __global__ void regraph_kernel(const uint32_t *src, size_t sstride, uint32_t *dst, size_t dstride, size_t n,
@@ -169,7 +180,7 @@ int b200ann_set_search_kernel(b200ann_handle_t h, int version, int ring_stages, 
     h->search_mode = mode;
   }
   if (version >= 0) {
-    if (version != 1 && version != 2) return set_err(h, B200ANN_ERR_ARG, "set_search_kernel: version must be 1 or 2");
+    if (version > 2) return set_err(h, B200ANN_ERR_ARG, "set_search_kernel: version must be 0 (auto), 1 or 2");
     h->search_version = version;
   }
   if (ring_stages >= 0) {
@@ -386,6 +397,60 @@ int b200ann_hnsw_insert_batch(b200ann_handle_t h, b200ann_index_t ix, const floa
   CU_CHECK(h, din.stage((const uint8_t *)data, nb * stride * esz, h->stream));
   CallTimer t(h);
   int rc = hnsw_insert_launch(h, ix, din.d, stride * esz, nb, labels, 0, 0, info);
+  t.stop();
+  if (rc) return rc;
+  CU_CHECK(h, t.sync());
+  return 0;
+}
+
+int b200ann_index_set_labels(b200ann_index_t ix, const uint32_t *ids, const uint64_t *labels, size_t nb) {
+  if (!ix) return B200ANN_ERR_ARG;
+  b200ann_handle *h = ix->h;
+  if (!ids || !labels) return set_err(h, B200ANN_ERR_ARG, "index_set_labels: need ids and labels");
+  if (!ix->has_hnsw) return set_err(h, B200ANN_ERR_STATE, "index_set_labels: index has no HNSW graph");
+  if (nb == 0) return 0;
+  CU_CHECK(h, cudaSetDevice(h->device));
+  std::vector<uint32_t> hid(nb);
+  CU_CHECK(h, cudaMemcpy(hid.data(), ids, nb * 4, cudaMemcpyDefault));
+  for (size_t i = 0; i < nb; i++)
+    if (hid[i] >= ix->n) return set_err(h, B200ANN_ERR_ARG, "index_set_labels: an id is not a row of the index");
+  if (!ix->labels) {  // label == row number so far
+    CU_CHECK(h, cudaMalloc((void **)&ix->labels, ix->n * 8));
+    ix->cap_labels = ix->n;
+    iota_labels_kernel<<<(unsigned)((ix->n + 255) / 256), 256, 0, h->stream>>>(ix->labels, ix->n);
+    h->launches++;
+  }
+  InArg<uint32_t> iin; InArg<uint64_t> lin;
+  CU_CHECK(h, iin.stage(ids, nb, h->stream));
+  CU_CHECK(h, lin.stage(labels, nb, h->stream));
+  set_labels_kernel<<<(unsigned)((nb + 255) / 256), 256, 0, h->stream>>>(ix->labels, iin.d, lin.d, nb);
+  h->launches++;
+  CU_CHECK(h, cudaGetLastError());
+  CU_CHECK(h, cudaStreamSynchronize(h->stream));
+  return 0;
+}
+
+int b200ann_hnsw_update_batch(b200ann_handle_t h, b200ann_index_t ix, const uint32_t *ids, const float *data, size_t stride,
+                              size_t nb, uint64_t *info) {
+  if (!h || !ix) return B200ANN_ERR_ARG;
+  if (!ids || !data || stride < ix->dim) return set_err(h, B200ANN_ERR_ARG, "hnsw_update_batch: bad ids / data / stride");
+  if (nb == 0) return 0;
+  CU_CHECK(h, cudaSetDevice(h->device));
+  std::vector<uint32_t> hid(nb);
+  CU_CHECK(h, cudaMemcpy(hid.data(), ids, nb * 4, cudaMemcpyDefault));
+  {
+    std::vector<uint32_t> srt(hid);
+    std::sort(srt.begin(), srt.end());
+    if (srt.back() >= ix->n) return set_err(h, B200ANN_ERR_ARG, "hnsw_update_batch: an id is not a row of the index");
+    for (size_t i = 1; i < nb; i++)
+      if (srt[i] == srt[i - 1]) return set_err(h, B200ANN_ERR_ARG, "hnsw_update_batch: ids must be distinct within one call");
+  }
+  const size_t esz = ix_u8(ix) ? 1 : 4;
+  InArg<uint8_t> din; InArg<uint32_t> iin;
+  CU_CHECK(h, din.stage((const uint8_t *)data, nb * stride * esz, h->stream));
+  CU_CHECK(h, iin.stage(ids, nb, h->stream));
+  CallTimer t(h);
+  int rc = hnsw_update_launch(h, ix, iin.d, nb, din.d, stride * esz, info);
   t.stop();
   if (rc) return rc;
   CU_CHECK(h, t.sync());

@@ -34,7 +34,7 @@ struct b200ann_handle {
   int search_prefetch = 1;   // beam.cuh prefetch_next_row (B200ANN_SEARCH_PREFETCH=0 turns it off for A/B runs)
   int visited_compact = 0;   // 1: 16-bit visited-set entries when n allows - twice the slots in the same shared memory, but ~3x the
                              // instructions per probe; measured slower than 32-bit ids with a few % more re-evaluations (B200ANN_VISITED_COMPACT)
-  int search_version = 2;    // 2: beam2.cuh (TMA row ring, register pool); 1: round-1 kernel (B200ANN_SEARCH_VERSION)
+  int search_version = 0;    // 0: auto (v2 for L <= 64, else v1); 2: beam2.cuh (TMA row ring, register pool); 1: round-1 kernel (B200ANN_SEARCH_VERSION)
   int search_mode = 0;       // v2: 0 = auto split between one query per warp / per block, 1 = per warp only, 2 = per block only (B200ANN_SEARCH_MODE)
   int search_tail = -1;      // v2 experiments: queries run one per block at the end of a batch (-1 = the launcher's rule; B200ANN_SEARCH_TAIL)
   int ring_stages = 0;       // v2: stages of the per-warp row ring (0 = default 3; B200ANN_RING_STAGES)
@@ -201,6 +201,8 @@ void knn_tc_free(b200ann_index *ix);
 // HNSW construction (hnsw_build.cu): builds and installs the graph in the index
 int hnsw_build_launch(b200ann_handle *h, b200ann_index *ix, size_t M, size_t efc, uint32_t seed, size_t ratio, size_t bmax,
                       const uint64_t *labels_host_or_dev, uint64_t *info8);
+int hnsw_update_launch(b200ann_handle *h, b200ann_index *ix, const uint32_t *ids, size_t nb, const void *data, size_t dstride_bytes,
+                       uint64_t *info8);
 int hnsw_insert_launch(b200ann_handle *h, b200ann_index *ix, const void *data, size_t dstride_bytes, size_t nb,
                        const uint64_t *labels_host_or_dev, size_t ratio, size_t bmax, uint64_t *info8);
 

@@ -24,6 +24,7 @@
 #include <random>
 #include <vector>
 #include "beam.cuh"
+#include "topbuf.cuh"
 
 using namespace beam;
 
@@ -40,6 +41,11 @@ struct InsertParams {
   uint32_t *rev_row, *rev_src; float *rev_d;   // [(e-s) * nlev * M]
   uint32_t *rcount, *touched, *counters;       // [n + rows], [n + rows], {ntouched, maxgroup, cursor}
   unsigned long long *stats;                   // {beam distance evaluations, hops, heuristic evaluations}
+  // update mode (hnsw_update_launch, phase B = repairConnectionsForUpdate, hnswalg.h:1073-1140): the batch is
+  // upd_ids[s..e) - elements that are IN the graph; the point itself is filtered out of its candidates (:1112-1118)
+  // and its new rows go to a staging area (other warps are walking the rows it would overwrite)
+  const uint32_t *upd_ids;                     // NULL = insertion of rows [s, e)
+  uint32_t *own_stage, *own_ridx;              // [(e-s) * nlev, gstride], [(e-s) * nlev] (row index or INVALID)
 };
 
 __host__ __device__ inline uint32_t insert_smem_words(const InsertParams &ip) {
@@ -51,8 +57,9 @@ __global__ void __launch_bounds__(WARPS * 32) hnsw_insert_kernel(const InsertPar
   extern __shared__ uint32_t smem[];
   const SearchParams &p = ip.sp;
   const int warp = threadIdx.x >> 5;
-  const uint32_t pt = ip.s + blockIdx.x * WARPS + warp;
-  if (pt >= ip.e) return;
+  const uint32_t pos = blockIdx.x * WARPS + warp;  // position in the batch
+  if (ip.s + pos >= ip.e) return;
+  const uint32_t pt = ip.upd_ids ? ip.upd_ids[ip.s + pos] : ip.s + pos;
   uint32_t *base = smem + (size_t)warp * insert_smem_words(ip);
   typedef Beam<TEAM, NCH, IP, true> B;
   B b(p, base);
@@ -80,6 +87,27 @@ __global__ void __launch_bounds__(WARPS * 32) hnsw_insert_kernel(const InsertPar
     b.np = 1;
     __syncwarp();
     b.expand_all(rec);
+    if (ip.upd_ids) {  // the element finds itself (distance 0 to its own new vector): drop it from the candidates
+      int at = -1;
+      for (uint32_t j0 = 0; j0 < b.np && at < 0; j0 += 32) {
+        uint32_t j = j0 + b.lane;
+        unsigned mk = __ballot_sync(0xffffffffu, j < b.np && (b.pool_i[j] & ~FLAG) == pt);
+        if (mk) at = (int)j0 + __ffs(mk) - 1;
+      }
+      if (at >= 0) {
+        for (uint32_t j0 = (uint32_t)at; j0 + 1 < b.np; j0 += 32) {
+          uint32_t j = j0 + b.lane;
+          float td = 0.f; uint32_t ti = 0;
+          bool mv = j + 1 < b.np;
+          if (mv) { td = b.pool_d[j + 1]; ti = b.pool_i[j + 1]; }
+          __syncwarp();
+          if (mv) { b.pool_d[j] = td; b.pool_i[j] = ti; }
+          __syncwarp();
+        }
+        b.np--;
+      }
+      if (b.np == 0) continue;  // nothing but itself was reachable: the rows stay as they are (:1122)
+    }
     // ---- getNeighborsByHeuristic2(top_candidates, M): fewer than M -> all kept
     uint32_t nres = 0;
     if (b.np < ip.M) {
@@ -95,8 +123,12 @@ __global__ void __launch_bounds__(WARPS * 32) hnsw_insert_kernel(const InsertPar
     uint32_t *row; uint32_t rl;
     if (level == 0) { row = ip.links0 + (size_t)pt * p.gstride; rl = p.gstride; }
     else { row = ip.upper_links + ((size_t)p.upper_ptr[pt] + (level - 1)) * p.maxM; rl = p.maxM; }
+    if (ip.upd_ids) {
+      row = ip.own_stage + ((size_t)pos * ip.nlev + level) * p.gstride;
+      if (b.lane == 0) ip.own_ridx[(size_t)pos * ip.nlev + level] = level == 0 ? pt : p.n + p.upper_ptr[pt] + (level - 1);
+    }
     for (uint32_t i = b.lane; i < rl; i += 32) row[i] = i < nres ? res_i[nres - 1 - i] : INVALID_ID;
-    const size_t eb = ((size_t)(pt - ip.s) * ip.nlev + level) * ip.M;
+    const size_t eb = ((size_t)pos * ip.nlev + level) * ip.M;
     for (uint32_t i = b.lane; i < nres; i += 32) {
       uint32_t sn = res_i[i];
       uint32_t ridx = level == 0 ? sn : p.n + p.upper_ptr[sn] + (level - 1);
@@ -142,6 +174,7 @@ struct ReverseParams {
   uint32_t *rcount, *rfill;
   uint32_t mcap;                    // candidates a warp can hold: Mmax0 + largest group
   unsigned long long *stats;
+  int update;                       // 1: a source already present in the row is skipped (isUpdate, hnswalg.h:548-560)
 };
 __host__ __device__ inline uint32_t reverse_smem_words(const ReverseParams &rp) {
   return smem_words(rp.sp.pool_cap, rp.sp.cand_cap, rp.sp.hbits) + 4 * rp.mcap + 2 * rp.sp.gstride;
@@ -179,12 +212,25 @@ __global__ void __launch_bounds__(WARPS * 32) hnsw_reverse_kernel(const ReverseP
     if (j < cap) b.cand_i[j] = id;
   }
   __syncwarp();
+  // new sources -> ui/ud[c ..): all of the group, or (update) those the row does not hold yet
+  uint32_t kn = 0;
+  for (uint32_t i0 = 0; i0 < k; i0 += 32) {
+    uint32_t i = i0 + lane;
+    uint32_t src = i < k ? rp.g_src[off + i] : INVALID_ID;
+    bool ok = i < k;
+    if (ok && rp.update)
+      for (uint32_t j = 0; j < c; j++) ok &= b.cand_i[j] != src;
+    unsigned mk = __ballot_sync(0xffffffffu, ok);
+    if (ok) { uint32_t at = c + kn + __popc(mk & ((1u << lane) - 1)); ui[at] = src; ud[at] = rp.g_d[off + i]; }
+    kn += __popc(mk);
+  }
+  __syncwarp();
   uint32_t n_heur = 0;
-  if (c + k <= cap) {
+  if (c + kn <= cap) {
     // append in ascending id (the order a one-thread addPoint loop would append them in)
-    for (uint32_t i = lane; i < k; i += 32) {
-      uint32_t id = rp.g_src[off + i], r = 0;
-      for (uint32_t j = 0; j < k; j++) r += rp.g_src[off + j] < id;
+    for (uint32_t i = lane; i < kn; i += 32) {
+      uint32_t id = ui[c + i], r = 0;
+      for (uint32_t j = 0; j < kn; j++) r += ui[c + j] < id;
       row[c + r] = id;
     }
   } else {
@@ -193,8 +239,7 @@ __global__ void __launch_bounds__(WARPS * 32) hnsw_reverse_kernel(const ReverseP
     b.n_dist = 0;
     b.eval(c);
     for (uint32_t i = lane; i < c; i += 32) { ui[i] = b.cand_i[i]; ud[i] = b.cand_d[i]; }
-    for (uint32_t i = lane; i < k; i += 32) { ui[c + i] = rp.g_src[off + i]; ud[c + i] = rp.g_d[off + i]; }
-    const uint32_t m = c + k;
+    const uint32_t m = c + kn;
     __syncwarp();
     for (uint32_t i = lane; i < m; i += 32) {
       float di = ud[i]; uint32_t ii = ui[i], r = 0;
@@ -264,6 +309,153 @@ int launch_insert(b200ann_handle *h, const InsertParams &ip, int met) {
 int launch_reverse(b200ann_handle *h, const ReverseParams &rp, uint32_t ntouched, int met) {
   int nch = rp.sp.nch;
   HB_DISPATCH(launch_reverse_t, h, rp, ntouched);
+}
+
+// ---------------------------------------------------------------- updatePoint, phase A (hnswalg.h:993-1070)
+// The one-hop neighbours of an updated element get NEW lists: the ef_construction closest of sCand = {element} +
+// one-hop + two-hop neighbours (minus the neighbour itself), through the heuristic with Mmax. Batch form (oracle.c
+// orc_hnsw_update variant 1): every list is computed on the graph as it was before the call and staged; a row
+// claimed by several updated elements is computed for the last of them.
+struct UpdParams {
+  SearchParams sp;               // vec/stride/nch/dim, graph = links0 (gstride = maxM0), upper_*, maxM; L = ef_construction
+  const uint32_t *ids; uint32_t nb, nlev;
+  const int32_t *levels;
+  uint32_t cap2;                 // collector capacity (power of two >= 2 * ef_construction)
+  uint32_t *claim;               // [n + rows] zero-initialised
+  uint32_t *stage, *stage_ridx;  // [nb * nlev * maxM0, maxM0], [nb * nlev * maxM0]
+  unsigned long long *stats;     // [2] += heuristic evaluations; [3] += rows rewritten
+};
+__device__ __forceinline__ const uint32_t *upd_row(const SearchParams &p, uint32_t node, int layer, uint32_t &cap) {
+  if (layer == 0) { cap = p.gstride; return p.graph + (size_t)node * p.gstride; }
+  cap = p.maxM;
+  return p.upper_links + ((size_t)p.upper_ptr[node] + (layer - 1)) * p.maxM;
+}
+// work item w = (position, layer, slot) of the updated elements' lists
+__global__ void upd_claim_kernel(const UpdParams up) {
+  const SearchParams &p = up.sp;
+  size_t w = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (w >= (size_t)up.nb * up.nlev * p.gstride) return;
+  const uint32_t slot = (uint32_t)(w % p.gstride), layer = (uint32_t)((w / p.gstride) % up.nlev), pos = (uint32_t)(w / ((size_t)p.gstride * up.nlev));
+  const uint32_t u = up.ids[pos];
+  if ((int)layer > up.levels[u]) return;
+  uint32_t cap;
+  const uint32_t *row = upd_row(p, u, (int)layer, cap);
+  if (slot >= cap) return;
+  const uint32_t neigh = row[slot];
+  if (neigh == INVALID_ID) return;
+  const uint32_t ridx = layer == 0 ? neigh : p.n + p.upper_ptr[neigh] + (layer - 1);
+  atomicMax(&up.claim[ridx], pos + 1);
+}
+__host__ __device__ inline uint32_t upd_smem_words(const UpdParams &up) {
+  return smem_words(up.sp.pool_cap, up.sp.cand_cap, up.sp.hbits) + 2 * up.cap2 + 2 * up.sp.gstride;
+}
+template <int TEAM, int NCH, int IP>
+__global__ void __launch_bounds__(WARPS * 32) hnsw_update_neighbors_kernel(const UpdParams up) {
+  extern __shared__ uint32_t smem[];
+  const SearchParams &p = up.sp;
+  const int warp = threadIdx.x >> 5;
+  const size_t w = (size_t)blockIdx.x * WARPS + warp;
+  if (w >= (size_t)up.nb * up.nlev * p.gstride) return;
+  const uint32_t slot = (uint32_t)(w % p.gstride), layer = (uint32_t)((w / p.gstride) % up.nlev), pos = (uint32_t)(w / ((size_t)p.gstride * up.nlev));
+  const uint32_t u = up.ids[pos];
+  if ((int)layer > up.levels[u]) return;
+  uint32_t cap;
+  const uint32_t *r1 = upd_row(p, u, (int)layer, cap);
+  if (slot >= cap) return;
+  const uint32_t neigh = r1[slot];
+  if (neigh == INVALID_ID) return;
+  const uint32_t ridx = layer == 0 ? neigh : p.n + p.upper_ptr[neigh] + (layer - 1);
+  if (up.claim[ridx] != pos + 1) return;
+
+  uint32_t *base = smem + (size_t)warp * upd_smem_words(up);
+  typedef Beam<TEAM, NCH, IP, true> B;
+  B b(p, base);
+  TopBuf tb;
+  tb.d = reinterpret_cast<float *>(base + smem_words(p.pool_cap, p.cand_cap, p.hbits));
+  tb.i = base + smem_words(p.pool_cap, p.cand_cap, p.hbits) + up.cap2;
+  tb.cap2 = up.cap2; tb.keep = p.L; tb.lane = b.lane;
+  tb.reset();
+  uint32_t *res_i = base + smem_words(p.pool_cap, p.cand_cap, p.hbits) + 2 * up.cap2;
+  float *res_d = reinterpret_cast<float *>(res_i + p.gstride);
+  const int lane = b.lane;
+  b.load_query(p.vec + (size_t)neigh * p.stride);
+  b.n_dist = 0;
+  // chunk -1: the element and its one-hop list; chunk a: the list of one-hop neighbour a (two-hop)
+  for (int a = -1; a < (int)cap; a++) {
+    const uint32_t *row = r1;
+    if (a >= 0) {
+      const uint32_t wn = r1[a];
+      if (wn == INVALID_ID) break;
+      uint32_t c2;
+      row = upd_row(p, wn, (int)layer, c2);
+    }
+    uint32_t m = 0;
+    __syncwarp();
+    if (a < 0 && u != neigh) { if (lane == 0) b.cand_i[0] = u; m = 1; }
+    for (uint32_t j0 = 0; j0 < cap; j0 += 32) {
+      uint32_t j = j0 + lane;
+      uint32_t id = j < cap ? row[j] : INVALID_ID;
+      bool ok = id != INVALID_ID && id != neigh;
+      unsigned mk = __ballot_sync(0xffffffffu, ok);
+      if (ok) b.cand_i[m + __popc(mk & ((1u << lane) - 1))] = id;
+      m += __popc(mk);
+    }
+    __syncwarp();
+    b.eval(m);
+    tb.push_batch(b.cand_i, b.cand_d, m, 0.f, 0u, false);
+  }
+  tb.compact();
+  uint32_t nres = 0, n_heur = 0;
+  if (tb.cnt < cap) {   // getNeighborsByHeuristic2: fewer than Mmax -> all kept
+    for (uint32_t i = lane; i < tb.cnt; i += 32) { res_i[i] = tb.i[i]; res_d[i] = tb.d[i]; }
+    nres = tb.cnt;
+  } else {
+    occlude_scan(b, tb.d, tb.i, 0, tb.cnt, cap, res_i, res_d, nres, n_heur);
+  }
+  __syncwarp();
+  uint32_t *out = up.stage + w * p.gstride;
+  for (uint32_t i = lane; i < p.gstride; i += 32) out[i] = i < nres ? res_i[nres - 1 - i] : INVALID_ID;
+  if (lane == 0) {
+    up.stage_ridx[w] = ridx;
+    atomicAdd(up.stats + 0, (unsigned long long)b.n_dist);
+    atomicAdd(up.stats + 2, (unsigned long long)n_heur);
+    atomicAdd(up.stats + 3, 1ull);
+  }
+}
+// staged rows -> the graph: item t holds the new content of row ridx[t] (INVALID = nothing staged)
+__global__ void apply_rows_kernel(const uint32_t *stage, const uint32_t *ridx, size_t items, uint32_t sstride, uint32_t *links0,
+                                  uint32_t *upper_links, uint32_t n, uint32_t maxM0, uint32_t maxM) {
+  size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (e >= items * sstride) return;
+  const size_t t = e / sstride; const uint32_t j = (uint32_t)(e % sstride);
+  const uint32_t r = ridx[t];
+  if (r == INVALID_ID) return;
+  if (r < n) { if (j < maxM0) links0[(size_t)r * maxM0 + j] = stage[e]; }
+  else if (j < maxM) upper_links[(size_t)(r - n) * maxM + j] = stage[e];
+}
+// new vectors of the updated elements: row ids[i] of the index := row i of src (rb payload bytes; the padding stays 0)
+__global__ void scatter_rows_kernel(const unsigned char *src, size_t sstride_bytes, const uint32_t *ids, size_t nb, unsigned char *vec,
+                                    size_t vstride_bytes, size_t rb) {
+  size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (e >= nb * rb) return;
+  const size_t i = e / rb, c = e % rb;
+  vec[(size_t)ids[i] * vstride_bytes + c] = src[i * sstride_bytes + c];
+}
+template <int TEAM, int NCH, int IP>
+int launch_updn_t(b200ann_handle *h, const UpdParams &up) {
+  size_t smem = (size_t)WARPS * upd_smem_words(up) * 4;
+  if (smem > 227 * 1024) return set_err(h, B200ANN_ERR_ARG, "hnsw_update: ef_construction / M need more than 227 KB shared memory per block");
+  auto kern = hnsw_update_neighbors_kernel<TEAM, NCH, IP>;
+  CU_CHECK(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const size_t items = (size_t)up.nb * up.nlev * up.sp.gstride;
+  kern<<<(unsigned)((items + WARPS - 1) / WARPS), WARPS * 32, smem, h->stream>>>(up);
+  h->launches++;
+  return 0;
+}
+
+int launch_updn(b200ann_handle *h, const UpdParams &up, int met) {
+  int nch = up.sp.nch;
+  HB_DISPATCH(launch_updn_t, h, up);
 }
 
 __global__ void fill_u32_kernel(uint32_t *p, size_t count, uint32_t v) {
@@ -566,6 +758,150 @@ int hnsw_insert_launch(b200ann_handle *h, b200ann_index *ix, const void *data, s
   if (rc) return rc;
   if (info8) {
     info8[0] = hs[0]; info8[1] = hs[1]; info8[2] = hs[2]; info8[3] = batches; info8[4] = ix->upper_rows;
+    info8[5] = (uint64_t)ix->maxlevel; info8[6] = ix->hnsw_ep; info8[7] = biggest;
+  }
+  return 0;
+}
+
+// updatePoint for nb elements of a built index (hnswalg.h:993-1140; what addPoint does for a label that exists):
+// ids [nb] = DISTINCT internal ids, data = their new vectors (nb rows dstride_bytes apart), both device memory.
+// Batch form (oracle.c orc_hnsw_update variant 1): the vectors are replaced; phase A gives every one-hop neighbour of
+// an updated element a new list computed on the graph as it was; phase B re-links the elements themselves like an
+// insertion into the graph phase A left (own rows staged, reverse links grouped, present sources skipped).
+// Levels, entry point and labels do not change. info8 = {beam evaluations, hops, heuristic evaluations, chunks,
+// rows rewritten by phase A, maxlevel, entry point, largest reverse group}.
+int hnsw_update_launch(b200ann_handle *h, b200ann_index *ix, const uint32_t *ids, size_t nb, const void *data, size_t dstride_bytes,
+                       uint64_t *info8) {
+  if (!ix->has_hnsw) return set_err(h, B200ANN_ERR_STATE, "hnsw_update_batch: index has no HNSW graph (hnsw_build / set_hnsw first)");
+  cudaStream_t st = h->stream;
+  const size_t n = ix->n, rows = ix->upper_rows, maxM0 = ix->maxM0, maxM = ix->maxM;
+  const size_t M = ix->hnsw_M ? ix->hnsw_M : maxM;
+  size_t efc = ix->hnsw_efc ? ix->hnsw_efc : 200;
+  if (efc < M) efc = M;
+  if (n == 1) {  // :999-1001: a single element that is its own entry point: only the vector changes
+    scatter_rows_kernel<<<1, 256, 0, st>>>((const unsigned char *)data, dstride_bytes, ids, 1, (unsigned char *)ix->vec, ix->stride * 4, ix_row_bytes(ix));
+    h->launches++;
+    CU_CHECK(h, cudaStreamSynchronize(st));
+    return 0;
+  }
+  if (!ix->upper_owner && rows) {  // a graph installed by b200ann_index_set_hnsw: the owner of every upper row
+    std::vector<int32_t> lv(n);
+    std::vector<uint32_t> up(n), owner(rows);
+    CU_CHECK(h, cudaMemcpy(lv.data(), ix->levels, n * 4, cudaMemcpyDeviceToHost));
+    CU_CHECK(h, cudaMemcpy(up.data(), ix->upper_ptr, n * 4, cudaMemcpyDeviceToHost));
+    for (size_t i = 0; i < n; i++)
+      for (int l = 0; l < lv[i]; l++) owner[up[i] + l] = (uint32_t)i;
+    CU_CHECK(h, cudaMalloc((void **)&ix->upper_owner, rows * 4));
+    ix->cap_owner = rows;
+    CU_CHECK(h, cudaMemcpy(ix->upper_owner, owner.data(), rows * 4, cudaMemcpyHostToDevice));
+  }
+  const uint32_t nlev = (uint32_t)ix->maxlevel + 1;
+  const size_t rb = ix_row_bytes(ix);
+  {
+    const size_t tot = nb * rb;
+    scatter_rows_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>((const unsigned char *)data, dstride_bytes, ids, nb,
+                                                                     (unsigned char *)ix->vec, ix->stride * 4, rb);
+    h->launches++;
+  }
+  if (ix->graph) { cudaFree(ix->graph); ix->graph = nullptr; }
+  knn_tc_free(ix);
+  const int met = ix->metric == B200ANN_IP ? MET_IP : (ix_u8(ix) ? MET_U8 : MET_L2);
+  const size_t nr = n + rows;
+  size_t chunk = std::min<size_t>(nb, 8192);
+  while (chunk > 64 && chunk * nlev * maxM0 * maxM0 * 4 > ((size_t)1 << 30)) chunk /= 2;  // <= 1 GiB of staged phase-A rows
+  DevBuf<uint32_t> rstate, touched, counters, rev_row, rev_src, g_src, claim, stage, stage_ridx, own_stage, own_ridx;
+  DevBuf<float> rev_d, g_d;
+  DevBuf<unsigned long long> stats;
+  const size_t ecap = chunk * nlev * M, items = chunk * nlev * maxM0, oitems = chunk * nlev;
+  CU_CHECK(h, rstate.alloc(3 * nr, st));
+  CU_CHECK(h, touched.alloc(nr, st));
+  CU_CHECK(h, counters.alloc(4, st));
+  CU_CHECK(h, rev_row.alloc(ecap, st)); CU_CHECK(h, rev_src.alloc(ecap, st)); CU_CHECK(h, rev_d.alloc(ecap, st));
+  CU_CHECK(h, g_src.alloc(ecap, st)); CU_CHECK(h, g_d.alloc(ecap, st));
+  CU_CHECK(h, claim.alloc(nr, st));
+  CU_CHECK(h, stage.alloc(items * maxM0, st)); CU_CHECK(h, stage_ridx.alloc(items, st));
+  CU_CHECK(h, own_stage.alloc(oitems * maxM0, st)); CU_CHECK(h, own_ridx.alloc(oitems, st));
+  CU_CHECK(h, stats.alloc(4, st));
+  CU_CHECK(h, cudaMemsetAsync(rstate.p, 0, 3 * nr * 4, st));
+  CU_CHECK(h, cudaMemsetAsync(claim.p, 0, nr * 4, st));
+  CU_CHECK(h, cudaMemsetAsync(stats.p, 0, 4 * sizeof(unsigned long long), st));
+  uint32_t *rcount = rstate.p, *rfill = rstate.p + nr, *roff = rstate.p + 2 * nr;
+
+  SearchParams sp = {};
+  sp.vec = ix->vec; sp.stride = ix->stride; sp.n = (uint32_t)n; sp.nch = ix_nch(ix); sp.dim = (uint32_t)ix->dim;
+  sp.graph = ix->links0; sp.gstride = (uint32_t)maxM0;
+  sp.upper_links = ix->upper_links; sp.upper_ptr = ix->upper_ptr; sp.maxM = (uint32_t)maxM;
+  sp.L = (uint32_t)efc; sp.K = (uint32_t)M; sp.ep = ix->hnsw_ep; sp.maxlevel = ix->maxlevel;
+  UpdParams up = {};
+  up.sp = sp; up.sp.pool_cap = 32; up.sp.hbits = 5; up.sp.cand_cap = round_up((uint32_t)maxM0 + 1, 32);
+  up.nlev = nlev; up.levels = ix->levels;
+  up.cap2 = 64; while (up.cap2 < 2 * efc) up.cap2 <<= 1;
+  up.claim = claim.p; up.stage = stage.p; up.stage_ridx = stage_ridx.p; up.stats = stats.p;
+  InsertParams ip = {};
+  ip.sp = sp;
+  ip.sp.hbits = (h->link_visited_bits && h->link_visited_bits < 11) ? h->link_visited_bits : 11;
+  ip.sp.pool_cap = round_up((uint32_t)efc + 1, 32);
+  ip.sp.cand_cap = round_up((uint32_t)maxM0, 32);
+  ip.M = (uint32_t)M; ip.nlev = nlev; ip.levels = ix->levels; ip.links0 = ix->links0; ip.upper_links = ix->upper_links;
+  ip.rev_row = rev_row.p; ip.rev_src = rev_src.p; ip.rev_d = rev_d.p;
+  ip.rcount = rcount; ip.touched = touched.p; ip.counters = counters.p; ip.stats = stats.p;
+  ip.upd_ids = ids; ip.own_stage = own_stage.p; ip.own_ridx = own_ridx.p;
+  ReverseParams rp = {};
+  rp.sp = ip.sp; rp.sp.pool_cap = 32; rp.sp.hbits = 5;
+  rp.links0 = ix->links0; rp.upper_links = ix->upper_links; rp.row_owner = ix->upper_owner;
+  rp.touched = touched.p; rp.counters = counters.p; rp.roff = roff; rp.g_src = g_src.p; rp.g_d = g_d.p;
+  rp.rcount = rcount; rp.rfill = rfill; rp.stats = stats.p; rp.update = 1;
+  const size_t max_group = (227 * 1024 / (WARPS * 4) - smem_words(32, round_up((uint32_t)maxM0, 32), 5) - 2 * maxM0) / 4 - maxM0 - 32;
+
+  uint64_t chunks = 0, biggest = 0;
+  for (size_t s = 0; s < nb; s += chunk) {
+    const size_t e = std::min(nb, s + chunk), cn = e - s;
+    chunks++;
+    // ---- phase A
+    up.ids = ids + s; up.nb = (uint32_t)cn;
+    const size_t it = cn * nlev * maxM0;
+    CU_CHECK(h, cudaMemsetAsync(stage_ridx.p, 0xFF, it * 4, st));
+    upd_claim_kernel<<<(unsigned)((it + 255) / 256), 256, 0, st>>>(up);
+    h->launches++;
+    int rc = launch_updn(h, up, met);
+    if (rc) return rc;
+    apply_rows_kernel<<<(unsigned)((it * maxM0 + 255) / 256), 256, 0, st>>>(stage.p, stage_ridx.p, it, (uint32_t)maxM0, ix->links0,
+                                                                        ix->upper_links, (uint32_t)n, (uint32_t)maxM0, (uint32_t)maxM);
+    h->launches++;
+    CU_CHECK(h, cudaMemsetAsync(claim.p, 0, nr * 4, st));
+    // ---- phase B
+    const size_t total = cn * nlev * M;
+    CU_CHECK(h, cudaMemsetAsync(rev_row.p, 0xFF, total * 4, st));
+    CU_CHECK(h, cudaMemsetAsync(counters.p, 0, 4 * 4, st));
+    CU_CHECK(h, cudaMemsetAsync(own_ridx.p, 0xFF, cn * nlev * 4, st));
+    ip.s = (uint32_t)s; ip.e = (uint32_t)e;
+    rc = launch_insert(h, ip, met);
+    if (rc) return rc;
+    apply_rows_kernel<<<(unsigned)((cn * nlev * maxM0 + 255) / 256), 256, 0, st>>>(own_stage.p, own_ridx.p, cn * nlev, (uint32_t)maxM0,
+                                                                               ix->links0, ix->upper_links, (uint32_t)n,
+                                                                               (uint32_t)maxM0, (uint32_t)maxM);
+    h->launches++;
+    uint32_t hc[4];
+    CU_CHECK(h, cudaMemcpyAsync(hc, counters.p, sizeof hc, cudaMemcpyDeviceToHost, st));
+    CU_CHECK(h, cudaStreamSynchronize(st));
+    if (hc[0]) {
+      if (hc[1] > max_group)
+        return set_err(h, B200ANN_ERR_ARG, "hnsw_update_batch: one element collects more reverse links than a warp can hold; update in smaller batches");
+      biggest = std::max<uint64_t>(biggest, hc[1]);
+      rev_offsets_kernel<<<(hc[0] + 255) / 256, 256, 0, st>>>(touched.p, counters.p, rcount, roff, counters.p + 2);
+      rev_group_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(rev_row.p, rev_src.p, rev_d.p, total, roff, rfill, g_src.p, g_d.p);
+      h->launches += 2;
+      rp.mcap = round_up((uint32_t)maxM0 + hc[1], 32);
+      rc = launch_reverse(h, rp, hc[0], met);
+      if (rc) return rc;
+    }
+  }
+  unsigned long long hs[4] = {0, 0, 0, 0};
+  CU_CHECK(h, cudaMemcpyAsync(hs, stats.p, sizeof hs, cudaMemcpyDeviceToHost, st));
+  CU_CHECK(h, cudaStreamSynchronize(st));
+  CU_CHECK(h, cudaGetLastError());
+  if (info8) {
+    info8[0] = hs[0]; info8[1] = hs[1]; info8[2] = hs[2]; info8[3] = chunks; info8[4] = hs[3];
     info8[5] = (uint64_t)ix->maxlevel; info8[6] = ix->hnsw_ep; info8[7] = biggest;
   }
   return 0;

@@ -125,7 +125,9 @@ int launch_dim(b200ann_handle *h, const SearchParams &p0) {
   while (p.nbits < 32 && (1ull << p.nbits) < (unsigned long long)p.n) p.nbits++;
   if (p.nbits < p.hbits + 1) p.nbits = p.hbits + 1;
   p.vis16 = (h->visited_compact && p.nbits - (p.hbits + 1) <= 12) ? 1 : 0;
-  if (h->search_version != 1 && IP != MET_U8) {  // byte rows (MET_U8) run on the v1 kernel; v2: TMA row ring + register pool (beam2.cuh); B200ANN_SEARCH_VERSION=1 keeps v1 for A/B runs
+  // version 0 (default): v2 where its register pool applies (L <= 64), v1 beyond (measured, 1M x 128 NSG, L = 100:
+  // 4.33 ms v1 against 5.10 ms v2 - the shared-memory pool form of v2 has the smaller visited table)
+  if (h->search_version != 1 && IP != MET_U8 && (h->search_version == 2 || p.L <= 64)) {  // byte rows (MET_U8) run on the v1 kernel; v2: TMA row ring + register pool (beam2.cuh); B200ANN_SEARCH_VERSION=1 keeps v1 for A/B runs
     if (p.L <= 32) return launch_search2_pr1(h, p, IP == MET_IP, HNSW);
     if (p.L <= 64) return launch_search2_pr2(h, p, IP == MET_IP, HNSW);
     return launch_search2_pr0(h, p, IP == MET_IP, HNSW);

@@ -187,6 +187,8 @@ class Index:
         self._ix = None
         self._dirty = True
         self._graph = None                                        # flat HNSW dict when loaded from a file
+        self._built = 0                                           # rows linked into the device graph
+        self._upd, self._relab = set(), set()                     # linked rows whose vector / label changed since
 
     # ---- construction
     def init_index(self, max_elements, M=16, ef_construction=200, random_seed=100, allow_replace_deleted=False):
@@ -210,8 +212,11 @@ class Index:
 
     def add_items(self, data, ids=None, num_threads=-1, replace_deleted=False):
         """bindings.cpp:250-330. A label that is already present replaces that element's vector (the reference's
-        updatePoint, hnswalg.h:1158-1175); the graph is rebuilt on the next query either way."""
+        updatePoint, hnswalg.h:1158-1175). On the next query new rows are linked into the live device graph
+        (b200ann_hnsw_insert_batch) and moved rows re-linked in place (b200ann_hnsw_update_batch); nothing is rebuilt."""
         self._need_init()
+        if self._graph is not None and self._ix is None:
+            self._build()                                         # a loaded graph goes to the device before it is extended
         if replace_deleted and not self._allow_replace:           # hnswalg.h:955-957
             raise RuntimeError("Replacement of deleted elements is disabled in constructor")
         # replace_deleted (hnswalg.h:954-992): a new point takes the slot (internal id, vector, label) of an element
@@ -233,6 +238,8 @@ class Index:
                     self._lookup[lab] = at
                     self._deleted[at] = False                     # unmarkDeletedInternal, :989
                     self._vec[at] = rows[r]
+                    if at < self._built:                          # :989-991 updatePoint on the reused slot
+                        self._upd.add(at); self._relab.add(at)
                     continue
                 at = self._lookup.get(lab)
                 if at is not None:
@@ -242,6 +249,8 @@ class Index:
                     if at < len(self._vec):
                         self._vec[at] = rows[r]
                         self._deleted[at] = False                 # hnswalg.h:1166-1168: an update un-deletes
+                        if at < self._built:
+                            self._upd.add(at)
                     else:
                         new_rows[at - len(self._vec)] = r
                     continue
@@ -264,9 +273,25 @@ class Index:
         if not self._dirty and self._ix is not None:
             return
         B = _B()
+        if self._ix is not None and self._built > 0:              # a live graph: append and update in place
+            n = len(self._vec)
+            if n > self._built:
+                self._ix.hnsw_insert_batch(self._vec[self._built:], labels=self._labels[self._built:], efc=self._efc)
+            if self._upd:
+                ids = np.array(sorted(self._upd), np.uint32)
+                self._ix.hnsw_update_batch(ids, self._vec[ids])
+                if self._relab:
+                    rl = np.array(sorted(self._relab), np.uint32)
+                    self._ix.set_labels(rl, self._labels[rl])
+            self._built = n
+            self._upd, self._relab = set(), set()
+            self._dirty = False
+            return
         if self._ix is not None:
             self._ix.close()
             self._ix = None
+        self._built = 0
+        self._upd, self._relab = set(), set()
         if len(self._vec) == 0:
             self._dirty = False
             return
@@ -278,6 +303,7 @@ class Index:
         else:
             ix.hnsw_build(self._M, self._efc, self._seed, labels=self._labels)
         self._ix = ix
+        self._built = len(self._vec)
         self._dirty = False
 
     # ---- search

@@ -112,6 +112,23 @@ int b200ann_hnsw_build(b200ann_handle_t h, b200ann_index_t ix, size_t M, size_t 
 int b200ann_hnsw_insert_batch(b200ann_handle_t h, b200ann_index_t ix, const float *data /*[h|d]*/, size_t stride,
                               const uint64_t *labels /*[h|d] or NULL*/, size_t nb, size_t ef_construction,
                               uint64_t *info /*[h]*/);
+/* replaces HierarchicalNSW::updatePoint(dataPoint, internalId, 1.0) + repairConnectionsForUpdate (hnswalg.h:993-1140),
+ * i.e. what addPoint does for a label that already exists (:1160-1174), for nb elements at once and IN PLACE: ids [nb]
+ * = distinct internal ids (rows of the index), data [nb, stride] = their new vectors (bytes for a u8 index). The
+ * vectors are replaced; every one-hop neighbour of an updated element gets a new list from {element, one-hop,
+ * two-hop} through the heuristic (phase A, on the graph as it was before the call; a list claimed by several
+ * updated elements is computed for the last of them); then the elements are re-linked like an insertion with
+ * themselves filtered out of their candidates, sources already present in a neighbour's list skipped (phase B).
+ * Levels, entry point and labels do not change; no rebuild, cost proportional to nb. Any NSG graph of the index is
+ * dropped. The batch form is restated by oracle.c orc_hnsw_update variant 1 and equals it link for link; its
+ * variant 0 is the reference's one-at-a-time form, pinned to the compiled reference. Calls of more than 8192 elements
+ * are processed in chunks. info (optional, 8 x u64): {distance evaluations, expanded nodes, heuristic evaluations,
+ * chunks, lists rewritten by phase A, maxlevel, entry point, largest reverse-link group}. */
+int b200ann_hnsw_update_batch(b200ann_handle_t h, b200ann_index_t ix, const uint32_t *ids /*[h|d]*/,
+                              const float *data /*[h|d]*/, size_t stride, size_t nb, uint64_t *info /*[h]*/);
+/* new labels for single elements of an index that holds an HNSW graph: what addPoint(.., replace_deleted = true) does
+ * to the slot it reuses (hnswalg.h:982-987 setExternalLabel). ids [nb] internal ids, labels [nb]. */
+int b200ann_index_set_labels(b200ann_index_t ix, const uint32_t *ids /*[h|d]*/, const uint64_t *labels /*[h|d]*/, size_t nb);
 /* sizes of the index's HNSW graph: {maxM0, maxM, upper_rows, maxlevel, entry point} */
 int b200ann_index_hnsw_shape(b200ann_index_t ix, uint64_t *out5 /*[h]*/);
 /* copy the HNSW graph back in the layout b200ann_index_set_hnsw takes (what HierarchicalNSW::saveIndex
@@ -321,9 +338,10 @@ int b200ann_set_async(b200ann_handle_t h, int on);
  *   (a probe costs ~3x the instructions of a 32-bit atomicCAS; measured slower despite fewer re-evaluations).
  * ctas_per_sm: cap on resident blocks per SM of the persistent kernel (0 = what occupancy allows). */
 int b200ann_set_search_options(b200ann_handle_t h, int prefetch, int visited_compact, int ctas_per_sm);
-/* Which graph-search kernel runs (results are bit-identical): version 2 (default) = rows through the TMA bulk-copy
+/* Which graph-search kernel runs (results are bit-identical): version 2 = rows through the TMA bulk-copy
  * engine into a per-warp shared-memory ring of `ring_stages` stages (0 = default 1) with the pool in registers for
- * L <= 64 (csrc/beam2.cuh); version 1 = the round-1 register-load kernel (csrc/beam.cuh), kept for A/B measurements.
+ * L <= 64 (csrc/beam2.cuh); version 1 = the round-1 register-load kernel (csrc/beam.cuh); version 0 (default) =
+ * version 2 for beams of L <= 64, version 1 beyond (where it is the faster one) and for byte-row indexes.
  * mode (version 2): 0 (default) = full rounds of the resident warps run one query per warp, a remainder of at most one
  * round of blocks runs one query per block of 4 warps; 1 = one query per warp only; 2 = one query per block only.
  * -1 leaves a value as it is. */

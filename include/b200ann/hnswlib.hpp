@@ -602,7 +602,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
   // replace_deleted (:954-992, needs allow_replace_deleted in the ctor): the new point takes the slot (internal id,
   // vector, label) of an element marked deleted instead of growing the index; with no deleted element it is a plain
   // add. The reference takes *deleted_elements.begin() of an unordered_set (an unspecified one); here the smallest
-  // deleted internal id. The reference re-links the slot in place (updatePoint); here the graph is rebuilt on next use.
+  // deleted internal id. Like the reference, the slot is re-linked in place (updatePoint -> b200ann_hnsw_update_batch on next use).
   void addPoint(const void *datapoint, labeltype label, bool replace_deleted = false) override {
     if (!allow_replace_deleted_ && replace_deleted) throw std::runtime_error("Replacement of deleted elements is disabled in constructor");  // :955-957
     std::unique_lock<std::mutex> lock(mu_);
@@ -614,7 +614,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
       label_lookup_[label] = id;
       deleted_[id] = 0; num_deleted_--;      // unmarkDeletedInternal :989
       std::memcpy(&vec_[id * rw_], datapoint, data_size_);
-      needs_rebuild_ = true;
+      if (id < built_count_) { pending_upd_.insert(id); pending_lab_.insert(id); }  // :989-991 updatePoint on the slot
       return;
     }
     auto it = label_lookup_.find(label);
@@ -623,7 +623,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
         throw std::runtime_error("Can't use addPoint to update deleted elements if replacement of deleted elements is enabled.");
       if (deleted_[it->second]) { deleted_[it->second] = 0; num_deleted_--; }  // :1166-1168: an update un-deletes
       std::memcpy(&vec_[it->second * rw_], datapoint, data_size_);
-      if (it->second < built_count_) needs_rebuild_ = true;  // a linked element moved: re-link (updatePoint)
+      if (it->second < built_count_) pending_upd_.insert((tableint)it->second);  // a linked element moved: updatePoint (:1172)
       return;
     }
     if (cur_element_count >= max_elements_) throw std::runtime_error("The number of elements exceeds the specified limit");  // :1178
@@ -860,11 +860,26 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     HierarchicalNSW *self = const_cast<HierarchicalNSW *>(this);
     const size_t n = cur_element_count;
     if (n == 0) return;
-    if (ix_ && !needs_rebuild_ && built_count_ == n) return;
-    if (ix_ && !needs_rebuild_ && built_count_ > 0 && built_count_ < n) {
-      std::vector<uint64_t> lab(labels_.begin() + built_count_, labels_.end());
-      detail::check(gpu_.h, b200ann_hnsw_insert_batch(gpu_.h, ix_, &vec_[built_count_ * rw_], row_stride(), lab.data(), n - built_count_,
-                                                      ef_construction_, info8), "HierarchicalNSW::addPoint (b200ann_hnsw_insert_batch)");
+    if (ix_ && !needs_rebuild_ && built_count_ == n && pending_upd_.empty()) return;
+    if (ix_ && !needs_rebuild_ && built_count_ > 0) {
+      if (built_count_ < n) {  // appended points: linked into the live graph
+        std::vector<uint64_t> lab(labels_.begin() + built_count_, labels_.end());
+        detail::check(gpu_.h, b200ann_hnsw_insert_batch(gpu_.h, ix_, &vec_[built_count_ * rw_], row_stride(), lab.data(), n - built_count_,
+                                                        ef_construction_, info8), "HierarchicalNSW::addPoint (b200ann_hnsw_insert_batch)");
+      }
+      if (!pending_upd_.empty()) {  // moved points (addPoint on an existing label, a replaced deleted slot): updatePoint in place
+        std::vector<uint32_t> ids(pending_upd_.begin(), pending_upd_.end());
+        std::vector<float> rows(ids.size() * rw_);
+        for (size_t i = 0; i < ids.size(); i++) std::memcpy(&rows[i * rw_], &vec_[(size_t)ids[i] * rw_], rw_ * sizeof(float));
+        detail::check(gpu_.h, b200ann_hnsw_update_batch(gpu_.h, ix_, ids.data(), rows.data(), row_stride(), ids.size(), info8),
+                      "HierarchicalNSW::addPoint (b200ann_hnsw_update_batch)");
+        if (!pending_lab_.empty()) {
+          std::vector<uint32_t> lid(pending_lab_.begin(), pending_lab_.end());
+          std::vector<uint64_t> lab(lid.size());
+          for (size_t i = 0; i < lid.size(); i++) lab[i] = labels_[lid[i]];
+          detail::check(gpu_.h, b200ann_index_set_labels(ix_, lid.data(), lab.data(), lid.size()), "b200ann_index_set_labels");
+        }
+      }
     } else {
       if (self->ix_) { b200ann_index_destroy(self->ix_); self->ix_ = nullptr; }
       detail::check(gpu_.h, create_index(n, &self->ix_), "b200ann_index_create");
@@ -880,6 +895,8 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     self->built_count_ = n;
     self->needs_rebuild_ = false;
     self->host_graph_valid_ = false;
+    self->pending_upd_.clear();
+    self->pending_lab_.clear();
   }
   // host copy of the graph (saveIndex, relabel_to_labels): fetched from the device only when needed; caller holds mu_
   void sync_host_graph_locked() const {
@@ -920,7 +937,9 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
   std::vector<uint32_t> links0_, upper_ptr_, upper_links_;
   b200ann_index_t ix_ = nullptr;
   mutable size_t built_count_ = 0;        // elements linked into the device graph
-  mutable bool needs_rebuild_ = false;    // an existing element's vector changed since the graph was built
+  mutable bool needs_rebuild_ = false;    // the device graph must be built from scratch on next use
+  mutable std::set<tableint> pending_upd_;  // linked elements whose vector changed: b200ann_hnsw_update_batch on next use
+  mutable std::set<tableint> pending_lab_;  // ... whose label changed as well (replaced deleted slots)
   mutable bool host_graph_valid_ = false; // links0_ / upper_* / element_levels_ mirror the device graph
   mutable std::mutex mu_;
 };

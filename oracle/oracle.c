@@ -2059,3 +2059,237 @@ EXPORT int orc_hnsw_build(const float *data, size_t n, size_t dim, size_t stride
   free(h.cnt0); free(h.cntu); free(h.visited); free(top); free(cand); free(expanded); free(tmp); free(rev);
   return 0;
 }
+
+/* ------------------------------------------------------------------ HNSW updatePoint */
+/* HierarchicalNSW::updatePoint(dataPoint, internalId, updateNeighborProbability = 1.0) + repairConnectionsForUpdate
+ * (hnswalg.h:993-1140; what addPoint does for a label that already exists, :1160-1174), for nb elements ids[0..nb)
+ * whose new vectors are newvec [nb, stride]. data [n, stride] holds the current vectors and is updated in place;
+ * links0 / upper_links [in/out] are the flat graph (padded with ORC_INVALID); levels, upper_ptr, ep, maxlevel do not
+ * change. No element is marked deleted.
+ * variant 0: the reference, one element at a time:
+ *   A. per layer <= level(p): sCand = {p} + one-hop + two-hop neighbours (:1006-1027); every one-hop neighbour gets
+ *      a NEW list: the min(ef_construction, |sCand \ {neigh}|) closest of sCand to it (:1029-1052) through the
+ *      heuristic with Mmax (:1055), written farthest first (:1057-1068).
+ *   B. repairConnectionsForUpdate: greedy descent to level(p)+1, then per level searchBaseLayer from the running entry
+ *      point, p itself filtered out (:1112-1118), mutuallyConnectNewElement(isUpdate = true): heuristic with M, p's row
+ *      rewritten, p appended to each selected neighbour unless already there (:548-560), heuristic on overflow.
+ * variant 1: the CUDA path's batch form (csrc/hnsw_build.cu hnsw_update_launch): all new vectors are stored first;
+ *   phase A for all elements on the graph as it was before the call (a row claimed by several updated elements is
+ *   computed for the LAST of them in `ids` order), rows staged and then written; phase B for all elements on the
+ *   graph phase A left (single-pool beam), own rows staged and then written, reverse links grouped per (neighbour,
+ *   level): sources already present skipped, appended in ascending id if they fit, else heuristic over existing + new.
+ * info [2] = {distance evaluations, rows rewritten by phase A}. */
+static size_t hb_row_get(hb_t *h, uint32_t node, int level, uint32_t **row) {
+  uint32_t *cnt; unsigned cap;
+  *row = hb_row(h, node, level, &cnt, &cap);
+  return *cnt;
+}
+/* phase A for one (p, layer, neigh): the new list of neigh -> sel[0..return) ascending (d,id) */
+static size_t hb_update_neighbor(hb_t *h, uint32_t p, int layer, uint32_t neigh, orc_pair *buf, size_t bufcap) {
+  uint32_t *r1, *r2;
+  size_t n1 = hb_row_get(h, p, layer, &r1), m = 0;
+  const float *nv = h->data + h->stride * (size_t)neigh;
+  unsigned cap = layer == 0 ? h->maxM0 : h->maxM;
+  (void)bufcap;
+  /* sCand = {p} + one-hop + two-hop, as a multiset; duplicates carry identical (d,id) and are dropped after the sort */
+  if (p != neigh) { buf[m].d = hb_dist(h, nv, p); buf[m].id = p; m++; }
+  for (size_t a = 0; a < n1; a++) {
+    uint32_t w = r1[a];
+    if (w != neigh) { buf[m].d = hb_dist(h, nv, w); buf[m].id = w; m++; }
+    size_t n2 = hb_row_get(h, w, layer, &r2);
+    for (size_t b = 0; b < n2; b++)
+      if (r2[b] != neigh) { buf[m].d = hb_dist(h, nv, r2[b]); buf[m].id = r2[b]; m++; }
+  }
+  qsort(buf, m, sizeof(orc_pair), pair_cmp);
+  size_t u = 0;
+  for (size_t i = 0; i < m; i++)
+    if (u == 0 || buf[u - 1].id != buf[i].id || buf[u - 1].d != buf[i].d) buf[u++] = buf[i];
+  if (u > h->efc) u = h->efc;                                       /* elementsToKeep closest (:1034-1050) */
+  return hb_heuristic(h, buf, u, cap);
+}
+EXPORT int orc_hnsw_update(float *data, size_t n, size_t dim, size_t stride, unsigned M, unsigned efc, int mode, int variant,
+                           const int32_t *levels, uint32_t *links0, uint32_t *upper_ptr, uint32_t *upper_links, size_t rows,
+                           uint32_t ep, int maxlevel, const uint32_t *ids, const float *newvec, size_t nb, uint64_t *info) {
+  hb_t h; memset(&h, 0, sizeof h);
+  h.data = data; h.n = n; h.dim = dim; h.stride = stride; h.mode = mode;
+  h.M = M; h.maxM = M; h.maxM0 = 2 * M; h.efc = efc > M ? efc : M;
+  h.links0 = links0; h.levels = levels; h.upper_ptr = upper_ptr; h.upper_links = upper_links;
+  h.ep = ep; h.maxlevel = maxlevel;
+  h.cnt0 = (uint32_t *)calloc(n, 4); h.cntu = (uint32_t *)calloc(rows ? rows : 1, 4);
+  h.visited = (uint32_t *)calloc(n, 4);
+  for (size_t i = 0; i < n; i++) { unsigned c = 0; while (c < h.maxM0 && links0[i * h.maxM0 + c] != ORC_INVALID) c++; h.cnt0[i] = c; }
+  for (size_t r = 0; r < rows; r++) { unsigned c = 0; while (c < h.maxM && upper_links[r * h.maxM + c] != ORC_INVALID) c++; h.cntu[r] = c; }
+  const size_t bufcap = 1 + (size_t)h.maxM0 * (h.maxM0 + 1) + 8;
+  orc_pair *buf = (orc_pair *)malloc(sizeof(orc_pair) * bufcap);
+  size_t capc = h.efc + h.maxM0 + 8;
+  orc_pair *top = (orc_pair *)malloc(sizeof(orc_pair) * (capc + 1)), *cand = (orc_pair *)malloc(sizeof(orc_pair) * (n + 1));
+  uint8_t *expanded = (uint8_t *)malloc(capc + 1);
+  orc_pair *tmp = (orc_pair *)malloc(sizeof(orc_pair) * (h.maxM0 + nb + 8));
+  uint64_t rewritten = 0;
+  const size_t row_bytes = stride * sizeof(float);
+  if (variant == 0) {
+    for (size_t i = 0; i < nb; i++) {
+      const uint32_t p = ids[i];
+      memcpy(data + stride * (size_t)p, newvec + stride * i, row_bytes);
+      if (ep == p && n == 1) continue;
+      const float *q = data + stride * (size_t)p;
+      const int el = levels[p];
+      for (int layer = 0; layer <= el; layer++) {                   /* phase A */
+        uint32_t *r1;
+        size_t n1 = hb_row_get(&h, p, layer, &r1);
+        if (n1 == 0) continue;
+        /* sCand is fixed before any list of this layer is rewritten: compute all new lists, then write them */
+        uint32_t *neighs = (uint32_t *)malloc(4 * n1);
+        orc_pair *lists = (orc_pair *)malloc(sizeof(orc_pair) * n1 * h.maxM0);
+        size_t *lens = (size_t *)malloc(sizeof(size_t) * n1);
+        memcpy(neighs, r1, 4 * n1);
+        for (size_t a = 0; a < n1; a++) {
+          lens[a] = hb_update_neighbor(&h, p, layer, neighs[a], buf, bufcap);
+          memcpy(lists + a * h.maxM0, buf, sizeof(orc_pair) * lens[a]);
+        }
+        for (size_t a = 0; a < n1; a++) {
+          uint32_t *cnt; unsigned cap;
+          uint32_t *row = hb_row(&h, neighs[a], layer, &cnt, &cap);
+          hb_write_row(row, cnt, lists + a * h.maxM0, lens[a]);
+          rewritten++;
+        }
+        free(neighs); free(lists); free(lens);
+      }
+      uint32_t cur = ep;                                            /* phase B */
+      if (el < maxlevel) cur = hb_descend(&h, q, cur, maxlevel, el);
+      for (int level = el; level >= 0; level--) {
+        size_t nt = hb_search(&h, cur, q, level, 0, top, cand, expanded), f = 0;
+        for (size_t t = 0; t < nt; t++) if (top[t].id != p) top[f++] = top[t];
+        if (f == 0) continue;
+        size_t k = hb_heuristic(&h, top, f, h.M);
+        uint32_t *cnt; unsigned cap;
+        uint32_t *row = hb_row(&h, p, level, &cnt, &cap);
+        hb_write_row(row, cnt, top, k);
+        cur = top[0].id;
+        for (size_t t = 0; t < k; t++) {
+          uint32_t sn = top[k - 1 - t].id;
+          uint32_t *ocnt; unsigned ocap;
+          uint32_t *orow = hb_row(&h, sn, level, &ocnt, &ocap);
+          int present = 0;
+          for (unsigned j = 0; j < *ocnt; j++) present |= orow[j] == p;
+          if (present) continue;                                    /* :548-560 */
+          if (*ocnt < ocap) { orow[(*ocnt)++] = p; continue; }
+          size_t m = 0;
+          tmp[m].d = hb_dist(&h, q, sn); tmp[m].id = p; m++;
+          for (unsigned j = 0; j < *ocnt; j++) { tmp[m].d = hb_dist(&h, data + stride * (size_t)orow[j], sn); tmp[m].id = orow[j]; m++; }
+          size_t kk = hb_heuristic(&h, tmp, m, ocap);
+          hb_write_row(orow, ocnt, tmp, kk);
+        }
+      }
+    }
+  } else {
+    for (size_t i = 0; i < nb; i++) memcpy(data + stride * (size_t)ids[i], newvec + stride * i, row_bytes);
+    /* phase A on the snapshot: claim = last batch position per (row); staged rows */
+    const size_t nrow = n + rows;
+    uint32_t *claim = (uint32_t *)calloc(nrow, 4);
+    for (size_t i = 0; i < nb; i++) {
+      const uint32_t p = ids[i];
+      for (int layer = 0; layer <= levels[p]; layer++) {
+        uint32_t *r1; size_t n1 = hb_row_get(&h, p, layer, &r1);
+        for (size_t a = 0; a < n1; a++) {
+          size_t ridx = layer == 0 ? r1[a] : n + upper_ptr[r1[a]] + (layer - 1);
+          claim[ridx] = (uint32_t)i + 1;
+        }
+      }
+    }
+    typedef struct { uint32_t node; int layer; size_t len; } stg_t;
+    stg_t *stg = NULL; orc_pair *stgl = NULL; size_t ns = 0, caps = 0;
+    for (size_t i = 0; i < nb; i++) {
+      const uint32_t p = ids[i];
+      for (int layer = 0; layer <= levels[p]; layer++) {
+        uint32_t *r1; size_t n1 = hb_row_get(&h, p, layer, &r1);
+        for (size_t a = 0; a < n1; a++) {
+          size_t ridx = layer == 0 ? r1[a] : n + upper_ptr[r1[a]] + (layer - 1);
+          if (claim[ridx] != (uint32_t)i + 1) continue;
+          if (ns == caps) { caps = caps ? caps * 2 : 1024; stg = (stg_t *)realloc(stg, caps * sizeof(stg_t)); stgl = (orc_pair *)realloc(stgl, caps * h.maxM0 * sizeof(orc_pair)); }
+          stg[ns].node = r1[a]; stg[ns].layer = layer;
+          stg[ns].len = hb_update_neighbor(&h, p, layer, r1[a], buf, bufcap);
+          memcpy(stgl + ns * h.maxM0, buf, sizeof(orc_pair) * stg[ns].len);
+          ns++;
+          claim[ridx] = 0;   /* a row listed twice by the same element is computed once */
+        }
+      }
+    }
+    for (size_t t = 0; t < ns; t++) {
+      uint32_t *cnt; unsigned cap;
+      uint32_t *row = hb_row(&h, stg[t].node, stg[t].layer, &cnt, &cap);
+      hb_write_row(row, cnt, stgl + t * h.maxM0, stg[t].len);
+    }
+    rewritten = ns;
+    free(claim); free(stg); free(stgl);
+    /* phase B on the graph phase A left: own rows staged, reverse links grouped */
+    const unsigned nlev = (unsigned)maxlevel + 1;
+    orc_pair *own = (orc_pair *)malloc(sizeof(orc_pair) * nb * nlev * (h.M ? h.M : 1));
+    size_t *ownk = (size_t *)calloc(nb * nlev, sizeof(size_t));
+    uint8_t *ownset = (uint8_t *)calloc(nb * nlev, 1);
+    hb_rev *rev = NULL; size_t nrev = 0, caprev = 0;
+    for (size_t i = 0; i < nb; i++) {
+      const uint32_t p = ids[i];
+      const float *q = data + stride * (size_t)p;
+      if (ep == p && n == 1) continue;
+      const int el = levels[p];
+      uint32_t cur = ep;
+      if (el < maxlevel) cur = hb_descend(&h, q, cur, maxlevel, el);
+      for (int level = el; level >= 0; level--) {
+        size_t nt = hb_search(&h, cur, q, level, 1, top, cand, expanded), f = 0;
+        for (size_t t = 0; t < nt; t++) if (top[t].id != p) top[f++] = top[t];
+        if (f == 0) continue;
+        size_t k = hb_heuristic(&h, top, f, h.M);
+        memcpy(own + (i * nlev + level) * h.M, top, sizeof(orc_pair) * k);
+        ownk[i * nlev + level] = k; ownset[i * nlev + level] = 1;
+        cur = top[0].id;
+        for (size_t t = 0; t < k; t++) {
+          if (nrev == caprev) { caprev = caprev ? caprev * 2 : 4096; rev = (hb_rev *)realloc(rev, caprev * sizeof(hb_rev)); }
+          rev[nrev].row_node = top[t].id; rev[nrev].level = level; rev[nrev].src = p; rev[nrev].d = top[t].d;
+          nrev++;
+        }
+      }
+    }
+    for (size_t i = 0; i < nb; i++)
+      for (unsigned level = 0; level < nlev; level++)
+        if (ownset[i * nlev + level]) {
+          uint32_t *cnt; unsigned cap;
+          uint32_t *row = hb_row(&h, ids[i], (int)level, &cnt, &cap);
+          hb_write_row(row, cnt, own + (i * nlev + level) * h.M, ownk[i * nlev + level]);
+        }
+    if (nrev) {
+      qsort(rev, nrev, sizeof(hb_rev), rev_cmp);
+      for (size_t a = 0; a < nrev;) {
+        size_t b = a;
+        while (b < nrev && rev[b].row_node == rev[a].row_node && rev[b].level == rev[a].level) b++;
+        uint32_t sn = rev[a].row_node;
+        uint32_t *ocnt; unsigned ocap;
+        uint32_t *orow = hb_row(&h, sn, rev[a].level, &ocnt, &ocap);
+        size_t m = 0, knew = 0;
+        for (size_t t = a; t < b; t++) {
+          int present = 0;
+          for (unsigned j = 0; j < *ocnt; j++) present |= orow[j] == rev[t].src;
+          for (size_t t2 = a; t2 < t; t2++) present |= rev[t2].src == rev[t].src;   /* the same element twice in `ids` */
+          if (!present) { tmp[h.maxM0 + knew].d = rev[t].d; tmp[h.maxM0 + knew].id = rev[t].src; knew++; }
+        }
+        if (*ocnt + knew <= ocap) {
+          for (size_t t = 0; t < knew; t++) orow[(*ocnt)++] = tmp[h.maxM0 + t].id;
+        } else {
+          for (unsigned j = 0; j < *ocnt; j++) { tmp[m].d = hb_dist(&h, data + stride * (size_t)sn, orow[j]); tmp[m].id = orow[j]; m++; }
+          for (size_t t = 0; t < knew; t++) tmp[m++] = tmp[h.maxM0 + t];
+          size_t kk = hb_heuristic(&h, tmp, m, ocap);
+          hb_write_row(orow, ocnt, tmp, kk);
+        }
+        a = b;
+      }
+    }
+    free(own); free(ownk); free(ownset); free(rev);
+  }
+  for (size_t i = 0; i < n; i++)
+    for (unsigned j = h.cnt0[i]; j < h.maxM0; j++) links0[i * h.maxM0 + j] = ORC_INVALID;
+  for (size_t r = 0; r < rows; r++)
+    for (unsigned j = h.cntu[r]; j < h.maxM; j++) upper_links[r * h.maxM + j] = ORC_INVALID;
+  if (info) { info[0] = h.n_dist; info[1] = rewritten; }
+  free(h.cnt0); free(h.cntu); free(h.visited); free(buf); free(top); free(cand); free(expanded); free(tmp);
+  return 0;
+}

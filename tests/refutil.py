@@ -90,6 +90,8 @@ def oracle():
                                                 u32p, C.c_uint, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, f32p,
                                                 C.c_size_t, C.c_size_t, C.c_float, C.c_size_t, C.c_size_t, C.c_int,
                                                 u64p, f32p, u32p, C.c_void_p]
+        lib.orc_hnsw_update.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_uint, C.c_uint, C.c_int, C.c_int, i32p,
+                                        u32p, u32p, u32p, C.c_size_t, C.c_uint32, C.c_int, u32p, f32p, C.c_size_t, C.c_void_p]
         lib.orc_hnsw_levels.argtypes = [C.c_size_t, C.c_uint, C.c_uint32, i32p]
         lib.orc_hnsw_batch_end.restype = C.c_size_t
         lib.orc_hnsw_batch_end.argtypes = [C.c_size_t, C.c_size_t, i32p, C.c_int, C.c_uint, C.c_uint]
@@ -344,6 +346,30 @@ def orc_hnsw_build(base, M, efc, mode, variant, ratio=16, bmax=4096, seed=100, l
     return dict(n=n, dim=dim, M=M, maxM=M, maxM0=2 * M, efc=max(efc, M), ep=ep.value, maxlevel=ml.value, links0=links0,
                 levels=lv, upper_ptr=upper_ptr, upper_links=upper[:rows], labels=np.arange(n, dtype=np.uint64) + label0,
                 info=info)
+
+
+def orc_hnsw_update(base, h, ids, newvec, mode, variant, efc=None, dim=None):
+    """updatePoint for the elements `ids` (internal ids) with the vectors `newvec`: returns (new base, new graph dict).
+    variant 0 = the reference one element at a time, 1 = the CUDA path's batch form. h: dict as parse_hnsw returns."""
+    n, sdim = base.shape
+    dim = dim or sdim
+    data = np.ascontiguousarray(base).copy()
+    links0 = np.ascontiguousarray(h["links0"]).copy()
+    up = np.ascontiguousarray(h["upper_links"]).copy()
+    rows = up.shape[0] if up.ndim == 2 and up.size else 0
+    M = h["maxM"]
+    if rows == 0:
+        up = np.full((1, max(1, M)), INVALID, np.uint32)
+    info = np.zeros(2, np.uint64)
+    rc = oracle().orc_hnsw_update(data, n, dim, sdim, M, efc if efc is not None else h.get("efc", 200), mode, variant,
+                                  np.ascontiguousarray(h["levels"], np.int32), links0,
+                                  np.ascontiguousarray(h["upper_ptr"], np.uint32), up, rows, h["ep"], h["maxlevel"],
+                                  np.ascontiguousarray(ids, np.uint32), np.ascontiguousarray(newvec, base.dtype), len(ids),
+                                  _vp(info))
+    assert rc == 0
+    g = dict(h)
+    g.update(links0=links0, upper_links=up[:rows] if rows else h["upper_links"], info=info)
+    return data, g
 
 
 def orc_merge_topk(d, ids, kout):

@@ -22,7 +22,7 @@ def _build(name, tmp):
 
 
 @pytest.mark.parametrize("name", ["test_efanna_shim", "test_hnswlib_shim", "test_hybrid_shim", "test_l2spacei_shim", "test_replace_deleted",
-                                  "test_hybrid_order", "test_epsilon_search", "test_hnswlib_int"])
+                                  "test_hybrid_order", "test_epsilon_search", "test_hnswlib_int", "test_updates"])
 def test_shims_compile_and_fail_loudly_without_gpu(tmp_path, name):
     exe = _build(name, tmp_path)
     try:
@@ -87,6 +87,35 @@ def test_hnswlib_int_driver(tmp_path):
     p = subprocess.run([exe, path, str(dim), str(tmp_path / "expect.bin")], capture_output=True, text=True)
     print(p.stdout, p.stderr)
     assert p.returncode == 0 and "vs reference file ok" in p.stdout
+
+
+@pytest.mark.gpu
+def test_updates_driver(tmp_path):
+    """hnswlib/tests/cpp/updates_test.cpp in "update" mode on the reference's golden data: all 100000 elements are moved
+    with addPoint on their existing labels (updatePoint, in place on the GPU), then recall > 0.99 must be reachable.
+    batch_dummy_00 is regenerated the way hnswlib/tests/cpp/update_gen_data.py made it (np.random.seed(1)); the
+    regenerated final batch must equal the committed golden file."""
+    import shutil
+    gold = os.path.join(R.ROOT, "tests", "golden")
+    n, mult, nq, d, k = [int(x) for x in open(os.path.join(gold, "hnswlib_updates_config.txt")).read().split()]
+
+    def normalized(a):
+        l2 = np.atleast_1d(np.linalg.norm(a, 2, -1))
+        l2[l2 == 0] = 1
+        return a / np.expand_dims(l2, -1)
+
+    np.random.seed(1)
+    dummies = [normalized(np.float32(np.random.random((n, d)))) for _ in range(mult)]
+    final = normalized(np.float32(np.random.random((n, d))))
+    gold_final = np.fromfile(os.path.join(gold, "hnswlib_updates_batch_final.bin"), np.float32).reshape(n, d)
+    assert np.array_equal(final, gold_final)
+    dummies[0].astype(np.float32).tofile(str(tmp_path / "batch_dummy_00.bin"))
+    for f in ("batch_final.bin", "queries.bin", "gt.bin", "config.txt"):
+        shutil.copyfile(os.path.join(gold, "hnswlib_updates_" + f), str(tmp_path / f))
+    exe = _build("test_updates", tmp_path)
+    p = subprocess.run([exe, str(tmp_path)], capture_output=True, text=True)
+    print(p.stdout, p.stderr)
+    assert p.returncode == 0 and "updates ok" in p.stdout
 
 
 @pytest.mark.gpu

@@ -54,6 +54,7 @@ _lib.b200ann_index_get_hnsw.argtypes = [_vp, _vp, _vp, _vp, _vp, _vp]
 _lib.b200ann_nndescent.argtypes = [_vp, _vp, _sz, _sz, _sz, _sz, _sz, C.c_uint32, _vp, _vp, _vp]
 _lib.b200ann_nsg_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, C.c_uint32, _vp, _vp, _vp]
 _lib.b200ann_hnsw_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _vp, _vp, _vp]
+_lib.b200ann_hnsw_search_multivector.argtypes = [_vp, _vp, _vp, _sz, _sz, _vp, _sz, _sz, _sz, _vp, C.c_int, _vp, _vp, _vp, _vp]
 _lib.b200ann_index_set_labels.argtypes = [_vp, _vp, _vp, _sz]
 _lib.b200ann_hnsw_update_batch.argtypes = [_vp, _vp, _vp, _vp, _sz, _sz, _vp]
 _lib.b200ann_index_create_u8.argtypes = [_vp, _vp, _sz, _sz, _sz, _vp]
@@ -95,6 +96,7 @@ EXPORTS = [
     "b200ann_index_create_u8",
     "b200ann_hnsw_update_batch",
     "b200ann_index_set_labels",
+    "b200ann_hnsw_search_multivector",
     "b200ann_hnsw_search_epsilon",
     "b200ann_set_link_visited_bits", "b200ann_nsg_build", "b200ann_nsg_init_ep", "b200ann_nsg_link",
     "b200ann_nsg_interinsert", "b200ann_nsg_finish", "b200ann_merge_topk", "b200ann_nsg_search_from",
@@ -482,6 +484,31 @@ class Index:
         self.h._check(_lib.b200ann_hnsw_search_epsilon(self.h._h, self._ix, _ptr(q), q.shape[0], q.shape[1],
                                                        float(epsilon), int(min_num_candidates), mx, _ptr(words),
                                                        1 if internal_ids else 0, _ptr(lab), _ptr(d), _ptr(cnt), _ptr(st)))
+        return (lab, d, cnt, st) if want_stats else (lab, d, cnt)
+
+    def hnsw_search_multivector(self, q, doc_ids, num_docs, ef_collection, max_results, allow=None, internal_ids=False,
+                                want_stats=False):
+        """searchStopConditionClosest(query, MultiVectorSearchStopCondition(space, num_docs, ef_collection), filter)
+        batched (stop_condition.h:146-215). doc_ids [n] u32 by internal id. -> (labels [nq,max_results], dists,
+        counts[, stats]); row q holds counts[q] results ascending by distance covering num_docs documents."""
+        q = np.ascontiguousarray(q, self._qt)
+        doc = np.ascontiguousarray(doc_ids, np.uint32)
+        assert doc.shape == (self.n,)
+        words = None
+        if allow is not None:
+            a = np.asarray(allow).astype(bool)
+            bits = np.packbits(a, bitorder="little")
+            words = np.zeros(((self.n + 31) // 32) * 4, np.uint8)
+            words[:len(bits)] = bits
+            words = words.view(np.uint32)
+        mx = int(max_results)
+        lab = np.empty((q.shape[0], mx), np.uint64)
+        d = np.empty((q.shape[0], mx), self._dt)
+        cnt = np.zeros(q.shape[0], np.uint32)
+        st = np.zeros((q.shape[0], 2), np.uint32) if want_stats else None
+        self.h._check(_lib.b200ann_hnsw_search_multivector(self.h._h, self._ix, _ptr(q), q.shape[0], q.shape[1], _ptr(doc),
+                                                           int(num_docs), int(ef_collection), mx, _ptr(words),
+                                                           1 if internal_ids else 0, _ptr(lab), _ptr(d), _ptr(cnt), _ptr(st)))
         return (lab, d, cnt, st) if want_stats else (lab, d, cnt)
 
     def nsg_search_from(self, q, entry, K, L, seed=0, want_stats=False):

@@ -82,7 +82,8 @@ __host__ __device__ inline uint32_t smem_words(uint32_t pool_cap, uint32_t cand_
 
 // COHERENT: adjacency rows are read with ordinary (L2-coherent) loads instead of the read-only path,
 // for kernels that append edges while they search (tree_grow).
-template <int TEAM, int NCH, int IP, bool HNSW, bool COHERENT = false>
+// ROWS: candidate rows a team evaluates per round of eval() (2, or 4 for latency-bound kernels with spare registers).
+template <int TEAM, int NCH, int IP, bool HNSW, bool COHERENT = false, int ROWS = 2>
 struct Beam {
   static constexpr int TPW = 32 / TEAM;
   static constexpr int TEAMSZ = TEAM, NCHUNK = NCH;
@@ -182,16 +183,36 @@ struct Beam {
   // distances of cand_i[0..m) -> cand_d[0..m)
   __device__ __forceinline__ void eval(uint32_t m) {
     __syncwarp();
-    for (uint32_t c0 = 0; c0 < m; c0 += 2 * TPW) {
-      uint32_t i0 = c0 + g, i1 = c0 + TPW + g;
-      const float4 *r0 = nullptr, *r1 = nullptr;
-      if (i0 < m) r0 = reinterpret_cast<const float4 *>(p.vec + (size_t)cand_i[i0] * p.stride);
-      if (i1 < m) r1 = reinterpret_cast<const float4 *>(p.vec + (size_t)cand_i[i1] * p.stride);
-      float d0, d1;
-      team_dist2<TEAM, NCH, IP>(r0, r1, qreg, t, p.nch, d0, d1);
-      if (t == 0) {
-        if (i0 < m) cand_d[i0] = d0;
-        if (i1 < m) cand_d[i1] = d1;
+    if constexpr (ROWS > 2) {
+      for (uint32_t c0 = 0; c0 < m; c0 += ROWS * TPW) {
+        const float4 *r[ROWS];
+        float d[ROWS];
+#pragma unroll
+        for (int k = 0; k < ROWS; k++) {
+          const uint32_t i = c0 + k * TPW + g;
+          r[k] = i < m ? reinterpret_cast<const float4 *>(p.vec + (size_t)cand_i[i] * p.stride) : nullptr;
+        }
+        team_dist_rows<TEAM, NCH, IP, ROWS>(r, qreg, t, p.nch, d);
+        if (t == 0) {
+#pragma unroll
+          for (int k = 0; k < ROWS; k++) {
+            const uint32_t i = c0 + k * TPW + g;
+            if (i < m) cand_d[i] = d[k];
+          }
+        }
+      }
+    } else {
+      for (uint32_t c0 = 0; c0 < m; c0 += 2 * TPW) {
+        uint32_t i0 = c0 + g, i1 = c0 + TPW + g;
+        const float4 *r0 = nullptr, *r1 = nullptr;
+        if (i0 < m) r0 = reinterpret_cast<const float4 *>(p.vec + (size_t)cand_i[i0] * p.stride);
+        if (i1 < m) r1 = reinterpret_cast<const float4 *>(p.vec + (size_t)cand_i[i1] * p.stride);
+        float d0, d1;
+        team_dist2<TEAM, NCH, IP>(r0, r1, qreg, t, p.nch, d0, d1);
+        if (t == 0) {
+          if (i0 < m) cand_d[i0] = d0;
+          if (i1 < m) cand_d[i1] = d1;
+        }
       }
     }
     n_dist += m;

@@ -768,8 +768,11 @@ int b200ann_hnsw_search(b200ann_handle_t h, b200ann_index_t ix, const float *q, 
 // queries the first pass could not prove exact). allow == NULL: every element may be returned.
 static int filtered_common(b200ann_handle_t h, b200ann_index_t ix, const char *who, const float *q, size_t nq, size_t qstride,
                            size_t k, size_t ef, const uint32_t *allow, uint64_t *labels, float *dists, uint32_t *stats,
-                           uint8_t *inexact, float eps, size_t min_cand, uint32_t *counts, bool internal_ids) {
+                           uint8_t *inexact, float eps, size_t min_cand, uint32_t *counts, bool internal_ids,
+                           const uint32_t *doc = nullptr, size_t efcoll = 0, size_t docs_keep = 0) {
   CU_CHECK(h, cudaSetDevice(h->device));
+  InArg<uint32_t> docin;
+  CU_CHECK(h, docin.stage(doc, doc ? ix->n : 0, h->stream));
   QueryArg qin; InArg<uint32_t> ain; OutArg<uint64_t> ol; OutArg<float> od; OutArg<uint32_t> os, oc;
   DevBuf<uint8_t> flags;
   DevBuf<uint32_t> ones;
@@ -794,7 +797,8 @@ static int filtered_common(b200ann_handle_t h, b200ann_index_t ix, const char *w
   size_t left = 0;
   for (int pass = 0; pass < 2; pass++) {
     int rc = launch_hnsw_search_filtered(h, ix, qin.d, nq, qin.qstride, k, ef, adev, 0, pass == 1, pass ? flags.p : nullptr,
-                                         ol.d, od.d, os.d, flags.p, nullptr, eps, min_cand, oc.d, internal_ids);
+                                         ol.d, od.d, os.d, flags.p, nullptr, eps, min_cand, oc.d, internal_ids, docin.d, efcoll,
+                                         docs_keep);
     if (rc) return rc;
     CU_CHECK(h, cudaMemcpyAsync(hf.data(), flags.p, nq, cudaMemcpyDeviceToHost, h->stream));
     CU_CHECK(h, cudaStreamSynchronize(h->stream));
@@ -811,8 +815,10 @@ static int filtered_common(b200ann_handle_t h, b200ann_index_t ix, const char *w
   CU_CHECK(h, t.sync());
   if (inexact) std::memcpy(inexact, hf.data(), nq);
   else if (left) {
-    std::string m = std::string(who) + ": the filter is too selective for the graph walk on some queries "
-                    "(candidate set overflow); pass `inexact` to see which, or scan the allowed rows with bf_knn";
+    std::string m = std::string(who) + (doc ? ": the result list of some query needs more than max_results slots (or its candidate set "
+                                              "overflowed); raise max_results"
+                                            : ": the filter is too selective for the graph walk on some queries "
+                                              "(candidate set overflow); pass `inexact` to see which, or scan the allowed rows with bf_knn");
     return set_err(h, B200ANN_ERR_CAPACITY, m.c_str());
   }
   return 0;
@@ -844,6 +850,20 @@ int b200ann_hnsw_search_epsilon(b200ann_handle_t h, b200ann_index_t ix, const fl
   if (nq == 0) return 0;
   return filtered_common(h, ix, "hnsw_search_epsilon", q, nq, qstride, max_num_candidates, max_num_candidates, allow, labels, dists,
                          stats, nullptr, epsilon, min_num_candidates, counts, internal_ids != 0);
+}
+
+int b200ann_hnsw_search_multivector(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_t nq, size_t qstride,
+                                    const uint32_t *doc_ids, size_t num_docs_to_search, size_t ef_collection, size_t max_results,
+                                    const uint32_t *allow, int internal_ids, uint64_t *labels, float *dists, uint32_t *counts,
+                                    uint32_t *stats) {
+  if (!h || !ix) return B200ANN_ERR_ARG;
+  if (!ix->has_hnsw) return set_err(h, B200ANN_ERR_STATE, "hnsw_search_multivector: index has no HNSW graph (set_hnsw / hnsw_build first)");
+  if (!q || !doc_ids || !labels || !dists || !counts || max_results == 0 || num_docs_to_search == 0 || qstride < ix->dim)
+    return set_err(h, B200ANN_ERR_ARG, "hnsw_search_multivector: need q, doc_ids, labels, dists, counts, num_docs_to_search > 0, max_results > 0, qstride >= dim");
+  if (ef_collection < num_docs_to_search) ef_collection = num_docs_to_search;  // stop_condition.h:164
+  if (nq == 0) return 0;
+  return filtered_common(h, ix, "hnsw_search_multivector", q, nq, qstride, max_results, max_results, allow, labels, dists, stats, nullptr,
+                         INFINITY, 0, counts, internal_ids != 0, doc_ids, ef_collection, num_docs_to_search);
 }
 
 }  // extern "C"

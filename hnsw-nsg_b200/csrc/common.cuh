@@ -183,7 +183,7 @@ int launch_hnsw_search_filtered(b200ann_handle *h, const b200ann_index *ix, cons
                                 size_t k, size_t ef, const uint32_t *allow_bits, size_t ccap, bool big,
                                 const uint8_t *only, uint64_t *labels, float *dists, uint32_t *stats, uint8_t *inexact,
                                 size_t *ccap_used, float eps = INFINITY, size_t min_cand = 0, uint32_t *counts = nullptr,
-                                bool internal_ids = false);
+                                bool internal_ids = false, const uint32_t *doc = nullptr, size_t efcoll = 0, size_t docs_keep = 0);
 int launch_merge_topk(b200ann_handle *h, const float *d, const uint32_t *ids, size_t parts, size_t nq, size_t k, size_t kout,
                       float *out_d, uint32_t *out_i);
 int launch_bf_knn(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,

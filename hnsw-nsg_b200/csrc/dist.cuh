@@ -118,5 +118,44 @@ __device__ __forceinline__ void team_dist2(const float4 *r0, const float4 *r1, c
   }
 }
 
+// The same for ROWS rows per team in one go (ROWS * NCH independent 16-byte loads in flight per lane): for kernels that
+// are bound by the latency of a single warp's dependent hops and have registers to spare (the HNSW insertion beam).
+// Per-row arithmetic and its order are those of team_dist2: same bits.
+template <int TEAM, int NCH, int IP, int ROWS>
+__device__ __forceinline__ void team_dist_rows(const float4 *const (&r)[ROWS], const float4 (&q)[NCH], int t, int nch,
+                                               float (&d)[ROWS]) {
+  float4 v[ROWS][NCH];
+  const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int k = 0; k < ROWS; k++)
+#pragma unroll
+    for (int c = 0; c < NCH; c++) {
+      int ch = t + c * TEAM;
+      v[k][c] = (r[k] != nullptr && ch < nch) ? ld_row16(r[k] + ch) : z;
+    }
+  if constexpr (IP == MET_U8) {
+#pragma unroll
+    for (int k = 0; k < ROWS; k++) {
+      uint32_t u = 0;
+#pragma unroll
+      for (int c = 0; c < NCH; c++)
+        if (t + c * TEAM < nch) u = acc16_u8(u, q[c], v[k][c]);
+#pragma unroll
+      for (int off = TEAM / 2; off >= 1; off >>= 1) u += __shfl_xor_sync(0xffffffffu, u, off);
+      d[k] = __uint_as_float(u);
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < ROWS; k++) {
+      float a = 0.f;
+#pragma unroll
+      for (int c = 0; c < NCH; c++)
+        if (t + c * TEAM < nch) a = acc4<IP>(a, q[c], v[k][c]);
+      a = team_reduce<TEAM>(a);
+      d[k] = IP == MET_IP ? 1.0f - a : a;
+    }
+  }
+}
+
 // team size / chunks-per-lane rule shared by all launchers (and restated in tests via b200ann_dist_team)
 __host__ __device__ inline int dist_team_for_nch(int nch) { return nch <= 64 ? 8 : 32; }

@@ -61,7 +61,7 @@ __global__ void __launch_bounds__(WARPS * 32) hnsw_insert_kernel(const InsertPar
   if (ip.s + pos >= ip.e) return;
   const uint32_t pt = ip.upd_ids ? ip.upd_ids[ip.s + pos] : ip.s + pos;
   uint32_t *base = smem + (size_t)warp * insert_smem_words(ip);
-  typedef Beam<TEAM, NCH, IP, true> B;
+  typedef Beam<TEAM, NCH, IP, true, false, (NCH <= 4 ? 4 : 2)> B;  // 4 rows per team in flight: one warp's hops are the critical path
   B b(p, base);
   uint32_t *res_i = base + smem_words(p.pool_cap, p.cand_cap, p.hbits);
   float *res_d = reinterpret_cast<float *>(res_i + p.gstride);

@@ -40,10 +40,16 @@ struct FilterParams {
   float eps;
   uint32_t min_cand;
   uint32_t *counts;
+  // MultiVectorSearchStopCondition (stop_condition.h:146-215): doc [n] = document id of every element (NULL = off).
+  // The result set is bounded by its number of DISTINCT documents (efcoll), not by its size; afterwards the farthest
+  // results are dropped until docs_keep documents are left. s.L = capacity of the result list (an overflow is reported
+  // through `inexact`).
+  const uint32_t *doc;
+  uint32_t efcoll, docs_keep;
 };
 
 __host__ __device__ inline uint32_t fsmem_words(const FilterParams &p) {
-  return smem_words(p.s.pool_cap, p.s.cand_cap, 0) + (p.gheap_d ? 0u : 2 * p.ccap);
+  return smem_words(p.s.pool_cap, p.s.cand_cap, 0) + (p.gheap_d ? 0u : 2 * p.ccap) + (p.doc ? p.s.pool_cap : 0u);
 }
 
 // number of entries of a[lo, lo+n) ordered before (d,id)
@@ -72,6 +78,27 @@ __device__ __forceinline__ void shift_up(float *ad, uint32_t *ai, int from, int 
     if (mv) { ad[j + 1] = td; ai[j + 1] = ti; }
     __syncwarp();
   }
+}
+__device__ __forceinline__ void shift_up1(uint32_t *a, int from, int to, int lane) {
+  if (to <= from) return;
+  for (int jb = from + ((to - 1 - from) / 32) * 32; jb >= from; jb -= 32) {
+    int j = jb + lane;
+    bool mv = j < to;
+    uint32_t t = 0;
+    if (mv) t = a[j];
+    __syncwarp();
+    if (mv) a[j + 1] = t;
+    __syncwarp();
+  }
+}
+// is document D among a[0, n)?
+__device__ __forceinline__ bool has_doc(const uint32_t *a, uint32_t n, uint32_t D, int lane) {
+  bool f = false;
+  for (uint32_t j0 = 0; j0 < n && !f; j0 += 32) {
+    uint32_t j = j0 + lane;
+    f = __any_sync(0xffffffffu, j < n && a[j] == D);
+  }
+  return f;
 }
 __device__ __forceinline__ bool pless(float da, uint32_t ia, float db, uint32_t ib) {
   return da < db || (da == db && ia < ib);
@@ -141,6 +168,8 @@ __global__ void __launch_bounds__(FW * 32) hnsw_filtered_kernel(const FilterPara
   uint32_t *vis = fp.visited + (size_t)gw * fp.vwords;
   const int lane = b.lane;
   const uint32_t ef = p.L;
+  const bool docm = fp.doc != nullptr;
+  uint32_t *pool_doc = base + smem_words(p.pool_cap, p.cand_cap, 0) + (fp.gheap_d ? 0u : 2 * fp.ccap);  // doc mode only
 
   for (uint32_t qi = gw; qi < p.nq; qi += fp.total_warps) {
     if (fp.only && !fp.only[qi]) continue;
@@ -151,7 +180,7 @@ __global__ void __launch_bounds__(FW * 32) hnsw_filtered_kernel(const FilterPara
     }
     float curdist;
     const uint32_t ep = b.descend_upper(p.ep, curdist);
-    uint32_t nt = 0, nc = 0;
+    uint32_t nt = 0, nc = 0, ndocs = 0;
     float LB, dmin = INFINITY;
     bool bad = false;
     const bool ep_ok = (__ldg(fp.allow + (ep >> 5)) >> (ep & 31)) & 1u;
@@ -159,6 +188,7 @@ __global__ void __launch_bounds__(FW * 32) hnsw_filtered_kernel(const FilterPara
       LB = curdist;
       if (lane == 0) { b.pool_d[0] = curdist; b.pool_i[0] = ep; cd[0] = curdist; ci[0] = ep; }
       nt = 1;
+      if (docm) { if (lane == 0) pool_doc[0] = __ldg(fp.doc + ep); ndocs = 1; }
     } else {      // :334-337: queued at FLT_MAX, never evaluated by the base layer
       LB = 3.402823466e+38f;
       if (lane == 0) { cd[0] = LB; ci[0] = ep; }
@@ -169,10 +199,12 @@ __global__ void __launch_bounds__(FW * 32) hnsw_filtered_kernel(const FilterPara
 
     for (;;) {
       const float c0d = nc ? cd[0] : INFINITY;
-      if (dmin < INFINITY && (nc == 0 || dmin <= c0d) && !(dmin > LB && nt == ef) &&
+      // "the result set is full": ef elements, or (multi-vector) efcoll distinct documents (stop_condition.h:186-199)
+      bool full = docm ? ndocs == fp.efcoll : nt == ef;
+      if (dmin < INFINITY && (nc == 0 || dmin <= c0d) && !(dmin > LB && full) &&
           !(dmin > fp.eps && nt >= fp.min_cand)) bad = true;
       if (nc == 0) break;
-      if (c0d > LB && nt == ef) break;  // :355, stop_condition.h:243
+      if (c0d > LB && full) break;  // :355, stop_condition.h:243 / :186
       if (c0d > fp.eps && nt >= fp.min_cand) break;  // stop_condition.h:247: out of the epsilon ball, enough seen
       const uint32_t node = ci[0];
       __syncwarp();
@@ -201,14 +233,16 @@ __global__ void __launch_bounds__(FW * 32) hnsw_filtered_kernel(const FilterPara
       for (uint32_t c0 = 0; c0 < m; c0 += 32) {
         uint32_t c = c0 + lane;
         float d = c < m ? b.cand_d[c] : INFINITY;
-        bool pass = c < m && (nt < ef || d < LB);
+        full = docm ? ndocs == fp.efcoll : nt == ef;
+        bool pass = c < m && (!full || d < LB);
         unsigned mask = __ballot_sync(0xffffffffu, pass);
         while (mask) {
           int bsel = __ffs(mask) - 1;
           mask &= mask - 1;
           float dd = __shfl_sync(0xffffffffu, d, bsel);
           uint32_t id = b.cand_i[c0 + bsel];
-          if (!(nt < ef || dd < LB)) continue;  // :395 with the live bound
+          full = docm ? ndocs == fp.efcoll : nt == ef;
+          if (!(!full || dd < LB)) continue;  // :395 with the live bound
           // candidate_set.emplace (:398)
           if (nc == fp.ccap) {  // full: the farthest of (entries, new) goes
             uint32_t slot = heap_argmax(cd, ci, nc, lane);
@@ -220,7 +254,7 @@ __global__ void __launch_bounds__(FW * 32) hnsw_filtered_kernel(const FilterPara
               yd = ld;
               if (lane == 0) heap_sift_up(cd, ci, slot, dd, id);  // a leaf got smaller: it can only move up
             }
-            if (!(nt == ef && yd > LB) && yd < dmin) dmin = yd;
+            if (!(full && yd > LB) && yd < dmin) dmin = yd;
           } else {
             if (lane == 0) heap_sift_up(cd, ci, nc, dd, id);
             nc++;
@@ -228,12 +262,37 @@ __global__ void __launch_bounds__(FW * 32) hnsw_filtered_kernel(const FilterPara
           __syncwarp();
           // top_candidates.emplace for allowed elements (:406-408), pop the farthest beyond ef (:413-424)
           if ((__ldg(fp.allow + (id >> 5)) >> (id & 31)) & 1u) {
-            if (nt == ef) nt--;  // the new element is closer than the farthest one (dd < LB)
-            uint32_t before = count_before(b.pool_d, b.pool_i, 0, nt, dd, id, lane);
-            shift_up(b.pool_d, b.pool_i, (int)before, (int)nt, lane);
-            if (lane == 0) { b.pool_d[before] = dd; b.pool_i[before] = id; }
-            nt++;
-            __syncwarp();
+            if (!docm) {
+              if (nt == ef) nt--;  // the new element is closer than the farthest one (dd < LB)
+              uint32_t before = count_before(b.pool_d, b.pool_i, 0, nt, dd, id, lane);
+              shift_up(b.pool_d, b.pool_i, (int)before, (int)nt, lane);
+              if (lane == 0) { b.pool_d[before] = dd; b.pool_i[before] = id; }
+              nt++;
+              __syncwarp();
+            } else {
+              // add_point_to_result (stop_condition.h:167-174), then drop the farthest results while more than efcoll
+              // documents are held (should_remove_extra / remove_point_from_result, :176-183, :201-204)
+              const uint32_t D = __ldg(fp.doc + id);
+              uint32_t before = count_before(b.pool_d, b.pool_i, 0, nt, dd, id, lane);
+              if (nt == ef) {          // the list is out of slots: the farthest of (list, new) cannot be kept
+                bad = true;
+                if (before == nt) before = 0xffffffffu;
+                else { const uint32_t Dl = pool_doc[nt - 1]; nt--; if (!has_doc(pool_doc, nt, Dl, lane)) ndocs--; }
+              }
+              if (before != 0xffffffffu) {
+                if (!has_doc(pool_doc, nt, D, lane)) ndocs++;
+                shift_up(b.pool_d, b.pool_i, (int)before, (int)nt, lane);
+                shift_up1(pool_doc, (int)before, (int)nt, lane);
+                if (lane == 0) { b.pool_d[before] = dd; b.pool_i[before] = id; pool_doc[before] = D; }
+                nt++;
+                __syncwarp();
+                while (ndocs > fp.efcoll) {
+                  const uint32_t Dl = pool_doc[nt - 1];
+                  nt--;
+                  if (!has_doc(pool_doc, nt, Dl, lane)) ndocs--;
+                }
+              }
+            }
           }
           if (nt) LB = b.pool_d[nt - 1];  // :426-427
         }
@@ -242,6 +301,13 @@ __global__ void __launch_bounds__(FW * 32) hnsw_filtered_kernel(const FilterPara
 
     // filter_results (stop_condition.h:265-272): the list is ascending, so dropping the tail beyond epsilon leaves
     // the entries with distance <= epsilon (NaN-free data); nt <= ef = max_num_candidates already
+    if (docm) {  // multi-vector filter_results (:206-219): the farthest results go until docs_keep documents are left
+      while (ndocs > fp.docs_keep && nt > 0) {
+        const uint32_t Dl = pool_doc[nt - 1];
+        nt--;
+        if (!has_doc(pool_doc, nt, Dl, lane)) ndocs--;
+      }
+    }
     uint32_t nres = 0;
     for (uint32_t i0 = 0; i0 < nt; i0 += 32) {
       uint32_t i = i0 + lane;
@@ -296,8 +362,10 @@ int launch_fdim(b200ann_handle *h, FilterParams &fp) {
 int launch_hnsw_search_filtered(b200ann_handle *h, const b200ann_index *ix, const float *q, size_t nq, size_t qstride,
                                 size_t k, size_t ef, const uint32_t *allow_bits, size_t ccap, bool big,
                                 const uint8_t *only, uint64_t *labels, float *dists, uint32_t *stats, uint8_t *inexact,
-                                size_t *ccap_used, float eps, size_t min_cand, uint32_t *counts, bool internal_ids) {
+                                size_t *ccap_used, float eps, size_t min_cand, uint32_t *counts, bool internal_ids,
+                                const uint32_t *doc, size_t efcoll, size_t docs_keep) {
   FilterParams fp = {};
+  fp.doc = doc; fp.efcoll = (uint32_t)efcoll; fp.docs_keep = (uint32_t)docs_keep;
   fp.eps = eps; fp.min_cand = (uint32_t)min_cand; fp.counts = counts;
   if (ix_u8(ix) && eps < INFINITY)  // int distances travel as bit patterns (dist.cuh): d > eps <=> bits(d) > bits(floor(eps))
   {
@@ -322,7 +390,7 @@ int launch_hnsw_search_filtered(b200ann_handle *h, const b200ann_index *ix, cons
   p.labels_out = labels; p.dists = dists; p.stats = stats;
   fp.allow = allow_bits; fp.inexact = inexact; fp.only = only;
   fp.vwords = round_up((uint32_t)((ix->n + 31) / 32), 4);
-  const size_t fixed = smem_words(p.pool_cap, p.cand_cap, 0);
+  const size_t fixed = smem_words(p.pool_cap, p.cand_cap, 0) + (doc ? p.pool_cap : 0u);
   // warps per block: FW, fewer when one warp's result list is large (an epsilon search with max_num_candidates in the
   // thousands), so that the list plus a candidate heap of >= 512 entries still fits the block's 227 KB
   fp.wpb = FW;

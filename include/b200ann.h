@@ -258,6 +258,24 @@ int b200ann_hnsw_search_epsilon(b200ann_handle_t h, b200ann_index_t ix, const fl
                                 uint64_t *labels /*[h|d] [nq,max]*/, float *dists /*[h|d] [nq,max]*/,
                                 uint32_t *counts /*[h|d] [nq]*/, uint32_t *stats /*[h|d] or NULL*/);
 
+/* replaces hnswlib::HierarchicalNSW::searchStopConditionClosest(query, MultiVectorSearchStopCondition(space,
+ * num_docs_to_search, ef_collection), isIdAllowed) for a batch of queries over a multi-vector space
+ * (stop_condition.h:9-215: every element carries a document id behind its vector, several elements per document;
+ * hnswalg.h:1327-1378, :309-440). doc_ids [n] = the document id of every element (internal id order; what
+ * BaseMultiVectorSpace::get_doc_id reads from the row). The walk bounds its result set by the number of DISTINCT
+ * documents in it (ef_collection, raised to num_docs_to_search like the reference) instead of by its size: a
+ * candidate is considered while fewer documents are held or it is closer than the farthest result; the farthest
+ * results are dropped while more than ef_collection documents are held; afterwards the farthest results go until
+ * num_docs_to_search documents are left (filter_results). Rows of max_results slots, ascending by distance,
+ * counts[q] valid; a query whose result list would need more slots -> B200ANN_ERR_CAPACITY (raise max_results; at
+ * most about 28000). allow / internal_ids as in b200ann_hnsw_search_epsilon. */
+int b200ann_hnsw_search_multivector(b200ann_handle_t h, b200ann_index_t ix, const float *q /*[h|d]*/, size_t nq,
+                                    size_t qstride, const uint32_t *doc_ids /*[h|d] [n]*/, size_t num_docs_to_search,
+                                    size_t ef_collection, size_t max_results, const uint32_t *allow /*[h|d] or NULL*/,
+                                    int internal_ids, uint64_t *labels /*[h|d] [nq,max_results]*/,
+                                    float *dists /*[h|d] [nq,max_results]*/, uint32_t *counts /*[h|d] [nq]*/,
+                                    uint32_t *stats /*[h|d] or NULL*/);
+
 /* replaces hnsw_nsg::IndexNSG::SearchFromEnterpoint (hnsw_nsg/src/index_nsg.cpp:703-782) for a batch:
  * like b200ann_nsg_search, but query i starts from entry[i] instead of the navigating node. The
  * reference's seed rules are kept: the entry point itself is marked visited and never

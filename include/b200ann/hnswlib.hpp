@@ -13,6 +13,7 @@
 //   has fewer than k results, bindings.cpp:646-648)
 #ifndef B200ANN_HNSWLIB_HPP
 #define B200ANN_HNSWLIB_HPP
+#include <algorithm>
 #include <atomic>
 #include <cmath>
 #include <cstdint>
@@ -164,12 +165,87 @@ class L2SpaceI : public SpaceInterface<int> {
   void *get_dist_func_param() override { return &dim_; }
 };
 
+// stop_condition.h:9-122: spaces whose elements carry a document id behind the vector (several vectors per document).
+// get_data_size() = dim * 4 + sizeof(DOCIDTYPE); the distance reads the vector only. (The reference's
+// MultiVectorInnerProductSpace never sets its dim_, :85-122; this one does.)
+template <typename DOCIDTYPE>
+class BaseMultiVectorSpace : public SpaceInterface<float> {
+ public:
+  virtual DOCIDTYPE get_doc_id(const void *datapoint) = 0;
+  virtual void set_doc_id(void *datapoint, DOCIDTYPE doc_id) = 0;
+  virtual int b200ann_metric() const = 0;
+};
+namespace detail {
+inline float mv_unused_dist(const void *, const void *, const void *) {
+  throw std::runtime_error("b200ann: distances are evaluated on the GPU; the host DISTFUNC of this space is not callable");
+}
+}  // namespace detail
+template <typename DOCIDTYPE, int METRIC>
+class MultiVectorSpaceT : public BaseMultiVectorSpace<DOCIDTYPE> {
+  size_t data_size_, vector_size_, dim_;
+
+ public:
+  explicit MultiVectorSpaceT(size_t dim) : data_size_(dim * sizeof(float) + sizeof(DOCIDTYPE)), vector_size_(dim * sizeof(float)), dim_(dim) {
+    static_assert(sizeof(DOCIDTYPE) == 4, "b200ann: document ids are 32-bit (rows stay 4-byte aligned)");
+  }
+  size_t get_data_size() override { return data_size_; }
+  DISTFUNC<float> get_dist_func() override { return detail::mv_unused_dist; }
+  void *get_dist_func_param() override { return &dim_; }
+  DOCIDTYPE get_doc_id(const void *datapoint) override { DOCIDTYPE v; std::memcpy(&v, (const char *)datapoint + vector_size_, sizeof v); return v; }
+  void set_doc_id(void *datapoint, DOCIDTYPE doc_id) override { std::memcpy((char *)datapoint + vector_size_, &doc_id, sizeof doc_id); }
+  int b200ann_metric() const override { return METRIC; }
+};
+template <typename DOCIDTYPE> using MultiVectorL2Space = MultiVectorSpaceT<DOCIDTYPE, B200ANN_L2>;
+template <typename DOCIDTYPE> using MultiVectorInnerProductSpace = MultiVectorSpaceT<DOCIDTYPE, B200ANN_IP>;
+
+// stop_condition.h:146-215, same constructor; the walk itself runs on the GPU (b200ann_hnsw_search_multivector), which
+// reads num_docs_to_search() / ef_collection() and the document ids of the index's rows. The virtual hooks count
+// documents like the reference's for a host-side caller.
+template <typename DOCIDTYPE, typename dist_t>
+class MultiVectorSearchStopCondition : public BaseSearchStopCondition<dist_t> {
+  size_t curr_num_docs_, num_docs_to_search_, ef_collection_;
+  std::unordered_map<DOCIDTYPE, size_t> doc_counter_;
+  std::priority_queue<std::pair<dist_t, DOCIDTYPE>> search_results_;
+  BaseMultiVectorSpace<DOCIDTYPE> &space_;
+
+ public:
+  MultiVectorSearchStopCondition(BaseMultiVectorSpace<DOCIDTYPE> &space, size_t num_docs_to_search, size_t ef_collection = 10)
+      : curr_num_docs_(0), num_docs_to_search_(num_docs_to_search), ef_collection_(std::max(ef_collection, num_docs_to_search)), space_(space) {}
+  size_t num_docs_to_search() const { return num_docs_to_search_; }
+  size_t ef_collection() const { return ef_collection_; }
+  void add_point_to_result(labeltype, const void *datapoint, dist_t dist) override {
+    DOCIDTYPE doc_id = space_.get_doc_id(datapoint);
+    if (doc_counter_[doc_id] == 0) curr_num_docs_ += 1;
+    search_results_.emplace(dist, doc_id);
+    doc_counter_[doc_id] += 1;
+  }
+  void remove_point_from_result(labeltype, const void *datapoint, dist_t) override {
+    DOCIDTYPE doc_id = space_.get_doc_id(datapoint);
+    doc_counter_[doc_id] -= 1;
+    if (doc_counter_[doc_id] == 0) curr_num_docs_ -= 1;
+    search_results_.pop();
+  }
+  bool should_stop_search(dist_t candidate_dist, dist_t lowerBound) override { return candidate_dist > lowerBound && curr_num_docs_ == ef_collection_; }
+  bool should_consider_candidate(dist_t candidate_dist, dist_t lowerBound) override { return curr_num_docs_ < ef_collection_ || lowerBound > candidate_dist; }
+  bool should_remove_extra() override { return curr_num_docs_ > ef_collection_; }
+  void filter_results(std::vector<std::pair<dist_t, labeltype>> &candidates) override {
+    while (curr_num_docs_ > num_docs_to_search_) {
+      DOCIDTYPE doc_id = search_results_.top().second;
+      doc_counter_[doc_id] -= 1;
+      if (doc_counter_[doc_id] == 0) curr_num_docs_ -= 1;
+      search_results_.pop();
+      candidates.pop_back();
+    }
+  }
+};
+
 namespace detail {
 // metric + dim of a Space; anything but the two known spaces is rejected
 inline void space_info(SpaceInterface<float> *s, int &metric, size_t &dim) {
   if (dynamic_cast<L2Space *>(s)) metric = B200ANN_L2;
   else if (dynamic_cast<InnerProductSpace *>(s)) metric = B200ANN_IP;
-  else throw std::runtime_error("b200ann: only L2Space and InnerProductSpace run on the GPU (a device kernel cannot call a host DISTFUNC)");
+  else if (auto *mv = dynamic_cast<BaseMultiVectorSpace<unsigned int> *>(s)) metric = mv->b200ann_metric();
+  else throw std::runtime_error("b200ann: only L2Space, InnerProductSpace and the multi-vector spaces run on the GPU (a device kernel cannot call a host DISTFUNC)");
   dim = *(size_t *)s->get_dist_func_param();
 }
 // HierarchicalNSW<int>: L2SpaceI (unsigned-byte rows, int squared L2) -> a B200ANN_L2_U8 index
@@ -464,7 +540,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
   HierarchicalNSW(SpaceInterface<dist_t> *s, size_t max_elements, size_t M = 16, size_t ef_construction = 200,
                   size_t random_seed = 100, bool allow_replace_deleted = false, int device = 0)
       : gpu_(device), allow_replace_deleted_(allow_replace_deleted) {
-    detail::space_info(s, metric_, dim_); set_geometry();
+    detail::space_info(s, metric_, dim_); set_geometry(s->get_data_size());
     max_elements_ = max_elements;
     M_ = M <= 10000 ? M : 10000;                       // :98-104
     maxM_ = M_; maxM0_ = M_ * 2;
@@ -476,7 +552,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
   HierarchicalNSW(SpaceInterface<dist_t> *s, const std::string &location, bool = false, size_t max_elements = 0,
                   bool allow_replace_deleted = false, int device = 0)
       : gpu_(device), allow_replace_deleted_(allow_replace_deleted) {
-    detail::space_info(s, metric_, dim_); set_geometry();
+    detail::space_info(s, metric_, dim_); set_geometry(s->get_data_size());
     loadIndex(location, s, max_elements);
   }
   ~HierarchicalNSW() { if (ix_) b200ann_index_destroy(ix_); }
@@ -487,7 +563,7 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
   void loadIndex(const std::string &location, SpaceInterface<dist_t> *s, size_t max_elements_i = 0) {
     std::ifstream in(location, std::ios::binary);
     if (!in.is_open()) throw std::runtime_error("Cannot open file");
-    detail::space_info(s, metric_, dim_); set_geometry();
+    detail::space_info(s, metric_, dim_); set_geometry(s->get_data_size());
     size_t offsetLevel0, size_data_per_element, label_offset, offsetData;
     rd(in, offsetLevel0); rd(in, max_elements_); rd(in, cur_element_count); rd(in, size_data_per_element);
     rd(in, label_offset); rd(in, offsetData); rd(in, maxlevel_); rd(in, enterpoint_node_); rd(in, maxM_); rd(in, maxM0_);
@@ -735,8 +811,10 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
                                                                        BaseFilterFunctor *isIdAllowed = nullptr) const {
     std::vector<std::pair<dist_t, labeltype>> result;
     if (cur_element_count == 0) return result;
+    if (auto *mv = dynamic_cast<MultiVectorSearchStopCondition<unsigned int, dist_t> *>(&stop_condition))
+      return search_multivector(query_data, mv->num_docs_to_search(), mv->ef_collection(), isIdAllowed);
     auto *eps = dynamic_cast<EpsilonSearchStopCondition<dist_t> *>(&stop_condition);
-    if (!eps) throw std::runtime_error("searchStopConditionClosest: only EpsilonSearchStopCondition runs on the GPU");
+    if (!eps) throw std::runtime_error("searchStopConditionClosest: EpsilonSearchStopCondition and MultiVectorSearchStopCondition<unsigned int> run on the GPU");
     const size_t mx = eps->max_num_candidates();
     if (mx == 0) return result;
     std::vector<labeltype> ids(mx);
@@ -747,6 +825,35 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
     result.resize(cnt);
     for (unsigned i = 0; i < cnt; i++) result[i] = std::make_pair(d[i], ids[i]);
     return result;
+  }
+  // MultiVectorSearchStopCondition (stop_condition.h:146-215) for one query: the document ids are read from the rows
+  // (behind the vector, where set_doc_id put them); the result list grows until it fits (a document may own many rows)
+  std::vector<std::pair<dist_t, labeltype>> search_multivector(const void *query_data, size_t num_docs, size_t ef_collection,
+                                                               BaseFilterFunctor *isIdAllowed) const {
+    std::vector<std::pair<dist_t, labeltype>> result;
+    std::unique_lock<std::mutex> lock(mu_);
+    build_locked(nullptr);
+    if (!ix_) return result;
+    if (data_size_ != dim_ * sizeof(float) + 4) throw std::runtime_error("MultiVectorSearchStopCondition needs an index over a multi-vector space");
+    const size_t n = cur_element_count;
+    std::vector<uint32_t> doc(n), allow;
+    for (size_t i = 0; i < n; i++) std::memcpy(&doc[i], (const char *)&vec_[i * rw_] + dim_ * sizeof(float), 4);
+    const bool filtered = num_deleted_ || isIdAllowed;
+    if (filtered) allow = allow_bitmap(isIdAllowed);
+    size_t mx = std::min<size_t>(n, std::max<size_t>(256, 8 * ef_collection));
+    for (;;) {
+      std::vector<uint64_t> lab(mx);
+      std::vector<dist_t> d(mx);
+      uint32_t cnt = 0, st[2] = {0, 0};
+      int rc = b200ann_hnsw_search_multivector(gpu_.h, ix_, (const float *)query_data, 1, dim_, doc.data(), num_docs, ef_collection, mx,
+                                               filtered ? allow.data() : nullptr, 1, lab.data(), (float *)d.data(), &cnt, st);
+      if (rc == B200ANN_ERR_CAPACITY && mx < n) { mx = std::min(n, mx * 4); continue; }
+      detail::check(gpu_.h, rc, "HierarchicalNSW::searchStopConditionClosest (multi-vector)");
+      count_metrics(std::vector<uint32_t>(st, st + 2));
+      result.resize(cnt);
+      for (uint32_t i = 0; i < cnt; i++) result[i] = std::make_pair(d[i], (labeltype)lab[i]);
+      return result;
+    }
   }
   // batched form: ids / dists [nq, max_num_candidates] ascending, counts[q] valid entries per row, the rest ~0 / +inf
   void searchEpsilonBatch(const void *queries, size_t nq, float epsilon, size_t min_num_candidates, size_t max_num_candidates,
@@ -919,15 +1026,18 @@ class HierarchicalNSW : public AlgorithmInterface<dist_t> {
   size_t dim_ = 0;
   size_t data_size_ = 0;  // bytes per element: dim floats, or dim unsigned bytes for HierarchicalNSW<int> / L2SpaceI
   size_t rw_ = 0;         // floats of vec_ one row occupies (byte rows are padded to 4 bytes)
-  void set_geometry() {
+  // space_data_size = SpaceInterface::get_data_size(): dim floats, dim bytes, or (multi-vector spaces) dim floats + a
+  // 32-bit document id that travels with the row (file format, getDataByLabel) and is skipped by the distance
+  void set_geometry(size_t space_data_size) {
     const bool u8 = metric_ == B200ANN_L2_U8;
-    data_size_ = u8 ? dim_ : dim_ * sizeof(float);
-    rw_ = u8 ? (dim_ + 3) / 4 : dim_;
+    data_size_ = u8 ? dim_ : space_data_size;
+    if (!u8 && (data_size_ < dim_ * sizeof(float) || data_size_ % 4 != 0)) throw std::runtime_error("b200ann: unsupported element size of the space");
+    rw_ = (data_size_ + 3) / 4;
   }
-  size_t row_stride() const { return metric_ == B200ANN_L2_U8 ? rw_ * 4 : dim_; }  // elements between rows of vec_
+  size_t row_stride() const { return metric_ == B200ANN_L2_U8 ? rw_ * 4 : rw_; }  // elements between rows of vec_
   int create_index(size_t n, b200ann_index_t *out) const {
     if (metric_ == B200ANN_L2_U8) return b200ann_index_create_u8(gpu_.h, (const uint8_t *)vec_.data(), n, dim_, rw_ * 4, out);
-    return b200ann_index_create(gpu_.h, vec_.data(), n, dim_, dim_, metric_, out);
+    return b200ann_index_create(gpu_.h, vec_.data(), n, dim_, rw_, metric_, out);
   }
   size_t seed_ = 100;
   size_t gen_ = 0;

@@ -949,6 +949,112 @@ EXPORT int orc_hnsw_search_epsilon(const float *data, size_t n, size_t dim, size
   return 0;
 }
 
+/* HierarchicalNSW::searchStopConditionClosest(query, MultiVectorSearchStopCondition(space, num_docs, ef_collection),
+ * isIdAllowed) batched (hnswalg.h:1327-1378 -> searchBaseLayerST<false> :309-440; stop_condition.h:146-215). doc [n] =
+ * document id of every element (what BaseMultiVectorSpace::get_doc_id reads from the row). The result set is bounded
+ * by its number of distinct documents: should_consider_candidate (:191-194), add / remove_point (:167-183),
+ * should_remove_extra (:196-199), should_stop_search (:186-189); filter_results drops the farthest results until
+ * num_docs documents are left (:201-215). ef_collection = max(ef_collection, num_docs) (:164). Output rows of
+ * max_results slots (ids, or labels when labels != NULL), counts [nq]; returns -2 if a row needs more slots. */
+EXPORT int orc_hnsw_search_multivector(const float *data, size_t n, size_t dim, size_t stride, const uint32_t *links0,
+                                       unsigned maxM0, const int32_t *levels, const uint32_t *upper_ptr,
+                                       const uint32_t *upper_links, unsigned maxM, const uint64_t *labels, uint32_t ep,
+                                       int maxlevel, const uint8_t *allow, const uint32_t *doc, const float *q, size_t nq,
+                                       size_t qstride, size_t num_docs, size_t ef_collection, size_t max_results, int mode,
+                                       uint64_t *out_labels, float *out_dists, uint32_t *counts, uint64_t *stats) {
+  orc_hnsw ix = {data, n, dim, stride, links0, maxM0, levels, upper_ptr, upper_links, maxM, ep, maxlevel, mode};
+  if (stats) memset(stats, 0, sizeof(uint64_t) * 2 * nq);
+  if (num_docs == 0 || max_results == 0) return -1;
+  if (ef_collection < num_docs) ef_collection = num_docs;
+  uint32_t maxdoc = 0;
+  for (size_t i = 0; i < n; i++) if (doc[i] > maxdoc) maxdoc = doc[i];
+  uint8_t *all = NULL;
+  if (!allow) { all = (uint8_t *)malloc(n ? n : 1); memset(all, 1, n); allow = all; }
+  int rc = 0;
+#pragma omp parallel
+  {
+    uint8_t *visited = (uint8_t *)malloc(n ? n : 1);
+    orc_pair *top = (orc_pair *)malloc(sizeof(orc_pair) * (n + 2));
+    orc_pair *cand = (orc_pair *)malloc(sizeof(orc_pair) * (n + 2));
+    uint32_t *dc = (uint32_t *)calloc((size_t)maxdoc + 1, 4);
+#pragma omp for schedule(dynamic, 8)
+    for (long qi = 0; qi < (long)nq; qi++) {
+      const float *qv = q + (size_t)qi * qstride;
+      size_t nt = 0, nc = 0, ndocs = 0;
+      uint64_t *st = stats ? stats + 2 * qi : NULL;
+      if (n) {
+        memset(visited, 0, n);
+        float cdv;
+        uint32_t cur = hnsw_descend(&ix, qv, &cdv, st);
+        if (st && allow[cur]) st[0]--;
+        float lowerBound;
+        if (allow[cur]) {
+          float dist = orc_dist(mode, qv, data + stride * (size_t)cur, dim);
+          if (st) st[0]++;
+          lowerBound = dist;
+          orc_pair e = {dist, cur};
+          hpush(top, &nt, e, +1);
+          if (dc[doc[cur]]++ == 0) ndocs++;
+          hpush(cand, &nc, e, -1);
+        } else {
+          lowerBound = FLT_MAX;
+          orc_pair e = {lowerBound, cur};
+          hpush(cand, &nc, e, -1);
+        }
+        visited[cur] = 1;
+        while (nc) {
+          orc_pair c0 = cand[0];
+          if (c0.d > lowerBound && ndocs == ef_collection) break;
+          hpop(cand, &nc, -1);
+          const uint32_t *row = links0 + (size_t)c0.id * maxM0;
+          if (st) st[1]++;
+          for (unsigned j = 0; j < maxM0 && row[j] != ORC_INVALID; j++) {
+            uint32_t cid = row[j];
+            if (visited[cid]) continue;
+            visited[cid] = 1;
+            float d = orc_dist(mode, qv, data + stride * (size_t)cid, dim);
+            if (st) st[0]++;
+            if (ndocs < ef_collection || lowerBound > d) {
+              orc_pair c = {d, cid};
+              hpush(cand, &nc, c, -1);
+              if (allow[cid]) {
+                hpush(top, &nt, c, +1);
+                if (dc[doc[cid]]++ == 0) ndocs++;
+              }
+              while (ndocs > ef_collection) {
+                uint32_t id = top[0].id;
+                hpop(top, &nt, +1);
+                if (--dc[doc[id]] == 0) ndocs--;
+              }
+              if (nt) lowerBound = top[0].d;
+            }
+          }
+        }
+        qsort(top, nt, sizeof(orc_pair), pair_cmp);
+        while (ndocs > num_docs) {                  /* filter_results */
+          uint32_t id = top[nt - 1].id;
+          nt--;
+          if (--dc[doc[id]] == 0) ndocs--;
+        }
+        for (size_t t = 0; t < nt; t++) dc[doc[top[t].id]] = 0;   /* the counters go back to zero for the next query */
+      }
+      if (nt > max_results) {
+#pragma omp atomic write
+        rc = -2;
+        nt = max_results;
+      }
+      counts[qi] = (uint32_t)nt;
+      for (size_t j = 0; j < max_results; j++) {
+        out_labels[(size_t)qi * max_results + j] = j < nt ? (labels ? labels[top[j].id] : top[j].id) : ~(uint64_t)0;
+        out_dists[(size_t)qi * max_results + j] = j < nt ? top[j].d : INFINITY;
+      }
+    }
+    free(visited); free(top); free(cand); free(dc);
+  }
+  free(all);
+  return rc;
+}
+
 /* ------------------------------------------------------------------ hybrid HNSW_NSG search */
 /* IndexNSG::SearchFromEnterpoint (hnsw_nsg/src/index_nsg.cpp:703-782), statement for statement,
  * quirks included:

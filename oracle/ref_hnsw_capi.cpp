@@ -224,6 +224,62 @@ int ref_hnsw_links(void *p, size_t id, int level, unsigned *out) {
 }
 }
 
+// ---- multi-vector spaces + MultiVectorSearchStopCondition (stop_condition.h:9-215): rows = [dim floats][u32 doc id]
+struct RefHnswMV {
+  BaseMultiVectorSpace<unsigned> *space;
+  HierarchicalNSW<float> *index;
+  size_t dim;
+};
+extern "C" {
+void *ref_hnswmv_new(int metric, size_t dim, size_t max_elements, size_t M, size_t efc, size_t seed) {
+  RefHnswMV *h = new RefHnswMV;
+  h->dim = dim;
+  if (metric == 1) h->space = new MultiVectorInnerProductSpace<unsigned>(dim);
+  else h->space = new MultiVectorL2Space<unsigned>(dim);
+  h->index = new HierarchicalNSW<float>(h->space, max_elements, M, efc, seed);
+  return h;
+}
+void ref_hnswmv_free(void *p) {
+  RefHnswMV *h = (RefHnswMV *)p;
+  delete h->index; delete h->space; delete h;
+}
+// data [n, dim] floats + doc [n]: the rows the reference stores are assembled here (vector, then the document id)
+int ref_hnswmv_add(void *p, const float *data, const unsigned *doc, size_t n, size_t label0) {
+  RefHnswMV *h = (RefHnswMV *)p;
+  std::vector<char> row(h->space->get_data_size());
+  for (size_t i = 0; i < n; i++) {
+    memcpy(row.data(), data + i * h->dim, h->dim * sizeof(float));
+    h->space->set_doc_id(row.data(), doc[i]);
+    h->index->addPoint(row.data(), label0 + i);
+  }
+  return 0;
+}
+int ref_hnswmv_search(void *p, const float *q, size_t nq, size_t num_docs, size_t ef_collection, size_t max_results,
+                      const unsigned char *allow, unsigned long long *ids, float *dists, unsigned *counts, int threads) {
+  RefHnswMV *h = (RefHnswMV *)p;
+  if (threads <= 0) threads = omp_get_max_threads();
+  int rc = 0;
+#pragma omp parallel for num_threads(threads) schedule(dynamic, 16)
+  for (long i = 0; i < (long)nq; i++) {
+    BitmapFilter f(allow);
+    MultiVectorSearchStopCondition<unsigned, float> stop(*h->space, num_docs, ef_collection);
+    auto r = h->index->searchStopConditionClosest(q + i * h->dim, stop, allow ? &f : nullptr);
+    size_t m = r.size();
+    if (m > max_results) { rc = -2; m = max_results; }
+    counts[i] = (unsigned)m;
+    for (size_t j = 0; j < max_results; j++) {
+      ids[i * max_results + j] = j < m ? (unsigned long long)r[j].second : (unsigned long long)-1;
+      dists[i * max_results + j] = j < m ? r[j].first : -1.f;
+    }
+  }
+  return rc;
+}
+int ref_hnswmv_save(void *p, const char *path) {
+  try { ((RefHnswMV *)p)->index->saveIndex(path); } catch (std::exception &e) { return -1; }
+  return 0;
+}
+}
+
 // ---- HierarchicalNSW<int> over L2SpaceI (space_l2.h:255-323): unsigned-byte rows, int distances. Same drivers as
 // the float wrappers above, on the UNMODIFIED reference templates instantiated with dist_t = int.
 struct RefHnswI {

@@ -92,6 +92,10 @@ def oracle():
                                                 u64p, f32p, u32p, C.c_void_p]
         lib.orc_hnsw_update.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_uint, C.c_uint, C.c_int, C.c_int, i32p,
                                         u32p, u32p, u32p, C.c_size_t, C.c_uint32, C.c_int, u32p, f32p, C.c_size_t, C.c_void_p]
+        lib.orc_hnsw_search_multivector.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, u32p, C.c_uint, i32p, u32p, u32p,
+                                                    C.c_uint, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, u32p, f32p,
+                                                    C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int,
+                                                    u64p, f32p, u32p, C.c_void_p]
         lib.orc_hnsw_levels.argtypes = [C.c_size_t, C.c_uint, C.c_uint32, i32p]
         lib.orc_hnsw_batch_end.restype = C.c_size_t
         lib.orc_hnsw_batch_end.argtypes = [C.c_size_t, C.c_size_t, i32p, C.c_int, C.c_uint, C.c_uint]
@@ -207,6 +211,28 @@ def orc_hnsw_search_epsilon(base, h, q, eps, min_cand, max_cand, mode, allow=Non
                                           h["ep"], h["maxlevel"], _vp(a), q, nq, q.shape[1], eps, min_cand, max_cand,
                                           mode, lab, d, cnt, _vp(st))
     assert rc == 0
+    return (lab, d, cnt, st) if want_stats else (lab, d, cnt)
+
+
+def orc_hnsw_search_multivector(base, h, doc, q, num_docs, ef_collection, max_results, mode, allow=None, internal_ids=True,
+                                want_stats=False):
+    """searchStopConditionClosest with MultiVectorSearchStopCondition; doc [n] u32 by internal id.
+    Returns (ids or labels [nq,max_results], d, counts[, stats])."""
+    n, dim = base.shape
+    nq = q.shape[0]
+    lab = np.empty((nq, max_results), np.uint64)
+    d = np.empty((nq, max_results), np.float32)
+    cnt = np.zeros(nq, np.uint32)
+    st = np.zeros((nq, 2), np.uint64) if want_stats else None
+    up = h["upper_links"]
+    if up.size == 0:
+        up = np.full((1, max(1, h["maxM"])), INVALID, np.uint32)
+    a = None if allow is None else np.ascontiguousarray(allow, np.uint8)
+    rc = oracle().orc_hnsw_search_multivector(base, n, dim, dim, h["links0"], h["links0"].shape[1], h["levels"],
+                                              h["upper_ptr"], up, up.shape[1], None if internal_ids else _vp(h["labels"]),
+                                              h["ep"], h["maxlevel"], _vp(a), np.ascontiguousarray(doc, np.uint32), q, nq,
+                                              q.shape[1], num_docs, ef_collection, max_results, mode, lab, d, cnt, _vp(st))
+    assert rc == 0, rc
     return (lab, d, cnt, st) if want_stats else (lab, d, cnt)
 
 
@@ -554,6 +580,13 @@ def reflib(name):
         lib.ref_hnsw_mark_deleted.argtypes = [C.c_void_p, C.c_size_t, C.c_int]
         lib.ref_hnsw_search_epsilon.argtypes = [C.c_void_p, f32p, C.c_size_t, C.c_float, C.c_size_t, C.c_size_t,
                                                 C.c_void_p, u64p, f32p, u32p, C.c_int]
+        lib.ref_hnswmv_new.restype = C.c_void_p
+        lib.ref_hnswmv_new.argtypes = [C.c_int] + [C.c_size_t] * 5
+        lib.ref_hnswmv_free.argtypes = [C.c_void_p]
+        lib.ref_hnswmv_add.argtypes = [C.c_void_p, f32p, u32p, C.c_size_t, C.c_size_t]
+        lib.ref_hnswmv_search.argtypes = [C.c_void_p, f32p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, C.c_void_p, u64p,
+                                          f32p, u32p, C.c_int]
+        lib.ref_hnswmv_save.argtypes = [C.c_void_p, C.c_char_p]
         lib.ref_hnswi_new.restype = C.c_void_p
         lib.ref_hnswi_new.argtypes = [C.c_size_t] * 5
         lib.ref_hnswi_load.restype = C.c_void_p
@@ -625,6 +658,38 @@ def ref_bf_knn_u8(base, q, k, lib="hnsw", threads=0):
     d = np.empty((q.shape[0], k), np.int32)
     reflib(lib).ref_bf_knn_u8(base, n, dim, q, q.shape[0], k, lab, d, threads)
     return lab, d
+
+
+class RefHnswMV:
+    """the unmodified HierarchicalNSW<float> over MultiVectorL2Space / MultiVectorInnerProductSpace<unsigned>
+    (oracle/ref_hnsw_capi.cpp ref_hnswmv_*): rows = vector + document id"""
+
+    def __init__(self, metric, dim, max_elements, M=16, efc=200, seed=100):
+        self.lib = reflib("hnsw")
+        self.dim = dim
+        self.h = self.lib.ref_hnswmv_new(metric, dim, max_elements, M, efc, seed)
+        assert self.h
+
+    def add(self, data, doc, label0=0):
+        self.lib.ref_hnswmv_add(self.h, np.ascontiguousarray(data, np.float32), np.ascontiguousarray(doc, np.uint32),
+                                data.shape[0], label0)
+
+    def search(self, q, num_docs, ef_collection, max_results, allow_by_label=None, threads=0):
+        ids = np.empty((q.shape[0], max_results), np.uint64)
+        d = np.empty((q.shape[0], max_results), np.float32)
+        cnt = np.zeros(q.shape[0], np.uint32)
+        a = None if allow_by_label is None else np.ascontiguousarray(allow_by_label, np.uint8)
+        rc = self.lib.ref_hnswmv_search(self.h, q, q.shape[0], num_docs, ef_collection, max_results, _vp(a), ids, d, cnt, threads)
+        assert rc == 0
+        return ids, d, cnt
+
+    def save(self, path):
+        assert self.lib.ref_hnswmv_save(self.h, path.encode()) == 0
+
+    def close(self):
+        if self.h:
+            self.lib.ref_hnswmv_free(self.h)
+            self.h = None
 
 
 class RefHnswI:

@@ -22,7 +22,7 @@ def _build(name, tmp):
 
 
 @pytest.mark.parametrize("name", ["test_efanna_shim", "test_hnswlib_shim", "test_hybrid_shim", "test_l2spacei_shim", "test_replace_deleted",
-                                  "test_hybrid_order", "test_epsilon_search", "test_hnswlib_int", "test_updates"])
+                                  "test_hybrid_order", "test_epsilon_search", "test_hnswlib_int", "test_updates", "test_multivector_search"])
 def test_shims_compile_and_fail_loudly_without_gpu(tmp_path, name):
     exe = _build(name, tmp_path)
     try:
@@ -116,6 +116,15 @@ def test_updates_driver(tmp_path):
     p = subprocess.run([exe, str(tmp_path)], capture_output=True, text=True)
     print(p.stdout, p.stderr)
     assert p.returncode == 0 and "updates ok" in p.stdout
+
+
+@pytest.mark.gpu
+def test_multivector_search_driver(tmp_path):
+    """MultiVectorL2Space + MultiVectorSearchStopCondition, the flow of hnswlib/tests/cpp/multivector_search_test.cpp"""
+    exe = _build("test_multivector_search", tmp_path)
+    p = subprocess.run([exe], capture_output=True, text=True)
+    print(p.stdout, p.stderr)
+    assert p.returncode == 0 and "multivector search ok" in p.stdout
 
 
 @pytest.mark.gpu

@@ -165,3 +165,30 @@ def test_epsilon_search_labels_ip_and_errors(B, H):
     with pytest.raises(Exception, match="NaN"):
         ix.hnsw_search_epsilon(q, float("nan"), 0, 40)
     ix.close()
+
+
+@pytest.mark.parametrize("ndocs,efcoll,keep,nd", [(10, 15, 1.0, 500), (5, 5, 1.0, 500), (20, 40, 0.3, 500), (3, 1, 1.0, 50),
+                                                  (8, 30, 1.0, 20000)])
+def test_multivector_search_vs_oracle(B, case, ndocs, efcoll, keep, nd):
+    """b200ann_hnsw_search_multivector == the oracle's MultiVectorSearchStopCondition restatement (pinned bit for bit to
+    the compiled reference in test_oracle_pinning.py): ids, distances, counts, work counters; every row covers exactly
+    num_docs distinct documents (the reference test's own invariant, multivector_search_test.cpp:86)"""
+    base, ix, G, q = case
+    n = len(base)
+    rng = np.random.default_rng(ndocs * 100 + efcoll)
+    doc = rng.integers(0, nd, n).astype(np.uint32)
+    allow = None if keep == 1.0 else (rng.random(n) < keep)
+    mx = 4096
+    ol, od, oc, os_ = R.orc_hnsw_search_multivector(base, G, doc, q, ndocs, efcoll, mx, R.L2_GPU, allow=allow, want_stats=True)
+    lab, d, cnt, st = ix.hnsw_search_multivector(q, doc, ndocs, efcoll, mx, allow=allow, internal_ids=True, want_stats=True)
+    assert (cnt == oc).all() and (lab == ol).all() and np.array_equal(d, od)
+    assert (st.astype(np.uint64) == os_).all()
+    for i in range(len(q)):
+        got = lab[i, :cnt[i]].astype(np.int64)
+        assert len(set(doc[got].tolist())) == ndocs
+        if allow is not None:
+            assert allow[got].all()
+    # too few result slots: refused with the reason, never a silently short answer
+    if nd == 50:
+        with pytest.raises(Exception, match="max_results"):
+            ix.hnsw_search_multivector(q, doc, ndocs, efcoll, int(cnt.max()) - 1)

@@ -158,6 +158,38 @@ def test_hnsw_update_point_vs_reference(tmp_path, metric, mode):
     assert (lab[:, 0] == ids).mean() >= 0.97
 
 
+@needs_ref
+@pytest.mark.parametrize("metric,mode,ndocs,efcoll,keep", [(0, R.L2_SCALAR, 10, 15, 1.0), (0, R.L2_SCALAR, 5, 5, 1.0),
+                                                           (0, R.L2_SCALAR, 20, 40, 0.5), (0, R.L2_SCALAR, 3, 1, 1.0)])
+def test_hnsw_multivector_search_vs_reference(tmp_path, metric, mode, ndocs, efcoll, keep):
+    """oracle multi-vector search == HierarchicalNSW::searchStopConditionClosest(q, MultiVectorSearchStopCondition(space,
+    num_docs, ef_collection), filter) over a MultiVector space of the unmodified reference: ids, distances, counts;
+    the reference's own invariant (multivector_search_test.cpp:86): exactly num_docs distinct documents come back.
+    L2 only: the reference's MultiVectorInnerProductSpace never sets dim_ (stop_condition.h:85-122), its distance
+    function reads an uninitialised dimension (it crashed here)."""
+    n, dim, nd = 3000, 16, 150
+    gen = R.data_uniform if metric == 0 else R.data_glove_like
+    base, q = gen(n, dim, 1), gen(100, dim, 2)
+    doc = np.random.default_rng(3).integers(0, nd, n).astype(np.uint32)
+    h = R.RefHnswMV(metric, dim, n, 16, 100)
+    h.add(base, doc)
+    p = str(tmp_path / "mv.bin")
+    h.save(p)
+    H = R.parse_hnsw(p)
+    assert (np.ascontiguousarray(H["vectors"][:, :dim]) == base).all()
+    assert (np.ascontiguousarray(H["vectors"][:, dim]).view(np.uint32) == doc).all()   # the document id sits behind the vector
+    allow = None if keep == 1.0 else (np.random.default_rng(4).random(n) < keep).astype(np.uint8)
+    ri, rd, rc = h.search(q, ndocs, efcoll, n, allow, threads=1)
+    oi, od, oc = R.orc_hnsw_search_multivector(base, H, doc, q, ndocs, efcoll, n, mode, allow=allow)
+    rd = np.where(ri == np.uint64(0xFFFFFFFFFFFFFFFF), np.float32(np.inf), rd)
+    assert (rc == oc).all() and (ri == oi).all() and (rd == od).all()
+    for i in range(len(q)):
+        got = oi[i, :oc[i]].astype(np.int64)
+        assert len(set(doc[got].tolist())) == ndocs
+        if allow is not None:
+            assert allow[got].all()
+
+
 @pytest.fixture(scope="module")
 def hnsw_u8_case(tmp_path_factory):
     rng = np.random.default_rng(5)

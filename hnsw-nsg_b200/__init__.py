@@ -55,6 +55,8 @@ _lib.b200ann_nndescent.argtypes = [_vp, _vp, _sz, _sz, _sz, _sz, _sz, C.c_uint32
 _lib.b200ann_nsg_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, C.c_uint32, _vp, _vp, _vp]
 _lib.b200ann_hnsw_search.argtypes = [_vp, _vp, _vp, _sz, _sz, _sz, _sz, _vp, _vp, _vp]
 _lib.b200ann_hnsw_search_multivector.argtypes = [_vp, _vp, _vp, _sz, _sz, _vp, _sz, _sz, _sz, _vp, C.c_int, _vp, _vp, _vp, _vp]
+_lib.b200ann_kdtree_graph.argtypes = [_vp, _vp, _sz, _sz, _sz, C.c_uint32, _vp, _vp, _vp]
+_lib.b200ann_nndescent_refine.argtypes = [_vp, _vp, _sz, _sz, _sz, _sz, _sz, C.c_uint32, _vp, _sz, _vp, _vp, _vp]
 _lib.b200ann_index_set_labels.argtypes = [_vp, _vp, _vp, _sz]
 _lib.b200ann_hnsw_update_batch.argtypes = [_vp, _vp, _vp, _vp, _sz, _sz, _vp]
 _lib.b200ann_index_create_u8.argtypes = [_vp, _vp, _sz, _sz, _sz, _vp]
@@ -96,6 +98,8 @@ EXPORTS = [
     "b200ann_index_create_u8",
     "b200ann_hnsw_update_batch",
     "b200ann_index_set_labels",
+    "b200ann_nndescent_refine",
+    "b200ann_kdtree_graph",
     "b200ann_hnsw_search_multivector",
     "b200ann_hnsw_search_epsilon",
     "b200ann_set_link_visited_bits", "b200ann_nsg_build", "b200ann_nsg_init_ep", "b200ann_nsg_link",
@@ -370,6 +374,28 @@ class Index:
                                                   _ptr(upper) if rows else None, _ptr(labels)))
         return dict(n=self.n, maxM=maxM, maxM0=maxM0, ep=ep, maxlevel=maxlevel, links0=links0, levels=levels,
                     upper_ptr=upper_ptr, upper_links=upper, labels=labels)
+
+    def kdtree_graph(self, K, n_trees, m_level, seed=0, want_dists=False):
+        """IndexKDtree::Build: initial kNN graph [n,K] from n_trees randomized KD-trees merged below depth m_level"""
+        knn = np.empty((self.n, K), np.uint32)
+        d = np.empty((self.n, K), np.float32) if want_dists else None
+        info = np.zeros(8, np.uint64)
+        self.h._check(_lib.b200ann_kdtree_graph(self.h._h, self._ix, K, n_trees, m_level, seed, _ptr(knn), _ptr(d), _ptr(info)))
+        inf = dict(zip(("dist_evals", "nodes", "leaves", "deepest", "levels"), (int(x) for x in info)))
+        return (knn, d, inf) if want_dists else (knn, inf)
+
+    def nndescent_refine(self, init_graph, K, L, it, S, R, seed=0, want_dists=False):
+        """IndexGraph::RefineGraph: NN-descent started from the rows of init_graph [n, init_k] (u32, INVALID padding)"""
+        g = np.ascontiguousarray(init_graph, np.uint32)
+        assert g.shape[0] == self.n
+        knn = np.empty((self.n, K), np.uint32)
+        d = np.empty((self.n, K), np.float32) if want_dists else None
+        info = np.zeros(8, np.uint64)
+        self.h._check(_lib.b200ann_nndescent_refine(self.h._h, self._ix, K, L, it, S, R, seed, _ptr(g), g.shape[1], _ptr(knn),
+                                                    _ptr(d), _ptr(info)))
+        keys = ("dist_evals", "offers", "inserts", "iterations", "join_us", "update_us")
+        inf = dict(zip(keys, (int(x) for x in info)))
+        return (knn, d, inf) if want_dists else (knn, inf)
 
     def nndescent(self, K, L, it, S, R, seed=0, want_dists=False, out=None):
         """IndexGraph::Build (NN-descent) on the GPU: returns knn [n,K] (+ dists) and the info dict.

@@ -636,6 +636,45 @@ int b200ann_nndescent(b200ann_handle_t h, b200ann_index_t ix, size_t K, size_t L
   return 0;
 }
 
+int b200ann_kdtree_graph(b200ann_handle_t h, b200ann_index_t ix, size_t K, size_t nTrees, size_t mLevel, uint32_t seed, uint32_t *knn,
+                         float *dists, uint64_t *info) {
+  FLOAT_ONLY(h, ix, "kdtree_graph");
+  if (!h || !ix) return B200ANN_ERR_ARG;
+  if (!knn) return set_err(h, B200ANN_ERR_ARG, "kdtree_graph: knn output is NULL");
+  CU_CHECK(h, cudaSetDevice(h->device));
+  OutArg<uint32_t> oi; OutArg<float> od;
+  CU_CHECK(h, oi.stage(knn, ix->n * K, h->stream));
+  CU_CHECK(h, od.stage(dists, ix->n * K, h->stream));
+  CallTimer t(h);
+  int rc = kdtree_launch(h, ix, K, nTrees, mLevel, seed, oi.d, od.d, info);
+  t.stop();
+  if (rc) return rc;
+  CU_CHECK(h, oi.finish(h->stream));
+  CU_CHECK(h, od.finish(h->stream));
+  CU_CHECK(h, t.sync());
+  return 0;
+}
+
+int b200ann_nndescent_refine(b200ann_handle_t h, b200ann_index_t ix, size_t K, size_t L, size_t iter, size_t S, size_t R,
+                             uint32_t seed, const uint32_t *init_graph, size_t init_k, uint32_t *knn, float *dists, uint64_t *info) {
+  FLOAT_ONLY(h, ix, "nndescent_refine");
+  if (!h || !ix) return B200ANN_ERR_ARG;
+  if (!knn || !init_graph || init_k == 0) return set_err(h, B200ANN_ERR_ARG, "nndescent_refine: need knn, init_graph, init_k > 0");
+  CU_CHECK(h, cudaSetDevice(h->device));
+  InArg<uint32_t> gin; OutArg<uint32_t> oi; OutArg<float> od;
+  CU_CHECK(h, gin.stage(init_graph, ix->n * init_k, h->stream));
+  CU_CHECK(h, oi.stage(knn, ix->n * K, h->stream));
+  CU_CHECK(h, od.stage(dists, ix->n * K, h->stream));
+  CallTimer t(h);
+  int rc = nndescent_launch(h, ix, K, L, iter, S, R, seed, oi.d, od.d, info, gin.d, init_k);
+  t.stop();
+  if (rc) return rc;
+  CU_CHECK(h, oi.finish(h->stream));
+  CU_CHECK(h, od.finish(h->stream));
+  CU_CHECK(h, t.sync());
+  return 0;
+}
+
 int b200ann_nsg_search(b200ann_handle_t h, b200ann_index_t ix, const float *q, size_t nq, size_t qstride, size_t K,
                        size_t L, uint32_t seed, uint32_t *ids, float *dists, uint32_t *stats) {
   FLOAT_ONLY(h, ix, "nsg_search");

@@ -208,7 +208,11 @@ int hnsw_insert_launch(b200ann_handle *h, b200ann_index *ix, const void *data, s
 
 // NN-descent (nndescent.cu); device pointers only
 int nndescent_launch(b200ann_handle *h, const b200ann_index *ix, size_t K, size_t L, size_t iter, size_t S, size_t R,
-                     uint32_t seed, uint32_t *knn, float *knn_d, uint64_t *info8);
+                     uint32_t seed, uint32_t *knn, float *knn_d, uint64_t *info8, const uint32_t *init_graph = nullptr,
+                     size_t init_k = 0);
+
+int kdtree_launch(b200ann_handle *h, const b200ann_index *ix, size_t K, size_t nTrees, size_t ml, uint32_t seed, uint32_t *knn,
+                  float *knn_d, uint64_t *info8);
 
 // NSG build phases (nsg_build.cu); device pointers only
 int nsg_centroid_launch(b200ann_handle *h, const b200ann_index *ix, float *center);

@@ -51,6 +51,8 @@ struct State {
   uint32_t *n_rnew, *n_rold;            // [n]
   uint32_t *lock_pool, *lock_rnew, *lock_rold;  // [n]
   const uint32_t *leaf_rank;            // [L+1]
+  const uint32_t *init_graph;           // [n, init_k] or NULL: RefineGraph (index_graph.cpp:203-262) - the pools start from these rows
+  uint32_t init_k;
   unsigned long long *stats;            // {distance evaluations, offers queued, inserts done, next node}
 };
 
@@ -87,23 +89,97 @@ __global__ void init_kernel(State s, uint32_t seed) {
   s.n_fold[i] = 0; s.n_rnew[i] = 0; s.n_rold[i] = 0;
   s.M[i] = s.S;
   s.lock_pool[i] = 0; s.lock_rnew[i] = 0; s.lock_rold[i] = 0;
-  gen_random(seed ^ SEED_POOL, i, tmp, s.S + 1, s.n);
   uint64_t *pool = s.pool + (size_t)i * s.L;
   uint32_t sz = 0;
-  for (uint32_t j = 0; j < s.S; ++j) {
-    uint32_t id = tmp[j];
-    if (id == i) continue;
-    float d = seq_l2(s.vec + (size_t)i * s.stride, s.vec + (size_t)id * s.stride, s.dim);
-    uint64_t key = ((uint64_t)__float_as_uint(d) << 32) | (id << 1) | 1u;
-    uint32_t p = sz;
-    while (p > 0 && pool[p - 1] > key) { pool[p] = pool[p - 1]; --p; }
-    pool[p] = key;
-    ++sz;
+  unsigned long long evals = 0;
+  if (sz == 0) {
+    gen_random(seed ^ SEED_POOL, i, tmp, s.S + 1, s.n);
+    for (uint32_t j = 0; j < s.S; ++j) {
+      uint32_t id = tmp[j];
+      if (id == i) continue;
+      float d = seq_l2(s.vec + (size_t)i * s.stride, s.vec + (size_t)id * s.stride, s.dim);
+      ++evals;
+      uint64_t key = ((uint64_t)__float_as_uint(d) << 32) | (id << 1) | 1u;
+      uint32_t p = sz;
+      while (p > 0 && pool[p - 1] > key) { pool[p] = pool[p - 1]; --p; }
+      pool[p] = key;
+      ++sz;
+    }
   }
   for (uint32_t j = sz; j < s.L; ++j) pool[j] = EMPTY;
   s.psize[i] = sz;
   s.worst[i] = (uint32_t)(pool[sz - 1] >> 32);
-  atomicAdd(s.stats + 0, (unsigned long long)sz);
+  atomicAdd(s.stats + 0, evals);
+}
+
+// RefineGraph's start (InitializeGraph_Refine, index_graph.cpp:203-232), one warp per node, run AFTER init_kernel: the
+// pool becomes the node's row of the initializer's graph - self, out-of-range ids and duplicates dropped, every entry
+// flagged new, the L smallest (distance, id) kept in ascending order. A row with no usable entry keeps the random start.
+constexpr int RF_WARPS = 4, RF_MAXK = 512;
+__global__ void __launch_bounds__(RF_WARPS * 32) init_refine_kernel(State s) {
+  __shared__ uint64_t keys_s[RF_WARPS][RF_MAXK];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t i = blockIdx.x * RF_WARPS + warp;
+  if (i >= s.n) return;
+  uint64_t *keys = keys_s[warp];
+  const uint32_t k = s.init_k;
+  uint32_t evals = 0;
+  for (uint32_t j0 = 0; j0 < k; j0 += 32) {
+    const uint32_t j = j0 + lane;
+    uint64_t key = EMPTY;
+    if (j < k) {
+      const uint32_t id = s.init_graph[(size_t)i * k + j];
+      if (id != 0xFFFFFFFFu && id != i && id < s.n) {
+        const float d = seq_l2(s.vec + (size_t)i * s.stride, s.vec + (size_t)id * s.stride, s.dim);
+        key = ((uint64_t)__float_as_uint(d) << 32) | (id << 1) | 1u;
+        ++evals;
+      }
+      keys[j] = key;
+    }
+  }
+  __syncwarp();
+  // duplicates: the same id twice gives the same key; only its first occurrence stays
+  bool dupf[RF_MAXK / 32];
+#pragma unroll
+  for (int t = 0; t < RF_MAXK / 32; ++t) {
+    const uint32_t j = t * 32 + lane;
+    dupf[t] = false;
+    if (j < k && keys[j] != EMPTY)
+      for (uint32_t u = 0; u < j; ++u) dupf[t] |= keys[u] == keys[j];
+  }
+  __syncwarp();
+#pragma unroll
+  for (int t = 0; t < RF_MAXK / 32; ++t) {
+    const uint32_t j = t * 32 + lane;
+    if (j < k && dupf[t]) keys[j] = EMPTY;
+  }
+  __syncwarp();
+  uint32_t cnt = 0;
+  for (uint32_t j0 = 0; j0 < k; j0 += 32) {
+    const uint32_t j = j0 + lane;
+    cnt += __popc(__ballot_sync(0xffffffffu, j < k && keys[j] != EMPTY));
+  }
+  evals = __reduce_add_sync(0xffffffffu, evals);
+  if (cnt == 0) return;   // the random start of init_kernel stays
+  uint64_t *pool = s.pool + (size_t)i * s.L;
+  for (uint32_t j = lane; j < s.L; j += 32) pool[j] = EMPTY;
+  __syncwarp();
+  for (uint32_t j = lane; j < k; j += 32) {
+    const uint64_t key = keys[j];
+    if (key == EMPTY) continue;
+    uint32_t r = 0;
+    for (uint32_t u = 0; u < k; ++u) r += keys[u] < key;   // EMPTY is the largest value: never counted
+    if (r < s.L) pool[r] = key;
+  }
+  __syncwarp();
+  if (lane == 0) {
+    const uint32_t sz = cnt < s.L ? cnt : s.L;
+    // the random start's evaluations were counted by init_kernel; the reference evaluates only the initializer's rows
+    const unsigned long long old = s.psize[i];
+    s.psize[i] = sz;
+    s.worst[i] = (uint32_t)(pool[sz - 1] >> 32);
+    atomicAdd(s.stats + 0, (unsigned long long)evals - old);
+  }
 }
 
 // ---- warp-cooperative "keep the cap smallest keys, sorted" under a per-list lock -------------------------
@@ -594,12 +670,208 @@ __global__ void extract_kernel(State s, uint32_t *knn, float *knn_d) {
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// KD-tree initializer: efanna2e::IndexKDtree::Build (CNNS/efanna_graph/src/index_kdtree.cpp:279-435) in the batch form
+// oracle.c orc_kdtree_graph restates (see there for the rules); equal to it bit for bit. Level-synchronous build of all
+// trees at once: one warp per active node picks the cut (meanSplit / selectDivision), one CTA per active node does the
+// stable three-way partition of its segment and creates the two children; then one warp per (tree, point) walks the
+// point's path and, below the merge level, searches the sibling subtree whenever the point sits in the smaller child
+// (mergeSubGraphs), offering every distance to both ends' K-lists through the locked sorted insert of the join above.
+constexpr uint32_t KD_SEED = 0x4B445452U;
+constexpr uint32_t KD_TNS = 10, KD_SAMPLE = 101;
+constexpr int KD_RAND_DIM = 5;
+struct KdState {
+  const float *vec; size_t stride; uint32_t n, dim, K, T, ml, seed;
+  uint32_t *ids, *tmp;                         // [T, n] the trees' point orders; partition scratch
+  uint32_t *n_start, *n_end, *n_left, *n_depth; int *n_cutdim; float *n_cutval;   // nodes (roots = 0..T-1; left = INVALID: leaf)
+  uint32_t *act_in, *act_out;                  // active nodes of this / the next level
+  uint32_t *counters;                          // {nodes allocated, next active count, deepest level, 0}
+  uint64_t *lists; uint32_t *lsize, *lock;     // [n, K], [n], [n]
+  unsigned long long *stats;                   // {distance evaluations}
+};
+__global__ void kd_perm_kernel(KdState s, const uint32_t *ab) {
+  size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (e >= (size_t)s.T * s.n) return;
+  const uint32_t t = (uint32_t)(e / s.n), j = (uint32_t)(e % s.n);
+  s.ids[e] = (uint32_t)(((uint64_t)ab[2 * t] * j + ab[2 * t + 1]) % s.n);
+}
+// meanSplit (:17-52) + selectDivision (:110-133) for active node a: one warp, lane = dimensions lane, lane + 32, ...
+__global__ void __launch_bounds__(128) kd_cut_kernel(KdState s, uint32_t n_act) {
+  extern __shared__ float kd_sm[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t a = blockIdx.x * 4 + warp;
+  if (a >= n_act) return;
+  float *mean = kd_sm + (size_t)warp * 2 * s.dim, *var = mean + s.dim;
+  const uint32_t x = s.act_in[a];
+  const uint32_t start = s.n_start[x], count = s.n_end[x] - start;
+  const uint32_t t = start / s.n;   // segments are positions in the [T, n] array
+  const uint32_t *ids = s.ids + start;
+  const uint32_t cnt = count < KD_SAMPLE ? count : KD_SAMPLE;
+  const float div = 1.0f / (float)cnt;
+  for (uint32_t k = lane; k < s.dim; k += 32) {
+    float m = 0.f;
+    for (uint32_t j = 0; j < cnt; ++j) m += s.vec[(size_t)ids[j] * s.stride + k];
+    m *= div;
+    float v = 0.f;
+    for (uint32_t j = 0; j < cnt; ++j) { float d = s.vec[(size_t)ids[j] * s.stride + k] - m; v = __fadd_rn(v, __fmul_rn(d, d)); }  // no fma: the oracle's order
+    mean[k] = m; var[k] = v;
+  }
+  __syncwarp();
+  if (lane == 0) {
+    uint32_t topind[KD_RAND_DIM];
+    int num = 0;
+    for (uint32_t i = 0; i < s.dim; ++i) {
+      if (num < KD_RAND_DIM || var[i] > var[topind[num - 1]]) {
+        if (num < KD_RAND_DIM) topind[num++] = i; else topind[num - 1] = i;
+        int j = num - 1;
+        while (j > 0 && var[topind[j]] > var[topind[j - 1]]) { uint32_t w = topind[j]; topind[j] = topind[j - 1]; topind[j - 1] = w; --j; }
+      }
+    }
+    const uint32_t pick = seed_hash(s.seed ^ KD_SEED, t, (start - t * s.n) * 31u + count);
+    const uint32_t cd = topind[pick % (uint32_t)num];
+    s.n_cutdim[x] = (int)cd;
+    s.n_cutval[x] = mean[cd];
+  }
+}
+// stable three-way partition of active node a's segment (planeSplit's outcome, :69-108) + the split index (:54-62);
+// creates the children and queues those that are still larger than a leaf
+__global__ void __launch_bounds__(256) kd_partition_kernel(KdState s, uint32_t n_act) {
+  __shared__ uint32_t wtot[8][3];
+  __shared__ uint32_t tot[2];
+  const uint32_t a = blockIdx.x;
+  if (a >= n_act) return;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t x = s.act_in[a];
+  const uint32_t start = s.n_start[x], count = s.n_end[x] - start;
+  const int cd = s.n_cutdim[x];
+  const float cv = s.n_cutval[x];
+  uint32_t *ids = s.ids + start, *tmp = s.tmp + start;
+  // pass 1: lim1 = #(< cutval), lim2 = #(<= cutval)
+  uint32_t c1 = 0, c2 = 0;
+  for (uint32_t j = tid; j < count; j += 256) {
+    const float v = s.vec[(size_t)ids[j] * s.stride + cd];
+    c1 += v < cv; c2 += v <= cv;
+  }
+  c1 = __reduce_add_sync(0xffffffffu, c1); c2 = __reduce_add_sync(0xffffffffu, c2);
+  if (lane == 0) { wtot[warp][0] = c1; wtot[warp][1] = c2; }
+  __syncthreads();
+  if (tid == 0) {
+    uint32_t l1 = 0, l2 = 0;
+    for (int w = 0; w < 8; ++w) { l1 += wtot[w][0]; l2 += wtot[w][1]; }
+    tot[0] = l1; tot[1] = l2;
+  }
+  __syncthreads();
+  const uint32_t lim1 = tot[0], lim2 = tot[1];
+  // pass 2: stable scatter, class 0 -> [0, lim1), 1 -> [lim1, lim2), 2 -> [lim2, count)
+  uint32_t run[3] = {0, lim1, lim2};
+  for (uint32_t j0 = 0; j0 < count; j0 += 256) {
+    const uint32_t j = j0 + tid;
+    int cls = -1;
+    uint32_t id = 0;
+    if (j < count) {
+      id = ids[j];
+      const float v = s.vec[(size_t)id * s.stride + cd];
+      cls = v < cv ? 0 : (v == cv ? 1 : 2);
+    }
+    uint32_t wr = 0;
+    __syncthreads();
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const unsigned m = __ballot_sync(0xffffffffu, cls == c);
+      if (cls == c) wr = __popc(m & ((1u << lane) - 1));
+      if (lane == 0) wtot[warp][c] = __popc(m);
+    }
+    __syncthreads();
+    if (cls >= 0) {
+      uint32_t off = wr;
+      for (int w = 0; w < warp; ++w) off += wtot[w][cls];
+      tmp[run[cls] + off] = id;
+    }
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+      for (int w = 0; w < 8; ++w) run[c] += wtot[w][c];
+  }
+  __syncthreads();
+  for (uint32_t j = tid; j < count; j += 256) ids[j] = tmp[j];
+  if (tid == 0) {
+    uint32_t index;
+    if (lim1 > count / 2) index = lim1; else if (lim2 < count / 2) index = lim2; else index = count / 2;
+    if (lim1 == count || lim2 == 0) index = count / 2;
+    const uint32_t L = atomicAdd(&s.counters[0], 2u);
+    const uint32_t dep = s.n_depth[x] + 1;
+    s.n_left[x] = L;
+    s.n_start[L] = start; s.n_end[L] = start + index; s.n_left[L] = INVALID_ID; s.n_depth[L] = dep;
+    s.n_start[L + 1] = start + index; s.n_end[L + 1] = start + count; s.n_left[L + 1] = INVALID_ID; s.n_depth[L + 1] = dep;
+    atomicMax(&s.counters[2], dep);
+    if (index > KD_TNS) s.act_out[atomicAdd(&s.counters[1], 1u)] = L;
+    if (count - index > KD_TNS) s.act_out[atomicAdd(&s.counters[1], 1u)] = L + 1;
+  }
+}
+// mergeSubGraphs (:221-275) from the point's side: warp w = (tree t, position pos of the tree's final order)
+__global__ void __launch_bounds__(128) kd_merge_kernel(KdState s) {
+  const int lane = threadIdx.x & 31;
+  const size_t w = (size_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (w >= (size_t)s.T * s.n) return;
+  const uint32_t t = (uint32_t)(w / s.n);
+  const uint32_t gpos = (uint32_t)w;                 // position in the [T, n] array = what n_start / n_end hold
+  const uint32_t p = s.ids[w];
+  const float *pv = s.vec + (size_t)p * s.stride;
+  uint32_t x = t, evals = 0;
+  while (true) {
+    const uint32_t L = s.n_left[x];
+    if (L == INVALID_ID) break;
+    const uint32_t R = L + 1;
+    const uint32_t endL = s.n_end[L];
+    const bool inL = gpos < endL;
+    const uint32_t numL = endL - s.n_start[L], numR = s.n_end[R] - s.n_start[R];
+    const bool searchers_left = numL < numR;
+    if (s.n_depth[x] >= s.ml && inL == searchers_left) {
+      uint32_t y = inL ? R : L;
+      for (uint32_t yl = s.n_left[y]; yl != INVALID_ID; yl = s.n_left[y]) y = pv[s.n_cutdim[y]] < s.n_cutval[y] ? yl : yl + 1;
+      const uint32_t ls = s.n_start[y], ln = s.n_end[y] - ls;   // a leaf: <= KD_TNS points
+      uint32_t q = INVALID_ID;
+      float d = 0.f;
+      if ((uint32_t)lane < ln) {
+        q = s.ids[ls + lane];
+        d = seq_l2(s.vec + (size_t)q * s.stride, pv, s.dim);
+      }
+      evals += ln;
+      for (uint32_t j = 0; j < ln; ++j) {
+        const uint32_t qj = __shfl_sync(0xffffffffu, q, (int)j);
+        const uint64_t db = (uint64_t)__float_as_uint(__shfl_sync(0xffffffffu, d, (int)j)) << 32;
+        topl_insert_dispatch(s.lists + (size_t)qj * s.K, s.lsize + qj, s.lock + qj, s.K, db | ((uint64_t)p << 1), true, lane);
+        topl_insert_dispatch(s.lists + (size_t)p * s.K, s.lsize + p, s.lock + p, s.K, db | ((uint64_t)qj << 1), true, lane);
+      }
+    }
+    x = inL ? L : R;
+  }
+  if (lane == 0 && evals) atomicAdd(s.stats + 0, (unsigned long long)evals);
+}
+// rows ascending (distance, id); short rows filled with distinct hashed ids at distance +inf (:413-424)
+__global__ void kd_extract_kernel(KdState s, uint32_t *knn, float *knn_d) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= s.n) return;
+  uint32_t sz = s.lsize[i], ctr = 0;
+  const uint64_t *l = s.lists + (size_t)i * s.K;
+  uint32_t *row = knn + (size_t)i * s.K;
+  for (uint32_t j = 0; j < sz; ++j) { row[j] = (uint32_t)l[j] >> 1; if (knn_d) knn_d[(size_t)i * s.K + j] = __uint_as_float((uint32_t)(l[j] >> 32)); }
+  while (sz < s.K) {
+    const uint32_t id = seed_hash(s.seed ^ KD_SEED, i, 1000u + ctr++) % s.n;
+    bool dup = false;
+    for (uint32_t j = 0; j < sz; ++j) dup |= row[j] == id;
+    if (dup) continue;
+    row[sz] = id;
+    if (knn_d) knn_d[(size_t)i * s.K + sz] = __int_as_float(0x7f800000);
+    ++sz;
+  }
+}
+
 }  // namespace nnd
 
 // Host driver. knn [n,K] / knn_d [n,K] are device pointers. info8 = {distance evaluations, offers queued,
 // pool inserts, iterations, join ms, update ms, 0, 0}.
 int nndescent_launch(b200ann_handle *h, const b200ann_index *ix, size_t K, size_t L, size_t iter, size_t S, size_t R,
-                     uint32_t seed, uint32_t *knn, float *knn_d, uint64_t *info8) {
+                     uint32_t seed, uint32_t *knn, float *knn_d, uint64_t *info8, const uint32_t *init_graph, size_t init_k) {
   using namespace nnd;
   const size_t n = ix->n;
   if (ix->metric != B200ANN_L2)
@@ -645,6 +917,13 @@ int nndescent_launch(b200ann_handle *h, const b200ann_index *ix, size_t K, size_
   const unsigned nb = (unsigned)((n + TB - 1) / TB);
   init_kernel<<<nb, TB, 0, st>>>(s, seed);
   h->launches++;
+  if (init_graph) {
+    if (init_k == 0 || init_k > L || init_k > (size_t)RF_MAXK)
+      return set_err(h, B200ANN_ERR_ARG, "nndescent_refine: need 0 < init_k <= L (<= 512)");
+    s.init_graph = init_graph; s.init_k = (uint32_t)init_k;
+    init_refine_kernel<<<(unsigned)((n + RF_WARPS - 1) / RF_WARPS), RF_WARPS * 32, 0, st>>>(s);
+    h->launches++;
+  }
   const uint32_t cn_max = (uint32_t)(std::max(2 * S, S + R) + 2 * R);
   const size_t smem = 2 * (size_t)TILE * ROWF * sizeof(float) + (size_t)TILE * DROW * sizeof(uint32_t) + 2 * (size_t)cn_max * sizeof(uint32_t);
   CU_CHECK(h, cudaFuncSetAttribute(join_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -700,6 +979,92 @@ int nndescent_launch(b200ann_handle *h, const b200ann_index *ix, size_t K, size_
     fprintf(stderr, "NND_PROF merges %llu: avg cycles lock %llu load %llu insert %llu writeback+fence %llu\n", gp[4], gp[0] / (gp[4] + 1),
             gp[1] / (gp[4] + 1), gp[2] / (gp[4] + 1), gp[3] / (gp[4] + 1));
 #endif
+  }
+  return 0;
+}
+
+// KD-tree initializer (see the kernels above). knn [n,K] / knn_d device pointers. info8 = {distance evaluations, tree
+// nodes, leaves, deepest level, levels run, 0, 0, 0}.
+int kdtree_launch(b200ann_handle *h, const b200ann_index *ix, size_t K, size_t nTrees, size_t ml, uint32_t seed, uint32_t *knn,
+                  float *knn_d, uint64_t *info8) {
+  using namespace nnd;
+  const size_t n = ix->n, T = nTrees;
+  if (ix->metric != B200ANN_L2) return set_err(h, B200ANN_ERR_ARG, "kdtree_graph: L2 only (efanna2e::Index always builds DistanceL2)");
+  if (n < 2 || K == 0 || K >= n || K > 512 || T == 0 || T > 64 || T * n >= (1ull << 31) || ix->dim > 4096)
+    return set_err(h, B200ANN_ERR_ARG, "kdtree_graph: need 0 < K < n, K <= 512, 1 <= nTrees <= 64, nTrees * n < 2^31, dim <= 4096");
+  cudaStream_t st = h->stream;
+  KdState s{};
+  s.vec = ix->vec; s.stride = ix->stride; s.n = (uint32_t)n; s.dim = (uint32_t)ix->dim; s.K = (uint32_t)K; s.T = (uint32_t)T;
+  s.ml = (uint32_t)ml; s.seed = seed;
+  const size_t capn = 2 * T * n + 8;
+  DevBuf<uint32_t> ids, tmp, nodes, act, counters, lsz, ab;
+  DevBuf<float> cutv;
+  DevBuf<uint64_t> lists;
+  DevBuf<unsigned long long> stats;
+  CU_CHECK(h, ids.alloc(T * n, st)); CU_CHECK(h, tmp.alloc(T * n, st));
+  CU_CHECK(h, nodes.alloc(5 * capn, st)); CU_CHECK(h, cutv.alloc(capn, st));
+  CU_CHECK(h, act.alloc(2 * capn, st)); CU_CHECK(h, counters.alloc(4, st));
+  CU_CHECK(h, lists.alloc(n * K, st)); CU_CHECK(h, lsz.alloc(2 * n, st));
+  CU_CHECK(h, ab.alloc(2 * T, st)); CU_CHECK(h, stats.alloc(4, st));
+  s.ids = ids.p; s.tmp = tmp.p;
+  s.n_start = nodes.p; s.n_end = nodes.p + capn; s.n_left = nodes.p + 2 * capn; s.n_depth = nodes.p + 3 * capn;
+  s.n_cutdim = reinterpret_cast<int *>(nodes.p + 4 * capn); s.n_cutval = cutv.p;
+  s.counters = counters.p; s.lists = lists.p; s.lsize = lsz.p; s.lock = lsz.p + n; s.stats = stats.p;
+  // tree t lists the points in the order (a_t * j + b_t) mod n, a_t coprime to n (oracle.c kd_mult)
+  auto mix = [](uint32_t x) { x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16; return x; };
+  auto hash = [&](uint32_t sd, uint32_t q, uint32_t c) { return mix(mix(sd ^ (q * 0x9E3779B9U)) + c * 0x85EBCA6BU); };
+  auto gcd = [](uint32_t a, uint32_t b) { while (b) { uint32_t t = a % b; a = b; b = t; } return a; };
+  std::vector<uint32_t> hab(2 * T), hn(5 * T), hact(T);
+  for (uint32_t t = 0; t < T; ++t) {
+    uint32_t a = hash(seed ^ KD_SEED, t, 0x7001u) % (uint32_t)n;
+    if (a == 0) a = 1;
+    while (gcd(a, (uint32_t)n) != 1) a = a + 1 == (uint32_t)n ? 1 : a + 1;
+    hab[2 * t] = a; hab[2 * t + 1] = hash(seed ^ KD_SEED, t, 0x7002u) % (uint32_t)n;
+  }
+  CU_CHECK(h, cudaMemcpyAsync(ab.p, hab.data(), 2 * T * 4, cudaMemcpyHostToDevice, st));
+  kd_perm_kernel<<<(unsigned)((T * n + 255) / 256), 256, 0, st>>>(s, ab.p);
+  // roots: node t = the whole of tree t
+  std::vector<uint32_t> rs(T), re(T), rl(T, INVALID_ID), rd(T, 0u);
+  for (uint32_t t = 0; t < T; ++t) { rs[t] = (uint32_t)(t * n); re[t] = (uint32_t)((t + 1) * n); hact[t] = t; }
+  CU_CHECK(h, cudaMemcpyAsync(s.n_start, rs.data(), T * 4, cudaMemcpyHostToDevice, st));
+  CU_CHECK(h, cudaMemcpyAsync(s.n_end, re.data(), T * 4, cudaMemcpyHostToDevice, st));
+  CU_CHECK(h, cudaMemcpyAsync(s.n_left, rl.data(), T * 4, cudaMemcpyHostToDevice, st));
+  CU_CHECK(h, cudaMemcpyAsync(s.n_depth, rd.data(), T * 4, cudaMemcpyHostToDevice, st));
+  uint32_t hc[4] = {(uint32_t)T, 0u, 0u, 0u};
+  CU_CHECK(h, cudaMemcpyAsync(counters.p, hc, sizeof hc, cudaMemcpyHostToDevice, st));
+  CU_CHECK(h, cudaMemcpyAsync(act.p, hact.data(), T * 4, cudaMemcpyHostToDevice, st));
+  CU_CHECK(h, cudaMemsetAsync(stats.p, 0, 4 * sizeof(unsigned long long), st));
+  CU_CHECK(h, cudaMemsetAsync(lsz.p, 0, 2 * n * 4, st));
+  fill_u64_kernel<<<h->sm_count * 8, 256, 0, st>>>(lists.p, n * K, EMPTY);
+  h->launches += 2;
+  const size_t cut_smem = (size_t)4 * 2 * ix->dim * sizeof(float);
+  CU_CHECK(h, cudaFuncSetAttribute(kd_cut_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cut_smem));
+  uint32_t n_act = n > KD_TNS ? (uint32_t)T : 0u, levels = 0;
+  uint32_t *ain = act.p, *aout = act.p + capn;
+  while (n_act) {
+    s.act_in = ain; s.act_out = aout;
+    kd_cut_kernel<<<(n_act + 3) / 4, 128, cut_smem, st>>>(s, n_act);
+    kd_partition_kernel<<<n_act, 256, 0, st>>>(s, n_act);
+    h->launches += 2;
+    CU_CHECK(h, cudaMemcpyAsync(hc, counters.p, sizeof hc, cudaMemcpyDeviceToHost, st));
+    CU_CHECK(h, cudaStreamSynchronize(st));
+    n_act = hc[1];
+    CU_CHECK(h, cudaMemsetAsync(counters.p + 1, 0, 4, st));
+    std::swap(ain, aout);
+    if (++levels > 4096) return set_err(h, B200ANN_ERR_CUDA, "kdtree_graph: the tree build does not terminate");
+  }
+  kd_merge_kernel<<<(unsigned)((T * n + 3) / 4), 128, 0, st>>>(s);
+  kd_extract_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(s, knn, knn_d);
+  h->launches += 2;
+  CU_CHECK(h, cudaGetLastError());
+  unsigned long long hs[4];
+  CU_CHECK(h, cudaMemcpyAsync(hs, stats.p, sizeof hs, cudaMemcpyDeviceToHost, st));
+  CU_CHECK(h, cudaMemcpyAsync(hc, counters.p, sizeof hc, cudaMemcpyDeviceToHost, st));
+  CU_CHECK(h, cudaStreamSynchronize(st));
+  if (info8) {
+    // every internal node has two children: nodes = T + 2 * internal, leaves = nodes - internal
+    const uint64_t nn = hc[0], internal = (nn - T) / 2;
+    info8[0] = hs[0]; info8[1] = nn; info8[2] = nn - internal; info8[3] = hc[2]; info8[4] = levels; info8[5] = info8[6] = info8[7] = 0;
   }
   return 0;
 }

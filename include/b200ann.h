@@ -195,6 +195,30 @@ int b200ann_knn_graph_rows(b200ann_handle_t h, b200ann_index_t ix, size_t row0, 
 int b200ann_nndescent(b200ann_handle_t h, b200ann_index_t ix, size_t K, size_t L, size_t iter, size_t S, size_t R,
                       uint32_t seed, uint32_t *knn /*[h|d]*/, float *dists /*[h|d] or NULL*/, uint64_t *info /*[h]*/);
 
+/* replaces efanna2e::IndexKDtree::Build (CNNS/efanna_graph/src/index_kdtree.cpp:279-435; driver
+ * efanna_graph/tests/test_kdtree_graph.cpp): an initial approximate kNN graph from nTrees randomized KD-trees
+ * (meanSplit over 101 sampled points, a random one of the 5 highest-variance dimensions, leaves of <= 10 points) whose
+ * subtrees below depth mLevel are "conquered" - every point of an internal node's smaller child walks the other
+ * child to a leaf and the distances to that leaf's points are offered to both ends' K-lists. "nTrees", "mLevel", "K"
+ * are the reference's parameters of those names. The reference is not reproducible (std::random_shuffle, generators
+ * seeded with the OpenMP thread number); this is the batch form oracle.c orc_kdtree_graph restates, bit for bit: the
+ * shuffle of tree t is an affine permutation, the random pick a counter hash of (seed, tree, node), partitions are
+ * stable, a K-list is the set of the K smallest (distance, id) offered. knn [n,K] ascending (distance, id); rows with
+ * fewer than K entries are filled with distinct pseudo-random ids (dists +inf) like :413-424. L2 only. Feed it to
+ * b200ann_nndescent_refine (IndexGraph::RefineGraph). info (optional, 8 x u64): {distance evaluations, tree nodes,
+ * leaves, deepest level, levels, 0, 0, 0}. */
+int b200ann_kdtree_graph(b200ann_handle_t h, b200ann_index_t ix, size_t K, size_t nTrees, size_t mLevel, uint32_t seed,
+                         uint32_t *knn /*[h|d]*/, float *dists /*[h|d] or NULL*/, uint64_t *info /*[h]*/);
+/* replaces efanna2e::IndexGraph::RefineGraph (CNNS/efanna_graph/src/index_graph.cpp:235-262 = InitializeGraph_Refine
+ * :203-232 + NNDescent :122-136): NN-descent whose pools start from the rows of an initializer's graph - init_graph
+ * [n, init_k], B200ANN_INVALID padding allowed, self / duplicate / out-of-range ids dropped, every entry flagged new,
+ * init_k <= L - instead of from S random ids (what the KD-tree initializer of the reference feeds it, index_kdtree.cpp;
+ * here any graph: b200ann_kdtree_graph, a previous b200ann_nndescent result, a graph file). Everything else is
+ * b200ann_nndescent. Bit-exact against oracle.c orc_nndescent_refine. */
+int b200ann_nndescent_refine(b200ann_handle_t h, b200ann_index_t ix, size_t K, size_t L, size_t iter, size_t S, size_t R,
+                             uint32_t seed, const uint32_t *init_graph /*[h|d]*/, size_t init_k, uint32_t *knn /*[h|d]*/,
+                             float *dists /*[h|d] or NULL*/, uint64_t *info /*[h]*/);
+
 /* Which kernel b200ann_bf_knn / b200ann_knn_graph run on: 0 = auto (tensor cores when n >= 4096 and
  * nq*n >= 2^24, else fp32 SIMT), 1 = fp32 SIMT tiles (csrc/bf_knn.cu), 2 = tcgen05 tensor cores with fp32
  * re-ranking (csrc/knn_tc.cu). Both give the same bits. slack = extra shortlist entries per row kept by the

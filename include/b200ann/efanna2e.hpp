@@ -249,6 +249,47 @@ class IndexNSG : public Index {
   unsigned ep_ = 0;
 };
 
+// efanna2e::IndexKDtree (efanna_graph/include/efanna2e/index_kdtree.h, src/index_kdtree.cpp:279-435; driver
+// efanna_graph/tests/test_kdtree_graph.cpp): the KD-tree initializer. Build(n, data, {"K", "nTrees", "mLevel"}) computes
+// an initial kNN graph on the GPU (b200ann_kdtree_graph); Save writes it like the reference ([K][K ids] per row, :436-445).
+// Hand it to IndexGraph as the initializer and call RefineGraph. "seed" (default 0) replaces the reference's generators.
+class IndexKDtree : public Index {
+ public:
+  explicit IndexKDtree(const size_t dimension, const size_t n, Metric m, Index *initializer, int device = 0)
+      : Index(dimension, n, m), gpu_(device) { (void)initializer; }
+  void Build(size_t n, const float *data, const Parameters &parameters) override {
+    K_ = parameters.Get<unsigned>("K");
+    nd_ = n; data_ = data;
+    b200ann_index_t ix = nullptr;
+    detail::check(gpu_.h, b200ann_index_create(gpu_.h, data, n, dimension_, dimension_, B200ANN_L2, &ix), "b200ann_index_create");
+    knn_.resize(n * (size_t)K_);
+    int rc = b200ann_kdtree_graph(gpu_.h, ix, K_, parameters.Get<unsigned>("nTrees"), parameters.Get<unsigned>("mLevel"),
+                                  parameters.Get<unsigned>("seed", 0u), knn_.data(), nullptr, info_);
+    b200ann_index_destroy(ix);
+    detail::check(gpu_.h, rc, "IndexKDtree::Build");
+    has_built = true;
+  }
+  void Search(const float *, const float *, size_t, const Parameters &, unsigned *) override {}  // empty in the reference too (:450-456)
+  void Save(const char *filename) override {
+    std::ofstream out(filename, std::ios::binary | std::ios::out);
+    if (!out) throw std::runtime_error(std::string("cannot open ") + filename);
+    for (size_t i = 0; i < nd_; i++) {
+      out.write((const char *)&K_, 4);
+      out.write((const char *)&knn_[i * K_], (std::streamsize)K_ * 4);
+    }
+  }
+  void Load(const char *) override {}  // empty in the reference (:447-448)
+  const std::vector<uint32_t> &Graph() const { return knn_; }  // [n,K] row-major
+  unsigned K() const { return K_; }
+  const uint64_t *BuildInfo() const { return info_; }
+
+ private:
+  detail::Gpu gpu_;
+  std::vector<uint32_t> knn_;
+  unsigned K_ = 0;
+  uint64_t info_[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+};
+
 // efanna2e::IndexGraph (efanna_graph/include/efanna2e/index_graph.h:23-72): Build produces the kNN
 // graph NSG consumes. Like the reference (index_graph.cpp:265-294) Build runs NN-descent with "K","L",
 // "iter","S","R" (b200ann_nndescent: InitializeGraph from random ids, iter x {join, update}, top K).
@@ -279,6 +320,32 @@ class IndexGraph : public Index {
     }
     b200ann_index_destroy(ix);
     detail::check(gpu_.h, rc, "IndexGraph::Build");
+    has_built = true;
+  }
+  // index_graph.cpp:235-262: NN-descent started from the initializer's graph (an IndexKDtree that has been built, or
+  // this object's own graph from a previous Build / Load) instead of from random ids -> b200ann_nndescent_refine
+  void RefineGraph(const float *data, const Parameters &parameters) {
+    const std::vector<uint32_t> *g = &knn_;
+    unsigned gk = K_;
+    if (auto *kd = dynamic_cast<IndexKDtree *>(initializer_)) {
+      if (!kd->HasBuilt()) throw std::runtime_error("IndexGraph::RefineGraph: the initializer has not been built");
+      g = &kd->Graph(); gk = kd->K();
+    }
+    if (g->empty() || g->size() != nd_ * (size_t)gk) {
+      if (g == &knn_) throw std::runtime_error("IndexGraph::RefineGraph: no initial graph (an IndexKDtree initializer, or Build / Load first)");
+      nd_ = g->size() / gk;
+    }
+    data_ = data;
+    const unsigned K = parameters.Get<unsigned>("K");
+    b200ann_index_t ix = nullptr;
+    detail::check(gpu_.h, b200ann_index_create(gpu_.h, data, nd_, dimension_, dimension_, B200ANN_L2, &ix), "b200ann_index_create");
+    std::vector<uint32_t> out(nd_ * (size_t)K);
+    int rc = b200ann_nndescent_refine(gpu_.h, ix, K, parameters.Get<unsigned>("L"), parameters.Get<unsigned>("iter"),
+                                      parameters.Get<unsigned>("S"), parameters.Get<unsigned>("R"), parameters.Get<unsigned>("seed", 0u),
+                                      g->data(), gk, out.data(), nullptr, info_);
+    b200ann_index_destroy(ix);
+    detail::check(gpu_.h, rc, "IndexGraph::RefineGraph");
+    knn_.swap(out); K_ = K;
     has_built = true;
   }
   // Search over a bare kNN graph is not on the drivers' path (index_graph.cpp:296-346 is only used by

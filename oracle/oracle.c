@@ -1788,10 +1788,23 @@ static int topl_insert(uint64_t *list, unsigned *size, unsigned cap, uint64_t ke
   return 1;
 }
 #define NND_SEED_POOL 0x68E31DA4U
+/* init_graph [n, init_k] (or NULL): IndexGraph::RefineGraph (index_graph.cpp:235-262) = InitializeGraph_Refine
+ * (:203-232) + NNDescent: the pools start from the rows of an initializer's graph (ids sorted, duplicates and the
+ * node itself dropped, every entry flagged new) instead of S random ids; nn_new is the nhood ctor's random draw
+ * either way. Rows may be padded with ORC_INVALID; init_k <= L. */
+EXPORT int orc_nndescent_refine(const float *data, size_t n, size_t dim, size_t stride, unsigned K, unsigned L,
+                                unsigned iter, unsigned S, unsigned R, uint32_t seed, int mode, const uint32_t *init_graph,
+                                unsigned init_k, uint32_t *knn, float *knn_d, uint64_t *info);
 EXPORT int orc_nndescent_batch(const float *data, size_t n, size_t dim, size_t stride, unsigned K, unsigned L,
                                unsigned iter, unsigned S, unsigned R, uint32_t seed, int mode, uint32_t *knn,
                                float *knn_d, uint64_t *info) {
+  return orc_nndescent_refine(data, n, dim, stride, K, L, iter, S, R, seed, mode, NULL, 0, knn, knn_d, info);
+}
+EXPORT int orc_nndescent_refine(const float *data, size_t n, size_t dim, size_t stride, unsigned K, unsigned L,
+                                unsigned iter, unsigned S, unsigned R, uint32_t seed, int mode, const uint32_t *init_graph,
+                                unsigned init_k, uint32_t *knn, float *knn_d, uint64_t *info) {
   if (n <= 2 * S + 1 || S + 1 > L || K > L || R == 0 || S == 0 || n >= (1u << 31)) return -1;
+  if (init_graph && (init_k == 0 || init_k > L)) return -1;
   orc_bhood *g = (orc_bhood *)calloc(n, sizeof(orc_bhood));
   uint32_t *oldmax = (uint32_t *)malloc(sizeof(uint32_t) * n);
   unsigned cap_new = (2 * S > S + R ? 2 * S : S + R), cap_old = 2 * R;
@@ -1821,13 +1834,24 @@ EXPORT int orc_nndescent_batch(const float *data, size_t n, size_t dim, size_t s
     orc_hs s1 = {seed, (uint32_t)i, 0};
     gen_random(hs_next, &s1, h->fwd_new, 2 * S, (unsigned)n);    /* nhood ctor, neighbor.h:41-47 */
     h->n_fnew = 2 * S;
-    orc_hs s2 = {seed ^ NND_SEED_POOL, (uint32_t)i, 0};
-    gen_random(hs_next, &s2, tmp, S + 1, (unsigned)n);           /* IndexRandom::Search, :189 */
-    for (unsigned j = 0; j < S; j++) {
-      if (tmp[j] == i) continue;
-      float d = orc_dist(mode, data + i * stride, data + (size_t)tmp[j] * stride, dim);
-      n_dist++;
-      topl_insert(h->pool, &h->psize, L, ((uint64_t)f2u(d) << 32) | (tmp[j] << 1) | 1u, 1);
+    if (init_graph) {                                             /* InitializeGraph_Refine, :215-226 */
+      for (unsigned j = 0; j < init_k; j++) {
+        uint32_t id = init_graph[i * init_k + j];
+        if (id == ORC_INVALID || id == i || id >= n) continue;
+        float d = orc_dist(mode, data + i * stride, data + (size_t)id * stride, dim);
+        n_dist++;
+        topl_insert(h->pool, &h->psize, L, ((uint64_t)f2u(d) << 32) | (id << 1) | 1u, 1);
+      }
+    }
+    if (!init_graph || h->psize == 0) {
+      orc_hs s2 = {seed ^ NND_SEED_POOL, (uint32_t)i, 0};
+      gen_random(hs_next, &s2, tmp, S + 1, (unsigned)n);         /* IndexRandom::Search, :189 */
+      for (unsigned j = 0; j < S; j++) {
+        if (tmp[j] == i) continue;
+        float d = orc_dist(mode, data + i * stride, data + (size_t)tmp[j] * stride, dim);
+        n_dist++;
+        topl_insert(h->pool, &h->psize, L, ((uint64_t)f2u(d) << 32) | (tmp[j] << 1) | 1u, 1);
+      }
     }
   }
   for (unsigned it = 0; it < iter; it++) {
@@ -2163,6 +2187,153 @@ EXPORT int orc_hnsw_build(const float *data, size_t n, size_t dim, size_t stride
   *ep_out = h.ep; *maxlevel_out = h.maxlevel;
   if (info) { info[0] = h.n_dist; info[1] = batches; info[2] = info[3] = 0; }
   free(h.cnt0); free(h.cntu); free(h.visited); free(top); free(cand); free(expanded); free(tmp); free(rev);
+  return 0;
+}
+
+/* ------------------------------------------------------------------ KD-tree initializer */
+/* efanna2e::IndexKDtree::Build (CNNS/efanna_graph/src/index_kdtree.cpp:279-435): nTrees randomized KD-trees (meanSplit
+ * :17-67 over the first SAMPLE_NUM+1 = 101 points of a node, selectDivision :110-133 = a random one of the RAND_DIM = 5
+ * highest-variance dimensions, planeSplit :69-108, leaves of <= TNS = 10 points, DFSbuild :135-160), then below the
+ * merge level ml every internal node is "conquered" (mergeSubGraphs :221-275): each point of its smaller child walks
+ * the other child's subtree to a leaf (SearchToLeaf :207-218) and the distances to that leaf's points are offered to
+ * both ends' K-lists. The reference is not reproducible (std::random_shuffle, mt19937 seeded with the OpenMP thread
+ * number, lock order), so this is the batch form the CUDA path computes (csrc/kdtree.cu), equal to it bit for bit:
+ *   shuffle    tree t lists the points in the order  id_j = (a_t * j + b_t) mod n  (a_t odd-ish, coprime to n)
+ *   split      as meanSplit, the random pick = orc_seed_hash(seed ^ KD_SEED, t, start * 31 + count) % num; the
+ *              partition is the stable three-way one (< cutval | == cutval | > cutval), the split index the
+ *              reference's rule (:54-62)
+ *   lists      a K-list is the set of the K smallest (distance, id) it was offered (what a bounded heap holds,
+ *              in any order); distances in the sequential-fma order (ORC_L2_SEQ_FMA)
+ *   output     rows ascending (distance, id); a row with fewer than K entries is filled with distinct ids
+ *              orc_seed_hash(seed ^ KD_SEED, i, 1000 + draw) % n not yet present (:413-424 fills with rng() % N), their
+ *              distance +inf.
+ * info [4] = {distance evaluations, tree nodes, leaves, deepest level}. */
+#define KD_SEED 0x4B445452U
+#define KD_TNS 10
+#define KD_SAMPLE 101
+#define KD_RAND_DIM 5
+typedef struct { uint32_t start, end, left; int cutdim; float cutval; int depth; } kd_node;
+static uint32_t kd_gcd(uint32_t a, uint32_t b) { while (b) { uint32_t t = a % b; a = b; b = t; } return a; }
+/* multiplier of tree t's permutation: the first value >= hash % n that is coprime to n (1 for n == 1) */
+static uint32_t kd_mult(uint32_t seed, uint32_t t, uint32_t n) {
+  uint32_t a = orc_seed_hash(seed ^ KD_SEED, t, 0x7001u) % n;
+  if (a == 0) a = 1;
+  while (kd_gcd(a, n) != 1) a = a + 1 == n ? 1 : a + 1;
+  return a;
+}
+/* meanSplit over ids[0..count): returns the split index, sets cutdim / cutval; ids are partitioned (stable 3-way) */
+static uint32_t kd_split(const float *data, size_t dim, size_t stride, uint32_t *ids, uint32_t count, uint32_t pick_hash,
+                         float *mean, float *var, uint32_t *tmp, int *cutdim_out, float *cutval_out) {
+  uint32_t cnt = count < KD_SAMPLE ? count : KD_SAMPLE;
+  for (size_t k = 0; k < dim; k++) { mean[k] = 0.f; var[k] = 0.f; }
+  for (uint32_t j = 0; j < cnt; j++) {
+    const float *v = data + (size_t)ids[j] * stride;
+    for (size_t k = 0; k < dim; k++) mean[k] += v[k];
+  }
+  float div = 1.0f / (float)cnt;
+  for (size_t k = 0; k < dim; k++) mean[k] *= div;
+  for (uint32_t j = 0; j < cnt; j++) {
+    const float *v = data + (size_t)ids[j] * stride;
+    for (size_t k = 0; k < dim; k++) { float d = v[k] - mean[k]; var[k] += d * d; }
+  }
+  size_t topind[KD_RAND_DIM];
+  int num = 0;
+  for (size_t i = 0; i < dim; i++) {               /* selectDivision :110-133 */
+    if (num < KD_RAND_DIM || var[i] > var[topind[num - 1]]) {
+      if (num < KD_RAND_DIM) topind[num++] = i; else topind[num - 1] = i;
+      int j = num - 1;
+      while (j > 0 && var[topind[j]] > var[topind[j - 1]]) { size_t t = topind[j]; topind[j] = topind[j - 1]; topind[j - 1] = t; --j; }
+    }
+  }
+  int cutdim = (int)topind[pick_hash % (uint32_t)num];
+  float cutval = mean[cutdim];
+  uint32_t lim1 = 0, lim2 = 0, o = 0;
+  for (uint32_t j = 0; j < count; j++) { float x = data[(size_t)ids[j] * stride + cutdim]; lim1 += x < cutval; lim2 += x <= cutval; }
+  for (int cls = 0; cls < 3; cls++)
+    for (uint32_t j = 0; j < count; j++) {
+      float x = data[(size_t)ids[j] * stride + cutdim];
+      int c = x < cutval ? 0 : (x == cutval ? 1 : 2);
+      if (c == cls) tmp[o++] = ids[j];
+    }
+  memcpy(ids, tmp, sizeof(uint32_t) * count);
+  uint32_t index;
+  if (lim1 > count / 2) index = lim1; else if (lim2 < count / 2) index = lim2; else index = count / 2;
+  if (lim1 == count || lim2 == 0) index = count / 2;
+  *cutdim_out = cutdim; *cutval_out = cutval;
+  return index;
+}
+EXPORT int orc_kdtree_graph(const float *data, size_t n, size_t dim, size_t stride, unsigned K, unsigned nTrees, unsigned ml,
+                            uint32_t seed, uint32_t *knn, float *knn_d, uint64_t *info) {
+  if (n < 2 || K == 0 || K >= n || nTrees == 0 || n >= (1u << 31)) return -1;
+  uint64_t *lists = (uint64_t *)malloc(sizeof(uint64_t) * n * K);
+  unsigned *lsize = (unsigned *)calloc(n, sizeof(unsigned));
+  uint32_t *ids = (uint32_t *)malloc(4 * n), *tmp = (uint32_t *)malloc(4 * n);
+  float *mean = (float *)malloc(4 * dim), *var = (float *)malloc(4 * dim);
+  size_t capn = 2 * n + 8;
+  kd_node *nodes = (kd_node *)malloc(sizeof(kd_node) * capn);
+  uint64_t n_dist = 0, n_nodes = 0, n_leaves = 0, deepest = 0;
+  for (unsigned t = 0; t < nTrees; t++) {
+    const uint32_t a = kd_mult(seed, t, (uint32_t)n), b = orc_seed_hash(seed ^ KD_SEED, t, 0x7002u) % (uint32_t)n;
+    for (size_t j = 0; j < n; j++) ids[j] = (uint32_t)(((uint64_t)a * j + b) % n);
+    /* level-synchronous build: nodes[lo, hi) is the current level */
+    size_t nn = 0, lo = 0, hi = 1;
+    nodes[nn].start = 0; nodes[nn].end = (uint32_t)n; nodes[nn].left = ORC_INVALID; nodes[nn].depth = 0; nodes[nn].cutdim = -1; nn++;
+    while (lo < hi) {
+      for (size_t x = lo; x < hi; x++) {
+        kd_node *nd = &nodes[x];
+        uint32_t count = nd->end - nd->start;
+        if ((uint64_t)nd->depth > deepest) deepest = (uint64_t)nd->depth;
+        if (count <= KD_TNS) { n_leaves++; continue; }
+        uint32_t pick = orc_seed_hash(seed ^ KD_SEED, t, nd->start * 31u + count);
+        uint32_t idx = kd_split(data, dim, stride, ids + nd->start, count, pick, mean, var, tmp, &nd->cutdim, &nd->cutval);
+        nd->left = (uint32_t)nn;
+        nodes[nn].start = nd->start; nodes[nn].end = nd->start + idx; nodes[nn].left = ORC_INVALID; nodes[nn].depth = nd->depth + 1; nodes[nn].cutdim = -1; nn++;
+        nodes[nn].start = nd->start + idx; nodes[nn].end = nd->end; nodes[nn].left = ORC_INVALID; nodes[nn].depth = nd->depth + 1; nodes[nn].cutdim = -1; nn++;
+      }
+      lo = hi; hi = nn;
+    }
+    n_nodes += nn;
+    /* conquer: every point walks its own path; below the merge level the points of the smaller child search the other child */
+    for (size_t pos = 0; pos < n; pos++) {
+      const uint32_t p = ids[pos];
+      const float *pv = data + (size_t)p * stride;
+      uint32_t x = 0;
+      while (nodes[x].left != ORC_INVALID) {
+        const uint32_t L = nodes[x].left, R = L + 1;
+        const int inL = pos < nodes[L].end;
+        const uint32_t numL = nodes[L].end - nodes[L].start, numR = nodes[R].end - nodes[R].start;
+        const int searchers_left = numL < numR;          /* :229-237 */
+        if ((unsigned)nodes[x].depth >= ml && inL == searchers_left) {
+          uint32_t y = inL ? R : L;
+          while (nodes[y].left != ORC_INVALID) y = pv[nodes[y].cutdim] < nodes[y].cutval ? nodes[y].left : nodes[y].left + 1;
+          for (uint32_t j = nodes[y].start; j < nodes[y].end; j++) {
+            const uint32_t q = ids[j];
+            float d = seq_fma(data + (size_t)q * stride, pv, dim, 0);
+            n_dist++;
+            uint64_t db = (uint64_t)f2u(d) << 32;
+            topl_insert(lists + (size_t)q * K, &lsize[q], K, db | ((uint64_t)p << 1), 1);
+            topl_insert(lists + (size_t)p * K, &lsize[p], K, db | ((uint64_t)q << 1), 1);
+          }
+        }
+        x = inL ? L : R;
+      }
+    }
+  }
+  for (size_t i = 0; i < n; i++) {
+    unsigned sz = lsize[i], ctr = 0;
+    uint64_t *l = lists + i * K;
+    for (unsigned j = 0; j < sz; j++) { knn[i * K + j] = (uint32_t)l[j] >> 1; if (knn_d) knn_d[i * K + j] = u2f((uint32_t)(l[j] >> 32)); }
+    while (sz < K) {                                       /* :413-424 */
+      uint32_t id = orc_seed_hash(seed ^ KD_SEED, (uint32_t)i, 1000u + ctr++) % (uint32_t)n;
+      int dup = 0;
+      for (unsigned j = 0; j < sz; j++) dup |= knn[i * K + j] == id;
+      if (dup) continue;
+      knn[i * K + sz] = id; if (knn_d) knn_d[i * K + sz] = INFINITY;
+      sz++;
+    }
+  }
+  if (info) { info[0] = n_dist; info[1] = n_nodes; info[2] = n_leaves; info[3] = deepest; }
+  free(lists); free(lsize); free(ids); free(tmp); free(mean); free(var); free(nodes);
   return 0;
 }
 

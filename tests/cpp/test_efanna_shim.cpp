@@ -63,6 +63,36 @@ int main(int argc, char **argv) {
   }
   double recall = (double)hit / (nq * K);
   bool same = res == res4 && res2 == res3;
+  // KD-tree initializer + RefineGraph (efanna_graph/tests/test_kdtree_graph.cpp; index_graph.cpp:235-262): the refined graph
+  // has the requested shape, lists no node in its own row, and is closer to the exact graph than the same NN-descent
+  // effort from a random start
+  {
+    efanna2e::IndexKDtree kd(dim, n, efanna2e::L2, nullptr);
+    efanna2e::Parameters kp;
+    kp.Set<unsigned>("K", 40); kp.Set<unsigned>("nTrees", 8); kp.Set<unsigned>("mLevel", 4);
+    kd.Build(n, base.data(), kp);
+    kd.Save((std::string(dir) + "/shim_kd.graph").c_str());
+    efanna2e::IndexGraph warm(dim, n, efanna2e::L2, (efanna2e::Index *)(&kd)), cold(dim, n, efanna2e::L2, (efanna2e::Index *)(&init)),
+        exact(dim, n, efanna2e::L2, (efanna2e::Index *)(&init));
+    efanna2e::Parameters rp;
+    rp.Set<unsigned>("K", 20); rp.Set<unsigned>("L", 40); rp.Set<unsigned>("iter", 2); rp.Set<unsigned>("S", 8); rp.Set<unsigned>("R", 30);
+    warm.RefineGraph(base.data(), rp);
+    cold.Build(n, base.data(), rp);
+    efanna2e::Parameters ep;
+    ep.Set<unsigned>("K", 20); ep.Set<unsigned>("exact", 1);
+    exact.Build(n, base.data(), ep);
+    auto overlap = [&](const efanna2e::IndexGraph &g) {
+      size_t h = 0;
+      for (size_t i = 0; i < 500; i++) {
+        std::set<unsigned> t(exact.Graph().begin() + i * 20, exact.Graph().begin() + (i + 1) * 20);
+        for (size_t j = 0; j < 20; j++) { h += t.count(g.Graph()[i * 20 + j]); if (g.Graph()[i * 20 + j] == i) return -1.0; }
+      }
+      return (double)h / (500 * 20);
+    };
+    double rw = overlap(warm), rc = overlap(cold);
+    printf("kd-tree init + RefineGraph: graph recall %.4f (random start, same effort: %.4f)\n", rw, rc);
+    if (!(warm.K() == 20 && warm.Graph().size() == n * 20 && rw > rc && rc >= 0)) return 1;
+  }
   bool threw = false;
   try { efanna2e::Parameters e; e.Get<unsigned>("missing"); } catch (std::invalid_argument &) { threw = true; }
   printf("recall@10 %.4f batch==single==reloaded %d width %u ep %u missing-key-throws %d\n", recall, (int)same, index.GetWidth(),

@@ -337,6 +337,35 @@ def orc_nndescent_batch(base, K, L, it, S, R_, mode, seed=1):
     return knn, d, info
 
 
+def orc_kdtree_graph(base, K, n_trees, m_level, seed=0):
+    """IndexKDtree::Build in the batch form the CUDA path computes -> (knn [n,K], d, info[4])"""
+    n, dim = base.shape
+    knn = np.empty((n, K), np.uint32)
+    d = np.empty((n, K), np.float32)
+    info = np.zeros(4, np.uint64)
+    lib = oracle()
+    lib.orc_kdtree_graph.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_uint, C.c_uint, C.c_uint, C.c_uint32, u32p,
+                                     C.c_void_p, C.c_void_p]
+    rc = lib.orc_kdtree_graph(base, n, dim, dim, K, n_trees, m_level, seed, knn, _vp(d), _vp(info))
+    assert rc == 0
+    return knn, d, info
+
+
+def orc_nndescent_refine(base, init_graph, K, L, it, S, R_, mode, seed=1):
+    """IndexGraph::RefineGraph in batch form: NN-descent whose pools start from init_graph [n, init_k]"""
+    n, dim = base.shape
+    g = np.ascontiguousarray(init_graph, np.uint32)
+    knn = np.empty((n, K), np.uint32)
+    d = np.empty((n, K), np.float32)
+    info = np.zeros(4, np.uint64)
+    lib = oracle()
+    lib.orc_nndescent_refine.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_uint, C.c_uint, C.c_uint, C.c_uint,
+                                         C.c_uint, C.c_uint32, C.c_int, u32p, C.c_uint, u32p, C.c_void_p, C.c_void_p]
+    rc = lib.orc_nndescent_refine(base, n, dim, dim, K, L, it, S, R_, seed, mode, g, g.shape[1], knn, _vp(d), _vp(info))
+    assert rc == 0
+    return knn, d, info
+
+
 def orc_nsg_search_qidx(base, graph, ep, q, qidx, K, L, mode, seed=0):
     n, dim = base.shape
     nq = q.shape[0]

@@ -109,3 +109,70 @@ def test_nndescent_argument_errors(B, H):
     ipx = B.Index(H, base, B.IP)
     with pytest.raises(B.B200AnnError):
         ipx.nndescent(5, 20, 1, 4, 4)
+
+
+@pytest.mark.parametrize("n,dim,K,L,it,S,Rr,k0", [
+    (3000, 32, 20, 40, 0, 8, 20, 25),      # InitializeGraph_Refine only
+    (3000, 32, 20, 40, 3, 8, 20, 40),      # init_k == L
+    (2500, 100, 10, 30, 2, 5, 12, 10),
+])
+def test_nndescent_refine_vs_oracle(B, H, n, dim, K, L, it, S, Rr, k0):
+    """b200ann_nndescent_refine (IndexGraph::RefineGraph, index_graph.cpp:203-262) == oracle batch form bit for bit. The
+    initializer's graph: a coarse NN-descent result with some rows spoiled (self, duplicates, padding, an empty row)."""
+    base = R.data_uniform(n, dim, 11)
+    ix = B.Index(H, base, B.L2)
+    g0, _ = ix.nndescent(k0, max(k0, 2 * S + 2), 1, S, Rr, seed=9)
+    g0 = g0.copy()
+    g0[5, :3] = 5                          # the node itself
+    g0[6, 1] = g0[6, 0]                    # a duplicate
+    g0[7, k0 // 2:] = R.INVALID            # padding
+    g0[8, :] = R.INVALID                   # nothing usable: the random start stays
+    knn, d, info = ix.nndescent_refine(g0, K, L, it, S, Rr, seed=5, want_dists=True)
+    oknn, od, oinfo = R.orc_nndescent_refine(base, g0, K, L, it, S, Rr, R.L2_SEQ_FMA, seed=5)
+    assert (knn == oknn).all()
+    assert (d.view(np.uint32) == od.view(np.uint32)).all()
+    assert info["dist_evals"] == int(oinfo[0])
+    # a refined graph is at least as good as its start, and better than the same effort from a random start
+    if it >= 2:
+        truth = ix.knn_graph(K)
+        rec = lambda g: np.mean([len(set(a.tolist()) & set(b.tolist())) for a, b in zip(g[:500], truth[:500])]) / K
+        cold, _ = ix.nndescent(K, L, it, S, Rr, seed=5)
+        assert rec(knn) >= rec(cold)
+
+
+@pytest.mark.parametrize("n,dim,K,nt,ml,kind", [
+    (5000, 32, 20, 4, 0, "u"),
+    (8000, 64, 30, 8, 4, "u"),
+    (3000, 100, 10, 3, 2, "u"),       # dim not a multiple of 32
+    (6000, 128, 24, 4, 3, "s"),       # integer-valued data: equal coordinates (the == class of the partition), distance ties
+    (40, 8, 5, 2, 0, "u"),            # barely deeper than a leaf; short rows get the pseudo-random fill
+    (3000, 16, 12, 2, 30, "u"),       # merge level below every leaf: nothing is conquered, all rows are fill
+])
+def test_kdtree_graph_vs_oracle(B, H, n, dim, K, nt, ml, kind):
+    """b200ann_kdtree_graph (efanna2e::IndexKDtree::Build, index_kdtree.cpp:279-435) == oracle.c orc_kdtree_graph, bit for
+    bit: ids, distances, number of distance evaluations, tree shape"""
+    base = R.data_uniform(n, dim, 11) if kind == "u" else R.data_sift_like(n, dim, 11)
+    ix = B.Index(H, base, B.L2)
+    knn, d, info = ix.kdtree_graph(K, nt, ml, seed=7, want_dists=True)
+    oknn, od, oinfo = R.orc_kdtree_graph(base, K, nt, ml, seed=7)
+    assert (knn == oknn).all()
+    assert (d.view(np.uint32) == od.view(np.uint32)).all()
+    assert info["dist_evals"] == int(oinfo[0]) and info["nodes"] == int(oinfo[1]) and info["leaves"] == int(oinfo[2])
+    assert info["deepest"] == int(oinfo[3])
+    assert (knn != np.arange(n, dtype=np.uint32)[:, None]).all() or ml >= 30   # a conquered row never lists itself
+    for i in range(0, n, max(1, n // 50)):
+        assert len(set(knn[i].tolist())) == K
+
+
+def test_kdtree_init_speeds_up_nndescent(B, H):
+    """the point of the initializer (IndexGraph::RefineGraph over IndexKDtree's graph): the same NN-descent effort started
+    from the KD-tree graph ends at a better graph than started from random ids"""
+    n, dim, K = 20000, 64, 20
+    base = R.data_sift_like(n, dim, 3)
+    ix = B.Index(H, base, B.L2)
+    truth = ix.knn_graph(K)
+    rec = lambda g: np.mean([len(set(a.tolist()) & set(b.tolist())) for a, b in zip(g[:1000], truth[:1000])]) / K
+    g0, _ = ix.kdtree_graph(K, 8, 4, seed=1)
+    cold, _ = ix.nndescent(K, 40, 2, 8, 20, seed=5)
+    warm, _ = ix.nndescent_refine(g0, K, 40, 2, 8, 20, seed=5)
+    assert rec(g0) > 0.1 and rec(warm) > rec(cold) + 0.05, (rec(g0), rec(cold), rec(warm))

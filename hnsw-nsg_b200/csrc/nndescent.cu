@@ -51,6 +51,13 @@ struct State {
   uint32_t *n_rnew, *n_rold;            // [n]
   uint32_t *lock_pool, *lock_rnew, *lock_rold;  // [n]
   const uint32_t *leaf_rank;            // [L+1]
+  // lock-free join (two passes over the same tiles): offers are counted per destination, then written to the
+  // destination's segment of one buffer, then merged by one warp per destination (merge_offers_kernel)
+  uint32_t *ocnt, *ofill;               // [n] offers per destination this iteration / write cursors
+  const unsigned long long *ooff;       // [n + 1] exclusive scan of ocnt
+  uint64_t *obuf;                       // [ooff[n]] offer keys, grouped by destination
+  ulonglong2 *rec;                      // MODE 3: (key, destination) records in arrival order, scattered by scatter_offers_kernel
+  unsigned long long *rec_cursor;       // MODE 3: records written
   const uint32_t *init_graph;           // [n, init_k] or NULL: RefineGraph (index_graph.cpp:203-262) - the pools start from these rows
   uint32_t init_k;
   unsigned long long *stats;            // {distance evaluations, offers queued, inserts done, next node}
@@ -434,6 +441,10 @@ __device__ __forceinline__ void tile_fma(const float *As, const float *Bs, float
   }
 }
 
+// MODE 0: offers are merged into the pools on the spot under per-destination locks (round 1). MODE 1 / 2: the lock-free
+// form, pass 1 counts the offers per destination, pass 2 writes them; the pools are not touched by either, so the
+// admission threshold is exactly the pool's largest distance at the start of the join (oracle.c: db <= oldmax).
+template <int MODE>
 __global__ void __launch_bounds__(JT, 3) join_kernel(State s, uint32_t cn_max) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float *As = reinterpret_cast<float *>(smem_raw);
@@ -560,12 +571,41 @@ __global__ void __launch_bounds__(JT, 3) join_kernel(State s, uint32_t cn_max) {
           src[2] = c[2] != NO_PAIR ? ids[p0] : 0u; src[3] = c[3] != NO_PAIR ? ids[p1] : 0u;
           const uint32_t dst = ids[pd];
           my_offer += (c[0] <= t) + (c[1] <= t) + (c[2] <= t) + (c[3] <= t);
-          uint32_t new_last;
-          uint32_t ins = pool_merge_dispatch(s.pool + (size_t)dst * s.L, s.psize + dst, s.lock_pool + dst, s.L, c, src, t,
-                                             lane, &new_last);
-          if (lane == 0) {
-            my_ins += ins;
-            if (new_last < t) thr[pd] = new_last;                    // tighter threshold for the next tiles
+          if (MODE == 0) {
+            uint32_t new_last;
+            uint32_t ins = pool_merge_dispatch(s.pool + (size_t)dst * s.L, s.psize + dst, s.lock_pool + dst, s.L, c, src, t,
+                                               lane, &new_last);
+            if (lane == 0) {
+              my_ins += ins;
+              if (new_last < t) thr[pd] = new_last;                  // tighter threshold for the next tiles
+            }
+          } else {
+            // this warp step's offers to dst: one atomic for all of them
+            uint32_t rank[4], total = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const unsigned m = __ballot_sync(0xffffffffu, c[k] <= t);
+              rank[k] = total + __popc(m & ((1u << lane) - 1));
+              total += __popc(m);
+            }
+            uint32_t base = 0;
+            if (MODE == 3) {  // one pass: count per destination and append (key, destination) records
+              unsigned long long cur = 0;
+              if (lane == 0) { atomicAdd(s.ocnt + dst, total); cur = atomicAdd(s.rec_cursor, (unsigned long long)total); }
+              cur = __shfl_sync(0xffffffffu, cur, 0);
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                if (c[k] <= t) s.rec[cur + rank[k]] = make_ulonglong2(((uint64_t)c[k] << 32) | ((uint64_t)src[k] << 1) | 1ull, dst);
+              continue;
+            }
+            if (lane == 0) base = atomicAdd((MODE == 1 ? s.ocnt : s.ofill) + dst, total);
+            if (MODE == 2) {
+              base = __shfl_sync(0xffffffffu, base, 0);
+              uint64_t *seg = s.obuf + s.ooff[dst] + base;
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                if (c[k] <= t) seg[rank[k]] = ((uint64_t)c[k] << 32) | ((uint64_t)src[k] << 1) | 1ull;
+            }
           }
         }
         __syncthreads();
@@ -573,9 +613,11 @@ __global__ void __launch_bounds__(JT, 3) join_kernel(State s, uint32_t cn_max) {
       }
     }
   }
-  if (my_dist) atomicAdd(s.stats + 0, my_dist);
-  if (my_offer) atomicAdd(s.stats + 1, my_offer);
-  if (my_ins) atomicAdd(s.stats + 2, my_ins);
+  if (MODE != 2) {  // the second pass of the lock-free form repeats the first one's work
+    if (my_dist) atomicAdd(s.stats + 0, my_dist);
+    if (my_offer) atomicAdd(s.stats + 1, my_offer);
+    if (my_ins) atomicAdd(s.stats + 2, my_ins);
+  }
 #ifdef NND_PROF
   if (tid == 0) {
     atomicAdd(s.stats + 8, sum_nn); atomicAdd(s.stats + 9, sum_no); atomicAdd(s.stats + 10, sum_tiles);
@@ -585,6 +627,114 @@ __global__ void __launch_bounds__(JT, 3) join_kernel(State s, uint32_t cn_max) {
     atomicAdd(s.stats + 6, (unsigned long long)t_drain);
   }
 #endif
+}
+
+// ---- lock-free join, step 3: one warp per destination merges its offers into its pool -------------------------
+// pool' = the L smallest keys of (pool + offers) with one entry per id; a pool entry wins over an offer of the same
+// id (same distance, its flag bit sorts first) - nhood::insert rejects an id that is already there (neighbor.h:61-66).
+constexpr int MG_WARPS = 4, MG_CAP = 1024, MG_CHUNK = 512;
+__device__ __forceinline__ void warp_bitonic_u64(uint64_t *a, uint32_t ns, int lane) {
+  for (uint32_t k = 2; k <= ns; k <<= 1)
+    for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+      for (uint32_t x = lane; x < (ns >> 1); x += 32) {
+        const uint32_t lo = ((x & ~(j - 1)) << 1) | (x & (j - 1)), hi = lo | j;
+        const uint64_t vl = a[lo], vh = a[hi];
+        const bool up = (lo & k) == 0;
+        if (up ? vh < vl : vl < vh) { a[lo] = vh; a[hi] = vl; }
+      }
+      __syncwarp();
+    }
+}
+__global__ void __launch_bounds__(MG_WARPS * 32) merge_offers_kernel(State s) {
+  __shared__ uint64_t buf_s[MG_WARPS][MG_CAP];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t d = blockIdx.x * MG_WARPS + warp;
+  if (d >= s.n) return;
+  const uint32_t m = s.ocnt[d];
+  if (m == 0) return;
+  uint64_t *buf = buf_s[warp];
+  uint64_t *pool = s.pool + (size_t)d * s.L;
+  uint32_t sz = s.psize[d];
+  for (uint32_t j = lane; j < sz; j += 32) buf[j] = pool[j];
+  __syncwarp();
+  const uint64_t *off = s.obuf + s.ooff[d];
+  for (uint32_t c0 = 0; c0 < m; c0 += MG_CHUNK) {
+    // offers of this chunk that can still enter (below the current L-th key when the pool is full)
+    const uint64_t bound = sz == s.L ? buf[s.L - 1] : EMPTY;
+    uint32_t cnt = sz;
+    for (uint32_t j0 = c0; j0 < c0 + MG_CHUNK && j0 < m; j0 += 32) {
+      const uint32_t j = j0 + lane;
+      const uint64_t key = (j < m && j < c0 + MG_CHUNK) ? off[j] : EMPTY;
+      const bool keep = key < bound;
+      const unsigned mk = __ballot_sync(0xffffffffu, keep);
+      if (keep) buf[cnt + __popc(mk & ((1u << lane) - 1))] = key;
+      cnt += __popc(mk);
+    }
+    if (cnt == sz) continue;
+    uint32_t ns = 64;
+    while (ns < cnt) ns <<= 1;
+    for (uint32_t j = cnt + lane; j < ns; j += 32) buf[j] = EMPTY;
+    __syncwarp();
+    warp_bitonic_u64(buf, ns, lane);
+    // one entry per id (the first of equal ids: the pool's own entry, flag 0, sorts before an offer), the L smallest
+    uint32_t out = 0;
+    for (uint32_t j0 = 0; j0 < cnt && out < s.L; j0 += 32) {
+      const uint32_t j = j0 + lane;
+      uint64_t key = EMPTY;
+      bool ok = false;
+      if (j < cnt) { key = buf[j]; ok = !(j > 0 && (buf[j - 1] >> 1) == (key >> 1)); }
+      __syncwarp();
+      const unsigned mk = __ballot_sync(0xffffffffu, ok);
+      const uint32_t pos = out + __popc(mk & ((1u << lane) - 1));
+      if (ok && pos < s.L) buf[pos] = key;
+      out += __popc(mk);
+      __syncwarp();
+    }
+    sz = out < s.L ? out : s.L;
+  }
+  for (uint32_t j = lane; j < s.L; j += 32) pool[j] = j < sz ? buf[j] : EMPTY;
+  if (lane == 0) s.psize[d] = sz;
+}
+// upper bound of the pairs one join evaluates (each pair makes at most two offers): sum over the nodes' sample lists
+__global__ void join_bound_kernel(State s, unsigned long long *out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned long long pairs = 0;
+  if (i < s.n) {
+    const unsigned long long nn = s.n_fnew[i] + s.n_rnew[i];
+    unsigned long long no = s.n_fold[i] + s.n_rold[i];
+    if (no > 2ull * s.R) no = 2ull * s.R;
+    pairs = nn * (nn - 1) / 2 + nn * no;
+  }
+  for (int o = 16; o; o >>= 1) pairs += __shfl_xor_sync(0xffffffffu, pairs, o);
+  if ((threadIdx.x & 31) == 0 && pairs) atomicAdd(out, pairs);
+}
+// records (key, destination) -> the destination's segment of obuf
+__global__ void scatter_offers_kernel(State s, unsigned long long total) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  for (; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const ulonglong2 r = s.rec[i];
+    const uint32_t d = (uint32_t)r.y;
+    s.obuf[s.ooff[d] + atomicAdd(s.ofill + d, 1u)] = r.x;
+  }
+}
+// exclusive scan of cnt[0..n) into 64-bit offsets, one block
+__global__ void scan_u32_u64_kernel(const uint32_t *cnt, uint32_t n, unsigned long long *off) {
+  __shared__ unsigned long long part[1024];
+  const uint32_t tid = threadIdx.x, nt = blockDim.x;
+  const uint32_t per = (n + nt - 1) / nt;
+  const uint32_t b = min(n, tid * per), e = min(n, b + per);
+  unsigned long long sum = 0;
+  for (uint32_t i = b; i < e; i++) sum += cnt[i];
+  part[tid] = sum;
+  __syncthreads();
+  if (tid == 0) {
+    unsigned long long run = 0;
+    for (uint32_t t = 0; t < nt; t++) { unsigned long long v = part[t]; part[t] = run; run += v; }
+    off[n] = run;
+  }
+  __syncthreads();
+  sum = part[tid];
+  for (uint32_t i = b; i < e; i++) { off[i] = sum; sum += cnt[i]; }
 }
 
 // ---- update (:34-120) ------------------------------------------------------------------------------------
@@ -926,9 +1076,23 @@ int nndescent_launch(b200ann_handle *h, const b200ann_index *ix, size_t K, size_
   }
   const uint32_t cn_max = (uint32_t)(std::max(2 * S, S + R) + 2 * R);
   const size_t smem = 2 * (size_t)TILE * ROWF * sizeof(float) + (size_t)TILE * DROW * sizeof(uint32_t) + 2 * (size_t)cn_max * sizeof(uint32_t);
-  CU_CHECK(h, cudaFuncSetAttribute(join_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  CU_CHECK(h, cudaFuncSetAttribute(join_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  CU_CHECK(h, cudaFuncSetAttribute(join_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  CU_CHECK(h, cudaFuncSetAttribute(join_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  CU_CHECK(h, cudaFuncSetAttribute(join_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int occ = 0;
-  CU_CHECK(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, join_kernel, JT, smem));
+  CU_CHECK(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, join_kernel<1>, JT, smem));
+  // B200ANN_NND_LOCKFREE=0: the round-1 join (offers merged under per-destination locks), for A/B runs
+  // 2 (default): one tile pass + record scatter; 1: two tile passes (count, then write), no record buffer
+  int lockfree = 2;
+  if (const char *e = getenv("B200ANN_NND_LOCKFREE")) lockfree = atoi(e);
+  DevBuf<unsigned long long> cursors;
+  CU_CHECK(h, cursors.alloc(2, st));
+  DevBuf<uint32_t> ocnt;
+  DevBuf<unsigned long long> ooff;
+  CU_CHECK(h, ocnt.alloc(2 * n, st));
+  CU_CHECK(h, ooff.alloc(n + 1, st));
+  s.ocnt = ocnt.p; s.ofill = ocnt.p + n; s.ooff = ooff.p;
   if (occ < 1) return set_err(h, B200ANN_ERR_ARG, "nndescent: sample lists do not fit in shared memory (S, R too large)");
   const unsigned jgrid = (unsigned)std::min<size_t>((size_t)h->sm_count * occ, n);
   struct Events {  // destroyed on every return path
@@ -941,7 +1105,46 @@ int nndescent_launch(b200ann_handle *h, const b200ann_index *ix, size_t K, size_
   for (size_t it = 0; it < iter; ++it) {
     cudaMemsetAsync(stats.p + 3, 0, sizeof(unsigned long long), st);
     cudaEventRecord(e0, st);
-    join_kernel<<<jgrid, JT, smem, st>>>(s, cn_max);
+    if (!lockfree) {
+      join_kernel<0><<<jgrid, JT, smem, st>>>(s, cn_max);
+      h->launches++;
+    } else if (lockfree == 2) {
+      // one tile pass: offers go to a record buffer sized by the pair bound, then to their destinations' segments
+      cudaMemsetAsync(ocnt.p, 0, 2 * n * sizeof(uint32_t), st);
+      cudaMemsetAsync(cursors.p, 0, 2 * sizeof(unsigned long long), st);
+      join_bound_kernel<<<nb, TB, 0, st>>>(s, cursors.p + 1);
+      unsigned long long bound = 0;
+      CU_CHECK(h, cudaMemcpyAsync(&bound, cursors.p + 1, sizeof bound, cudaMemcpyDeviceToHost, st));
+      CU_CHECK(h, cudaStreamSynchronize(st));
+      DevBuf<ulonglong2> rec;
+      CU_CHECK(h, rec.alloc(2 * bound + 1, st));
+      s.rec = rec.p; s.rec_cursor = cursors.p;
+      join_kernel<3><<<jgrid, JT, smem, st>>>(s, cn_max);
+      scan_u32_u64_kernel<<<1, 1024, 0, st>>>(s.ocnt, (uint32_t)n, ooff.p);
+      unsigned long long total = 0;
+      CU_CHECK(h, cudaMemcpyAsync(&total, ooff.p + n, sizeof total, cudaMemcpyDeviceToHost, st));
+      CU_CHECK(h, cudaStreamSynchronize(st));
+      DevBuf<uint64_t> obuf;
+      CU_CHECK(h, obuf.alloc(total ? total : 1, st));
+      s.obuf = obuf.p;
+      if (total) scatter_offers_kernel<<<h->sm_count * 16, 256, 0, st>>>(s, total);
+      merge_offers_kernel<<<(unsigned)((n + MG_WARPS - 1) / MG_WARPS), MG_WARPS * 32, 0, st>>>(s);
+      h->launches += 5;
+    } else {
+      cudaMemsetAsync(ocnt.p, 0, 2 * n * sizeof(uint32_t), st);
+      join_kernel<1><<<jgrid, JT, smem, st>>>(s, cn_max);
+      scan_u32_u64_kernel<<<1, 1024, 0, st>>>(s.ocnt, (uint32_t)n, ooff.p);
+      unsigned long long total = 0;
+      CU_CHECK(h, cudaMemcpyAsync(&total, ooff.p + n, sizeof total, cudaMemcpyDeviceToHost, st));
+      CU_CHECK(h, cudaStreamSynchronize(st));
+      DevBuf<uint64_t> obuf;
+      CU_CHECK(h, obuf.alloc(total ? total : 1, st));
+      s.obuf = obuf.p;
+      cudaMemsetAsync(stats.p + 3, 0, sizeof(unsigned long long), st);
+      join_kernel<2><<<jgrid, JT, smem, st>>>(s, cn_max);
+      merge_offers_kernel<<<(unsigned)((n + MG_WARPS - 1) / MG_WARPS), MG_WARPS * 32, 0, st>>>(s);
+      h->launches += 4;
+    }
     cudaEventRecord(e1, st);
     update_a_kernel<<<nb, TB, 0, st>>>(s);
     fill_u64_kernel<<<h->sm_count * 8, 256, 0, st>>>(rnew.p, n * R, EMPTY);
@@ -949,7 +1152,7 @@ int nndescent_launch(b200ann_handle *h, const b200ann_index *ix, size_t K, size_
     const uint32_t seed_new = seed + (uint32_t)(2 * it + 1) * 0x9E3779B1U, seed_old = seed + (uint32_t)(2 * it + 2) * 0x9E3779B1U;
     update_b_kernel<<<(unsigned)((n * 32 + 255) / 256), 256, 0, st>>>(s, seed_new, seed_old);
     cudaEventRecord(e2, st);
-    h->launches += 5;
+    h->launches += 4;
     CU_CHECK(h, cudaEventSynchronize(e2));
     float a = 0.f, b = 0.f;
     cudaEventElapsedTime(&a, e0, e1); cudaEventElapsedTime(&b, e1, e2);

@@ -44,6 +44,7 @@ def test_nndescent_vs_oracle_batch_form(B, H, n, dim, K, L, it, S, Rr, kind):
     assert (knn == oknn).all()
     assert (d.view(np.uint32) == od.view(np.uint32)).all()
     assert info["dist_evals"] == int(oinfo[0])          # same pairs evaluated
+    assert info["offers"] == int(oinfo[1])              # same offers admitted (threshold = the pool's largest at the join's start)
     assert info["iterations"] == it
 
 

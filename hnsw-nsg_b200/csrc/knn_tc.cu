@@ -171,6 +171,8 @@ struct SweepParams {
   uint32_t Kp, cap, rows_pad;
   float *cand_d; uint32_t *cand_i;    // [splits, rows_pad, cap]
   uint32_t *cand_n; float *cand_tau;  // [splits, rows_pad]
+  uint32_t tile_step;                 // 1: every tile of the split; s: every s-th tile (the sampling pass)
+  const float *tau0;                  // [rows_pad] or NULL: start threshold per row (from the sampling pass)
   unsigned long long *prof;           // optional [8]: per-epilogue-warp cycle sums {wait tmem_full, process, compaction, total}, compactions
 };
 
@@ -379,7 +381,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap mA_hi, const __grid_constant__ 
           tma_load_2d(sA + b * A_BYTES, b < p.nkb ? &mA_hi : &mA_lo, (int)((b % p.nkb) * BK), (int)m0, a_full);
       }
       uint32_t stage = 0, phase = 0;
-      for (uint32_t tile = tile_begin; tile < tile_end; tile++) {
+      for (uint32_t tile = tile_begin; tile < tile_end; tile += p.tile_step) {
         const int n0 = (int)(tile * BN);
         for (uint32_t t = 0; t < T; t++) {
           const uint32_t seg = t / p.nkb, kb = t % p.nkb;
@@ -396,7 +398,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap mA_hi, const __grid_constant__ 
     // ===== MMA issuer =====
     if (p.a_resident) mbar_wait(a_full, 0);
     uint32_t stage = 0, phase = 0, ti = 0;
-    for (uint32_t tile = tile_begin; tile < tile_end; tile++, ti++) {
+    for (uint32_t tile = tile_begin; tile < tile_end; tile += p.tile_step, ti++) {
       const uint32_t as = ti & 1u, aphase = (ti >> 1) & 1u;
       mbar_wait_relaxed(&tmem_empty[as], aphase ^ 1u);
       tc_fence_after();
@@ -437,7 +439,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap mA_hi, const __grid_constant__ 
     long long pf_wait = 0, pf_proc = 0, pf_comp = 0, pf_t0 = clock64();
     uint32_t pf_ncomp = 0;
 
-    if (hf == 0) { cnt_s[rowi] = 0; tau_s[rowi] = row_valid ? INFINITY : -INFINITY; }
+    if (hf == 0) { cnt_s[rowi] = 0; tau_s[rowi] = row_valid ? (p.tau0 ? p.tau0[blockIdx.x * BM + rowi] : INFINITY) : -INFINITY; }
     asm volatile("bar.sync 1, 256;" ::: "memory");
     float tau = tau_s[rowi];
 
@@ -467,7 +469,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap mA_hi, const __grid_constant__ 
     };
 
     uint32_t ti = 0;
-    for (uint32_t tile = tile_begin; tile < tile_end; tile++, ti++) {
+    for (uint32_t tile = tile_begin; tile < tile_end; tile += p.tile_step, ti++) {
       const uint32_t as = ti & 1u, aphase = (ti >> 1) & 1u;
       const uint32_t n0 = tile * BN;
       {
@@ -858,8 +860,22 @@ int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t n
   const uint32_t P = next_pow2(splits * Kp);
   const uint32_t rows_pad = mtiles0 * tc::BM;
 
-  DevBuf<float> cand_d, cand_tau; DevBuf<uint32_t> cand_i, cand_n, fail; DevBuf<unsigned long long> ncand;
+  // start thresholds from a sampled pre-pass (B200ANN_KNN_SAMPLE=0 turns it off; =s sets the tile stride): worth it
+  // when the base is large against the shortlist. sample_m = 2.25 * Kp / step + 8: the sample_m-th key of a 1/step
+  // sample sits ~4 standard deviations above the Kp-th key of the whole base.
+  uint32_t sample_step = ntiles >= 2048 ? 16u : 0u, sample_m = 0;
+  if (const char *e = getenv("B200ANN_KNN_SAMPLE")) sample_step = (uint32_t)atoi(e);
+  if (sample_step < 2 || ntiles < 8 * sample_step) sample_step = 0;
+  if (sample_step) {
+    double margin = 2.25;
+    if (const char *e = getenv("B200ANN_KNN_SAMPLE_MARGIN")) margin = atof(e);
+    sample_m = (uint32_t)(margin * Kp / sample_step) + 8;
+    if (sample_m < 16) sample_m = 16;
+    if (sample_m >= Kp) sample_step = 0;
+  }
+  DevBuf<float> cand_d, cand_tau, tau0; DevBuf<uint32_t> cand_i, cand_n, fail; DevBuf<unsigned long long> ncand;
   const size_t slots = (size_t)splits * rows_pad;
+  if (sample_step) CU_CHECK(h, tau0.alloc(rows_pad, h->stream));
   CU_CHECK(h, cand_d.alloc(slots * cap, h->stream));
   CU_CHECK(h, cand_i.alloc(slots * cap, h->stream));
   CU_CHECK(h, cand_n.alloc(slots, h->stream));
@@ -893,6 +909,18 @@ int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t n
     sp.exclude_self = exclude_self; sp.self_base = self_base; sp.Kp = Kp; sp.cap = cap; sp.rows_pad = rows_pad;
     sp.cand_d = cand_d.p; sp.cand_i = cand_i.p; sp.cand_n = cand_n.p; sp.cand_tau = cand_tau.p;
     sp.prof = want_prof ? prof.p : nullptr;
+    sp.tile_step = 1; sp.tau0 = nullptr;
+    if (sample_step) {
+      // sampling pass: every sample_step-th tile, keep the sample_m smallest keys per row; the sample_m-th of the
+      // sample is (with margin) above the Kp-th of the whole base, so the full pass starts from it instead of from
+      // +inf and appends ~3x fewer hits. A row for which it turns out too tight fails its proof and is recomputed.
+      tc::SweepParams ss = sp;
+      ss.tile_step = sample_step; ss.Kp = sample_m; ss.tiles_per_split = ntiles; ss.prof = nullptr;
+      tc::sweep_kernel<<<dim3(mtiles, 1), tc::NTHREADS, sweep_smem, h->stream>>>(mA_hi, mA_lo, mB_hi, mB_lo, ss);
+      h->launches++;
+      CU_CHECK(h, cudaMemcpyAsync(tau0.p, cand_tau.p, (size_t)rows_pad * sizeof(float), cudaMemcpyDeviceToDevice, h->stream));
+      sp.tau0 = tau0.p;
+    }
     tc::sweep_kernel<<<dim3(mtiles, splits), tc::NTHREADS, sweep_smem, h->stream>>>(mA_hi, mA_lo, mB_hi, mB_lo, sp);
     h->launches++;
     CU_CHECK(h, cudaGetLastError());

@@ -117,3 +117,35 @@ def test_knn_graph_rows_union_equals_whole(B, H, mode, n, dim, K):
         assert (np.concatenate(parts) == whole).all()
     finally:
         H.set_knn_mode(0)
+
+
+@pytest.mark.parametrize("step,kind", [("4", "sift"), ("8", "sorted")])
+def test_knn_tc_sampled_start_threshold(B, step, kind):
+    """the sweep's start thresholds from a sampled pre-pass (every step-th tile): results stay exact - the same rows as
+    without sampling and as the SIMT kernel - and only a handful of rows fail their proof. "sorted": rows ordered
+    by their first coordinate, the adversarial layout for a sample by position (neighbours sit in the same tiles)."""
+    import os
+    h = B.Handle(0)
+    n = 60000
+    base = R.data_sift_shape(n, 128, 5)
+    if kind == "sorted":
+        base = np.ascontiguousarray(base[np.argsort(base[:, 0], kind="stable")])
+    ix = B.Index(h, base, 0)
+    h.set_knn_mode(2)
+    old = os.environ.get("B200ANN_KNN_SAMPLE")
+    try:
+        os.environ["B200ANN_KNN_SAMPLE"] = "0"
+        plain = ix.knn_graph(40)
+        f0 = h.knn_last_stats["fallback_rows"]
+        os.environ["B200ANN_KNN_SAMPLE"] = step
+        sampled = ix.knn_graph(40)
+        st = h.knn_last_stats
+    finally:
+        if old is None:
+            os.environ.pop("B200ANN_KNN_SAMPLE", None)
+        else:
+            os.environ["B200ANN_KNN_SAMPLE"] = old
+    assert (sampled == plain).all()
+    assert st["rows"] == n and st["fallback_rows"] <= f0 + n // 100, (st, f0)
+    ix.close()
+    h.close()

@@ -57,7 +57,8 @@ struct State {
   const unsigned long long *ooff;       // [n + 1] exclusive scan of ocnt
   uint64_t *obuf;                       // [ooff[n]] offer keys, grouped by destination
   ulonglong2 *rec;                      // MODE 3: (key, destination) records in arrival order, scattered by scatter_offers_kernel
-  unsigned long long *rec_cursor;       // MODE 3: records written
+  unsigned long long *rec_cursor;       // MODE 3: records written (counts past rec_cap too: the host re-runs the pass then)
+  unsigned long long rec_cap;           // MODE 3: records the buffer holds
   const uint32_t *init_graph;           // [n, init_k] or NULL: RefineGraph (index_graph.cpp:203-262) - the pools start from these rows
   uint32_t init_k;
   unsigned long long *stats;            // {distance evaluations, offers queued, inserts done, next node}
@@ -595,7 +596,7 @@ __global__ void __launch_bounds__(JT, 3) join_kernel(State s, uint32_t cn_max) {
               cur = __shfl_sync(0xffffffffu, cur, 0);
 #pragma unroll
               for (int k = 0; k < 4; ++k)
-                if (c[k] <= t) s.rec[cur + rank[k]] = make_ulonglong2(((uint64_t)c[k] << 32) | ((uint64_t)src[k] << 1) | 1ull, dst);
+                if (c[k] <= t && cur + rank[k] < s.rec_cap) s.rec[cur + rank[k]] = make_ulonglong2(((uint64_t)c[k] << 32) | ((uint64_t)src[k] << 1) | 1ull, dst);
               continue;
             }
             if (lane == 0) base = atomicAdd((MODE == 1 ? s.ocnt : s.ofill) + dst, total);
@@ -1088,6 +1089,11 @@ int nndescent_launch(b200ann_handle *h, const b200ann_index *ix, size_t K, size_
   if (const char *e = getenv("B200ANN_NND_LOCKFREE")) lockfree = atoi(e);
   DevBuf<unsigned long long> cursors;
   CU_CHECK(h, cursors.alloc(2, st));
+  DevBuf<ulonglong2> rec;      // offer records and per-destination segments, kept across the iterations
+  DevBuf<uint64_t> obuf;
+  unsigned long long rec_cap = 0, obuf_cap = 0;
+  DevBuf<unsigned long long> stats_keep;
+  CU_CHECK(h, stats_keep.alloc(3, st));
   DevBuf<uint32_t> ocnt;
   DevBuf<unsigned long long> ooff;
   CU_CHECK(h, ocnt.alloc(2 * n, st));
@@ -1116,20 +1122,43 @@ int nndescent_launch(b200ann_handle *h, const b200ann_index *ix, size_t K, size_
       unsigned long long bound = 0;
       CU_CHECK(h, cudaMemcpyAsync(&bound, cursors.p + 1, sizeof bound, cudaMemcpyDeviceToHost, st));
       CU_CHECK(h, cudaStreamSynchronize(st));
-      DevBuf<ulonglong2> rec;
-      CU_CHECK(h, rec.alloc(2 * bound + 1, st));
-      s.rec = rec.p; s.rec_cursor = cursors.p;
-      join_kernel<3><<<jgrid, JT, smem, st>>>(s, cn_max);
-      scan_u32_u64_kernel<<<1, 1024, 0, st>>>(s.ocnt, (uint32_t)n, ooff.p);
+      // The record buffer is sized by the pair bound once (first iteration: nearly every pair is an offer); later
+      // bounds overshoot the offers 3-6x, and growing a multi-GB buffer costs more than the join (0.9 s measured at
+      // 1M rows), so later iterations keep the buffer and re-run the pass in the rare case the records overflow it -
+      // the pass only reads the graph, so a re-run writes the same records.
+      if (!rec_cap) {
+        rec_cap = (2 * bound + 1) + (2 * bound + 1) / 4;
+        if (const char *e = getenv("B200ANN_NND_REC_CAP")) rec_cap = std::max(1ll, atoll(e));  // tests: force the re-run path
+        CU_CHECK(h, rec.alloc(rec_cap, st));
+      }
+      s.rec = rec.p; s.rec_cursor = cursors.p; s.rec_cap = rec_cap;
       unsigned long long total = 0;
-      CU_CHECK(h, cudaMemcpyAsync(&total, ooff.p + n, sizeof total, cudaMemcpyDeviceToHost, st));
-      CU_CHECK(h, cudaStreamSynchronize(st));
-      DevBuf<uint64_t> obuf;
-      CU_CHECK(h, obuf.alloc(total ? total : 1, st));
+      for (;;) {
+        cudaMemcpyAsync(stats_keep.p, stats.p, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToDevice, st);
+        join_kernel<3><<<jgrid, JT, smem, st>>>(s, cn_max);
+        scan_u32_u64_kernel<<<1, 1024, 0, st>>>(s.ocnt, (uint32_t)n, ooff.p);
+        CU_CHECK(h, cudaMemcpyAsync(&total, ooff.p + n, sizeof total, cudaMemcpyDeviceToHost, st));
+        CU_CHECK(h, cudaStreamSynchronize(st));
+        h->launches += 2;
+        if (total <= rec_cap) break;
+        cudaFreeAsync(rec.p, st); rec.p = nullptr;
+        rec_cap = total + total / 4;
+        CU_CHECK(h, rec.alloc(rec_cap, st));
+        s.rec = rec.p; s.rec_cap = rec_cap;
+        cudaMemcpyAsync(stats.p, stats_keep.p, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToDevice, st);
+        cudaMemsetAsync(ocnt.p, 0, 2 * n * sizeof(uint32_t), st);
+        cudaMemsetAsync(cursors.p, 0, sizeof(unsigned long long), st);
+        cudaMemsetAsync(stats.p + 3, 0, sizeof(unsigned long long), st);   // the tile pass's work counter
+      }
+      if (total + 1 > obuf_cap) {
+        if (obuf.p) { cudaFreeAsync(obuf.p, st); obuf.p = nullptr; }
+        obuf_cap = (total + 1) + (total + 1) / 4;
+        CU_CHECK(h, obuf.alloc(obuf_cap, st));
+      }
       s.obuf = obuf.p;
       if (total) scatter_offers_kernel<<<h->sm_count * 16, 256, 0, st>>>(s, total);
       merge_offers_kernel<<<(unsigned)((n + MG_WARPS - 1) / MG_WARPS), MG_WARPS * 32, 0, st>>>(s);
-      h->launches += 5;
+      h->launches += 3;
     } else {
       cudaMemsetAsync(ocnt.p, 0, 2 * n * sizeof(uint32_t), st);
       join_kernel<1><<<jgrid, JT, smem, st>>>(s, cn_max);

@@ -48,6 +48,18 @@ def test_nndescent_vs_oracle_batch_form(B, H, n, dim, K, L, it, S, Rr, kind):
     assert info["iterations"] == it
 
 
+def test_nndescent_record_buffer_overflow_reruns_the_pass(B, H, monkeypatch):
+    """The offer-record buffer is sized once and kept; an iteration whose offers do not fit re-runs its tile pass with
+    a larger buffer. Forced here with a buffer of 1000 records: graph, distances and counters equal the oracle's."""
+    monkeypatch.setenv("B200ANN_NND_REC_CAP", "1000")
+    base = R.data_uniform(3000, 32, 11)
+    ix = B.Index(H, base, B.L2)
+    knn, d, info = ix.nndescent(20, 40, 4, 8, 20, seed=5, want_dists=True)
+    oknn, od, oinfo = R.orc_nndescent_batch(base, 20, 40, 4, 8, 20, R.L2_SEQ_FMA, seed=5)
+    assert (knn == oknn).all() and (d.view(np.uint32) == od.view(np.uint32)).all()
+    assert info["dist_evals"] == int(oinfo[0]) and info["offers"] == int(oinfo[1])
+
+
 def test_nndescent_deterministic_across_runs(B, H):
     base = R.data_sift_like(5000, 48, 3)
     ix = B.Index(H, base, B.L2)

@@ -150,6 +150,52 @@ struct Beam {
     return false;
   }
 
+  // The same test for a whole adjacency row (lane = entry, all 32 lanes call it): plain loads, and a new id claims
+  // its slot by store + read-back - the table belongs to this warp alone, so of the lanes that store to one slot in
+  // the same round exactly one reads its own entry back and the others probe on. Shared-memory atomics cost the
+  // insertion beam ~1500 cycles per hop (32 tests, most of them for ids already in the set). Two lanes with the
+  // SAME id would both report "new": the caller passes each id once (load_row).
+  __device__ __forceinline__ bool test_and_set_row(uint32_t id, bool valid) {
+    bool seen = false, done = !valid;
+    if (p.vis16) {
+      const uint32_t x = (id * 0x9E3779B1u) & nmask;
+      const uint32_t s = x >> rbits;
+      const uint32_t tag = (x & rmask) << 3;
+      volatile unsigned short *t16 = reinterpret_cast<volatile unsigned short *>(tab);  // no store -> load forwarding
+#pragma unroll 1
+      for (uint32_t pr = 0; pr < (uint32_t)PROBES; pr++) {
+        const uint32_t sl = (s + pr) & smask;
+        const unsigned short me = (unsigned short)(tag | pr);
+        const unsigned short e = done ? (unsigned short)0 : t16[sl];
+        if (!done && e == me) { seen = true; done = true; }
+        const bool claim = !done && e == 0xFFFFu;
+        if (claim) t16[sl] = me;
+        __syncwarp();
+        if (claim && t16[sl] == me) done = true;
+        if (__all_sync(0xffffffffu, done)) break;
+      }
+      if (!done) t16[s] = (unsigned short)tag;  // probe sequence full: forget the home slot's entry
+      __syncwarp();
+      return seen;
+    }
+    const uint32_t s = slot(id);
+    volatile uint32_t *vt = tab;
+#pragma unroll 1
+    for (int pr = 0; pr < PROBES; pr++) {
+      const uint32_t sl = (s + pr) & hmask;
+      const uint32_t e = done ? 0u : vt[sl];
+      if (!done && e == id) { seen = true; done = true; }
+      const bool claim = !done && e == INVALID_ID;
+      if (claim) vt[sl] = id;
+      __syncwarp();
+      if (claim && vt[sl] == id) done = true;
+      if (__all_sync(0xffffffffu, done)) break;
+    }
+    if (!done) vt[s] = id;
+    __syncwarp();
+    return seen;
+  }
+
   __device__ __forceinline__ void load_query(const float *qv) {
     if constexpr (IP == MET_U8) {  // qv = p.dim unsigned bytes (any alignment); bytes past dim read as 0
       const unsigned char *qb = reinterpret_cast<const unsigned char *>(qv);
@@ -225,14 +271,22 @@ struct Beam {
   }
 
   // copy an adjacency row into cand_i; with `filter`, drop ids already in the visited set.
-  __device__ __forceinline__ uint32_t load_row(const uint32_t *row, uint32_t rowlen, uint32_t limit, bool filter) {
+  // have_pre: the caller already holds the row's first 32 entries (pre = entry `lane`, see expand_all)
+  __device__ __forceinline__ uint32_t load_row(const uint32_t *row, uint32_t rowlen, uint32_t limit, bool filter,
+                                               bool have_pre = false, uint32_t pre = INVALID_ID) {
     uint32_t m = 0;
     __syncwarp();
     for (uint32_t j0 = 0; j0 < rowlen; j0 += 32) {
       uint32_t j = j0 + lane;
-      uint32_t id = (j < rowlen && j < limit) ? ld_adj(row + j) : INVALID_ID;
+      uint32_t id = (j < rowlen && j < limit) ? ((have_pre && j0 == 0) ? pre : ld_adj(row + j)) : INVALID_ID;
       bool valid = id != INVALID_ID;
-      if (valid && filter) valid = id != never && !test_and_set(id);
+      if (filter) {
+        valid = valid && id != never;
+        // a row listing a node twice: the first copy stands (test_and_set_row would call both new)
+        const unsigned same = __match_any_sync(0xffffffffu, id);   // every lane takes part: no short-circuit
+        valid = valid && (uint32_t)__ffs(same) - 1u == (uint32_t)lane;
+        valid = !test_and_set_row(id, valid) && valid;
+      }
       unsigned mask = __ballot_sync(0xffffffffu, valid);
       if (valid) cand_i[m + __popc(mask & ((1u << lane) - 1))] = id;
       m += __popc(mask);
@@ -273,6 +327,93 @@ struct Beam {
     if (np < cap) np++;
     __syncwarp();
     return pos;
+  }
+
+  // HNSW pools of up to 32 * MCH entries: one chunk of candidates (one per lane) merged into the pool in ONE pass,
+  // with the result the sequential loop above produces candidate by candidate (lane order = arrival order):
+  //  * candidate c is accepted iff  #{pool: dist <= d_c} + #{earlier candidates that are no duplicates: dist <= d_c}
+  //    < cap. (Sequential rule: accepted iff the pool is not full or d_c < the pool's largest distance, i.e. iff fewer
+  //    than cap of the current entries have dist <= d_c; the current entries are the cap smallest of pool + accepted,
+  //    and a candidate rejected earlier with dist <= d_c implies c is rejected too, so "accepted earlier" can be
+  //    replaced by "earlier".) A candidate equal to a pool entry (the visited set forgot it) changes nothing.
+  //  * the new pool is the cap (distance, id)-smallest of pool + accepted: an accepted candidate lands at
+  //    (#pool entries before it) + (#accepted before it); the pool entries fill the other positions in order.
+  // Every lane searches its own candidate (three levels of independent probes: strides 32, 4, 1); the pool sits in
+  // registers (entry i * 32 + lane) and every entry moves up by the number of accepted candidates before it. A
+  // chunk costs about the same however many candidates it inserts (the sequential form re-scans and shifts the
+  // pool per candidate: 3500 cycles per hop at ef_construction 200, where 7-10 of a hop's ~13 evaluated rows pass).
+  // Returns the smallest position written (BIGPOS if none).
+  static constexpr int MCH = 8;
+  __device__ __forceinline__ int merge_chunk(float d, uint32_t id, bool valid) {
+    const uint32_t np0 = np;
+    const bool pass = valid && (np0 < cap || d < pool_d[np0 - 1]);
+    const unsigned mask = __ballot_sync(0xffffffffu, pass);
+    if (!mask) return BIGPOS;
+    float pd[MCH]; uint32_t pi[MCH];
+    const int nchk = (int)((np0 + 31) >> 5);
+#pragma unroll
+    for (int i = 0; i < MCH; i++) {
+      const uint32_t j = (uint32_t)i * 32u + lane;
+      const bool in = i < nchk && j < np0;
+      pd[i] = in ? pool_d[j] : INFINITY;
+      pi[i] = in ? pool_i[j] : 0u;
+    }
+    uint32_t lex = 0, le = 0;   // pool entries (distance, id)-before mine / with distance <= mine
+    bool dup = false;
+    if (pass) {
+      uint32_t c = 0;           // entries with distance < d: whole 32-blocks, then 4-blocks, then single entries
+#pragma unroll
+      for (int t = 1; t < MCH; t++) c += ((uint32_t)t * 32u - 1u < np0 && pool_d[t * 32 - 1] < d) ? 1u : 0u;
+      uint32_t base = c * 32u;
+      c = 0;
+#pragma unroll
+      for (int t = 1; t < 8; t++) c += (base + (uint32_t)t * 4u - 1u < np0 && pool_d[base + t * 4 - 1] < d) ? 1u : 0u;
+      base += c * 4u;
+      c = 0;
+#pragma unroll
+      for (int t = 0; t < 3; t++) c += (base + (uint32_t)t < np0 && pool_d[base + t] < d) ? 1u : 0u;
+      lex = le = base + c;
+      if (lex < np0 && pool_d[lex] == d) {  // ties in distance: order by id, find a duplicate
+        while (lex < np0 && pool_d[lex] == d && (pool_i[lex] & ~FLAG) < id) lex++;
+        dup = lex < np0 && pool_d[lex] == d && (pool_i[lex] & ~FLAG) == id;
+        while (le < np0 && pool_d[le] == d) le++;
+      }
+    }
+    __syncwarp();
+    const unsigned live = __ballot_sync(0xffffffffu, pass && !dup);
+    uint32_t earlier = 0;
+    for (unsigned mm = live; mm; mm &= mm - 1) {
+      const int b = __ffs(mm) - 1;
+      const float db = __shfl_sync(0xffffffffu, d, b);
+      earlier += (b < lane && db <= d) ? 1u : 0u;
+    }
+    const bool acc = pass && !dup && le + earlier < cap;
+    const unsigned amask = __ballot_sync(0xffffffffu, acc);
+    if (!amask) return BIGPOS;
+    uint32_t before = 0, sh[MCH];
+#pragma unroll
+    for (int i = 0; i < MCH; i++) sh[i] = 0;
+    for (unsigned mm = amask; mm; mm &= mm - 1) {
+      const int b = __ffs(mm) - 1;
+      const float db = __shfl_sync(0xffffffffu, d, b);
+      const uint32_t idb = __shfl_sync(0xffffffffu, id, b);
+      const uint32_t lxb = __shfl_sync(0xffffffffu, lex, b);
+      before += (db < d || (db == d && idb < id)) ? 1u : 0u;
+#pragma unroll
+      for (int i = 0; i < MCH; i++) sh[i] += (lxb <= (uint32_t)i * 32u + lane) ? 1u : 0u;
+    }
+    const uint32_t at = lex + before;
+    const int first = (int)__reduce_min_sync(0xffffffffu, acc ? at : (uint32_t)BIGPOS);
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < MCH; i++) {
+      const uint32_t j = (uint32_t)i * 32u + lane;
+      if (i < nchk && j < np0 && sh[i] && j + sh[i] < cap) { pool_d[j + sh[i]] = pd[i]; pool_i[j + sh[i]] = pi[i]; }
+    }
+    if (acc && at < cap) { pool_d[at] = d; pool_i[at] = id | FLAG; }
+    np = min(cap, np0 + (uint32_t)__popc(amask));
+    __syncwarp();
+    return first;
   }
 
   // query -> registers (any alignment / stride), empty visited set
@@ -458,10 +599,33 @@ struct Beam {
   }
 
   // main loop (index_nsg.cpp:539-564 / hnswalg.h:342-436)
+#ifdef BEAM_PROF
+  long long tp[6] = {0, 0, 0, 0, 0, 0};   // load_row, eval, insert, total of expand_all, speculation hits, spec scan
+#define BP_T(x) const long long x = clock64()
+#define BP_ADD(i, a, b) tp[i] += (b) - (a)
+#else
+#define BP_T(x)
+#define BP_ADD(i, a, b)
+#endif
   template <class Rec>
   __device__ __forceinline__ void expand_all(Rec &rec) {
     uint32_t k = 0;
+    // HNSW level 0: while a node's neighbours are evaluated, the adjacency row of the node the loop most likely
+    // turns to next (the next unexpanded pool entry) is loaded into a register per lane; when the guess holds - no
+    // closer candidate arrived - the next hop starts without its dependent row load. A wrong guess is dropped.
+    uint32_t spec_node = INVALID_ID, spec_val = INVALID_ID;
+    BP_T(t_begin);
     while (k < np) {
+      {  // skip to the first unexpanded entry at or after k, 32 entries per step
+        uint32_t kk = np;
+        for (uint32_t j0 = k & ~31u; j0 < np; j0 += 32) {
+          const uint32_t j = j0 + lane;
+          const unsigned mf = __ballot_sync(0xffffffffu, j >= k && j < np && (pool_i[j] & FLAG));
+          if (mf) { kk = j0 + __ffs(mf) - 1; break; }
+        }
+        if (kk >= np) break;
+        k = kk;
+      }
       int nk = (int)np;
       uint32_t e = pool_i[k];
       if (e & FLAG) {
@@ -476,12 +640,40 @@ struct Beam {
           row = p.upper_links + ((size_t)__ldg(p.upper_ptr + node) + (lvl - 1)) * p.maxM;
           rl = p.maxM;
         }
-        uint32_t m = load_row(row, rl, rl, true);
+        BP_T(t0);
+        const bool hit = HNSW && !COHERENT && lvl == 0 && node == spec_node;
+        uint32_t m = load_row(row, rl, rl, true, hit, spec_val);
+#ifdef BEAM_PROF
+        tp[4] += hit;
+        const long long ts0 = clock64();
+#endif
+        if (HNSW && !COHERENT && lvl == 0) {
+          spec_node = INVALID_ID;
+          for (uint32_t j0 = (k + 1) & ~31u; j0 < np; j0 += 32) {
+            const uint32_t j = j0 + lane;
+            const uint32_t pe = (j > k && j < np) ? pool_i[j] : 0u;
+            const unsigned mf = __ballot_sync(0xffffffffu, (pe & FLAG) != 0);
+            if (mf) { spec_node = __shfl_sync(0xffffffffu, pe, __ffs(mf) - 1) & ~FLAG; break; }
+          }
+          if (spec_node != INVALID_ID)
+            spec_val = (uint32_t)lane < p.gstride ? ld_adj(p.graph + (size_t)spec_node * p.gstride + lane) : INVALID_ID;
+        }
+#ifdef BEAM_PROF
+        tp[5] += clock64() - ts0;
+#endif
+        BP_T(t1);
         eval(m);
+        BP_T(t2);
+        BP_ADD(0, t0, t1); BP_ADD(1, t1, t2);
         rec(cand_i, cand_d, m, false);
         for (uint32_t c0 = 0; c0 < m; c0 += 32) {
           uint32_t c = c0 + lane;
           float d = c < m ? cand_d[c] : INFINITY;
+          if (HNSW && cap <= 32u * MCH) {
+            const int r = merge_chunk(d, c < m ? cand_i[c] : INVALID_ID, c < m);
+            if (r < nk) nk = r;
+            continue;
+          }
           float last = pool_d[np - 1];
           bool pass = c < m && ((HNSW && np < cap) || d < last);
           unsigned mask = __ballot_sync(0xffffffffu, pass);
@@ -496,10 +688,14 @@ struct Beam {
             if (r < nk) nk = r;
           }
         }
+        BP_T(t3);
+        BP_ADD(2, t2, t3);
       }
       k = ((uint32_t)nk <= k) ? (uint32_t)nk : k + 1;
     }
     __syncwarp();
+    BP_T(t_end);
+    BP_ADD(3, t_begin, t_end);
   }
 };
 

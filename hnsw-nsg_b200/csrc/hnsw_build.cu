@@ -67,6 +67,10 @@ __global__ void __launch_bounds__(WARPS * 32) hnsw_insert_kernel(const InsertPar
   float *res_d = reinterpret_cast<float *>(res_i + p.gstride);
   NoRec rec;
   const float *qv = p.vec + (size_t)pt * p.stride;
+#ifdef BEAM_PROF
+  const long long tk0 = clock64();
+  long long t_heur = 0;
+#endif
   b.begin(qv);
   const int curlevel = ip.levels[pt];
   uint32_t cur = p.ep;
@@ -115,8 +119,14 @@ __global__ void __launch_bounds__(WARPS * 32) hnsw_insert_kernel(const InsertPar
       nres = b.np;
       __syncwarp();
     } else {
+#ifdef BEAM_PROF
+      const long long th0 = clock64();
+#endif
       occlude_scan(b, b.pool_d, b.pool_i, 0, b.np, ip.M, res_i, res_d, nres, n_heur);
       b.load_query(qv);  // occlude_scan used the query registers for the candidate rows
+#ifdef BEAM_PROF
+      t_heur += clock64() - th0;
+#endif
     }
     __syncwarp();
     // ---- own row, farthest first; reverse edges
@@ -144,6 +154,16 @@ __global__ void __launch_bounds__(WARPS * 32) hnsw_insert_kernel(const InsertPar
     atomicAdd(ip.stats + 0, (unsigned long long)b.n_dist);
     atomicAdd(ip.stats + 1, (unsigned long long)b.n_hops);
     atomicAdd(ip.stats + 2, (unsigned long long)n_heur);
+#ifdef BEAM_PROF
+    atomicAdd(ip.stats + 4, (unsigned long long)(clock64() - tk0));
+    atomicAdd(ip.stats + 5, (unsigned long long)b.tp[3]);
+    atomicAdd(ip.stats + 6, (unsigned long long)b.tp[0]);
+    atomicAdd(ip.stats + 7, (unsigned long long)b.tp[1]);
+    atomicAdd(ip.stats + 8, (unsigned long long)b.tp[2]);
+    atomicAdd(ip.stats + 9, (unsigned long long)t_heur);
+    atomicAdd(ip.stats + 10, (unsigned long long)b.tp[4]);
+    atomicAdd(ip.stats + 11, (unsigned long long)b.tp[5]);
+#endif
   }
 }
 
@@ -504,6 +524,22 @@ static cudaError_t grow(T **p, size_t keep, size_t need, size_t *cap, cudaStream
   return e;
 }
 
+// The insertion beam's visited set: 2^11 words per warp (measured on 1M x 128, M=16, efC=200: 2^10 1.68 s, 2^11 1.64 s,
+// 2^12 2.10 s, 2^13 3.2 s - a smaller table re-evaluates ~5 % more rows but doubles the resident warps), holding
+// 16-bit tags instead of 32-bit ids when the row count allows: twice the slots in the same words, so a beam that
+// visits 3-4k rows no longer overfills its table (every test then ran the whole probe sequence and forgot an entry).
+// What the set forgets only costs re-evaluations: a re-evaluated row is in the pool already or fails the pool's
+// threshold again, so the links do not depend on the table.
+static void insert_visited_set(const b200ann_handle *h, SearchParams &sp, size_t n) {
+  sp.hbits = (h->link_visited_bits && h->link_visited_bits < 11) ? h->link_visited_bits : 11;
+  if (const char *e = getenv("B200ANN_HNSW_HBITS")) sp.hbits = std::min(13, std::max(6, atoi(e)));   // A/B runs
+  sp.nbits = 1;
+  while (sp.nbits < 32 && (1ull << sp.nbits) < (unsigned long long)n) sp.nbits++;
+  if (sp.nbits < sp.hbits + 1) sp.nbits = sp.hbits + 1;
+  sp.vis16 = sp.nbits - (sp.hbits + 1) <= 12 ? 1 : 0;
+  if (const char *e = getenv("B200ANN_HNSW_VIS16")) sp.vis16 = sp.vis16 && atoi(e);   // A/B runs
+}
+
 // Inserts rows [s0, n) of the index (vectors, levels, upper_ptr and the INVALID-filled link rows are in place) into
 // the HNSW graph held by the index, batch by batch; updates the entry point / top level. levels = host levels of
 // rows [s0, n). stats4 += {beam evaluations, hops, heuristic evaluations, 0}.
@@ -533,9 +569,9 @@ static int hnsw_run_batches(b200ann_handle *h, b200ann_index *ix, size_t s0, con
   CU_CHECK(h, counters.alloc(4, st));
   CU_CHECK(h, rev_row.alloc(ecap, st)); CU_CHECK(h, rev_src.alloc(ecap, st)); CU_CHECK(h, rev_d.alloc(ecap, st));
   CU_CHECK(h, g_src.alloc(ecap, st)); CU_CHECK(h, g_d.alloc(ecap, st));
-  CU_CHECK(h, stats.alloc(4, st));
+  CU_CHECK(h, stats.alloc(16, st));
   CU_CHECK(h, cudaMemsetAsync(rstate.p, 0, 3 * nr * 4, st));
-  CU_CHECK(h, cudaMemsetAsync(stats.p, 0, 4 * sizeof(unsigned long long), st));
+  CU_CHECK(h, cudaMemsetAsync(stats.p, 0, 16 * sizeof(unsigned long long), st));
   uint32_t *rcount = rstate.p, *rfill = rstate.p + nr, *roff = rstate.p + 2 * nr;
 
   const int ipm = ix->metric == B200ANN_IP ? MET_IP : (ix_u8(ix) ? MET_U8 : MET_L2);
@@ -545,16 +581,14 @@ static int hnsw_run_batches(b200ann_handle *h, b200ann_index *ix, size_t s0, con
   ip.sp.graph = ix->links0; ip.sp.gstride = (uint32_t)maxM0;
   ip.sp.upper_links = ix->upper_links; ip.sp.upper_ptr = ix->upper_ptr; ip.sp.maxM = (uint32_t)maxM;
   ip.sp.L = (uint32_t)efc; ip.sp.K = (uint32_t)M;
-  // visited hash of 2^11 slots per warp: measured on 1M x 128, M=16, efC=200: 2^10 1.68 s, 2^11 1.64 s, 2^12 2.10 s,
-  // 2^13 3.2 s (a smaller table re-evaluates ~5 % more rows but doubles the resident warps)
-  ip.sp.hbits = (h->link_visited_bits && h->link_visited_bits < 11) ? h->link_visited_bits : 11;
+  insert_visited_set(h, ip.sp, n);
   ip.sp.pool_cap = round_up((uint32_t)efc + 1, 32);
   ip.sp.cand_cap = round_up((uint32_t)maxM0, 32);
   ip.M = (uint32_t)M; ip.nlev = nlev; ip.levels = ix->levels; ip.links0 = ix->links0; ip.upper_links = ix->upper_links;
   ip.rev_row = rev_row.p; ip.rev_src = rev_src.p; ip.rev_d = rev_d.p;
   ip.rcount = rcount; ip.touched = touched.p; ip.counters = counters.p; ip.stats = stats.p;
   ReverseParams rp = {};
-  rp.sp = ip.sp; rp.sp.pool_cap = 32; rp.sp.hbits = 5;
+  rp.sp = ip.sp; rp.sp.pool_cap = 32; rp.sp.hbits = 5; rp.sp.vis16 = 0;
   rp.links0 = ix->links0; rp.upper_links = ix->upper_links; rp.row_owner = ix->upper_owner;
   rp.touched = touched.p; rp.counters = counters.p; rp.roff = roff; rp.g_src = g_src.p; rp.g_d = g_d.p;
   rp.rcount = rcount; rp.rfill = rfill; rp.stats = stats.p;
@@ -621,6 +655,15 @@ static int hnsw_run_batches(b200ann_handle *h, b200ann_index *ix, size_t s0, con
   if (rc == 0) {
     cudaMemcpyAsync(hs, stats.p, sizeof hs, cudaMemcpyDeviceToHost, st);
     cudaError_t ce = cudaStreamSynchronize(st);
+#ifdef BEAM_PROF
+    {
+      unsigned long long ps[16];
+      cudaMemcpy(ps, stats.p, sizeof ps, cudaMemcpyDeviceToHost);
+      const double pts = (double)(n - s0);
+      fprintf(stderr, "HB_PROF rows %zu: cycles/row total %.0f | expand_all %.0f (load_row %.0f eval %.0f insert %.0f) | heuristic %.0f | hops/row %.1f evals/row %.0f | spec hits/row %.1f scan cycles %.0f\n",
+              n - s0, ps[4] / pts, ps[5] / pts, ps[6] / pts, ps[7] / pts, ps[8] / pts, ps[9] / pts, ps[1] / pts, ps[0] / pts, ps[10] / pts, ps[11] / pts);
+    }
+#endif
     if (ce == cudaSuccess) ce = cudaGetLastError();
     if (ce != cudaSuccess) rc = set_err(h, B200ANN_ERR_CUDA, std::string("hnsw insert: ") + cudaGetErrorString(ce));
   }
@@ -821,10 +864,10 @@ int hnsw_update_launch(b200ann_handle *h, b200ann_index *ix, const uint32_t *ids
   CU_CHECK(h, claim.alloc(nr, st));
   CU_CHECK(h, stage.alloc(items * maxM0, st)); CU_CHECK(h, stage_ridx.alloc(items, st));
   CU_CHECK(h, own_stage.alloc(oitems * maxM0, st)); CU_CHECK(h, own_ridx.alloc(oitems, st));
-  CU_CHECK(h, stats.alloc(4, st));
+  CU_CHECK(h, stats.alloc(16, st));
   CU_CHECK(h, cudaMemsetAsync(rstate.p, 0, 3 * nr * 4, st));
   CU_CHECK(h, cudaMemsetAsync(claim.p, 0, nr * 4, st));
-  CU_CHECK(h, cudaMemsetAsync(stats.p, 0, 4 * sizeof(unsigned long long), st));
+  CU_CHECK(h, cudaMemsetAsync(stats.p, 0, 16 * sizeof(unsigned long long), st));
   uint32_t *rcount = rstate.p, *rfill = rstate.p + nr, *roff = rstate.p + 2 * nr;
 
   SearchParams sp = {};
@@ -839,7 +882,7 @@ int hnsw_update_launch(b200ann_handle *h, b200ann_index *ix, const uint32_t *ids
   up.claim = claim.p; up.stage = stage.p; up.stage_ridx = stage_ridx.p; up.stats = stats.p;
   InsertParams ip = {};
   ip.sp = sp;
-  ip.sp.hbits = (h->link_visited_bits && h->link_visited_bits < 11) ? h->link_visited_bits : 11;
+  insert_visited_set(h, ip.sp, n);
   ip.sp.pool_cap = round_up((uint32_t)efc + 1, 32);
   ip.sp.cand_cap = round_up((uint32_t)maxM0, 32);
   ip.M = (uint32_t)M; ip.nlev = nlev; ip.levels = ix->levels; ip.links0 = ix->links0; ip.upper_links = ix->upper_links;
@@ -847,7 +890,7 @@ int hnsw_update_launch(b200ann_handle *h, b200ann_index *ix, const uint32_t *ids
   ip.rcount = rcount; ip.touched = touched.p; ip.counters = counters.p; ip.stats = stats.p;
   ip.upd_ids = ids; ip.own_stage = own_stage.p; ip.own_ridx = own_ridx.p;
   ReverseParams rp = {};
-  rp.sp = ip.sp; rp.sp.pool_cap = 32; rp.sp.hbits = 5;
+  rp.sp = ip.sp; rp.sp.pool_cap = 32; rp.sp.hbits = 5; rp.sp.vis16 = 0;
   rp.links0 = ix->links0; rp.upper_links = ix->upper_links; rp.row_owner = ix->upper_owner;
   rp.touched = touched.p; rp.counters = counters.p; rp.roff = roff; rp.g_src = g_src.p; rp.g_d = g_d.p;
   rp.rcount = rcount; rp.rfill = rfill; rp.stats = stats.p; rp.update = 1;

@@ -712,7 +712,7 @@ int hnsw_build_launch(b200ann_handle *h, b200ann_index *ix, size_t M, size_t efc
   if (M < 2 || M > 128 || n >= (1ull << 31))
     return set_err(h, B200ANN_ERR_ARG, "hnsw_build: need 2 <= M <= 128");
   if (efc < M) efc = M;                                        // hnswalg.h:107
-  if (ratio == 0) ratio = 64;
+  if (ratio == 0) ratio = 32;
   if (bmax == 0) bmax = 8192;
   cudaStream_t st = h->stream;
   // the caller freed any previous HNSW graph: start from empty arrays
@@ -748,7 +748,7 @@ int hnsw_insert_launch(b200ann_handle *h, b200ann_index *ix, const void *data, s
                        const uint64_t *labels_host_or_dev, size_t ratio, size_t bmax, uint64_t *info8) {
   if (!ix->has_hnsw) return set_err(h, B200ANN_ERR_STATE, "hnsw_insert_batch: index has no HNSW graph (hnsw_build / set_hnsw first)");
   if (ix->n + nb >= (1ull << 31)) return set_err(h, B200ANN_ERR_ARG, "hnsw_insert_batch: too many rows");
-  if (ratio == 0) ratio = 64;
+  if (ratio == 0) ratio = 32;
   if (bmax == 0) bmax = 8192;
   cudaStream_t st = h->stream;
   const size_t n_old = ix->n, n = n_old + nb;

@@ -713,7 +713,7 @@ int hnsw_build_launch(b200ann_handle *h, b200ann_index *ix, size_t M, size_t efc
     return set_err(h, B200ANN_ERR_ARG, "hnsw_build: need 2 <= M <= 128");
   if (efc < M) efc = M;                                        // hnswalg.h:107
   if (ratio == 0) ratio = 32;
-  if (bmax == 0) bmax = 8192;
+  if (bmax == 0) bmax = 16384;
   cudaStream_t st = h->stream;
   // the caller freed any previous HNSW graph: start from empty arrays
   ix->maxM = M; ix->maxM0 = 2 * M; ix->upper_rows = 0; ix->hnsw_ep = 0; ix->maxlevel = -1;
@@ -749,7 +749,7 @@ int hnsw_insert_launch(b200ann_handle *h, b200ann_index *ix, const void *data, s
   if (!ix->has_hnsw) return set_err(h, B200ANN_ERR_STATE, "hnsw_insert_batch: index has no HNSW graph (hnsw_build / set_hnsw first)");
   if (ix->n + nb >= (1ull << 31)) return set_err(h, B200ANN_ERR_ARG, "hnsw_insert_batch: too many rows");
   if (ratio == 0) ratio = 32;
-  if (bmax == 0) bmax = 8192;
+  if (bmax == 0) bmax = 16384;
   cudaStream_t st = h->stream;
   const size_t n_old = ix->n, n = n_old + nb;
   const size_t M = ix->hnsw_M ? ix->hnsw_M : ix->maxM;

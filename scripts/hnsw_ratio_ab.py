@@ -23,7 +23,7 @@ def main():
             best = 1e9
             for rep in range(2):
                 ix = B.Index(h, base, B.L2)
-                t = time.time(); info = ix.hnsw_build(16, 200, seed=100, ratio=ratio); dt = time.time() - t
+                t = time.time(); info = ix.hnsw_build(16, 200, seed=100, ratio=ratio, bmax=int(os.environ.get("BMAX", "0"))); dt = time.time() - t
                 best = min(best, dt)
                 if rep == 1:
                     if truth is None: truth, _ = ix.bf_knn(q, 10)

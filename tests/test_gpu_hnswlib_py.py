@@ -129,7 +129,7 @@ def test_custom_labels_match_oracle(hnswlib):
     q = R.data_uniform(200, dim, 10)
     lab, d = p.knn_query(q, k=10)
     R.oracle().orc_set_gpu_team(B.dist_team(dim))
-    O = R.orc_hnsw_build(base, M, efc, R.L2_GPU, 1, ratio=32, bmax=8192)
+    O = R.orc_hnsw_build(base, M, efc, R.L2_GPU, 1, ratio=32, bmax=16384)
     O["labels"] = labs
     ol, od = R.orc_hnsw_search(base, O, q, 10, 64, R.L2_GPU)
     assert (lab == ol).all()

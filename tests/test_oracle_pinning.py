@@ -633,7 +633,7 @@ def test_hnsw_build_batch_form_quality_and_schedule():
     base = R.data_uniform(n, dim, 5)
     q = R.data_uniform(2000, dim, 6)
     H0 = R.orc_hnsw_build(base, M, efc, R.L2_SCALAR, 0)
-    H1 = R.orc_hnsw_build(base, M, efc, R.L2_SCALAR, 1, ratio=32, bmax=8192)   # the product's default schedule
+    H1 = R.orc_hnsw_build(base, M, efc, R.L2_SCALAR, 1, ratio=32, bmax=16384)   # the product's default schedule
     assert (H0["levels"] == H1["levels"]).all() and H0["ep"] == H1["ep"] and H0["maxlevel"] == H1["maxlevel"]
     assert int(H1["info"][1]) < n // 8   # batches
     for i in range(0, n, 37):

@@ -501,6 +501,13 @@ int nsg_link_launch(b200ann_handle *h, const b200ann_index *ix, const uint32_t *
   lp.sp.graph = knn; lp.sp.gstride = (uint32_t)kstride; lp.sp.ep = ep;
   lp.sp.L = (uint32_t)L; lp.sp.K = (uint32_t)L; lp.sp.seed = seed;
   lp.sp.hbits = h->link_visited_bits ? h->link_visited_bits : (ix->dim <= 128 ? 9 : 10);
+  // 16-bit tags in the same words (twice the slots) when the row count allows: what the set forgets is re-evaluated
+  // (24 % of the beam's rows with 2^9 32-bit slots at 1M), never lost - the candidate buffer drops duplicates
+  lp.sp.nbits = 1;
+  while (lp.sp.nbits < 32 && (1ull << lp.sp.nbits) < (unsigned long long)ix->n) lp.sp.nbits++;
+  if (lp.sp.nbits < lp.sp.hbits + 1) lp.sp.nbits = lp.sp.hbits + 1;
+  lp.sp.vis16 = lp.sp.nbits - (lp.sp.hbits + 1) <= 12 ? 1 : 0;
+  if (const char *e = getenv("B200ANN_LINK_VIS16")) lp.sp.vis16 = lp.sp.vis16 && atoi(e);   // A/B runs
   size_t cc = kstride > L ? kstride : L;
   if (R > cc) cc = R;
   lp.sp.cand_cap = round_up((uint32_t)cc, 32);

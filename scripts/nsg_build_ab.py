@@ -11,6 +11,7 @@ base = S.sift_shape(n, 128, seed=1000)
 ix = B.Index(h, base, B.L2)
 knn = torch.empty((n, 200), dtype=torch.int32, device="cuda")
 ix.knn_graph_raw(200, knn)
+if os.environ.get("LINK_BITS"): h.set_link_visited_bits(int(os.environ["LINK_BITS"]))
 for rep in range(2):
     t = time.time(); info = ix.nsg_build((knn, 200), 40, 50, 500, seed=1); dt = time.time() - t
     print("nsg_build", round(dt, 3), h.last_kernel_ms, {k: info[k] for k in list(info)[:6]}, flush=True)

@@ -450,9 +450,21 @@ int b200ann_hnsw_update_batch(b200ann_handle_t h, b200ann_index_t ix, const uint
   CU_CHECK(h, din.stage((const uint8_t *)data, nb * stride * esz, h->stream));
   CU_CHECK(h, iin.stage(ids, nb, h->stream));
   CallTimer t(h);
-  int rc = hnsw_update_launch(h, ix, iin.d, nb, din.d, stride * esz, info);
+  // Like the build's batches, one pass moves at most 1/32 of the index: the elements of a pass do not see each other's
+  // new positions, and 10 % of an index moved in one pass measured 0.011 recall@10 below a rebuild. A larger call is
+  // a sequence of passes, each a call of its own as far as the result goes.
+  const size_t sub = std::max<size_t>(1, ix->n / 32);
+  uint64_t acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  int rc = 0;
+  for (size_t s = 0; s < nb && rc == 0; s += sub) {
+    uint64_t one[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    rc = hnsw_update_launch(h, ix, iin.d + s, std::min(sub, nb - s), din.d + s * stride * esz, stride * esz, one);
+    for (int i = 0; i < 5; i++) acc[i] += one[i];
+    acc[5] = one[5]; acc[6] = one[6]; acc[7] = std::max(acc[7], one[7]);
+  }
   t.stop();
   if (rc) return rc;
+  if (info) memcpy(info, acc, sizeof acc);
   CU_CHECK(h, t.sync());
   return 0;
 }

@@ -1127,7 +1127,7 @@ int nndescent_launch(b200ann_handle *h, const b200ann_index *ix, size_t K, size_
       // 1M rows), so later iterations keep the buffer and re-run the pass in the rare case the records overflow it -
       // the pass only reads the graph, so a re-run writes the same records.
       if (!rec_cap) {
-        rec_cap = (2 * bound + 1) + (2 * bound + 1) / 4;
+        rec_cap = 2 * bound + 1;   // cannot overflow in this iteration; a later one that does re-runs its pass
         if (const char *e = getenv("B200ANN_NND_REC_CAP")) rec_cap = std::max(1ll, atoll(e));  // tests: force the re-run path
         CU_CHECK(h, rec.alloc(rec_cap, st));
       }

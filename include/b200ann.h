@@ -106,7 +106,7 @@ int b200ann_hnsw_build(b200ann_handle_t h, b200ann_index_t ix, size_t M, size_t 
  * place - the device arrays grow with doubling capacity, the rows already linked are not touched except through the
  * reverse links the new points add, and the level generator continues where the build / the previous append left it
  * (a graph installed with b200ann_index_set_hnsw starts a fresh generator with seed 100 like the reference's load
- * ctor). The new rows are inserted with the batch schedule of b200ann_hnsw_build (one batch for nb <= n/64).
+ * ctor). The new rows are inserted with the batch schedule of b200ann_hnsw_build (one batch for nb <= n/32).
  * ef_construction: 0 = the value of the build (200 for an installed graph). Any NSG graph of the index is dropped.
  * b200ann_index_size grows by nb. info (optional, 8 x u64): as b200ann_hnsw_build, counters of this call. */
 int b200ann_hnsw_insert_batch(b200ann_handle_t h, b200ann_index_t ix, const float *data /*[h|d]*/, size_t stride,
@@ -121,8 +121,10 @@ int b200ann_hnsw_insert_batch(b200ann_handle_t h, b200ann_index_t ix, const floa
  * themselves filtered out of their candidates, sources already present in a neighbour's list skipped (phase B).
  * Levels, entry point and labels do not change; no rebuild, cost proportional to nb. Any NSG graph of the index is
  * dropped. The batch form is restated by oracle.c orc_hnsw_update variant 1 and equals it link for link; its
- * variant 0 is the reference's one-at-a-time form, pinned to the compiled reference. Calls of more than 8192 elements
- * are processed in chunks. info (optional, 8 x u64): {distance evaluations, expanded nodes, heuristic evaluations,
+ * variant 0 is the reference's one-at-a-time form, pinned to the compiled reference. One pass moves at most n/32
+ * elements (the build's batch ratio: elements of a pass do not see each other's new positions); a larger call is a
+ * sequence of passes, each on the graph the previous one left, and gives the same result as that sequence of calls.
+ * info (optional, 8 x u64): {distance evaluations, expanded nodes, heuristic evaluations,
  * chunks, lists rewritten by phase A, maxlevel, entry point, largest reverse-link group}. */
 int b200ann_hnsw_update_batch(b200ann_handle_t h, b200ann_index_t ix, const uint32_t *ids /*[h|d]*/,
                               const float *data /*[h|d]*/, size_t stride, size_t nb, uint64_t *info /*[h]*/);

@@ -416,12 +416,20 @@ def orc_hnsw_update(base, h, ids, newvec, mode, variant, efc=None, dim=None):
     if rows == 0:
         up = np.full((1, max(1, M)), INVALID, np.uint32)
     info = np.zeros(2, np.uint64)
-    rc = oracle().orc_hnsw_update(data, n, dim, sdim, M, efc if efc is not None else h.get("efc", 200), mode, variant,
-                                  np.ascontiguousarray(h["levels"], np.int32), links0,
-                                  np.ascontiguousarray(h["upper_ptr"], np.uint32), up, rows, h["ep"], h["maxlevel"],
-                                  np.ascontiguousarray(ids, np.uint32), np.ascontiguousarray(newvec, base.dtype), len(ids),
-                                  _vp(info))
-    assert rc == 0
+    ids = np.ascontiguousarray(ids, np.uint32)
+    newvec = np.ascontiguousarray(newvec, base.dtype)
+    # the batch form moves at most 1/32 of the index per pass (b200ann_hnsw_update_batch, capi.cu): a larger call is a
+    # sequence of passes, each on the graph the previous one left
+    sub = len(ids) if variant == 0 else max(1, n // 32)
+    for s in range(0, len(ids), sub):
+        one = np.zeros(2, np.uint64)
+        rc = oracle().orc_hnsw_update(data, n, dim, sdim, M, efc if efc is not None else h.get("efc", 200), mode, variant,
+                                      np.ascontiguousarray(h["levels"], np.int32), links0,
+                                      np.ascontiguousarray(h["upper_ptr"], np.uint32), up, rows, h["ep"], h["maxlevel"],
+                                      np.ascontiguousarray(ids[s:s + sub]), np.ascontiguousarray(newvec[s:s + sub]),
+                                      len(ids[s:s + sub]), _vp(one))
+        assert rc == 0
+        info += one
     g = dict(h)
     g.update(links0=links0, upper_links=up[:rows] if rows else h["upper_links"], info=info)
     return data, g

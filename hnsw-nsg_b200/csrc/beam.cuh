@@ -58,6 +58,7 @@ struct SearchParams {
   int vis16;                    // visited set entries: 0 = u32 ids (2^hbits slots), 1 = u16 tags (2^(hbits+1) slots)
   int nbits;                    // vis16: ids are hashed as nbits-bit numbers (n <= 2^nbits)
   int prefetch;                 // 1: expand_all prefetches the adjacency row of the next unexpanded pool entry
+  uint32_t merge_min;           // HNSW pools below this many entries insert one candidate at a time (A/B knob, 0: never)
   uint32_t nst;                 // search core v2 (beam2.cuh): stages of the per-warp row ring
   uint32_t q1;                  // search core v2: work items [0, q1) run one per warp, [q1, nq) one per block; work[0..1] = the two queues
 };
@@ -669,7 +670,7 @@ struct Beam {
         for (uint32_t c0 = 0; c0 < m; c0 += 32) {
           uint32_t c = c0 + lane;
           float d = c < m ? cand_d[c] : INFINITY;
-          if (HNSW && cap <= 32u * MCH) {
+          if (HNSW && cap <= 32u * MCH && cap >= p.merge_min) {
             const int r = merge_chunk(d, c < m ? cand_i[c] : INVALID_ID, c < m);
             if (r < nk) nk = r;
             continue;

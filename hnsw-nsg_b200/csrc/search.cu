@@ -121,6 +121,7 @@ int launch_dim(b200ann_handle *h, const SearchParams &p0) {
   p.order = (h->query_order && h->query_order_n == p.nq) ? h->query_order : nullptr;
   p.prefetch = h->search_prefetch;
   p.id_base = h->id_base;
+  if (const char *e = getenv("B200ANN_MERGE_MIN")) p.merge_min = (uint32_t)atoi(e);   // A/B runs
   p.nbits = 1;
   while (p.nbits < 32 && (1ull << p.nbits) < (unsigned long long)p.n) p.nbits++;
   if (p.nbits < p.hbits + 1) p.nbits = p.hbits + 1;

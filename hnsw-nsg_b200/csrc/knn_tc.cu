@@ -30,7 +30,7 @@ namespace tc {
 
 constexpr int BM = 128, BN = 256, BK = 64;          // tile rows (queries), tile columns (base rows), bf16 per K-block
 constexpr int A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2;  // 16 KB, 32 KB
-constexpr int A_SLOTS = 4;                          // at most this many resident A K-blocks (64 KB)
+constexpr int A_SLOTS = 5;                          // at most this many resident A K-blocks (80 KB): 128-d hi + lo + the norm block
 constexpr int NTHREADS = 320;                       // warp0 TMA, warp1 MMA, warps 2-9 epilogue
 constexpr int SMEM_MISC = 49152;                    // spill 36 KB, norms 2 KB, histograms 8 KB, row state 1 KB, barriers
 constexpr int SMEM_MAX = 232448;                    // 227 KB opt-in limit of sm_100
@@ -155,6 +155,31 @@ __global__ void prep_kernel(const float *src, size_t sstride, uint32_t n, uint32
   }
 }
 
+// The norm rides the contraction: one more K-block whose B rows hold -||y||^2 / 2 as three bf16 terms (columns 0-2;
+// hi + mid + lo carry the 24 significant bits of the fp32 norm) and whose A rows hold 1.0 in those columns, so the
+// accumulator ends as  x.y - ||y||^2 / 2 = -key / 2  and the epilogue's filter is one compare per element.
+__global__ void ext_b_kernel(const float *norms, uint32_t n, __nv_bfloat16 *ext) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;   // one thread per (row, 8-column group)
+  if (i >= n * 8u) return;
+  const uint32_t row = i >> 3, g = i & 7u;
+  __nv_bfloat16 v[8];
+#pragma unroll
+  for (int c = 0; c < 8; c++) v[c] = __float2bfloat16_rn(0.f);
+  if (g == 0) {
+    const float x = -0.5f * norms[row];
+    const __nv_bfloat16 h = __float2bfloat16_rn(x);
+    const float r1 = x - __bfloat162float(h);
+    const __nv_bfloat16 m = __float2bfloat16_rn(r1);
+    const float r2 = r1 - __bfloat162float(m);
+    v[0] = h; v[1] = m; v[2] = __float2bfloat16_rn(r2);
+  }
+  *reinterpret_cast<uint4 *>(ext + (size_t)row * 64 + g * 8) = *reinterpret_cast<const uint4 *>(v);
+}
+__global__ void ext_a_kernel(__nv_bfloat16 *ext) {   // [128, 64]
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < 128u * 64u) ext[i] = __float2bfloat16_rn((i & 63u) < 3u ? 1.f : 0.f);
+}
+
 // ---------------------------------------------------------------- sweep kernel
 struct SweepParams {
   uint32_t nq_rows;   // query rows of this launch
@@ -166,7 +191,7 @@ struct SweepParams {
   uint32_t a_resident;
   uint32_t a_slots, nstage;  // shared-memory carve: A K-block slots, B (and streamed A) ring stages
   uint32_t ntiles, tiles_per_split;
-  const float *ny;    // base row norms; NULL for inner product
+  uint32_t ext;       // 1 (L2): one more K-block step per tile carries -||y||^2 / 2 (mA_ext / mB_ext); 0: inner product
   int exclude_self;
   uint32_t Kp, cap, rows_pad;
   float *cand_d; uint32_t *cand_i;    // [splits, rows_pad, cap]
@@ -329,7 +354,8 @@ __device__ float compact_row_reg(float *cd, uint32_t *ci, uint32_t cnt, uint32_t
 // per-row state (count, threshold) in shared memory and synchronise on a 64-thread named barrier per tile.
 __global__ void __launch_bounds__(NTHREADS, 1)
 sweep_kernel(const __grid_constant__ CUtensorMap mA_hi, const __grid_constant__ CUtensorMap mA_lo,
-             const __grid_constant__ CUtensorMap mB_hi, const __grid_constant__ CUtensorMap mB_lo, const SweepParams p) {
+             const __grid_constant__ CUtensorMap mB_hi, const __grid_constant__ CUtensorMap mB_lo,
+             const __grid_constant__ CUtensorMap mA_ext, const __grid_constant__ CUtensorMap mB_ext, const SweepParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment for the 128B swizzle; plain pointer arithmetic keeps the shared address space
   // known to the compiler (LDS/STS/ATOMS instead of generic accesses)
@@ -339,7 +365,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap mA_hi, const __grid_constant__ 
   uint8_t *sB = smem + p.a_slots * A_BYTES;            // NS x 32 KB
   uint8_t *misc = sB + NS * B_BYTES;
   float *spill = (float *)misc;                        // [8 warps][32 lanes][36]
-  float *ny_s = (float *)(misc + 36864);               // [2][256]
+  // (misc + 36864: 2 KB once used for the staged norms)
   uint32_t *hist = (uint32_t *)(misc + 36864 + 2048);  // [8][256]
   uint32_t *cnt_s = (uint32_t *)(misc + 36864 + 2048 + 8192);  // [128]
   float *tau_s = (float *)(cnt_s + 128);                       // [128]
@@ -352,7 +378,9 @@ sweep_kernel(const __grid_constant__ CUtensorMap mA_hi, const __grid_constant__ 
   const uint32_t m0 = p.q_row0 + blockIdx.x * BM;
   const uint32_t tile_begin = blockIdx.y * p.tiles_per_split;
   const uint32_t tile_end = min(p.ntiles, tile_begin + p.tiles_per_split);
-  const uint32_t T = p.nkb * p.passes;  // K-block steps per tile
+  const uint32_t Tm = p.nkb * p.passes;  // K-block steps of the data per tile
+  const uint32_t T = Tm + p.ext;         // + the norm block (last)
+  const uint32_t nA = p.nkb * (p.passes == 3 ? 2u : 1u) + p.ext;  // resident A K-blocks (the norm block's ones last)
 
   if (warp == 0 && lane == 0) {
     for (uint32_t i = 0; i < NS; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
@@ -375,10 +403,10 @@ sweep_kernel(const __grid_constant__ CUtensorMap mA_hi, const __grid_constant__ 
     // ===== TMA producer =====
     if (lane == 0) {
       if (p.a_resident) {
-        const uint32_t nA = p.nkb * (p.passes == 3 ? 2u : 1u);
         mbar_expect_tx(a_full, nA * A_BYTES);
-        for (uint32_t b = 0; b < nA; b++)
+        for (uint32_t b = 0; b < nA - p.ext; b++)
           tma_load_2d(sA + b * A_BYTES, b < p.nkb ? &mA_hi : &mA_lo, (int)((b % p.nkb) * BK), (int)m0, a_full);
+        if (p.ext) tma_load_2d(sA + (nA - 1) * A_BYTES, &mA_ext, 0, 0, a_full);
       }
       uint32_t stage = 0, phase = 0;
       for (uint32_t tile = tile_begin; tile < tile_end; tile += p.tile_step) {
@@ -387,9 +415,14 @@ sweep_kernel(const __grid_constant__ CUtensorMap mA_hi, const __grid_constant__ 
           const uint32_t seg = t / p.nkb, kb = t % p.nkb;
           mbar_wait_relaxed(&empty[stage], phase ^ 1u);
           mbar_expect_tx(&full[stage], B_BYTES + (p.a_resident ? 0 : A_BYTES));
-          tma_load_2d(sB + stage * B_BYTES, seg == 1 ? &mB_lo : &mB_hi, (int)(kb * BK), n0, &full[stage]);
-          if (!p.a_resident)
-            tma_load_2d(sA + stage * A_BYTES, seg == 2 ? &mA_lo : &mA_hi, (int)(kb * BK), (int)m0, &full[stage]);
+          if (t < Tm) {
+            tma_load_2d(sB + stage * B_BYTES, seg == 1 ? &mB_lo : &mB_hi, (int)(kb * BK), n0, &full[stage]);
+            if (!p.a_resident)
+              tma_load_2d(sA + stage * A_BYTES, seg == 2 ? &mA_lo : &mA_hi, (int)(kb * BK), (int)m0, &full[stage]);
+          } else {
+            tma_load_2d(sB + stage * B_BYTES, &mB_ext, 0, n0, &full[stage]);
+            if (!p.a_resident) tma_load_2d(sA + stage * A_BYTES, &mA_ext, 0, 0, &full[stage]);
+          }
           if (++stage == NS) { stage = 0; phase ^= 1u; }
         }
       }
@@ -408,11 +441,15 @@ sweep_kernel(const __grid_constant__ CUtensorMap mA_hi, const __grid_constant__ 
         mbar_wait(&full[stage], phase);
         tc_fence_after();
         if (lane == 0) {
-          const uint32_t aslot = p.a_resident ? (seg == 2 ? p.nkb : 0u) + kb : stage;
+          const uint32_t aslot = p.a_resident ? (t < Tm ? (seg == 2 ? p.nkb : 0u) + kb : nA - 1u) : stage;
           const uint32_t a_addr = smem_u32(sA + aslot * A_BYTES), b_addr = smem_u32(sB + stage * B_BYTES);
+          if (t < Tm) {
 #pragma unroll
-          for (int k = 0; k < BK / 16; k++)
-            tc_mma(d_tmem, smem_desc(a_addr + k * 32), smem_desc(b_addr + k * 32), IDESC, (t > 0 || k > 0) ? 1u : 0u);
+            for (int k = 0; k < BK / 16; k++)
+              tc_mma(d_tmem, smem_desc(a_addr + k * 32), smem_desc(b_addr + k * 32), IDESC, (t > 0 || k > 0) ? 1u : 0u);
+          } else {
+            tc_mma(d_tmem, smem_desc(a_addr), smem_desc(b_addr), IDESC, 1u);   // the norm block: 3 of its first 16 columns
+          }
           tc_commit(&empty[stage]);                   // frees the smem stage once these MMAs have read it
           if (t == T - 1) tc_commit(&tmem_full[as]);  // accumulator complete
         }
@@ -425,7 +462,6 @@ sweep_kernel(const __grid_constant__ CUtensorMap mA_hi, const __grid_constant__ 
     const int ew = warp - 2;   // 0..7
     const int q = warp & 3;    // TMEM lane quarter this warp may read
     const int hf = ew >> 2;    // column half of every tile
-    const int et = ew * 32 + lane;
     const int rowi = q * 32 + lane;  // row within the CTA
     const uint32_t row_local = blockIdx.x * BM + rowi;
     const bool row_valid = row_local < p.nq_rows;
@@ -472,41 +508,29 @@ sweep_kernel(const __grid_constant__ CUtensorMap mA_hi, const __grid_constant__ 
     for (uint32_t tile = tile_begin; tile < tile_end; tile += p.tile_step, ti++) {
       const uint32_t as = ti & 1u, aphase = (ti >> 1) & 1u;
       const uint32_t n0 = tile * BN;
-      {
-        const uint32_t c0 = n0 + et;
-        ny_s[as * BN + et] = c0 < p.n ? (p.ny ? __ldg(p.ny + c0) : 0.f) : INFINITY;
-      }
-      asm volatile("bar.sync 1, 256;" ::: "memory");
       { long long c0 = clock64(); mbar_wait(&tmem_full[as], aphase); pf_wait += clock64() - c0; }
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + hf * 128;
-      const float *nys = ny_s + as * BN + hf * 128;
       const uint32_t colh = n0 + hf * 128;
+      // the accumulator holds -key / 2 (x.y - ||y||^2 / 2, or x.y for the inner product): key < tau  <=>  acc > -tau / 2
+      const float ntau = -0.5f * tau;
       long long pc0 = clock64();
 
       auto process = [&](const uint32_t(&v)[32], int c) {
         uint4 *dst = (uint4 *)sp;
 #pragma unroll
         for (int j = 0; j < 8; j++) dst[j] = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-        const float4 *ny4 = (const float4 *)(nys + c * 32);
         uint32_t hm = 0;
 #pragma unroll
-        for (int j = 0; j < 8; j++) {
-          const float4 y = ny4[j];
-          const float d0 = fmaf(-2.f, __uint_as_float(v[4 * j + 0]), y.x), d1 = fmaf(-2.f, __uint_as_float(v[4 * j + 1]), y.y);
-          const float d2 = fmaf(-2.f, __uint_as_float(v[4 * j + 2]), y.z), d3 = fmaf(-2.f, __uint_as_float(v[4 * j + 3]), y.w);
-          if (d0 < tau) hm |= 1u << (4 * j + 0);
-          if (d1 < tau) hm |= 1u << (4 * j + 1);
-          if (d2 < tau) hm |= 1u << (4 * j + 2);
-          if (d3 < tau) hm |= 1u << (4 * j + 3);
-        }
+        for (int j = 0; j < 32; j++)
+          if (__uint_as_float(v[j]) > ntau) hm |= 1u << j;
         if (__any_sync(0xffffffffu, hm != 0)) {
-          while (hm) {  // rare (~0.3 % of the elements): lanes diverge here
+          while (hm) {  // rare (~0.1 % of the elements): lanes diverge here
             const int j = __ffs(hm) - 1;
             hm &= hm - 1;
             const uint32_t col = colh + c * 32 + j;
-            if (col != self) {
-              const float d = fmaf(-2.f, sp[j], nys[c * 32 + j]);
+            if (col < p.n && col != self) {   // columns past the base are zero-filled tiles: acc = 0 may pass
+              const float d = -2.f * sp[j];
               const uint32_t pos = atomicAdd(&cnt_s[rowi], 1u);
               __stcg(cd + pos, d);
               __stcg(ci + pos, col);
@@ -774,6 +798,8 @@ uint32_t shortlist_size(const b200ann_handle *h, size_t k) {
 }  // namespace
 
 void knn_tc_free(b200ann_index *ix) {
+  if (ix->tc_ext) cudaFree(ix->tc_ext);
+  ix->tc_ext = nullptr;
   if (ix->tc_hi) cudaFree(ix->tc_hi);
   if (ix->tc_lo) cudaFree(ix->tc_lo);
   if (ix->tc_norms) cudaFree(ix->tc_norms);
@@ -803,6 +829,17 @@ int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t n
     ix->tc_hi = b.hi; ix->tc_lo = b.lo; ix->tc_norms = b.norms; ix->tc_dpad = dpad;
     ix->tc_inexact = b.inexact; ix->tc_ny_max = b.nmax;
   }
+  const uint32_t ext = ip ? 0u : 1u;
+  if (ext && !ix->tc_ext) {
+    CU_CHECK(h, cudaMalloc(&ix->tc_ext, n * 64 * 2));
+    tc::ext_b_kernel<<<(unsigned)((n * 8 + 255) / 256), 256, 0, h->stream>>>(ix->tc_norms, (uint32_t)n, (__nv_bfloat16 *)ix->tc_ext);
+    h->launches++;
+    CU_CHECK(h, cudaGetLastError());
+  }
+  DevBuf<__nv_bfloat16> a_ext;
+  CU_CHECK(h, a_ext.alloc(128 * 64, h->stream));
+  tc::ext_a_kernel<<<32, 256, 0, h->stream>>>(a_ext.p);
+  h->launches++;
   Bf16Set qs;
   // queries that are rows of the index itself (the whole base, or a block of rows of it: b200ann_knn_graph_rows) use
   // the cached bf16 copies
@@ -819,10 +856,10 @@ int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t n
   }
   const uint32_t passes = (ix->tc_inexact || qs.inexact) ? 3u : 1u;
   const uint32_t nkb = (uint32_t)(dpad / tc::BK);
-  const uint32_t a_res = nkb * (passes == 3 ? 2u : 1u) <= (uint32_t)tc::A_SLOTS ? 1u : 0u;
+  const uint32_t a_res = nkb * (passes == 3 ? 2u : 1u) + ext <= (uint32_t)tc::A_SLOTS ? 1u : 0u;
   uint32_t a_slots, nstage;
   if (a_res) {
-    a_slots = nkb * (passes == 3 ? 2u : 1u);
+    a_slots = nkb * (passes == 3 ? 2u : 1u) + ext;
     nstage = (tc::SMEM_MAX - 1024 - tc::SMEM_MISC - a_slots * tc::A_BYTES) / tc::B_BYTES;
   } else {
     nstage = (tc::SMEM_MAX - 1024 - tc::SMEM_MISC) / (tc::A_BYTES + tc::B_BYTES);
@@ -831,9 +868,12 @@ int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t n
   if (nstage > 6) nstage = 6;
   const int sweep_smem = 1024 + (int)(a_slots * tc::A_BYTES + nstage * tc::B_BYTES) + tc::SMEM_MISC;
 
-  CUtensorMap mA_hi, mA_lo, mB_hi, mB_lo;
+  CUtensorMap mA_hi, mA_lo, mB_hi, mB_lo, mA_ext, mB_ext;
+  // inner product: no norm block; the two maps are never used but must be valid kernel arguments
   if (!make_map(&mA_hi, qs.hi, nq, dpad, tc::BM) || !make_map(&mA_lo, qs.lo, nq, dpad, tc::BM) ||
-      !make_map(&mB_hi, ix->tc_hi, n, dpad, tc::BN) || !make_map(&mB_lo, ix->tc_lo, n, dpad, tc::BN))
+      !make_map(&mB_hi, ix->tc_hi, n, dpad, tc::BN) || !make_map(&mB_lo, ix->tc_lo, n, dpad, tc::BN) ||
+      !make_map(&mA_ext, a_ext.p, 128, 64, tc::BM) ||
+      !make_map(&mB_ext, ext ? ix->tc_ext : (void *)a_ext.p, ext ? n : 128, 64, ext ? tc::BN : tc::BM))
     return set_err(h, B200ANN_ERR_CUDA, "knn (tensor path): cuTensorMapEncodeTiled failed");
 
   // 2. geometry
@@ -894,7 +934,7 @@ int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t n
   const double keff = (double)dpad * passes;
   const float c_in = passes == 3 ? ldexpf(1.f, -16) : 0.f;
   const float c1 = 2.f * (c_in + (float)keff * ldexpf(1.f, -22));
-  const float c2 = (float)(dim + 8) * ldexpf(1.f, -23);
+  const float c2 = (float)(dim + 24) * ldexpf(1.f, -23);   // + the three norm terms added into the accumulator
   const float ny_max = ip ? ix->tc_ny_max : ix->tc_ny_max;
 
   DevBuf<unsigned long long> prof;
@@ -905,7 +945,7 @@ int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t n
     const uint32_t mtiles = (rows + tc::BM - 1) / tc::BM;
     tc::SweepParams sp = {};
     sp.nq_rows = rows; sp.q_row0 = (uint32_t)r0; sp.n = (uint32_t)n; sp.nkb = nkb; sp.passes = passes; sp.a_resident = a_res; sp.a_slots = a_slots; sp.nstage = nstage;
-    sp.ntiles = ntiles; sp.tiles_per_split = tiles_per_split; sp.ny = ip ? nullptr : ix->tc_norms;
+    sp.ntiles = ntiles; sp.tiles_per_split = tiles_per_split; sp.ext = ext;
     sp.exclude_self = exclude_self; sp.self_base = self_base; sp.Kp = Kp; sp.cap = cap; sp.rows_pad = rows_pad;
     sp.cand_d = cand_d.p; sp.cand_i = cand_i.p; sp.cand_n = cand_n.p; sp.cand_tau = cand_tau.p;
     sp.prof = want_prof ? prof.p : nullptr;
@@ -916,12 +956,12 @@ int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t n
       // +inf and appends ~3x fewer hits. A row for which it turns out too tight fails its proof and is recomputed.
       tc::SweepParams ss = sp;
       ss.tile_step = sample_step; ss.Kp = sample_m; ss.tiles_per_split = ntiles; ss.prof = nullptr;
-      tc::sweep_kernel<<<dim3(mtiles, 1), tc::NTHREADS, sweep_smem, h->stream>>>(mA_hi, mA_lo, mB_hi, mB_lo, ss);
+      tc::sweep_kernel<<<dim3(mtiles, 1), tc::NTHREADS, sweep_smem, h->stream>>>(mA_hi, mA_lo, mB_hi, mB_lo, mA_ext, mB_ext, ss);
       h->launches++;
       CU_CHECK(h, cudaMemcpyAsync(tau0.p, cand_tau.p, (size_t)rows_pad * sizeof(float), cudaMemcpyDeviceToDevice, h->stream));
       sp.tau0 = tau0.p;
     }
-    tc::sweep_kernel<<<dim3(mtiles, splits), tc::NTHREADS, sweep_smem, h->stream>>>(mA_hi, mA_lo, mB_hi, mB_lo, sp);
+    tc::sweep_kernel<<<dim3(mtiles, splits), tc::NTHREADS, sweep_smem, h->stream>>>(mA_hi, mA_lo, mB_hi, mB_lo, mA_ext, mB_ext, sp);
     h->launches++;
     CU_CHECK(h, cudaGetLastError());
     tc::FinParams fp = {};

@@ -70,7 +70,7 @@ struct b200ann_index {
   size_t hnsw_M = 0, hnsw_efc = 0;
   // tensor-core kNN cache (knn_tc.cu): bf16 hi/lo copies [n, tc_dpad], fp32 row norms
   void *tc_hi = nullptr, *tc_lo = nullptr;
-  void *tc_ext = nullptr;   // [n, 64] bf16: -||row||^2 / 2 as three bf16 terms in columns 0-2 (knn_tc.cu: the norm rides the contraction)
+  void *tc_ext = nullptr;   // [n, 16] bf16: -||row||^2 / 2 as three bf16 terms in columns 0-2 (knn_tc.cu: the norm rides the contraction)
   float *tc_norms = nullptr;
   size_t tc_dpad = 0;
   bool tc_inexact = false;

@@ -30,6 +30,7 @@ namespace tc {
 
 constexpr int BM = 128, BN = 256, BK = 64;          // tile rows (queries), tile columns (base rows), bf16 per K-block
 constexpr int A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2;  // 16 KB, 32 KB
+constexpr int A_EXT_BYTES = BM * 32, B_EXT_BYTES = BN * 32;  // the norm step's tiles: 4 KB, 8 KB
 constexpr int A_SLOTS = 5;                          // at most this many resident A K-blocks (80 KB): 128-d hi + lo + the norm block
 constexpr int NTHREADS = 320;                       // warp0 TMA, warp1 MMA, warps 2-9 epilogue
 constexpr int SMEM_MISC = 49152;                    // spill 36 KB, norms 2 KB, histograms 8 KB, row state 1 KB, barriers
@@ -104,6 +105,16 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t saddr) {
   d |= (uint64_t)2 << 61;                 // SWIZZLE_128B
   return d;
 }
+// K-major, 32B-swizzled operand tile of ONE K step (16 bf16 = 32 B per row): 8-row groups 256 B apart
+__device__ __forceinline__ uint64_t smem_desc32(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(256 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)6 << 61;                 // SWIZZLE_32B
+  return d;
+}
 // instruction descriptor: D=f32, A=B=bf16, both K-major, N=256, M=128
 constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
 
@@ -155,29 +166,28 @@ __global__ void prep_kernel(const float *src, size_t sstride, uint32_t n, uint32
   }
 }
 
-// The norm rides the contraction: one more K-block whose B rows hold -||y||^2 / 2 as three bf16 terms (columns 0-2;
+// The norm rides the contraction: one more K step (16 columns, a 32-byte row, 32B swizzle) whose B rows hold -||y||^2 / 2 as three bf16 terms (columns 0-2;
 // hi + mid + lo carry the 24 significant bits of the fp32 norm) and whose A rows hold 1.0 in those columns, so the
 // accumulator ends as  x.y - ||y||^2 / 2 = -key / 2  and the epilogue's filter is one compare per element.
-__global__ void ext_b_kernel(const float *norms, uint32_t n, __nv_bfloat16 *ext) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;   // one thread per (row, 8-column group)
-  if (i >= n * 8u) return;
-  const uint32_t row = i >> 3, g = i & 7u;
-  __nv_bfloat16 v[8];
+__global__ void ext_b_kernel(const float *norms, uint32_t n, __nv_bfloat16 *ext) {   // [n, 16]
+  const uint32_t row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= n) return;
+  __nv_bfloat16 v[16];
 #pragma unroll
-  for (int c = 0; c < 8; c++) v[c] = __float2bfloat16_rn(0.f);
-  if (g == 0) {
-    const float x = -0.5f * norms[row];
-    const __nv_bfloat16 h = __float2bfloat16_rn(x);
-    const float r1 = x - __bfloat162float(h);
-    const __nv_bfloat16 m = __float2bfloat16_rn(r1);
-    const float r2 = r1 - __bfloat162float(m);
-    v[0] = h; v[1] = m; v[2] = __float2bfloat16_rn(r2);
-  }
-  *reinterpret_cast<uint4 *>(ext + (size_t)row * 64 + g * 8) = *reinterpret_cast<const uint4 *>(v);
+  for (int c = 0; c < 16; c++) v[c] = __float2bfloat16_rn(0.f);
+  const float x = -0.5f * norms[row];
+  const __nv_bfloat16 h = __float2bfloat16_rn(x);
+  const float r1 = x - __bfloat162float(h);
+  const __nv_bfloat16 m = __float2bfloat16_rn(r1);
+  const float r2 = r1 - __bfloat162float(m);
+  v[0] = h; v[1] = m; v[2] = __float2bfloat16_rn(r2);
+  uint4 *dst = reinterpret_cast<uint4 *>(ext + (size_t)row * 16);
+  dst[0] = reinterpret_cast<const uint4 *>(v)[0];
+  dst[1] = reinterpret_cast<const uint4 *>(v)[1];
 }
-__global__ void ext_a_kernel(__nv_bfloat16 *ext) {   // [128, 64]
+__global__ void ext_a_kernel(__nv_bfloat16 *ext) {   // [128, 16]
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < 128u * 64u) ext[i] = __float2bfloat16_rn((i & 63u) < 3u ? 1.f : 0.f);
+  if (i < 128u * 16u) ext[i] = __float2bfloat16_rn((i & 15u) < 3u ? 1.f : 0.f);
 }
 
 // ---------------------------------------------------------------- sweep kernel
@@ -403,7 +413,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap mA_hi, const __grid_constant__ 
     // ===== TMA producer =====
     if (lane == 0) {
       if (p.a_resident) {
-        mbar_expect_tx(a_full, nA * A_BYTES);
+        mbar_expect_tx(a_full, (nA - p.ext) * A_BYTES + p.ext * A_EXT_BYTES);
         for (uint32_t b = 0; b < nA - p.ext; b++)
           tma_load_2d(sA + b * A_BYTES, b < p.nkb ? &mA_hi : &mA_lo, (int)((b % p.nkb) * BK), (int)m0, a_full);
         if (p.ext) tma_load_2d(sA + (nA - 1) * A_BYTES, &mA_ext, 0, 0, a_full);
@@ -414,7 +424,8 @@ sweep_kernel(const __grid_constant__ CUtensorMap mA_hi, const __grid_constant__ 
         for (uint32_t t = 0; t < T; t++) {
           const uint32_t seg = t / p.nkb, kb = t % p.nkb;
           mbar_wait_relaxed(&empty[stage], phase ^ 1u);
-          mbar_expect_tx(&full[stage], B_BYTES + (p.a_resident ? 0 : A_BYTES));
+          if (t < Tm) mbar_expect_tx(&full[stage], B_BYTES + (p.a_resident ? 0 : A_BYTES));
+          else mbar_expect_tx(&full[stage], B_EXT_BYTES + (p.a_resident ? 0 : A_EXT_BYTES));
           if (t < Tm) {
             tma_load_2d(sB + stage * B_BYTES, seg == 1 ? &mB_lo : &mB_hi, (int)(kb * BK), n0, &full[stage]);
             if (!p.a_resident)
@@ -448,7 +459,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap mA_hi, const __grid_constant__ 
             for (int k = 0; k < BK / 16; k++)
               tc_mma(d_tmem, smem_desc(a_addr + k * 32), smem_desc(b_addr + k * 32), IDESC, (t > 0 || k > 0) ? 1u : 0u);
           } else {
-            tc_mma(d_tmem, smem_desc(a_addr), smem_desc(b_addr), IDESC, 1u);   // the norm block: 3 of its first 16 columns
+            tc_mma(d_tmem, smem_desc32(a_addr), smem_desc32(b_addr), IDESC, 1u);   // the norm step
           }
           tc_commit(&empty[stage]);                   // frees the smem stage once these MMAs have read it
           if (t == T - 1) tc_commit(&tmem_full[as]);  // accumulator complete
@@ -517,14 +528,28 @@ sweep_kernel(const __grid_constant__ CUtensorMap mA_hi, const __grid_constant__ 
       long long pc0 = clock64();
 
       auto process = [&](const uint32_t(&v)[32], int c) {
-        uint4 *dst = (uint4 *)sp;
+        // the largest of every 8 elements against the threshold: 9 instructions per 8 elements; the elements of a
+        // group that passes (rare) are looked at one by one below
+        uint32_t gm = 0;
 #pragma unroll
-        for (int j = 0; j < 8; j++) dst[j] = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-        uint32_t hm = 0;
+        for (int g = 0; g < 4; g++) {
+          const float m01 = fmaxf(__uint_as_float(v[8 * g + 0]), __uint_as_float(v[8 * g + 1]));
+          const float m23 = fmaxf(__uint_as_float(v[8 * g + 2]), __uint_as_float(v[8 * g + 3]));
+          const float m45 = fmaxf(__uint_as_float(v[8 * g + 4]), __uint_as_float(v[8 * g + 5]));
+          const float m67 = fmaxf(__uint_as_float(v[8 * g + 6]), __uint_as_float(v[8 * g + 7]));
+          if (fmaxf(fmaxf(m01, m23), fmaxf(m45, m67)) > ntau) gm |= 1u << g;
+        }
+        if (__any_sync(0xffffffffu, gm != 0)) {
+          uint4 *dst = (uint4 *)sp;   // dynamic indexing below: through shared memory
 #pragma unroll
-        for (int j = 0; j < 32; j++)
-          if (__uint_as_float(v[j]) > ntau) hm |= 1u << j;
-        if (__any_sync(0xffffffffu, hm != 0)) {
+          for (int j = 0; j < 8; j++) dst[j] = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          uint32_t hm = 0;
+          while (gm) {
+            const int g = __ffs(gm) - 1;
+            gm &= gm - 1;
+            for (int e = 0; e < 8; e++)
+              if (sp[8 * g + e] > ntau) hm |= 1u << (8 * g + e);
+          }
           while (hm) {  // rare (~0.1 % of the elements): lanes diverge here
             const int j = __ffs(hm) - 1;
             hm &= hm - 1;
@@ -756,6 +781,18 @@ bool make_map(CUtensorMap *m, void *ptr, uint64_t rows, uint64_t dpad, uint32_t 
              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// bf16 [rows, 16] row-major (32 B rows), box = 16 x box_rows, 32B swizzle: the norm step's tiles
+bool make_map_ext(CUtensorMap *m, void *ptr, uint64_t rows, uint32_t box_rows) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return false;
+  cuuint64_t dims[2] = {16, rows};
+  cuuint64_t strides[1] = {32};
+  cuuint32_t box[2] = {16, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  return enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+             CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 struct Bf16Set {  // bf16 hi/lo + norms of a row set
   void *hi = nullptr, *lo = nullptr;
   float *norms = nullptr;
@@ -831,14 +868,14 @@ int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t n
   }
   const uint32_t ext = ip ? 0u : 1u;
   if (ext && !ix->tc_ext) {
-    CU_CHECK(h, cudaMalloc(&ix->tc_ext, n * 64 * 2));
-    tc::ext_b_kernel<<<(unsigned)((n * 8 + 255) / 256), 256, 0, h->stream>>>(ix->tc_norms, (uint32_t)n, (__nv_bfloat16 *)ix->tc_ext);
+    CU_CHECK(h, cudaMalloc(&ix->tc_ext, n * 16 * 2));
+    tc::ext_b_kernel<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(ix->tc_norms, (uint32_t)n, (__nv_bfloat16 *)ix->tc_ext);
     h->launches++;
     CU_CHECK(h, cudaGetLastError());
   }
   DevBuf<__nv_bfloat16> a_ext;
-  CU_CHECK(h, a_ext.alloc(128 * 64, h->stream));
-  tc::ext_a_kernel<<<32, 256, 0, h->stream>>>(a_ext.p);
+  CU_CHECK(h, a_ext.alloc(128 * 16, h->stream));
+  tc::ext_a_kernel<<<8, 256, 0, h->stream>>>(a_ext.p);
   h->launches++;
   Bf16Set qs;
   // queries that are rows of the index itself (the whole base, or a block of rows of it: b200ann_knn_graph_rows) use
@@ -872,8 +909,8 @@ int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t n
   // inner product: no norm block; the two maps are never used but must be valid kernel arguments
   if (!make_map(&mA_hi, qs.hi, nq, dpad, tc::BM) || !make_map(&mA_lo, qs.lo, nq, dpad, tc::BM) ||
       !make_map(&mB_hi, ix->tc_hi, n, dpad, tc::BN) || !make_map(&mB_lo, ix->tc_lo, n, dpad, tc::BN) ||
-      !make_map(&mA_ext, a_ext.p, 128, 64, tc::BM) ||
-      !make_map(&mB_ext, ext ? ix->tc_ext : (void *)a_ext.p, ext ? n : 128, 64, ext ? tc::BN : tc::BM))
+      !make_map_ext(&mA_ext, a_ext.p, 128, tc::BM) ||
+      !make_map_ext(&mB_ext, ext ? ix->tc_ext : (void *)a_ext.p, ext ? n : 128, ext ? tc::BN : tc::BM))
     return set_err(h, B200ANN_ERR_CUDA, "knn (tensor path): cuTensorMapEncodeTiled failed");
 
   // 2. geometry

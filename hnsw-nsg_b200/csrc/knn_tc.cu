@@ -9,9 +9,12 @@
 //                fp32 row norms, max norm.
 //   2. sweep     one CTA = 128 query rows x a range of 256-row base tiles. TMA (128B swizzle) stages the
 //                bf16 K-blocks, one thread issues tcgen05.mma (M128 N256 K16, fp32 accumulators in TMEM,
-//                two accumulator stages), four epilogue warps read TMEM (thread = query row), form the
-//                ranking key  ||y||^2 - 2 x.y  (L2) /  -2 x.y  (IP) and keep, per row, a SHORTLIST of the
-//                K' = K + slack smallest keys: threshold filter + warp-cooperative radix-select compaction.
+//                two accumulator stages). The base norm rides the contraction (one more 16-column K step:
+//                -||y||^2/2 as three bf16 terms against 1.0 columns), so the accumulator IS the ranking key
+//                ||y||^2 - 2 x.y  (L2) /  -2 x.y  (IP) times -1/2. Eight epilogue warps read TMEM (thread =
+//                query row, two warps per lane quarter split the columns) and keep, per row, a SHORTLIST of the
+//                K' = K + slack smallest keys: one compare per element + warp-cooperative radix-select
+//                compaction. The epilogue runs at the TMEM read pipe's 64 B/clk (2048 cycles per 128 KB tile).
 //                Inexact data uses three passes hi*hi + hi*lo + lo*hi (bf16x3, error ~2^-16).
 //   3. finalize  CTA per query row: fp32 distances of the shortlisted rows in the canonical sequential-fma
 //                order of bf_knn.cu, bitonic sort by (distance,id), top K out. PROOF of exactness per row:

@@ -208,3 +208,41 @@ def test_hnsw_build_survives_reverse_group_overflow(B, H, monkeypatch):
     G = ix.get_hnsw()
     deg = (G["links0"] != R.INVALID).sum(1)
     assert (deg[1:] > 0).all()             # every point got linked
+
+
+@pytest.mark.parametrize("kind,n,dim,M,ef", [
+    ("s", 6000, 24, 8, 100),     # integer-valued rows: exact distance ties at the pool's boundary
+    ("dup", 4000, 16, 6, 120),   # every vector stored twice: zero distances, equal (distance) pairs with different ids
+    ("u", 5000, 32, 12, 200),
+    ("u", 3000, 8, 16, 30),      # small pool: one 32-entry block
+])
+def test_one_pass_pool_merge_equals_sequential_insertion(B, H, monkeypatch, kind, n, dim, M, ef):
+    """Beam::merge_chunk (beam.cuh: a hop's candidates merged into the pool in one pass through the closed-form
+    acceptance rule) against the candidate-by-candidate loop it replaces (B200ANN_MERGE_MIN turns the merge off for
+    search launches): same labels, same distance bits, same number of evaluations, on data full of ties. The search
+    also equals the oracle's (hnswalg.h:342-436 searchBaseLayerST)."""
+    if kind == "u":
+        base = R.data_uniform(n, dim, 41)
+    elif kind == "s":
+        base = R.data_sift_like(n, dim, 41)
+    else:
+        half = R.data_sift_like(n // 2, dim, 41)
+        base = np.ascontiguousarray(np.concatenate([half, half]))
+    q = base[::7][:300].copy() if kind != "u" else R.data_uniform(300, dim, 42)
+    ix = B.Index(H, base, 0)
+    ix.hnsw_build(M, 60, seed=100)
+    H.set_search_kernel(1)                       # the Beam kernel for every ef (the v2 kernel has its own pool)
+    try:
+        lab1, d1, st1 = ix.hnsw_search(q, 10, ef, want_stats=True)
+        monkeypatch.setenv("B200ANN_MERGE_MIN", "100000")
+        lab0, d0, st0 = ix.hnsw_search(q, 10, ef, want_stats=True)
+        monkeypatch.delenv("B200ANN_MERGE_MIN")
+    finally:
+        H.set_search_kernel(0)
+    assert (lab1 == lab0).all() and (d1.view(np.uint32) == d0.view(np.uint32)).all()
+    assert (st1 == st0).all()                    # per query: distance evaluations, hops
+    G = ix.get_hnsw()
+    R.oracle().orc_set_gpu_team(B.dist_team(dim))
+    ol, od = R.orc_hnsw_search(base, G, q, 10, ef, R.L2_GPU)
+    assert (lab1 == ol).all()
+    ix.close()

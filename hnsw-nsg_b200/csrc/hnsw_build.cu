@@ -7,7 +7,7 @@
 //
 // The reference inserts one point at a time under per-node mutexes. Here points are inserted in batches
 // ("batch form", restated serially by oracle/oracle.c orc_hnsw_build variant 1 and compared link for link):
-//   schedule   batch = min(bmax, max(1, inserted / ratio)) consecutive rows; a row whose level exceeds the
+//   schedule   batch = min(bmax, max(1, inserted / ratio)) consecutive rows (ratio at most 8 below min(2048, n/16) rows); a row whose level exceeds the
 //              current top level is a batch of its own (it becomes the new entry point, :1262-1265).
 //   insert     one warp per new point, on the graph as it was BEFORE the batch: greedy descent to the point's
 //              level, then per level the ef_construction beam (beam.cuh, single-pool form) and the heuristic
@@ -607,11 +607,21 @@ static int hnsw_run_batches(b200ann_handle *h, b200ann_index *ix, size_t s0, con
   size_t max_group = (227 * 1024 / (WARPS * 4) - smem_words(32, round_up((uint32_t)maxM0, 32), 5) - 2 * maxM0) / 4 - maxM0 - 32;
   if (const char *e = getenv("B200ANN_HNSW_MAX_GROUP")) max_group = std::min<size_t>(max_group, (size_t)atol(e));  // tests
   size_t bcap = bmax;
+  // The first min(2048, n/16) rows go in batches of up to 1/8 of the graph instead of 1/ratio: they are a small share of any
+  // index worth building here and nearly all their links are rewritten by the rows that follow, while at 1/32 they
+  // are 160 of a 50k-row build's 290 latency-bound batches. Measured against the reference-built graph
+  // (scripts/hnsw_ratio_vs_ref.py, recall@10 at ef 10 - 100): still within 0.005 everywhere (worst -0.0037; 4096
+  // rows at 1/8 or 2048 rows at 1/4 are not: -0.0054, -0.0086); 50k rows 0.183 -> 0.136 s.
+  // An index of fewer than 32k rows takes n/16 rows instead (6000 x 32 uniform with 2048 early rows: -0.0055).
+  size_t early_rows = std::min<size_t>(2048, n / 16), early_ratio = 8;
+  if (const char *e = getenv("B200ANN_HNSW_EARLY")) { early_rows = (size_t)atol(e); if (const char *c = strchr(e, ',')) early_ratio = (size_t)atol(c + 1); }  // A/B runs
   while (s < n && rc == 0) {
     size_t e;
     if (level_of(s) > maxlevel) e = s + 1;
     else {
-      size_t b = std::min(std::min(bmax, bcap), std::max<size_t>(1, s / ratio));
+      size_t r_eff = ratio;
+      if (early_rows && s < early_rows) r_eff = std::min(ratio, early_ratio);
+      size_t b = std::min(std::min(bmax, bcap), std::max<size_t>(1, s / r_eff));
       e = std::min(n, s + b);
       for (size_t i = s + 1; i < e; i++)
         if (level_of(i) > maxlevel) { e = i; break; }

@@ -95,7 +95,7 @@ int b200ann_index_set_hnsw(b200ann_index_t ix, const uint32_t *links0, size_t ma
  * :225-305 searchBaseLayer, :443-483 getNeighborsByHeuristic2, :506-630 mutuallyConnectNewElement; driven like
  * hnswlib/tests/cpp/sift_1m.cpp:321-336). Levels are drawn exactly like the reference (:206-210, same generator
  * and seed); rows are inserted in batches (DESIGN.md "HNSW build"): ratio = rows already inserted per new row of a
- * batch (0 = 32), bmax = largest batch (0 = 16384). labels [n] (NULL = row number) are what addPoint's `label` is.
+ * batch (0 = 32; at most 8 for the first min(2048, n/16) rows), bmax = largest batch (0 = 16384). labels [n] (NULL = row number) are what addPoint's `label` is.
  * On success the index holds the HNSW graph (b200ann_hnsw_search, b200ann_index_get_hnsw, hybrid search).
  * info (optional, 8 x u64): {beam distance evaluations, expanded nodes, heuristic distance evaluations, batches,
  * upper rows, maxlevel, entry point, largest reverse-link group}. */

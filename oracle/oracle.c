@@ -2074,7 +2074,8 @@ static uint32_t hb_descend(hb_t *h, const float *q, uint32_t cur, int from, int 
  * rows = sum(levels), all padded with ORC_INVALID. ep_out/maxlevel_out.
  * variant 0: the reference statement for statement, one point at a time (pinned to the compiled reference).
  * variant 1: the CUDA path's batch form (csrc/hnsw_build.cu): points are inserted in batches of
- *   min(bmax, max(1, inserted/ratio)) (a point whose level exceeds the current top level is a batch of its own);
+ *   min(bmax, max(1, inserted/ratio)), ratio at most 8 while fewer than min(2048, n/16) rows are inserted (a point whose level
+ *   exceeds the current top level is a batch of its own);
  *   every point of a batch searches the graph as it was BEFORE the batch (single-pool beam) and selects its M
  *   links with the heuristic; then, per (neighbour, level), all new reverse links are merged at once: appended in
  *   ascending id if they fit in Mmax, else the heuristic runs over existing + new (the reference does the same
@@ -2089,6 +2090,8 @@ static int rev_cmp(const void *x, const void *y) {
 }
 EXPORT size_t orc_hnsw_batch_end(size_t s, size_t n, const int32_t *levels, int maxlevel, unsigned ratio, unsigned bmax) {
   if (s == 0 || levels[s] > maxlevel) return s + 1;
+  /* the first min(2048, n/16) rows: batches of up to 1/8 (hnsw_build.cu hnsw_run_batches) */
+  if (s < (n / 16 < 2048 ? n / 16 : 2048) && ratio > 8) ratio = 8;
   size_t b = s / ratio;
   if (b < 1) b = 1;
   if (b > bmax) b = bmax;

@@ -27,9 +27,9 @@ def main():
         truth, _ = rix.bf_knn(q, 10)
         efs = (10, 20, 50, 100)
         row = {"case": name, "n": n, "reference": [round(R.recall(rix.hnsw_search(q, 10, ef)[0].astype(np.uint32), truth), 4) for ef in efs]}
-        for ratio in (64, 32, 16, 8):
+        for ratio in [int(x) for x in os.environ.get("RATIOS", "64,32,16,8").split(",")]:
             gix = B.Index(H, base, metric)
-            gix.hnsw_build(M, efc, seed=100, ratio=ratio)
+            import time as _t; _t0 = _t.time(); gix.hnsw_build(M, efc, seed=100, ratio=ratio); row["build_s %d" % ratio] = round(_t.time() - _t0, 4)
             row["ratio %d" % ratio] = [round(R.recall(gix.hnsw_search(q, 10, ef)[0].astype(np.uint32), truth), 4) for ef in efs]
             gix.close()
         rix.close()

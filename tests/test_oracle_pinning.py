@@ -655,7 +655,7 @@ def test_hnsw_build_batch_form_quality_and_schedule():
     s, ml = 0, -1
     while s < n:
         e = R.oracle().orc_hnsw_batch_end(s, n, lv, ml, 32, 64)
-        assert s < e <= n and e - s <= max(1, min(64, s // 32))
+        assert s < e <= n and e - s <= max(1, min(64, s // (8 if s < min(2048, n // 16) else 32)))   # the first rows: 1/8
         assert all(lv[i] <= ml for i in range(s + 1, e))
         ml = max(ml, int(lv[s:e].max()))
         s = e

@@ -932,7 +932,10 @@ int launch_knn_tc(b200ann_handle *h, b200ann_index *ix, const float *q, size_t n
     for (uint32_t s = 1; s <= smax; s++) {
       uint32_t tps = (ntiles + s - 1) / s;
       double waves = ceil((double)mtiles0 * s / h->sm_count);
-      double t = waves * (tps + 2.0);  // +2: per-CTA start-up
+      // +2: per-CTA start-up; every further split also triples-in-kind the finalize work (it reranks splits x K'
+      // candidates per row: 0.155 us per row and split against 2.5 us per tile - measured: 49k rows x 1M, 3 splits
+      // 37.8 ms against 29.4 ms unsplit, where the wave count alone predicted a gain)
+      double t = waves * (tps + 2.0) + 0.062 * (double)rows0 * (s - 1);
       if (t < best * 0.98) { best = t; splits = s; }
     }
   }

@@ -246,3 +246,34 @@ def test_one_pass_pool_merge_equals_sequential_insertion(B, H, monkeypatch, kind
     ol, od = R.orc_hnsw_search(base, G, q, 10, ef, R.L2_GPU)
     assert (lab1 == ol).all()
     ix.close()
+
+
+def test_graphs_do_not_depend_on_the_visited_table(B, H, monkeypatch):
+    """The beam's visited set only saves re-evaluations (a forgotten id is evaluated again and is either in the pool
+    already or fails its threshold again; the Link candidate buffer drops duplicates): 16-bit tags or 32-bit ids,
+    2^11 or 2^8 words - same HNSW links, same NSG graph, only the evaluation counts move."""
+    n, dim = 6000, 32
+    base = R.data_uniform(n, dim, 77)
+    ix = B.Index(H, base, 0)
+    i0 = ix.hnsw_build(12, 120, seed=100)
+    G0 = ix.get_hnsw()
+    knn, _ = ix.bf_knn(base, 41)
+    knn = np.ascontiguousarray(knn[:, 1:].astype(np.uint32))
+    n0 = ix.nsg_build(knn, 30, 24, 200, seed=1)
+    N0 = ix.get_graph()
+    monkeypatch.setenv("B200ANN_HNSW_VIS16", "0")
+    monkeypatch.setenv("B200ANN_LINK_VIS16", "0")
+    monkeypatch.setenv("B200ANN_HNSW_HBITS", "8")
+    H.set_link_visited_bits(7)
+    try:
+        i1 = ix.hnsw_build(12, 120, seed=100)
+        G1 = ix.get_hnsw()
+        n1 = ix.nsg_build(knn, 30, 24, 200, seed=1)
+        N1 = ix.get_graph()
+    finally:
+        H.set_link_visited_bits(0)
+    assert (G0["links0"] == G1["links0"]).all() and (G0["upper_links"] == G1["upper_links"]).all()
+    assert np.array_equal(np.asarray(N0[0]), np.asarray(N1[0])) and N0[1:] == N1[1:]
+    assert i1["beam_evals"] > i0["beam_evals"] and n1["beam_evals"] > n0["beam_evals"]   # the small tables forget more
+    assert n1["ep"] == n0["ep"] and n1["width"] == n0["width"]
+    ix.close()
